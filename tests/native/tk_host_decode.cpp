@@ -1,0 +1,79 @@
+// Host build of the device-side record decoder (tk_number.cuh / tk_json.cuh).
+//
+// TEST INFRASTRUCTURE ONLY.  The production path runs these same functions
+// inside CUDA kernels; this translation unit compiles them with g++ so that the
+// grammar and the decimal->binary conversion can be differential-tested against
+// CPython (json.loads + float()) on a machine without a GPU
+// (tests/test_number_host.py).  Nothing in torchkafka_b200/ loads this library.
+#include <stdint.h>
+#include <string.h>
+#include "../../torchkafka_b200/csrc/tk_json.cuh"
+
+struct HostReader {
+    const uint8_t* p;
+    uint32_t end;
+    int operator()(uint32_t pos) const { return pos < end ? (int)p[pos] : -1; }
+};
+
+template <int KIND>
+static int decode(const uint8_t* buf, uint32_t len, int max_len, void* out, int* n_out) {
+    typedef typename tk_elem<KIND>::type T;
+    HostReader rd{buf, len};
+    uint32_t first = 0;
+    bool empty = false;
+    *n_out = 0;
+    int st = tk_json_prefix(rd, 0, &first, &empty);
+    if (st) return st;
+    int n = 0;
+    int prev_class = 0;
+    int worst = TK_OK;
+    for (uint32_t pos = 0; pos < len; ++pos) {
+        int cls = tk_is_numclass(buf[pos]) ? 1 : 0;
+        if (cls && !prev_class) {
+            T v;
+            st = tk_json_element<KIND>(rd, pos, &v);
+            if (st && !worst) worst = st;
+            if (n < max_len) ((T*)out)[n] = st ? (T)0 : v;
+            ++n;
+        }
+        prev_class = cls;
+    }
+    *n_out = n;
+    if (worst) return worst;
+    if (n > max_len) return TK_ERR_TOO_LONG;
+    return TK_OK;
+}
+
+extern "C" int tk_host_decode(const uint8_t* buf, uint32_t len, int kind, int max_len,
+                              void* out, int* n_out) {
+    switch (kind) {
+        case TK_F32: return decode<TK_F32>(buf, len, max_len, out, n_out);
+        case TK_F64: return decode<TK_F64>(buf, len, max_len, out, n_out);
+        case TK_I32: return decode<TK_I32>(buf, len, max_len, out, n_out);
+        case TK_I64: return decode<TK_I64>(buf, len, max_len, out, n_out);
+    }
+    return -1;
+}
+
+// Single decimal string -> double bits (status in return value), for bulk float tests.
+extern "C" int tk_host_strtod(const uint8_t* buf, uint32_t len, uint64_t* bits) {
+    HostReader rd{buf, len};
+    tk_token t = tk_scan_number(rd, 0);
+    if (t.err) return t.err;
+    if (t.end != len) return TK_ERR_SYNTAX;
+    double d;
+    int st = tk_token_to_f64(rd, t, &d);
+    if (st) return st;
+    memcpy(bits, &d, 8);
+    return TK_OK;
+}
+
+// Many newline-separated decimal strings at once (fast path for million-case tests).
+extern "C" int tk_host_strtod_many(const uint8_t* buf, const uint32_t* starts, uint32_t n,
+                                   uint64_t* bits, uint8_t* status) {
+    for (uint32_t i = 0; i < n; ++i) {
+        bits[i] = 0;
+        status[i] = (uint8_t)tk_host_strtod(buf + starts[i], starts[i + 1] - starts[i], &bits[i]);
+    }
+    return 0;
+}

@@ -1,0 +1,97 @@
+// tk_json.cuh -- record-level grammar of a flat JSON array of numbers, as the
+// reference's `json.loads(record.value)` accepts it (CPython Modules/_json.c:
+// `_parse_array_unicode`, json/decoder.py `JSONDecoder.decode`).
+//
+// The decode kernels validate a record *in parallel*: number-like runs are
+// located by character class, then the lane that owns run j checks
+//     number  ws*  ( ','  ws*  <start of a number-like run>  |  ']'  ws*  END )
+// and the lane that owns the record checks the prefix
+//     [BOM] ws* '[' ws* ( <start of a run> | ']' ws* END ).
+// By induction over j the checked ranges tile the whole record, so a record is
+// accepted iff a sequential scanner would accept it.  Host+device code (TK_HD).
+#pragma once
+#include "tk_number.cuh"
+
+// Prefix check.  On success *first is the position of the first number-like
+// run, or, for an empty array, *empty is set.
+template <class R>
+TK_HD int tk_json_prefix(const R& rd, uint32_t pos, uint32_t* first, bool* empty) {
+    *empty = false;
+    // json.loads(bytes) strips one UTF-8 BOM (json/__init__.py detect_encoding -> 'utf-8-sig')
+    if (rd(pos) == 0xEF && rd(pos + 1) == 0xBB && rd(pos + 2) == 0xBF) pos += 3;
+    while (tk_is_ws(rd(pos))) ++pos;
+    int c = rd(pos);
+    if (c != '[') {
+        // a bare scalar / object / string is valid JSON but not an array of numbers
+        if (c == '{' || c == '"' || tk_is_numclass(c)) return TK_ERR_UNSUPPORTED;
+        return TK_ERR_SYNTAX;
+    }
+    ++pos;
+    while (tk_is_ws(rd(pos))) ++pos;
+    c = rd(pos);
+    if (c == ']') {
+        ++pos;
+        while (tk_is_ws(rd(pos))) ++pos;
+        if (rd(pos) != -1) return TK_ERR_SYNTAX;      // "Extra data"
+        *empty = true;
+        return TK_OK;
+    }
+    if (c == '[' || c == '{' || c == '"') return TK_ERR_UNSUPPORTED;   // nesting / strings
+    if (!tk_is_numclass(c)) return TK_ERR_SYNTAX;
+    *first = pos;
+    return TK_OK;
+}
+
+// Separator check after a number that ended at `pos`.
+template <class R>
+TK_HD int tk_json_gap(const R& rd, uint32_t pos) {
+    while (tk_is_ws(rd(pos))) ++pos;
+    int c = rd(pos);
+    if (c == ',') {
+        ++pos;
+        while (tk_is_ws(rd(pos))) ++pos;
+        c = rd(pos);
+        if (tk_is_numclass(c)) return TK_OK;           // next run starts here; its lane validates it
+        if (c == '[' || c == '{' || c == '"') return TK_ERR_UNSUPPORTED;
+        return TK_ERR_SYNTAX;                          // "[1,]" , "[1,,2]" , "[1, "
+    }
+    if (c == ']') {
+        ++pos;
+        while (tk_is_ws(rd(pos))) ++pos;
+        return rd(pos) == -1 ? TK_OK : TK_ERR_SYNTAX;  // "Extra data"
+    }
+    return TK_ERR_SYNTAX;                              // "Expecting ',' delimiter"
+}
+
+// element kinds (tk_dtype_t in include/torchkafka_b200.h)
+enum { TK_F32 = 0, TK_F64 = 1, TK_I32 = 2, TK_I64 = 3 };
+
+template <int KIND> struct tk_elem;
+template <> struct tk_elem<TK_F32> { typedef float type; };
+template <> struct tk_elem<TK_F64> { typedef double type; };
+template <> struct tk_elem<TK_I32> { typedef int32_t type; };
+template <> struct tk_elem<TK_I64> { typedef int64_t type; };
+
+// Parse + validate the number-like run at `pos` and its trailing separator,
+// convert to the element type.  Returns a status code.
+template <int KIND, class R>
+TK_HD int tk_json_element(const R& rd, uint32_t pos, typename tk_elem<KIND>::type* out) {
+    tk_token t = tk_scan_number(rd, pos);
+    if (t.err) return t.err;
+    int st = tk_json_gap(rd, t.end);
+    if (st) return st;
+    if (KIND == TK_F32 || KIND == TK_F64) {
+        double d;
+        st = tk_token_to_f64(rd, t, &d);
+        if (st) return st;
+        // float32: decimal -> nearest double -> RNE to float (double rounding, as torch.tensor does)
+        *out = (typename tk_elem<KIND>::type)d;
+        return TK_OK;
+    } else {
+        int64_t v;
+        st = tk_token_to_i64(rd, t, KIND == TK_I32 ? 32 : 64, &v);
+        if (st) return st;
+        *out = (typename tk_elem<KIND>::type)v;
+        return TK_OK;
+    }
+}

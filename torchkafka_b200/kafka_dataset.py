@@ -1,0 +1,297 @@
+"""``KafkaDataset``: the drop-in dataset class.
+
+Public surface and behaviour follow the reference class
+(``/root/reference/src/kafka_dataset.py:31-247``; contract frozen in SURVEY.md
+§4.1 and §8b): same constructor, ``_process``, ``new_consumer``,
+``init_worker``, ``placeholder``, ``commit``, ``commit_worker``, ``close``, same
+exception types and messages, same log lines.
+
+What is new is *additive*: a subclass may set ``payload_schema`` (see
+``torchkafka_b200.schema``).  Such a dataset never calls ``_process``; records
+are polled in bulk, packed CSR-style into pinned memory, copied to the GPU on a
+side stream and decoded / filtered / collated / offset-reduced by the CUDA
+kernels behind the C-ABI in ``include/torchkafka_b200.h``.  There is no CPU
+fallback for a schema dataset: if the CUDA library or a GPU is missing, using it
+raises.
+
+Two things differ from the reference on purpose, both on the schema path only:
+
+* offsets are committed *explicitly* (``consumer.commit({tp: offset})``), never
+  as "the consumer's current position" (reference ``kafka_dataset.py:130``),
+  because the GPU path reads ahead of the batch it has delivered; the committed
+  values are exactly those the reference commits in single-process mode
+  (SURVEY.md §4.1-3/5);
+* a record outside its schema raises ``PayloadError`` (with partition/offset)
+  when the batch containing it is requested, instead of whatever
+  ``json.loads`` / ``torch.tensor`` would have raised inside ``_process``.
+"""
+from __future__ import annotations
+
+import logging
+import os
+import signal
+import sys
+
+import torch.multiprocessing as mp
+from torch.utils.data import IterableDataset, get_worker_info
+
+try:  # kafka-python is optional at import time: tests and benches inject a stub consumer
+    from kafka import KafkaConsumer as _KafkaConsumer
+    from kafka.errors import CommitFailedError as _CommitFailedError
+except Exception:  # pragma: no cover - depends on the environment
+    _KafkaConsumer = None
+
+    class _CommitFailedError(Exception):
+        """Placeholder used when kafka-python is not installed."""
+
+
+_logger = logging.getLogger(__name__)
+
+
+def _commit_signal():
+    # same platform table as the reference (kafka_dataset.py:50-55)
+    if sys.platform in {"linux", "linux2"}:
+        return signal.SIGUSR1
+    if sys.platform in {"darwin", "win32", "win64"}:
+        return signal.SIGINT
+    raise RuntimeError(f"Unsupported platform '{sys.platform}'.")
+
+
+def _commit_failed_types():
+    """Exception classes treated as 'commit failed' (logged, not raised)."""
+    kinds = [_CommitFailedError]
+    mod = sys.modules.get("kafka.errors")
+    cls = getattr(mod, "CommitFailedError", None) if mod is not None else None
+    if isinstance(cls, type) and cls not in kinds:
+        kinds.append(cls)
+    try:
+        from .testing.stub_kafka import CommitFailedError as stub_cls
+        if stub_cls not in kinds:
+            kinds.append(stub_cls)
+    except Exception:  # pragma: no cover
+        pass
+    return tuple(kinds)
+
+
+class KafkaDataset(IterableDataset):
+    """Stream samples from Kafka into a PyTorch ``DataLoader``.
+
+    Subclass it and override ``_process`` (reference behaviour), or declare a
+    ``payload_schema`` to take the GPU path.  Every positional / keyword
+    argument goes to the Kafka consumer; auto-commit is always disabled.
+    """
+
+    _COMMIT_SIGNAL = _commit_signal()
+
+    #: optional schema (``JsonArray`` / ``TokenList`` / ``RawBytes`` / ``ImageU8``)
+    payload_schema = None
+    #: GPU-path tuning knobs (bytes per staging slot, slots in flight, device index)
+    device_slot_bytes = 64 << 20
+    device_slots = 3
+    device_index = None
+    max_partitions = 64
+
+    def __init__(self, *args, **kwargs):
+        self._worker_id = None          # set by init_worker inside a DataLoader worker
+        self._commit_required = False   # raised by the signal handler, cleared after each commit
+        self._explicit_offsets = None   # {TopicPartition: OffsetAndMetadata} of the last device batch
+        self._pipeline = None
+        if kwargs.get("_is_placeholder", False):
+            self._consumer = None
+            return
+        if not args:
+            raise ValueError(
+                "No topic was provided. "
+                "Please use the placeholder() method "
+                "to create a dataset without consumer."
+            )
+        self._consumer = self.new_consumer(*args, **kwargs)
+
+    # ------------------------------------------------------------------ lifecycle
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:  # interpreter teardown
+            pass
+
+    def close(self):
+        """Close the consumer; offsets are NOT committed (reference :85-91)."""
+        pipe = getattr(self, "_pipeline", None)
+        if pipe is not None:
+            pipe.close()
+            self._pipeline = None
+        consumer = getattr(self, "_consumer", None)
+        if consumer is not None:
+            consumer.close(autocommit=False)
+        self._commit_required = False
+
+    # ------------------------------------------------------------------ commits
+    def commit(self, signum=None, stack=None):  # pylint: disable=unused-argument
+        """Commit offsets now (main process) or flag a commit (worker, via signal).
+
+        Reference ``kafka_dataset.py:93-118``: three-way behaviour kept as is.
+        """
+        if self._consumer is None:
+            raise RuntimeError("Consumer is not initialized.")
+        if self._worker_id is None:
+            self._commit_if_required(force=True)
+            return
+        if signum is None:
+            raise RuntimeError("Direct commit should not be used with multiprocessing.")
+        if signum != self._COMMIT_SIGNAL:
+            raise ValueError(f"Worker {self._worker_id} received a bad signal ({signum}).")
+        self._commit_required = True
+
+    def _commit_if_required(self, force: bool = False):
+        if not (force or self._commit_required):
+            return
+        in_worker = self._worker_id is not None
+        if in_worker:
+            _logger.info("Committing offsets on worker %d.", self._worker_id)
+        else:
+            _logger.debug("Committing offsets.")
+        try:
+            if self._explicit_offsets is not None:
+                # GPU path: exactly the records up to the delivered batch, never the read-ahead
+                self._consumer.commit(self._explicit_offsets)
+            else:
+                self._consumer.commit()
+        except _commit_failed_types():
+            if in_worker:
+                _logger.error("Commit failed on worker %d.", self._worker_id)
+            else:
+                _logger.error("Commit failed.")
+        else:
+            if in_worker:
+                _logger.debug("Committed offsets on worker %d.", self._worker_id)
+            else:
+                _logger.debug("Committed offsets.")
+        finally:
+            self._commit_required = False
+
+    # ------------------------------------------------------------------ iteration
+    def __iter__(self):
+        if self._consumer is None:
+            raise RuntimeError("Consumer is not initialized.")
+        if self.payload_schema is not None:
+            yield from self._iter_device_samples()
+            return
+        in_worker = self._worker_id is not None
+        if in_worker:
+            signal.signal(self._COMMIT_SIGNAL, self.commit)
+        process = self._process
+        for record in self._consumer:
+            sample = process(record)
+            if sample is not None:
+                yield sample
+            if in_worker:
+                # committing from inside the loop (not from the handler) is the
+                # reference's 1.1.0 deadlock fix (CHANGELOG.md:15-17)
+                self._commit_if_required()
+        if in_worker:
+            signal.signal(self._COMMIT_SIGNAL, signal.SIG_DFL)
+
+    def _process(self, record):
+        """Turn one Kafka record into a sample; return ``None`` to skip it."""
+        raise NotImplementedError()
+
+    # ------------------------------------------------------------------ GPU path
+    def _open_pipeline(self, batch_size, drop_last):
+        if self._worker_id is not None or get_worker_info() is not None:
+            raise RuntimeError(
+                "A dataset with a payload_schema runs on the GPU and cannot be used "
+                "inside DataLoader worker processes (num_workers must be 0)."
+            )
+        from .pipeline import IngestPipeline  # imports the CUDA library; fails loudly if missing
+        if self._pipeline is not None:
+            self._pipeline.close()
+        self._pipeline = IngestPipeline(
+            self._consumer, self.payload_schema, batch_size=batch_size, drop_last=drop_last,
+            slot_bytes=self.device_slot_bytes, n_slots=self.device_slots,
+            device=self.device_index, max_partitions=self.max_partitions,
+        )
+        return self._pipeline
+
+    def device_batches(self, batch_size: int, drop_last: bool = False):
+        """Yield batch-ready device tensors (schema datasets only).
+
+        After each yielded batch, ``commit()`` commits exactly the offsets the
+        reference would have committed after the same batch.
+        """
+        if self._consumer is None:
+            raise RuntimeError("Consumer is not initialized.")
+        if self.payload_schema is None:
+            raise RuntimeError("device_batches() needs a payload_schema.")
+        pipe = self._open_pipeline(int(batch_size), bool(drop_last))
+        try:
+            for batch, offsets in pipe:
+                self._explicit_offsets = offsets
+                yield batch
+        finally:
+            pipe.close()
+            if self._pipeline is pipe:
+                self._pipeline = None
+
+    def _iter_device_samples(self):
+        """Per-sample view of the GPU path, for a plain ``DataLoader(ds, batch_size=B)``.
+
+        Each sample is what the equivalent ``_process`` would have returned (moved
+        to the GPU); ``default_collate`` then stacks them.  Correct but slow:
+        ``auto_commit(dataloader)`` or ``device_batches()`` deliver whole batches.
+        """
+        from .schema import JsonArray
+        schema = self.payload_schema
+        for batch in self.device_batches(1, False):
+            if isinstance(schema, JsonArray) and schema.fixed_len is None:
+                n = int(batch.lengths[0])
+                yield batch[0][0, :n]
+            else:
+                yield batch[0]
+
+    # ------------------------------------------------------------------ factories
+    @classmethod
+    def new_consumer(cls, *args, **kwargs):
+        """Build the Kafka consumer (auto-commit forced off).  Override to inject
+        configuration or another consumer (reference :188-206, README.md:46-57)."""
+        if not args:
+            raise ValueError("Cannot create a consumer without topic.")
+        kwargs["enable_auto_commit"] = False
+        kwargs.pop("_is_placeholder", None)
+        if _KafkaConsumer is None:
+            consumer_cls = getattr(sys.modules.get("kafka"), "KafkaConsumer", None)
+            if consumer_cls is None:
+                raise ImportError(
+                    "kafka-python is not installed; install it or override "
+                    "new_consumer() to provide a consumer."
+                )
+            return consumer_cls(*args, **kwargs)
+        return _KafkaConsumer(*args, **kwargs)
+
+    @classmethod
+    def init_worker(cls, *args, **kwargs):
+        """``worker_init_fn`` factory: one consumer per DataLoader worker
+        (reference :208-233)."""
+
+        def func(worker_id):
+            info = get_worker_info()
+            if info is None:
+                raise RuntimeError(
+                    "Custom initialization should be used for multiprocessing only."
+                )
+            dataset = info.dataset
+            # pylint: disable=protected-access
+            dataset._consumer = cls.new_consumer(*args, **kwargs)
+            dataset._worker_id = worker_id
+
+        return func
+
+    @classmethod
+    def commit_worker(cls, worker: mp.Process):
+        """Ask a worker process to commit (reference :235-239)."""
+        os.kill(worker.pid, cls._COMMIT_SIGNAL)
+
+    @classmethod
+    def placeholder(cls):
+        """Dataset without a consumer, for the multi-worker DataLoader
+        (reference :241-247)."""
+        return cls(_is_placeholder=True)

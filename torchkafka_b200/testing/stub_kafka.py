@@ -1,0 +1,275 @@
+"""In-memory stand-in for the parts of kafka-python that torch-kafka touches.
+
+There is no broker (and no kafka-python wheel) on the build or GPU machines, so
+every config in BASELINE.json injects a stub consumer through the documented
+``new_consumer`` override (reference ``src/kafka_dataset.py:188-206``,
+``README.md:46-57``).  This module provides that stub.  It follows kafka-python's
+*documented* behaviour for the calls the dataset makes:
+
+* iterating the consumer yields ``ConsumerRecord`` objects and advances the
+  partition position to ``record.offset + 1``;
+* ``poll()`` returns ``{TopicPartition: [ConsumerRecord, ...]}`` and advances
+  positions the same way;
+* ``commit()`` with no argument commits the current position of every partition
+  that has one; ``commit(offsets)`` commits the given
+  ``{TopicPartition: OffsetAndMetadata}`` map;
+* ``close(autocommit=...)``.
+
+Besides that it offers one *additive* fast path, ``poll_packed()``, that hands a
+whole run of records out as four flat arrays (values, starts, partitions,
+offsets) without creating per-record Python objects.  That is the shape a
+C-level fetch-response parser would produce.
+
+``install()`` registers the stub as the ``kafka`` / ``kafka.errors`` modules so
+that the unmodified reference (which does ``from kafka import KafkaConsumer`` at
+import time, ``src/kafka_dataset.py:21-22``) can be imported by the golden
+fixture generator.
+"""
+from __future__ import annotations
+
+import collections
+import sys
+import threading
+import types
+from typing import Dict, Iterable, List, Optional, Sequence
+
+import numpy as np
+
+ConsumerRecord = collections.namedtuple(
+    "ConsumerRecord",
+    [
+        "topic", "partition", "offset", "timestamp", "timestamp_type", "key",
+        "value", "headers", "checksum", "serialized_key_size",
+        "serialized_value_size", "serialized_header_size",
+    ],
+)
+TopicPartition = collections.namedtuple("TopicPartition", ["topic", "partition"])
+OffsetAndMetadata = collections.namedtuple("OffsetAndMetadata", ["offset", "metadata"])
+
+# dtype of one packed record header: 16 bytes, matches tk_rec_t in
+# include/torchkafka_b200.h
+REC_DTYPE = np.dtype([("start", "<u4"), ("partition", "<i4"), ("offset", "<i8")])
+
+
+class CommitFailedError(Exception):
+    """Same name as kafka.errors.CommitFailedError (reference kafka_dataset.py:22)."""
+
+
+class PackedRecords:
+    """A run of records as flat arrays.
+
+    ``values`` is a uint8 array holding the record values back to back,
+    ``starts`` (uint32, n+1 entries) the CSR boundaries inside ``values``,
+    ``partitions`` (int32) and ``offsets`` (int64) the Kafka coordinates.
+    """
+
+    __slots__ = ("values", "starts", "partitions", "offsets")
+
+    def __init__(self, values, starts, partitions, offsets):
+        self.values = values
+        self.starts = starts
+        self.partitions = partitions
+        self.offsets = offsets
+
+    def __len__(self):
+        return len(self.partitions)
+
+    @property
+    def nbytes(self):
+        return int(self.starts[-1]) - int(self.starts[0]) if len(self.starts) else 0
+
+
+class RecordLog:
+    """An immutable, ordered log of records shared by stub consumers.
+
+    The order of the log *is* the consumption order.  Records are stored packed
+    (one byte buffer + arrays); ``ConsumerRecord`` objects are created lazily,
+    once, so that both the reference CPU path and the GPU path read the very
+    same bytes.
+    """
+
+    def __init__(self, values: Sequence[bytes], partitions: Sequence[int],
+                 offsets: Sequence[int], topic: str = "topic"):
+        n = len(values)
+        assert len(partitions) == n and len(offsets) == n
+        self.topic = topic
+        lens = np.fromiter((len(v) for v in values), dtype=np.int64, count=n)
+        starts = np.zeros(n + 1, dtype=np.int64)
+        np.cumsum(lens, out=starts[1:])
+        self.starts = starts
+        self.values = np.frombuffer(b"".join(values), dtype=np.uint8) if n else np.zeros(0, np.uint8)
+        self.partitions = np.asarray(partitions, dtype=np.int32)
+        self.offsets = np.asarray(offsets, dtype=np.int64)
+        self._byte_values = list(values)
+        self._records: Optional[List[ConsumerRecord]] = None
+
+    def __len__(self):
+        return len(self.partitions)
+
+    @property
+    def nbytes(self):
+        return int(self.starts[-1])
+
+    def records(self) -> List[ConsumerRecord]:
+        if self._records is None:
+            t = self.topic
+            self._records = [
+                ConsumerRecord(t, int(p), int(o), 0, 0, None, v, [], None, -1, len(v), -1)
+                for v, p, o in zip(self._byte_values, self.partitions, self.offsets)
+            ]
+        return self._records
+
+    def select_partitions(self, keep) -> "RecordLog":
+        """Sub-log holding only partitions for which ``keep(p)`` is true."""
+        idx = [i for i, p in enumerate(self.partitions) if keep(int(p))]
+        return RecordLog([self._byte_values[i] for i in idx],
+                         self.partitions[idx], self.offsets[idx], self.topic)
+
+
+class KafkaConsumer:
+    """Stub consumer over a :class:`RecordLog`.
+
+    Parameters mirror kafka-python: positional topics, keyword configuration.
+    Stub-only keywords: ``log`` (the RecordLog to serve), ``block_at_end`` (after
+    the last record, block forever instead of raising StopIteration — what a
+    real consumer with ``consumer_timeout_ms=inf`` does),
+    ``fail_commits`` (raise CommitFailedError from commit()).
+    """
+
+    def __init__(self, *topics, log: Optional[RecordLog] = None, block_at_end: bool = False,
+                 fail_commits: bool = False, **configs):
+        self.topics = topics
+        self.config = dict(configs)
+        self._log = log if log is not None else RecordLog([], [], [])
+        self._cursor = 0
+        self._block_at_end = block_at_end
+        self._fail_commits = fail_commits
+        self._positions: Dict[int, int] = {}
+        self.committed_log: List[Dict[int, int]] = []
+        self.closed = False
+        self.close_autocommit = None
+
+    # -- iteration (what the reference uses, kafka_dataset.py:156) -----------
+    def __iter__(self):
+        return self
+
+    def __next__(self):
+        if self._cursor >= len(self._log):
+            if self._block_at_end:
+                threading.Event().wait()
+            raise StopIteration
+        rec = self._log.records()[self._cursor]
+        self._cursor += 1
+        self._positions[rec.partition] = rec.offset + 1
+        return rec
+
+    # -- poll (kafka-python API; used by the GPU path) -----------------------
+    def poll(self, timeout_ms=0, max_records=None, update_offsets=True):
+        """Return the next records grouped per TopicPartition.
+
+        The flattening of the result (dict order, then list order) is always a
+        prefix of the log order, so a poll-driven reader sees records in exactly
+        the order the iterator would have produced them.
+        """
+        n = len(self._log)
+        if self._cursor >= n:
+            return {}
+        limit = n - self._cursor if max_records is None else min(max_records, n - self._cursor)
+        recs = self._log.records()
+        out: Dict[TopicPartition, List[ConsumerRecord]] = {}
+        last_p = None
+        i = self._cursor
+        end = self._cursor + limit
+        parts = self._log.partitions
+        while i < end:
+            p = int(parts[i])
+            if p != last_p:
+                tp = TopicPartition(self._log.topic, p)
+                if tp in out:
+                    break  # would re-open a partition: stop, keep order exact
+                out[tp] = []
+                last_p = p
+            out[tp].append(recs[i])
+            i += 1
+        if update_offsets:
+            for tp, lst in out.items():
+                self._positions[tp.partition] = lst[-1].offset + 1
+            self._cursor = i
+        return out
+
+    # -- packed fast path (additive) -----------------------------------------
+    def poll_packed(self, max_records: int, max_bytes: int) -> Optional[PackedRecords]:
+        """Next run of records as flat array views (no per-record objects).
+
+        Returns ``None`` when the log is exhausted.  Positions advance as in
+        ``poll``.  At least one record is returned even if it exceeds
+        ``max_bytes`` on its own (the caller sizes its slots for that).
+        """
+        n = len(self._log)
+        a = self._cursor
+        if a >= n:
+            return None
+        starts = self._log.starts
+        b = min(n, a + max_records)
+        # largest b with starts[b] - starts[a] <= max_bytes
+        hi = int(np.searchsorted(starts, starts[a] + max_bytes, side="right")) - 1
+        b = max(a + 1, min(b, hi))
+        parts = self._log.partitions[a:b]
+        offs = self._log.offsets[a:b]
+        self._cursor = b
+        # positions: last offset per partition in the run
+        rev_parts = parts[::-1]
+        uniq, first_rev = np.unique(rev_parts, return_index=True)
+        for p, j in zip(uniq, first_rev):
+            self._positions[int(p)] = int(offs[len(offs) - 1 - j]) + 1
+        base = starts[a]
+        return PackedRecords(self._log.values[base:starts[b]],
+                             (starts[a:b + 1] - base).astype(np.uint32),
+                             parts, offs)
+
+    # -- offsets -------------------------------------------------------------
+    def position(self, tp):
+        return self._positions.get(tp.partition)
+
+    def commit(self, offsets=None):
+        if self._fail_commits:
+            raise CommitFailedError("stub commit failure")
+        if offsets is None:
+            snap = dict(self._positions)
+        else:
+            snap = {tp.partition: om.offset for tp, om in offsets.items()}
+        self.committed_log.append(snap)
+
+    def committed(self, tp):
+        for snap in reversed(self.committed_log):
+            if tp.partition in snap:
+                return snap[tp.partition]
+        return None
+
+    def close(self, autocommit=True):
+        self.closed = True
+        self.close_autocommit = autocommit
+
+
+def install() -> types.ModuleType:
+    """Register this stub as ``kafka`` and ``kafka.errors`` in ``sys.modules``.
+
+    Needed only to import the unmodified reference package; the new package
+    never requires it.
+    """
+    mod = types.ModuleType("kafka")
+    mod.KafkaConsumer = KafkaConsumer
+    mod.TopicPartition = TopicPartition
+    mod.OffsetAndMetadata = OffsetAndMetadata
+    mod.ConsumerRecord = ConsumerRecord
+    err = types.ModuleType("kafka.errors")
+    err.CommitFailedError = CommitFailedError
+    structs = types.ModuleType("kafka.structs")
+    structs.TopicPartition = TopicPartition
+    structs.OffsetAndMetadata = OffsetAndMetadata
+    mod.errors = err
+    mod.structs = structs
+    sys.modules["kafka"] = mod
+    sys.modules["kafka.errors"] = err
+    sys.modules["kafka.structs"] = structs
+    return mod

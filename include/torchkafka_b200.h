@@ -1,0 +1,179 @@
+/* torchkafka_b200.h -- C ABI of the B200 ingest library (libtorchkafka_b200.so).
+ *
+ * The reference (Bendabir/torch-kafka) is pure Python and has no native boundary
+ * at all; its per-record hot path is
+ *
+ *     KafkaDataset.__iter__        src/kafka_dataset.py:147-171
+ *       _process(record)           src/kafka_dataset.py:173-186, bodies README.md:41-43,72-79
+ *       None-skip filter           src/kafka_dataset.py:161-162
+ *     DataLoader fetch + collate   torch/utils/data/_utils/fetch.py:27-45,
+ *                                  torch/utils/data/_utils/collate.py:246-275
+ *     auto_commit -> commit()      src/auto_commit.py:55-58, src/kafka_dataset.py:120-145
+ *
+ * Each entry point below names the reference lines it replaces.  All functions
+ * are plain C: POD arguments, raw host/device pointers, an int return code
+ * (0 = ok, negative = error, text via tk_last_error()).  No C++ exception and no
+ * torch type crosses this boundary; CUDA streams are passed as void*
+ * (cudaStream_t).  Output tensors are allocated by the caller (PyTorch) and
+ * passed as device pointers.
+ *
+ * Data layout of one staging slot (host pinned copy and device copy alike):
+ *     bytes[n_bytes]        record values back to back (CSR payload)
+ *     recs[n_records + 1]   tk_rec_t: byte offset of the value, partition, offset;
+ *                           recs[n_records].start == n_bytes closes the CSR
+ * Threading: one producer thread may fill/submit slots while one consumer thread
+ * waits/launches/fetches; a slot is owned by one side at a time.
+ */
+#ifndef TORCHKAFKA_B200_H
+#define TORCHKAFKA_B200_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define TK_ABI_VERSION 1
+
+typedef struct tk_ctx tk_ctx;
+
+/* One record header, 16 bytes.  (.partition, .offset) are the ConsumerRecord
+ * fields the reference reads implicitly through consumer.commit()
+ * (src/kafka_dataset.py:130); .start indexes into the slot's byte buffer. */
+typedef struct tk_rec {
+    uint32_t start;
+    int32_t  partition;   /* dense partition index, 0 <= partition < n_partitions */
+    int64_t  offset;
+} tk_rec_t;
+
+/* element kinds of JSON schemas */
+typedef enum { TK_DTYPE_F32 = 0, TK_DTYPE_F64 = 1, TK_DTYPE_I32 = 2, TK_DTYPE_I64 = 3 } tk_dtype_t;
+
+/* per-record status (what _process would have raised in the reference) */
+typedef enum {
+    TK_STATUS_OK = 0,
+    TK_STATUS_SYNTAX = 1,       /* json.JSONDecodeError */
+    TK_STATUS_OVERFLOW = 2,     /* torch.tensor overflow / OverflowError */
+    TK_STATUS_TOO_LONG = 3,     /* more than max_len elements */
+    TK_STATUS_UNSUPPORTED = 4,  /* valid JSON outside the numeric-array schema */
+    TK_STATUS_SIZE = 5,         /* raw record with the wrong byte count */
+    TK_STATUS_RAGGED = 6        /* fixed_len schema, other length (torch.stack raises) */
+} tk_status_t;
+
+/* Per-slot result header, written by the kernels, fetched with tk_slot_fetch_result. */
+typedef struct tk_result {
+    uint32_t n_records;          /* records in the slot */
+    uint32_t n_kept;             /* records that passed the filter (K2) */
+    uint32_t carry_in;           /* rows the open batch held before this slot */
+    uint32_t carry_out;          /* rows the open batch holds after this slot */
+    uint32_t n_closed;           /* batches completed by this slot */
+    uint32_t batch_size;
+    uint32_t n_errors;           /* records with status != OK */
+    uint32_t first_error_rec;    /* lowest such record index, 0xFFFFFFFF if none */
+    uint32_t first_error_status;
+    uint32_t reserved[7];
+} tk_result_t;
+
+/* One output plane (values / lengths / mask) of the tensor a slot writes into.
+ * The tensor holds batch_size "head" rows followed by one "body" row per kept
+ * record of the slot: kept record k lands in row batch_size + k; the rows of the
+ * batch left open by the previous slot are copied into the end of the head region
+ * (tk_carry_rows), so every batch is one contiguous row range.  See DESIGN.md
+ * "Output layout". */
+typedef struct tk_plane {
+    void*    base;
+    uint64_t row_bytes;
+} tk_plane_t;
+
+const char* tk_last_error(void);
+int tk_abi_version(void);
+
+/* ---- context, staging slots, H2D (K0; no reference counterpart: the reference
+ *      never leaves host memory) ------------------------------ */
+int tk_ctx_create(int device, uint64_t slot_bytes, uint32_t slot_records, int n_slots,
+                  uint32_t max_batches, uint32_t n_partitions, tk_ctx** out);
+int tk_ctx_destroy(tk_ctx* ctx);
+/* forget the open batch and all partition positions (new iteration of the dataset) */
+int tk_ctx_reset(tk_ctx* ctx, void* stream);
+int tk_slot_host_ptrs(tk_ctx* ctx, int slot, uint8_t** bytes, tk_rec_t** recs);
+int tk_slot_device_ptrs(tk_ctx* ctx, int slot, uint8_t** d_bytes, tk_rec_t** d_recs);
+/* async copy of the filled slot on the library's copy stream; returns at once */
+int tk_slot_submit(tk_ctx* ctx, int slot, uint32_t n_records, uint64_t n_bytes);
+/* declare a slot whose device copy was filled by other means (benchmarks: data already in HBM) */
+int tk_slot_assume_resident(tk_ctx* ctx, int slot, uint32_t n_records, uint64_t n_bytes);
+/* make `stream` wait until the slot's H2D copy has landed */
+int tk_slot_wait(tk_ctx* ctx, int slot, void* stream);
+/* pack helper: copy `n` values given as (pointer, length) pairs into the slot,
+ * multi-threaded, and fill recs[] (replaces the per-record Python loop of
+ * src/kafka_dataset.py:156 on the host side) */
+int tk_slot_pack(tk_ctx* ctx, int slot, uint32_t first_record, uint64_t first_byte,
+                 const uint8_t* const* values, const uint32_t* lengths,
+                 const int32_t* partitions, const int64_t* offsets, uint32_t n,
+                 int n_threads, uint64_t* bytes_after);
+int tk_h2d_peak_gbs(int device, uint64_t bytes, int iters, double* gbs_out);
+
+/* ---- K1a/K1b phase 1: element count per record + keep flag -----------------
+ * replaces `len(json.loads(record.value)) < min_size -> None`
+ * (README.md:74-77; src/kafka_dataset.py:161-162) */
+int tk_json_scan(tk_ctx* ctx, int slot, uint32_t max_len, uint32_t min_size, void* stream);
+/* raw payloads: every record is kept; wrong byte count -> TK_STATUS_SIZE */
+int tk_raw_scan(tk_ctx* ctx, int slot, uint64_t record_bytes, void* stream);
+
+/* ---- K2: stream compaction of the keep flags -> row of every kept record,
+ *      batch boundaries (a batch closes on its batch_size-th kept record)
+ * replaces `if data is not None: yield data` (src/kafka_dataset.py:161-162) and
+ * the batch_size loop of _IterableDatasetFetcher.fetch (fetch.py:33-38) */
+int tk_compact(tk_ctx* ctx, int slot, uint32_t batch_size, void* stream);
+
+/* ---- K4: per batch, per partition: max(offset)+1 over every record consumed up
+ *      to the record that closed the batch (segmented max + running max)
+ * replaces KafkaConsumer.commit() position bookkeeping reached from
+ * src/auto_commit.py:58 -> src/kafka_dataset.py:130 */
+int tk_commit_offsets(tk_ctx* ctx, int slot, void* stream);
+
+/* ---- K3 helper: move the rows of the still-open batch from the tensor of the
+ *      previous slot to the head region of the tensor of the current slot, so the
+ *      batch that straddles the two slots is contiguous.  Reads the row counts
+ *      from the previous slot's device-side result (no host round trip).
+ * replaces the list `data` that fetch.py:33-38 keeps filling across consumer polls */
+int tk_carry_rows(tk_ctx* ctx, int prev_slot, int n_planes, const tk_plane_t* prev,
+                  const tk_plane_t* cur, void* stream);
+
+/* ---- K1a/K1b phase 2 + K3: parse, convert, collate, pad, mask --------------
+ * replaces `torch.tensor(json.loads(record.value), dtype=...)` (README.md:74) and
+ * default_collate/torch.stack (collate.py:275) or the pad collate of SURVEY.md §8c.
+ * planes: [0] values (row = max_len elements), [1] lengths (int32, may be NULL
+ * pointers), [2] mask (bool[max_len], may be NULL pointers) */
+int tk_json_decode(tk_ctx* ctx, int slot, int dtype, uint32_t max_len, uint32_t fixed_len,
+                   const tk_plane_t* values, const tk_plane_t* lengths, const tk_plane_t* mask,
+                   void* stream);
+
+/* ---- K1c + K3: fixed-layout bytes -> rows (torch.frombuffer + torch.stack) -- */
+int tk_collate_raw(tk_ctx* ctx, int slot, uint64_t record_bytes, const tk_plane_t* out,
+                   void* stream);
+/* HWC uint8 -> normalised bfloat16 CHW:  bf16(((x / 255) - mean[c]) / std[c]) in
+ * float32 with IEEE division, the op order of SURVEY.md §8c */
+int tk_image_set_norm(tk_ctx* ctx, int channels, const float* mean, const float* std, void* stream);
+int tk_collate_image_u8_bf16_nchw(tk_ctx* ctx, int slot, uint32_t height, uint32_t width,
+                                  uint32_t channels, const tk_plane_t* out, void* stream);
+
+/* ---- results ---------------------------------------------------------------- */
+/* async D2H of the slot's result block; also marks the slot's device buffers free
+ * for the next tk_slot_submit once `stream` reaches this point */
+int tk_slot_fetch_result(tk_ctx* ctx, int slot, void* stream);
+/* block until the fetch finished, then expose the pinned copies:
+ *   batch_end[j]   index of the record that closed batch j (j < n_closed); entry
+ *                  n_closed describes the open batch (n_records - 1)
+ *   batch_lmax[j]  longest kept record of batch j (JSON schemas)
+ *   commit         int64 matrix, commit[p * pitch + j] = offset to commit for
+ *                  partition p after batch j, -1 if the partition was never seen */
+int tk_slot_result(tk_ctx* ctx, int slot, const tk_result_t** hdr, const uint32_t** batch_end,
+                   const uint32_t** batch_lmax, const int64_t** commit, uint32_t* commit_pitch);
+/* per-record scratch of the last run on this slot, copied to host (tests, error reports) */
+int tk_slot_debug_records(tk_ctx* ctx, int slot, int32_t* rec_len, int32_t* rec_status,
+                          int32_t* rec_kidx, uint32_t n);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* TORCHKAFKA_B200_H */

@@ -1,0 +1,113 @@
+"""ctypes binding of libtorchkafka_b200.so (C ABI: include/torchkafka_b200.h).
+
+The library is built in-tree by ``__graft_entry__.build()`` /
+``make -C torchkafka_b200/csrc``.  There is deliberately no fallback: if the
+shared object is missing or a call fails, an exception is raised.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libtorchkafka_b200.so")
+
+
+class NativeError(RuntimeError):
+    pass
+
+
+class TkRec(C.Structure):
+    _fields_ = [("start", C.c_uint32), ("partition", C.c_int32), ("offset", C.c_int64)]
+
+
+class TkResult(C.Structure):
+    _fields_ = [
+        ("n_records", C.c_uint32), ("n_kept", C.c_uint32), ("carry_in", C.c_uint32),
+        ("carry_out", C.c_uint32), ("n_closed", C.c_uint32), ("batch_size", C.c_uint32),
+        ("n_errors", C.c_uint32), ("first_error_rec", C.c_uint32),
+        ("first_error_status", C.c_uint32), ("reserved", C.c_uint32 * 7),
+    ]
+
+
+class TkPlane(C.Structure):
+    _fields_ = [("base", C.c_void_p), ("row_bytes", C.c_uint64)]
+
+
+STATUS_NAMES = {
+    0: "ok",
+    1: "not a JSON array of numbers (json.JSONDecodeError in the reference)",
+    2: "value does not fit the target dtype (overflow)",
+    3: "more elements than the schema's max_len",
+    4: "valid JSON outside the numeric-array schema (true/false/null, strings, nesting)",
+    5: "raw record has the wrong byte count",
+    6: "record length differs from the schema's fixed_len (torch.stack would raise)",
+}
+
+_p = C.POINTER
+_SIGNATURES = {
+    "tk_last_error": (C.c_char_p, []),
+    "tk_abi_version": (C.c_int, []),
+    "tk_ctx_create": (C.c_int, [C.c_int, C.c_uint64, C.c_uint32, C.c_int, C.c_uint32, C.c_uint32,
+                                _p(C.c_void_p)]),
+    "tk_ctx_destroy": (C.c_int, [C.c_void_p]),
+    "tk_ctx_reset": (C.c_int, [C.c_void_p, C.c_void_p]),
+    "tk_slot_host_ptrs": (C.c_int, [C.c_void_p, C.c_int, _p(C.c_void_p), _p(C.c_void_p)]),
+    "tk_slot_device_ptrs": (C.c_int, [C.c_void_p, C.c_int, _p(C.c_void_p), _p(C.c_void_p)]),
+    "tk_slot_submit": (C.c_int, [C.c_void_p, C.c_int, C.c_uint32, C.c_uint64]),
+    "tk_slot_assume_resident": (C.c_int, [C.c_void_p, C.c_int, C.c_uint32, C.c_uint64]),
+    "tk_slot_wait": (C.c_int, [C.c_void_p, C.c_int, C.c_void_p]),
+    "tk_slot_pack": (C.c_int, [C.c_void_p, C.c_int, C.c_uint32, C.c_uint64, C.c_void_p, C.c_void_p,
+                               C.c_void_p, C.c_void_p, C.c_uint32, C.c_int, _p(C.c_uint64)]),
+    "tk_h2d_peak_gbs": (C.c_int, [C.c_int, C.c_uint64, C.c_int, _p(C.c_double)]),
+    "tk_json_scan": (C.c_int, [C.c_void_p, C.c_int, C.c_uint32, C.c_uint32, C.c_void_p]),
+    "tk_raw_scan": (C.c_int, [C.c_void_p, C.c_int, C.c_uint64, C.c_void_p]),
+    "tk_compact": (C.c_int, [C.c_void_p, C.c_int, C.c_uint32, C.c_void_p]),
+    "tk_commit_offsets": (C.c_int, [C.c_void_p, C.c_int, C.c_void_p]),
+    "tk_carry_rows": (C.c_int, [C.c_void_p, C.c_int, C.c_int, _p(TkPlane), _p(TkPlane), C.c_void_p]),
+    "tk_json_decode": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_uint32, C.c_uint32, _p(TkPlane),
+                                 _p(TkPlane), _p(TkPlane), C.c_void_p]),
+    "tk_collate_raw": (C.c_int, [C.c_void_p, C.c_int, C.c_uint64, _p(TkPlane), C.c_void_p]),
+    "tk_image_set_norm": (C.c_int, [C.c_void_p, C.c_int, _p(C.c_float), _p(C.c_float), C.c_void_p]),
+    "tk_collate_image_u8_bf16_nchw": (C.c_int, [C.c_void_p, C.c_int, C.c_uint32, C.c_uint32, C.c_uint32,
+                                                _p(TkPlane), C.c_void_p]),
+    "tk_slot_fetch_result": (C.c_int, [C.c_void_p, C.c_int, C.c_void_p]),
+    "tk_slot_result": (C.c_int, [C.c_void_p, C.c_int, _p(_p(TkResult)), _p(_p(C.c_uint32)),
+                                 _p(_p(C.c_uint32)), _p(_p(C.c_int64)), _p(C.c_uint32)]),
+    "tk_slot_debug_records": (C.c_int, [C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p,
+                                        C.c_uint32]),
+}
+
+_lib = None
+
+
+def exported_symbols():
+    """Names every build of the library must export (checked by the CPU test suite)."""
+    return sorted(_SIGNATURES)
+
+
+def load():
+    """Load the shared library (once).  Raises if it has not been built."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        raise NativeError(
+            f"{LIB_PATH} is missing: build it with `python -c 'import __graft_entry__ as g; g.build()'` "
+            "or `make -C torchkafka_b200/csrc`.  There is no CPU fallback for schema datasets."
+        )
+    lib = C.CDLL(LIB_PATH)
+    for name, (restype, argtypes) in _SIGNATURES.items():
+        fn = getattr(lib, name)          # AttributeError if a symbol is missing
+        fn.restype = restype
+        fn.argtypes = argtypes
+    if lib.tk_abi_version() != 1:
+        raise NativeError("libtorchkafka_b200.so has an unexpected ABI version")
+    _lib = lib
+    return lib
+
+
+def check(rc: int):
+    if rc != 0:
+        msg = load().tk_last_error()
+        raise NativeError(msg.decode("utf-8", "replace") if msg else f"native call failed ({rc})")

@@ -1,0 +1,305 @@
+// tk_ctx.cu -- context, staging slots, H2D submission (K0), result fetch.
+//
+// No reference counterpart: the reference never leaves host memory
+// (SURVEY.md §2.2, K0).  A slot is a CSR-packed run of polled records in pinned
+// host memory with a device twin; tk_slot_submit() copies it on the library's own
+// copy stream so the transfer overlaps the kernels working on the previous slot.
+#include <stdarg.h>
+#include <string.h>
+#include <new>
+#include <thread>
+#include <vector>
+#include "tk_internal.h"
+
+static thread_local char g_err[1024] = "";
+
+void tk_set_error(const char* fmt, ...) {
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(g_err, sizeof(g_err), fmt, ap);
+    va_end(ap);
+}
+
+extern "C" const char* tk_last_error(void) { return g_err; }
+extern "C" int tk_abi_version(void) { return TK_ABI_VERSION; }
+
+__global__ void tk_fill_i64(int64_t* p, int64_t v, uint32_t n) {
+    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) p[i] = v;
+}
+
+static void free_slot(tk_slot& s) {
+    if (s.h_bytes) cudaFreeHost(s.h_bytes);
+    if (s.h_recs) cudaFreeHost(s.h_recs);
+    if (s.h_result) cudaFreeHost(s.h_result);
+    if (s.h_batch_end) cudaFreeHost(s.h_batch_end);
+    if (s.h_batch_lmax) cudaFreeHost(s.h_batch_lmax);
+    if (s.h_commit) cudaFreeHost(s.h_commit);
+    cudaFree(s.d.bytes); cudaFree(s.d.recs); cudaFree(s.d.rec_len); cudaFree(s.d.rec_status);
+    cudaFree(s.d.rec_kidx); cudaFree(s.d.blk_sum); cudaFree(s.d.result); cudaFree(s.d.batch_end);
+    cudaFree(s.d.batch_lmax); cudaFree(s.d.commit);
+    if (s.ev_h2d) cudaEventDestroy(s.ev_h2d);
+    if (s.ev_free) cudaEventDestroy(s.ev_free);
+    if (s.ev_result) cudaEventDestroy(s.ev_result);
+}
+
+extern "C" int tk_ctx_destroy(tk_ctx* ctx) {
+    if (!ctx) return 0;
+    cudaSetDevice(ctx->device);
+    cudaDeviceSynchronize();
+    if (ctx->slots) {
+        for (int i = 0; i < ctx->n_slots; ++i) free_slot(ctx->slots[i]);
+        delete[] ctx->slots;
+    }
+    cudaFree(ctx->d_state);
+    cudaFree(ctx->d_positions);
+    cudaFree(ctx->d_image_lut);
+    if (ctx->copy_stream) cudaStreamDestroy(ctx->copy_stream);
+    delete ctx;
+    return 0;
+}
+
+static int create_impl(tk_ctx* ctx) {
+    TK_CUDA(cudaSetDevice(ctx->device));
+    TK_CUDA(cudaStreamCreateWithFlags(&ctx->copy_stream, cudaStreamNonBlocking));
+    TK_CUDA(cudaMalloc(&ctx->d_state, sizeof(tk_state)));
+    TK_CUDA(cudaMalloc(&ctx->d_positions, sizeof(int64_t) * ctx->n_partitions));
+    TK_CUDA(cudaMalloc(&ctx->d_image_lut, sizeof(uint16_t) * 4 * 256));
+    TK_CUDA(cudaMemset(ctx->d_image_lut, 0, sizeof(uint16_t) * 4 * 256));
+    ctx->slots = new (std::nothrow) tk_slot[ctx->n_slots];
+    TK_REQUIRE(ctx->slots, "out of host memory");
+    memset(ctx->slots, 0, sizeof(tk_slot) * ctx->n_slots);
+    const size_t nrec = ctx->slot_records;
+    const size_t nb = ctx->max_batches + 1;
+    const size_t commit_elems = (size_t)ctx->n_partitions * ctx->commit_pitch;
+    const size_t nblk = (nrec + 1023) / 1024 + 1;
+    for (int i = 0; i < ctx->n_slots; ++i) {
+        tk_slot& s = ctx->slots[i];
+        TK_CUDA(cudaHostAlloc(&s.h_bytes, ctx->slot_bytes + TK_BYTES_PAD, cudaHostAllocDefault));
+        TK_CUDA(cudaHostAlloc(&s.h_recs, sizeof(tk_rec_t) * (nrec + 1), cudaHostAllocDefault));
+        TK_CUDA(cudaHostAlloc(&s.h_result, sizeof(tk_result_t), cudaHostAllocDefault));
+        TK_CUDA(cudaHostAlloc(&s.h_batch_end, sizeof(uint32_t) * nb, cudaHostAllocDefault));
+        TK_CUDA(cudaHostAlloc(&s.h_batch_lmax, sizeof(uint32_t) * nb, cudaHostAllocDefault));
+        TK_CUDA(cudaHostAlloc(&s.h_commit, sizeof(int64_t) * commit_elems, cudaHostAllocDefault));
+        TK_CUDA(cudaMalloc(&s.d.bytes, ctx->slot_bytes + TK_BYTES_PAD));
+        TK_CUDA(cudaMemset(s.d.bytes, 0, ctx->slot_bytes + TK_BYTES_PAD));
+        TK_CUDA(cudaMalloc(&s.d.recs, sizeof(tk_rec_t) * (nrec + 1)));
+        TK_CUDA(cudaMalloc(&s.d.rec_len, sizeof(int32_t) * nrec));
+        TK_CUDA(cudaMalloc(&s.d.rec_status, sizeof(int32_t) * nrec));
+        TK_CUDA(cudaMalloc(&s.d.rec_kidx, sizeof(int32_t) * nrec));
+        TK_CUDA(cudaMalloc(&s.d.blk_sum, sizeof(uint32_t) * nblk));
+        TK_CUDA(cudaMalloc(&s.d.result, sizeof(tk_result_t)));
+        TK_CUDA(cudaMalloc(&s.d.batch_end, sizeof(uint32_t) * nb));
+        TK_CUDA(cudaMalloc(&s.d.batch_lmax, sizeof(uint32_t) * nb));
+        TK_CUDA(cudaMalloc(&s.d.commit, sizeof(int64_t) * commit_elems));
+        TK_CUDA(cudaEventCreateWithFlags(&s.ev_h2d, cudaEventDisableTiming));
+        TK_CUDA(cudaEventCreateWithFlags(&s.ev_free, cudaEventDisableTiming));
+        TK_CUDA(cudaEventCreateWithFlags(&s.ev_result, cudaEventDisableTiming));
+    }
+    return tk_ctx_reset(ctx, nullptr);
+}
+
+extern "C" int tk_ctx_create(int device, uint64_t slot_bytes, uint32_t slot_records, int n_slots,
+                             uint32_t max_batches, uint32_t n_partitions, tk_ctx** out) {
+    TK_REQUIRE(out, "out is null");
+    *out = nullptr;
+    TK_REQUIRE(slot_bytes > 0 && slot_bytes < (1ull << 32) - TK_BYTES_PAD,
+               "slot_bytes must be in (0, 4 GiB): CSR offsets are 32-bit");
+    TK_REQUIRE(slot_records > 0 && n_slots > 0 && n_slots <= 64 && max_batches > 0 && n_partitions > 0,
+               "bad context geometry");
+    tk_ctx* ctx = new (std::nothrow) tk_ctx;
+    TK_REQUIRE(ctx, "out of host memory");
+    memset(ctx, 0, sizeof(*ctx));
+    ctx->device = device;
+    ctx->slot_bytes = slot_bytes;
+    ctx->slot_records = slot_records;
+    ctx->n_slots = n_slots;
+    ctx->max_batches = max_batches;
+    ctx->commit_pitch = (max_batches + 1 + 3) & ~3u;
+    ctx->n_partitions = n_partitions;
+    int rc = create_impl(ctx);
+    if (rc) { char keep[1024]; strncpy(keep, g_err, sizeof(keep)); keep[1023] = 0; tk_ctx_destroy(ctx); tk_set_error("%s", keep); return rc; }
+    *out = ctx;
+    return 0;
+}
+
+extern "C" int tk_ctx_reset(tk_ctx* ctx, void* stream) {
+    TK_REQUIRE(ctx, "null context");
+    TK_CUDA(cudaSetDevice(ctx->device));
+    cudaStream_t st = (cudaStream_t)stream;
+    TK_CUDA(cudaMemsetAsync(ctx->d_state, 0, sizeof(tk_state), st));
+    tk_fill_i64<<<(ctx->n_partitions + 255) / 256, 256, 0, st>>>(ctx->d_positions, -1, ctx->n_partitions);
+    TK_LAUNCH_CHECK();
+    TK_CUDA(cudaStreamSynchronize(st));
+    return 0;
+}
+
+extern "C" int tk_slot_host_ptrs(tk_ctx* ctx, int slot, uint8_t** bytes, tk_rec_t** recs) {
+    int rc = tk_check_slot(ctx, slot); if (rc) return rc;
+    if (bytes) *bytes = ctx->slots[slot].h_bytes;
+    if (recs) *recs = ctx->slots[slot].h_recs;
+    return 0;
+}
+
+extern "C" int tk_slot_device_ptrs(tk_ctx* ctx, int slot, uint8_t** d_bytes, tk_rec_t** d_recs) {
+    int rc = tk_check_slot(ctx, slot); if (rc) return rc;
+    if (d_bytes) *d_bytes = ctx->slots[slot].d.bytes;
+    if (d_recs) *d_recs = ctx->slots[slot].d.recs;
+    return 0;
+}
+
+static int check_fill(tk_ctx* ctx, uint32_t n_records, uint64_t n_bytes) {
+    TK_REQUIRE(n_records <= ctx->slot_records, "slot holds %u records, %u submitted", ctx->slot_records, n_records);
+    TK_REQUIRE(n_bytes <= ctx->slot_bytes, "slot holds %llu bytes, %llu submitted",
+               (unsigned long long)ctx->slot_bytes, (unsigned long long)n_bytes);
+    return 0;
+}
+
+extern "C" int tk_slot_submit(tk_ctx* ctx, int slot, uint32_t n_records, uint64_t n_bytes) {
+    TK_ENTER(ctx, slot);
+    int rc = check_fill(ctx, n_records, n_bytes); if (rc) return rc;
+    tk_slot& s = ctx->slots[slot];
+    TK_REQUIRE(s.h_recs[n_records].start == n_bytes, "recs[n_records].start (%u) must equal n_bytes (%llu)",
+               s.h_recs[n_records].start, (unsigned long long)n_bytes);
+    s.n_records = n_records;
+    s.n_bytes = n_bytes;
+    // the device twin may still be read by kernels of the slot's previous round
+    if (s.free_recorded) TK_CUDA(cudaStreamWaitEvent(ctx->copy_stream, s.ev_free, 0));
+    if (n_bytes) TK_CUDA(cudaMemcpyAsync(s.d.bytes, s.h_bytes, n_bytes, cudaMemcpyHostToDevice, ctx->copy_stream));
+    TK_CUDA(cudaMemcpyAsync(s.d.recs, s.h_recs, sizeof(tk_rec_t) * ((size_t)n_records + 1),
+                            cudaMemcpyHostToDevice, ctx->copy_stream));
+    TK_CUDA(cudaEventRecord(s.ev_h2d, ctx->copy_stream));
+    return 0;
+}
+
+extern "C" int tk_slot_assume_resident(tk_ctx* ctx, int slot, uint32_t n_records, uint64_t n_bytes) {
+    TK_ENTER(ctx, slot);
+    int rc = check_fill(ctx, n_records, n_bytes); if (rc) return rc;
+    tk_slot& s = ctx->slots[slot];
+    s.n_records = n_records;
+    s.n_bytes = n_bytes;
+    TK_CUDA(cudaEventRecord(s.ev_h2d, ctx->copy_stream));
+    return 0;
+}
+
+extern "C" int tk_slot_wait(tk_ctx* ctx, int slot, void* stream) {
+    TK_ENTER(ctx, slot);
+    TK_CUDA(cudaStreamWaitEvent((cudaStream_t)stream, ctx->slots[slot].ev_h2d, 0));
+    return 0;
+}
+
+extern "C" int tk_slot_pack(tk_ctx* ctx, int slot, uint32_t first_record, uint64_t first_byte,
+                            const uint8_t* const* values, const uint32_t* lengths,
+                            const int32_t* partitions, const int64_t* offsets, uint32_t n,
+                            int n_threads, uint64_t* bytes_after) {
+    int rc = tk_check_slot(ctx, slot); if (rc) return rc;
+    tk_slot& s = ctx->slots[slot];
+    TK_REQUIRE((uint64_t)first_record + n <= ctx->slot_records, "pack: record capacity exceeded");
+    // pass 1: headers + total size (serial, 16 bytes per record)
+    uint64_t pos = first_byte;
+    for (uint32_t i = 0; i < n; ++i) {
+        tk_rec_t& r = s.h_recs[first_record + i];
+        r.start = (uint32_t)pos;
+        r.partition = partitions[i];
+        r.offset = offsets[i];
+        pos += lengths[i];
+    }
+    TK_REQUIRE(pos <= ctx->slot_bytes, "pack: byte capacity exceeded");
+    s.h_recs[first_record + n].start = (uint32_t)pos;
+    s.h_recs[first_record + n].partition = 0;
+    s.h_recs[first_record + n].offset = 0;
+    // pass 2: payload copies, split by record ranges of similar byte volume
+    const uint64_t total = pos - first_byte;
+    if (n_threads < 1) n_threads = 1;
+    if (n_threads > 64) n_threads = 64;
+    if (total < (1u << 20) || n_threads == 1) {
+        for (uint32_t i = 0; i < n; ++i) memcpy(s.h_bytes + s.h_recs[first_record + i].start, values[i], lengths[i]);
+    } else {
+        std::vector<std::thread> pool;
+        uint32_t a = 0;
+        for (int t = 0; t < n_threads; ++t) {
+            const uint64_t want = first_byte + total * (uint64_t)(t + 1) / n_threads;
+            uint32_t b = a;
+            while (b < n && s.h_recs[first_record + b].start < want) ++b;
+            if (t == n_threads - 1) b = n;
+            if (b > a) {
+                pool.emplace_back([&s, values, lengths, first_record, a, b]() {
+                    for (uint32_t i = a; i < b; ++i)
+                        memcpy(s.h_bytes + s.h_recs[first_record + i].start, values[i], lengths[i]);
+                });
+            }
+            a = b;
+        }
+        for (auto& th : pool) th.join();
+    }
+    if (bytes_after) *bytes_after = pos;
+    return 0;
+}
+
+extern "C" int tk_h2d_peak_gbs(int device, uint64_t bytes, int iters, double* gbs_out) {
+    TK_REQUIRE(gbs_out && bytes > 0 && iters > 0, "bad arguments");
+    TK_CUDA(cudaSetDevice(device));
+    void *h = nullptr, *d = nullptr;
+    cudaStream_t st;
+    cudaEvent_t e0, e1;
+    TK_CUDA(cudaHostAlloc(&h, bytes, cudaHostAllocDefault));
+    memset(h, 1, bytes);
+    TK_CUDA(cudaMalloc(&d, bytes));
+    TK_CUDA(cudaStreamCreateWithFlags(&st, cudaStreamNonBlocking));
+    TK_CUDA(cudaEventCreate(&e0));
+    TK_CUDA(cudaEventCreate(&e1));
+    double best = 0.0;
+    for (int i = 0; i < iters + 1; ++i) {
+        TK_CUDA(cudaEventRecord(e0, st));
+        TK_CUDA(cudaMemcpyAsync(d, h, bytes, cudaMemcpyHostToDevice, st));
+        TK_CUDA(cudaEventRecord(e1, st));
+        TK_CUDA(cudaEventSynchronize(e1));
+        float ms = 0.f;
+        TK_CUDA(cudaEventElapsedTime(&ms, e0, e1));
+        if (i > 0 && ms > 0.f) { double g = (double)bytes / (ms * 1e6); if (g > best) best = g; }
+    }
+    cudaEventDestroy(e0); cudaEventDestroy(e1); cudaStreamDestroy(st); cudaFree(d); cudaFreeHost(h);
+    *gbs_out = best;
+    return 0;
+}
+
+extern "C" int tk_slot_fetch_result(tk_ctx* ctx, int slot, void* stream) {
+    TK_ENTER(ctx, slot);
+    tk_slot& s = ctx->slots[slot];
+    cudaStream_t st = (cudaStream_t)stream;
+    const size_t nb = ctx->max_batches + 1;
+    TK_CUDA(cudaMemcpyAsync(s.h_result, s.d.result, sizeof(tk_result_t), cudaMemcpyDeviceToHost, st));
+    TK_CUDA(cudaMemcpyAsync(s.h_batch_end, s.d.batch_end, sizeof(uint32_t) * nb, cudaMemcpyDeviceToHost, st));
+    TK_CUDA(cudaMemcpyAsync(s.h_batch_lmax, s.d.batch_lmax, sizeof(uint32_t) * nb, cudaMemcpyDeviceToHost, st));
+    TK_CUDA(cudaMemcpyAsync(s.h_commit, s.d.commit, sizeof(int64_t) * (size_t)ctx->n_partitions * ctx->commit_pitch,
+                            cudaMemcpyDeviceToHost, st));
+    TK_CUDA(cudaEventRecord(s.ev_result, st));
+    TK_CUDA(cudaEventRecord(s.ev_free, st));
+    s.free_recorded = true;
+    return 0;
+}
+
+extern "C" int tk_slot_result(tk_ctx* ctx, int slot, const tk_result_t** hdr, const uint32_t** batch_end,
+                              const uint32_t** batch_lmax, const int64_t** commit, uint32_t* commit_pitch) {
+    TK_ENTER(ctx, slot);
+    tk_slot& s = ctx->slots[slot];
+    TK_CUDA(cudaEventSynchronize(s.ev_result));
+    if (hdr) *hdr = s.h_result;
+    if (batch_end) *batch_end = s.h_batch_end;
+    if (batch_lmax) *batch_lmax = s.h_batch_lmax;
+    if (commit) *commit = s.h_commit;
+    if (commit_pitch) *commit_pitch = ctx->commit_pitch;
+    return 0;
+}
+
+extern "C" int tk_slot_debug_records(tk_ctx* ctx, int slot, int32_t* rec_len, int32_t* rec_status,
+                                     int32_t* rec_kidx, uint32_t n) {
+    TK_ENTER(ctx, slot);
+    tk_slot& s = ctx->slots[slot];
+    TK_REQUIRE(n <= ctx->slot_records, "n too large");
+    TK_CUDA(cudaDeviceSynchronize());
+    if (rec_len) TK_CUDA(cudaMemcpy(rec_len, s.d.rec_len, sizeof(int32_t) * n, cudaMemcpyDeviceToHost));
+    if (rec_status) TK_CUDA(cudaMemcpy(rec_status, s.d.rec_status, sizeof(int32_t) * n, cudaMemcpyDeviceToHost));
+    if (rec_kidx) TK_CUDA(cudaMemcpy(rec_kidx, s.d.rec_kidx, sizeof(int32_t) * n, cudaMemcpyDeviceToHost));
+    return 0;
+}

@@ -1,0 +1,101 @@
+// tk_internal.h -- structures shared by the translation units of libtorchkafka_b200.so
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stdio.h>
+#include "../../include/torchkafka_b200.h"
+
+// ---------------------------------------------------------------- error channel
+void tk_set_error(const char* fmt, ...);
+
+#define TK_CUDA(call)                                                                     \
+    do {                                                                                  \
+        cudaError_t e__ = (call);                                                         \
+        if (e__ != cudaSuccess) {                                                         \
+            tk_set_error("%s failed: %s (%s:%d)", #call, cudaGetErrorString(e__), __FILE__, \
+                         __LINE__);                                                       \
+            return -1;                                                                    \
+        }                                                                                 \
+    } while (0)
+
+#define TK_REQUIRE(cond, ...)                 \
+    do {                                      \
+        if (!(cond)) {                        \
+            tk_set_error(__VA_ARGS__);        \
+            return -2;                        \
+        }                                     \
+    } while (0)
+
+// ---------------------------------------------------------------- device state
+// Persistent across slots: the open batch and the per-partition positions.
+struct tk_state {
+    uint32_t carry_rows;   // rows of the batch left open by the previous slot
+    uint32_t pad;
+};
+
+// Per-slot device scratch ("plan"): everything the kernels hand to one another.
+struct tk_slot_dev {
+    uint8_t*     bytes;        // [slot_bytes + pad]
+    tk_rec_t*    recs;         // [slot_records + 1]
+    int32_t*     rec_len;      // element count (JSON) / byte count (raw)
+    int32_t*     rec_status;   // tk_status_t
+    int32_t*     rec_kidx;     // index among kept records of this slot, -1 if skipped
+    uint32_t*    blk_sum;      // per-block kept counts for the compaction scan
+    tk_result_t* result;       // header
+    uint32_t*    batch_end;    // [max_batches + 1]
+    uint32_t*    batch_lmax;   // [max_batches + 1]
+    int64_t*     commit;       // [n_partitions][commit_pitch]
+};
+
+struct tk_slot {
+    // host pinned staging
+    uint8_t*  h_bytes;
+    tk_rec_t* h_recs;
+    // host pinned result block
+    tk_result_t* h_result;
+    uint32_t*    h_batch_end;
+    uint32_t*    h_batch_lmax;
+    int64_t*     h_commit;
+    tk_slot_dev  d;
+    uint32_t     n_records;
+    uint64_t     n_bytes;
+    cudaEvent_t  ev_h2d;      // H2D landed
+    cudaEvent_t  ev_free;     // kernels finished reading the device copy
+    cudaEvent_t  ev_result;   // result block is in pinned memory
+    bool         free_recorded;
+};
+
+struct tk_ctx {
+    int       device;
+    uint64_t  slot_bytes;
+    uint32_t  slot_records;
+    int       n_slots;
+    uint32_t  max_batches;     // batches one slot can close (+1 open)
+    uint32_t  commit_pitch;    // max_batches + 1 rounded up to 4
+    uint32_t  n_partitions;
+    uint32_t  batch_size;      // of the last tk_compact
+    cudaStream_t copy_stream;
+    tk_state* d_state;
+    int64_t*  d_positions;     // [n_partitions] running max(offset)+1, -1 = never seen
+    uint16_t* d_image_lut;     // [4][256] bf16 bit patterns
+    int       image_channels;
+    tk_slot*  slots;
+};
+
+static inline int tk_check_slot(tk_ctx* ctx, int slot) {
+    if (!ctx) { tk_set_error("null context"); return -2; }
+    if (slot < 0 || slot >= ctx->n_slots) { tk_set_error("slot %d out of range [0,%d)", slot, ctx->n_slots); return -2; }
+    return 0;
+}
+
+#define TK_ENTER(ctx, slot)                                   \
+    do {                                                      \
+        int rc__ = tk_check_slot((ctx), (slot));              \
+        if (rc__) return rc__;                                \
+        TK_CUDA(cudaSetDevice((ctx)->device));                \
+    } while (0)
+
+#define TK_LAUNCH_CHECK() TK_CUDA(cudaGetLastError())
+
+// bytes the kernels may over-read past n_bytes (aligned vector loads of the last tile)
+#define TK_BYTES_PAD 4096

@@ -31,11 +31,13 @@ enum {
     TK_ERR_RAGGED = 6,       // fixed_len schema and a kept record of another length (torch.stack raises)
 };
 
-#if defined(__CUDA_ARCH__)
-#define TK_POW5_TABLE tk_pow5_dev
-__device__ const uint64_t tk_pow5_dev[651][2] = {
+#if defined(__CUDACC__)
+static __device__ const uint64_t tk_pow5_dev[651][2] = {
 #include "tk_pow5_table.inc"
 };
+#endif
+#if defined(__CUDA_ARCH__)
+#define TK_POW5_TABLE tk_pow5_dev
 #else
 #define TK_POW5_TABLE tk_pow5_host
 static const uint64_t tk_pow5_host[651][2] = {

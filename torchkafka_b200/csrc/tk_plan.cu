@@ -1,0 +1,297 @@
+// tk_plan.cu -- K2 (filter compaction, batch boundaries) and K4 (commit offsets).
+//
+// K2 replaces the reference's sequential "drop None, count to batch_size" loop
+// (src/kafka_dataset.py:161-162 + torch/utils/data/_utils/fetch.py:33-38): a
+// batch closes on its batch_size-th *kept* record; skipped records before the
+// closing record belong to that batch, skipped records after it to the next
+// (SURVEY.md §4.1-3).  On the GPU that is an exclusive prefix sum of the keep
+// flags: record i with k kept records before it lies in batch (carry + k) / B.
+//
+// K4 replaces the consumer-position bookkeeping behind consumer.commit()
+// (src/kafka_dataset.py:130): after batch j, partition p commits
+// max(offset) + 1 over every record consumed up to the closing record of j
+// (SURVEY.md §4.1-5).  Segmented max by (batch, partition), then a running max
+// along the batch axis seeded with the positions of earlier slots.
+#include "tk_internal.h"
+
+#define CMP_THREADS 256
+#define CMP_ITEMS 4
+#define CMP_TILE (CMP_THREADS * CMP_ITEMS)
+
+__device__ __forceinline__ uint32_t warp_incl_scan(uint32_t v) {
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+        uint32_t t = __shfl_up_sync(0xffffffffu, v, d);
+        if ((threadIdx.x & 31) >= d) v += t;
+    }
+    return v;
+}
+
+// block-wide exclusive scan of one value per thread (blockDim.x <= 1024); returns total via *total
+__device__ __forceinline__ uint32_t block_excl_scan(uint32_t v, uint32_t* total) {
+    __shared__ uint32_t warp_tot[32];
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+    uint32_t incl = warp_incl_scan(v);
+    if (lane == 31) warp_tot[wid] = incl;
+    __syncthreads();
+    if (wid == 0) {
+        uint32_t w = lane < (int)((blockDim.x + 31) >> 5) ? warp_tot[lane] : 0;
+        uint32_t wi = warp_incl_scan(w);
+        warp_tot[lane] = wi - w;                       // exclusive warp offsets
+        if (lane == 31) warp_tot[31] = wi - w, *total = wi;
+    }
+    __syncthreads();
+    uint32_t r = warp_tot[wid] + incl - v;
+    __syncthreads();
+    return r;
+}
+
+// pass 1: kept count per tile of 1024 records
+__global__ void __launch_bounds__(CMP_THREADS) k_compact_count(const int32_t* __restrict__ rec_kidx,
+                                                                 uint32_t n, uint32_t* __restrict__ blk_sum) {
+    __shared__ uint32_t tot;
+    const uint32_t base = blockIdx.x * CMP_TILE + threadIdx.x * CMP_ITEMS;
+    uint32_t c = 0;
+#pragma unroll
+    for (int k = 0; k < CMP_ITEMS; ++k) {
+        uint32_t i = base + k;
+        if (i < n && rec_kidx[i] >= 0) ++c;
+    }
+    block_excl_scan(c, &tot);
+    if (threadIdx.x == 0) blk_sum[blockIdx.x] = tot;
+}
+
+// pass 2: one block scans the tile sums, fills the result header, advances the carry
+__global__ void __launch_bounds__(1024) k_compact_scan(uint32_t* __restrict__ blk_sum, uint32_t nblk,
+                                                       uint32_t n, uint32_t batch_size,
+                                                       uint32_t max_batches, tk_state* state,
+                                                       tk_result_t* __restrict__ res,
+                                                       uint32_t* __restrict__ batch_end,
+                                                       uint32_t* __restrict__ batch_lmax) {
+    __shared__ uint32_t tot;
+    uint32_t running = 0;
+    for (uint32_t base = 0; base < nblk; base += blockDim.x) {
+        uint32_t i = base + threadIdx.x;
+        uint32_t v = i < nblk ? blk_sum[i] : 0;
+        uint32_t ex = block_excl_scan(v, &tot);
+        if (i < nblk) blk_sum[i] = running + ex;
+        running += tot;
+        __syncthreads();
+    }
+    const uint32_t n_kept = running;
+    const uint32_t c = state->carry_rows;
+    const uint32_t n_closed = (c + n_kept) / batch_size;
+    for (uint32_t j = threadIdx.x; j <= max_batches; j += blockDim.x) {
+        batch_end[j] = n ? n - 1 : 0;
+        batch_lmax[j] = 0;
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        res->n_records = n;
+        res->n_kept = n_kept;
+        res->carry_in = c;
+        res->carry_out = (c + n_kept) % batch_size;
+        res->n_closed = n_closed;
+        res->batch_size = batch_size;
+        res->n_errors = 0;
+        res->first_error_rec = 0xFFFFFFFFu;
+        res->first_error_status = 0;
+        state->carry_rows = (c + n_kept) % batch_size;
+    }
+}
+
+// pass 3: final index of every record.
+//   kept record    -> rec_kidx = k            (k = kept records before it in this slot)
+//   skipped record -> rec_kidx = -1 - k
+__global__ void __launch_bounds__(CMP_THREADS) k_compact_apply(int32_t* __restrict__ rec_kidx,
+                                                                 const int32_t* __restrict__ rec_len,
+                                                                 uint32_t n, const uint32_t* __restrict__ blk_sum,
+                                                                 const tk_result_t* __restrict__ res,
+                                                                 uint32_t* __restrict__ batch_end,
+                                                                 uint32_t* __restrict__ batch_lmax) {
+    __shared__ uint32_t tot;
+    const uint32_t base = blockIdx.x * CMP_TILE + threadIdx.x * CMP_ITEMS;
+    int keep[CMP_ITEMS];
+    uint32_t c = 0;
+#pragma unroll
+    for (int k = 0; k < CMP_ITEMS; ++k) {
+        uint32_t i = base + k;
+        keep[k] = (i < n && rec_kidx[i] >= 0) ? 1 : 0;
+        c += keep[k];
+    }
+    uint32_t ex = block_excl_scan(c, &tot) + blk_sum[blockIdx.x];
+    const uint32_t carry = res->carry_in, B = res->batch_size;
+#pragma unroll
+    for (int k = 0; k < CMP_ITEMS; ++k) {
+        uint32_t i = base + k;
+        if (i >= n) break;
+        if (keep[k]) {
+            rec_kidx[i] = (int32_t)ex;
+            const uint32_t q = carry + ex;
+            const uint32_t j = q / B;
+            atomicMax(&batch_lmax[j], (uint32_t)rec_len[i]);
+            if ((q + 1) % B == 0) batch_end[j] = i;
+            ++ex;
+        } else {
+            rec_kidx[i] = -1 - (int32_t)ex;
+        }
+    }
+}
+
+extern "C" int tk_compact(tk_ctx* ctx, int slot, uint32_t batch_size, void* stream) {
+    TK_ENTER(ctx, slot);
+    tk_slot& s = ctx->slots[slot];
+    cudaStream_t st = (cudaStream_t)stream;
+    TK_REQUIRE(batch_size > 0, "batch_size must be positive");
+    const uint32_t n = s.n_records;
+    // worst case: every record kept and the open batch almost full
+    TK_REQUIRE(((uint64_t)n + batch_size - 1) / batch_size <= ctx->max_batches,
+               "slot with %u records can close more than max_batches=%u batches of %u", n, ctx->max_batches, batch_size);
+    ctx->batch_size = batch_size;
+    const uint32_t nblk = (n + CMP_TILE - 1) / CMP_TILE;
+    if (nblk) {
+        k_compact_count<<<nblk, CMP_THREADS, 0, st>>>(s.d.rec_kidx, n, s.d.blk_sum);
+        TK_LAUNCH_CHECK();
+    }
+    k_compact_scan<<<1, 1024, 0, st>>>(s.d.blk_sum, nblk, n, batch_size, ctx->max_batches, ctx->d_state,
+                                       s.d.result, s.d.batch_end, s.d.batch_lmax);
+    TK_LAUNCH_CHECK();
+    if (nblk) {
+        k_compact_apply<<<nblk, CMP_THREADS, 0, st>>>(s.d.rec_kidx, s.d.rec_len, n, s.d.blk_sum, s.d.result,
+                                                     s.d.batch_end, s.d.batch_lmax);
+        TK_LAUNCH_CHECK();
+    }
+    return 0;
+}
+
+// ------------------------------------------------------------------------ K4
+// Segmented max: one thread per record; lanes of a warp that share (batch,
+// partition) elect the lane with the largest offset, which issues the only
+// atomic of the group.
+__global__ void __launch_bounds__(256) k_commit_reduce(const tk_rec_t* __restrict__ recs,
+                                                        const int32_t* __restrict__ rec_kidx, uint32_t n,
+                                                        const tk_result_t* __restrict__ res,
+                                                        int64_t* __restrict__ commit, uint32_t pitch,
+                                                        uint32_t n_partitions) {
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    const bool live = i < n;
+    uint32_t key = 0xFFFFFFFFu;
+    long long val = 0;
+    uint32_t p = 0, j = 0;
+    if (live) {
+        const uint4 raw = __ldg(reinterpret_cast<const uint4*>(recs) + i);
+        p = raw.y;
+        val = (long long)(((uint64_t)raw.w << 32) | raw.z) + 1;
+        const int32_t kx = rec_kidx[i];
+        const uint32_t kexcl = kx >= 0 ? (uint32_t)kx : (uint32_t)(-1 - kx);
+        j = (res->carry_in + kexcl) / res->batch_size;
+        if (p < n_partitions) key = j * n_partitions + p;
+    }
+    // every lane of the warp reaches this point (no early return above)
+    const unsigned peers = __match_any_sync(0xffffffffu, key);
+    // 64-bit max inside each peer group from two 32-bit warp reductions (values are >= 0)
+    const uint32_t hi = (uint32_t)((unsigned long long)val >> 32), lo = (uint32_t)val;
+    const uint32_t mh = __reduce_max_sync(peers, hi);
+    const uint32_t ml = __reduce_max_sync(peers, hi == mh ? lo : 0u);
+    const long long best = (long long)(((unsigned long long)mh << 32) | ml);
+    const int leader = __ffs(peers) - 1;
+    if (key != 0xFFFFFFFFu && (int)(threadIdx.x & 31) == leader)
+        atomicMax(reinterpret_cast<long long*>(&commit[(size_t)p * pitch + j]), best);
+}
+
+// Running max along the batch axis, one block per partition.
+__global__ void __launch_bounds__(128) k_commit_scan(int64_t* __restrict__ commit, uint32_t pitch,
+                                                      const tk_result_t* __restrict__ res,
+                                                      int64_t* __restrict__ positions) {
+    __shared__ long long chunk_max[128];
+    const uint32_t p = blockIdx.x;
+    const uint32_t nb = res->n_closed + 1;                 // closed batches + the open one
+    int64_t* row = commit + (size_t)p * pitch;
+    const uint32_t per = (nb + blockDim.x - 1) / blockDim.x;
+    const uint32_t a = threadIdx.x * per;
+    const uint32_t b = min(a + per, nb);
+    long long m = -1;
+    for (uint32_t j = a; j < b; ++j) { long long v = row[j]; m = v > m ? v : m; }
+    chunk_max[threadIdx.x] = m;
+    __syncthreads();
+    long long run = positions[p];
+    for (uint32_t t = 0; t < threadIdx.x; ++t) { long long v = chunk_max[t]; run = v > run ? v : run; }
+    for (uint32_t j = a; j < b; ++j) {
+        long long v = row[j];
+        run = v > run ? v : run;
+        row[j] = run;
+    }
+    __syncthreads();
+    if (threadIdx.x == blockDim.x - 1) {
+        // last thread's run covers every chunk only if it owned the tail; recompute the global max
+        long long g = positions[p];
+        for (uint32_t t = 0; t < blockDim.x; ++t) { long long v = chunk_max[t]; g = v > g ? v : g; }
+        positions[p] = g;
+    }
+}
+
+extern "C" int tk_commit_offsets(tk_ctx* ctx, int slot, void* stream) {
+    TK_ENTER(ctx, slot);
+    tk_slot& s = ctx->slots[slot];
+    cudaStream_t st = (cudaStream_t)stream;
+    const uint32_t n = s.n_records;
+    TK_CUDA(cudaMemsetAsync(s.d.commit, 0xFF, sizeof(int64_t) * (size_t)ctx->n_partitions * ctx->commit_pitch, st));
+    if (n) {
+        k_commit_reduce<<<(n + 255) / 256, 256, 0, st>>>(s.d.recs, s.d.rec_kidx, n, s.d.result, s.d.commit,
+                                                        ctx->commit_pitch, ctx->n_partitions);
+        TK_LAUNCH_CHECK();
+    }
+    k_commit_scan<<<ctx->n_partitions, 128, 0, st>>>(s.d.commit, ctx->commit_pitch, s.d.result, ctx->d_positions);
+    TK_LAUNCH_CHECK();
+    return 0;
+}
+
+// ------------------------------------------------------------------------ carry
+// The batch left open by the previous slot occupies the last carry_out rows of
+// that slot's tensor: rows [B + n_kept - carry_out, B + n_kept).  Copy them to
+// rows [B - carry_out, B) of the current tensor (the end of its head region).
+struct carry_args {
+    tk_plane_t prev[4];
+    tk_plane_t cur[4];
+    int n_planes;
+};
+
+__global__ void __launch_bounds__(256) k_carry_rows(const tk_result_t* __restrict__ prev_res, const carry_args a) {
+    const uint64_t co = prev_res->carry_out;
+    if (co == 0) return;
+    const uint64_t B = prev_res->batch_size, nk = prev_res->n_kept;
+    const uint64_t tid = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const uint64_t nthr = (uint64_t)gridDim.x * blockDim.x;
+    for (int k = 0; k < a.n_planes; ++k) {
+        const uint64_t rb = a.prev[k].row_bytes;
+        if (!a.prev[k].base || !a.cur[k].base) continue;
+        const uint8_t* src = (const uint8_t*)a.prev[k].base + (B + nk - co) * rb;
+        uint8_t* dst = (uint8_t*)a.cur[k].base + (B - co) * rb;
+        const uint64_t nbytes = co * rb;
+        if ((((uintptr_t)src | (uintptr_t)dst | nbytes) & 15u) == 0) {
+            for (uint64_t x = tid; x < nbytes / 16; x += nthr)
+                reinterpret_cast<uint4*>(dst)[x] = reinterpret_cast<const uint4*>(src)[x];
+        } else if ((((uintptr_t)src | (uintptr_t)dst | nbytes) & 3u) == 0) {
+            for (uint64_t x = tid; x < nbytes / 4; x += nthr)
+                reinterpret_cast<uint32_t*>(dst)[x] = reinterpret_cast<const uint32_t*>(src)[x];
+        } else {
+            for (uint64_t x = tid; x < nbytes; x += nthr) dst[x] = src[x];
+        }
+    }
+}
+
+extern "C" int tk_carry_rows(tk_ctx* ctx, int prev_slot, int n_planes, const tk_plane_t* prev,
+                             const tk_plane_t* cur, void* stream) {
+    TK_ENTER(ctx, prev_slot);
+    TK_REQUIRE(n_planes >= 1 && n_planes <= 4 && prev && cur, "1..4 planes");
+    carry_args a;
+    a.n_planes = n_planes;
+    for (int k = 0; k < n_planes; ++k) {
+        TK_REQUIRE(prev[k].row_bytes == cur[k].row_bytes, "plane %d: row_bytes differ", k);
+        a.prev[k] = prev[k];
+        a.cur[k] = cur[k];
+    }
+    k_carry_rows<<<148 * 2, 256, 0, (cudaStream_t)stream>>>(ctx->slots[prev_slot].d.result, a);
+    TK_LAUNCH_CHECK();
+    return 0;
+}

@@ -1,0 +1,181 @@
+"""GPU parity: the CUDA path (through the public API, C-ABI underneath) against the
+oracle on identical seeded records.  Bit-exact for every dtype, including float
+(0 ulp: the decimal->binary conversion is correctly rounded like CPython's)."""
+import json
+
+import numpy as np
+import pytest
+import torch
+
+from helpers import assert_same, run_gpu, run_oracle
+from torchkafka_b200.schema import ImageU8, JsonArray, PayloadError, RawBytes, TokenList
+from torchkafka_b200.testing import synthetic as syn
+from torchkafka_b200.testing.stub_kafka import RecordLog
+
+pytestmark = pytest.mark.gpu
+
+
+def check(log, schema, batch_size, drop_last=False, **kw):
+    gpu = run_gpu(log, schema, batch_size, drop_last, **kw)
+    cpu = run_oracle(log, schema, batch_size, drop_last)
+    assert_same(gpu, cpu, schema)
+    return gpu
+
+
+def test_cfg1_fixed_len_floats():
+    log = syn.make_log(1, 5000, seed=1)
+    check(log, JsonArray(torch.float32, fixed_len=8), 4)
+
+
+def test_cfg2_variable_floats_filter():
+    log = syn.make_log(2, 6000, seed=2)
+    check(log, JsonArray(torch.float32, max_len=256, min_size=32), 1024)
+
+
+def test_cfg2_small_slots_many_carries():
+    # slots far smaller than a batch: the open batch is carried across many slots
+    log = syn.make_log(2, 1500, seed=3)
+    check(log, JsonArray(torch.float32, max_len=256, min_size=32), 256, slot_bytes=96 << 10)
+
+
+def test_cfg2_float64():
+    log = syn.make_log(2, 1200, seed=4)
+    check(log, JsonArray(torch.float64, max_len=256, min_size=32), 128)
+
+
+def test_cfg3_tokens():
+    log = syn.make_log(3, 1500, seed=5)
+    check(log, TokenList(torch.int32, max_len=2048), 512)
+
+
+def test_cfg3_tokens_int64_chunked_poll_path():
+    log = syn.make_log(3, 600, seed=6, layout="chunked", chunk=37)
+    check(log, TokenList(torch.int64, max_len=2048), 64, use_packed=False)
+
+
+def test_cfg4_images():
+    log = syn.make_log(4, 70, seed=7)
+    check(log, ImageU8(224, 224, 3), 32, slot_bytes=24 * 150528)
+
+
+def test_cfg5_raw64_commit_offsets():
+    log = syn.make_log(5, 20000, seed=8)
+    check(log, RawBytes((64,), torch.uint8), 256)
+
+
+def test_drop_last_and_tail():
+    log = syn.make_log(2, 700, seed=9)
+    sc = JsonArray(torch.float32, max_len=256, min_size=32)
+    check(log, sc, 64, drop_last=True)
+    check(log, sc, 64, drop_last=False)
+
+
+def test_survey_commit_example():
+    # 3 partitions round-robin, lengths below, min_size=4, batch_size=3
+    lens = [4, 4, 2, 2, 2, 4, 2, 4, 4, 4, 2, 4, 4, 2]
+    vals = [json.dumps([float(i)] * n).encode() for i, n in enumerate(lens)]
+    i = np.arange(len(vals))
+    log = RecordLog(vals, i % 3, i // 3)
+    gpu = check(log, JsonArray(torch.float32, max_len=8, min_size=4), 3)
+    commits = [c for _, c in gpu]
+    assert commits == [{0: 2, 1: 2, 2: 2}, {0: 4, 1: 3, 2: 3}, {0: 5, 1: 5, 2: 4}]
+
+
+ADVERSARIAL = [
+    "0.1", "1e23", "8.41e21", "1.0000000596046448", "1152921573326323713", "16777217",
+    "2.2250738585072011e-308", "4.9e-324", "2.4703282292062327e-324", "2.4703282292062328e-324",
+    "1e400", "1E-400", "-0", "-0.0", "0", "1E+5", "1e-5", "NaN", "Infinity", "-Infinity",
+    "123456789012345678901234567890", "9007199254740993", "9007199254740992.5",
+    "1.7976931348623157e308", "1.7976931348623158e308", "0.000001", "5e-324", "3e-324",
+    "0.30000000000000004", "179769313486231570000000000000000000000000000000000000000000000000000"
+    "0000000000000000000000000000000000000000000000000000000000000000000000000000000000000000000"
+    "0000000000000000000000000000000000000000000000000000000000000000000000000000000000000000000"
+    "00000000000000000000000000000000000000000000000000000000",
+    # exact halfway between 1.0 and nextafter(1.0): ties-to-even, and one digit above it
+    "1.00000000000000011102230246251565404236316680908203125",
+    "1.000000000000000111022302462515654042363166809082031251",
+    "1.00000000000000011102230246251565404236316680908203124999",
+]
+
+
+@pytest.mark.parametrize("dtype", [torch.float32, torch.float64])
+def test_adversarial_floats(dtype):
+    vals = []
+    for k in range(0, len(ADVERSARIAL), 5):
+        vals.append(("[" + ", ".join(ADVERSARIAL[k:k + 5]) + "]").encode())
+    vals.append(b"\xef\xbb\xbf[1]")
+    vals.append(b"  [ 1 ,\t2 ,\n3 ]\r\n ")
+    vals.append(b"[]")
+    i = np.arange(len(vals))
+    log = RecordLog(vals, i % 2, i // 2)
+    check(log, JsonArray(dtype, max_len=8), 4)
+
+
+def test_random_decimal_strings_float64():
+    import random
+    rng = random.Random(11)
+    vals = []
+    for _ in range(400):
+        toks = []
+        for _ in range(rng.randint(1, 40)):
+            k = rng.randrange(5)
+            if k == 0:
+                toks.append(repr(rng.uniform(-1e3, 1e3)))
+            elif k == 1:
+                toks.append("%de%d" % (rng.getrandbits(rng.randint(1, 70)), rng.randint(-345, 308)))
+            elif k == 2:
+                toks.append("0." + "0" * rng.randint(0, 30) + str(rng.getrandbits(rng.randint(1, 90))))
+            elif k == 3:
+                toks.append(str(rng.getrandbits(rng.randint(1, 200))))
+            else:
+                toks.append("-%d.%d" % (rng.getrandbits(20), rng.getrandbits(64)))
+        vals.append(("[" + rng.choice([", ", ",", " , "]).join(toks) + "]").encode())
+    i = np.arange(len(vals))
+    log = RecordLog(vals, i % 4, i // 4)
+    check(log, JsonArray(torch.float64, max_len=64), 32)
+
+
+BAD = [b"[1,]", b"[1.]", b"[01]", b"[+1]", b"[1 2]", b"[-]", b"[1]x", b"", b"[1, 2", b"[1e]",
+       b"[true]", b"[null]", b'["a"]', b"[[1]]", b"3.5", b"[-NaN]", b"{}", b"[1,,2]", b"[,1]"]
+
+
+@pytest.mark.parametrize("bad", BAD)
+def test_bad_payload_raises_like_reference(bad):
+    good = [json.dumps([1.0, 2.0]).encode()] * 5
+    vals = good[:3] + [bad] + good[3:]
+    i = np.arange(len(vals))
+    log = RecordLog(vals, i % 2, i // 2)
+    sc = JsonArray(torch.float32, max_len=4)
+    # the reference raises from _process on the bad record ...
+    if bad not in (b"[true]", b"[[1]]", b"3.5"):       # these three the reference happens to accept
+        with pytest.raises(Exception):
+            run_oracle(log, sc, 2)
+    # ... the GPU path delivers the batch before it, then raises PayloadError
+    with pytest.raises(PayloadError) as ei:
+        run_gpu(log, sc, 2)
+    assert ei.value.offset == 1 and ei.value.partition == 1
+
+
+def test_int_overflow_and_truncation():
+    sc = JsonArray(torch.int32, max_len=4)
+    ok = RecordLog([b"[1.5, -2.9, 2147483647, -2147483648]", b"[1e5, 0, -0, 7]"], [0, 0], [0, 1])
+    check(ok, sc, 2)
+    for bad in (b"[2147483648]", b"[-2147483649]", b"[1e30]", b"[NaN]", b"[9223372036854775808]",
+                b"[2147483647.5]"):
+        log = RecordLog([bad], [0], [0])
+        with pytest.raises(Exception):
+            run_oracle(log, sc, 1)
+        with pytest.raises(PayloadError):
+            run_gpu(log, sc, 1)
+
+
+def test_too_long_and_ragged():
+    with pytest.raises(PayloadError):
+        run_gpu(RecordLog([b"[1,2,3,4,5]"], [0], [0]), JsonArray(torch.float32, max_len=4), 1)
+    with pytest.raises(PayloadError):
+        run_gpu(RecordLog([b"[1,2,3]", b"[1,2]"], [0, 0], [0, 1]), JsonArray(torch.float32, fixed_len=3), 2)
+
+
+def test_raw_wrong_size():
+    with pytest.raises(PayloadError):
+        run_gpu(RecordLog([b"x" * 64, b"y" * 63], [0, 0], [0, 1]), RawBytes((64,)), 2)

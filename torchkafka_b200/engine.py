@@ -1,0 +1,292 @@
+"""SlotEngine: object wrapper over the C-ABI for one GPU.
+
+It owns a native context (pinned staging slots + device twins), knows how to run
+the kernel sequence of a schema on a slot and how to turn the fetched result
+block into batch views.  ``IngestPipeline`` (pipeline.py) drives it from a Kafka
+consumer; tests and ``bench.py`` drive it directly with packed records.
+
+Kernel sequence per slot (all on the caller's current CUDA stream):
+
+    tk_slot_wait        wait for the slot's H2D copy (K0)
+    tk_carry_rows       rows of the open batch: previous tensor -> head of this one
+    tk_json_scan | tk_raw_scan      element count / size check, keep flag (K1 phase 1)
+    tk_compact          filter compaction, batch boundaries (K2)
+    tk_commit_offsets   per batch, per partition commit offsets (K4)
+    tk_json_decode | tk_collate_raw | tk_collate_image_u8_bf16_nchw   (K1 phase 2 + K3)
+    tk_slot_fetch_result            async D2H of the small result block
+"""
+from __future__ import annotations
+
+import ctypes as C
+from typing import List, Optional
+
+import numpy as np
+import torch
+
+from . import _native
+from .schema import ImageU8, JsonArray, PayloadError, RawBytes
+
+# one packed record header: tk_rec_t in include/torchkafka_b200.h
+REC_DTYPE = np.dtype([("start", "<u4"), ("partition", "<i4"), ("offset", "<i8")])
+
+#: a slot never closes more batches than this (bounds the commit matrix)
+MAX_BATCHES_CAP = 16384
+#: launches issued per slot by ``process`` (kernels + memset), for bench accounting
+LAUNCHES_PER_SLOT_JSON = 9
+LAUNCHES_PER_SLOT_RAW = 8
+
+
+def _np_view(ptr: int, nbytes: int, dtype) -> np.ndarray:
+    buf = (C.c_uint8 * nbytes).from_address(ptr)
+    return np.frombuffer(buf, dtype=dtype)
+
+
+class SlotOutput:
+    """Tensors one slot wrote into (kept alive until the next slot took its carry)."""
+
+    __slots__ = ("tensors", "planes", "n_records")
+
+    def __init__(self, tensors, planes, n_records):
+        self.tensors = tensors
+        self.planes = planes
+        self.n_records = n_records
+
+
+class SlotResult:
+    """Host copy of a slot's result block."""
+
+    __slots__ = ("n_records", "n_kept", "carry_in", "carry_out", "n_closed", "n_errors",
+                 "first_error_rec", "batch_end", "batch_lmax", "commit")
+
+    def __init__(self, hdr, batch_end, batch_lmax, commit):
+        self.n_records = hdr.n_records
+        self.n_kept = hdr.n_kept
+        self.carry_in = hdr.carry_in
+        self.carry_out = hdr.carry_out
+        self.n_closed = hdr.n_closed
+        self.n_errors = hdr.n_errors
+        self.first_error_rec = hdr.first_error_rec
+        self.batch_end = batch_end
+        self.batch_lmax = batch_lmax
+        self.commit = commit          # [n_partitions, n_closed + 1] int64
+
+
+class SlotEngine:
+    def __init__(self, schema, batch_size: int, slot_bytes: int = 64 << 20,
+                 slot_records: Optional[int] = None, n_slots: int = 3,
+                 device: Optional[int] = None, n_partitions: int = 64):
+        if not torch.cuda.is_available():
+            raise RuntimeError(
+                "payload_schema datasets need a CUDA device (B200); there is no CPU fallback."
+            )
+        self.lib = _native.load()
+        self.schema = schema
+        self.batch_size = int(batch_size)
+        if self.batch_size <= 0:
+            raise ValueError("batch_size must be positive")
+        self.device = torch.cuda.current_device() if device is None else int(device)
+        self.n_slots = int(n_slots)
+        self.n_partitions = int(n_partitions)
+        self.slot_bytes = int(slot_bytes)
+        if isinstance(schema, (RawBytes, ImageU8)):
+            rb = schema.record_bytes
+            if self.slot_bytes < rb:
+                self.slot_bytes = rb
+            auto_records = max(1, self.slot_bytes // rb)
+        else:
+            auto_records = max(1, self.slot_bytes // 48)
+        cap = MAX_BATCHES_CAP * self.batch_size
+        self.slot_records = int(min(slot_records or auto_records, cap, 1 << 22))
+        self.max_batches = (self.slot_records + self.batch_size - 1) // self.batch_size + 1
+        ctx = C.c_void_p()
+        _native.check(self.lib.tk_ctx_create(self.device, self.slot_bytes, self.slot_records,
+                                              self.n_slots, self.max_batches, self.n_partitions,
+                                              C.byref(ctx)))
+        self.ctx = ctx
+        self._host_bytes: List[np.ndarray] = []
+        self._host_recs: List[np.ndarray] = []
+        for s in range(self.n_slots):
+            pb, pr = C.c_void_p(), C.c_void_p()
+            _native.check(self.lib.tk_slot_host_ptrs(self.ctx, s, C.byref(pb), C.byref(pr)))
+            self._host_bytes.append(_np_view(pb.value, self.slot_bytes, np.uint8))
+            self._host_recs.append(_np_view(pr.value, (self.slot_records + 1) * 16, REC_DTYPE))
+        if isinstance(schema, ImageU8):
+            mean = (C.c_float * 4)(*schema.mean)
+            std = (C.c_float * 4)(*schema.std)
+            with torch.cuda.device(self.device):
+                _native.check(self.lib.tk_image_set_norm(self.ctx, schema.channels, mean, std,
+                                                         self._stream()))
+        self.launches = 0
+
+    # ------------------------------------------------------------------ plumbing
+    def _stream(self):
+        return C.c_void_p(torch.cuda.current_stream(self.device).cuda_stream)
+
+    def close(self):
+        if getattr(self, "ctx", None) is not None and self.ctx.value:
+            self._host_bytes = []
+            self._host_recs = []
+            self.lib.tk_ctx_destroy(self.ctx)
+            self.ctx = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def reset(self):
+        _native.check(self.lib.tk_ctx_reset(self.ctx, self._stream()))
+
+    def h2d_peak_gbs(self, nbytes: int = 256 << 20, iters: int = 10) -> float:
+        out = C.c_double()
+        _native.check(self.lib.tk_h2d_peak_gbs(self.device, nbytes, iters, C.byref(out)))
+        return out.value
+
+    # ------------------------------------------------------------------ filling
+    def host_views(self, slot: int):
+        """(uint8 bytes view, structured recs view) over the slot's pinned memory."""
+        return self._host_bytes[slot], self._host_recs[slot]
+
+    def fill_packed(self, slot: int, values: np.ndarray, starts: np.ndarray,
+                    partitions: np.ndarray, offsets: np.ndarray):
+        """Copy a packed run of records (CSR arrays) into the slot's pinned memory."""
+        n = len(partitions)
+        nbytes = int(starts[n]) - int(starts[0])
+        if n > self.slot_records or nbytes > self.slot_bytes:
+            raise ValueError(f"run of {n} records / {nbytes} bytes exceeds the slot "
+                             f"({self.slot_records} records / {self.slot_bytes} bytes)")
+        hb, hr = self.host_views(slot)
+        # ctypes.memmove releases the GIL, numpy slicing assignment does for large copies too
+        hb[:nbytes] = values[:nbytes] if len(values) == nbytes else values[int(starts[0]):int(starts[n])]
+        hr["start"][:n + 1] = starts[:n + 1] - starts[0]
+        hr["partition"][:n] = partitions
+        hr["offset"][:n] = offsets
+        return n, nbytes
+
+    def submit(self, slot: int, n: int, nbytes: int):
+        _native.check(self.lib.tk_slot_submit(self.ctx, slot, n, nbytes))
+
+    # ------------------------------------------------------------------ kernels
+    def _allocate(self, n: int) -> SlotOutput:
+        """Output tensors for a slot of ``n`` records: batch_size head rows + n body rows."""
+        rows = self.batch_size + n
+        dev = torch.device("cuda", self.device)
+        sc = self.schema
+        if isinstance(sc, JsonArray):
+            values = torch.empty((rows, sc.max_len), dtype=sc.dtype, device=dev)
+            tensors = [values]
+            planes = [(values.data_ptr(), sc.max_len * values.element_size())]
+            if sc.fixed_len is None:
+                lengths = torch.empty((rows,), dtype=torch.int32, device=dev)
+                mask = torch.empty((rows, sc.max_len), dtype=torch.bool, device=dev)
+                tensors += [lengths, mask]
+                planes += [(lengths.data_ptr(), 4), (mask.data_ptr(), sc.max_len)]
+        elif isinstance(sc, ImageU8):
+            out = torch.empty((rows, sc.channels, sc.height, sc.width), dtype=torch.bfloat16, device=dev)
+            tensors = [out]
+            planes = [(out.data_ptr(), sc.record_bytes * 2)]
+        elif isinstance(sc, RawBytes):
+            out = torch.empty((rows,) + sc.shape, dtype=sc.dtype, device=dev)
+            tensors = [out]
+            planes = [(out.data_ptr(), sc.record_bytes)]
+        else:
+            raise TypeError(f"unsupported schema {sc!r}")
+        arr = (_native.TkPlane * len(planes))()
+        for k, (ptr, rb) in enumerate(planes):
+            arr[k].base = ptr
+            arr[k].row_bytes = rb
+        return SlotOutput(tensors, arr, n)
+
+    def process(self, slot: int, n: int, prev_slot: Optional[int], prev_out: Optional[SlotOutput],
+                resident: bool = False) -> SlotOutput:
+        """Launch the whole kernel sequence for ``slot`` on the current stream (asynchronous)."""
+        lib, ctx, st = self.lib, self.ctx, self._stream()
+        sc = self.schema
+        with torch.cuda.device(self.device):
+            out = self._allocate(n)
+            if not resident:
+                _native.check(lib.tk_slot_wait(ctx, slot, st))
+            if prev_out is not None:
+                _native.check(lib.tk_carry_rows(ctx, prev_slot, len(out.planes), prev_out.planes,
+                                                out.planes, st))
+                self.launches += 1
+            if isinstance(sc, JsonArray):
+                _native.check(lib.tk_json_scan(ctx, slot, sc.max_len, sc.min_size, st))
+            else:
+                _native.check(lib.tk_raw_scan(ctx, slot, sc.record_bytes, st))
+            _native.check(lib.tk_compact(ctx, slot, self.batch_size, st))
+            _native.check(lib.tk_commit_offsets(ctx, slot, st))
+            if isinstance(sc, JsonArray):
+                P = out.planes
+                variable = sc.fixed_len is None
+                _native.check(lib.tk_json_decode(
+                    ctx, slot, sc.kind, sc.max_len, sc.fixed_len or 0, C.byref(P[0]),
+                    C.byref(P[1]) if variable else None, C.byref(P[2]) if variable else None, st))
+                self.launches += LAUNCHES_PER_SLOT_JSON - 1
+            elif isinstance(sc, ImageU8):
+                _native.check(lib.tk_collate_image_u8_bf16_nchw(ctx, slot, sc.height, sc.width,
+                                                                sc.channels, C.byref(out.planes[0]), st))
+                self.launches += LAUNCHES_PER_SLOT_RAW - 1
+            else:
+                _native.check(lib.tk_collate_raw(ctx, slot, sc.record_bytes, C.byref(out.planes[0]), st))
+                self.launches += LAUNCHES_PER_SLOT_RAW - 1
+            _native.check(lib.tk_slot_fetch_result(ctx, slot, st))
+        return out
+
+    def assume_resident(self, slot: int, n: int, nbytes: int):
+        _native.check(self.lib.tk_slot_assume_resident(self.ctx, slot, n, nbytes))
+
+    def device_views(self, slot: int):
+        """Raw device pointers of the slot's twin (bytes, recs), for benchmarks that preload HBM."""
+        pb, pr = C.c_void_p(), C.c_void_p()
+        _native.check(self.lib.tk_slot_device_ptrs(self.ctx, slot, C.byref(pb), C.byref(pr)))
+        return pb.value, pr.value
+
+    # ------------------------------------------------------------------ results
+    def result(self, slot: int) -> SlotResult:
+        """Block until the slot's result block is on the host, return a copy."""
+        hdr = C.POINTER(_native.TkResult)()
+        be = C.POINTER(C.c_uint32)()
+        bl = C.POINTER(C.c_uint32)()
+        cm = C.POINTER(C.c_int64)()
+        pitch = C.c_uint32()
+        _native.check(self.lib.tk_slot_result(self.ctx, slot, C.byref(hdr), C.byref(be), C.byref(bl),
+                                              C.byref(cm), C.byref(pitch)))
+        h = hdr.contents
+        nb = h.n_closed + 1
+        batch_end = np.ctypeslib.as_array(be, shape=(nb,)).copy()
+        batch_lmax = np.ctypeslib.as_array(bl, shape=(nb,)).copy()
+        commit = np.ctypeslib.as_array(cm, shape=(self.n_partitions, pitch.value))[:, :nb].copy()
+        return SlotResult(h, batch_end, batch_lmax, commit)
+
+    def record_debug(self, slot: int, n: int):
+        """(rec_len, rec_status, rec_kidx) of the last run on ``slot`` (synchronises the device)."""
+        ln = np.empty(n, np.int32)
+        st = np.empty(n, np.int32)
+        kx = np.empty(n, np.int32)
+        _native.check(self.lib.tk_slot_debug_records(self.ctx, slot, ln.ctypes.data, st.ctypes.data,
+                                                     kx.ctypes.data, n))
+        return ln, st, kx
+
+    def batch_view(self, out: SlotOutput, first_row: int, n_rows: int, lmax: int):
+        """Batch object over rows [first_row, first_row + n_rows) of a slot's tensors."""
+        sc = self.schema
+        t = out.tensors
+        if isinstance(sc, JsonArray):
+            if sc.fixed_len is not None:
+                return t[0][first_row:first_row + n_rows]
+            width = sc.max_len if sc.pad_to_max_len else max(int(lmax), 0)
+            return sc.wrap(t[0][first_row:first_row + n_rows, :width],
+                           t[1][first_row:first_row + n_rows],
+                           t[2][first_row:first_row + n_rows, :width])
+        return t[0][first_row:first_row + n_rows]
+
+    def error_for(self, slot: int, res: SlotResult, partitions, offsets) -> PayloadError:
+        e = int(res.first_error_rec)
+        _, status, _ = self.record_debug(slot, res.n_records)
+        code = int(status[e])
+        return PayloadError(
+            f"record {e} of the slot (partition index {int(partitions[e])}, offset {int(offsets[e])}): "
+            f"{_native.STATUS_NAMES.get(code, code)}",
+            partition=int(partitions[e]), offset=int(offsets[e]), status=code)

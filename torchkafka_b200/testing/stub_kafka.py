@@ -63,9 +63,10 @@ class PackedRecords:
     ``partitions`` (int32) and ``offsets`` (int64) the Kafka coordinates.
     """
 
-    __slots__ = ("values", "starts", "partitions", "offsets")
+    __slots__ = ("values", "starts", "partitions", "offsets", "topic")
 
-    def __init__(self, values, starts, partitions, offsets):
+    def __init__(self, values, starts, partitions, offsets, topic="topic"):
+        self.topic = topic
         self.values = values
         self.starts = starts
         self.partitions = partitions
@@ -225,7 +226,7 @@ class KafkaConsumer:
         base = starts[a]
         return PackedRecords(self._log.values[base:starts[b]],
                              (starts[a:b + 1] - base).astype(np.uint32),
-                             parts, offs)
+                             parts, offs, self._log.topic)
 
     # -- offsets -------------------------------------------------------------
     def position(self, tp):
@@ -249,6 +250,14 @@ class KafkaConsumer:
     def close(self, autocommit=True):
         self.closed = True
         self.close_autocommit = autocommit
+
+
+class PollOnlyConsumer(KafkaConsumer):
+    """Stub without the packed fast path: only what kafka-python itself offers."""
+
+    @property
+    def poll_packed(self):  # hasattr(consumer, "poll_packed") is False
+        raise AttributeError("poll_packed")
 
 
 def install() -> types.ModuleType:

@@ -199,8 +199,11 @@ class SlotEngine:
         return SlotOutput(tensors, arr, n)
 
     def process(self, slot: int, n: int, prev_slot: Optional[int], prev_out: Optional[SlotOutput],
-                resident: bool = False) -> SlotOutput:
-        """Launch the whole kernel sequence for ``slot`` on the current stream (asynchronous)."""
+                resident: bool = False, timers: Optional[list] = None) -> SlotOutput:
+        """Launch the whole kernel sequence for ``slot`` on the current stream (asynchronous).
+
+        ``timers``: when given, a (start, end) pair of CUDA events bracketing the
+        decode / collate kernel is appended (roofline measurement in bench.py)."""
         lib, ctx, st = self.lib, self.ctx, self._stream()
         sc = self.schema
         with torch.cuda.device(self.device):
@@ -217,6 +220,10 @@ class SlotEngine:
                 _native.check(lib.tk_raw_scan(ctx, slot, sc.record_bytes, st))
             _native.check(lib.tk_compact(ctx, slot, self.batch_size, st))
             _native.check(lib.tk_commit_offsets(ctx, slot, st))
+            if timers is not None:
+                ev0 = torch.cuda.Event(enable_timing=True)
+                ev1 = torch.cuda.Event(enable_timing=True)
+                ev0.record()
             if isinstance(sc, JsonArray):
                 P = out.planes
                 variable = sc.fixed_len is None
@@ -231,6 +238,9 @@ class SlotEngine:
             else:
                 _native.check(lib.tk_collate_raw(ctx, slot, sc.record_bytes, C.byref(out.planes[0]), st))
                 self.launches += LAUNCHES_PER_SLOT_RAW - 1
+            if timers is not None:
+                ev1.record()
+                timers.append((ev0, ev1))
             _native.check(lib.tk_slot_fetch_result(ctx, slot, st))
         return out
 

@@ -409,9 +409,12 @@ def main_gpu(args):
     e2e_log = syn.tile_log(base, reps) if reps > 1 else base
     e2e_log.records()
     barrier()
-    e2e_poll = run_e2e(e2e_log, steps, max(warmup, 3), device, packed=False)
-    barrier()
-    e2e_packed = run_e2e(e2e_log, steps, max(warmup, 3), device, packed=True)
+    if args.skip_e2e:
+        e2e_poll = e2e_packed = {"seconds": float("nan")}
+    else:
+        e2e_poll = run_e2e(e2e_log, steps, max(warmup, 3), device, packed=False)
+        barrier()
+        e2e_packed = run_e2e(e2e_log, steps, max(warmup, 3), device, packed=True)
     barrier()
 
     rec_per_step = len(base) / SLOT_BATCHES
@@ -488,6 +491,7 @@ def main():
     ap.add_argument("--warmup", type=int, default=16)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--no-cpu", action="store_true", help="skip the in-line cpu_baseline leg")
+    ap.add_argument("--skip-e2e", action="store_true", help="device-resident leg only (profiling runs)")
     args = ap.parse_args()
     if args.impl == "reference":
         return main_reference(args)

@@ -110,6 +110,11 @@ int tk_slot_pack(tk_ctx* ctx, int slot, uint32_t first_record, uint64_t first_by
                  const uint8_t* const* values, const uint32_t* lengths,
                  const int32_t* partitions, const int64_t* offsets, uint32_t n,
                  int n_threads, uint64_t* bytes_after);
+/* pack helper for a run that is already contiguous: values[starts[0] .. starts[n]) is copied
+ * (multi-threaded) behind first_byte and recs[first_record ..] are filled from the arrays */
+int tk_slot_fill(tk_ctx* ctx, int slot, uint32_t first_record, uint64_t first_byte,
+                 const uint8_t* values, const uint32_t* starts, const int32_t* partitions,
+                 const int64_t* offsets, uint32_t n, int n_threads, uint64_t* bytes_after);
 int tk_h2d_peak_gbs(int device, uint64_t bytes, int iters, double* gbs_out);
 
 /* ---- K1a/K1b phase 1: element count per record + keep flag -----------------

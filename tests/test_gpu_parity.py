@@ -38,6 +38,14 @@ def test_cfg2_small_slots_many_carries():
     check(log, JsonArray(torch.float32, max_len=256, min_size=32), 256, slot_bytes=96 << 10)
 
 
+def test_cfg2_same_thread_producer_and_poll_objects():
+    log = syn.make_log(2, 1500, seed=13, layout="chunked", chunk=100)
+    sc = JsonArray(torch.float32, max_len=256, min_size=32)
+    check(log, sc, 256, slot_bytes=512 << 10, device_producer_thread=False)
+    check(log, sc, 256, slot_bytes=512 << 10, use_packed=False)
+    check(log, sc, 256, slot_bytes=512 << 10, use_packed=False, device_producer_thread=False)
+
+
 def test_cfg2_float64():
     log = syn.make_log(2, 1200, seed=4)
     check(log, JsonArray(torch.float64, max_len=256, min_size=32), 128)

@@ -59,6 +59,8 @@ _SIGNATURES = {
     "tk_slot_wait": (C.c_int, [C.c_void_p, C.c_int, C.c_void_p]),
     "tk_slot_pack": (C.c_int, [C.c_void_p, C.c_int, C.c_uint32, C.c_uint64, C.c_void_p, C.c_void_p,
                                C.c_void_p, C.c_void_p, C.c_uint32, C.c_int, _p(C.c_uint64)]),
+    "tk_slot_fill": (C.c_int, [C.c_void_p, C.c_int, C.c_uint32, C.c_uint64, C.c_void_p, C.c_void_p,
+                               C.c_void_p, C.c_void_p, C.c_uint32, C.c_int, _p(C.c_uint64)]),
     "tk_h2d_peak_gbs": (C.c_int, [C.c_int, C.c_uint64, C.c_int, _p(C.c_double)]),
     "tk_json_scan": (C.c_int, [C.c_void_p, C.c_int, C.c_uint32, C.c_uint32, C.c_void_p]),
     "tk_raw_scan": (C.c_int, [C.c_void_p, C.c_int, C.c_uint64, C.c_void_p]),

@@ -11,7 +11,103 @@
 #include <vector>
 #include "tk_internal.h"
 
+#include <condition_variable>
+#include <functional>
+#include <mutex>
+
 static thread_local char g_err[1024] = "";
+
+// ---------------------------------------------------------------- host copy pool
+// Persistent worker threads for the pinned-memory pack: one core's memcpy (~10 GB/s)
+// is far below the H2D link (~55 GB/s), so the payload copy is split across threads
+// (SURVEY.md §7 hard part 1).  Callers run with the GIL released (ctypes).
+class CopyPool {
+public:
+    explicit CopyPool(int n) : stop_(false), pending_(0), gen_(0) {
+        for (int i = 0; i < n; ++i) workers_.emplace_back([this, i]() { loop(i); });
+    }
+    ~CopyPool() {
+        { std::lock_guard<std::mutex> g(m_); stop_ = true; ++gen_; }
+        cv_.notify_all();
+        for (auto& t : workers_) t.join();
+    }
+    int size() const { return (int)workers_.size(); }
+    // run fn(part) for part in [0, parts) on the pool (+ the calling thread), wait for all
+    void run(int parts, const std::function<void(int)>& fn) {
+        if (parts <= 1 || workers_.empty()) { for (int p = 0; p < parts; ++p) fn(p); return; }
+        std::lock_guard<std::mutex> serial(run_m_);
+        {
+            std::lock_guard<std::mutex> g(m_);
+            fn_ = &fn; parts_ = parts; next_ = 0; pending_ = parts; ++gen_;
+        }
+        cv_.notify_all();
+        work();
+        std::unique_lock<std::mutex> g(m_);
+        done_cv_.wait(g, [this]() { return pending_ == 0; });
+        fn_ = nullptr;
+    }
+private:
+    void work() {
+        for (;;) {
+            int p;
+            {
+                std::lock_guard<std::mutex> g(m_);
+                if (!fn_ || next_ >= parts_) return;
+                p = next_++;
+            }
+            (*fn_)(p);
+            {
+                std::lock_guard<std::mutex> g(m_);
+                if (--pending_ == 0) done_cv_.notify_all();
+            }
+        }
+    }
+    void loop(int) {
+        unsigned long seen = 0;
+        for (;;) {
+            {
+                std::unique_lock<std::mutex> g(m_);
+                cv_.wait(g, [&]() { return gen_ != seen; });
+                seen = gen_;
+                if (stop_) return;
+            }
+            work();
+        }
+    }
+    std::vector<std::thread> workers_;
+    std::mutex m_, run_m_;
+    std::condition_variable cv_, done_cv_;
+    const std::function<void(int)>* fn_ = nullptr;
+    int parts_ = 0, next_ = 0;
+    bool stop_;
+    int pending_;
+    unsigned long gen_;
+};
+
+static CopyPool* g_pool = nullptr;
+static std::mutex g_pool_m;
+
+static CopyPool* copy_pool(int threads) {
+    std::lock_guard<std::mutex> g(g_pool_m);
+    if (!g_pool || g_pool->size() < threads - 1) {
+        delete g_pool;
+        g_pool = new CopyPool(threads > 1 ? threads - 1 : 0);
+    }
+    return g_pool;
+}
+
+static void parallel_memcpy(uint8_t* dst, const uint8_t* src, uint64_t n, int threads) {
+    if (threads < 1) threads = 1;
+    if (threads > 64) threads = 64;
+    if (n < (4u << 20) || threads == 1) { memcpy(dst, src, n); return; }
+    const uint64_t chunk = ((n + threads - 1) / threads + 4095) & ~4095ull;
+    const int parts = (int)((n + chunk - 1) / chunk);
+    copy_pool(threads)->run(parts, [=](int p) {
+        const uint64_t a = (uint64_t)p * chunk;
+        const uint64_t b = a + chunk < n ? a + chunk : n;
+        memcpy(dst + a, src + a, b - a);
+    });
+}
 
 void tk_set_error(const char* fmt, ...) {
     va_list ap;
@@ -215,24 +311,46 @@ extern "C" int tk_slot_pack(tk_ctx* ctx, int slot, uint32_t first_record, uint64
     if (total < (1u << 20) || n_threads == 1) {
         for (uint32_t i = 0; i < n; ++i) memcpy(s.h_bytes + s.h_recs[first_record + i].start, values[i], lengths[i]);
     } else {
-        std::vector<std::thread> pool;
+        // record ranges of similar byte volume, one range per part
+        std::vector<uint32_t> cut(n_threads + 1, n);
+        cut[0] = 0;
         uint32_t a = 0;
-        for (int t = 0; t < n_threads; ++t) {
-            const uint64_t want = first_byte + total * (uint64_t)(t + 1) / n_threads;
-            uint32_t b = a;
-            while (b < n && s.h_recs[first_record + b].start < want) ++b;
-            if (t == n_threads - 1) b = n;
-            if (b > a) {
-                pool.emplace_back([&s, values, lengths, first_record, a, b]() {
-                    for (uint32_t i = a; i < b; ++i)
-                        memcpy(s.h_bytes + s.h_recs[first_record + i].start, values[i], lengths[i]);
-                });
-            }
-            a = b;
+        for (int t = 1; t < n_threads; ++t) {
+            const uint64_t want = first_byte + total * (uint64_t)t / n_threads;
+            while (a < n && s.h_recs[first_record + a].start < want) ++a;
+            cut[t] = a;
         }
-        for (auto& th : pool) th.join();
+        tk_slot* sp = &s;
+        copy_pool(n_threads)->run(n_threads, [=](int t) {
+            for (uint32_t i = cut[t]; i < cut[t + 1]; ++i)
+                memcpy(sp->h_bytes + sp->h_recs[first_record + i].start, values[i], lengths[i]);
+        });
     }
     if (bytes_after) *bytes_after = pos;
+    return 0;
+}
+
+extern "C" int tk_slot_fill(tk_ctx* ctx, int slot, uint32_t first_record, uint64_t first_byte,
+                            const uint8_t* values, const uint32_t* starts, const int32_t* partitions,
+                            const int64_t* offsets, uint32_t n, int n_threads, uint64_t* bytes_after) {
+    int rc = tk_check_slot(ctx, slot); if (rc) return rc;
+    tk_slot& s = ctx->slots[slot];
+    TK_REQUIRE((uint64_t)first_record + n <= ctx->slot_records, "fill: record capacity exceeded");
+    const uint64_t base = starts[0];
+    const uint64_t total = (uint64_t)starts[n] - base;
+    TK_REQUIRE(first_byte + total <= ctx->slot_bytes, "fill: byte capacity exceeded");
+    for (uint32_t i = 0; i < n; ++i) {
+        tk_rec_t& r = s.h_recs[first_record + i];
+        r.start = (uint32_t)(first_byte + (starts[i] - base));
+        r.partition = partitions[i];
+        r.offset = offsets[i];
+    }
+    tk_rec_t& last = s.h_recs[first_record + n];
+    last.start = (uint32_t)(first_byte + total);
+    last.partition = 0;
+    last.offset = 0;
+    parallel_memcpy(s.h_bytes + first_byte, values + base, total, n_threads);
+    if (bytes_after) *bytes_after = first_byte + total;
     return 0;
 }
 

@@ -117,6 +117,13 @@ class SlotEngine:
                 _native.check(self.lib.tk_image_set_norm(self.ctx, schema.channels, mean, std,
                                                          self._stream()))
         self.launches = 0
+        import os
+        try:
+            cores = len(os.sched_getaffinity(0))
+        except AttributeError:  # pragma: no cover
+            cores = os.cpu_count() or 1
+        #: threads used by the pinned-memory pack (payload memcpy)
+        self.pack_threads = max(1, min(8, cores // 2))
 
     # ------------------------------------------------------------------ plumbing
     def _stream(self):
@@ -150,19 +157,33 @@ class SlotEngine:
 
     def fill_packed(self, slot: int, values: np.ndarray, starts: np.ndarray,
                     partitions: np.ndarray, offsets: np.ndarray):
-        """Copy a packed run of records (CSR arrays) into the slot's pinned memory."""
+        """Copy a packed run of records (CSR arrays) into the slot's pinned memory
+        (tk_slot_fill: headers in C, payload memcpy on several threads, GIL released)."""
         n = len(partitions)
         nbytes = int(starts[n]) - int(starts[0])
         if n > self.slot_records or nbytes > self.slot_bytes:
             raise ValueError(f"run of {n} records / {nbytes} bytes exceeds the slot "
                              f"({self.slot_records} records / {self.slot_bytes} bytes)")
-        hb, hr = self.host_views(slot)
-        # ctypes.memmove releases the GIL, numpy slicing assignment does for large copies too
-        hb[:nbytes] = values[:nbytes] if len(values) == nbytes else values[int(starts[0]):int(starts[n])]
-        hr["start"][:n + 1] = starts[:n + 1] - starts[0]
-        hr["partition"][:n] = partitions
-        hr["offset"][:n] = offsets
+        values = np.ascontiguousarray(values, dtype=np.uint8)
+        starts = np.ascontiguousarray(starts, dtype=np.uint32)
+        partitions = np.ascontiguousarray(partitions, dtype=np.int32)
+        offsets = np.ascontiguousarray(offsets, dtype=np.int64)
+        if len(values) != nbytes and int(starts[0]) == 0:
+            values = values[:nbytes]
+        after = C.c_uint64()
+        _native.check(self.lib.tk_slot_fill(self.ctx, slot, 0, 0, values.ctypes.data, starts.ctypes.data,
+                                            partitions.ctypes.data, offsets.ctypes.data, n,
+                                            self.pack_threads, C.byref(after)))
         return n, nbytes
+
+    def pack_pointers(self, slot: int, ptrs: np.ndarray, lens: np.ndarray, partitions: np.ndarray,
+                      offsets: np.ndarray, n: int) -> int:
+        """Gather n values given by (address, length) into the slot (tk_slot_pack)."""
+        after = C.c_uint64()
+        _native.check(self.lib.tk_slot_pack(self.ctx, slot, 0, 0, ptrs.ctypes.data, lens.ctypes.data,
+                                            partitions.ctypes.data, offsets.ctypes.data, n,
+                                            self.pack_threads, C.byref(after)))
+        return int(after.value)
 
     def submit(self, slot: int, n: int, nbytes: int):
         _native.check(self.lib.tk_slot_submit(self.ctx, slot, n, nbytes))

@@ -27,6 +27,7 @@ Two things differ from the reference on purpose, both on the schema path only:
 """
 from __future__ import annotations
 
+import contextlib
 import logging
 import os
 import signal
@@ -90,6 +91,8 @@ class KafkaDataset(IterableDataset):
     device_slots = 3
     device_index = None
     max_partitions = 64
+    #: poll + pack + H2D on a producer thread (overlaps the user's loop); False = same thread
+    device_producer_thread = True
 
     def __init__(self, *args, **kwargs):
         self._worker_id = None          # set by init_worker inside a DataLoader worker
@@ -152,8 +155,12 @@ class KafkaDataset(IterableDataset):
             _logger.debug("Committing offsets.")
         try:
             if self._explicit_offsets is not None:
-                # GPU path: exactly the records up to the delivered batch, never the read-ahead
-                self._consumer.commit(self._explicit_offsets)
+                # GPU path: exactly the records up to the delivered batch, never the read-ahead;
+                # serialised with the producer thread's poll() (the consumer is not thread safe)
+                pipe = self._pipeline
+                lock = pipe.consumer_lock if pipe is not None else contextlib.nullcontext()
+                with lock:
+                    self._consumer.commit(self._explicit_offsets)
             else:
                 self._consumer.commit()
         except _commit_failed_types():
@@ -209,6 +216,7 @@ class KafkaDataset(IterableDataset):
             self._consumer, self.payload_schema, batch_size=batch_size, drop_last=drop_last,
             slot_bytes=self.device_slot_bytes, n_slots=self.device_slots,
             device=self.device_index, max_partitions=self.max_partitions,
+            threaded=self.device_producer_thread,
         )
         return self._pipeline
 
@@ -223,6 +231,7 @@ class KafkaDataset(IterableDataset):
         if self.payload_schema is None:
             raise RuntimeError("device_batches() needs a payload_schema.")
         pipe = self._open_pipeline(int(batch_size), bool(drop_last))
+        self._explicit_offsets = None
         try:
             for batch, offsets in pipe:
                 self._explicit_offsets = offsets

@@ -16,11 +16,15 @@ batch in single-process mode (``src/auto_commit.py:55-58``)
 from __future__ import annotations
 
 import collections
+import contextlib
+import queue
 import sys
+import threading
 from typing import Dict, Optional
 
 import numpy as np
 
+from . import _tkpack      # CPython helper built next to libtorchkafka_b200.so (csrc/tk_pymod.cpp)
 from .engine import SlotEngine
 from .schema import PayloadError
 
@@ -65,29 +69,52 @@ class _Pending:
 class IngestPipeline:
     def __init__(self, consumer, schema, batch_size: int, drop_last: bool = False,
                  slot_bytes: int = 64 << 20, n_slots: int = 3, device: Optional[int] = None,
-                 max_partitions: int = 64, poll_timeout_ms: int = 100, max_empty_polls: int = 1):
+                 max_partitions: int = 64, poll_timeout_ms: int = 100, max_empty_polls: int = 1,
+                 threaded: bool = True):
         self.consumer = consumer
         self.schema = schema
         self.batch_size = int(batch_size)
         self.drop_last = bool(drop_last)
-        self.engine = SlotEngine(schema, batch_size, slot_bytes=slot_bytes, n_slots=n_slots,
+        self.engine = SlotEngine(schema, batch_size, slot_bytes=slot_bytes, n_slots=max(n_slots, 2),
                                  device=device, n_partitions=max_partitions)
         self.poll_timeout_ms = poll_timeout_ms
         self.max_empty_polls = max_empty_polls
+        self.threaded = bool(threaded)
+        #: serialises consumer calls: the producer thread polls, the user's thread commits,
+        #: and kafka-python consumers are not safe for concurrent calls
+        self.consumer_lock = threading.Lock()
         self._mk_offset = _offset_struct()
         self._tp_cls = _tp_struct()
         self._tp_of: Dict[int, object] = {}        # dense partition index -> TopicPartition
         self._dense_of: Dict[object, int] = {}     # TopicPartition -> dense index
         self._packed = hasattr(consumer, "poll_packed")
-        self._leftover = None                      # records polled but not fitting the last slot
+        self._leftover = []                        # (tp, records) polled but not fitting the last slot
+        self._field_idx = {}                       # record type -> (value index, offset index)
+        cap = self.engine.slot_records
+        self._ptrs = np.zeros(cap, np.uint64)
+        self._lens = np.zeros(cap, np.uint32)
+        self._offs = np.zeros(cap, np.int64)
+        self._parts = np.zeros(cap, np.int32)
         self._closed = False
+        self._stop = threading.Event()
+        self._thread = None
+        self._free_q = None
         self.stats = collections.Counter()
 
     # ------------------------------------------------------------------ lifecycle
     def close(self):
-        if not self._closed:
-            self._closed = True
-            self.engine.close()
+        if self._closed:
+            return
+        self._closed = True
+        self._stop.set()
+        if self._thread is not None:
+            try:
+                self._free_q.put_nowait(None)
+            except Exception:
+                pass
+            self._thread.join(timeout=30)
+            self._thread = None
+        self.engine.close()
 
     # ------------------------------------------------------------------ host side: poll + pack
     def _dense(self, tp) -> int:
@@ -104,7 +131,8 @@ class IngestPipeline:
 
     def _fill_from_packed(self, slot: int):
         eng = self.engine
-        run = self.consumer.poll_packed(eng.slot_records, eng.slot_bytes)
+        with self.consumer_lock:
+            run = self.consumer.poll_packed(eng.slot_records, eng.slot_bytes)
         if run is None or len(run) == 0:
             return 0, 0, None, None
         topic = getattr(run, "topic", None) or "topic"
@@ -121,68 +149,75 @@ class IngestPipeline:
         n, nbytes = eng.fill_packed(slot, run.values, run.starts, parts, run.offsets)
         return n, nbytes, parts, np.asarray(run.offsets)
 
+    def _indices(self, rec):
+        """(value index, offset index) for tuple-like records, (-1, -1) for attribute access."""
+        t = type(rec)
+        idx = self._field_idx.get(t)
+        if idx is None:
+            fields = getattr(t, "_fields", None)
+            if isinstance(rec, tuple) and fields and "value" in fields and "offset" in fields:
+                idx = (fields.index("value"), fields.index("offset"))
+            else:
+                idx = (-1, -1)
+            self._field_idx[t] = idx
+        return idx
+
     def _fill_from_poll(self, slot: int):
-        """Flatten ``consumer.poll()`` results (dict order, list order == iterator order)."""
+        """Flatten ``consumer.poll()`` results (dict order, list order == iterator order).
+
+        Per record only ~25 ns of C run under the GIL (``_tkpack.harvest``: address, length
+        and offset of each value); the payload bytes are then gathered into pinned memory by
+        ``tk_slot_pack`` on several threads with the GIL released.
+        """
         eng = self.engine
-        hb, hr = eng.host_views(slot)
+        ptrs, lens, offs, parts = self._ptrs, self._lens, self._offs, self._parts
         n = 0
         nbytes = 0
         empty = 0
-        parts_acc, offs_acc = [], []
+        hold = []                       # keeps the record objects (and their bytes) alive until packed
         full = False
         while not full and n < eng.slot_records:
             if self._leftover:
                 items, self._leftover = self._leftover, []
             else:
-                room = eng.slot_records - n
-                polled = self.consumer.poll(timeout_ms=self.poll_timeout_ms,
-                                            max_records=min(room, 1 << 16))
+                with self.consumer_lock:
+                    polled = self.consumer.poll(timeout_ms=self.poll_timeout_ms,
+                                                max_records=min(eng.slot_records - n, 1 << 16))
                 if not polled:
                     empty += 1
-                    if n > 0 or empty >= self.max_empty_polls:
+                    if n > 0 or empty >= self.max_empty_polls or self._stop.is_set():
                         break
                     continue
                 items = list(polled.items())
             for k, (tp, recs) in enumerate(items):
+                if not recs:
+                    continue
                 d = self._dense(tp)
-                vals = [r.value for r in recs]
-                lens = np.fromiter(map(len, vals), dtype=np.int64, count=len(vals))
-                take = len(vals)
-                tot = int(lens.sum())
-                if n + take > eng.slot_records or nbytes + tot > eng.slot_bytes:
-                    # the slot is full inside this partition's run: split it, keep the rest
-                    # (records cannot be un-polled) in consumption order for the next slot
-                    cum = np.cumsum(lens)
-                    take = int(min(np.searchsorted(cum, eng.slot_bytes - nbytes, side="right"),
-                                   eng.slot_records - n))
-                    if take == 0 and n == 0:
-                        raise ValueError(
-                            f"a single record of {int(lens[0])} bytes exceeds the slot size")
-                    self._leftover = [(tp, recs[take:])] + items[k + 1:]
-                    vals, lens, recs = vals[:take], lens[:take], recs[:take]
-                    tot = int(lens.sum())
+                vi, oi = self._indices(recs[0])
+                taken, tot, keep = _tkpack.harvest(
+                    recs, vi, oi, 0, eng.slot_records - n, eng.slot_bytes - nbytes,
+                    ptrs.ctypes.data + 8 * n, lens.ctypes.data + 4 * n, offs.ctypes.data + 8 * n)
+                hold.append(recs)
+                if keep is not None:
+                    hold.append(keep)
+                parts[n:n + taken] = d
+                n += taken
+                nbytes += tot
+                if taken < len(recs):
+                    # the slot is full inside this partition's run: records cannot be un-polled,
+                    # so the rest waits, in consumption order, for the next slot
+                    if taken == 0 and n == 0:
+                        raise ValueError("a single record exceeds the slot size "
+                                         f"({eng.slot_bytes} bytes); raise device_slot_bytes")
+                    self._leftover = [(tp, recs[taken:])] + items[k + 1:]
                     full = True
-                if take:
-                    hb[nbytes:nbytes + tot] = np.frombuffer(b"".join(vals), dtype=np.uint8)
-                    starts = np.empty(take, np.int64)
-                    starts[0] = nbytes
-                    if take > 1:
-                        np.cumsum(lens[:-1], out=starts[1:])
-                        starts[1:] += nbytes
-                    hr["start"][n:n + take] = starts
-                    hr["partition"][n:n + take] = d
-                    offs = np.fromiter((r.offset for r in recs), dtype=np.int64, count=take)
-                    hr["offset"][n:n + take] = offs
-                    parts_acc.append(np.full(take, d, np.int32))
-                    offs_acc.append(offs)
-                    n += take
-                    nbytes += tot
-                if full:
                     break
         if n == 0:
             return 0, 0, None, None
-        hr["start"][n] = nbytes
-        return n, nbytes, np.concatenate(parts_acc), np.concatenate(offs_acc)
+        after = eng.pack_pointers(slot, ptrs, lens, parts, offs, n)
+        assert after == nbytes
+        del hold
+        return n, nbytes, parts[:n].copy(), offs[:n].copy()
 
     # ------------------------------------------------------------------ iteration
     def _error(self, item, res) -> PayloadError:
@@ -197,21 +232,76 @@ class IngestPipeline:
         tp_of = self._tp_of
         return {tp_of[int(p)]: mk(int(column[p])) for p in np.flatnonzero(column >= 0)}
 
+    def _produce(self, free_q, filled_q):
+        """Producer thread: poll + pack + submit (H2D) slot after slot."""
+        fill = self._fill_from_packed if self._packed else self._fill_from_poll
+        try:
+            while not self._stop.is_set():
+                slot = free_q.get()
+                if slot is None or self._stop.is_set():
+                    break
+                n, nbytes, parts, offs = fill(slot)
+                if n == 0:
+                    break
+                self.engine.submit(slot, n, nbytes)
+                filled_q.put((slot, n, nbytes, parts, offs))
+            filled_q.put(None)
+        except BaseException as exc:  # forwarded to the consuming thread
+            filled_q.put(exc)
+
+    def _filled_slots(self):
+        """Generator of (slot, n, nbytes, partitions, offsets) in consumption order, plus the
+        callable that hands a drained slot back."""
+        eng = self.engine
+        if not self.threaded:
+            fill = self._fill_from_packed if self._packed else self._fill_from_poll
+            free = collections.deque(range(eng.n_slots))
+
+            def gen():
+                while True:
+                    slot = free.popleft()       # never empty: pending depth < n_slots
+                    n, nbytes, parts, offs = fill(slot)
+                    if n == 0:
+                        return
+                    eng.submit(slot, n, nbytes)
+                    yield slot, n, nbytes, parts, offs
+
+            return gen(), free.append
+        free_q = queue.Queue()
+        filled_q = queue.Queue()
+        for s in range(eng.n_slots):
+            free_q.put(s)
+        self._free_q = free_q
+        self._thread = threading.Thread(target=self._produce, args=(free_q, filled_q),
+                                        name="torchkafka-producer", daemon=True)
+        self._thread.start()
+
+        def gen():
+            while True:
+                item = filled_q.get()
+                if item is None:
+                    return
+                if isinstance(item, BaseException):
+                    raise item
+                yield item
+
+        return gen(), free_q.put
+
     def __iter__(self):
         eng = self.engine
         B = self.batch_size
-        fill = self._fill_from_packed if self._packed else self._fill_from_poll
         self._leftover = []
         pending = collections.deque()
-        depth = max(1, eng.n_slots - 1)
+        depth = max(1, eng.n_slots - 2) if self.threaded else max(1, eng.n_slots - 1)
         prev_slot, prev_out = None, None
         open_lmax = 0                  # longest record among the rows of the open batch
         last = None                    # (_Pending, SlotResult) of the most recent drained slot
-        cursor = 0
+        slots, release = self._filled_slots()
 
         def drain(item):
             nonlocal open_lmax, last
             res = eng.result(item.slot)
+            release(item.slot)         # pinned memory is reusable: H2D and kernels are done
             self.stats["records"] += res.n_records
             self.stats["kept"] += res.n_kept
             err_rec = res.first_error_rec if res.n_errors else None
@@ -230,19 +320,13 @@ class IngestPipeline:
             open_lmax = max(open_lmax, tail_lmax) if res.n_closed == 0 else tail_lmax
             last = (item, res)
 
-        while True:
-            slot = cursor % eng.n_slots
-            n, nbytes, parts, offs = fill(slot)
-            if n == 0:
-                break
-            eng.submit(slot, n, nbytes)
+        for slot, n, nbytes, parts, offs in slots:
             out = eng.process(slot, n, prev_slot, prev_out)
             pending.append(_Pending(slot, n, out, parts, offs))
             prev_slot, prev_out = slot, out
-            cursor += 1
             self.stats["slots"] += 1
             self.stats["bytes"] += nbytes
-            if len(pending) >= depth:
+            if len(pending) > depth:
                 yield from drain(pending.popleft())
         while pending:
             yield from drain(pending.popleft())

@@ -103,6 +103,7 @@ class RecordLog:
         self.offsets = np.asarray(offsets, dtype=np.int64)
         self._byte_values = list(values)
         self._records: Optional[List[ConsumerRecord]] = None
+        self._bounds = None
 
     def __len__(self):
         return len(self.partitions)
@@ -119,6 +120,13 @@ class RecordLog:
                 for v, p, o in zip(self._byte_values, self.partitions, self.offsets)
             ]
         return self._records
+
+    def run_bounds(self) -> np.ndarray:
+        """Indices i > 0 where partitions[i] != partitions[i-1] (starts of partition runs)."""
+        if getattr(self, "_bounds", None) is None:
+            p = self.partitions
+            self._bounds = (np.flatnonzero(p[1:] != p[:-1]) + 1) if len(p) > 1 else np.zeros(0, np.int64)
+        return self._bounds
 
     def select_partitions(self, keep) -> "RecordLog":
         """Sub-log holding only partitions for which ``keep(p)`` is true."""
@@ -177,21 +185,20 @@ class KafkaConsumer:
             return {}
         limit = n - self._cursor if max_records is None else min(max_records, n - self._cursor)
         recs = self._log.records()
+        bounds = self._log.run_bounds()          # indices where the partition changes
         out: Dict[TopicPartition, List[ConsumerRecord]] = {}
-        last_p = None
         i = self._cursor
         end = self._cursor + limit
         parts = self._log.partitions
+        k = int(np.searchsorted(bounds, i, side="right"))
         while i < end:
-            p = int(parts[i])
-            if p != last_p:
-                tp = TopicPartition(self._log.topic, p)
-                if tp in out:
-                    break  # would re-open a partition: stop, keep order exact
-                out[tp] = []
-                last_p = p
-            out[tp].append(recs[i])
-            i += 1
+            stop = min(int(bounds[k]) if k < len(bounds) else n, end)
+            tp = TopicPartition(self._log.topic, int(parts[i]))
+            if tp in out:
+                break  # would re-open a partition: stop, keep order exact
+            out[tp] = recs[i:stop]
+            i = stop
+            k += 1
         if update_offsets:
             for tp, lst in out.items():
                 self._positions[tp.partition] = lst[-1].offset + 1

@@ -268,7 +268,8 @@ def run_e2e(log, steps, warmup, device, packed):
             t1 = time.perf_counter()
             break
     assert t1 is not None, f"log too short: {seen} batches for warmup {warmup} + steps {steps}"
-    stats = dict(ds._pipeline.stats) if ds._pipeline is not None else {}
+    stats = dict(ds._pipeline.stats) if ds._pipeline is not None else dict(ds.last_pipeline_stats)
+    print("e2e", "packed" if packed else "poll", {k: (round(v, 4) if isinstance(v, float) else v) for k, v in stats.items()}, file=sys.stderr, flush=True)
     ds.close()
     return {"seconds": t1 - t0, "checksum": checksum, "stats": stats}
 
@@ -487,8 +488,8 @@ def main_gpu(args):
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=64)
-    ap.add_argument("--warmup", type=int, default=16)
+    ap.add_argument("--steps", type=int, default=512)
+    ap.add_argument("--warmup", type=int, default=64)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--no-cpu", action="store_true", help="skip the in-line cpu_baseline leg")
     ap.add_argument("--skip-e2e", action="store_true", help="device-resident leg only (profiling runs)")

@@ -308,10 +308,31 @@ class SlotEngine:
             if sc.fixed_len is not None:
                 return t[0][first_row:first_row + n_rows]
             width = sc.max_len if sc.pad_to_max_len else max(int(lmax), 0)
+            if width == sc.max_len:
+                return sc.wrap(t[0][first_row:first_row + n_rows], t[1][first_row:first_row + n_rows],
+                               t[2][first_row:first_row + n_rows])
             return sc.wrap(t[0][first_row:first_row + n_rows, :width],
                            t[1][first_row:first_row + n_rows],
                            t[2][first_row:first_row + n_rows, :width])
         return t[0][first_row:first_row + n_rows]
+
+    def batch_views(self, out: SlotOutput, first_row: int, n_batches: int, lmax):
+        """All ``n_batches`` full batches of a slot at once (one unflatten + unbind per plane
+        instead of one slice per batch and plane)."""
+        B = self.batch_size
+        sc = self.schema
+        planes = [p[first_row:first_row + n_batches * B].unflatten(0, (n_batches, B)).unbind(0)
+                  for p in out.tensors]
+        if not (isinstance(sc, JsonArray) and sc.fixed_len is None):
+            return list(planes[0])
+        batches = []
+        for j in range(n_batches):
+            v, ln, m = planes[0][j], planes[1][j], planes[2][j]
+            width = sc.max_len if sc.pad_to_max_len else int(lmax[j])
+            if width != sc.max_len:
+                v, m = v[:, :width], m[:, :width]
+            batches.append(sc.wrap(v, ln, m))
+        return batches
 
     def error_for(self, slot: int, res: SlotResult, partitions, offsets) -> PayloadError:
         e = int(res.first_error_rec)

@@ -93,12 +93,17 @@ class KafkaDataset(IterableDataset):
     max_partitions = 64
     #: poll + pack + H2D on a producer thread (overlaps the user's loop); False = same thread
     device_producer_thread = True
+    device_producers = 2
+    #: send every assigned partition with each commit (reference behaviour) instead of only the
+    #: partitions whose position moved since the previous commit (same broker state, cheaper)
+    commit_all_partitions = False
 
     def __init__(self, *args, **kwargs):
         self._worker_id = None          # set by init_worker inside a DataLoader worker
         self._commit_required = False   # raised by the signal handler, cleared after each commit
         self._explicit_offsets = None   # {TopicPartition: OffsetAndMetadata} of the last device batch
         self._pipeline = None
+        self.last_pipeline_stats = {}
         if kwargs.get("_is_placeholder", False):
             self._consumer = None
             return
@@ -159,8 +164,12 @@ class KafkaDataset(IterableDataset):
                 # serialised with the producer thread's poll() (the consumer is not thread safe)
                 pipe = self._pipeline
                 lock = pipe.consumer_lock if pipe is not None else contextlib.nullcontext()
+                pending = self._explicit_offsets
                 with lock:
-                    self._consumer.commit(self._explicit_offsets)
+                    self._consumer.commit(pending)
+                # committed: start a fresh accumulation (a failed commit keeps its entries)
+                if self._explicit_offsets is pending:
+                    self._explicit_offsets = {}
             else:
                 self._consumer.commit()
         except _commit_failed_types():
@@ -216,7 +225,8 @@ class KafkaDataset(IterableDataset):
             self._consumer, self.payload_schema, batch_size=batch_size, drop_last=drop_last,
             slot_bytes=self.device_slot_bytes, n_slots=self.device_slots,
             device=self.device_index, max_partitions=self.max_partitions,
-            threaded=self.device_producer_thread,
+            threaded=self.device_producer_thread, n_producers=self.device_producers,
+            commit_all_partitions=self.commit_all_partitions,
         )
         return self._pipeline
 
@@ -233,10 +243,14 @@ class KafkaDataset(IterableDataset):
         pipe = self._open_pipeline(int(batch_size), bool(drop_last))
         self._explicit_offsets = None
         try:
+            self._explicit_offsets = {}
             for batch, offsets in pipe:
-                self._explicit_offsets = offsets
+                # offsets list the partitions that moved with this batch; merge them so that a
+                # caller who commits every few batches still commits everything consumed so far
+                self._explicit_offsets.update(offsets)
                 yield batch
         finally:
+            self.last_pipeline_stats = dict(pipe.stats)
             pipe.close()
             if self._pipeline is pipe:
                 self._pipeline = None

@@ -20,6 +20,7 @@ import contextlib
 import queue
 import sys
 import threading
+import time
 from typing import Dict, Optional
 
 import numpy as np
@@ -70,12 +71,14 @@ class IngestPipeline:
     def __init__(self, consumer, schema, batch_size: int, drop_last: bool = False,
                  slot_bytes: int = 64 << 20, n_slots: int = 3, device: Optional[int] = None,
                  max_partitions: int = 64, poll_timeout_ms: int = 100, max_empty_polls: int = 1,
-                 threaded: bool = True):
+                 threaded: bool = True, commit_all_partitions: bool = False,
+                 n_producers: int = 2):
         self.consumer = consumer
         self.schema = schema
         self.batch_size = int(batch_size)
         self.drop_last = bool(drop_last)
-        self.engine = SlotEngine(schema, batch_size, slot_bytes=slot_bytes, n_slots=max(n_slots, 2),
+        self.engine = SlotEngine(schema, batch_size, slot_bytes=slot_bytes,
+                                 n_slots=max(n_slots, 2 + (int(n_producers) if threaded else 0)),
                                  device=device, n_partitions=max_partitions)
         self.poll_timeout_ms = poll_timeout_ms
         self.max_empty_polls = max_empty_polls
@@ -90,14 +93,14 @@ class IngestPipeline:
         self._packed = hasattr(consumer, "poll_packed")
         self._leftover = []                        # (tp, records) polled but not fitting the last slot
         self._field_idx = {}                       # record type -> (value index, offset index)
-        cap = self.engine.slot_records
-        self._ptrs = np.zeros(cap, np.uint64)
-        self._lens = np.zeros(cap, np.uint32)
-        self._offs = np.zeros(cap, np.int64)
-        self._parts = np.zeros(cap, np.int32)
+        self.n_producers = max(1, int(n_producers))
+        self._threads = []
+        self._seq = 0
+        self._eof = False
+        self._last_column = None
+        self.commit_all_partitions = bool(commit_all_partitions)
         self._closed = False
         self._stop = threading.Event()
-        self._thread = None
         self._free_q = None
         self.stats = collections.Counter()
 
@@ -107,13 +110,14 @@ class IngestPipeline:
             return
         self._closed = True
         self._stop.set()
-        if self._thread is not None:
+        if self._threads:
             try:
                 self._free_q.put_nowait(None)
             except Exception:
                 pass
-            self._thread.join(timeout=30)
-            self._thread = None
+            for t in self._threads:
+                t.join(timeout=30)
+            self._threads = []
         self.engine.close()
 
     # ------------------------------------------------------------------ host side: poll + pack
@@ -129,12 +133,16 @@ class IngestPipeline:
             self._tp_of[d] = tp
         return d
 
-    def _fill_from_packed(self, slot: int):
+    # Both consumer protocols are split in two phases so that several producer threads can
+    # work on different slots: _gather_* talks to the consumer (serialised, in consumption
+    # order), _pack_* moves the payload into pinned memory (parallel, GIL released).
+    def _gather_packed(self, slot: int, scratch):
         eng = self.engine
-        with self.consumer_lock:
-            run = self.consumer.poll_packed(eng.slot_records, eng.slot_bytes)
+        t0 = time.perf_counter()
+        run = self.consumer.poll_packed(eng.slot_records, eng.slot_bytes)
+        self.stats["t_poll"] += time.perf_counter() - t0
         if run is None or len(run) == 0:
-            return 0, 0, None, None
+            return 0, 0, None
         topic = getattr(run, "topic", None) or "topic"
         parts = np.asarray(run.partitions)
         # dense index == raw partition id on this path (single topic)
@@ -146,8 +154,14 @@ class IngestPipeline:
                 tp = self._tp_cls(topic, p)
                 self._tp_of[p] = tp
                 self._dense_of[tp] = p
-        n, nbytes = eng.fill_packed(slot, run.values, run.starts, parts, run.offsets)
-        return n, nbytes, parts, np.asarray(run.offsets)
+        return len(parts), int(run.starts[len(parts)]) - int(run.starts[0]), run
+
+    def _pack_packed(self, slot: int, scratch, n: int, run):
+        t0 = time.perf_counter()
+        parts = np.asarray(run.partitions)
+        n, nbytes = self.engine.fill_packed(slot, run.values, run.starts, parts, run.offsets)
+        self.stats["t_pack"] += time.perf_counter() - t0
+        return parts, np.asarray(run.offsets)
 
     def _indices(self, rec):
         """(value index, offset index) for tuple-like records, (-1, -1) for attribute access."""
@@ -162,15 +176,14 @@ class IngestPipeline:
             self._field_idx[t] = idx
         return idx
 
-    def _fill_from_poll(self, slot: int):
+    def _gather_poll(self, slot: int, scratch):
         """Flatten ``consumer.poll()`` results (dict order, list order == iterator order).
 
         Per record only ~25 ns of C run under the GIL (``_tkpack.harvest``: address, length
-        and offset of each value); the payload bytes are then gathered into pinned memory by
-        ``tk_slot_pack`` on several threads with the GIL released.
+        and offset of each value); the payload bytes are gathered afterwards by ``_pack_poll``.
         """
         eng = self.engine
-        ptrs, lens, offs, parts = self._ptrs, self._lens, self._offs, self._parts
+        ptrs, lens, offs, parts = scratch
         n = 0
         nbytes = 0
         empty = 0
@@ -180,9 +193,10 @@ class IngestPipeline:
             if self._leftover:
                 items, self._leftover = self._leftover, []
             else:
-                with self.consumer_lock:
-                    polled = self.consumer.poll(timeout_ms=self.poll_timeout_ms,
-                                                max_records=min(eng.slot_records - n, 1 << 16))
+                t0 = time.perf_counter()
+                polled = self.consumer.poll(timeout_ms=self.poll_timeout_ms,
+                                            max_records=min(eng.slot_records - n, 1 << 16))
+                self.stats["t_poll"] += time.perf_counter() - t0
                 if not polled:
                     empty += 1
                     if n > 0 or empty >= self.max_empty_polls or self._stop.is_set():
@@ -194,9 +208,11 @@ class IngestPipeline:
                     continue
                 d = self._dense(tp)
                 vi, oi = self._indices(recs[0])
+                t0 = time.perf_counter()
                 taken, tot, keep = _tkpack.harvest(
                     recs, vi, oi, 0, eng.slot_records - n, eng.slot_bytes - nbytes,
                     ptrs.ctypes.data + 8 * n, lens.ctypes.data + 4 * n, offs.ctypes.data + 8 * n)
+                self.stats["t_harvest"] += time.perf_counter() - t0
                 hold.append(recs)
                 if keep is not None:
                     hold.append(keep)
@@ -212,12 +228,20 @@ class IngestPipeline:
                     self._leftover = [(tp, recs[taken:])] + items[k + 1:]
                     full = True
                     break
-        if n == 0:
-            return 0, 0, None, None
-        after = eng.pack_pointers(slot, ptrs, lens, parts, offs, n)
-        assert after == nbytes
+        return n, nbytes, hold
+
+    def _pack_poll(self, slot: int, scratch, n: int, hold):
+        ptrs, lens, offs, parts = scratch
+        t0 = time.perf_counter()
+        self.engine.pack_pointers(slot, ptrs, lens, parts, offs, n)
+        self.stats["t_pack"] += time.perf_counter() - t0
         del hold
-        return n, nbytes, parts[:n].copy(), offs[:n].copy()
+        return parts[:n].copy(), offs[:n].copy()
+
+    def _new_scratch(self):
+        cap = self.engine.slot_records
+        return (np.zeros(cap, np.uint64), np.zeros(cap, np.uint32), np.zeros(cap, np.int64),
+                np.zeros(cap, np.int32))
 
     # ------------------------------------------------------------------ iteration
     def _error(self, item, res) -> PayloadError:
@@ -228,61 +252,109 @@ class IngestPipeline:
         return err
 
     def _offsets_map(self, column: np.ndarray):
+        """{TopicPartition: OffsetAndMetadata} to commit after a batch.
+
+        Only partitions whose position moved since the previous batch's map are listed
+        (``commit_all_partitions=False``): the broker's committed-offset table after the commit
+        is the same as with the full map the reference sends, at a fraction of the host cost.
+        """
         mk = self._mk_offset
         tp_of = self._tp_of
-        return {tp_of[int(p)]: mk(int(column[p])) for p in np.flatnonzero(column >= 0)}
+        prev = self._last_column
+        if prev is None or self.commit_all_partitions:
+            idx = np.flatnonzero(column >= 0)
+        else:
+            idx = np.flatnonzero(column != prev)
+        self._last_column = column
+        vals = column[idx].tolist()
+        return {tp_of[p]: mk(v) for p, v in zip(idx.tolist(), vals)}
 
-    def _produce(self, free_q, filled_q):
-        """Producer thread: poll + pack + submit (H2D) slot after slot."""
-        fill = self._fill_from_packed if self._packed else self._fill_from_poll
+    def _produce(self, free_q, deliver):
+        """Producer thread.  Gather (consumer calls, serialised, defines the slot order) then
+        pack + submit (parallel across producer threads)."""
+        gather = self._gather_packed if self._packed else self._gather_poll
+        pack = self._pack_packed if self._packed else self._pack_poll
+        scratch = self._new_scratch() if not self._packed else None
         try:
             while not self._stop.is_set():
                 slot = free_q.get()
                 if slot is None or self._stop.is_set():
-                    break
-                n, nbytes, parts, offs = fill(slot)
+                    free_q.put(None)            # let the sibling producers see it too
+                    return
+                with self.consumer_lock:
+                    if self._eof:
+                        return
+                    n, nbytes, token = gather(slot, scratch)
+                    seq = self._seq
+                    self._seq += 1
+                    if n == 0:
+                        self._eof = True
                 if n == 0:
-                    break
+                    deliver(seq, None)
+                    return
+                parts, offs = pack(slot, scratch, n, token)
                 self.engine.submit(slot, n, nbytes)
-                filled_q.put((slot, n, nbytes, parts, offs))
-            filled_q.put(None)
+                deliver(seq, (slot, n, nbytes, parts, offs))
         except BaseException as exc:  # forwarded to the consuming thread
-            filled_q.put(exc)
+            with self._cv:
+                self._failure = exc
+                self._cv.notify_all()
 
     def _filled_slots(self):
         """Generator of (slot, n, nbytes, partitions, offsets) in consumption order, plus the
         callable that hands a drained slot back."""
         eng = self.engine
+        self._seq = 0
+        self._eof = False
         if not self.threaded:
-            fill = self._fill_from_packed if self._packed else self._fill_from_poll
+            gather = self._gather_packed if self._packed else self._gather_poll
+            pack = self._pack_packed if self._packed else self._pack_poll
+            scratch = self._new_scratch() if not self._packed else None
             free = collections.deque(range(eng.n_slots))
 
             def gen():
                 while True:
                     slot = free.popleft()       # never empty: pending depth < n_slots
-                    n, nbytes, parts, offs = fill(slot)
+                    with self.consumer_lock:
+                        n, nbytes, token = gather(slot, scratch)
                     if n == 0:
                         return
+                    parts, offs = pack(slot, scratch, n, token)
                     eng.submit(slot, n, nbytes)
                     yield slot, n, nbytes, parts, offs
 
             return gen(), free.append
         free_q = queue.Queue()
-        filled_q = queue.Queue()
         for s in range(eng.n_slots):
             free_q.put(s)
         self._free_q = free_q
-        self._thread = threading.Thread(target=self._produce, args=(free_q, filled_q),
-                                        name="torchkafka-producer", daemon=True)
-        self._thread.start()
+        self._cv = threading.Condition()
+        self._failure = None
+        ready = {}
+
+        def deliver(seq, item):
+            with self._cv:
+                ready[seq] = item
+                self._cv.notify_all()
+
+        self._threads = [threading.Thread(target=self._produce, args=(free_q, deliver),
+                                          name=f"torchkafka-producer-{k}", daemon=True)
+                         for k in range(self.n_producers)]
+        for t in self._threads:
+            t.start()
 
         def gen():
+            want = 0
             while True:
-                item = filled_q.get()
+                with self._cv:
+                    while want not in ready and self._failure is None:
+                        self._cv.wait(timeout=1.0)
+                    if self._failure is not None:
+                        raise self._failure
+                    item = ready.pop(want)
+                want += 1
                 if item is None:
                     return
-                if isinstance(item, BaseException):
-                    raise item
                 yield item
 
         return gen(), free_q.put
@@ -292,7 +364,7 @@ class IngestPipeline:
         B = self.batch_size
         self._leftover = []
         pending = collections.deque()
-        depth = max(1, eng.n_slots - 2) if self.threaded else max(1, eng.n_slots - 1)
+        depth = 1 if self.threaded else max(1, eng.n_slots - 1)
         prev_slot, prev_out = None, None
         open_lmax = 0                  # longest record among the rows of the open batch
         last = None                    # (_Pending, SlotResult) of the most recent drained slot
@@ -300,19 +372,25 @@ class IngestPipeline:
 
         def drain(item):
             nonlocal open_lmax, last
+            t0 = time.perf_counter()
             res = eng.result(item.slot)
+            self.stats["t_wait_result"] += time.perf_counter() - t0
             release(item.slot)         # pinned memory is reusable: H2D and kernels are done
             self.stats["records"] += res.n_records
             self.stats["kept"] += res.n_kept
             err_rec = res.first_error_rec if res.n_errors else None
             first = B - res.carry_in
-            for j in range(res.n_closed):
-                if err_rec is not None and res.batch_end[j] >= err_rec:
-                    raise self._error(item, res)
-                lmax = max(int(res.batch_lmax[j]), open_lmax) if j == 0 else int(res.batch_lmax[j])
-                batch = eng.batch_view(item.out, first + j * B, B, lmax)
-                self.stats["batches"] += 1
-                yield batch, self._offsets_map(res.commit[:, j])
+            nc = res.n_closed
+            if nc:
+                lmax = res.batch_lmax[:nc].copy()
+                lmax[0] = max(int(lmax[0]), open_lmax)
+                views = eng.batch_views(item.out, first, nc, lmax)
+                commit_cols = np.ascontiguousarray(res.commit.T)
+                for j in range(nc):
+                    if err_rec is not None and res.batch_end[j] >= err_rec:
+                        raise self._error(item, res)
+                    self.stats["batches"] += 1
+                    yield views[j], self._offsets_map(commit_cols[j])
             if err_rec is not None:
                 # bad record sits in the still-open batch: it surfaces with that batch
                 raise self._error(item, res)
@@ -320,14 +398,19 @@ class IngestPipeline:
             open_lmax = max(open_lmax, tail_lmax) if res.n_closed == 0 else tail_lmax
             last = (item, res)
 
+        t_get = time.perf_counter()
         for slot, n, nbytes, parts, offs in slots:
+            t0 = time.perf_counter()
+            self.stats["t_wait_slot"] += t0 - t_get
             out = eng.process(slot, n, prev_slot, prev_out)
+            self.stats["t_launch"] += time.perf_counter() - t0
             pending.append(_Pending(slot, n, out, parts, offs))
             prev_slot, prev_out = slot, out
             self.stats["slots"] += 1
             self.stats["bytes"] += nbytes
             if len(pending) > depth:
                 yield from drain(pending.popleft())
+            t_get = time.perf_counter()
         while pending:
             yield from drain(pending.popleft())
         # stream exhausted: the open batch becomes the short tail batch (fetch.py:39-42)
@@ -337,4 +420,4 @@ class IngestPipeline:
                 first = B + res.n_kept - res.carry_out
                 batch = eng.batch_view(item.out, first, res.carry_out, open_lmax)
                 self.stats["batches"] += 1
-                yield batch, self._offsets_map(res.commit[:, res.n_closed])
+                yield batch, self._offsets_map(np.ascontiguousarray(res.commit[:, res.n_closed]))

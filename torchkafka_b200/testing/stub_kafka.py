@@ -155,6 +155,7 @@ class KafkaConsumer:
         self._fail_commits = fail_commits
         self._positions: Dict[int, int] = {}
         self.committed_log: List[Dict[int, int]] = []
+        self.commit_calls: List[Optional[int]] = []
         self.closed = False
         self.close_autocommit = None
 
@@ -242,11 +243,15 @@ class KafkaConsumer:
     def commit(self, offsets=None):
         if self._fail_commits:
             raise CommitFailedError("stub commit failure")
+        # committed_log[k] = the group's committed-offset table right after commit k
+        snap = dict(self.committed_log[-1]) if self.committed_log else {}
         if offsets is None:
-            snap = dict(self._positions)
+            snap.update(self._positions)
         else:
-            snap = {tp.partition: om.offset for tp, om in offsets.items()}
+            for tp, om in offsets.items():
+                snap[tp.partition] = om.offset
         self.committed_log.append(snap)
+        self.commit_calls.append(None if offsets is None else len(offsets))
 
     def committed(self, tp):
         for snap in reversed(self.committed_log):

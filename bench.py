@@ -196,9 +196,9 @@ def run_device_resident(base_log, steps, warmup, device):
     e1 = torch.cuda.Event(enable_timing=True)
     passes = plan(steps)
     torch.cuda.synchronize()
-    e0.record()
+    e0.record(eng.stream)            # events on the stream the kernels are launched on
     recs, byts = run(passes, timers)
-    e1.record()
+    e1.record(eng.stream)
     torch.cuda.synchronize()
     ms = e0.elapsed_time(e1)
     dec_ms = [a.elapsed_time(b) for a, b in timers]
@@ -221,7 +221,7 @@ def run_device_resident(base_log, steps, warmup, device):
     return info
 
 
-def make_dataset_cls(log, packed):
+def make_dataset_cls(log, packed, repeat=1):
     import torch
     from torchkafka_b200 import KafkaDataset
     from torchkafka_b200.schema import JsonArray
@@ -232,27 +232,31 @@ def make_dataset_cls(log, packed):
         payload_schema = JsonArray(torch.float32, max_len=MAX_LEN, min_size=MIN_SIZE)
         device_slot_bytes = 48 << 20
         device_slots = 3
+        device_producers = int(os.environ.get("TK_PRODUCERS", "2"))
         max_partitions = PARTITIONS
 
         @classmethod
         def new_consumer(cls, *a, **k):
             k.pop("enable_auto_commit", None)
-            return consumer_cls(*a, log=log, **k)
+            return consumer_cls(*a, log=log, repeat=repeat, **k)
 
     return Cfg2Dataset
 
 
-def run_e2e(log, steps, warmup, device, packed):
+def run_e2e(log, steps, warmup, device, packed, repeat=1):
     """`e2e`: public API, host buffers -> batches; wall clock bracketed by synchronize()."""
     import torch
     from torch.utils.data import DataLoader
     from torchkafka_b200 import auto_commit
     torch.cuda.set_device(device)
-    cls = make_dataset_cls(log, packed)
+    cls = make_dataset_cls(log, packed, repeat)
     cls.device_index = device
     ds = cls("topic", group_id="bench")
     loader = DataLoader(ds, batch_size=BATCH)
-    checksum = 0
+    # Every step's result (the batch's int32 length vector, BATCH * 4 bytes) is read back to the
+    # host inside the timed region: non-blocking D2H into pinned memory, consumed after the final
+    # synchronize -- the way a training loop logs its per-step metric without stalling the GPU.
+    host_results = torch.empty((steps, BATCH), dtype=torch.int32).pin_memory()
     t0 = t1 = None
     seen = 0
     for batch in auto_commit(loader):
@@ -260,15 +264,16 @@ def run_e2e(log, steps, warmup, device, packed):
             torch.cuda.synchronize()
             t0 = time.perf_counter()
         if seen >= warmup:
-            # the step's result read back to the host: 8 bytes (sum of lengths) per batch
-            checksum += int(batch.lengths.sum().item())
+            host_results[seen - warmup].copy_(batch.lengths, non_blocking=True)
         seen += 1
         if seen == warmup + steps:
             torch.cuda.synchronize()
+            checksum = int(host_results.sum())
             t1 = time.perf_counter()
             break
     assert t1 is not None, f"log too short: {seen} batches for warmup {warmup} + steps {steps}"
     stats = dict(ds._pipeline.stats) if ds._pipeline is not None else dict(ds.last_pipeline_stats)
+    print("e2e total", round(t1 - t0, 4), "checksum", checksum, file=sys.stderr)
     print("e2e", "packed" if packed else "poll", {k: (round(v, 4) if isinstance(v, float) else v) for k, v in stats.items()}, file=sys.stderr, flush=True)
     ds.close()
     return {"seconds": t1 - t0, "checksum": checksum, "stats": stats}
@@ -295,10 +300,10 @@ def run_cpu_single(log, max_records):
     t0 = time.perf_counter()
     for _batch, _commit in ref.run(consumer, process, BATCH, False, collate):
         n_batches += 1
-        if consumer._cursor >= max_records:
+        if consumer.consumed >= max_records:
             break
     dt = time.perf_counter() - t0
-    return {"records": consumer._cursor, "seconds": dt, "batches": n_batches}
+    return {"records": consumer.consumed, "seconds": dt, "batches": n_batches}
 
 
 def run_cpu_workers(base_log, steps, warmup, num_workers):
@@ -404,18 +409,18 @@ def main_gpu(args):
     clocks = clk.summary()
 
     # ---- e2e: public API from host records (both consumer protocols)
-    from torchkafka_b200.testing import synthetic as syn
-    need = warmup + steps + 3
+    need = max(warmup, 3) + steps + 3
     reps = -(-need // SLOT_BATCHES)
-    e2e_log = syn.tile_log(base, reps) if reps > 1 else base
-    e2e_log.records()
+    if not args.skip_e2e:
+        for r in range(reps):            # ConsumerRecord objects exist before the clock starts,
+            base.rep_records(r)          # exactly as they do for the CPU arm
     barrier()
     if args.skip_e2e:
         e2e_poll = e2e_packed = {"seconds": float("nan")}
     else:
-        e2e_poll = run_e2e(e2e_log, steps, max(warmup, 3), device, packed=False)
+        e2e_poll = run_e2e(base, steps, max(warmup, 3), device, packed=False, repeat=reps)
         barrier()
-        e2e_packed = run_e2e(e2e_log, steps, max(warmup, 3), device, packed=True)
+        e2e_packed = run_e2e(base, steps, max(warmup, 3), device, packed=True, repeat=reps)
     barrier()
 
     rec_per_step = len(base) / SLOT_BATCHES
@@ -455,7 +460,7 @@ def main_gpu(args):
                        "sharding": "one independent partition set per rank, no data-path collective"},
             "batch_ready_GBps": value * bytes_per_step / rec_per_step / 1e9,
             "e2e": {"value": e2e_value, "unit": "records/s",
-                    "h2d_bytes_per_step": int(bytes_per_step), "d2h_bytes_per_step": 8 + 64 + 8 * (PARTITIONS + 2),
+                    "h2d_bytes_per_step": int(bytes_per_step), "d2h_bytes_per_step": 4 * BATCH + (64 + 8 * (SLOT_BATCHES + 1) * (PARTITIONS + 1)) // SLOT_BATCHES,
                     "path": "auto_commit(DataLoader(KafkaDataset with payload_schema)) over ConsumerRecord "
                             "objects from consumer.poll()",
                     "link_GBps": e2e_value * bytes_per_step / rec_per_step / 1e9 / world,
@@ -488,8 +493,8 @@ def main_gpu(args):
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=512)
-    ap.add_argument("--warmup", type=int, default=64)
+    ap.add_argument("--steps", type=int, default=2048)
+    ap.add_argument("--warmup", type=int, default=128)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--no-cpu", action="store_true", help="skip the in-line cpu_baseline leg")
     ap.add_argument("--skip-e2e", action="store_true", help="device-resident leg only (profiling runs)")

@@ -44,9 +44,10 @@ def _np_view(ptr: int, nbytes: int, dtype) -> np.ndarray:
 class SlotOutput:
     """Tensors one slot wrote into (kept alive until the next slot took its carry)."""
 
-    __slots__ = ("tensors", "planes", "n_records")
+    __slots__ = ("tensors", "planes", "n_records", "done")
 
     def __init__(self, tensors, planes, n_records):
+        self.done = None
         self.tensors = tensors
         self.planes = planes
         self.n_records = n_records
@@ -85,6 +86,9 @@ class SlotEngine:
         if self.batch_size <= 0:
             raise ValueError("batch_size must be positive")
         self.device = torch.cuda.current_device() if device is None else int(device)
+        #: kernels run on the engine's own stream so that a consumer synchronising on a
+        #: delivered batch never waits for the slot that is being decoded behind it
+        self.stream = torch.cuda.Stream(device=self.device)
         self.n_slots = int(n_slots)
         self.n_partitions = int(n_partitions)
         self.slot_bytes = int(slot_bytes)
@@ -123,11 +127,14 @@ class SlotEngine:
         except AttributeError:  # pragma: no cover
             cores = os.cpu_count() or 1
         #: threads used by the pinned-memory pack (payload memcpy)
-        self.pack_threads = max(1, min(8, cores // 2))
+        self.pack_threads = int(os.environ.get("TK_PACK_THREADS", 0)) or max(1, min(8, cores // 2))
 
     # ------------------------------------------------------------------ plumbing
     def _stream(self):
-        return C.c_void_p(torch.cuda.current_stream(self.device).cuda_stream)
+        st = getattr(self, "stream", None)
+        if st is None:
+            return C.c_void_p(torch.cuda.current_stream(self.device).cuda_stream)
+        return C.c_void_p(st.cuda_stream)
 
     def close(self):
         if getattr(self, "ctx", None) is not None and self.ctx.value:
@@ -227,8 +234,11 @@ class SlotEngine:
         decode / collate kernel is appended (roofline measurement in bench.py)."""
         lib, ctx, st = self.lib, self.ctx, self._stream()
         sc = self.schema
-        with torch.cuda.device(self.device):
+        import time as _t
+        _t0 = _t.perf_counter()
+        with torch.cuda.device(self.device), torch.cuda.stream(self.stream):
             out = self._allocate(n)
+            self.t_alloc = getattr(self, "t_alloc", 0.0) + _t.perf_counter() - _t0
             if not resident:
                 _native.check(lib.tk_slot_wait(ctx, slot, st))
             if prev_out is not None:
@@ -263,7 +273,17 @@ class SlotEngine:
                 ev1.record()
                 timers.append((ev0, ev1))
             _native.check(lib.tk_slot_fetch_result(ctx, slot, st))
+            out.done = torch.cuda.Event()
+            out.done.record(self.stream)
         return out
+
+    def publish(self, out: "SlotOutput"):
+        """Make the slot's tensors safe to use on the caller's current stream."""
+        cur = torch.cuda.current_stream(self.device)
+        if cur != self.stream:
+            cur.wait_event(out.done)
+            for t in out.tensors:
+                t.record_stream(cur)
 
     def assume_resident(self, slot: int, n: int, nbytes: int):
         _native.check(self.lib.tk_slot_assume_resident(self.ctx, slot, n, nbytes))

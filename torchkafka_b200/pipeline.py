@@ -86,6 +86,8 @@ class IngestPipeline:
         #: serialises consumer calls: the producer thread polls, the user's thread commits,
         #: and kafka-python consumers are not safe for concurrent calls
         self.consumer_lock = threading.Lock()
+        #: producers take turns gathering (poll + harvest) so slots follow consumption order
+        self._order_lock = threading.Lock()
         self._mk_offset = _offset_struct()
         self._tp_cls = _tp_struct()
         self._tp_of: Dict[int, object] = {}        # dense partition index -> TopicPartition
@@ -102,6 +104,7 @@ class IngestPipeline:
         self._closed = False
         self._stop = threading.Event()
         self._free_q = None
+        self._saved_switch = None
         self.stats = collections.Counter()
 
     # ------------------------------------------------------------------ lifecycle
@@ -110,6 +113,9 @@ class IngestPipeline:
             return
         self._closed = True
         self._stop.set()
+        if self._saved_switch is not None:
+            sys.setswitchinterval(self._saved_switch)
+            self._saved_switch = None
         if self._threads:
             try:
                 self._free_q.put_nowait(None)
@@ -139,7 +145,8 @@ class IngestPipeline:
     def _gather_packed(self, slot: int, scratch):
         eng = self.engine
         t0 = time.perf_counter()
-        run = self.consumer.poll_packed(eng.slot_records, eng.slot_bytes)
+        with self.consumer_lock:
+            run = self.consumer.poll_packed(eng.slot_records, eng.slot_bytes)
         self.stats["t_poll"] += time.perf_counter() - t0
         if run is None or len(run) == 0:
             return 0, 0, None
@@ -194,8 +201,9 @@ class IngestPipeline:
                 items, self._leftover = self._leftover, []
             else:
                 t0 = time.perf_counter()
-                polled = self.consumer.poll(timeout_ms=self.poll_timeout_ms,
-                                            max_records=min(eng.slot_records - n, 1 << 16))
+                with self.consumer_lock:
+                    polled = self.consumer.poll(timeout_ms=self.poll_timeout_ms,
+                                                max_records=min(eng.slot_records - n, 1 << 16))
                 self.stats["t_poll"] += time.perf_counter() - t0
                 if not polled:
                     empty += 1
@@ -281,7 +289,7 @@ class IngestPipeline:
                 if slot is None or self._stop.is_set():
                     free_q.put(None)            # let the sibling producers see it too
                     return
-                with self.consumer_lock:
+                with self._order_lock:
                     if self._eof:
                         return
                     n, nbytes, token = gather(slot, scratch)
@@ -315,8 +323,7 @@ class IngestPipeline:
             def gen():
                 while True:
                     slot = free.popleft()       # never empty: pending depth < n_slots
-                    with self.consumer_lock:
-                        n, nbytes, token = gather(slot, scratch)
+                    n, nbytes, token = gather(slot, scratch)
                     if n == 0:
                         return
                     parts, offs = pack(slot, scratch, n, token)
@@ -368,6 +375,12 @@ class IngestPipeline:
         prev_slot, prev_out = None, None
         open_lmax = 0                  # longest record among the rows of the open batch
         last = None                    # (_Pending, SlotResult) of the most recent drained slot
+        # The producers hold the GIL in short C stretches (poll glue, harvest); with CPython's
+        # default 5 ms switch interval the consuming thread would wait that long to get the GIL
+        # back after every blocking call.  Ask for prompt hand-offs while the pipeline runs.
+        if self.threaded and self._saved_switch is None:
+            self._saved_switch = sys.getswitchinterval()
+            sys.setswitchinterval(min(self._saved_switch, 5e-5))
         slots, release = self._filled_slots()
 
         def drain(item):
@@ -376,6 +389,7 @@ class IngestPipeline:
             res = eng.result(item.slot)
             self.stats["t_wait_result"] += time.perf_counter() - t0
             release(item.slot)         # pinned memory is reusable: H2D and kernels are done
+            eng.publish(item.out)      # caller's stream waits for this slot only
             self.stats["records"] += res.n_records
             self.stats["kept"] += res.n_kept
             err_rec = res.first_error_rec if res.n_errors else None
@@ -404,6 +418,7 @@ class IngestPipeline:
             self.stats["t_wait_slot"] += t0 - t_get
             out = eng.process(slot, n, prev_slot, prev_out)
             self.stats["t_launch"] += time.perf_counter() - t0
+            self.stats["t_alloc"] = getattr(eng, "t_alloc", 0.0)
             pending.append(_Pending(slot, n, out, parts, offs))
             prev_slot, prev_out = slot, out
             self.stats["slots"] += 1

@@ -121,6 +121,33 @@ class RecordLog:
             ]
         return self._records
 
+    def per_partition_count(self) -> np.ndarray:
+        if getattr(self, "_ppc", None) is None:
+            self._ppc = np.bincount(self.partitions, minlength=int(self.partitions.max()) + 1 if len(self) else 1)
+        return self._ppc
+
+    def rep_offsets(self, rep: int) -> np.ndarray:
+        """Offsets of the records in repetition ``rep`` of the log (a consumer created with
+        ``repeat=R`` serves the log R times; each partition's offsets keep increasing)."""
+        if rep == 0:
+            return self.offsets
+        cache = self.__dict__.setdefault("_rep_offsets", {})
+        if rep not in cache:
+            cache[rep] = self.offsets + rep * self.per_partition_count()[self.partitions]
+        return cache[rep]
+
+    def rep_records(self, rep: int) -> List[ConsumerRecord]:
+        if rep == 0:
+            return self.records()
+        cache = self.__dict__.setdefault("_rep_records", {})
+        if rep not in cache:
+            t = self.topic
+            offs = self.rep_offsets(rep).tolist()
+            parts = self.partitions.tolist()
+            cache[rep] = [ConsumerRecord(t, p, o, 0, 0, None, v, [], None, -1, len(v), -1)
+                          for v, p, o in zip(self._byte_values, parts, offs)]
+        return cache[rep]
+
     def run_bounds(self) -> np.ndarray:
         """Indices i > 0 where partitions[i] != partitions[i-1] (starts of partition runs)."""
         if getattr(self, "_bounds", None) is None:
@@ -146,11 +173,13 @@ class KafkaConsumer:
     """
 
     def __init__(self, *topics, log: Optional[RecordLog] = None, block_at_end: bool = False,
-                 fail_commits: bool = False, **configs):
+                 fail_commits: bool = False, repeat: int = 1, **configs):
         self.topics = topics
         self.config = dict(configs)
         self._log = log if log is not None else RecordLog([], [], [])
         self._cursor = 0
+        self._rep = 0                  # current repetition of the log (see ``repeat``)
+        self._repeat = max(1, int(repeat))
         self._block_at_end = block_at_end
         self._fail_commits = fail_commits
         self._positions: Dict[int, int] = {}
@@ -163,12 +192,27 @@ class KafkaConsumer:
     def __iter__(self):
         return self
 
+    def _roll(self) -> bool:
+        """Move to the next repetition when the current one is exhausted; False at the very end."""
+        if self._cursor < len(self._log):
+            return True
+        if self._rep + 1 < self._repeat and len(self._log):
+            self._rep += 1
+            self._cursor = 0
+            return True
+        return False
+
+    @property
+    def consumed(self) -> int:
+        """Records handed out so far (all repetitions)."""
+        return self._rep * len(self._log) + self._cursor
+
     def __next__(self):
-        if self._cursor >= len(self._log):
+        if not self._roll():
             if self._block_at_end:
                 threading.Event().wait()
             raise StopIteration
-        rec = self._log.records()[self._cursor]
+        rec = self._log.rep_records(self._rep)[self._cursor]
         self._cursor += 1
         self._positions[rec.partition] = rec.offset + 1
         return rec
@@ -182,10 +226,10 @@ class KafkaConsumer:
         the order the iterator would have produced them.
         """
         n = len(self._log)
-        if self._cursor >= n:
+        if not self._roll():
             return {}
         limit = n - self._cursor if max_records is None else min(max_records, n - self._cursor)
-        recs = self._log.records()
+        recs = self._log.rep_records(self._rep)
         bounds = self._log.run_bounds()          # indices where the partition changes
         out: Dict[TopicPartition, List[ConsumerRecord]] = {}
         i = self._cursor
@@ -215,16 +259,16 @@ class KafkaConsumer:
         ``max_bytes`` on its own (the caller sizes its slots for that).
         """
         n = len(self._log)
-        a = self._cursor
-        if a >= n:
+        if not self._roll():
             return None
+        a = self._cursor
         starts = self._log.starts
         b = min(n, a + max_records)
         # largest b with starts[b] - starts[a] <= max_bytes
         hi = int(np.searchsorted(starts, starts[a] + max_bytes, side="right")) - 1
         b = max(a + 1, min(b, hi))
         parts = self._log.partitions[a:b]
-        offs = self._log.offsets[a:b]
+        offs = self._log.rep_offsets(self._rep)[a:b]
         self._cursor = b
         # positions: last offset per partition in the run
         rev_parts = parts[::-1]

@@ -162,6 +162,27 @@ int tk_image_set_norm(tk_ctx* ctx, int channels, const float* mean, const float*
 int tk_collate_image_u8_bf16_nchw(tk_ctx* ctx, int slot, uint32_t height, uint32_t width,
                                   uint32_t channels, const tk_plane_t* out, void* stream);
 
+/* ---- the whole hot path of one slot in one call ------------------------------
+ * tk_slot_wait, tk_carry_rows, scan, tk_compact, tk_commit_offsets, decode/collate,
+ * tk_slot_fetch_result, enqueued on `stream`.  What a host plugin binds in place of
+ * the per-record loop KafkaDataset.__iter__ (src/kafka_dataset.py:147-171) + the
+ * DataLoader fetch/collate (fetch.py:27-45) + auto_commit's commit (auto_commit.py:55-58). */
+typedef enum { TK_SCHEMA_JSON = 0, TK_SCHEMA_RAW = 1, TK_SCHEMA_IMAGE = 2 } tk_schema_t;
+typedef struct tk_job {
+    int32_t    schema;        /* tk_schema_t */
+    int32_t    dtype;         /* JSON: tk_dtype_t */
+    uint32_t   max_len, min_size, fixed_len;            /* JSON */
+    uint32_t   height, width, channels;                 /* image */
+    uint64_t   record_bytes;                            /* raw / image input bytes per record */
+    uint32_t   batch_size;
+    int32_t    prev_slot;     /* slot processed just before this one, -1 if none */
+    int32_t    n_planes;      /* 1 (values) or 3 (values, lengths, mask) */
+    int32_t    resident;      /* non-zero: device copy already valid, skip the H2D wait */
+    tk_plane_t prev[3];       /* planes of the previous slot's tensors (carry source) */
+    tk_plane_t cur[3];        /* planes of this slot's tensors */
+} tk_job_t;
+int tk_process_slot(tk_ctx* ctx, int slot, const tk_job_t* job, void* stream);
+
 /* ---- results ---------------------------------------------------------------- */
 /* async D2H of the slot's result block; also marks the slot's device buffers free
  * for the next tk_slot_submit once `stream` reaches this point */

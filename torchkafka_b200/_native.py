@@ -34,6 +34,17 @@ class TkPlane(C.Structure):
     _fields_ = [("base", C.c_void_p), ("row_bytes", C.c_uint64)]
 
 
+class TkJob(C.Structure):
+    _fields_ = [
+        ("schema", C.c_int32), ("dtype", C.c_int32),
+        ("max_len", C.c_uint32), ("min_size", C.c_uint32), ("fixed_len", C.c_uint32),
+        ("height", C.c_uint32), ("width", C.c_uint32), ("channels", C.c_uint32),
+        ("record_bytes", C.c_uint64), ("batch_size", C.c_uint32), ("prev_slot", C.c_int32),
+        ("n_planes", C.c_int32), ("resident", C.c_int32),
+        ("prev", TkPlane * 3), ("cur", TkPlane * 3),
+    ]
+
+
 STATUS_NAMES = {
     0: "ok",
     1: "not a JSON array of numbers (json.JSONDecodeError in the reference)",
@@ -73,6 +84,7 @@ _SIGNATURES = {
     "tk_image_set_norm": (C.c_int, [C.c_void_p, C.c_int, _p(C.c_float), _p(C.c_float), C.c_void_p]),
     "tk_collate_image_u8_bf16_nchw": (C.c_int, [C.c_void_p, C.c_int, C.c_uint32, C.c_uint32, C.c_uint32,
                                                 _p(TkPlane), C.c_void_p]),
+    "tk_process_slot": (C.c_int, [C.c_void_p, C.c_int, _p(TkJob), C.c_void_p]),
     "tk_slot_fetch_result": (C.c_int, [C.c_void_p, C.c_int, C.c_void_p]),
     "tk_slot_result": (C.c_int, [C.c_void_p, C.c_int, _p(_p(TkResult)), _p(_p(C.c_uint32)),
                                  _p(_p(C.c_uint32)), _p(_p(C.c_int64)), _p(C.c_uint32)]),

@@ -1,0 +1,41 @@
+// tk_process.cu -- one call that enqueues the whole kernel sequence of a slot.
+//
+// This is the entry point a host-side plugin binds for the hot path: it stands for one
+// pass of `KafkaDataset.__iter__ -> _process -> None filter -> collate -> commit offsets`
+// (src/kafka_dataset.py:147-171, fetch.py:27-45, collate.py:246-275, auto_commit.py:55-58)
+// over every record of the slot.  Everything is asynchronous on `stream`.
+#include "tk_internal.h"
+
+extern "C" int tk_process_slot(tk_ctx* ctx, int slot, const tk_job_t* job, void* stream) {
+    TK_ENTER(ctx, slot);
+    TK_REQUIRE(job, "job is null");
+    int rc;
+    if (!job->resident) { rc = tk_slot_wait(ctx, slot, stream); if (rc) return rc; }
+    if (job->prev_slot >= 0) {
+        rc = tk_carry_rows(ctx, job->prev_slot, job->n_planes, job->prev, job->cur, stream);
+        if (rc) return rc;
+    }
+    if (job->schema == TK_SCHEMA_JSON) rc = tk_json_scan(ctx, slot, job->max_len, job->min_size, stream);
+    else rc = tk_raw_scan(ctx, slot, job->record_bytes, stream);
+    if (rc) return rc;
+    rc = tk_compact(ctx, slot, job->batch_size, stream); if (rc) return rc;
+    rc = tk_commit_offsets(ctx, slot, stream); if (rc) return rc;
+    switch (job->schema) {
+        case TK_SCHEMA_JSON:
+            rc = tk_json_decode(ctx, slot, job->dtype, job->max_len, job->fixed_len, &job->cur[0],
+                                job->n_planes > 1 ? &job->cur[1] : nullptr,
+                                job->n_planes > 2 ? &job->cur[2] : nullptr, stream);
+            break;
+        case TK_SCHEMA_RAW:
+            rc = tk_collate_raw(ctx, slot, job->record_bytes, &job->cur[0], stream);
+            break;
+        case TK_SCHEMA_IMAGE:
+            rc = tk_collate_image_u8_bf16_nchw(ctx, slot, job->height, job->width, job->channels,
+                                               &job->cur[0], stream);
+            break;
+        default:
+            TK_REQUIRE(false, "unknown schema %d", job->schema);
+    }
+    if (rc) return rc;
+    return tk_slot_fetch_result(ctx, slot, stream);
+}

@@ -39,8 +39,21 @@ static PyObject* harvest(PyObject*, PyObject* args) {
 
     Py_ssize_t taken = 0;
     unsigned long long total = 0;
+    const bool fast = vi >= 0;
     for (Py_ssize_t i = first; i < n && taken < max_records; ++i) {
         PyObject* rec = items[i];
+        // Each record is three dependent cache misses (record tuple -> value bytes header,
+        // offset int).  Prefetch the tuple 16 records ahead and its two fields 8 ahead.
+        if (fast) {
+            if (i + 16 < n) __builtin_prefetch(items[i + 16]);
+            if (i + 8 < n) {
+                PyObject* r8 = items[i + 8];
+                if (PyTuple_Check(r8) && PyTuple_GET_SIZE(r8) > vi && PyTuple_GET_SIZE(r8) > oi) {
+                    __builtin_prefetch(PyTuple_GET_ITEM(r8, vi));
+                    __builtin_prefetch(PyTuple_GET_ITEM(r8, oi));
+                }
+            }
+        }
         PyObject *val, *off;
         bool own = false;
         if (vi >= 0 && PyTuple_Check(rec) && PyTuple_GET_SIZE(rec) > vi && PyTuple_GET_SIZE(rec) > oi) {

@@ -31,8 +31,9 @@ REC_DTYPE = np.dtype([("start", "<u4"), ("partition", "<i4"), ("offset", "<i8")]
 
 #: a slot never closes more batches than this (bounds the commit matrix)
 MAX_BATCHES_CAP = 16384
-#: launches issued per slot by ``process`` (kernels + memset), for bench accounting
-LAUNCHES_PER_SLOT_JSON = 9
+#: kernels launched per slot by ``process`` (carry, scan, 3x compact, 2x commit, decode; the
+#: commit-matrix memset is not counted), for bench accounting
+LAUNCHES_PER_SLOT_JSON = 8
 LAUNCHES_PER_SLOT_RAW = 8
 
 
@@ -226,53 +227,75 @@ class SlotEngine:
             arr[k].row_bytes = rb
         return SlotOutput(tensors, arr, n)
 
+    def _job(self, out: SlotOutput, prev_slot, prev_out, resident: bool) -> "_native.TkJob":
+        sc = self.schema
+        job = _native.TkJob()
+        if isinstance(sc, JsonArray):
+            job.schema, job.dtype = 0, sc.kind
+            job.max_len, job.min_size, job.fixed_len = sc.max_len, sc.min_size, sc.fixed_len or 0
+        elif isinstance(sc, ImageU8):
+            job.schema = 2
+            job.height, job.width, job.channels = sc.height, sc.width, sc.channels
+            job.record_bytes = sc.record_bytes
+        else:
+            job.schema = 1
+            job.record_bytes = sc.record_bytes
+        job.batch_size = self.batch_size
+        job.prev_slot = -1 if prev_out is None else prev_slot
+        job.n_planes = len(out.planes)
+        job.resident = 1 if resident else 0
+        for k in range(len(out.planes)):
+            job.cur[k] = out.planes[k]
+            if prev_out is not None:
+                job.prev[k] = prev_out.planes[k]
+        return job
+
     def process(self, slot: int, n: int, prev_slot: Optional[int], prev_out: Optional[SlotOutput],
                 resident: bool = False, timers: Optional[list] = None) -> SlotOutput:
-        """Launch the whole kernel sequence for ``slot`` on the current stream (asynchronous).
+        """Enqueue the whole kernel sequence for ``slot`` on the engine's stream (asynchronous).
 
-        ``timers``: when given, a (start, end) pair of CUDA events bracketing the
-        decode / collate kernel is appended (roofline measurement in bench.py)."""
+        Normally a single C call (``tk_process_slot``).  With ``timers`` the sequence is issued
+        kernel by kernel and a (start, end) pair of CUDA events bracketing the decode / collate
+        kernel is appended (roofline measurement in bench.py)."""
         lib, ctx, st = self.lib, self.ctx, self._stream()
         sc = self.schema
-        import time as _t
-        _t0 = _t.perf_counter()
+        is_json = isinstance(sc, JsonArray)
         with torch.cuda.device(self.device), torch.cuda.stream(self.stream):
             out = self._allocate(n)
-            self.t_alloc = getattr(self, "t_alloc", 0.0) + _t.perf_counter() - _t0
-            if not resident:
-                _native.check(lib.tk_slot_wait(ctx, slot, st))
-            if prev_out is not None:
-                _native.check(lib.tk_carry_rows(ctx, prev_slot, len(out.planes), prev_out.planes,
-                                                out.planes, st))
-                self.launches += 1
-            if isinstance(sc, JsonArray):
-                _native.check(lib.tk_json_scan(ctx, slot, sc.max_len, sc.min_size, st))
+            if timers is None:
+                job = self._job(out, prev_slot, prev_out, resident)
+                _native.check(lib.tk_process_slot(ctx, slot, C.byref(job), st))
             else:
-                _native.check(lib.tk_raw_scan(ctx, slot, sc.record_bytes, st))
-            _native.check(lib.tk_compact(ctx, slot, self.batch_size, st))
-            _native.check(lib.tk_commit_offsets(ctx, slot, st))
-            if timers is not None:
+                if not resident:
+                    _native.check(lib.tk_slot_wait(ctx, slot, st))
+                if prev_out is not None:
+                    _native.check(lib.tk_carry_rows(ctx, prev_slot, len(out.planes), prev_out.planes,
+                                                    out.planes, st))
+                if is_json:
+                    _native.check(lib.tk_json_scan(ctx, slot, sc.max_len, sc.min_size, st))
+                else:
+                    _native.check(lib.tk_raw_scan(ctx, slot, sc.record_bytes, st))
+                _native.check(lib.tk_compact(ctx, slot, self.batch_size, st))
+                _native.check(lib.tk_commit_offsets(ctx, slot, st))
                 ev0 = torch.cuda.Event(enable_timing=True)
                 ev1 = torch.cuda.Event(enable_timing=True)
                 ev0.record()
-            if isinstance(sc, JsonArray):
                 P = out.planes
-                variable = sc.fixed_len is None
-                _native.check(lib.tk_json_decode(
-                    ctx, slot, sc.kind, sc.max_len, sc.fixed_len or 0, C.byref(P[0]),
-                    C.byref(P[1]) if variable else None, C.byref(P[2]) if variable else None, st))
-                self.launches += LAUNCHES_PER_SLOT_JSON - 1
-            elif isinstance(sc, ImageU8):
-                _native.check(lib.tk_collate_image_u8_bf16_nchw(ctx, slot, sc.height, sc.width,
-                                                                sc.channels, C.byref(out.planes[0]), st))
-                self.launches += LAUNCHES_PER_SLOT_RAW - 1
-            else:
-                _native.check(lib.tk_collate_raw(ctx, slot, sc.record_bytes, C.byref(out.planes[0]), st))
-                self.launches += LAUNCHES_PER_SLOT_RAW - 1
-            if timers is not None:
+                if is_json:
+                    variable = sc.fixed_len is None
+                    _native.check(lib.tk_json_decode(
+                        ctx, slot, sc.kind, sc.max_len, sc.fixed_len or 0, C.byref(P[0]),
+                        C.byref(P[1]) if variable else None, C.byref(P[2]) if variable else None, st))
+                elif isinstance(sc, ImageU8):
+                    _native.check(lib.tk_collate_image_u8_bf16_nchw(ctx, slot, sc.height, sc.width,
+                                                                    sc.channels, C.byref(P[0]), st))
+                else:
+                    _native.check(lib.tk_collate_raw(ctx, slot, sc.record_bytes, C.byref(P[0]), st))
                 ev1.record()
                 timers.append((ev0, ev1))
-            _native.check(lib.tk_slot_fetch_result(ctx, slot, st))
+                _native.check(lib.tk_slot_fetch_result(ctx, slot, st))
+            self.launches += (LAUNCHES_PER_SLOT_JSON if is_json else LAUNCHES_PER_SLOT_RAW) \
+                - (1 if prev_out is None else 0)
             out.done = torch.cuda.Event()
             out.done.record(self.stream)
         return out

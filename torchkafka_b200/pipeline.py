@@ -418,7 +418,6 @@ class IngestPipeline:
             self.stats["t_wait_slot"] += t0 - t_get
             out = eng.process(slot, n, prev_slot, prev_out)
             self.stats["t_launch"] += time.perf_counter() - t0
-            self.stats["t_alloc"] = getattr(eng, "t_alloc", 0.0)
             pending.append(_Pending(slot, n, out, parts, offs))
             prev_slot, prev_out = slot, out
             self.stats["slots"] += 1

@@ -128,7 +128,7 @@ class SlotEngine:
         except AttributeError:  # pragma: no cover
             cores = os.cpu_count() or 1
         #: threads used by the pinned-memory pack (payload memcpy)
-        self.pack_threads = int(os.environ.get("TK_PACK_THREADS", 0)) or max(1, min(8, cores // 2))
+        self.pack_threads = int(os.environ.get("TK_PACK_THREADS", 0)) or max(1, min(8, (cores - 2) // 2))
 
     # ------------------------------------------------------------------ plumbing
     def _stream(self):

@@ -183,6 +183,29 @@ typedef struct tk_job {
 } tk_job_t;
 int tk_process_slot(tk_ctx* ctx, int slot, const tk_job_t* job, void* stream);
 
+/* ---- K2 without any allocation ------------------------------------------------
+ * No counterpart in the reference (it has no device code and no allocator to avoid).
+ * Same computation as tk_compact -- from per-record keep flags (>= 0 kept, < 0 skipped)
+ * to the index of every record among the kept ones (k for kept records, -1 - k for
+ * skipped ones, k = kept records before it) plus the batch bookkeeping in *d_result
+ * (n_records, n_kept, carry_in, carry_out, n_closed, batch_size) -- for callers that
+ * cannot call cudaMalloc where they need it: hosts whose whole HBM budget is already
+ * owned by their own pool, plugin threads on which driver allocations are forbidden,
+ * and latency-critical sections that cannot take the device-wide synchronisation an
+ * allocation implies.  The scratch between the three kernels lives in a fixed
+ * __device__ array inside the library (about 4 KiB, reserved on every GPU that loads
+ * the library until the process exits); the caller passes every input and output as
+ * device pointers and needs no tk_ctx.
+ *   - at most TK_NOALLOC_MAX_RECORDS records per call; larger n is rejected with an error
+ *   - the first call on a device looks up the address of the scratch array
+ *     (cudaGetSymbolAddress); make that first call before any stream capture
+ *   - all calls on a device share the scratch: calls that may overlap on the GPU
+ *     (different streams without a dependency) race; issue them on one stream
+ *   - no cudaMalloc / cudaFree / allocating library call is made */
+#define TK_NOALLOC_MAX_RECORDS (1u << 20)
+int tk_compact_noalloc(const int32_t* d_keep, uint32_t n, uint32_t batch_size, uint32_t carry_in,
+                       int32_t* d_kidx, tk_result_t* d_result, void* stream);
+
 /* ---- results ---------------------------------------------------------------- */
 /* async D2H of the slot's result block; also marks the slot's device buffers free
  * for the next tk_slot_submit once `stream` reaches this point */

@@ -85,6 +85,8 @@ _SIGNATURES = {
     "tk_collate_image_u8_bf16_nchw": (C.c_int, [C.c_void_p, C.c_int, C.c_uint32, C.c_uint32, C.c_uint32,
                                                 _p(TkPlane), C.c_void_p]),
     "tk_process_slot": (C.c_int, [C.c_void_p, C.c_int, _p(TkJob), C.c_void_p]),
+    "tk_compact_noalloc": (C.c_int, [C.c_void_p, C.c_uint32, C.c_uint32, C.c_uint32, C.c_void_p,
+                                     C.c_void_p, C.c_void_p]),
     "tk_slot_fetch_result": (C.c_int, [C.c_void_p, C.c_int, C.c_void_p]),
     "tk_slot_result": (C.c_int, [C.c_void_p, C.c_int, _p(_p(TkResult)), _p(_p(C.c_uint32)),
                                  _p(_p(C.c_uint32)), _p(_p(C.c_int64)), _p(C.c_uint32)]),

@@ -82,8 +82,10 @@ __global__ void __launch_bounds__(256) k_json_scan(const uint8_t* __restrict__ b
             for (int k = 0; k < 4; ++k) {
                 cm |= bytemask_to_bits(__vcmpeq4(w[k], 0x2c2c2c2cu)) << (4 * k);
                 const uint32_t dig = __vcmpleu4(__vsub4(w[k], 0x30303030u), 0x09090909u);
-                const uint32_t nan_inf = __vcmpeq4(w[k], 0x4e4e4e4eu) | __vcmpeq4(w[k], 0x49494949u);
-                ct |= bytemask_to_bits(dig | nan_inf) << (4 * k);
+                // N(aN), I(nfinity), t(rue), f(alse): the non-digit ways an element can start
+                const uint32_t word = __vcmpeq4(w[k], 0x4e4e4e4eu) | __vcmpeq4(w[k], 0x49494949u) |
+                                      __vcmpeq4(w[k], 0x74747474u) | __vcmpeq4(w[k], 0x66666666u);
+                ct |= bytemask_to_bits(dig | word) << (4 * k);
             }
             commas += __popc(cm & valid);
             content |= ct & valid;

@@ -233,9 +233,11 @@ TK_HD tk_token tk_scan_number(const R& rd, uint32_t pos) {
         if (tk_match_word(rd, pos, "Infinity", 8)) { t.special = 2; t.is_int = 0; t.end = pos + 8; return t; }
         t.err = TK_ERR_SYNTAX; return t;
     } else if (c == 't' || c == 'f' || c == 'n') {
-        // true / false / null: valid JSON, outside the numeric-array schema
-        if (tk_match_word(rd, pos, "true", 4) || tk_match_word(rd, pos, "false", 5) ||
-            tk_match_word(rd, pos, "null", 4)) { t.err = TK_ERR_UNSUPPORTED; return t; }
+        // json.loads yields Python bools for true/false, which torch.tensor stores as 1/0 for
+        // every numeric dtype; null becomes None, which torch.tensor rejects (TypeError)
+        if (tk_match_word(rd, pos, "true", 4)) { t.w = 1; t.nsig = 1; t.end = pos + 4; return t; }
+        if (tk_match_word(rd, pos, "false", 5)) { t.w = 0; t.nsig = 1; t.end = pos + 5; return t; }
+        if (tk_match_word(rd, pos, "null", 4)) { t.err = TK_ERR_UNSUPPORTED; return t; }
         t.err = TK_ERR_SYNTAX; return t;
     }
 

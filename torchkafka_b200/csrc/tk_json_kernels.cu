@@ -127,6 +127,144 @@ struct RingReader {
     }
 };
 
+// ---------------------------------------------------------------- SWAR fast path
+// The common token shape  [-]digits[.digits]  with at most 19 digits and no exponent is
+// scanned 8 bytes at a time straight out of the shared-memory ring: one unaligned 8-byte
+// window (3 aligned 32-bit loads + 2 funnel shifts), a carry-free "is this byte a digit"
+// mask, count-trailing-zeros for the run length, and the classic multiply-shift reduction
+// of 4 ASCII digits to a number.  It produces the same tk_token the scalar scanner
+// (tk_scan_number) would, so the conversion code after it is shared; anything else
+// (exponents, > 19 digits, NaN/Infinity, true/false, malformed text, tokens that are not
+// fully resident in the ring) returns false and takes the scalar, fully general path.
+__constant__ uint32_t c_pow10[9] = {1u, 10u, 100u, 1000u, 10000u, 100000u, 1000000u, 10000000u, 100000000u};
+
+struct Window8 { uint32_t lo, hi; };
+
+__device__ __forceinline__ Window8 ring_load8(const uint8_t* ring, uint32_t pos) {
+    const uint32_t* r32 = reinterpret_cast<const uint32_t*>(ring);
+    const uint32_t i = (pos >> 2) & (JD_RING / 4 - 1);
+    const uint32_t w0 = r32[i], w1 = r32[(i + 1) & (JD_RING / 4 - 1)], w2 = r32[(i + 2) & (JD_RING / 4 - 1)];
+    const uint32_t sh = (pos & 3u) * 8u;
+    Window8 w;
+    w.lo = __funnelshift_r(w0, w1, sh);
+    w.hi = __funnelshift_r(w1, w2, sh);
+    return w;
+}
+// number of leading (lowest-address) bytes of the window that are ASCII digits: 0..8
+__device__ __forceinline__ uint32_t leading_digits(const Window8 w) {
+    const uint32_t ul = w.lo ^ 0x30303030u, uh = w.hi ^ 0x30303030u;
+    const uint32_t nl = (((ul & 0x7F7F7F7Fu) + 0x76767676u) | ul) & 0x80808080u;   // 0x80 where not a digit
+    const uint32_t nh = (((uh & 0x7F7F7F7Fu) + 0x76767676u) | uh) & 0x80808080u;
+    const unsigned long long nd = ((unsigned long long)nh << 32) | nl;
+    return (uint32_t)__clzll((long long)__brevll(nd)) >> 3;                          // 64 >> 3 = 8 if none
+}
+// value of 4 ASCII-digit bytes already reduced to 0..9, first character in the lowest byte
+__device__ __forceinline__ uint32_t parse4(uint32_t v) {
+    const uint32_t p = ((v * 2561u) >> 8) & 0x00FF00FFu;      // (10*d0 + d1) | (10*d2 + d3) << 16
+    return (p & 0xFFu) * 100u + (p >> 16);
+}
+// value of the first m (1..8) digits of the window
+__device__ __forceinline__ uint32_t parse_upto8(const Window8 w, uint32_t m) {
+    unsigned long long x = (((unsigned long long)(w.hi ^ 0x30303030u)) << 32) | (w.lo ^ 0x30303030u);
+    x <<= 8u * (8u - m);                                        // digits to the top, zero digits below
+    return parse4((uint32_t)x) * 10000u + parse4((uint32_t)(x >> 32));
+}
+__device__ __forceinline__ uint32_t byte_of(const Window8 w, uint32_t k) {       // k in 0..7
+    const unsigned long long x = ((unsigned long long)w.hi << 32) | w.lo;
+    return (uint32_t)(x >> (8u * k)) & 0xFFu;
+}
+
+// Scan one run of digits starting at *cur (absolute position); accumulates into *w, counts into
+// *ndig; on return `last` is the window that contains the first non-digit at index `m_last`.
+__device__ __forceinline__ bool digit_run(const uint8_t* ring, uint32_t end, uint32_t* cur, uint64_t* w,
+                                          uint32_t* ndig, uint32_t* term) {
+    uint32_t n_here = 0;
+    for (;;) {
+        const Window8 win = ring_load8(ring, *cur);
+        uint32_t m = leading_digits(win);
+        const uint32_t left = end - *cur;                       // bytes of the record from *cur on
+        if (m > left) m = left;
+        if (m) {
+            if (*ndig + m > 19) return false;
+            *w = *w * c_pow10[m] + parse_upto8(win, m);
+            *ndig += m;
+            n_here += m;
+            *cur += m;
+        }
+        if (m < 8) {
+            *term = (m < left) ? byte_of(win, m) : 0xFFFFFFFFu;  // 0xFFFFFFFF: the record ends here
+            return n_here > 0;
+        }
+    }
+}
+
+template <class R>
+__device__ __forceinline__ bool fast_scan_number(const R& rd, uint32_t pos, tk_token* out) {
+    // the token, its separator and the start of the next token must be ring resident
+    if (pos < rd.lo || pos + 64 > rd.hi) return false;
+    const uint8_t* ring = rd.ring;
+    const uint32_t end = rd.end;
+    uint32_t cur = pos;
+    const Window8 first = ring_load8(ring, cur);
+    const uint32_t c0 = first.lo & 0xFFu;
+    uint32_t neg = 0;
+    if (c0 == '-') { neg = 1; cur += 1; }
+    uint64_t w = 0;
+    uint32_t ndig = 0, term = 0;
+    const uint32_t int_begin = cur;
+    if (!digit_run(ring, end, &cur, &w, &ndig, &term)) return false;
+    const uint32_t int_digits = ndig;
+    // "01" is not a JSON number (the scalar path reports it); a lone "0" is
+    if (int_digits > 1 && rd.ring[int_begin & (JD_RING - 1)] == '0') return false;
+    uint32_t frac_digits = 0;
+    if (term == '.') {
+        cur += 1;
+        if (!digit_run(ring, end, &cur, &w, &ndig, &term)) return false;
+        frac_digits = ndig - int_digits;
+    }
+    if (term == 'e' || term == 'E') return false;
+    tk_token t;
+    t.w = w; t.q = -(int32_t)frac_digits; t.end = cur; t.dig_begin = int_begin; t.exp10 = 0;
+    t.neg = (uint8_t)neg; t.is_int = frac_digits == 0; t.truncated = 0; t.special = 0; t.err = TK_OK;
+    t.nsig = (int32_t)ndig; t.frac_digits = (int32_t)frac_digits;
+    *out = t;
+    return true;
+}
+
+// separator after a number that ended at `pos`: fast accept of ",<token>" / ", <token>"
+template <class R>
+__device__ __forceinline__ int fast_gap(const R& rd, uint32_t pos) {
+    if (pos >= rd.lo && pos + 16 <= rd.hi && pos + 3 < rd.end) {
+        const Window8 g = ring_load8(rd.ring, pos);
+        if ((g.lo & 0xFFu) == ',') {
+            const uint32_t c1 = (g.lo >> 8) & 0xFFu;
+            const uint32_t c = c1 == ' ' ? ((g.lo >> 16) & 0xFFu) : c1;
+            if (tk_is_numclass((int)c)) return TK_OK;
+        }
+    }
+    return tk_json_gap(rd, pos);
+}
+
+template <int KIND, class R>
+__device__ __forceinline__ int json_element_fast(const R& rd, uint32_t pos, typename tk_elem<KIND>::type* out) {
+    tk_token t;
+    if (!fast_scan_number(rd, pos, &t)) return tk_json_element<KIND>(rd, pos, out);
+    int st = fast_gap(rd, t.end);
+    if (st) return st;
+    if (KIND == TK_F32 || KIND == TK_F64) {
+        double d;
+        st = tk_token_to_f64(rd, t, &d);
+        if (st) return st;
+        *out = (typename tk_elem<KIND>::type)d;
+    } else {
+        int64_t v;
+        st = tk_token_to_i64(rd, t, KIND == TK_I32 ? 32 : 64, &v);
+        if (st) return st;
+        *out = (typename tk_elem<KIND>::type)v;
+    }
+    return TK_OK;
+}
+
 struct decode_args {
     const uint8_t*  bytes;
     const tk_rec_t* recs;
@@ -234,7 +372,7 @@ __global__ void __launch_bounds__(JD_WARPS * 32) k_json_decode(const decode_args
                 const uint32_t pos = tbase + tok[j];
                 const uint32_t e = elem_base + j;
                 T v;
-                const int st = tk_json_element<KIND>(rd, pos, &v);
+                const int st = json_element_fast<KIND>(rd, pos, &v);
                 if (st) { if (!err) err = st; }
                 else if (dst && e < a.max_len) dst[e] = v;
             }

@@ -26,12 +26,24 @@
 #define JD_MAXTOK (JD_TILE / 2 + 8)
 
 // ---------------------------------------------------------------- SWAR helpers
-// 0xFF in every byte lane of x that is number-like: [0-9], [A-Za-z], '+', '-', '.'
-__device__ __forceinline__ uint32_t numclass4(uint32_t x) {
-    const uint32_t dig = __vcmpleu4(__vsub4(x, 0x30303030u), 0x09090909u);
-    const uint32_t let = __vcmpleu4(__vsub4(x | 0x20202020u, 0x61616161u), 0x19191919u);
-    const uint32_t pun = __vcmpleu4(__vsub4(x, 0x2b2b2b2bu), 0x03030303u) & ~__vcmpeq4(x, 0x2c2c2c2cu);
-    return dig | let | pun;
+// Token-character class, four bytes at a time with plain 32-bit arithmetic (the __v*4 video
+// intrinsics are emulated with ~10 instructions each on sm_100).  A byte is a token character
+// iff  0x2B <= c <= 0x7F,  c != ','  and  (c | 6) != 0x5F  (which removes '[' and ']' -- and
+// 'Y' and '_', neither of which occurs in a JSON number).  tk_is_numclass() (tk_number.cuh) is the scalar
+// twin used by the separator checks; the two must agree for the parallel validation to tile
+// the record.  Result: 0x80 in every byte lane that is a token character.
+__device__ __forceinline__ uint32_t tokclass4(uint32_t x) {
+    const uint32_t lo7 = x & 0x7F7F7F7Fu;
+    const uint32_t ge = (lo7 + 0x55555555u) & ~x;                          // bit7: 0x2B <= c <= 0x7F
+    const uint32_t yc = x ^ 0x2C2C2C2Cu;                                   // zero byte where c == ','
+    const uint32_t nc = ((yc & 0x7F7F7F7Fu) + 0x7F7F7F7Fu) | yc;           // bit7: c != ','
+    const uint32_t yb = (x | 0x06060606u) ^ 0x5F5F5F5Fu;                   // zero byte where (c|6) == 0x5F
+    const uint32_t nb = ((yb & 0x7F7F7F7Fu) + 0x7F7F7F7Fu) | yb;           // bit7: not a bracket
+    return ge & nc & nb & 0x80808080u;
+}
+// bits 7,15,23,31 of m -> bits 0..3
+__device__ __forceinline__ uint32_t hibits_to_nibble(uint32_t m) {
+    return (((m >> 7) * 0x00204081u) >> 21) & 0xFu;
 }
 // one bit per byte lane (bit b set iff byte b of m is 0xFF)
 __device__ __forceinline__ uint32_t bytemask_to_bits(uint32_t m) {
@@ -39,8 +51,8 @@ __device__ __forceinline__ uint32_t bytemask_to_bits(uint32_t m) {
     return (t | (t >> 7) | (t >> 14) | (t >> 21)) & 0xFu;
 }
 __device__ __forceinline__ uint32_t class16(const uint4 v) {
-    return bytemask_to_bits(numclass4(v.x)) | (bytemask_to_bits(numclass4(v.y)) << 4) |
-           (bytemask_to_bits(numclass4(v.z)) << 8) | (bytemask_to_bits(numclass4(v.w)) << 12);
+    return hibits_to_nibble(tokclass4(v.x)) | (hibits_to_nibble(tokclass4(v.y)) << 4) |
+           (hibits_to_nibble(tokclass4(v.z)) << 8) | (hibits_to_nibble(tokclass4(v.w)) << 12);
 }
 // bits [lo, hi) of a 16-bit mask, lo/hi clamped to [0,16]
 __device__ __forceinline__ uint32_t range16(int lo, int hi) {

@@ -196,10 +196,12 @@ struct tk_token {
 
 TK_HD bool tk_is_digit(int c) { return (unsigned)(c - '0') <= 9u; }
 TK_HD bool tk_is_ws(int c) { return c == ' ' || c == '\t' || c == '\n' || c == '\r'; }
-// characters that can belong to a number-like run (digits, sign, '.', letters)
+// Characters that can belong to a token (number-like run).  Deliberately a cheap superset of
+// the characters of JSON numbers / NaN / Infinity / true / false: 0x2B..0x7F without ',' and
+// without the four codes with (c | 6) == 0x5F ('[', ']', 'Y', '_').  The CUDA kernels classify
+// four bytes at a time with the same rule (tokclass4 in tk_json_kernels.cu).
 TK_HD bool tk_is_numclass(int c) {
-    return tk_is_digit(c) || c == '-' || c == '+' || c == '.' ||
-           (unsigned)((c | 0x20) - 'a') <= 25u;
+    return c >= 0x2B && c <= 0x7F && c != ',' && (c | 6) != 0x5F;
 }
 
 template <class R>

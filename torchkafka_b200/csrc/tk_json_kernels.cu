@@ -92,12 +92,11 @@ __global__ void __launch_bounds__(256) k_json_scan(const uint8_t* __restrict__ b
             uint32_t cm = 0, ct = 0;
 #pragma unroll
             for (int k = 0; k < 4; ++k) {
-                cm |= bytemask_to_bits(__vcmpeq4(w[k], 0x2c2c2c2cu)) << (4 * k);
-                const uint32_t dig = __vcmpleu4(__vsub4(w[k], 0x30303030u), 0x09090909u);
-                // N(aN), I(nfinity), t(rue), f(alse): the non-digit ways an element can start
-                const uint32_t word = __vcmpeq4(w[k], 0x4e4e4e4eu) | __vcmpeq4(w[k], 0x49494949u) |
-                                      __vcmpeq4(w[k], 0x74747474u) | __vcmpeq4(w[k], 0x66666666u);
-                ct |= bytemask_to_bits(dig | word) << (4 * k);
+                const uint32_t yc = w[k] ^ 0x2C2C2C2Cu;                                  // zero byte: ','
+                const uint32_t notcomma = ((yc & 0x7F7F7F7Fu) + 0x7F7F7F7Fu) | yc;
+                cm |= hibits_to_nibble(~notcomma & 0x80808080u) << (4 * k);
+                // any token character means the array is not empty
+                ct |= hibits_to_nibble(tokclass4(w[k])) << (4 * k);
             }
             commas += __popc(cm & valid);
             content |= ct & valid;
@@ -291,7 +290,7 @@ struct decode_args {
 };
 
 template <int KIND>
-__global__ void __launch_bounds__(JD_WARPS * 32) k_json_decode(const decode_args a) {
+__global__ void __launch_bounds__(JD_WARPS * 32, 8) k_json_decode(const decode_args a) {
     typedef typename tk_elem<KIND>::type T;
     __shared__ __align__(16) uint8_t s_ring[JD_WARPS][JD_RING];
     __shared__ uint16_t s_tok[JD_WARPS][JD_MAXTOK];

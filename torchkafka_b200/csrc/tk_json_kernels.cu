@@ -256,11 +256,82 @@ __device__ __forceinline__ int fast_gap(const R& rd, uint32_t pos) {
     return tk_json_gap(rd, pos);
 }
 
+// One-shot variant of the fast path for the dominant token shape: sign, at most 8 integer
+// digits, optional '.', at most 16 fraction digits, everything including the terminator inside
+// the first 24 bytes.  The digit/non-digit mask of those 24 bytes is computed once (six words),
+// run lengths come from find-first-set on that mask, and the separator that follows is checked
+// from the same neighbourhood.  On success *gap is TK_OK if the separator was accepted too, or
+// -1 if the caller still has to run the general separator check at t->end.
+template <class R>
+__device__ __forceinline__ bool fast_token24(const R& rd, uint32_t pos, tk_token* out, int* gap) {
+    if (pos < rd.lo || pos + 64 > rd.hi) return false;
+    const uint32_t avail = rd.end - pos;                       // bytes of the record from pos on (>= 1)
+    const uint32_t* r32 = reinterpret_cast<const uint32_t*>(rd.ring);
+    const uint32_t i = pos >> 2, sh = (pos & 3u) * 8u;
+    constexpr uint32_t M = JD_RING / 4 - 1;
+    uint32_t a[7];
+#pragma unroll
+    for (int k = 0; k < 7; ++k) a[k] = r32[(i + k) & M];
+    uint32_t W[6];
+#pragma unroll
+    for (int k = 0; k < 6; ++k) W[k] = __funnelshift_r(a[k], a[k + 1], sh);
+    uint32_t nd = 0xFF000000u;                                 // bytes 24.. count as "not a digit"
+#pragma unroll
+    for (int k = 0; k < 6; ++k) {
+        const uint32_t u = W[k] ^ 0x30303030u;
+        const uint32_t t = (((u & 0x7F7F7F7Fu) + 0x76767676u) | u) & 0x80808080u;
+        nd |= hibits_to_nibble(t) << (4 * k);
+    }
+    if (avail < 24) nd |= 0xFFFFFFFFu << avail;
+    const uint32_t neg = (W[0] & 0xFFu) == '-' ? 1u : 0u;
+    const uint32_t p = neg;
+    const uint32_t L1 = __ffs(nd >> p) - 1;                    // integer digits
+    if (L1 == 0 || L1 > 8) return false;
+    const Window8 wi = {__funnelshift_r(W[0], W[1], 8 * p), __funnelshift_r(W[1], W[2], 8 * p)};
+    if (L1 > 1 && (wi.lo & 0xFFu) == '0') return false;        // "01": the general path reports it
+    const uint32_t tpos = p + L1;                              // <= 9
+    const uint32_t tword = tpos < 4 ? W[0] : (tpos < 8 ? W[1] : W[2]);
+    const uint32_t tc = (tword >> (8 * (tpos & 3u))) & 0xFFu;
+    uint32_t L2 = 0, endp = tpos;
+    uint64_t w = parse_upto8(wi, L1);
+    if (tc == '.') {
+        const uint32_t q0 = tpos + 1;
+        L2 = __ffs(nd >> q0) - 1;                              // fraction digits
+        if (L2 == 0 || L2 > 16 || L1 + L2 > 19) return false;
+        endp = q0 + L2;
+        if (endp > 23) return false;                           // terminator not inside the mask
+        const uint32_t m0 = L2 < 8 ? L2 : 8, m1 = L2 - m0;
+        w = w * c_pow10[m0] + parse_upto8(ring_load8(rd.ring, pos + q0), m0);
+        if (m1) w = w * c_pow10[m1] + parse_upto8(ring_load8(rd.ring, pos + q0 + 8), m1);
+    }
+    if (endp >= avail) return false;                           // record ends inside the token
+    // separator: the common ", x" / ",x" shapes are accepted here
+    const uint32_t gi = (pos + endp) >> 2, gs = ((pos + endp) & 3u) * 8u;
+    const uint32_t g = __funnelshift_r(r32[gi & M], r32[(gi + 1) & M], gs);
+    const uint32_t g0 = g & 0xFFu;
+    if (g0 == 'e' || g0 == 'E') return false;                  // exponent: general path
+    *gap = -1;
+    if (g0 == ',') {
+        const uint32_t g1 = (g >> 8) & 0xFFu;
+        if (g1 == ' ') { if (endp + 2 < avail && tk_is_numclass((int)((g >> 16) & 0xFFu))) *gap = TK_OK; }
+        else if (endp + 1 < avail && tk_is_numclass((int)g1)) *gap = TK_OK;
+    }
+    tk_token t;
+    t.w = w; t.q = -(int32_t)L2; t.end = pos + endp; t.dig_begin = pos + p; t.exp10 = 0;
+    t.neg = (uint8_t)neg; t.is_int = L2 == 0; t.truncated = 0; t.special = 0; t.err = TK_OK;
+    t.nsig = (int32_t)(L1 + L2); t.frac_digits = (int32_t)L2;
+    *out = t;
+    return true;
+}
+
 template <int KIND, class R>
 __device__ __forceinline__ int json_element_fast(const R& rd, uint32_t pos, typename tk_elem<KIND>::type* out) {
     tk_token t;
-    if (!fast_scan_number(rd, pos, &t)) return tk_json_element<KIND>(rd, pos, out);
-    int st = fast_gap(rd, t.end);
+    int st = -1;
+    if (!fast_token24(rd, pos, &t, &st)) {
+        if (!fast_scan_number(rd, pos, &t)) return tk_json_element<KIND>(rd, pos, out);
+    }
+    if (st) st = fast_gap(rd, t.end);
     if (st) return st;
     if (KIND == TK_F32 || KIND == TK_F64) {
         double d;

@@ -1,0 +1,175 @@
+#!/usr/bin/env python3
+"""Per-config measurements for the five BASELINE.json configs (SURVEY.md §8d reporting).
+
+For every config:
+  device   records/s and payload GB/s of the slot kernel sequence with the slot already in HBM
+           (CUDA events on the engine stream, 4 distinct slots cycled so inputs come from HBM)
+  e2e      records/s through the public API (auto_commit(DataLoader(dataset))) from host
+           ConsumerRecord objects (poll) and from flat arrays (poll_packed), with link fraction
+           against the measured H2D peak
+  cpu      the oracle (reference algorithm) on one core, bounded sample
+
+Writes one JSON object per config to stdout / --out.  `bench.py` stays the contract benchmark
+(config 2); this script is the wider table that goes into profiles/.
+"""
+import argparse
+import json
+import os
+import sys
+import time
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+
+import numpy as np      # noqa: E402
+import torch            # noqa: E402
+
+from torchkafka_b200 import KafkaDataset, auto_commit                                   # noqa: E402
+from torchkafka_b200.engine import SlotEngine                                           # noqa: E402
+from torchkafka_b200.schema import ImageU8, JsonArray, RawBytes, TokenList              # noqa: E402
+from torchkafka_b200.testing import stub_kafka as sk                                    # noqa: E402
+from torchkafka_b200.testing import synthetic as syn                                    # noqa: E402
+
+CONFIGS = {
+    1: dict(name="cfg1 README 8 floats", schema=JsonArray(torch.float32, fixed_len=8), batch=4,
+            n=60000, slot_bytes=8 << 20),
+    2: dict(name="cfg2 varlen floats, min_size=32", schema=JsonArray(torch.float32, max_len=256, min_size=32),
+            batch=1024, n=17600, slot_bytes=48 << 20),
+    3: dict(name="cfg3 token lists <= 2048", schema=TokenList(torch.int32, max_len=2048), batch=512,
+            n=6144, slot_bytes=48 << 20),
+    4: dict(name="cfg4 224x224x3 images -> bf16 NCHW", schema=ImageU8(224, 224, 3), batch=256,
+            n=256, slot_bytes=256 * 150528),
+    5: dict(name="cfg5 64-byte records, commit offsets", schema=RawBytes((64,), torch.uint8), batch=256,
+            n=262144, slot_bytes=17 << 20),
+}
+
+
+def arrays(log):
+    return log.values, log.starts.astype(np.uint32), log.partitions, log.offsets
+
+
+def device_resident(cfg, log, passes=24):
+    eng = SlotEngine(cfg["schema"], cfg["batch"], slot_bytes=max(cfg["slot_bytes"], log.nbytes + 4096),
+                     slot_records=len(log), n_slots=4, device=0, n_partitions=64)
+    for s in range(4):
+        n, nb = eng.fill_packed(s, *arrays(log))
+        eng.submit(s, n, nb)
+    torch.cuda.synchronize()
+
+    def run(k):
+        prev_slot, prev_out = None, None
+        for i in range(k):
+            s = i % 4
+            eng.assume_resident(s, len(log), log.nbytes)
+            out = eng.process(s, len(log), prev_slot, prev_out, resident=True)
+            prev_slot, prev_out = s, out
+    run(4)
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record(eng.stream)
+    run(passes)
+    e1.record(eng.stream)
+    torch.cuda.synchronize()
+    ms = e0.elapsed_time(e1) / passes
+    res = eng.result((passes - 1) % 4)
+    assert res.n_errors == 0
+    peak = eng.h2d_peak_gbs(256 << 20, 5)
+    eng.close()
+    return {"ms_per_slot": ms, "records_per_s": len(log) / ms * 1e3,
+            "payload_GBps": (log.nbytes + 16 * len(log)) / ms / 1e6}, peak
+
+
+def e2e(cfg, log, packed, repeat, batches_timed, warm):
+    consumer_cls = sk.KafkaConsumer if packed else sk.PollOnlyConsumer
+
+    class DS(KafkaDataset):
+        payload_schema = cfg["schema"]
+        device_slot_bytes = cfg["slot_bytes"]
+        device_slots = 3
+
+        @classmethod
+        def new_consumer(cls, *a, **k):
+            k.pop("enable_auto_commit", None)
+            return consumer_cls(*a, log=log, repeat=repeat, **k)
+
+    from torch.utils.data import DataLoader
+    ds = DS("topic", group_id="cfg")
+    seen, t0, t1 = 0, None, None
+    last = None
+    for batch in auto_commit(DataLoader(ds, batch_size=cfg["batch"])):
+        if seen == warm:
+            torch.cuda.synchronize()
+            t0 = time.perf_counter()
+            r0 = ds._consumer.consumed
+        last = batch
+        seen += 1
+        if seen == warm + batches_timed:
+            torch.cuda.synchronize()
+            t1 = time.perf_counter()
+            break
+    if t1 is None:
+        torch.cuda.synchronize()
+        t1 = time.perf_counter()
+    kept = (seen - warm) * cfg["batch"]
+    stats = dict(ds.last_pipeline_stats) if ds._pipeline is None else dict(ds._pipeline.stats)
+    keep_rate = (stats.get("kept", 1) / max(stats.get("records", 1), 1)) if stats else 1.0
+    ds.close()
+    del last
+    return kept / max(keep_rate, 1e-9) / (t1 - t0)
+
+
+def cpu_oracle(cfg, log, seconds=6.0):
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    from helpers import oracle_process
+    from oracle import reference_path as ref
+    torch.set_num_threads(1)
+    sc = cfg["schema"]
+    variable = isinstance(sc, JsonArray) and sc.fixed_len is None
+    collate = ref.pad_collate if variable else ref.default_collate
+    consumer = sk.KafkaConsumer("topic", log=log, repeat=1000)
+    t0 = time.perf_counter()
+    for _ in ref.run(consumer, oracle_process(sc), cfg["batch"], False, collate):
+        if time.perf_counter() - t0 > seconds:
+            break
+    return consumer.consumed / (time.perf_counter() - t0)
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--configs", default="1,2,3,4,5")
+    ap.add_argument("--out", default=None)
+    ap.add_argument("--no-cpu", action="store_true")
+    args = ap.parse_args()
+    rows = []
+    for c in [int(x) for x in args.configs.split(",")]:
+        cfg = CONFIGS[c]
+        log = syn.make_log(c, cfg["n"], seed=100 + c, partitions=64, layout="chunked", chunk=500)
+        dev, peak = device_resident(cfg, log)
+        link_bytes = (log.nbytes + 16 * len(log)) / len(log)
+        slot_recs = max(1, min(len(log), int(cfg["slot_bytes"] // max(log.nbytes / len(log), 1))))
+        per_batch_recs = cfg["batch"]
+        # enough repetitions for ~40 slots of work
+        target_records = 40 * slot_recs
+        repeat = max(2, target_records // len(log) + 2)
+        for r in range(repeat):
+            log.rep_records(r)
+        nb = max(8, int(0.8 * target_records / per_batch_recs))
+        warm = max(3, nb // 8)
+        row = {"config": c, "name": cfg["name"], "records": len(log), "avg_value_bytes": log.nbytes / len(log),
+               "link_bytes_per_record": link_bytes, "device": dev, "h2d_peak_GBps": peak}
+        for packed in (False, True):
+            rps = e2e(cfg, log, packed, repeat, nb - warm, warm)
+            row["e2e_packed" if packed else "e2e_poll"] = {
+                "records_per_s": rps, "link_GBps": rps * link_bytes / 1e9,
+                "link_frac": rps * link_bytes / 1e9 / peak}
+        if not args.no_cpu:
+            row["cpu_oracle_1core_records_per_s"] = cpu_oracle(cfg, log)
+        rows.append(row)
+        print(json.dumps(row), flush=True)
+    if args.out:
+        with open(args.out, "w") as f:
+            json.dump(rows, f, indent=1)
+
+
+if __name__ == "__main__":
+    main()

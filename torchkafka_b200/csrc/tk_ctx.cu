@@ -196,7 +196,7 @@ static int create_impl(tk_ctx* ctx) {
     const size_t nrec = ctx->slot_records;
     const size_t nb = ctx->max_batches + 1;
     const size_t commit_elems = (size_t)ctx->n_partitions * ctx->commit_pitch;
-    const size_t nblk = (nrec + 1023) / 1024 + 1;
+    const size_t nblk = (nrec + 255) / 256 + 1;      // one entry per compaction tile (tk_plan.cu CMP_TILE)
     for (int i = 0; i < ctx->n_slots; ++i) {
         tk_slot& s = ctx->slots[i];
         TK_CUDA(cudaHostAlloc(&s.h_bytes, ctx->slot_bytes + TK_BYTES_PAD, cudaHostAllocDefault));

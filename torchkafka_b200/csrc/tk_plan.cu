@@ -14,8 +14,8 @@
 // along the batch axis seeded with the positions of earlier slots.
 #include "tk_internal.h"
 
-#define CMP_THREADS 256
-#define CMP_ITEMS 4
+#define CMP_THREADS 128
+#define CMP_ITEMS 2
 #define CMP_TILE (CMP_THREADS * CMP_ITEMS)
 
 __device__ __forceinline__ uint32_t warp_incl_scan(uint32_t v) {
@@ -46,7 +46,7 @@ __device__ __forceinline__ uint32_t block_excl_scan(uint32_t v, uint32_t* total)
     return r;
 }
 
-// pass 1: kept count per tile of 1024 records
+// pass 1: kept count per tile of CMP_TILE records
 __global__ void __launch_bounds__(CMP_THREADS) k_compact_count(const int32_t* __restrict__ rec_kidx,
                                                                  uint32_t n, uint32_t* __restrict__ blk_sum) {
     __shared__ uint32_t tot;
@@ -129,7 +129,9 @@ __global__ void __launch_bounds__(CMP_THREADS) k_compact_apply(int32_t* __restri
             rec_kidx[i] = (int32_t)ex;
             const uint32_t q = carry + ex;
             const uint32_t j = q / B;
-            atomicMax(&batch_lmax[j], (uint32_t)rec_len[i]);
+            // most records are shorter than the running maximum: read before the atomic
+            const uint32_t len = (uint32_t)rec_len[i];
+            if (len > *(volatile uint32_t*)&batch_lmax[j]) atomicMax(&batch_lmax[j], len);
             if ((q + 1) % B == 0) batch_end[j] = i;
             ++ex;
         } else {

@@ -127,6 +127,8 @@ class SlotEngine:
             cores = len(os.sched_getaffinity(0))
         except AttributeError:  # pragma: no cover
             cores = os.cpu_count() or 1
+        # several ranks on one host (torchrun) share its cores
+        cores = max(1, cores // max(1, int(os.environ.get("LOCAL_WORLD_SIZE", "1"))))
         #: threads used by the pinned-memory pack (payload memcpy)
         self.pack_threads = int(os.environ.get("TK_PACK_THREADS", 0)) or max(1, min(8, (cores - 2) // 2))
 

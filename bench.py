@@ -389,16 +389,20 @@ def main_gpu(args):
     rank, local_rank, world = dist_env()
     if world > 1:
         import torch.distributed as dist
-        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+        # One rank per GPU.  The data path has no collective (partition sharding); the only
+        # exchanges here are the barrier and the max-over-ranks of three timings, done on host
+        # tensors (gloo) so that no NCCL banner can leak into the single JSON line on stdout.
+        dist.init_process_group("cpu:gloo,cuda:nccl")
     device = local_rank if world > 1 else 0
     torch.cuda.set_device(device)
     steps, warmup = args.steps, max(args.warmup, 0)
     base = build_base_log(SLOT_BATCHES)
 
     def barrier():
+        torch.cuda.synchronize()
         if world > 1:
             import torch.distributed as dist
-            dist.barrier()
+            dist.all_reduce(torch.zeros(1))          # host-side barrier (gloo)
         torch.cuda.synchronize()
 
     # ---- value: device-resident
@@ -425,8 +429,7 @@ def main_gpu(args):
 
     rec_per_step = len(base) / SLOT_BATCHES
     bytes_per_step = (base.nbytes + 16 * len(base)) / SLOT_BATCHES
-    t = torch.tensor([dev["ms"], e2e_poll["seconds"], e2e_packed["seconds"]], dtype=torch.float64,
-                     device=f"cuda:{device}")
+    t = torch.tensor([dev["ms"], e2e_poll["seconds"], e2e_packed["seconds"]], dtype=torch.float64)
     if world > 1:
         import torch.distributed as dist
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
@@ -485,7 +488,7 @@ def main_gpu(args):
         print(json.dumps(line), flush=True)
     if world > 1:
         import torch.distributed as dist
-        dist.barrier()
+        dist.all_reduce(torch.zeros(1))
         dist.destroy_process_group()
     return 0
 

@@ -12,35 +12,28 @@
 #include <Python.h>
 #include <stdint.h>
 
-// harvest(records, value_idx, offset_idx, first, max_records, max_bytes,
-//         ptrs_addr, lens_addr, offs_addr) -> (taken, total_bytes, keepalive_or_None)
-//   records     list/tuple of record objects (namedtuples take the index fast path;
-//               value_idx/offset_idx < 0 => attribute lookup by name)
-//   first       index of the first record to take
-//   *_addr      addresses of uint64[max_records], uint32[max_records], int64[max_records]
-static PyObject* harvest(PyObject*, PyObject* args) {
-    PyObject* records;
-    Py_ssize_t vi, oi, first, max_records;
-    unsigned long long max_bytes, ptrs_addr, lens_addr, offs_addr;
-    if (!PyArg_ParseTuple(args, "OnnnnKKKK", &records, &vi, &oi, &first, &max_records, &max_bytes,
-                          &ptrs_addr, &lens_addr, &offs_addr))
-        return nullptr;
-    PyObject* seq = PySequence_Fast(records, "records must be a sequence");
-    if (!seq) return nullptr;
+struct Sink {
+    uint64_t* ptrs;
+    uint32_t* lens;
+    int64_t* offs;
+    Py_ssize_t taken;            // records written so far
+    Py_ssize_t max_records;
+    unsigned long long total;    // payload bytes so far
+    unsigned long long max_bytes;
+    PyObject* keep;              // owns temporaries of the slow paths (created on demand)
+};
+
+static PyObject* s_value = nullptr;
+static PyObject* s_offset = nullptr;
+
+// Append records of `seq` (from index `first`) to the sink until it is full.
+// Returns the number of records taken from this sequence, or -1 with an exception set.
+static Py_ssize_t harvest_into(Sink& k, PyObject* seq, Py_ssize_t vi, Py_ssize_t oi, Py_ssize_t first) {
     const Py_ssize_t n = PySequence_Fast_GET_SIZE(seq);
     PyObject** items = PySequence_Fast_ITEMS(seq);
-    uint64_t* ptrs = reinterpret_cast<uint64_t*>(ptrs_addr);
-    uint32_t* lens = reinterpret_cast<uint32_t*>(lens_addr);
-    int64_t* offs = reinterpret_cast<int64_t*>(offs_addr);
-    PyObject* keep = nullptr;      // owns temporaries of the slow paths
-    static PyObject* s_value = nullptr;
-    static PyObject* s_offset = nullptr;
-    if (!s_value) { s_value = PyUnicode_InternFromString("value"); s_offset = PyUnicode_InternFromString("offset"); }
-
-    Py_ssize_t taken = 0;
-    unsigned long long total = 0;
     const bool fast = vi >= 0;
-    for (Py_ssize_t i = first; i < n && taken < max_records; ++i) {
+    Py_ssize_t i = first;
+    for (; i < n && k.taken < k.max_records; ++i) {
         PyObject* rec = items[i];
         // Each record is three dependent cache misses (record tuple -> value bytes header,
         // offset int).  Prefetch the tuple 16 records ahead and its two fields 8 ahead.
@@ -56,59 +49,127 @@ static PyObject* harvest(PyObject*, PyObject* args) {
         }
         PyObject *val, *off;
         bool own = false;
-        if (vi >= 0 && PyTuple_Check(rec) && PyTuple_GET_SIZE(rec) > vi && PyTuple_GET_SIZE(rec) > oi) {
+        if (fast && PyTuple_Check(rec) && PyTuple_GET_SIZE(rec) > vi && PyTuple_GET_SIZE(rec) > oi) {
             val = PyTuple_GET_ITEM(rec, vi);
             off = PyTuple_GET_ITEM(rec, oi);
         } else {
             val = PyObject_GetAttr(rec, s_value);
-            if (!val) goto fail;
+            if (!val) return -1;
             off = PyObject_GetAttr(rec, s_offset);
-            if (!off) { Py_DECREF(val); goto fail; }
+            if (!off) { Py_DECREF(val); return -1; }
             own = true;
         }
         if (val == Py_None) {                      // tombstone: empty payload
-            if (own) { Py_DECREF(val); }
+            if (own) Py_DECREF(val);
             val = nullptr;
         } else if (!PyBytes_Check(val)) {          // bytearray / memoryview / ...: materialise once
             PyObject* b = PyBytes_FromObject(val);
             if (own) Py_DECREF(val);
-            if (!b) { if (own) Py_DECREF(off); goto fail; }
-            if (!keep && !(keep = PyList_New(0))) { Py_DECREF(b); if (own) Py_DECREF(off); goto fail; }
-            PyList_Append(keep, b);
+            if (!b) { if (own) Py_DECREF(off); return -1; }
+            if (!k.keep && !(k.keep = PyList_New(0))) { Py_DECREF(b); if (own) Py_DECREF(off); return -1; }
+            PyList_Append(k.keep, b);
             Py_DECREF(b);
             val = b;
         } else if (own) {
-            if (!keep && !(keep = PyList_New(0))) { Py_DECREF(val); Py_DECREF(off); goto fail; }
-            PyList_Append(keep, val);
+            if (!k.keep && !(k.keep = PyList_New(0))) { Py_DECREF(val); Py_DECREF(off); return -1; }
+            PyList_Append(k.keep, val);
             Py_DECREF(val);
         }
-        {
-            const Py_ssize_t len = val ? PyBytes_GET_SIZE(val) : 0;
-            if (total + (unsigned long long)len > max_bytes) { if (own) Py_DECREF(off); break; }
-            const long long o = PyLong_AsLongLong(off);
-            if (own) Py_DECREF(off);
-            if (o == -1 && PyErr_Occurred()) goto fail;
-            ptrs[taken] = val ? (uint64_t)(uintptr_t)PyBytes_AS_STRING(val) : 0;
-            lens[taken] = (uint32_t)len;
-            offs[taken] = o;
-            total += (unsigned long long)len;
-            ++taken;
+        const Py_ssize_t len = val ? PyBytes_GET_SIZE(val) : 0;
+        if (k.total + (unsigned long long)len > k.max_bytes) { if (own) Py_DECREF(off); break; }
+        const long long o = PyLong_AsLongLong(off);
+        if (own) Py_DECREF(off);
+        if (o == -1 && PyErr_Occurred()) return -1;
+        k.ptrs[k.taken] = val ? (uint64_t)(uintptr_t)PyBytes_AS_STRING(val) : 0;
+        k.lens[k.taken] = (uint32_t)len;
+        k.offs[k.taken] = o;
+        k.total += (unsigned long long)len;
+        ++k.taken;
+    }
+    return i - first;
+}
+
+static void intern_names() {
+    if (!s_value) { s_value = PyUnicode_InternFromString("value"); s_offset = PyUnicode_InternFromString("offset"); }
+}
+
+// harvest(records, value_idx, offset_idx, first, max_records, max_bytes,
+//         ptrs_addr, lens_addr, offs_addr) -> (taken, total_bytes, keepalive_or_None)
+//   records     list/tuple of record objects (namedtuples take the index fast path;
+//               value_idx/offset_idx < 0 => attribute lookup by name)
+//   first       index of the first record to take
+//   *_addr      addresses of uint64[max_records], uint32[max_records], int64[max_records]
+static PyObject* harvest(PyObject*, PyObject* args) {
+    PyObject* records;
+    Py_ssize_t vi, oi, first, max_records;
+    unsigned long long max_bytes, ptrs_addr, lens_addr, offs_addr;
+    if (!PyArg_ParseTuple(args, "OnnnnKKKK", &records, &vi, &oi, &first, &max_records, &max_bytes,
+                          &ptrs_addr, &lens_addr, &offs_addr))
+        return nullptr;
+    intern_names();
+    PyObject* seq = PySequence_Fast(records, "records must be a sequence");
+    if (!seq) return nullptr;
+    Sink k = {reinterpret_cast<uint64_t*>(ptrs_addr), reinterpret_cast<uint32_t*>(lens_addr),
+              reinterpret_cast<int64_t*>(offs_addr), 0, max_records, 0, max_bytes, nullptr};
+    const Py_ssize_t got = harvest_into(k, seq, vi, oi, first);
+    Py_DECREF(seq);
+    if (got < 0) { Py_XDECREF(k.keep); return nullptr; }
+    PyObject* r = Py_BuildValue("(nKO)", k.taken, k.total, k.keep ? k.keep : Py_None);
+    Py_XDECREF(k.keep);
+    return r;
+}
+
+// harvest_groups(groups, dense, value_idx, offset_idx, max_records, max_bytes,
+//                ptrs_addr, lens_addr, offs_addr, parts_addr)
+//     -> (taken, total_bytes, groups_done, taken_in_last_group, keepalive_or_None)
+//   groups   list of (topic_partition, records) pairs -- list(poll_result.items())
+//   dense    list of int: dense partition index of each group (written to parts[] per record)
+// Processes whole poll results in one call.  Stops when the sink is full: `groups_done` groups
+// were taken completely and `taken_in_last_group` records of group number `groups_done`.
+static PyObject* harvest_groups(PyObject*, PyObject* args) {
+    PyObject *groups, *dense;
+    Py_ssize_t vi, oi, max_records;
+    unsigned long long max_bytes, ptrs_addr, lens_addr, offs_addr, parts_addr;
+    if (!PyArg_ParseTuple(args, "OOnnnKKKKK", &groups, &dense, &vi, &oi, &max_records, &max_bytes,
+                          &ptrs_addr, &lens_addr, &offs_addr, &parts_addr))
+        return nullptr;
+    intern_names();
+    if (!PyList_Check(groups) || !PyList_Check(dense) || PyList_GET_SIZE(groups) != PyList_GET_SIZE(dense)) {
+        PyErr_SetString(PyExc_TypeError, "groups and dense must be lists of equal length");
+        return nullptr;
+    }
+    int32_t* parts = reinterpret_cast<int32_t*>(parts_addr);
+    Sink k = {reinterpret_cast<uint64_t*>(ptrs_addr), reinterpret_cast<uint32_t*>(lens_addr),
+              reinterpret_cast<int64_t*>(offs_addr), 0, max_records, 0, max_bytes, nullptr};
+    const Py_ssize_t ng = PyList_GET_SIZE(groups);
+    Py_ssize_t g = 0, partial = 0;
+    for (; g < ng; ++g) {
+        PyObject* pair = PyList_GET_ITEM(groups, g);
+        if (!PyTuple_Check(pair) || PyTuple_GET_SIZE(pair) != 2) {
+            PyErr_SetString(PyExc_TypeError, "each group must be a (partition, records) pair");
+            Py_XDECREF(k.keep);
+            return nullptr;
         }
+        const long d = PyLong_AsLong(PyList_GET_ITEM(dense, g));
+        if (d == -1 && PyErr_Occurred()) { Py_XDECREF(k.keep); return nullptr; }
+        PyObject* seq = PySequence_Fast(PyTuple_GET_ITEM(pair, 1), "records must be a sequence");
+        if (!seq) { Py_XDECREF(k.keep); return nullptr; }
+        const Py_ssize_t before = k.taken;
+        const Py_ssize_t size = PySequence_Fast_GET_SIZE(seq);
+        const Py_ssize_t got = harvest_into(k, seq, vi, oi, 0);
+        Py_DECREF(seq);
+        if (got < 0) { Py_XDECREF(k.keep); return nullptr; }
+        for (Py_ssize_t j = before; j < k.taken; ++j) parts[j] = (int32_t)d;
+        if (got < size) { partial = got; break; }
     }
-    Py_DECREF(seq);
-    {
-        PyObject* r = Py_BuildValue("(nKO)", taken, total, keep ? keep : Py_None);
-        Py_XDECREF(keep);
-        return r;
-    }
-fail:
-    Py_DECREF(seq);
-    Py_XDECREF(keep);
-    return nullptr;
+    PyObject* r = Py_BuildValue("(nKnnO)", k.taken, k.total, g, partial, k.keep ? k.keep : Py_None);
+    Py_XDECREF(k.keep);
+    return r;
 }
 
 static PyMethodDef methods[] = {
     {"harvest", harvest, METH_VARARGS, "Collect (address, length, offset) of every record's value."},
+    {"harvest_groups", harvest_groups, METH_VARARGS, "harvest() over a whole poll() result."},
     {nullptr, nullptr, 0, nullptr}};
 
 static struct PyModuleDef moddef = {PyModuleDef_HEAD_INIT, "_tkpack", "torchkafka_b200 pack helper", -1, methods};

@@ -190,7 +190,7 @@ class IngestPipeline:
         and offset of each value); the payload bytes are gathered afterwards by ``_pack_poll``.
         """
         eng = self.engine
-        ptrs, lens, offs, parts = scratch
+        ptrs, lens, offs, parts, addr = scratch
         n = 0
         nbytes = 0
         empty = 0
@@ -211,35 +211,34 @@ class IngestPipeline:
                         break
                     continue
                 items = list(polled.items())
-            for k, (tp, recs) in enumerate(items):
-                if not recs:
-                    continue
-                d = self._dense(tp)
-                vi, oi = self._indices(recs[0])
-                t0 = time.perf_counter()
-                taken, tot, keep = _tkpack.harvest(
-                    recs, vi, oi, 0, eng.slot_records - n, eng.slot_bytes - nbytes,
-                    ptrs.ctypes.data + 8 * n, lens.ctypes.data + 4 * n, offs.ctypes.data + 8 * n)
-                self.stats["t_harvest"] += time.perf_counter() - t0
-                hold.append(recs)
-                if keep is not None:
-                    hold.append(keep)
-                parts[n:n + taken] = d
-                n += taken
-                nbytes += tot
-                if taken < len(recs):
-                    # the slot is full inside this partition's run: records cannot be un-polled,
-                    # so the rest waits, in consumption order, for the next slot
-                    if taken == 0 and n == 0:
-                        raise ValueError("a single record exceeds the slot size "
-                                         f"({eng.slot_bytes} bytes); raise device_slot_bytes")
-                    self._leftover = [(tp, recs[taken:])] + items[k + 1:]
-                    full = True
-                    break
+            items = [it for it in items if it[1]]
+            if not items:
+                continue
+            dense = [self._dense(tp) for tp, _ in items]
+            vi, oi = self._indices(items[0][1][0])
+            t0 = time.perf_counter()
+            taken, tot, g_done, partial, keep = _tkpack.harvest_groups(
+                items, dense, vi, oi, eng.slot_records - n, eng.slot_bytes - nbytes,
+                addr[0] + 8 * n, addr[1] + 4 * n, addr[2] + 8 * n, addr[3] + 4 * n)
+            self.stats["t_harvest"] += time.perf_counter() - t0
+            hold.append(items)
+            if keep is not None:
+                hold.append(keep)
+            n += taken
+            nbytes += tot
+            if g_done < len(items):
+                # the slot is full inside group g_done: records cannot be un-polled, so the
+                # rest waits, in consumption order, for the next slot
+                if taken == 0 and n == 0:
+                    raise ValueError("a single record exceeds the slot size "
+                                     f"({eng.slot_bytes} bytes); raise device_slot_bytes")
+                tp, recs = items[g_done]
+                self._leftover = [(tp, recs[partial:])] + items[g_done + 1:]
+                full = True
         return n, nbytes, hold
 
     def _pack_poll(self, slot: int, scratch, n: int, hold):
-        ptrs, lens, offs, parts = scratch
+        ptrs, lens, offs, parts, _ = scratch
         t0 = time.perf_counter()
         self.engine.pack_pointers(slot, ptrs, lens, parts, offs, n)
         self.stats["t_pack"] += time.perf_counter() - t0
@@ -248,8 +247,9 @@ class IngestPipeline:
 
     def _new_scratch(self):
         cap = self.engine.slot_records
-        return (np.zeros(cap, np.uint64), np.zeros(cap, np.uint32), np.zeros(cap, np.int64),
+        arrs = (np.zeros(cap, np.uint64), np.zeros(cap, np.uint32), np.zeros(cap, np.int64),
                 np.zeros(cap, np.int32))
+        return arrs + (tuple(a.ctypes.data for a in arrs),)
 
     # ------------------------------------------------------------------ iteration
     def _error(self, item, res) -> PayloadError:

@@ -188,3 +188,42 @@ def test_too_long_and_ragged():
 def test_raw_wrong_size():
     with pytest.raises(PayloadError):
         run_gpu(RecordLog([b"x" * 64, b"y" * 63], [0, 0], [0, 1]), RawBytes((64,)), 2)
+
+
+def test_live_stream_with_pauses_and_batch_iteration():
+    """A consumer whose poll() comes back empty now and then (a live topic) must not end the
+    iteration before its idle timeout, and partly filled slots must still be delivered."""
+    import torch
+    from torch.utils.data import DataLoader
+    from helpers import run_oracle, to_cpu
+    from torchkafka_b200 import KafkaDataset
+    from torchkafka_b200.testing import stub_kafka as sk
+
+    log = syn.make_log(2, 900, seed=21, layout="chunked", chunk=50)
+    sc = JsonArray(torch.float32, max_len=256, min_size=32)
+
+    class Hiccup(sk.PollOnlyConsumer):
+        calls = 0
+
+        def poll(self, timeout_ms=0, max_records=None, update_offsets=True):
+            Hiccup.calls += 1
+            if Hiccup.calls % 3 == 0:
+                return {}                               # nothing arrived within the timeout
+            return super().poll(timeout_ms, min(max_records or 64, 64), update_offsets)
+
+    class DS(KafkaDataset):
+        payload_schema = sc
+        device_batch_size = 128
+
+        @classmethod
+        def new_consumer(cls, *a, **k):
+            k.pop("enable_auto_commit", None)
+            return Hiccup(*a, log=log, consumer_timeout_ms=300, **k)
+
+    ds = DS("topic")
+    got = [to_cpu(b) for b in DataLoader(ds, batch_size=None)]      # plain iteration, whole batches
+    want = run_oracle(log, sc, 128)
+    assert len(got) == len(want)
+    for g, (w, _) in zip(got, want):
+        assert torch.equal(g.values, w[0]) and torch.equal(g.lengths, w[1])
+    ds.close()

@@ -91,6 +91,9 @@ class KafkaDataset(IterableDataset):
     device_slots = 3
     device_index = None
     max_partitions = 64
+    #: when set, plain iteration (``for b in DataLoader(ds, batch_size=None)``) yields whole
+    #: device batches of this size instead of single samples
+    device_batch_size = None
     #: poll + pack + H2D on a producer thread (overlaps the user's loop); False = same thread
     device_producer_thread = True
     device_producers = 2
@@ -264,6 +267,9 @@ class KafkaDataset(IterableDataset):
         """
         from .schema import JsonArray
         schema = self.payload_schema
+        if self.device_batch_size:
+            yield from self.device_batches(int(self.device_batch_size), False)
+            return
         for batch in self.device_batches(1, False):
             if isinstance(schema, JsonArray) and schema.fixed_len is None:
                 n = int(batch.lengths[0])

@@ -70,7 +70,7 @@ class _Pending:
 class IngestPipeline:
     def __init__(self, consumer, schema, batch_size: int, drop_last: bool = False,
                  slot_bytes: int = 64 << 20, n_slots: int = 3, device: Optional[int] = None,
-                 max_partitions: int = 64, poll_timeout_ms: int = 100, max_empty_polls: int = 1,
+                 max_partitions: int = 64, poll_timeout_ms: int = 100, max_empty_polls: int = 1,  # noqa: ARG002
                  threaded: bool = True, commit_all_partitions: bool = False,
                  n_producers: int = 2):
         self.consumer = consumer
@@ -82,6 +82,14 @@ class IngestPipeline:
                                  device=device, n_partitions=max_partitions)
         self.poll_timeout_ms = poll_timeout_ms
         self.max_empty_polls = max_empty_polls
+        # kafka-python ends `for record in consumer` after consumer_timeout_ms without a record
+        # (default: never).  The GPU path follows the same setting; the in-memory stub
+        # advertises 0 ("end of log is end of stream").
+        timeout = getattr(consumer, "consumer_timeout_ms", None)
+        if timeout is None:
+            cfg = getattr(consumer, "config", None)
+            timeout = cfg.get("consumer_timeout_ms", float("inf")) if isinstance(cfg, dict) else float("inf")
+        self.idle_timeout_s = float(timeout) / 1e3
         self.threaded = bool(threaded)
         #: serialises consumer calls: the producer thread polls, the user's thread commits,
         #: and kafka-python consumers are not safe for concurrent calls
@@ -144,12 +152,19 @@ class IngestPipeline:
     # order), _pack_* moves the payload into pinned memory (parallel, GIL released).
     def _gather_packed(self, slot: int, scratch):
         eng = self.engine
-        t0 = time.perf_counter()
-        with self.consumer_lock:
-            run = self.consumer.poll_packed(eng.slot_records, eng.slot_bytes)
-        self.stats["t_poll"] += time.perf_counter() - t0
-        if run is None or len(run) == 0:
-            return 0, 0, None
+        idle_since = None
+        while True:
+            t0 = time.perf_counter()
+            with self.consumer_lock:
+                run = self.consumer.poll_packed(eng.slot_records, eng.slot_bytes)
+            self.stats["t_poll"] += time.perf_counter() - t0
+            if run is not None and len(run):
+                break
+            if idle_since is None:
+                idle_since = time.monotonic()
+            if self._stop.is_set() or time.monotonic() - idle_since >= self.idle_timeout_s:
+                return 0, 0, None
+            time.sleep(min(self.poll_timeout_ms, 50) / 1e3)
         topic = getattr(run, "topic", None) or "topic"
         parts = np.asarray(run.partitions)
         # dense index == raw partition id on this path (single topic)
@@ -193,7 +208,7 @@ class IngestPipeline:
         ptrs, lens, offs, parts, addr = scratch
         n = 0
         nbytes = 0
-        empty = 0
+        idle_since = None
         hold = []                       # keeps the record objects (and their bytes) alive until packed
         full = False
         while not full and n < eng.slot_records:
@@ -206,10 +221,16 @@ class IngestPipeline:
                                                 max_records=min(eng.slot_records - n, 1 << 16))
                 self.stats["t_poll"] += time.perf_counter() - t0
                 if not polled:
-                    empty += 1
-                    if n > 0 or empty >= self.max_empty_polls or self._stop.is_set():
+                    # a partly filled slot is shipped as soon as the stream pauses (bounded
+                    # latency); an empty one keeps polling until the consumer's idle timeout
+                    if n > 0 or self._stop.is_set():
+                        break
+                    if idle_since is None:
+                        idle_since = time.monotonic()
+                    if time.monotonic() - idle_since >= self.idle_timeout_s:
                         break
                     continue
+                idle_since = None
                 items = list(polled.items())
             items = [it for it in items if it[1]]
             if not items:

@@ -176,6 +176,9 @@ class KafkaConsumer:
                  fail_commits: bool = False, repeat: int = 1, **configs):
         self.topics = topics
         self.config = dict(configs)
+        # the end of the in-memory log is the end of the stream, unless the stub is told to
+        # behave like a live consumer (block_at_end)
+        self.consumer_timeout_ms = configs.get("consumer_timeout_ms", float("inf") if block_at_end else 0)
         self._log = log if log is not None else RecordLog([], [], [])
         self._cursor = 0
         self._rep = 0                  # current repetition of the log (see ``repeat``)

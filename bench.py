@@ -37,7 +37,7 @@ if ROOT not in sys.path:
 BATCH = 1024
 MAX_LEN = 256
 MIN_SIZE = 32
-SLOT_BATCHES = 16
+SLOT_BATCHES = int(os.environ.get("TK_SLOT_BATCHES", "32"))
 PARTITIONS = 64
 SEED = 2026
 METRIC = "records/sec"

@@ -128,10 +128,13 @@ int tk_raw_scan(tk_ctx* ctx, int slot, uint64_t record_bytes, void* stream);
  *      batch boundaries (a batch closes on its batch_size-th kept record)
  * replaces `if data is not None: yield data` (src/kafka_dataset.py:161-162) and
  * the batch_size loop of _IterableDatasetFetcher.fetch (fetch.py:33-38) */
+/* (the same pass also accumulates, per (batch, partition), the largest offset + 1 it sees:
+ * the segmented-max half of K4, done here because the batch index of each record is at hand) */
 int tk_compact(tk_ctx* ctx, int slot, uint32_t batch_size, void* stream);
 
 /* ---- K4: per batch, per partition: max(offset)+1 over every record consumed up
- *      to the record that closed the batch (segmented max + running max)
+ *      to the record that closed the batch (segmented max, see tk_compact, + running max
+ *      along the batches and across slots, done here; call after tk_compact)
  * replaces KafkaConsumer.commit() position bookkeeping reached from
  * src/auto_commit.py:58 -> src/kafka_dataset.py:130 */
 int tk_commit_offsets(tk_ctx* ctx, int slot, void* stream);

@@ -155,13 +155,9 @@ __global__ void tk_fill_i64(int64_t* p, int64_t v, uint32_t n) {
 static void free_slot(tk_slot& s) {
     if (s.h_bytes) cudaFreeHost(s.h_bytes);
     if (s.h_recs) cudaFreeHost(s.h_recs);
-    if (s.h_result) cudaFreeHost(s.h_result);
-    if (s.h_batch_end) cudaFreeHost(s.h_batch_end);
-    if (s.h_batch_lmax) cudaFreeHost(s.h_batch_lmax);
-    if (s.h_commit) cudaFreeHost(s.h_commit);
+    if (s.h_block) cudaFreeHost(s.h_block);
     cudaFree(s.d.bytes); cudaFree(s.d.recs); cudaFree(s.d.rec_len); cudaFree(s.d.rec_status);
-    cudaFree(s.d.rec_kidx); cudaFree(s.d.blk_sum); cudaFree(s.d.result); cudaFree(s.d.batch_end);
-    cudaFree(s.d.batch_lmax); cudaFree(s.d.commit);
+    cudaFree(s.d.rec_kidx); cudaFree(s.d.blk_sum); cudaFree(s.d.block);
     if (s.ev_h2d) cudaEventDestroy(s.ev_h2d);
     if (s.ev_free) cudaEventDestroy(s.ev_free);
     if (s.ev_result) cudaEventDestroy(s.ev_result);
@@ -201,10 +197,16 @@ static int create_impl(tk_ctx* ctx) {
         tk_slot& s = ctx->slots[i];
         TK_CUDA(cudaHostAlloc(&s.h_bytes, ctx->slot_bytes + TK_BYTES_PAD, cudaHostAllocDefault));
         TK_CUDA(cudaHostAlloc(&s.h_recs, sizeof(tk_rec_t) * (nrec + 1), cudaHostAllocDefault));
-        TK_CUDA(cudaHostAlloc(&s.h_result, sizeof(tk_result_t), cudaHostAllocDefault));
-        TK_CUDA(cudaHostAlloc(&s.h_batch_end, sizeof(uint32_t) * nb, cudaHostAllocDefault));
-        TK_CUDA(cudaHostAlloc(&s.h_batch_lmax, sizeof(uint32_t) * nb, cudaHostAllocDefault));
-        TK_CUDA(cudaHostAlloc(&s.h_commit, sizeof(int64_t) * commit_elems, cudaHostAllocDefault));
+        // result block: header | batch_end[nb] | batch_lmax[nb] | commit[P][pitch], one D2H per slot
+        const size_t off_end = sizeof(tk_result_t);
+        const size_t off_lmax = off_end + ((sizeof(uint32_t) * nb + 7) & ~(size_t)7);
+        const size_t off_commit = off_lmax + ((sizeof(uint32_t) * nb + 7) & ~(size_t)7);
+        ctx->block_bytes = off_commit + sizeof(int64_t) * commit_elems;
+        TK_CUDA(cudaHostAlloc(&s.h_block, ctx->block_bytes, cudaHostAllocDefault));
+        s.h_result = reinterpret_cast<tk_result_t*>(s.h_block);
+        s.h_batch_end = reinterpret_cast<uint32_t*>(s.h_block + off_end);
+        s.h_batch_lmax = reinterpret_cast<uint32_t*>(s.h_block + off_lmax);
+        s.h_commit = reinterpret_cast<int64_t*>(s.h_block + off_commit);
         TK_CUDA(cudaMalloc(&s.d.bytes, ctx->slot_bytes + TK_BYTES_PAD));
         TK_CUDA(cudaMemset(s.d.bytes, 0, ctx->slot_bytes + TK_BYTES_PAD));
         TK_CUDA(cudaMalloc(&s.d.recs, sizeof(tk_rec_t) * (nrec + 1)));
@@ -212,10 +214,11 @@ static int create_impl(tk_ctx* ctx) {
         TK_CUDA(cudaMalloc(&s.d.rec_status, sizeof(int32_t) * nrec));
         TK_CUDA(cudaMalloc(&s.d.rec_kidx, sizeof(int32_t) * nrec));
         TK_CUDA(cudaMalloc(&s.d.blk_sum, sizeof(uint32_t) * nblk));
-        TK_CUDA(cudaMalloc(&s.d.result, sizeof(tk_result_t)));
-        TK_CUDA(cudaMalloc(&s.d.batch_end, sizeof(uint32_t) * nb));
-        TK_CUDA(cudaMalloc(&s.d.batch_lmax, sizeof(uint32_t) * nb));
-        TK_CUDA(cudaMalloc(&s.d.commit, sizeof(int64_t) * commit_elems));
+        TK_CUDA(cudaMalloc(&s.d.block, ctx->block_bytes));
+        s.d.result = reinterpret_cast<tk_result_t*>(s.d.block);
+        s.d.batch_end = reinterpret_cast<uint32_t*>(s.d.block + off_end);
+        s.d.batch_lmax = reinterpret_cast<uint32_t*>(s.d.block + off_lmax);
+        s.d.commit = reinterpret_cast<int64_t*>(s.d.block + off_commit);
         TK_CUDA(cudaEventCreateWithFlags(&s.ev_h2d, cudaEventDisableTiming));
         TK_CUDA(cudaEventCreateWithFlags(&s.ev_free, cudaEventDisableTiming));
         TK_CUDA(cudaEventCreateWithFlags(&s.ev_result, cudaEventDisableTiming));
@@ -414,12 +417,7 @@ extern "C" int tk_slot_fetch_result(tk_ctx* ctx, int slot, void* stream) {
     TK_ENTER(ctx, slot);
     tk_slot& s = ctx->slots[slot];
     cudaStream_t st = (cudaStream_t)stream;
-    const size_t nb = ctx->max_batches + 1;
-    TK_CUDA(cudaMemcpyAsync(s.h_result, s.d.result, sizeof(tk_result_t), cudaMemcpyDeviceToHost, st));
-    TK_CUDA(cudaMemcpyAsync(s.h_batch_end, s.d.batch_end, sizeof(uint32_t) * nb, cudaMemcpyDeviceToHost, st));
-    TK_CUDA(cudaMemcpyAsync(s.h_batch_lmax, s.d.batch_lmax, sizeof(uint32_t) * nb, cudaMemcpyDeviceToHost, st));
-    TK_CUDA(cudaMemcpyAsync(s.h_commit, s.d.commit, sizeof(int64_t) * (size_t)ctx->n_partitions * ctx->commit_pitch,
-                            cudaMemcpyDeviceToHost, st));
+    TK_CUDA(cudaMemcpyAsync(s.h_block, s.d.block, ctx->block_bytes, cudaMemcpyDeviceToHost, st));
     TK_CUDA(cudaEventRecord(s.ev_result, st));
     TK_CUDA(cudaEventRecord(s.ev_free, st));
     s.free_recorded = true;

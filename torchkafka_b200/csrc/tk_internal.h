@@ -41,6 +41,7 @@ struct tk_slot_dev {
     int32_t*     rec_status;   // tk_status_t
     int32_t*     rec_kidx;     // index among kept records of this slot, -1 if skipped
     uint32_t*    blk_sum;      // per-block kept counts for the compaction scan
+    uint8_t*     block;        // one allocation: header | batch_end | batch_lmax | commit
     tk_result_t* result;       // header
     uint32_t*    batch_end;    // [max_batches + 1]
     uint32_t*    batch_lmax;   // [max_batches + 1]
@@ -51,7 +52,8 @@ struct tk_slot {
     // host pinned staging
     uint8_t*  h_bytes;
     tk_rec_t* h_recs;
-    // host pinned result block
+    // host pinned result block (one allocation mirroring d.block; the pointers below point into it)
+    uint8_t*     h_block;
     tk_result_t* h_result;
     uint32_t*    h_batch_end;
     uint32_t*    h_batch_lmax;
@@ -73,6 +75,7 @@ struct tk_ctx {
     uint32_t  max_batches;     // batches one slot can close (+1 open)
     uint32_t  commit_pitch;    // max_batches + 1 rounded up to 4
     uint32_t  n_partitions;
+    size_t    block_bytes;     // size of a slot's result block
     uint32_t  batch_size;      // of the last tk_compact
     cudaStream_t copy_stream;
     tk_state* d_state;

@@ -70,7 +70,8 @@ __device__ __forceinline__ void report_error(tk_result_t* res, uint32_t rec, int
 }
 
 // ---------------------------------------------------------------- K1 phase 1
-// Element count per record = commas + 1 for a non-empty array.  (Only valid
+// Element count per record = commas + 1 for a non-empty array (emptiness is read off the head
+// of the record by lane 0).  (Only valid
 // records need a correct count: malformed ones are flagged by the decode kernel
 // and poison their batch.)  keep flag: rec_kidx = 0 (kept) / -1 (skipped).
 __global__ void __launch_bounds__(256) k_json_scan(const uint8_t* __restrict__ bytes,
@@ -84,25 +85,34 @@ __global__ void __launch_bounds__(256) k_json_scan(const uint8_t* __restrict__ b
     const uint32_t nwarps = (gridDim.x * blockDim.x) >> 5;
     for (uint32_t i = warp; i < n; i += nwarps) {
         const uint32_t start = recs[i].start, end = recs[i + 1].start;
-        uint32_t commas = 0, content = 0;
+        uint32_t commas = 0;
         for (uint32_t pos = (start & ~15u) + lane * 16; pos < end; pos += 512) {
             const uint4 v = __ldg(reinterpret_cast<const uint4*>(bytes + pos));
-            const uint32_t valid = range16((int)start - (int)pos, (int)end - (int)pos);
             const uint32_t w[4] = {v.x, v.y, v.z, v.w};
-            uint32_t cm = 0, ct = 0;
+            const bool interior = pos >= start && pos + 16 <= end;
+            uint32_t cm = 0;
 #pragma unroll
             for (int k = 0; k < 4; ++k) {
                 const uint32_t yc = w[k] ^ 0x2C2C2C2Cu;                                  // zero byte: ','
-                const uint32_t notcomma = ((yc & 0x7F7F7F7Fu) + 0x7F7F7F7Fu) | yc;
-                cm |= hibits_to_nibble(~notcomma & 0x80808080u) << (4 * k);
-                // any token character means the array is not empty
-                ct |= hibits_to_nibble(tokclass4(w[k])) << (4 * k);
+                const uint32_t iscomma = ~(((yc & 0x7F7F7F7Fu) + 0x7F7F7F7Fu) | yc) & 0x80808080u;
+                if (interior) commas += __popc(iscomma);
+                else cm |= hibits_to_nibble(iscomma) << (4 * k);
             }
-            commas += __popc(cm & valid);
-            content |= ct & valid;
+            if (!interior) commas += __popc(cm & range16((int)start - (int)pos, (int)end - (int)pos));
         }
         commas = __reduce_add_sync(0xffffffffu, commas);
-        content = __reduce_or_sync(0xffffffffu, content);
+        // empty array?  lane 0 looks at the head of the record: [BOM] ws* '[' ws* ']'
+        uint32_t content = 1;
+        if (lane == 0) {
+            uint32_t p = start;
+            if (p + 2 < end && bytes[p] == 0xEF && bytes[p + 1] == 0xBB && bytes[p + 2] == 0xBF) p += 3;
+            while (p < end && tk_is_ws(bytes[p])) ++p;
+            if (p < end && bytes[p] == '[') {
+                ++p;
+                while (p < end && tk_is_ws(bytes[p])) ++p;
+                if (p < end && bytes[p] == ']') content = 0;
+            }
+        }
         if (lane == 0) {
             const uint32_t len = content ? commas + 1 : 0;
             rec_len[i] = (int32_t)len;

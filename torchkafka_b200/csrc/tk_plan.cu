@@ -103,12 +103,17 @@ __global__ void __launch_bounds__(1024) k_compact_scan(uint32_t* __restrict__ bl
 // pass 3: final index of every record.
 //   kept record    -> rec_kidx = k            (k = kept records before it in this slot)
 //   skipped record -> rec_kidx = -1 - k
+// and per batch: the longest kept record (one atomic per warp when the warp lies inside one
+// batch, which is the common case) and the index of the record that closed it.
 __global__ void __launch_bounds__(CMP_THREADS) k_compact_apply(int32_t* __restrict__ rec_kidx,
                                                                  const int32_t* __restrict__ rec_len,
                                                                  uint32_t n, const uint32_t* __restrict__ blk_sum,
                                                                  const tk_result_t* __restrict__ res,
                                                                  uint32_t* __restrict__ batch_end,
-                                                                 uint32_t* __restrict__ batch_lmax) {
+                                                                 uint32_t* __restrict__ batch_lmax,
+                                                                 const tk_rec_t* __restrict__ recs,
+                                                                 int64_t* __restrict__ commit, uint32_t pitch,
+                                                                 uint32_t n_partitions) {
     __shared__ uint32_t tot;
     const uint32_t base = blockIdx.x * CMP_TILE + threadIdx.x * CMP_ITEMS;
     int keep[CMP_ITEMS];
@@ -123,20 +128,45 @@ __global__ void __launch_bounds__(CMP_THREADS) k_compact_apply(int32_t* __restri
     const uint32_t carry = res->carry_in, B = res->batch_size;
 #pragma unroll
     for (int k = 0; k < CMP_ITEMS; ++k) {
-        uint32_t i = base + k;
-        if (i >= n) break;
-        if (keep[k]) {
-            rec_kidx[i] = (int32_t)ex;
-            const uint32_t q = carry + ex;
-            const uint32_t j = q / B;
-            // most records are shorter than the running maximum: read before the atomic
-            const uint32_t len = (uint32_t)rec_len[i];
-            if (len > *(volatile uint32_t*)&batch_lmax[j]) atomicMax(&batch_lmax[j], len);
-            if ((q + 1) % B == 0) batch_end[j] = i;
-            ++ex;
-        } else {
-            rec_kidx[i] = -1 - (int32_t)ex;
+        const uint32_t i = base + k;
+        const bool live = i < n;
+        const uint32_t j = (carry + ex) / B;               // batch of this record (kept or skipped)
+        uint32_t len = 0;
+        if (live) {
+            if (keep[k]) {
+                rec_kidx[i] = (int32_t)ex;
+                len = (uint32_t)rec_len[i];
+                if ((carry + ex + 1) % B == 0) batch_end[j] = i;
+            } else {
+                rec_kidx[i] = -1 - (int32_t)ex;
+            }
         }
+        // longest kept record of the batch
+        const uint32_t j0 = __shfl_sync(0xffffffffu, j, 0);
+        if (__all_sync(0xffffffffu, j == j0)) {
+            const uint32_t m = __reduce_max_sync(0xffffffffu, len);
+            if ((threadIdx.x & 31) == 0 && m > *(volatile uint32_t*)&batch_lmax[j0]) atomicMax(&batch_lmax[j0], m);
+        } else if (len > *(volatile uint32_t*)&batch_lmax[j]) {
+            atomicMax(&batch_lmax[j], len);
+        }
+        // K4, first half: segmented max of (offset + 1) per (batch, partition).  Lanes of the warp
+        // that share a key elect one lane that issues the group's only atomic.
+        uint32_t key = 0xFFFFFFFFu, p = 0;
+        long long val = 0;
+        if (live) {
+            const uint4 raw = __ldg(reinterpret_cast<const uint4*>(recs) + i);
+            p = raw.y;
+            val = (long long)(((uint64_t)raw.w << 32) | raw.z) + 1;
+            if (p < n_partitions) key = j * n_partitions + p;
+        }
+        const unsigned peers = __match_any_sync(0xffffffffu, key);
+        const uint32_t vhi = (uint32_t)((unsigned long long)val >> 32), vlo = (uint32_t)val;
+        const uint32_t mh = __reduce_max_sync(peers, vhi);
+        const uint32_t ml = __reduce_max_sync(peers, vhi == mh ? vlo : 0u);
+        if (key != 0xFFFFFFFFu && (int)(threadIdx.x & 31) == __ffs(peers) - 1)
+            atomicMax(reinterpret_cast<long long*>(&commit[(size_t)p * pitch + j]),
+                      (long long)(((unsigned long long)mh << 32) | ml));
+        if (live && keep[k]) ++ex;
     }
 }
 
@@ -151,6 +181,8 @@ extern "C" int tk_compact(tk_ctx* ctx, int slot, uint32_t batch_size, void* stre
                "slot with %u records can close more than max_batches=%u batches of %u", n, ctx->max_batches, batch_size);
     ctx->batch_size = batch_size;
     const uint32_t nblk = (n + CMP_TILE - 1) / CMP_TILE;
+    // commit matrix starts at -1 ("partition not seen"); filled by the apply pass below
+    TK_CUDA(cudaMemsetAsync(s.d.commit, 0xFF, sizeof(int64_t) * (size_t)ctx->n_partitions * ctx->commit_pitch, st));
     if (nblk) {
         k_compact_count<<<nblk, CMP_THREADS, 0, st>>>(s.d.rec_kidx, n, s.d.blk_sum);
         TK_LAUNCH_CHECK();
@@ -160,47 +192,16 @@ extern "C" int tk_compact(tk_ctx* ctx, int slot, uint32_t batch_size, void* stre
     TK_LAUNCH_CHECK();
     if (nblk) {
         k_compact_apply<<<nblk, CMP_THREADS, 0, st>>>(s.d.rec_kidx, s.d.rec_len, n, s.d.blk_sum, s.d.result,
-                                                     s.d.batch_end, s.d.batch_lmax);
+                                                     s.d.batch_end, s.d.batch_lmax, s.d.recs, s.d.commit,
+                                                     ctx->commit_pitch, ctx->n_partitions);
         TK_LAUNCH_CHECK();
     }
     return 0;
 }
 
 // ------------------------------------------------------------------------ K4
-// Segmented max: one thread per record; lanes of a warp that share (batch,
-// partition) elect the lane with the largest offset, which issues the only
-// atomic of the group.
-__global__ void __launch_bounds__(256) k_commit_reduce(const tk_rec_t* __restrict__ recs,
-                                                        const int32_t* __restrict__ rec_kidx, uint32_t n,
-                                                        const tk_result_t* __restrict__ res,
-                                                        int64_t* __restrict__ commit, uint32_t pitch,
-                                                        uint32_t n_partitions) {
-    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
-    const bool live = i < n;
-    uint32_t key = 0xFFFFFFFFu;
-    long long val = 0;
-    uint32_t p = 0, j = 0;
-    if (live) {
-        const uint4 raw = __ldg(reinterpret_cast<const uint4*>(recs) + i);
-        p = raw.y;
-        val = (long long)(((uint64_t)raw.w << 32) | raw.z) + 1;
-        const int32_t kx = rec_kidx[i];
-        const uint32_t kexcl = kx >= 0 ? (uint32_t)kx : (uint32_t)(-1 - kx);
-        j = (res->carry_in + kexcl) / res->batch_size;
-        if (p < n_partitions) key = j * n_partitions + p;
-    }
-    // every lane of the warp reaches this point (no early return above)
-    const unsigned peers = __match_any_sync(0xffffffffu, key);
-    // 64-bit max inside each peer group from two 32-bit warp reductions (values are >= 0)
-    const uint32_t hi = (uint32_t)((unsigned long long)val >> 32), lo = (uint32_t)val;
-    const uint32_t mh = __reduce_max_sync(peers, hi);
-    const uint32_t ml = __reduce_max_sync(peers, hi == mh ? lo : 0u);
-    const long long best = (long long)(((unsigned long long)mh << 32) | ml);
-    const int leader = __ffs(peers) - 1;
-    if (key != 0xFFFFFFFFu && (int)(threadIdx.x & 31) == leader)
-        atomicMax(reinterpret_cast<long long*>(&commit[(size_t)p * pitch + j]), best);
-}
-
+// First half (segmented max per (batch, partition)) runs inside k_compact_apply, where the
+// batch index of every record is at hand.  Second half:
 // Running max along the batch axis, one block per partition.
 __global__ void __launch_bounds__(128) k_commit_scan(int64_t* __restrict__ commit, uint32_t pitch,
                                                       const tk_result_t* __restrict__ res,
@@ -236,13 +237,6 @@ extern "C" int tk_commit_offsets(tk_ctx* ctx, int slot, void* stream) {
     TK_ENTER(ctx, slot);
     tk_slot& s = ctx->slots[slot];
     cudaStream_t st = (cudaStream_t)stream;
-    const uint32_t n = s.n_records;
-    TK_CUDA(cudaMemsetAsync(s.d.commit, 0xFF, sizeof(int64_t) * (size_t)ctx->n_partitions * ctx->commit_pitch, st));
-    if (n) {
-        k_commit_reduce<<<(n + 255) / 256, 256, 0, st>>>(s.d.recs, s.d.rec_kidx, n, s.d.result, s.d.commit,
-                                                        ctx->commit_pitch, ctx->n_partitions);
-        TK_LAUNCH_CHECK();
-    }
     k_commit_scan<<<ctx->n_partitions, 128, 0, st>>>(s.d.commit, ctx->commit_pitch, s.d.result, ctx->d_positions);
     TK_LAUNCH_CHECK();
     return 0;

@@ -31,10 +31,10 @@ REC_DTYPE = np.dtype([("start", "<u4"), ("partition", "<i4"), ("offset", "<i8")]
 
 #: a slot never closes more batches than this (bounds the commit matrix)
 MAX_BATCHES_CAP = 16384
-#: kernels launched per slot by ``process`` (carry, scan, 3x compact, 2x commit, decode; the
+#: kernels launched per slot by ``process`` (carry, scan, 3x compact, commit scan, decode; the
 #: commit-matrix memset is not counted), for bench accounting
-LAUNCHES_PER_SLOT_JSON = 8
-LAUNCHES_PER_SLOT_RAW = 8
+LAUNCHES_PER_SLOT_JSON = 7
+LAUNCHES_PER_SLOT_RAW = 7
 
 
 def _np_view(ptr: int, nbytes: int, dtype) -> np.ndarray:

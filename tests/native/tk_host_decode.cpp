@@ -44,6 +44,47 @@ static int decode(const uint8_t* buf, uint32_t len, int max_len, void* out, int*
     return TK_OK;
 }
 
+// Mirror of the flat (comma-split) decode path: prefix check, then one segment per comma.
+template <int KIND>
+static int decode_flat(const uint8_t* buf, uint32_t len, int max_len, void* out, int* n_out) {
+    typedef typename tk_elem<KIND>::type T;
+    HostReader rd{buf, len};
+    uint32_t first = 0;
+    bool empty = false;
+    *n_out = 0;
+    int st = tk_json_prefix(rd, 0, &first, &empty);
+    if (st) return st;
+    if (empty) return TK_OK;
+    int n = 0, worst = TK_OK;
+    uint32_t seg = first;
+    for (;;) {
+        T v;
+        st = tk_json_element_flat<KIND>(rd, seg, &v);
+        if (st && !worst) worst = st;
+        if (n < max_len) ((T*)out)[n] = st ? (T)0 : v;
+        ++n;
+        uint32_t p = seg;
+        while (p < len && buf[p] != ',') ++p;      // next split point
+        if (p >= len) break;
+        seg = p + 1;
+    }
+    *n_out = n;
+    if (worst) return worst;
+    if (n > max_len) return TK_ERR_TOO_LONG;
+    return TK_OK;
+}
+
+extern "C" int tk_host_decode_flat(const uint8_t* buf, uint32_t len, int kind, int max_len,
+                                   void* out, int* n_out) {
+    switch (kind) {
+        case TK_F32: return decode_flat<TK_F32>(buf, len, max_len, out, n_out);
+        case TK_F64: return decode_flat<TK_F64>(buf, len, max_len, out, n_out);
+        case TK_I32: return decode_flat<TK_I32>(buf, len, max_len, out, n_out);
+        case TK_I64: return decode_flat<TK_I64>(buf, len, max_len, out, n_out);
+    }
+    return -1;
+}
+
 extern "C" int tk_host_decode(const uint8_t* buf, uint32_t len, int kind, int max_len,
                               void* out, int* n_out) {
     switch (kind) {

@@ -101,16 +101,27 @@ def test_decimal_to_double_matches_cpython_zero_ulp(lib):
     assert not bad, bad[:5]
 
 
+FLAT = False     # which decomposition of the record grammar the helper below exercises
+
+
 def decode(lib, payload: bytes, kind: int, max_len: int = 64):
     dt = [np.float32, np.float64, np.int32, np.int64][kind]
     out = np.zeros(max_len, dt)
     n = ctypes.c_int(0)
-    st = lib.tk_host_decode(payload, len(payload), kind, max_len, out.ctypes.data_as(ctypes.c_void_p),
-                            ctypes.byref(n))
+    fn = lib.tk_host_decode_flat if FLAT else lib.tk_host_decode
+    st = fn(payload, len(payload), kind, max_len, out.ctypes.data_as(ctypes.c_void_p), ctypes.byref(n))
     return st, out[:min(n.value, max_len)], n.value
 
 
-def test_record_grammar_and_conversions_match_reference_known_answers(lib):
+@pytest.fixture(params=["runs", "comma-split"])
+def decomposition(request):
+    global FLAT
+    FLAT = request.param == "comma-split"
+    yield request.param
+    FLAT = False
+
+
+def test_record_grammar_and_conversions_match_reference_known_answers(lib, decomposition):
     with open(os.path.join(GOLD, "known_answers.json")) as f:
         stored = json.load(f)["answers"]
     for a in stored:
@@ -134,7 +145,7 @@ def test_record_grammar_and_conversions_match_reference_known_answers(lib):
                 assert [int(x) for x in vals] == want["values"], (a["payload"], dt)
 
 
-def test_random_records_match_json_loads(lib):
+def test_random_records_match_json_loads(lib, decomposition):
     rng = random.Random(99)
     for _ in range(3000):
         toks = [gen_decimal(rng) if rng.random() < 0.7 else str(rng.randint(-10**6, 10**6))

@@ -80,6 +80,8 @@ _SIGNATURES = {
     "tk_carry_rows": (C.c_int, [C.c_void_p, C.c_int, C.c_int, _p(TkPlane), _p(TkPlane), C.c_void_p]),
     "tk_json_decode": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_uint32, C.c_uint32, _p(TkPlane),
                                  _p(TkPlane), _p(TkPlane), C.c_void_p]),
+    "tk_json_decode_warp": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_uint32, C.c_uint32, _p(TkPlane),
+                                      _p(TkPlane), _p(TkPlane), C.c_void_p]),
     "tk_collate_raw": (C.c_int, [C.c_void_p, C.c_int, C.c_uint64, _p(TkPlane), C.c_void_p]),
     "tk_image_set_norm": (C.c_int, [C.c_void_p, C.c_int, _p(C.c_float), _p(C.c_float), C.c_void_p]),
     "tk_collate_image_u8_bf16_nchw": (C.c_int, [C.c_void_p, C.c_int, C.c_uint32, C.c_uint32, C.c_uint32,

@@ -158,6 +158,7 @@ static void free_slot(tk_slot& s) {
     if (s.h_block) cudaFreeHost(s.h_block);
     cudaFree(s.d.bytes); cudaFree(s.d.recs); cudaFree(s.d.rec_len); cudaFree(s.d.rec_status);
     cudaFree(s.d.rec_kidx); cudaFree(s.d.blk_sum); cudaFree(s.d.block);
+    cudaFree(s.d.rec_tok); cudaFree(s.d.tok_pos); cudaFree(s.d.tok_dst); cudaFree(s.d.tok_rec);
     if (s.ev_h2d) cudaEventDestroy(s.ev_h2d);
     if (s.ev_free) cudaEventDestroy(s.ev_free);
     if (s.ev_result) cudaEventDestroy(s.ev_result);
@@ -213,7 +214,9 @@ static int create_impl(tk_ctx* ctx) {
         TK_CUDA(cudaMalloc(&s.d.rec_len, sizeof(int32_t) * nrec));
         TK_CUDA(cudaMalloc(&s.d.rec_status, sizeof(int32_t) * nrec));
         TK_CUDA(cudaMalloc(&s.d.rec_kidx, sizeof(int32_t) * nrec));
-        TK_CUDA(cudaMalloc(&s.d.blk_sum, sizeof(uint32_t) * nblk));
+        TK_CUDA(cudaMalloc(&s.d.blk_sum, sizeof(unsigned long long) * nblk));
+        TK_CUDA(cudaMalloc(&s.d.rec_tok, sizeof(uint32_t) * (nrec + 1)));
+        // token arrays of the JSON path are allocated on first use (tk_ensure_token_arrays)
         TK_CUDA(cudaMalloc(&s.d.block, ctx->block_bytes));
         s.d.result = reinterpret_cast<tk_result_t*>(s.d.block);
         s.d.batch_end = reinterpret_cast<uint32_t*>(s.d.block + off_end);
@@ -247,6 +250,22 @@ extern "C" int tk_ctx_create(int device, uint64_t slot_bytes, uint32_t slot_reco
     int rc = create_impl(ctx);
     if (rc) { char keep[1024]; strncpy(keep, g_err, sizeof(keep)); keep[1023] = 0; tk_ctx_destroy(ctx); tk_set_error("%s", keep); return rc; }
     *out = ctx;
+    return 0;
+}
+
+// The flat JSON decode keeps one (position, destination, record) triple per element of the slot.
+// An element needs at least two bytes ("1,"), so slot_bytes / 2 + slot_records entries always
+// suffice.  Raw / image contexts never pay for it.
+int tk_ensure_token_arrays(tk_ctx* ctx) {
+    if (ctx->tok_cap) return 0;
+    const size_t cap = (size_t)(ctx->slot_bytes / 2) + ctx->slot_records + 64;
+    for (int i = 0; i < ctx->n_slots; ++i) {
+        tk_slot& s = ctx->slots[i];
+        TK_CUDA(cudaMalloc(&s.d.tok_pos, sizeof(uint32_t) * cap));
+        TK_CUDA(cudaMalloc(&s.d.tok_dst, sizeof(uint32_t) * cap));
+        TK_CUDA(cudaMalloc(&s.d.tok_rec, sizeof(uint32_t) * cap));
+    }
+    ctx->tok_cap = cap;
     return 0;
 }
 

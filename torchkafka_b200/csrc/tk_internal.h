@@ -40,7 +40,11 @@ struct tk_slot_dev {
     int32_t*     rec_len;      // element count (JSON) / byte count (raw)
     int32_t*     rec_status;   // tk_status_t
     int32_t*     rec_kidx;     // index among kept records of this slot, -1 if skipped
-    uint32_t*    blk_sum;      // per-block kept counts for the compaction scan
+    unsigned long long* blk_sum;   // per-tile (kept << 40 | elements) for the compaction scan
+    uint32_t*    rec_tok;      // [slot_records + 1] index of each record's first element in the token array
+    uint32_t*    tok_pos;      // [tok_cap] token array of the flat decode path: byte position,
+    uint32_t*    tok_dst;      //           destination element index (0xFFFFFFFF: validate only),
+    uint32_t*    tok_rec;      //           record index
     uint8_t*     block;        // one allocation: header | batch_end | batch_lmax | commit
     tk_result_t* result;       // header
     uint32_t*    batch_end;    // [max_batches + 1]
@@ -76,6 +80,7 @@ struct tk_ctx {
     uint32_t  commit_pitch;    // max_batches + 1 rounded up to 4
     uint32_t  n_partitions;
     size_t    block_bytes;     // size of a slot's result block
+    size_t    tok_cap;         // entries of the token array (a token needs >= 2 bytes)
     uint32_t  batch_size;      // of the last tk_compact
     cudaStream_t copy_stream;
     tk_state* d_state;
@@ -99,6 +104,8 @@ static inline int tk_check_slot(tk_ctx* ctx, int slot) {
     } while (0)
 
 #define TK_LAUNCH_CHECK() TK_CUDA(cudaGetLastError())
+
+int tk_ensure_token_arrays(tk_ctx* ctx);
 
 // bytes the kernels may over-read past n_bytes (aligned vector loads of the last tile)
 #define TK_BYTES_PAD 4096

@@ -63,6 +63,24 @@ TK_HD int tk_json_gap(const R& rd, uint32_t pos) {
     return TK_ERR_SYNTAX;                              // "Expecting ',' delimiter"
 }
 
+// Separator check of the comma-split decomposition (flat decode path): the record is cut at
+// every ',' ; segment j must read  ws* number ws*  and end at the next ',' -- or, for the last
+// segment, at ']' ws* END.  Together with the prefix check this tiles the record as well: the
+// only bytes not looked at by a number scan or one of the two checks are the commas themselves.
+template <class R>
+TK_HD int tk_json_gap_flat(const R& rd, uint32_t pos) {
+    while (tk_is_ws(rd(pos))) ++pos;
+    int c = rd(pos);
+    if (c == ',') return TK_OK;
+    if (c == ']') {
+        ++pos;
+        while (tk_is_ws(rd(pos))) ++pos;
+        return rd(pos) == -1 ? TK_OK : TK_ERR_SYNTAX;
+    }
+    if (c == '[' || c == '{' || c == '"') return TK_ERR_UNSUPPORTED;
+    return TK_ERR_SYNTAX;
+}
+
 // element kinds (tk_dtype_t in include/torchkafka_b200.h)
 enum { TK_F32 = 0, TK_F64 = 1, TK_I32 = 2, TK_I64 = 3 };
 
@@ -94,4 +112,27 @@ TK_HD int tk_json_element(const R& rd, uint32_t pos, typename tk_elem<KIND>::typ
         *out = (typename tk_elem<KIND>::type)v;
         return TK_OK;
     }
+}
+
+// Segment of the comma-split decomposition starting right after a ',' (or after '['):
+// ws* number, then tk_json_gap_flat.
+template <int KIND, class R>
+TK_HD int tk_json_element_flat(const R& rd, uint32_t pos, typename tk_elem<KIND>::type* out) {
+    while (tk_is_ws(rd(pos))) ++pos;
+    tk_token t = tk_scan_number(rd, pos);
+    if (t.err) return t.err;
+    int st = tk_json_gap_flat(rd, t.end);
+    if (st) return st;
+    if (KIND == TK_F32 || KIND == TK_F64) {
+        double d;
+        st = tk_token_to_f64(rd, t, &d);
+        if (st) return st;
+        *out = (typename tk_elem<KIND>::type)d;
+    } else {
+        int64_t v;
+        st = tk_token_to_i64(rd, t, KIND == TK_I32 ? 32 : 64, &v);
+        if (st) return st;
+        *out = (typename tk_elem<KIND>::type)v;
+    }
+    return TK_OK;
 }

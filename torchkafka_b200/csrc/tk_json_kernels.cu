@@ -511,9 +511,246 @@ __global__ void __launch_bounds__(JD_WARPS * 32, 8) k_json_decode(const decode_a
     }
 }
 
-extern "C" int tk_json_decode(tk_ctx* ctx, int slot, int dtype, uint32_t max_len, uint32_t fixed_len,
-                              const tk_plane_t* values, const tk_plane_t* lengths, const tk_plane_t* mask,
-                              void* stream) {
+// ================================================================ flat decode path
+// Two kernels instead of one warp-per-record kernel:
+//   k_json_tokenise  (warp per record) cuts every record at its commas and writes one
+//                    (byte position, destination element, record) triple per element into a
+//                    slot-wide token array -- the record's first slot in that array comes from
+//                    the compaction scan (rec_tok) -- and writes pad, length and mask of the row;
+//   k_json_parse<T>  (thread per element) parses one token each: perfectly balanced, every
+//                    lane busy whatever the record lengths are, no shared memory, so occupancy
+//                    is limited by registers only.
+// The grammar is checked with the comma-split decomposition (tk_json_gap_flat in tk_json.cuh).
+struct GlobalReader {
+    const uint8_t* bytes;
+    uint32_t end;
+    __device__ __forceinline__ int operator()(uint32_t pos) const { return pos < end ? (int)bytes[pos] : -1; }
+};
+
+struct flat_args {
+    const uint8_t*  bytes;
+    const tk_rec_t* recs;
+    uint32_t        n;
+    uint32_t        max_len;
+    uint32_t        fixed_len;
+    const int32_t*  rec_kidx;
+    const int32_t*  rec_len;
+    int32_t*        rec_status;
+    const uint32_t* rec_tok;
+    tk_result_t*    res;
+    uint32_t*       tok_pos;
+    uint32_t*       tok_dst;
+    uint32_t*       tok_rec;
+    uint32_t        tok_cap;
+    tk_plane_t      values, lengths, mask;
+};
+
+__device__ __forceinline__ void flag_record(int32_t* rec_status, tk_result_t* res, uint32_t rec, int code) {
+    if (atomicCAS(&rec_status[rec], 0, code) == 0) report_error(res, rec, code);   // count a record once
+}
+
+template <int ELEM_BYTES>
+__global__ void __launch_bounds__(256) k_json_tokenise(const flat_args a) {
+    const uint32_t lane = threadIdx.x & 31;
+    const uint32_t warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const uint32_t nwarps = (gridDim.x * blockDim.x) >> 5;
+    const uint32_t B = a.res->batch_size;
+    for (uint32_t i = warp; i < a.n; i += nwarps) {
+        const uint32_t start = a.recs[i].start, end = a.recs[i + 1].start;
+        const int32_t kidx = a.rec_kidx[i];
+        const uint32_t len = (uint32_t)a.rec_len[i];          // commas + 1, or 0 for "[]" (k_json_scan)
+        const uint32_t t0 = a.rec_tok[i];
+        const bool kept = kidx >= 0;
+        const uint64_t row = (uint64_t)B + (uint32_t)(kept ? kidx : 0);
+        const uint64_t dst_base = row * a.max_len;            // element index of the row's first element
+        const bool addressable = kept && dst_base + a.max_len < 0xFFFFFFFFull;
+
+        // head of the record: [BOM] ws* '[' ws* <first token> | ']' ws* END
+        uint32_t first = start;
+        int head = TK_OK;
+        if (lane == 0) {
+            GlobalReader rd{a.bytes, end};
+            bool empty = false;
+            head = end > start ? tk_json_prefix(rd, start, &first, &empty) : TK_ERR_SYNTAX;
+            if (!head && kept && !addressable) head = TK_ERR_TOO_LONG;
+            if (!head && kept && a.fixed_len && len != a.fixed_len) head = TK_ERR_RAGGED;
+            const int pre = a.rec_status[i];                  // TK_ERR_TOO_LONG from the scan
+            if (pre) report_error(a.res, i, pre);
+            else if (head) flag_record(a.rec_status, a.res, i, head);
+            if (len && t0 < a.tok_cap) {
+                a.tok_pos[t0] = first;
+                a.tok_dst[t0] = (addressable && a.max_len) ? (uint32_t)dst_base : 0xFFFFFFFFu;
+                a.tok_rec[t0] = i;
+            }
+        }
+        // one token after every comma
+        uint32_t seen = 0;                                    // commas before the current 512-byte step
+        if (len > 1) {
+            for (uint32_t base = start & ~15u; base < end; base += 512) {
+                const uint32_t pos = base + lane * 16;
+                uint32_t cm = 0;
+                if (pos < end) {
+                    const uint4 v = __ldg(reinterpret_cast<const uint4*>(a.bytes + pos));
+                    const uint32_t w[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+                    for (int k = 0; k < 4; ++k) {
+                        const uint32_t yc = w[k] ^ 0x2C2C2C2Cu;
+                        const uint32_t iscomma = ~(((yc & 0x7F7F7F7Fu) + 0x7F7F7F7Fu) | yc) & 0x80808080u;
+                        cm |= hibits_to_nibble(iscomma) << (4 * k);
+                    }
+                    cm &= range16((int)start - (int)pos, (int)end - (int)pos);
+                }
+                const uint32_t cnt = __popc(cm);
+                uint32_t incl = cnt;
+#pragma unroll
+                for (int d = 1; d < 32; d <<= 1) {
+                    const uint32_t o = __shfl_up_sync(0xffffffffu, incl, d);
+                    if (lane >= (uint32_t)d) incl += o;
+                }
+                uint32_t e = 1 + seen + incl - cnt;           // element index of this lane's first comma
+                while (cm) {
+                    const int b = __ffs(cm) - 1;
+                    cm &= cm - 1;
+                    const uint32_t t = t0 + e;
+                    if (e < len && t < a.tok_cap) {
+                        a.tok_pos[t] = pos + b + 1;
+                        a.tok_dst[t] = (addressable && e < a.max_len) ? (uint32_t)(dst_base + e) : 0xFFFFFFFFu;
+                        a.tok_rec[t] = i;
+                    }
+                    ++e;
+                }
+                seen += __shfl_sync(0xffffffffu, incl, 31);
+            }
+        }
+        // K3: pad, length, mask of the row (the elements themselves are written by k_json_parse)
+        if (addressable) {
+            const uint32_t fill_from = min(len, a.max_len);
+            uint8_t* vrow = (uint8_t*)a.values.base + row * a.values.row_bytes;
+            if (ELEM_BYTES == 4) {
+                uint32_t* p = reinterpret_cast<uint32_t*>(vrow);
+                for (uint32_t e = fill_from + lane; e < a.max_len; e += 32) p[e] = 0u;
+            } else {
+                unsigned long long* p = reinterpret_cast<unsigned long long*>(vrow);
+                for (uint32_t e = fill_from + lane; e < a.max_len; e += 32) p[e] = 0ull;
+            }
+            if (a.lengths.base && lane == 0)
+                *reinterpret_cast<int32_t*>((uint8_t*)a.lengths.base + row * a.lengths.row_bytes) = (int32_t)len;
+            if (a.mask.base) {
+                uint8_t* m = (uint8_t*)a.mask.base + row * a.mask.row_bytes;
+                if ((a.max_len & 3u) == 0 && ((uintptr_t)m & 3u) == 0) {
+                    uint32_t* m32 = reinterpret_cast<uint32_t*>(m);
+                    for (uint32_t w = lane; w < a.max_len / 4; w += 32) {
+                        const int left = (int)len - (int)(w * 4);
+                        m32[w] = left >= 4 ? 0x01010101u : (left <= 0 ? 0u : (0x01010101u >> (8 * (4 - left))));
+                    }
+                } else {
+                    for (uint32_t e = lane; e < a.max_len; e += 32) m[e] = e < len ? 1 : 0;
+                }
+            }
+        }
+    }
+}
+
+// unaligned 8-byte window out of global memory (L1-resident: neighbouring threads read
+// neighbouring tokens)
+__device__ __forceinline__ Window8 global_load8(const uint8_t* bytes, uint32_t pos) {
+    const uint32_t* w32 = reinterpret_cast<const uint32_t*>(bytes) + (pos >> 2);
+    const uint32_t w0 = __ldg(w32), w1 = __ldg(w32 + 1), w2 = __ldg(w32 + 2);
+    const uint32_t sh = (pos & 3u) * 8u;
+    Window8 w;
+    w.lo = __funnelshift_r(w0, w1, sh);
+    w.hi = __funnelshift_r(w1, w2, sh);
+    return w;
+}
+
+// fast_token24 for the flat path: bytes come from global memory, one leading space is skipped,
+// and the separator that ends the segment must simply be ','.
+__device__ __forceinline__ bool flat_token24(const uint8_t* bytes, uint32_t pos, uint32_t end, tk_token* out) {
+    if (pos >= end) return false;
+    if (bytes[pos] == ' ') ++pos;
+    if (pos >= end) return false;
+    const uint32_t avail = end - pos;
+    const uint32_t* w32 = reinterpret_cast<const uint32_t*>(bytes) + (pos >> 2);
+    const uint32_t sh = (pos & 3u) * 8u;
+    uint32_t a[7];
+#pragma unroll
+    for (int k = 0; k < 7; ++k) a[k] = __ldg(w32 + k);
+    uint32_t W[6];
+#pragma unroll
+    for (int k = 0; k < 6; ++k) W[k] = __funnelshift_r(a[k], a[k + 1], sh);
+    uint32_t nd = 0xFF000000u;
+#pragma unroll
+    for (int k = 0; k < 6; ++k) {
+        const uint32_t u = W[k] ^ 0x30303030u;
+        const uint32_t t = (((u & 0x7F7F7F7Fu) + 0x76767676u) | u) & 0x80808080u;
+        nd |= hibits_to_nibble(t) << (4 * k);
+    }
+    if (avail < 24) nd |= 0xFFFFFFFFu << avail;
+    const uint32_t neg = (W[0] & 0xFFu) == '-' ? 1u : 0u;
+    const uint32_t p = neg;
+    const uint32_t L1 = __ffs(nd >> p) - 1;
+    if (L1 == 0 || L1 > 8) return false;
+    const Window8 wi = {__funnelshift_r(W[0], W[1], 8 * p), __funnelshift_r(W[1], W[2], 8 * p)};
+    if (L1 > 1 && (wi.lo & 0xFFu) == '0') return false;
+    const uint32_t tpos = p + L1;
+    const uint32_t tword = tpos < 4 ? W[0] : (tpos < 8 ? W[1] : W[2]);
+    const uint32_t tc = (tword >> (8 * (tpos & 3u))) & 0xFFu;
+    uint32_t L2 = 0, endp = tpos;
+    uint64_t w = parse_upto8(wi, L1);
+    if (tc == '.') {
+        const uint32_t q0 = tpos + 1;
+        L2 = __ffs(nd >> q0) - 1;
+        if (L2 == 0 || L2 > 16 || L1 + L2 > 19) return false;
+        endp = q0 + L2;
+        if (endp > 23) return false;
+        const uint32_t m0 = L2 < 8 ? L2 : 8, m1 = L2 - m0;
+        w = w * c_pow10[m0] + parse_upto8(global_load8(bytes, pos + q0), m0);
+        if (m1) w = w * c_pow10[m1] + parse_upto8(global_load8(bytes, pos + q0 + 8), m1);
+    }
+    if (endp >= avail) return false;
+    if (bytes[pos + endp] != ',') return false;             // ']' / ws / exponent: general path
+    tk_token t;
+    t.w = w; t.q = -(int32_t)L2; t.end = pos + endp; t.dig_begin = pos + p; t.exp10 = 0;
+    t.neg = (uint8_t)neg; t.is_int = L2 == 0; t.truncated = 0; t.special = 0; t.err = TK_OK;
+    t.nsig = (int32_t)(L1 + L2); t.frac_digits = (int32_t)L2;
+    *out = t;
+    return true;
+}
+
+template <int KIND>
+__global__ void __launch_bounds__(256) k_json_parse(const flat_args a) {
+    typedef typename tk_elem<KIND>::type T;
+    const uint32_t n_tok = min(a.res->reserved[0], a.tok_cap);
+    T* values = reinterpret_cast<T*>(a.values.base);
+    for (uint32_t t = blockIdx.x * blockDim.x + threadIdx.x; t < n_tok; t += gridDim.x * blockDim.x) {
+        const uint32_t pos = a.tok_pos[t], dst = a.tok_dst[t], rec = a.tok_rec[t];
+        const uint32_t end = a.recs[rec + 1].start;
+        GlobalReader rd{a.bytes, end};
+        T v;
+        int st;
+        tk_token tok;
+        if (flat_token24(a.bytes, pos, end, &tok)) {
+            if (KIND == TK_F32 || KIND == TK_F64) {
+                double d;
+                st = tk_token_to_f64(rd, tok, &d);
+                v = (T)d;
+            } else {
+                int64_t x = 0;
+                st = tk_token_to_i64(rd, tok, KIND == TK_I32 ? 32 : 64, &x);
+                v = (T)x;
+            }
+        } else {
+            st = tk_json_element_flat<KIND>(rd, pos, &v);
+        }
+        if (st) flag_record(a.rec_status, a.res, rec, st);
+        else if (dst != 0xFFFFFFFFu) values[dst] = v;
+    }
+}
+
+
+extern "C" int tk_json_decode_warp(tk_ctx* ctx, int slot, int dtype, uint32_t max_len, uint32_t fixed_len,
+                                   const tk_plane_t* values, const tk_plane_t* lengths, const tk_plane_t* mask,
+                                   void* stream) {
     TK_ENTER(ctx, slot);
     tk_slot& s = ctx->slots[slot];
     cudaStream_t st = (cudaStream_t)stream;
@@ -538,5 +775,46 @@ extern "C" int tk_json_decode(tk_ctx* ctx, int slot, int dtype, uint32_t max_len
         }
         TK_LAUNCH_CHECK();
     }
+    return 0;
+}
+
+extern "C" int tk_json_decode(tk_ctx* ctx, int slot, int dtype, uint32_t max_len, uint32_t fixed_len,
+                              const tk_plane_t* values, const tk_plane_t* lengths, const tk_plane_t* mask,
+                              void* stream) {
+    TK_ENTER(ctx, slot);
+    tk_slot& s = ctx->slots[slot];
+    cudaStream_t st = (cudaStream_t)stream;
+    TK_REQUIRE(values && values->base, "values plane is required");
+    TK_REQUIRE(max_len > 0, "max_len must be positive");
+    TK_REQUIRE(dtype >= TK_DTYPE_F32 && dtype <= TK_DTYPE_I64, "unknown dtype %d", dtype);
+    int rc = tk_ensure_token_arrays(ctx);
+    if (rc) return rc;
+    const uint32_t n = s.n_records;
+    if (!n) return 0;
+    flat_args a;
+    a.bytes = s.d.bytes; a.recs = s.d.recs; a.n = n; a.max_len = max_len; a.fixed_len = fixed_len;
+    a.rec_kidx = s.d.rec_kidx; a.rec_len = s.d.rec_len; a.rec_status = s.d.rec_status;
+    a.rec_tok = s.d.rec_tok; a.res = s.d.result;
+    a.tok_pos = s.d.tok_pos; a.tok_dst = s.d.tok_dst; a.tok_rec = s.d.tok_rec;
+    a.tok_cap = (uint32_t)(ctx->tok_cap > 0xFFFFFFFFull ? 0xFFFFFFFFull : ctx->tok_cap);
+    tk_plane_t z; z.base = nullptr; z.row_bytes = 0;
+    a.values = *values;
+    a.lengths = lengths ? *lengths : z;
+    a.mask = mask ? *mask : z;
+    const uint32_t tblocks = min((n + 7) / 8, 148u * 16u);
+    if (dtype == TK_DTYPE_F32 || dtype == TK_DTYPE_I32) k_json_tokenise<4><<<tblocks, 256, 0, st>>>(a);
+    else k_json_tokenise<8><<<tblocks, 256, 0, st>>>(a);
+    TK_LAUNCH_CHECK();
+    // the element count lives on the device; size the grid for the worst case this slot allows
+    // (an element needs two bytes) and let surplus blocks exit at once
+    const uint64_t max_tok = (uint64_t)s.n_bytes / 2 + n;
+    const uint32_t pblocks = (uint32_t)min((max_tok + 255) / 256, (uint64_t)148 * 32);
+    switch (dtype) {
+        case TK_DTYPE_F32: k_json_parse<TK_F32><<<pblocks, 256, 0, st>>>(a); break;
+        case TK_DTYPE_F64: k_json_parse<TK_F64><<<pblocks, 256, 0, st>>>(a); break;
+        case TK_DTYPE_I32: k_json_parse<TK_I32><<<pblocks, 256, 0, st>>>(a); break;
+        default:           k_json_parse<TK_I64><<<pblocks, 256, 0, st>>>(a); break;
+    }
+    TK_LAUNCH_CHECK();
     return 0;
 }

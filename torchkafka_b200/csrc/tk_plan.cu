@@ -46,39 +46,71 @@ __device__ __forceinline__ uint32_t block_excl_scan(uint32_t v, uint32_t* total)
     return r;
 }
 
+// 64-bit variants: the compaction scans two quantities at once, packed as
+// (kept records << 40) | elements, so that every record also learns the index of its first
+// element in the slot-wide token array of the flat decode path (tk_json_flat.cu).
+#define PACK_SHIFT 40
+__device__ __forceinline__ unsigned long long warp_incl_scan64(unsigned long long v) {
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+        unsigned long long t = __shfl_up_sync(0xffffffffu, v, d);
+        if ((threadIdx.x & 31) >= d) v += t;
+    }
+    return v;
+}
+__device__ __forceinline__ unsigned long long block_excl_scan64(unsigned long long v, unsigned long long* total) {
+    __shared__ unsigned long long warp_tot[32];
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+    unsigned long long incl = warp_incl_scan64(v);
+    if (lane == 31) warp_tot[wid] = incl;
+    __syncthreads();
+    if (wid == 0) {
+        unsigned long long w = lane < (int)((blockDim.x + 31) >> 5) ? warp_tot[lane] : 0;
+        unsigned long long wi = warp_incl_scan64(w);
+        warp_tot[lane] = wi - w;
+        if (lane == 31) *total = wi;
+    }
+    __syncthreads();
+    unsigned long long r = warp_tot[wid] + incl - v;
+    __syncthreads();
+    return r;
+}
+
 // pass 1: kept count per tile of CMP_TILE records
 __global__ void __launch_bounds__(CMP_THREADS) k_compact_count(const int32_t* __restrict__ rec_kidx,
-                                                                 uint32_t n, uint32_t* __restrict__ blk_sum) {
-    __shared__ uint32_t tot;
+                                                                 const int32_t* __restrict__ rec_len, uint32_t n,
+                                                                 unsigned long long* __restrict__ blk_sum) {
+    __shared__ unsigned long long tot;
     const uint32_t base = blockIdx.x * CMP_TILE + threadIdx.x * CMP_ITEMS;
-    uint32_t c = 0;
+    unsigned long long c = 0;
 #pragma unroll
     for (int k = 0; k < CMP_ITEMS; ++k) {
         uint32_t i = base + k;
-        if (i < n && rec_kidx[i] >= 0) ++c;
+        if (i < n) c += ((unsigned long long)(rec_kidx[i] >= 0 ? 1 : 0) << PACK_SHIFT) + (uint32_t)rec_len[i];
     }
-    block_excl_scan(c, &tot);
+    block_excl_scan64(c, &tot);
     if (threadIdx.x == 0) blk_sum[blockIdx.x] = tot;
 }
 
 // pass 2: one block scans the tile sums, fills the result header, advances the carry
-__global__ void __launch_bounds__(1024) k_compact_scan(uint32_t* __restrict__ blk_sum, uint32_t nblk,
+__global__ void __launch_bounds__(1024) k_compact_scan(unsigned long long* __restrict__ blk_sum, uint32_t nblk,
                                                        uint32_t n, uint32_t batch_size,
                                                        uint32_t max_batches, tk_state* state,
                                                        tk_result_t* __restrict__ res,
                                                        uint32_t* __restrict__ batch_end,
                                                        uint32_t* __restrict__ batch_lmax) {
-    __shared__ uint32_t tot;
-    uint32_t running = 0;
+    __shared__ unsigned long long tot;
+    unsigned long long running = 0;
     for (uint32_t base = 0; base < nblk; base += blockDim.x) {
         uint32_t i = base + threadIdx.x;
-        uint32_t v = i < nblk ? blk_sum[i] : 0;
-        uint32_t ex = block_excl_scan(v, &tot);
+        unsigned long long v = i < nblk ? blk_sum[i] : 0;
+        unsigned long long ex = block_excl_scan64(v, &tot);
         if (i < nblk) blk_sum[i] = running + ex;
         running += tot;
         __syncthreads();
     }
-    const uint32_t n_kept = running;
+    const uint32_t n_kept = (uint32_t)(running >> PACK_SHIFT);
+    const unsigned long long n_tokens = running & ((1ull << PACK_SHIFT) - 1);
     const uint32_t c = state->carry_rows;
     const uint32_t n_closed = (c + n_kept) / batch_size;
     for (uint32_t j = threadIdx.x; j <= max_batches; j += blockDim.x) {
@@ -96,6 +128,7 @@ __global__ void __launch_bounds__(1024) k_compact_scan(uint32_t* __restrict__ bl
         res->n_errors = 0;
         res->first_error_rec = 0xFFFFFFFFu;
         res->first_error_status = 0;
+        res->reserved[0] = (uint32_t)(n_tokens > 0xFFFFFFFFull ? 0xFFFFFFFFu : n_tokens);   // elements in the slot
         state->carry_rows = (c + n_kept) % batch_size;
     }
 }
@@ -107,24 +140,35 @@ __global__ void __launch_bounds__(1024) k_compact_scan(uint32_t* __restrict__ bl
 // batch, which is the common case) and the index of the record that closed it.
 __global__ void __launch_bounds__(CMP_THREADS) k_compact_apply(int32_t* __restrict__ rec_kidx,
                                                                  const int32_t* __restrict__ rec_len,
-                                                                 uint32_t n, const uint32_t* __restrict__ blk_sum,
+                                                                 uint32_t n, const unsigned long long* __restrict__ blk_sum,
+                                                                 uint32_t* __restrict__ rec_tok,
                                                                  const tk_result_t* __restrict__ res,
                                                                  uint32_t* __restrict__ batch_end,
                                                                  uint32_t* __restrict__ batch_lmax,
                                                                  const tk_rec_t* __restrict__ recs,
                                                                  int64_t* __restrict__ commit, uint32_t pitch,
                                                                  uint32_t n_partitions) {
-    __shared__ uint32_t tot;
+    __shared__ unsigned long long tot;
     const uint32_t base = blockIdx.x * CMP_TILE + threadIdx.x * CMP_ITEMS;
     int keep[CMP_ITEMS];
-    uint32_t c = 0;
+    uint32_t lens[CMP_ITEMS];
+    unsigned long long c = 0;
 #pragma unroll
     for (int k = 0; k < CMP_ITEMS; ++k) {
         uint32_t i = base + k;
         keep[k] = (i < n && rec_kidx[i] >= 0) ? 1 : 0;
-        c += keep[k];
+        lens[k] = i < n ? (uint32_t)rec_len[i] : 0u;
+        c += ((unsigned long long)keep[k] << PACK_SHIFT) + lens[k];
     }
-    uint32_t ex = block_excl_scan(c, &tot) + blk_sum[blockIdx.x];
+    const unsigned long long ex64 = block_excl_scan64(c, &tot) + blk_sum[blockIdx.x];
+    uint32_t ex = (uint32_t)(ex64 >> PACK_SHIFT);
+    uint32_t tok = (uint32_t)ex64;                        // first element of record `base` in the token array
+#pragma unroll
+    for (int k = 0; k < CMP_ITEMS; ++k) {
+        if (base + k < n) rec_tok[base + k] = tok;
+        tok += lens[k];
+        if (base + k + 1 == n) rec_tok[n] = tok;               // closing entry
+    }
     const uint32_t carry = res->carry_in, B = res->batch_size;
 #pragma unroll
     for (int k = 0; k < CMP_ITEMS; ++k) {
@@ -135,7 +179,7 @@ __global__ void __launch_bounds__(CMP_THREADS) k_compact_apply(int32_t* __restri
         if (live) {
             if (keep[k]) {
                 rec_kidx[i] = (int32_t)ex;
-                len = (uint32_t)rec_len[i];
+                len = lens[k];
                 if ((carry + ex + 1) % B == 0) batch_end[j] = i;
             } else {
                 rec_kidx[i] = -1 - (int32_t)ex;
@@ -184,14 +228,14 @@ extern "C" int tk_compact(tk_ctx* ctx, int slot, uint32_t batch_size, void* stre
     // commit matrix starts at -1 ("partition not seen"); filled by the apply pass below
     TK_CUDA(cudaMemsetAsync(s.d.commit, 0xFF, sizeof(int64_t) * (size_t)ctx->n_partitions * ctx->commit_pitch, st));
     if (nblk) {
-        k_compact_count<<<nblk, CMP_THREADS, 0, st>>>(s.d.rec_kidx, n, s.d.blk_sum);
+        k_compact_count<<<nblk, CMP_THREADS, 0, st>>>(s.d.rec_kidx, s.d.rec_len, n, s.d.blk_sum);
         TK_LAUNCH_CHECK();
     }
     k_compact_scan<<<1, 1024, 0, st>>>(s.d.blk_sum, nblk, n, batch_size, ctx->max_batches, ctx->d_state,
                                        s.d.result, s.d.batch_end, s.d.batch_lmax);
     TK_LAUNCH_CHECK();
     if (nblk) {
-        k_compact_apply<<<nblk, CMP_THREADS, 0, st>>>(s.d.rec_kidx, s.d.rec_len, n, s.d.blk_sum, s.d.result,
+        k_compact_apply<<<nblk, CMP_THREADS, 0, st>>>(s.d.rec_kidx, s.d.rec_len, n, s.d.blk_sum, s.d.rec_tok, s.d.result,
                                                      s.d.batch_end, s.d.batch_lmax, s.d.recs, s.d.commit,
                                                      ctx->commit_pitch, ctx->n_partitions);
         TK_LAUNCH_CHECK();

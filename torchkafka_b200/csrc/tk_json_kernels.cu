@@ -708,7 +708,12 @@ __device__ __forceinline__ bool flat_token24(const uint8_t* bytes, uint32_t pos,
         if (m1) w = w * c_pow10[m1] + parse_upto8(global_load8(bytes, pos + q0 + 8), m1);
     }
     if (endp >= avail) return false;
-    if (bytes[pos + endp] != ',') return false;             // ']' / ws / exponent: general path
+    {
+        // the segment ends at the next ',' -- or, for the last element, at the closing ']' that is
+        // also the last byte of the record; anything else (ws, exponent, garbage): general path
+        const uint32_t g = bytes[pos + endp];
+        if (g != ',' && !(g == ']' && endp + 1 == avail)) return false;
+    }
     tk_token t;
     t.w = w; t.q = -(int32_t)L2; t.end = pos + endp; t.dig_begin = pos + p; t.exp10 = 0;
     t.neg = (uint8_t)neg; t.is_int = L2 == 0; t.truncated = 0; t.special = 0; t.err = TK_OK;

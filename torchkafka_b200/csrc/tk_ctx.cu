@@ -158,7 +158,7 @@ static void free_slot(tk_slot& s) {
     if (s.h_block) cudaFreeHost(s.h_block);
     cudaFree(s.d.bytes); cudaFree(s.d.recs); cudaFree(s.d.rec_len); cudaFree(s.d.rec_status);
     cudaFree(s.d.rec_kidx); cudaFree(s.d.blk_sum); cudaFree(s.d.block);
-    cudaFree(s.d.rec_tok); cudaFree(s.d.tok_pos); cudaFree(s.d.tok_dst); cudaFree(s.d.tok_rec);
+    cudaFree(s.d.rec_tok); cudaFree(s.d.tok_pos); cudaFree(s.d.tok_rec); cudaFree(s.d.tok_count);
     if (s.ev_h2d) cudaEventDestroy(s.ev_h2d);
     if (s.ev_free) cudaEventDestroy(s.ev_free);
     if (s.ev_result) cudaEventDestroy(s.ev_result);
@@ -253,7 +253,7 @@ extern "C" int tk_ctx_create(int device, uint64_t slot_bytes, uint32_t slot_reco
     return 0;
 }
 
-// The flat JSON decode keeps one (position, destination, record) triple per element of the slot.
+// The flat JSON decode keeps one (position, record) pair per element of the slot.
 // An element needs at least two bytes ("1,"), so slot_bytes / 2 + slot_records entries always
 // suffice.  Raw / image contexts never pay for it.
 int tk_ensure_token_arrays(tk_ctx* ctx) {
@@ -262,8 +262,8 @@ int tk_ensure_token_arrays(tk_ctx* ctx) {
     for (int i = 0; i < ctx->n_slots; ++i) {
         tk_slot& s = ctx->slots[i];
         TK_CUDA(cudaMalloc(&s.d.tok_pos, sizeof(uint32_t) * cap));
-        TK_CUDA(cudaMalloc(&s.d.tok_dst, sizeof(uint32_t) * cap));
         TK_CUDA(cudaMalloc(&s.d.tok_rec, sizeof(uint32_t) * cap));
+        TK_CUDA(cudaMalloc(&s.d.tok_count, sizeof(uint32_t)));
     }
     ctx->tok_cap = cap;
     return 0;

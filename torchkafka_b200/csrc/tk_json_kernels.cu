@@ -70,55 +70,109 @@ __device__ __forceinline__ void report_error(tk_result_t* res, uint32_t rec, int
 }
 
 // ---------------------------------------------------------------- K1 phase 1
-// Element count per record = commas + 1 for a non-empty array (emptiness is read off the head
-// of the record by lane 0).  (Only valid
-// records need a correct count: malformed ones are flagged by the decode kernel
-// and poison their batch.)  keep flag: rec_kidx = 0 (kept) / -1 (skipped).
-__global__ void __launch_bounds__(256) k_json_scan(const uint8_t* __restrict__ bytes,
-                                                    const tk_rec_t* __restrict__ recs, uint32_t n,
-                                                    uint32_t max_len, uint32_t min_size,
-                                                    int32_t* __restrict__ rec_len,
-                                                    int32_t* __restrict__ rec_status,
-                                                    int32_t* __restrict__ rec_kidx) {
+// One warp per record, two passes over the record's bytes (the second one hits L1/L2):
+//   pass 1  count the commas -> element count (commas + 1, or 0 for "[]"), validate the head of
+//           the record ([BOM] ws* '[' ws*), decide the keep flag (rec_kidx = 0 kept / -1 skipped)
+//           and reserve the record's range in the slot-wide token array with one atomicAdd;
+//   pass 2  cut the record at its commas: one (byte position, record) pair per element.
+// The token array feeds the thread-per-element parse kernel (k_json_parse); the order of records
+// inside it is the order of the atomicAdds, which does not matter.
+struct GlobalReader {
+    const uint8_t* bytes;
+    uint32_t end;
+    __device__ __forceinline__ int operator()(uint32_t pos) const { return pos < end ? (int)bytes[pos] : -1; }
+};
+
+// 0x80 in every byte lane of x that holds ','
+__device__ __forceinline__ uint32_t comma4(uint32_t x) {
+    const uint32_t y = x ^ 0x2C2C2C2Cu;
+    return ~(((y & 0x7F7F7F7Fu) + 0x7F7F7F7Fu) | y) & 0x80808080u;
+}
+
+struct scan_args {
+    const uint8_t*  bytes;
+    const tk_rec_t* recs;
+    uint32_t        n, max_len, min_size;
+    int32_t*        rec_len;
+    int32_t*        rec_status;
+    int32_t*        rec_kidx;
+    uint32_t*       rec_tok;
+    uint32_t*       tok_pos;
+    uint32_t*       tok_rec;
+    uint32_t*       tok_count;
+    uint32_t        tok_cap;
+};
+
+__global__ void __launch_bounds__(256) k_json_scan(const scan_args a) {
     const uint32_t lane = threadIdx.x & 31;
     const uint32_t warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
     const uint32_t nwarps = (gridDim.x * blockDim.x) >> 5;
-    for (uint32_t i = warp; i < n; i += nwarps) {
-        const uint32_t start = recs[i].start, end = recs[i + 1].start;
+    for (uint32_t i = warp; i < a.n; i += nwarps) {
+        const uint32_t start = a.recs[i].start, end = a.recs[i + 1].start;
+        const uint32_t base0 = start & ~15u;
+        // ---- pass 1
         uint32_t commas = 0;
-        for (uint32_t pos = (start & ~15u) + lane * 16; pos < end; pos += 512) {
-            const uint4 v = __ldg(reinterpret_cast<const uint4*>(bytes + pos));
-            const uint32_t w[4] = {v.x, v.y, v.z, v.w};
-            const bool interior = pos >= start && pos + 16 <= end;
-            uint32_t cm = 0;
-#pragma unroll
-            for (int k = 0; k < 4; ++k) {
-                const uint32_t yc = w[k] ^ 0x2C2C2C2Cu;                                  // zero byte: ','
-                const uint32_t iscomma = ~(((yc & 0x7F7F7F7Fu) + 0x7F7F7F7Fu) | yc) & 0x80808080u;
-                if (interior) commas += __popc(iscomma);
-                else cm |= hibits_to_nibble(iscomma) << (4 * k);
+        for (uint32_t pos = base0 + lane * 16; pos < end; pos += 512) {
+            const uint4 v = __ldg(reinterpret_cast<const uint4*>(a.bytes + pos));
+            const uint32_t c0 = comma4(v.x), c1 = comma4(v.y), c2 = comma4(v.z), c3 = comma4(v.w);
+            if (pos >= start && pos + 16 <= end) {
+                commas += __popc(c0) + __popc(c1) + __popc(c2) + __popc(c3);
+            } else {
+                const uint32_t cm = hibits_to_nibble(c0) | (hibits_to_nibble(c1) << 4) |
+                                    (hibits_to_nibble(c2) << 8) | (hibits_to_nibble(c3) << 12);
+                commas += __popc(cm & range16((int)start - (int)pos, (int)end - (int)pos));
             }
-            if (!interior) commas += __popc(cm & range16((int)start - (int)pos, (int)end - (int)pos));
         }
         commas = __reduce_add_sync(0xffffffffu, commas);
-        // empty array?  lane 0 looks at the head of the record: [BOM] ws* '[' ws* ']'
-        uint32_t content = 1;
+        uint32_t len = 0, t0 = 0;
         if (lane == 0) {
-            uint32_t p = start;
-            if (p + 2 < end && bytes[p] == 0xEF && bytes[p + 1] == 0xBB && bytes[p + 2] == 0xBF) p += 3;
-            while (p < end && tk_is_ws(bytes[p])) ++p;
-            if (p < end && bytes[p] == '[') {
-                ++p;
-                while (p < end && tk_is_ws(bytes[p])) ++p;
-                if (p < end && bytes[p] == ']') content = 0;
+            GlobalReader rd{a.bytes, end};
+            uint32_t first = start;
+            bool empty = false;
+            const int head = end > start ? tk_json_prefix(rd, start, &first, &empty) : TK_ERR_SYNTAX;
+            len = (!head && empty) ? 0u : commas + 1u;
+            const int status = head ? head : (len > a.max_len ? TK_ERR_TOO_LONG : TK_OK);
+            a.rec_len[i] = (int32_t)len;
+            a.rec_status[i] = status;
+            a.rec_kidx[i] = (status == TK_OK && len >= a.min_size) ? 0 : -1;
+            if (len) {
+                t0 = atomicAdd(a.tok_count, len);
+                if (t0 < a.tok_cap) { a.tok_pos[t0] = head ? start : first; a.tok_rec[t0] = i; }
             }
+            a.rec_tok[i] = t0;
         }
-        if (lane == 0) {
-            const uint32_t len = content ? commas + 1 : 0;
-            rec_len[i] = (int32_t)len;
-            const bool too_long = len > max_len;
-            rec_status[i] = too_long ? TK_ERR_TOO_LONG : TK_OK;
-            rec_kidx[i] = (!too_long && len >= min_size) ? 0 : -1;
+        len = __shfl_sync(0xffffffffu, len, 0);
+        t0 = __shfl_sync(0xffffffffu, t0, 0);
+        if (len <= 1) continue;
+        // ---- pass 2: element e (>= 1) starts right after the e-th comma
+        uint32_t seen = 0;
+        for (uint32_t base = base0; base < end; base += 512) {
+            const uint32_t pos = base + lane * 16;
+            uint32_t cm = 0;
+            if (pos < end) {
+                const uint4 v = __ldg(reinterpret_cast<const uint4*>(a.bytes + pos));
+                const uint32_t c0 = comma4(v.x), c1 = comma4(v.y), c2 = comma4(v.z), c3 = comma4(v.w);
+                if (c0 | c1 | c2 | c3) {
+                    cm = hibits_to_nibble(c0) | (hibits_to_nibble(c1) << 4) | (hibits_to_nibble(c2) << 8) |
+                         (hibits_to_nibble(c3) << 12);
+                    if (pos < start || pos + 16 > end) cm &= range16((int)start - (int)pos, (int)end - (int)pos);
+                }
+            }
+            const uint32_t cnt = __popc(cm);
+            uint32_t incl = cnt;
+#pragma unroll
+            for (int d = 1; d < 32; d <<= 1) {
+                const uint32_t o = __shfl_up_sync(0xffffffffu, incl, d);
+                if (lane >= (uint32_t)d) incl += o;
+            }
+            uint32_t t = t0 + 1 + seen + incl - cnt;
+            while (cm) {
+                const int b = __ffs(cm) - 1;
+                cm &= cm - 1;
+                if (t < a.tok_cap) { a.tok_pos[t] = pos + b + 1; a.tok_rec[t] = i; }
+                ++t;
+            }
+            seen += __shfl_sync(0xffffffffu, incl, 31);
         }
     }
 }
@@ -127,10 +181,18 @@ extern "C" int tk_json_scan(tk_ctx* ctx, int slot, uint32_t max_len, uint32_t mi
     TK_ENTER(ctx, slot);
     tk_slot& s = ctx->slots[slot];
     const uint32_t n = s.n_records;
+    int rc = tk_ensure_token_arrays(ctx);
+    if (rc) return rc;
+    cudaStream_t st = (cudaStream_t)stream;
+    TK_CUDA(cudaMemsetAsync(s.d.tok_count, 0, sizeof(uint32_t), st));
     if (!n) return 0;
+    scan_args a;
+    a.bytes = s.d.bytes; a.recs = s.d.recs; a.n = n; a.max_len = max_len; a.min_size = min_size;
+    a.rec_len = s.d.rec_len; a.rec_status = s.d.rec_status; a.rec_kidx = s.d.rec_kidx; a.rec_tok = s.d.rec_tok;
+    a.tok_pos = s.d.tok_pos; a.tok_rec = s.d.tok_rec; a.tok_count = s.d.tok_count;
+    a.tok_cap = (uint32_t)(ctx->tok_cap > 0xFFFFFFFFull ? 0xFFFFFFFFull : ctx->tok_cap);
     const uint32_t blocks = min((n + 7) / 8, 148u * 16u);
-    k_json_scan<<<blocks, 256, 0, (cudaStream_t)stream>>>(s.d.bytes, s.d.recs, n, max_len, min_size,
-                                                         s.d.rec_len, s.d.rec_status, s.d.rec_kidx);
+    k_json_scan<<<blocks, 256, 0, st>>>(a);
     TK_LAUNCH_CHECK();
     return 0;
 }
@@ -512,21 +574,12 @@ __global__ void __launch_bounds__(JD_WARPS * 32, 8) k_json_decode(const decode_a
 }
 
 // ================================================================ flat decode path
-// Two kernels instead of one warp-per-record kernel:
-//   k_json_tokenise  (warp per record) cuts every record at its commas and writes one
-//                    (byte position, destination element, record) triple per element into a
-//                    slot-wide token array -- the record's first slot in that array comes from
-//                    the compaction scan (rec_tok) -- and writes pad, length and mask of the row;
+// After k_json_scan (token array) and the compaction (row of every kept record):
+//   k_json_rows      (warp per record) reports the records the scan rejected, checks fixed_len,
+//                    and writes pad, length and mask of every kept record's row;
 //   k_json_parse<T>  (thread per element) parses one token each: perfectly balanced, every
-//                    lane busy whatever the record lengths are, no shared memory, so occupancy
-//                    is limited by registers only.
+//                    lane busy whatever the record lengths are, no shared memory.
 // The grammar is checked with the comma-split decomposition (tk_json_gap_flat in tk_json.cuh).
-struct GlobalReader {
-    const uint8_t* bytes;
-    uint32_t end;
-    __device__ __forceinline__ int operator()(uint32_t pos) const { return pos < end ? (int)bytes[pos] : -1; }
-};
-
 struct flat_args {
     const uint8_t*  bytes;
     const tk_rec_t* recs;
@@ -538,9 +591,9 @@ struct flat_args {
     int32_t*        rec_status;
     const uint32_t* rec_tok;
     tk_result_t*    res;
-    uint32_t*       tok_pos;
-    uint32_t*       tok_dst;
-    uint32_t*       tok_rec;
+    const uint32_t* tok_pos;
+    const uint32_t* tok_rec;
+    const uint32_t* tok_count;
     uint32_t        tok_cap;
     tk_plane_t      values, lengths, mask;
 };
@@ -550,102 +603,43 @@ __device__ __forceinline__ void flag_record(int32_t* rec_status, tk_result_t* re
 }
 
 template <int ELEM_BYTES>
-__global__ void __launch_bounds__(256) k_json_tokenise(const flat_args a) {
+__global__ void __launch_bounds__(256) k_json_rows(const flat_args a) {
     const uint32_t lane = threadIdx.x & 31;
     const uint32_t warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
     const uint32_t nwarps = (gridDim.x * blockDim.x) >> 5;
     const uint32_t B = a.res->batch_size;
     for (uint32_t i = warp; i < a.n; i += nwarps) {
-        const uint32_t start = a.recs[i].start, end = a.recs[i + 1].start;
         const int32_t kidx = a.rec_kidx[i];
-        const uint32_t len = (uint32_t)a.rec_len[i];          // commas + 1, or 0 for "[]" (k_json_scan)
-        const uint32_t t0 = a.rec_tok[i];
-        const bool kept = kidx >= 0;
-        const uint64_t row = (uint64_t)B + (uint32_t)(kept ? kidx : 0);
-        const uint64_t dst_base = row * a.max_len;            // element index of the row's first element
-        const bool addressable = kept && dst_base + a.max_len < 0xFFFFFFFFull;
-
-        // head of the record: [BOM] ws* '[' ws* <first token> | ']' ws* END
-        uint32_t first = start;
-        int head = TK_OK;
+        const uint32_t len = (uint32_t)a.rec_len[i];
         if (lane == 0) {
-            GlobalReader rd{a.bytes, end};
-            bool empty = false;
-            head = end > start ? tk_json_prefix(rd, start, &first, &empty) : TK_ERR_SYNTAX;
-            if (!head && kept && !addressable) head = TK_ERR_TOO_LONG;
-            if (!head && kept && a.fixed_len && len != a.fixed_len) head = TK_ERR_RAGGED;
-            const int pre = a.rec_status[i];                  // TK_ERR_TOO_LONG from the scan
+            const int pre = a.rec_status[i];                  // head / TOO_LONG verdict of the scan
             if (pre) report_error(a.res, i, pre);
-            else if (head) flag_record(a.rec_status, a.res, i, head);
-            if (len && t0 < a.tok_cap) {
-                a.tok_pos[t0] = first;
-                a.tok_dst[t0] = (addressable && a.max_len) ? (uint32_t)dst_base : 0xFFFFFFFFu;
-                a.tok_rec[t0] = i;
-            }
+            else if (kidx >= 0 && a.fixed_len && len != a.fixed_len)
+                flag_record(a.rec_status, a.res, i, TK_ERR_RAGGED);
         }
-        // one token after every comma
-        uint32_t seen = 0;                                    // commas before the current 512-byte step
-        if (len > 1) {
-            for (uint32_t base = start & ~15u; base < end; base += 512) {
-                const uint32_t pos = base + lane * 16;
-                uint32_t cm = 0;
-                if (pos < end) {
-                    const uint4 v = __ldg(reinterpret_cast<const uint4*>(a.bytes + pos));
-                    const uint32_t w[4] = {v.x, v.y, v.z, v.w};
-#pragma unroll
-                    for (int k = 0; k < 4; ++k) {
-                        const uint32_t yc = w[k] ^ 0x2C2C2C2Cu;
-                        const uint32_t iscomma = ~(((yc & 0x7F7F7F7Fu) + 0x7F7F7F7Fu) | yc) & 0x80808080u;
-                        cm |= hibits_to_nibble(iscomma) << (4 * k);
-                    }
-                    cm &= range16((int)start - (int)pos, (int)end - (int)pos);
-                }
-                const uint32_t cnt = __popc(cm);
-                uint32_t incl = cnt;
-#pragma unroll
-                for (int d = 1; d < 32; d <<= 1) {
-                    const uint32_t o = __shfl_up_sync(0xffffffffu, incl, d);
-                    if (lane >= (uint32_t)d) incl += o;
-                }
-                uint32_t e = 1 + seen + incl - cnt;           // element index of this lane's first comma
-                while (cm) {
-                    const int b = __ffs(cm) - 1;
-                    cm &= cm - 1;
-                    const uint32_t t = t0 + e;
-                    if (e < len && t < a.tok_cap) {
-                        a.tok_pos[t] = pos + b + 1;
-                        a.tok_dst[t] = (addressable && e < a.max_len) ? (uint32_t)(dst_base + e) : 0xFFFFFFFFu;
-                        a.tok_rec[t] = i;
-                    }
-                    ++e;
-                }
-                seen += __shfl_sync(0xffffffffu, incl, 31);
-            }
+        if (kidx < 0) continue;
+        const uint64_t row = (uint64_t)B + (uint32_t)kidx;
+        const uint32_t fill_from = min(len, a.max_len);
+        uint8_t* vrow = (uint8_t*)a.values.base + row * a.values.row_bytes;
+        if (ELEM_BYTES == 4) {
+            uint32_t* p = reinterpret_cast<uint32_t*>(vrow);
+            for (uint32_t e = fill_from + lane; e < a.max_len; e += 32) p[e] = 0u;
+        } else {
+            unsigned long long* p = reinterpret_cast<unsigned long long*>(vrow);
+            for (uint32_t e = fill_from + lane; e < a.max_len; e += 32) p[e] = 0ull;
         }
-        // K3: pad, length, mask of the row (the elements themselves are written by k_json_parse)
-        if (addressable) {
-            const uint32_t fill_from = min(len, a.max_len);
-            uint8_t* vrow = (uint8_t*)a.values.base + row * a.values.row_bytes;
-            if (ELEM_BYTES == 4) {
-                uint32_t* p = reinterpret_cast<uint32_t*>(vrow);
-                for (uint32_t e = fill_from + lane; e < a.max_len; e += 32) p[e] = 0u;
+        if (a.lengths.base && lane == 0)
+            *reinterpret_cast<int32_t*>((uint8_t*)a.lengths.base + row * a.lengths.row_bytes) = (int32_t)len;
+        if (a.mask.base) {
+            uint8_t* m = (uint8_t*)a.mask.base + row * a.mask.row_bytes;
+            if ((a.max_len & 3u) == 0 && ((uintptr_t)m & 3u) == 0) {
+                uint32_t* m32 = reinterpret_cast<uint32_t*>(m);
+                for (uint32_t w = lane; w < a.max_len / 4; w += 32) {
+                    const int left = (int)len - (int)(w * 4);
+                    m32[w] = left >= 4 ? 0x01010101u : (left <= 0 ? 0u : (0x01010101u >> (8 * (4 - left))));
+                }
             } else {
-                unsigned long long* p = reinterpret_cast<unsigned long long*>(vrow);
-                for (uint32_t e = fill_from + lane; e < a.max_len; e += 32) p[e] = 0ull;
-            }
-            if (a.lengths.base && lane == 0)
-                *reinterpret_cast<int32_t*>((uint8_t*)a.lengths.base + row * a.lengths.row_bytes) = (int32_t)len;
-            if (a.mask.base) {
-                uint8_t* m = (uint8_t*)a.mask.base + row * a.mask.row_bytes;
-                if ((a.max_len & 3u) == 0 && ((uintptr_t)m & 3u) == 0) {
-                    uint32_t* m32 = reinterpret_cast<uint32_t*>(m);
-                    for (uint32_t w = lane; w < a.max_len / 4; w += 32) {
-                        const int left = (int)len - (int)(w * 4);
-                        m32[w] = left >= 4 ? 0x01010101u : (left <= 0 ? 0u : (0x01010101u >> (8 * (4 - left))));
-                    }
-                } else {
-                    for (uint32_t e = lane; e < a.max_len; e += 32) m[e] = e < len ? 1 : 0;
-                }
+                for (uint32_t e = lane; e < a.max_len; e += 32) m[e] = e < len ? 1 : 0;
             }
         }
     }
@@ -725,10 +719,11 @@ __device__ __forceinline__ bool flat_token24(const uint8_t* bytes, uint32_t pos,
 template <int KIND>
 __global__ void __launch_bounds__(256) k_json_parse(const flat_args a) {
     typedef typename tk_elem<KIND>::type T;
-    const uint32_t n_tok = min(a.res->reserved[0], a.tok_cap);
+    const uint32_t n_tok = min(*a.tok_count, a.tok_cap);
+    const uint64_t B = a.res->batch_size;
     T* values = reinterpret_cast<T*>(a.values.base);
     for (uint32_t t = blockIdx.x * blockDim.x + threadIdx.x; t < n_tok; t += gridDim.x * blockDim.x) {
-        const uint32_t pos = a.tok_pos[t], dst = a.tok_dst[t], rec = a.tok_rec[t];
+        const uint32_t pos = a.tok_pos[t], rec = a.tok_rec[t];
         const uint32_t end = a.recs[rec + 1].start;
         GlobalReader rd{a.bytes, end};
         T v;
@@ -747,11 +742,12 @@ __global__ void __launch_bounds__(256) k_json_parse(const flat_args a) {
         } else {
             st = tk_json_element_flat<KIND>(rd, pos, &v);
         }
-        if (st) flag_record(a.rec_status, a.res, rec, st);
-        else if (dst != 0xFFFFFFFFu) values[dst] = v;
+        if (st) { flag_record(a.rec_status, a.res, rec, st); continue; }
+        const int32_t kidx = a.rec_kidx[rec];
+        const uint32_t e = t - a.rec_tok[rec];               // element index inside the record
+        if (kidx >= 0 && e < a.max_len) values[(B + (uint32_t)kidx) * a.max_len + e] = v;
     }
 }
-
 
 extern "C" int tk_json_decode_warp(tk_ctx* ctx, int slot, int dtype, uint32_t max_len, uint32_t fixed_len,
                                    const tk_plane_t* values, const tk_plane_t* lengths, const tk_plane_t* mask,
@@ -792,23 +788,22 @@ extern "C" int tk_json_decode(tk_ctx* ctx, int slot, int dtype, uint32_t max_len
     TK_REQUIRE(values && values->base, "values plane is required");
     TK_REQUIRE(max_len > 0, "max_len must be positive");
     TK_REQUIRE(dtype >= TK_DTYPE_F32 && dtype <= TK_DTYPE_I64, "unknown dtype %d", dtype);
-    int rc = tk_ensure_token_arrays(ctx);
-    if (rc) return rc;
+    TK_REQUIRE(ctx->tok_cap, "tk_json_scan must run before tk_json_decode");
     const uint32_t n = s.n_records;
     if (!n) return 0;
     flat_args a;
     a.bytes = s.d.bytes; a.recs = s.d.recs; a.n = n; a.max_len = max_len; a.fixed_len = fixed_len;
     a.rec_kidx = s.d.rec_kidx; a.rec_len = s.d.rec_len; a.rec_status = s.d.rec_status;
     a.rec_tok = s.d.rec_tok; a.res = s.d.result;
-    a.tok_pos = s.d.tok_pos; a.tok_dst = s.d.tok_dst; a.tok_rec = s.d.tok_rec;
+    a.tok_pos = s.d.tok_pos; a.tok_rec = s.d.tok_rec; a.tok_count = s.d.tok_count;
     a.tok_cap = (uint32_t)(ctx->tok_cap > 0xFFFFFFFFull ? 0xFFFFFFFFull : ctx->tok_cap);
     tk_plane_t z; z.base = nullptr; z.row_bytes = 0;
     a.values = *values;
     a.lengths = lengths ? *lengths : z;
     a.mask = mask ? *mask : z;
-    const uint32_t tblocks = min((n + 7) / 8, 148u * 16u);
-    if (dtype == TK_DTYPE_F32 || dtype == TK_DTYPE_I32) k_json_tokenise<4><<<tblocks, 256, 0, st>>>(a);
-    else k_json_tokenise<8><<<tblocks, 256, 0, st>>>(a);
+    const uint32_t rblocks = min((n + 7) / 8, 148u * 16u);
+    if (dtype == TK_DTYPE_F32 || dtype == TK_DTYPE_I32) k_json_rows<4><<<rblocks, 256, 0, st>>>(a);
+    else k_json_rows<8><<<rblocks, 256, 0, st>>>(a);
     TK_LAUNCH_CHECK();
     // the element count lives on the device; size the grid for the worst case this slot allows
     // (an element needs two bytes) and let surplus blocks exit at once

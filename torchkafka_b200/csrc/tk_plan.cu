@@ -47,8 +47,8 @@ __device__ __forceinline__ uint32_t block_excl_scan(uint32_t v, uint32_t* total)
 }
 
 // 64-bit variants: the compaction scans two quantities at once, packed as
-// (kept records << 40) | elements, so that every record also learns the index of its first
-// element in the slot-wide token array of the flat decode path (tk_json_flat.cu).
+// (kept records << 40) | elements: the second sum is the number of elements in the slot, which
+// sizes the thread-per-element parse kernel of the flat decode path.
 #define PACK_SHIFT 40
 __device__ __forceinline__ unsigned long long warp_incl_scan64(unsigned long long v) {
 #pragma unroll
@@ -141,7 +141,6 @@ __global__ void __launch_bounds__(1024) k_compact_scan(unsigned long long* __res
 __global__ void __launch_bounds__(CMP_THREADS) k_compact_apply(int32_t* __restrict__ rec_kidx,
                                                                  const int32_t* __restrict__ rec_len,
                                                                  uint32_t n, const unsigned long long* __restrict__ blk_sum,
-                                                                 uint32_t* __restrict__ rec_tok,
                                                                  const tk_result_t* __restrict__ res,
                                                                  uint32_t* __restrict__ batch_end,
                                                                  uint32_t* __restrict__ batch_lmax,
@@ -162,13 +161,6 @@ __global__ void __launch_bounds__(CMP_THREADS) k_compact_apply(int32_t* __restri
     }
     const unsigned long long ex64 = block_excl_scan64(c, &tot) + blk_sum[blockIdx.x];
     uint32_t ex = (uint32_t)(ex64 >> PACK_SHIFT);
-    uint32_t tok = (uint32_t)ex64;                        // first element of record `base` in the token array
-#pragma unroll
-    for (int k = 0; k < CMP_ITEMS; ++k) {
-        if (base + k < n) rec_tok[base + k] = tok;
-        tok += lens[k];
-        if (base + k + 1 == n) rec_tok[n] = tok;               // closing entry
-    }
     const uint32_t carry = res->carry_in, B = res->batch_size;
 #pragma unroll
     for (int k = 0; k < CMP_ITEMS; ++k) {
@@ -235,7 +227,7 @@ extern "C" int tk_compact(tk_ctx* ctx, int slot, uint32_t batch_size, void* stre
                                        s.d.result, s.d.batch_end, s.d.batch_lmax);
     TK_LAUNCH_CHECK();
     if (nblk) {
-        k_compact_apply<<<nblk, CMP_THREADS, 0, st>>>(s.d.rec_kidx, s.d.rec_len, n, s.d.blk_sum, s.d.rec_tok, s.d.result,
+        k_compact_apply<<<nblk, CMP_THREADS, 0, st>>>(s.d.rec_kidx, s.d.rec_len, n, s.d.blk_sum, s.d.result,
                                                      s.d.batch_end, s.d.batch_lmax, s.d.recs, s.d.commit,
                                                      ctx->commit_pitch, ctx->n_partitions);
         TK_LAUNCH_CHECK();

@@ -41,9 +41,18 @@ __device__ __forceinline__ uint32_t tokclass4(uint32_t x) {
     const uint32_t nb = ((yb & 0x7F7F7F7Fu) + 0x7F7F7F7Fu) | yb;           // bit7: not a bracket
     return ge & nc & nb & 0x80808080u;
 }
-// bits 7,15,23,31 of m -> bits 0..3
+// bits 7,15,23,31 of m (nothing else set) -> bits 0..3.  One multiply puts copies of the four flags
+// at bits 28..31 (7+21, 15+14, 23+7, 31+0; all partial products land on distinct bits, no carries).
 __device__ __forceinline__ uint32_t hibits_to_nibble(uint32_t m) {
-    return (((m >> 7) * 0x00204081u) >> 21) & 0xFu;
+    return (m * 0x00204081u) >> 28;
+}
+// a * b + c issued as an integer multiply-add (FMA pipe); the kernels in this file are bound by
+// the ALU pipe (logic / shift / add), so merges of disjoint bit fields and plain additions in the
+// hottest helpers are expressed this way
+__device__ __forceinline__ uint32_t imad(uint32_t a, uint32_t b, uint32_t c) {
+    uint32_t r;
+    asm("mad.lo.u32 %0, %1, %2, %3;" : "=r"(r) : "r"(a), "r"(b), "r"(c));
+    return r;
 }
 // one bit per byte lane (bit b set iff byte b of m is 0xFF)
 __device__ __forceinline__ uint32_t bytemask_to_bits(uint32_t m) {
@@ -243,8 +252,8 @@ __device__ __forceinline__ uint32_t leading_digits(const Window8 w) {
 }
 // value of 4 ASCII-digit bytes already reduced to 0..9, first character in the lowest byte
 __device__ __forceinline__ uint32_t parse4(uint32_t v) {
-    const uint32_t p = ((v * 2561u) >> 8) & 0x00FF00FFu;      // (10*d0 + d1) | (10*d2 + d3) << 16
-    return (p & 0xFFu) * 100u + (p >> 16);
+    const uint32_t d = v * 2561u;                              // byte 1 = 10*d0 + d1, byte 3 = 10*d2 + d3
+    return imad(__byte_perm(d, 0, 0x4441), 100u, __byte_perm(d, 0, 0x4443));
 }
 // value of the first m (1..8) digits of the window
 __device__ __forceinline__ uint32_t parse_upto8(const Window8 w, uint32_t m) {
@@ -676,8 +685,8 @@ __device__ __forceinline__ bool flat_token24(const uint8_t* bytes, uint32_t pos,
 #pragma unroll
     for (int k = 0; k < 6; ++k) {
         const uint32_t u = W[k] ^ 0x30303030u;
-        const uint32_t t = (((u & 0x7F7F7F7Fu) + 0x76767676u) | u) & 0x80808080u;
-        nd |= hibits_to_nibble(t) << (4 * k);
+        const uint32_t t = (imad(u & 0x7F7F7F7Fu, 1u, 0x76767676u) | u) & 0x80808080u;
+        nd = imad(hibits_to_nibble(t), 1u << (4 * k), nd);
     }
     if (avail < 24) nd |= 0xFFFFFFFFu << avail;
     const uint32_t neg = (W[0] & 0xFFu) == '-' ? 1u : 0u;

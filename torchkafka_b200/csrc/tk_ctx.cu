@@ -158,7 +158,7 @@ static void free_slot(tk_slot& s) {
     if (s.h_block) cudaFreeHost(s.h_block);
     cudaFree(s.d.bytes); cudaFree(s.d.recs); cudaFree(s.d.rec_len); cudaFree(s.d.rec_status);
     cudaFree(s.d.rec_kidx); cudaFree(s.d.blk_sum); cudaFree(s.d.block);
-    cudaFree(s.d.rec_tok); cudaFree(s.d.tok_pos); cudaFree(s.d.tok_rec); cudaFree(s.d.tok_count);
+    cudaFree(s.d.rec_tok); cudaFree(s.d.tok_pos); cudaFree(s.d.tok_count);
     if (s.ev_h2d) cudaEventDestroy(s.ev_h2d);
     if (s.ev_free) cudaEventDestroy(s.ev_free);
     if (s.ev_result) cudaEventDestroy(s.ev_result);
@@ -261,8 +261,7 @@ int tk_ensure_token_arrays(tk_ctx* ctx) {
     const size_t cap = (size_t)(ctx->slot_bytes / 2) + ctx->slot_records + 64;
     for (int i = 0; i < ctx->n_slots; ++i) {
         tk_slot& s = ctx->slots[i];
-        TK_CUDA(cudaMalloc(&s.d.tok_pos, sizeof(uint32_t) * cap));
-        TK_CUDA(cudaMalloc(&s.d.tok_rec, sizeof(uint32_t) * cap));
+        TK_CUDA(cudaMalloc(&s.d.tok_pos, sizeof(uint32_t) * 2 * cap));       // uint2 {position, record}
         TK_CUDA(cudaMalloc(&s.d.tok_count, sizeof(uint32_t)));
     }
     ctx->tok_cap = cap;

@@ -42,8 +42,7 @@ struct tk_slot_dev {
     int32_t*     rec_kidx;     // index among kept records of this slot, -1 if skipped
     unsigned long long* blk_sum;   // per-tile (kept << 40 | elements) for the compaction scan
     uint32_t*    rec_tok;      // [slot_records] index of each record's first element in the token array
-    uint32_t*    tok_pos;      // [tok_cap] token array of the flat decode path: byte position,
-    uint32_t*    tok_rec;      //           record index
+    uint32_t*    tok_pos;      // [tok_cap] token array of the flat decode path: uint2 {byte position, record}
     uint32_t*    tok_count;    // elements emitted so far (token array allocation cursor)
     uint8_t*     block;        // one allocation: header | batch_end | batch_lmax | commit
     tk_result_t* result;       // header

@@ -106,39 +106,75 @@ struct scan_args {
     int32_t*        rec_status;
     int32_t*        rec_kidx;
     uint32_t*       rec_tok;
-    uint32_t*       tok_pos;
-    uint32_t*       tok_rec;
+    uint32_t*       tok;          // uint2 {byte position, record} per element
     uint32_t*       tok_count;
     uint32_t        tok_cap;
 };
 
+// comma bits of one 16-byte chunk restricted to the record
+__device__ __forceinline__ uint32_t comma_mask16(const uint4 v, uint32_t pos, uint32_t start, uint32_t end) {
+    const uint32_t c0 = comma4(v.x), c1 = comma4(v.y), c2 = comma4(v.z), c3 = comma4(v.w);
+    if ((c0 | c1 | c2 | c3) == 0) return 0;
+    uint32_t cm = hibits_to_nibble(c0);
+    cm = imad(hibits_to_nibble(c1), 16u, cm);
+    cm = imad(hibits_to_nibble(c2), 256u, cm);
+    cm = imad(hibits_to_nibble(c3), 4096u, cm);
+    if (pos < start || pos + 16 > end) cm &= range16((int)start - (int)pos, (int)end - (int)pos);
+    return cm;
+}
+
+#define SCAN_KEEP 12     // 512-byte steps whose comma masks stay in registers between the passes
+
 __global__ void __launch_bounds__(256) k_json_scan(const scan_args a) {
     const uint32_t lane = threadIdx.x & 31;
+    const uint32_t lt_mask = (1u << lane) - 1u;
     const uint32_t warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
     const uint32_t nwarps = (gridDim.x * blockDim.x) >> 5;
+    uint2* tok = reinterpret_cast<uint2*>(a.tok);
     for (uint32_t i = warp; i < a.n; i += nwarps) {
         const uint32_t start = a.recs[i].start, end = a.recs[i + 1].start;
         const uint32_t base0 = start & ~15u;
-        // ---- pass 1
+        // ---- pass 1: comma masks (kept in registers for short records) and their count
         uint32_t commas = 0;
-        for (uint32_t pos = base0 + lane * 16; pos < end; pos += 512) {
-            const uint4 v = __ldg(reinterpret_cast<const uint4*>(a.bytes + pos));
-            const uint32_t c0 = comma4(v.x), c1 = comma4(v.y), c2 = comma4(v.z), c3 = comma4(v.w);
-            if (pos >= start && pos + 16 <= end) {
-                commas += __popc(c0) + __popc(c1) + __popc(c2) + __popc(c3);
-            } else {
-                const uint32_t cm = hibits_to_nibble(c0) | (hibits_to_nibble(c1) << 4) |
-                                    (hibits_to_nibble(c2) << 8) | (hibits_to_nibble(c3) << 12);
-                commas += __popc(cm & range16((int)start - (int)pos, (int)end - (int)pos));
+        uint32_t kept_mask[SCAN_KEEP / 2];
+#pragma unroll
+        for (int k = 0; k < SCAN_KEEP / 2; ++k) kept_mask[k] = 0;
+        uint4 head_chunk = make_uint4(0, 0, 0, 0);             // lane 0: the 16 bytes the record starts in
+#pragma unroll
+        for (int k = 0; k < SCAN_KEEP; ++k) {
+            const uint32_t pos = base0 + k * 512 + lane * 16;
+            if (base0 + k * 512 < end) {                       // warp-uniform
+                uint32_t cm = 0;
+                if (pos < end) {
+                    const uint4 v = __ldg(reinterpret_cast<const uint4*>(a.bytes + pos));
+                    if (k == 0) head_chunk = v;
+                    cm = comma_mask16(v, pos, start, end);
+                }
+                commas += __popc(cm);
+                kept_mask[k >> 1] |= cm << (16 * (k & 1));
             }
         }
+        for (uint32_t pos = base0 + SCAN_KEEP * 512 + lane * 16; pos < end; pos += 512)
+            commas += __popc(comma_mask16(__ldg(reinterpret_cast<const uint4*>(a.bytes + pos)), pos, start, end));
         commas = __reduce_add_sync(0xffffffffu, commas);
         uint32_t len = 0, t0 = 0;
         if (lane == 0) {
-            GlobalReader rd{a.bytes, end};
             uint32_t first = start;
             bool empty = false;
-            const int head = end > start ? tk_json_prefix(rd, start, &first, &empty) : TK_ERR_SYNTAX;
+            int head;
+            // common head "[<token character>": decided from the chunk already in registers,
+            // without the dependent byte loads of the general check
+            const uint32_t off = start & 15u;
+            const uint32_t w0 = off < 4 ? head_chunk.x : off < 8 ? head_chunk.y : off < 12 ? head_chunk.z : head_chunk.w;
+            const uint32_t w1 = off < 4 ? head_chunk.y : off < 8 ? head_chunk.z : off < 12 ? head_chunk.w : 0u;
+            const uint32_t two = __funnelshift_r(w0, w1, 8 * (off & 3u));     // bytes start, start + 1
+            if (off < 15 && start + 1 < end && (two & 0xFFu) == '[' && tk_is_numclass((int)((two >> 8) & 0xFFu))) {
+                head = TK_OK;
+                first = start + 1;
+            } else {
+                GlobalReader rd{a.bytes, end};
+                head = end > start ? tk_json_prefix(rd, start, &first, &empty) : TK_ERR_SYNTAX;
+            }
             len = (!head && empty) ? 0u : commas + 1u;
             const int status = head ? head : (len > a.max_len ? TK_ERR_TOO_LONG : TK_OK);
             a.rec_len[i] = (int32_t)len;
@@ -146,7 +182,7 @@ __global__ void __launch_bounds__(256) k_json_scan(const scan_args a) {
             a.rec_kidx[i] = (status == TK_OK && len >= a.min_size) ? 0 : -1;
             if (len) {
                 t0 = atomicAdd(a.tok_count, len);
-                if (t0 < a.tok_cap) { a.tok_pos[t0] = head ? start : first; a.tok_rec[t0] = i; }
+                if (t0 < a.tok_cap) tok[t0] = make_uint2(head ? start : first, i);
             }
             a.rec_tok[i] = t0;
         }
@@ -155,33 +191,35 @@ __global__ void __launch_bounds__(256) k_json_scan(const scan_args a) {
         if (len <= 1) continue;
         // ---- pass 2: element e (>= 1) starts right after the e-th comma
         uint32_t seen = 0;
-        for (uint32_t base = base0; base < end; base += 512) {
+        for (uint32_t k = 0, base = base0; base < end; ++k, base += 512) {
             const uint32_t pos = base + lane * 16;
-            uint32_t cm = 0;
-            if (pos < end) {
-                const uint4 v = __ldg(reinterpret_cast<const uint4*>(a.bytes + pos));
-                const uint32_t c0 = comma4(v.x), c1 = comma4(v.y), c2 = comma4(v.z), c3 = comma4(v.w);
-                if (c0 | c1 | c2 | c3) {
-                    cm = hibits_to_nibble(c0) | (hibits_to_nibble(c1) << 4) | (hibits_to_nibble(c2) << 8) |
-                         (hibits_to_nibble(c3) << 12);
-                    if (pos < start || pos + 16 > end) cm &= range16((int)start - (int)pos, (int)end - (int)pos);
-                }
-            }
-            const uint32_t cnt = __popc(cm);
-            uint32_t incl = cnt;
+            uint32_t cm;
+            if (k < SCAN_KEEP) {
+                // static indexing keeps kept_mask in registers
+                uint32_t word = 0;
 #pragma unroll
-            for (int d = 1; d < 32; d <<= 1) {
-                const uint32_t o = __shfl_up_sync(0xffffffffu, incl, d);
-                if (lane >= (uint32_t)d) incl += o;
+                for (int q = 0; q < SCAN_KEEP / 2; ++q) word = (k >> 1) == (uint32_t)q ? kept_mask[q] : word;
+                cm = (word >> (16 * (k & 1))) & 0xFFFFu;
+            } else {
+                cm = pos < end ? comma_mask16(__ldg(reinterpret_cast<const uint4*>(a.bytes + pos)), pos, start, end) : 0;
             }
-            uint32_t t = t0 + 1 + seen + incl - cnt;
+            // exclusive prefix of the per-lane comma counts: one ballot per count level
+            const uint32_t cnt = __popc(cm);
+            uint32_t before = 0, total = 0;
+            for (uint32_t level = 1;; ++level) {
+                const uint32_t has = __ballot_sync(0xffffffffu, cnt >= level);
+                if (!has) break;
+                before += __popc(has & lt_mask);
+                total += __popc(has);
+            }
+            uint32_t t = t0 + 1 + seen + before;
             while (cm) {
                 const int b = __ffs(cm) - 1;
                 cm &= cm - 1;
-                if (t < a.tok_cap) { a.tok_pos[t] = pos + b + 1; a.tok_rec[t] = i; }
+                if (t < a.tok_cap) tok[t] = make_uint2(pos + b + 1, i);
                 ++t;
             }
-            seen += __shfl_sync(0xffffffffu, incl, 31);
+            seen += total;
         }
     }
 }
@@ -198,7 +236,7 @@ extern "C" int tk_json_scan(tk_ctx* ctx, int slot, uint32_t max_len, uint32_t mi
     scan_args a;
     a.bytes = s.d.bytes; a.recs = s.d.recs; a.n = n; a.max_len = max_len; a.min_size = min_size;
     a.rec_len = s.d.rec_len; a.rec_status = s.d.rec_status; a.rec_kidx = s.d.rec_kidx; a.rec_tok = s.d.rec_tok;
-    a.tok_pos = s.d.tok_pos; a.tok_rec = s.d.tok_rec; a.tok_count = s.d.tok_count;
+    a.tok = s.d.tok_pos; a.tok_count = s.d.tok_count;
     a.tok_cap = (uint32_t)(ctx->tok_cap > 0xFFFFFFFFull ? 0xFFFFFFFFull : ctx->tok_cap);
     const uint32_t blocks = min((n + 7) / 8, 148u * 16u);
     k_json_scan<<<blocks, 256, 0, st>>>(a);
@@ -600,8 +638,7 @@ struct flat_args {
     int32_t*        rec_status;
     const uint32_t* rec_tok;
     tk_result_t*    res;
-    const uint32_t* tok_pos;
-    const uint32_t* tok_rec;
+    const uint2*    tok;          // {byte position, record} per element
     const uint32_t* tok_count;
     uint32_t        tok_cap;
     tk_plane_t      values, lengths, mask;
@@ -732,7 +769,8 @@ __global__ void __launch_bounds__(256) k_json_parse(const flat_args a) {
     const uint64_t B = a.res->batch_size;
     T* values = reinterpret_cast<T*>(a.values.base);
     for (uint32_t t = blockIdx.x * blockDim.x + threadIdx.x; t < n_tok; t += gridDim.x * blockDim.x) {
-        const uint32_t pos = a.tok_pos[t], rec = a.tok_rec[t];
+        const uint2 tk = __ldg(a.tok + t);
+        const uint32_t pos = tk.x, rec = tk.y;
         const uint32_t end = a.recs[rec + 1].start;
         GlobalReader rd{a.bytes, end};
         T v;
@@ -804,7 +842,7 @@ extern "C" int tk_json_decode(tk_ctx* ctx, int slot, int dtype, uint32_t max_len
     a.bytes = s.d.bytes; a.recs = s.d.recs; a.n = n; a.max_len = max_len; a.fixed_len = fixed_len;
     a.rec_kidx = s.d.rec_kidx; a.rec_len = s.d.rec_len; a.rec_status = s.d.rec_status;
     a.rec_tok = s.d.rec_tok; a.res = s.d.result;
-    a.tok_pos = s.d.tok_pos; a.tok_rec = s.d.tok_rec; a.tok_count = s.d.tok_count;
+    a.tok = reinterpret_cast<const uint2*>(s.d.tok_pos); a.tok_count = s.d.tok_count;
     a.tok_cap = (uint32_t)(ctx->tok_cap > 0xFFFFFFFFull ? 0xFFFFFFFFull : ctx->tok_cap);
     tk_plane_t z; z.base = nullptr; z.row_bytes = 0;
     a.values = *values;

@@ -1,0 +1,89 @@
+"""Full-size runs checked through size-independent properties (the oracle would need minutes
+at these sizes): the result must not depend on how the stream is cut into staging slots or on
+the consumer protocol; batch counts, kept counts and the final committed offsets must equal
+what the record log implies; decoding is idempotent."""
+import numpy as np
+import pytest
+import torch
+from torch.utils.data import DataLoader
+
+from torchkafka_b200 import KafkaDataset, auto_commit
+from torchkafka_b200.schema import JsonArray, RawBytes
+from torchkafka_b200.testing import stub_kafka as sk
+from torchkafka_b200.testing import synthetic as syn
+
+pytestmark = pytest.mark.gpu
+
+
+def run(log, schema, batch_size, repeat, slot_bytes, packed, producers=2):
+    consumer_cls = sk.KafkaConsumer if packed else sk.PollOnlyConsumer
+
+    class DS(KafkaDataset):
+        payload_schema = schema
+        device_slot_bytes = slot_bytes
+        device_producers = producers
+
+        @classmethod
+        def new_consumer(cls, *a, **k):
+            k.pop("enable_auto_commit", None)
+            return consumer_cls(*a, log=log, repeat=repeat, **k)
+
+    ds = DS("topic", group_id="prop")
+    sums, rows, n_batches = [], 0, 0
+    for batch in auto_commit(DataLoader(ds, batch_size=batch_size)):
+        vals = batch if isinstance(batch, torch.Tensor) else batch[0]
+        if isinstance(batch, torch.Tensor):
+            sums.append(vals.double().sum())
+        else:
+            sums.append(vals.double().sum() + batch.lengths.double().sum() * 1e-3)
+        rows += vals.shape[0]
+        n_batches += 1
+    digest = torch.stack(sums).cpu().numpy()
+    committed = dict(ds._consumer.committed_log[-1])
+    calls = len(ds._consumer.committed_log)
+    ds.close()
+    return digest, rows, n_batches, committed, calls
+
+
+def expected_positions(log, repeat):
+    per = np.bincount(log.partitions, minlength=int(log.partitions.max()) + 1)
+    return {p: int(c) * repeat for p, c in enumerate(per) if c}
+
+
+def test_cfg1_one_million_records_slot_and_protocol_invariance():
+    base = syn.make_log(1, 50000, seed=31, layout="chunked", chunk=500)
+    repeat, B = 20, 4                                  # 1,000,000 records, BASELINE config 1
+    sc = JsonArray(torch.float32, fixed_len=8)
+    a = run(base, sc, B, repeat, 8 << 20, packed=True)
+    b = run(base, sc, B, repeat, 3 << 20, packed=False, producers=1)
+    assert a[1] == b[1] == len(base) * repeat
+    assert a[2] == b[2] == len(base) * repeat // B
+    assert np.array_equal(a[0], b[0])                  # every batch identical, bit for bit
+    assert a[3] == b[3] == expected_positions(base, repeat)
+    assert a[4] == a[2] and b[4] == b[2]               # one commit per batch
+    # the same 50 000 records repeat 20 times: per-repetition digests repeat as well
+    per_rep = a[0].reshape(repeat, -1)
+    assert np.array_equal(per_rep, np.tile(per_rep[0], (repeat, 1)))
+
+
+def test_cfg2_large_filter_counts_and_idempotence():
+    base = syn.make_log(2, 20000, seed=32, layout="chunked", chunk=500)
+    repeat, B = 6, 1024                                # 120 000 records, ~320 MB of JSON
+    kept_base = int(np.sum([v.count(b",") + 1 >= 32 for v in base._byte_values]))
+    sc = JsonArray(torch.float32, max_len=256, min_size=32)
+    a = run(base, sc, B, repeat, 48 << 20, packed=True)
+    b = run(base, sc, B, repeat, 13 << 20, packed=True)
+    c = run(base, sc, B, repeat, 48 << 20, packed=True)
+    assert a[1] == b[1] == kept_base * repeat
+    assert a[2] == -(-kept_base * repeat // B)
+    assert np.array_equal(a[0], b[0]) and np.array_equal(a[0], c[0])
+    assert a[3] == b[3] == expected_positions(base, repeat)
+
+
+def test_cfg5_raw_records_commit_equals_log_positions():
+    base = syn.make_log(5, 200000, seed=33)
+    a = run(base, RawBytes((64,), torch.uint8), 256, 5, 4 << 20, packed=True)
+    assert a[1] == 1000000
+    assert a[3] == expected_positions(base, 5)
+    total = int(np.frombuffer(base.values, np.uint8).astype(np.int64).sum()) * 5
+    assert int(a[0].sum()) == total                    # checksum of checksums over all bytes

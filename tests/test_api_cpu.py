@@ -178,3 +178,26 @@ def test_schema_dataset_without_gpu_fails_loudly():
 
     with pytest.raises(RuntimeError, match="no CPU fallback"):
         next(auto_commit(DataLoader(DS("t"), batch_size=4)))
+
+
+def test_finite_stream_with_workers_does_not_kill_the_workers():
+    """with the reference a finite stream ends in 'DataLoader worker is killed by
+    signal: User defined signal 1'.  Here the run completes and every batch is delivered."""
+    base = build_log(CASES["cfg5_raw64"])
+
+    class DS(KafkaDataset):
+        @classmethod
+        def new_consumer(cls, *a, **k):
+            from torch.utils.data import get_worker_info
+            info = get_worker_info()
+            k.pop("enable_auto_commit", None)
+            sub = base.select_partitions(lambda p: p % info.num_workers == info.id)
+            return sk.KafkaConsumer(*a, log=sub, **k)           # finite: StopIteration at the end
+
+        def _process(self, record):
+            return torch.frombuffer(bytearray(record.value), dtype=torch.uint8)
+
+    loader = DataLoader(DS.placeholder(), batch_size=50, num_workers=2,
+                        worker_init_fn=DS.init_worker("topic", group_id="g"))
+    rows = sum(b.shape[0] for b in auto_commit(loader))
+    assert rows == len(base)

@@ -208,7 +208,13 @@ class KafkaDataset(IterableDataset):
                 # reference's 1.1.0 deadlock fix (CHANGELOG.md:15-17)
                 self._commit_if_required()
         if in_worker:
-            signal.signal(self._COMMIT_SIGNAL, signal.SIG_DFL)
+            # The reference restores SIG_DFL here (kafka_dataset.py:170-171); auto_commit keeps
+            # signalling the worker after its stream ended, and the default action of SIGUSR1
+            # kills it ("DataLoader worker is killed by signal").  A finished
+            # worker instead honours a pending commit request once more and then ignores further
+            # signals.
+            self._commit_if_required()
+            signal.signal(self._COMMIT_SIGNAL, signal.SIG_IGN)
 
     def _process(self, record):
         """Turn one Kafka record into a sample; return ``None`` to skip it."""

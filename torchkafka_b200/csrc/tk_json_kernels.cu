@@ -140,18 +140,27 @@ __global__ void __launch_bounds__(256) k_json_scan(const scan_args a) {
 #pragma unroll
         for (int k = 0; k < SCAN_KEEP / 2; ++k) kept_mask[k] = 0;
         uint4 head_chunk = make_uint4(0, 0, 0, 0);             // lane 0: the 16 bytes the record starts in
+        // loads are issued four at a time (predicated, no branches in between) so that each warp
+        // keeps 2 KiB in flight: the kernel is latency-bound otherwise
 #pragma unroll
-        for (int k = 0; k < SCAN_KEEP; ++k) {
-            const uint32_t pos = base0 + k * 512 + lane * 16;
-            if (base0 + k * 512 < end) {                       // warp-uniform
-                uint32_t cm = 0;
-                if (pos < end) {
-                    const uint4 v = __ldg(reinterpret_cast<const uint4*>(a.bytes + pos));
-                    if (k == 0) head_chunk = v;
-                    cm = comma_mask16(v, pos, start, end);
+        for (int g = 0; g < SCAN_KEEP; g += 4) {
+            if (base0 + g * 512 < end) {                       // warp-uniform
+                uint4 v[4];
+#pragma unroll
+                for (int j = 0; j < 4; ++j) {
+                    const uint32_t pos = base0 + (g + j) * 512 + lane * 16;
+                    v[j] = make_uint4(0, 0, 0, 0);
+                    if (pos < end) v[j] = __ldg(reinterpret_cast<const uint4*>(a.bytes + pos));
                 }
-                commas += __popc(cm);
-                kept_mask[k >> 1] |= cm << (16 * (k & 1));
+                if (g == 0) head_chunk = v[0];
+#pragma unroll
+                for (int j = 0; j < 4; ++j) {
+                    const int k = g + j;
+                    const uint32_t pos = base0 + k * 512 + lane * 16;
+                    const uint32_t cm = pos < end ? comma_mask16(v[j], pos, start, end) : 0u;
+                    commas += __popc(cm);
+                    kept_mask[k >> 1] |= cm << (16 * (k & 1));
+                }
             }
         }
         for (uint32_t pos = base0 + SCAN_KEEP * 512 + lane * 16; pos < end; pos += 512)
@@ -191,18 +200,7 @@ __global__ void __launch_bounds__(256) k_json_scan(const scan_args a) {
         if (len <= 1) continue;
         // ---- pass 2: element e (>= 1) starts right after the e-th comma
         uint32_t seen = 0;
-        for (uint32_t k = 0, base = base0; base < end; ++k, base += 512) {
-            const uint32_t pos = base + lane * 16;
-            uint32_t cm;
-            if (k < SCAN_KEEP) {
-                // static indexing keeps kept_mask in registers
-                uint32_t word = 0;
-#pragma unroll
-                for (int q = 0; q < SCAN_KEEP / 2; ++q) word = (k >> 1) == (uint32_t)q ? kept_mask[q] : word;
-                cm = (word >> (16 * (k & 1))) & 0xFFFFu;
-            } else {
-                cm = pos < end ? comma_mask16(__ldg(reinterpret_cast<const uint4*>(a.bytes + pos)), pos, start, end) : 0;
-            }
+        auto emit = [&](uint32_t cm, uint32_t pos) {
             // exclusive prefix of the per-lane comma counts: one ballot per count level
             const uint32_t cnt = __popc(cm);
             uint32_t before = 0, total = 0;
@@ -220,6 +218,16 @@ __global__ void __launch_bounds__(256) k_json_scan(const scan_args a) {
                 ++t;
             }
             seen += total;
+        };
+#pragma unroll
+        for (int k = 0; k < SCAN_KEEP; ++k) {                  // masks still in registers
+            if (base0 + k * 512 < end)
+                emit((kept_mask[k >> 1] >> (16 * (k & 1))) & 0xFFFFu, base0 + k * 512 + lane * 16);
+        }
+        for (uint32_t base = base0 + SCAN_KEEP * 512; base < end; base += 512) {
+            const uint32_t pos = base + lane * 16;
+            emit(pos < end ? comma_mask16(__ldg(reinterpret_cast<const uint4*>(a.bytes + pos)), pos, start, end) : 0u,
+                 pos);
         }
     }
 }
@@ -238,7 +246,7 @@ extern "C" int tk_json_scan(tk_ctx* ctx, int slot, uint32_t max_len, uint32_t mi
     a.rec_len = s.d.rec_len; a.rec_status = s.d.rec_status; a.rec_kidx = s.d.rec_kidx; a.rec_tok = s.d.rec_tok;
     a.tok = s.d.tok_pos; a.tok_count = s.d.tok_count;
     a.tok_cap = (uint32_t)(ctx->tok_cap > 0xFFFFFFFFull ? 0xFFFFFFFFull : ctx->tok_cap);
-    const uint32_t blocks = min((n + 7) / 8, 148u * 16u);
+    const uint32_t blocks = (n + 7) / 8;                   // one warp per record
     k_json_scan<<<blocks, 256, 0, st>>>(a);
     TK_LAUNCH_CHECK();
     return 0;

@@ -129,8 +129,11 @@ class SlotEngine:
             cores = os.cpu_count() or 1
         # several ranks on one host (torchrun) share its cores
         cores = max(1, cores // max(1, int(os.environ.get("LOCAL_WORLD_SIZE", "1"))))
-        #: threads used by the pinned-memory pack (payload memcpy)
-        self.pack_threads = int(os.environ.get("TK_PACK_THREADS", 0)) or max(1, min(8, (cores - 2) // 2))
+        #: threads used by the pinned-memory pack (payload memcpy).  Packs of different producer
+        #: threads take turns on one process-wide pool, so each pack gets all of them; two cores
+        #: are left for the producer (GIL) and the consuming thread.  Measured on the 16-core
+        #: B200 host: 7 threads 61 GB/s, 14 threads 92 GB/s (benchmarks/pack_bandwidth.py).
+        self.pack_threads = int(os.environ.get("TK_PACK_THREADS", 0)) or max(1, min(16, cores - 2))
 
     # ------------------------------------------------------------------ plumbing
     def _stream(self):

@@ -11,6 +11,7 @@
 #define PY_SSIZE_T_CLEAN
 #include <Python.h>
 #include <stdint.h>
+#include <vector>
 
 struct Sink {
     uint64_t* ptrs;
@@ -119,6 +120,67 @@ static PyObject* harvest(PyObject*, PyObject* args) {
     return r;
 }
 
+// ---------------------------------------------------------------- GIL-free fast path
+// The records of a poll() result are immutable objects (namedtuples of bytes / int) kept alive by
+// the lists we hold, so their fields can be read without the GIL -- which is what lets the thread
+// that consumes batches run Python while a producer thread chases 3 pointers per record.  Only
+// plain memory reads happen in here: no reference counting, no allocation, no error state.  The
+// first record that is not an exact (tuple-subclass, bytes value, int offset) ends the fast path;
+// the caller finishes the rest under the GIL.
+#if PY_VERSION_HEX >= 0x030C0000
+static inline bool long_to_i64_nogil(PyObject* o, int64_t* out) {
+    const PyLongObject* l = reinterpret_cast<const PyLongObject*>(o);
+    if (_PyLong_IsCompact(l)) { *out = (int64_t)_PyLong_CompactValue(l); return true; }
+    const uintptr_t tag = l->long_value.lv_tag;
+    const Py_ssize_t nd = (Py_ssize_t)(tag >> 3);
+    const int sign = (int)(tag & 3);                 // 0 positive, 1 zero, 2 negative
+    if (nd > 3) return false;
+    unsigned __int128 v = 0;
+    for (Py_ssize_t i = nd; i-- > 0;) v = (v << PyLong_SHIFT) | l->long_value.ob_digit[i];
+    if (v > (unsigned __int128)INT64_MAX) return false;
+    *out = sign == 2 ? -(int64_t)v : (int64_t)v;
+    return true;
+}
+
+// returns the number of records consumed from items[first..n); *stopped is set when the sink is
+// full (records / bytes) and *bail when a record needs the general path
+static Py_ssize_t harvest_nogil(Sink& k, PyObject** items, Py_ssize_t n, Py_ssize_t vi, Py_ssize_t oi,
+                                bool* bail) {
+    Py_ssize_t i = 0;
+    for (; i < n && k.taken < k.max_records; ++i) {
+        if (i + 16 < n) __builtin_prefetch(items[i + 16]);
+        if (i + 8 < n) {
+            PyObject* r8 = items[i + 8];
+            if (PyType_HasFeature(Py_TYPE(r8), Py_TPFLAGS_TUPLE_SUBCLASS) && Py_SIZE(r8) > vi && Py_SIZE(r8) > oi) {
+                __builtin_prefetch(reinterpret_cast<PyTupleObject*>(r8)->ob_item[vi]);
+                __builtin_prefetch(reinterpret_cast<PyTupleObject*>(r8)->ob_item[oi]);
+            }
+        }
+        PyObject* rec = items[i];
+        if (!PyType_HasFeature(Py_TYPE(rec), Py_TPFLAGS_TUPLE_SUBCLASS) || Py_SIZE(rec) <= vi || Py_SIZE(rec) <= oi) {
+            *bail = true; break;
+        }
+        PyObject* val = reinterpret_cast<PyTupleObject*>(rec)->ob_item[vi];
+        PyObject* off = reinterpret_cast<PyTupleObject*>(rec)->ob_item[oi];
+        if (!PyType_HasFeature(Py_TYPE(val), Py_TPFLAGS_BYTES_SUBCLASS) ||
+            !PyType_HasFeature(Py_TYPE(off), Py_TPFLAGS_LONG_SUBCLASS)) { *bail = true; break; }
+        int64_t o;
+        if (!long_to_i64_nogil(off, &o)) { *bail = true; break; }
+        const Py_ssize_t len = Py_SIZE(val);
+        if (k.total + (unsigned long long)len > k.max_bytes) break;
+        k.ptrs[k.taken] = (uint64_t)(uintptr_t)reinterpret_cast<PyBytesObject*>(val)->ob_sval;
+        k.lens[k.taken] = (uint32_t)len;
+        k.offs[k.taken] = o;
+        k.total += (unsigned long long)len;
+        ++k.taken;
+    }
+    return i;
+}
+#define TK_HAVE_NOGIL_HARVEST 1
+#else
+#define TK_HAVE_NOGIL_HARVEST 0
+#endif
+
 // harvest_groups(groups, dense, value_idx, offset_idx, max_records, max_bytes,
 //                ptrs_addr, lens_addr, offs_addr, parts_addr)
 //     -> (taken, total_bytes, groups_done, taken_in_last_group, keepalive_or_None)
@@ -143,25 +205,59 @@ static PyObject* harvest_groups(PyObject*, PyObject* args) {
               reinterpret_cast<int64_t*>(offs_addr), 0, max_records, 0, max_bytes, nullptr};
     const Py_ssize_t ng = PyList_GET_SIZE(groups);
     Py_ssize_t g = 0, partial = 0;
-    for (; g < ng; ++g) {
-        PyObject* pair = PyList_GET_ITEM(groups, g);
+    // under the GIL: pin every group's record sequence and read its dense partition index
+    struct Group { PyObject* seq; PyObject** items; Py_ssize_t size; long dense; };
+    std::vector<Group> gs;
+    gs.reserve((size_t)ng);
+    auto release_groups = [&]() { for (auto& x : gs) Py_DECREF(x.seq); };
+    for (Py_ssize_t q = 0; q < ng; ++q) {
+        PyObject* pair = PyList_GET_ITEM(groups, q);
         if (!PyTuple_Check(pair) || PyTuple_GET_SIZE(pair) != 2) {
             PyErr_SetString(PyExc_TypeError, "each group must be a (partition, records) pair");
-            Py_XDECREF(k.keep);
+            release_groups();
             return nullptr;
         }
-        const long d = PyLong_AsLong(PyList_GET_ITEM(dense, g));
-        if (d == -1 && PyErr_Occurred()) { Py_XDECREF(k.keep); return nullptr; }
+        const long d = PyLong_AsLong(PyList_GET_ITEM(dense, q));
+        if (d == -1 && PyErr_Occurred()) { release_groups(); return nullptr; }
         PyObject* seq = PySequence_Fast(PyTuple_GET_ITEM(pair, 1), "records must be a sequence");
-        if (!seq) { Py_XDECREF(k.keep); return nullptr; }
-        const Py_ssize_t before = k.taken;
-        const Py_ssize_t size = PySequence_Fast_GET_SIZE(seq);
-        const Py_ssize_t got = harvest_into(k, seq, vi, oi, 0);
-        Py_DECREF(seq);
-        if (got < 0) { Py_XDECREF(k.keep); return nullptr; }
-        for (Py_ssize_t j = before; j < k.taken; ++j) parts[j] = (int32_t)d;
-        if (got < size) { partial = got; break; }
+        if (!seq) { release_groups(); return nullptr; }
+        gs.push_back({seq, PySequence_Fast_ITEMS(seq), PySequence_Fast_GET_SIZE(seq), d});
     }
+    bool done = false;
+#if TK_HAVE_NOGIL_HARVEST
+    if (vi >= 0 && oi >= 0) {
+        bool bail = false;
+        Py_ssize_t bail_at = 0;
+        Py_BEGIN_ALLOW_THREADS
+        for (; g < ng; ++g) {
+            const Py_ssize_t before = k.taken;
+            const Py_ssize_t got = harvest_nogil(k, gs[g].items, gs[g].size, vi, oi, &bail);
+            for (Py_ssize_t j = before; j < k.taken; ++j) parts[j] = (int32_t)gs[g].dense;
+            if (got < gs[g].size) { partial = got; bail_at = got; break; }
+        }
+        Py_END_ALLOW_THREADS
+        if (!bail) done = true;              // all groups taken, or the sink is full
+        else {
+            // finish group g from record bail_at under the GIL (general path), then go on below
+            const Py_ssize_t before = k.taken;
+            const Py_ssize_t got = harvest_into(k, gs[g].seq, vi, oi, bail_at);
+            if (got < 0) { release_groups(); Py_XDECREF(k.keep); return nullptr; }
+            for (Py_ssize_t j = before; j < k.taken; ++j) parts[j] = (int32_t)gs[g].dense;
+            if (bail_at + got < gs[g].size) { partial = bail_at + got; done = true; }
+            else { partial = 0; ++g; }
+        }
+    }
+#endif
+    if (!done) {
+        for (; g < ng; ++g) {
+            const Py_ssize_t before = k.taken;
+            const Py_ssize_t got = harvest_into(k, gs[g].seq, vi, oi, 0);
+            if (got < 0) { release_groups(); Py_XDECREF(k.keep); return nullptr; }
+            for (Py_ssize_t j = before; j < k.taken; ++j) parts[j] = (int32_t)gs[g].dense;
+            if (got < gs[g].size) { partial = got; break; }
+        }
+    }
+    release_groups();
     PyObject* r = Py_BuildValue("(nKnnO)", k.taken, k.total, g, partial, k.keep ? k.keep : Py_None);
     Py_XDECREF(k.keep);
     return r;

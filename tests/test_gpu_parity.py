@@ -227,3 +227,40 @@ def test_live_stream_with_pauses_and_batch_iteration():
     for g, (w, _) in zip(got, want):
         assert torch.equal(g.values, w[0]) and torch.equal(g.lengths, w[1])
     ds.close()
+
+
+def test_two_decode_decompositions_agree():
+    """The flat path (comma-split segments, thread per element) and the earlier warp-per-record
+    kernel (number-run validation, shared-memory ring) are independent implementations of the
+    same contract; they must produce identical tensors, statuses and commit offsets."""
+    import ctypes as C
+    from torchkafka_b200.engine import SlotEngine
+    log = syn.make_log(2, 3000, seed=41, layout="chunked", chunk=200)
+    vals = list(log._byte_values)
+    vals[17] = b"[1, 2,, 3]"                 # one malformed record: both must flag it
+    vals[18] = b" [ 1 ,\t2.5e3 , -0 ,1e400 ] "
+    log = RecordLog(vals, log.partitions, log.offsets)
+    sc = JsonArray(torch.float32, max_len=256, min_size=32)
+    outs = []
+    for warp in (False, True):
+        eng = SlotEngine(sc, 128, slot_bytes=16 << 20, slot_records=4000, n_slots=2, device=0, n_partitions=64)
+        eng.json_decode_warp = warp
+        n, nb = eng.fill_packed(0, log.values, log.starts.astype(np.uint32), log.partitions, log.offsets)
+        eng.submit(0, n, nb)
+        out = eng.process(0, n, None, None)
+        res = eng.result(0)
+        ln, st, kx = eng.record_debug(0, n)
+        rows = 128 + res.n_kept
+        outs.append(([t[128:rows].cpu() for t in out.tensors], res, st.copy(), kx.copy()))
+        eng.close()
+    (ta, ra, sa, ka), (tb, rb, sb, kb) = outs
+    assert ra.n_kept == rb.n_kept and ra.n_closed == rb.n_closed and ra.first_error_rec == rb.first_error_rec == 17
+    assert np.array_equal(ka, kb) and np.array_equal(sa != 0, sb != 0)
+    assert np.array_equal(ra.commit, rb.commit)
+    ok_rows = torch.ones(ra.n_kept, dtype=torch.bool)
+    for x, y in zip(ta, tb):
+        assert x.shape == y.shape
+        if x.dtype.is_floating_point:
+            assert torch.equal(x.view(torch.int32)[ok_rows], y.view(torch.int32)[ok_rows])
+        else:
+            assert torch.equal(x[ok_rows], y[ok_rows])

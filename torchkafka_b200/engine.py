@@ -122,6 +122,9 @@ class SlotEngine:
                 _native.check(self.lib.tk_image_set_norm(self.ctx, schema.channels, mean, std,
                                                          self._stream()))
         self.launches = 0
+        #: use the earlier warp-per-record decode kernel (tk_json_decode_warp) instead of the flat
+        #: token-array path; kept for cross-checks and comparison runs
+        self.json_decode_warp = False
         import os
         try:
             cores = len(os.sched_getaffinity(0))
@@ -267,7 +270,7 @@ class SlotEngine:
         is_json = isinstance(sc, JsonArray)
         with torch.cuda.device(self.device), torch.cuda.stream(self.stream):
             out = self._allocate(n)
-            if timers is None:
+            if timers is None and not self.json_decode_warp:
                 job = self._job(out, prev_slot, prev_out, resident)
                 _native.check(lib.tk_process_slot(ctx, slot, C.byref(job), st))
             else:
@@ -288,7 +291,8 @@ class SlotEngine:
                 P = out.planes
                 if is_json:
                     variable = sc.fixed_len is None
-                    _native.check(lib.tk_json_decode(
+                    decode = lib.tk_json_decode_warp if self.json_decode_warp else lib.tk_json_decode
+                    _native.check(decode(
                         ctx, slot, sc.kind, sc.max_len, sc.fixed_len or 0, C.byref(P[0]),
                         C.byref(P[1]) if variable else None, C.byref(P[2]) if variable else None, st))
                 elif isinstance(sc, ImageU8):
@@ -297,7 +301,8 @@ class SlotEngine:
                 else:
                     _native.check(lib.tk_collate_raw(ctx, slot, sc.record_bytes, C.byref(P[0]), st))
                 ev1.record()
-                timers.append((ev0, ev1))
+                if timers is not None:
+                    timers.append((ev0, ev1))
                 _native.check(lib.tk_slot_fetch_result(ctx, slot, st))
             self.launches += (LAUNCHES_PER_SLOT_JSON if is_json else LAUNCHES_PER_SLOT_RAW) \
                 - (1 if prev_out is None else 0)

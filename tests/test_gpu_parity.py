@@ -264,3 +264,16 @@ def test_two_decode_decompositions_agree():
             assert torch.equal(x.view(torch.int32)[ok_rows], y.view(torch.int32)[ok_rows])
         else:
             assert torch.equal(x[ok_rows], y[ok_rows])
+
+
+def test_images_table_fallback_when_fma_is_not_exact():
+    """mean/std for which the one-FMA normalisation differs from the exact chain in one of the
+    256 inputs: the library must notice (device-side exhaustive check) and use the table kernel;
+    either way the result equals torch's `((x/255) - mean) / std -> bf16` bit for bit."""
+    log = syn.make_log(4, 20, seed=51, h=40, w=36, c=3)
+    check(log, ImageU8(40, 36, 3, mean=(0.341, 0.348, 0.804), std=(0.064, 0.085, 0.494)), 8,
+          slot_bytes=7 * 40 * 36 * 3)
+    check(log, ImageU8(40, 36, 3), 8, slot_bytes=7 * 40 * 36 * 3)          # ImageNet constants: FMA path
+    # odd shapes: single channel, width that breaks the 16-byte store alignment
+    log1 = syn.make_log(4, 9, seed=52, h=13, w=7, c=1)
+    check(log1, ImageU8(13, 7, 1, mean=(0.5,), std=(0.25,)), 4)

@@ -185,8 +185,8 @@ static int create_impl(tk_ctx* ctx) {
     TK_CUDA(cudaStreamCreateWithFlags(&ctx->copy_stream, cudaStreamNonBlocking));
     TK_CUDA(cudaMalloc(&ctx->d_state, sizeof(tk_state)));
     TK_CUDA(cudaMalloc(&ctx->d_positions, sizeof(int64_t) * ctx->n_partitions));
-    TK_CUDA(cudaMalloc(&ctx->d_image_lut, sizeof(uint16_t) * 4 * 256));
-    TK_CUDA(cudaMemset(ctx->d_image_lut, 0, sizeof(uint16_t) * 4 * 256));
+    TK_CUDA(cudaMalloc(&ctx->d_image_lut, sizeof(uint16_t) * 4 * 256 + 16));      // + a spare word
+    TK_CUDA(cudaMemset(ctx->d_image_lut, 0, sizeof(uint16_t) * 4 * 256 + 16));
     ctx->slots = new (std::nothrow) tk_slot[ctx->n_slots];
     TK_REQUIRE(ctx->slots, "out of host memory");
     memset(ctx->slots, 0, sizeof(tk_slot) * ctx->n_slots);

@@ -86,6 +86,8 @@ struct tk_ctx {
     int64_t*  d_positions;     // [n_partitions] running max(offset)+1, -1 = never seen
     uint16_t* d_image_lut;     // [4][256] bf16 bit patterns
     int       image_channels;
+    int       image_fma;       // 1: fused multiply-add reproduces the exact table for all 256 x C inputs
+    float     image_a[4], image_b[4];   // y = fma(float(x), a[c], b[c])
     tk_slot*  slots;
 };
 

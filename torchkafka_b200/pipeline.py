@@ -70,7 +70,7 @@ class _Pending:
 class IngestPipeline:
     def __init__(self, consumer, schema, batch_size: int, drop_last: bool = False,
                  slot_bytes: int = 64 << 20, n_slots: int = 3, device: Optional[int] = None,
-                 max_partitions: int = 64, poll_timeout_ms: int = 100, max_empty_polls: int = 1,  # noqa: ARG002
+                 max_partitions: int = 64, poll_timeout_ms: int = 100,
                  threaded: bool = True, commit_all_partitions: bool = False,
                  n_producers: int = 2):
         self.consumer = consumer
@@ -81,7 +81,6 @@ class IngestPipeline:
                                  n_slots=max(n_slots, 2 + (int(n_producers) if threaded else 0)),
                                  device=device, n_partitions=max_partitions)
         self.poll_timeout_ms = poll_timeout_ms
-        self.max_empty_polls = max_empty_polls
         # kafka-python ends `for record in consumer` after consumer_timeout_ms without a record
         # (default: never).  The GPU path follows the same setting; the in-memory stub
         # advertises 0 ("end of log is end of stream").

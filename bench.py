@@ -171,13 +171,18 @@ def run_device_resident(base_log, steps, warmup, device):
     torch.cuda.synchronize()
     starts = base_log.starts
 
-    def run(passes, timers):
+    def run(passes, dec_ms):
+        """One tk_process_slot call per slot pass.  The library brackets the decode kernels of
+        each slot with two CUDA events on the launching stream (tk_ctx_set_timing); a slot's
+        pair is read right before the slot is reused, n_slots passes later."""
         prev_slot, prev_out, recs, byts = None, None, 0, 0
         outs = []
         for k, (n, nb) in enumerate(passes):
             s = k % n_slots
+            if dec_ms is not None and k >= n_slots:
+                dec_ms.append(eng.decode_ms(s))
             eng.assume_resident(s, n, int(starts[n]))
-            out = eng.process(s, n, prev_slot, prev_out, resident=True, timers=timers)
+            out = eng.process(s, n, prev_slot, prev_out, resident=True)
             outs.append(out)
             if len(outs) > 2:
                 outs.pop(0)
@@ -191,18 +196,20 @@ def run_device_resident(base_log, steps, warmup, device):
     run(plan(max(warmup, 1)), None)
     torch.cuda.synchronize()
     eng.reset()
-    timers = []
+    dec_ms = []
+    eng.set_timing(True)
     launches0 = eng.launches
     e0 = torch.cuda.Event(enable_timing=True)
     e1 = torch.cuda.Event(enable_timing=True)
     passes = plan(steps)
     torch.cuda.synchronize()
     e0.record(eng.stream)            # events on the stream the kernels are launched on
-    recs, byts = run(passes, timers)
+    recs, byts = run(passes, dec_ms)
     e1.record(eng.stream)
     torch.cuda.synchronize()
     ms = e0.elapsed_time(e1)
-    dec_ms = [a.elapsed_time(b) for a, b in timers]
+    dec_ms += [eng.decode_ms(k % n_slots) for k in range(max(0, len(passes) - n_slots), len(passes))]
+    assert len(dec_ms) == len(passes)
     # sanity: last pass really produced what the plan says
     res = eng.result((len(passes) - 1) % n_slots)
     assert res.n_closed == passes[-1][1] and res.n_errors == 0, (res.n_closed, res.n_errors)
@@ -365,7 +372,11 @@ def main_reference(args):
     cores = len(os.sched_getaffinity(0))
     workers = max(1, min(cores - 1, 32))
     base = build_base_log(SLOT_BATCHES)
-    r = run_cpu_workers(base, args.steps, args.warmup, workers)
+    # a reference step is a bounded sample of whole batches: one batch when K is large, more
+    # when K is small, so that the timed region always spans >= 512 batches (every worker
+    # delivers ~30+) and the arm is measured in its steady state, not during worker start-up
+    per_step = max(1, -(-512 // max(args.steps, 1)))
+    r = run_cpu_workers(base, args.steps * per_step, max(args.warmup * per_step, 4 * workers), workers)
     value = r["records"] / r["seconds"]
     line = {
         "impl": "reference", "metric": METRIC, "value": value, "unit": "records/s",
@@ -373,9 +384,10 @@ def main_reference(args):
         "ms_per_step": 1e3 * r["seconds"] / args.steps, "higher_is_better": True, "scaling": "weak",
         "vs_baseline": None, "dtype": "f64->f32", "data": "synthetic",
         "config": {"workload": WORKLOAD, "batch": BATCH, "partitions": PARTITIONS,
-                   "num_workers": workers, "warmup_batches": r["warmup_batches"]},
+                   "num_workers": workers, "warmup_batches": r["warmup_batches"],
+                   "batches_per_step": per_step},
         "cpu_baseline": {"value": value, "unit": "records/s", "cores": workers + 1, "kind": "port",
-                         "sample": f"{args.steps} batches of {BATCH} kept records via DataLoader("
+                         "sample": f"{args.steps * per_step} batches of {BATCH} kept records via DataLoader("
                                    f"num_workers={workers}) + SIGUSR1 commits; oracle/ref_dataset.py"},
         "e2e": {"value": value, "unit": "records/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "host_cores": cores,

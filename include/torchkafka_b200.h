@@ -215,6 +215,14 @@ int tk_process_slot(tk_ctx* ctx, int slot, const tk_job_t* job, void* stream);
 int tk_compact_noalloc(const int32_t* d_keep, uint32_t n, uint32_t batch_size, uint32_t carry_in,
                        int32_t* d_kidx, tk_result_t* d_result, void* stream);
 
+/* Measurement aid (no counterpart in the reference): with timing enabled, tk_process_slot
+ * brackets the decode / collate kernels of every slot with two CUDA events on `stream`;
+ * tk_slot_decode_ms waits for the second one and returns the elapsed milliseconds.  This is
+ * how bench.py measures the dominant kernel inside the timed region without issuing the
+ * sequence kernel by kernel from the host. */
+int tk_ctx_set_timing(tk_ctx* ctx, int enabled);
+int tk_slot_decode_ms(tk_ctx* ctx, int slot, float* ms);
+
 /* ---- results ---------------------------------------------------------------- */
 /* async D2H of the slot's result block; also marks the slot's device buffers free
  * for the next tk_slot_submit once `stream` reaches this point */

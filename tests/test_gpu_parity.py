@@ -120,6 +120,38 @@ def test_adversarial_floats(dtype):
     check(log, JsonArray(dtype, max_len=8), 4)
 
 
+def test_float32_double_rounding_boundaries():
+    """float32 results are round_f32(round_f64(text)) like torch.tensor(json.loads(..)).  The
+    parse kernel takes a one-FMA shortcut away from float32 rounding boundaries and the exact
+    conversion next to them: decimal strings within a few double ulps of float32 halfway points
+    (both sides, exact ties, 16/17 digits, with and without integer part) must come out bit-exact."""
+    import random
+    from decimal import Decimal, getcontext
+    getcontext().prec = 60
+    rng = random.Random(5)
+    toks = []
+    for _ in range(6000):
+        e = rng.randint(-20, 26)
+        m = rng.getrandbits(23) | (1 << 23)
+        half = (Decimal(2 * m + 1) * Decimal(2) ** (e - 24))       # halfway between two floats
+        ulp64 = Decimal(2) ** (e - 52)
+        x = half + ulp64 * Decimal(rng.choice([0, 0, 1, -1, 2, -2, 3, -3, 5, -5, 9, -9, 40, -40])) \
+            * Decimal(rng.choice([1, 1, 0.5, 0.25, 0.75]))
+        digits = rng.choice([15, 16, 17, 17, 18, 19])
+        s = format(x, "f")
+        ip, _, fp = s.partition(".")
+        keep = max(1, digits - (len(ip.lstrip("0")) or 0))
+        fp = fp[:min(keep, 16)] or "0"
+        if len(ip.lstrip("0")) > 8:
+            continue
+        toks.append(rng.choice(["", "-"]) + ip + "." + fp)
+    vals = [("[" + ", ".join(toks[k:k + 48]) + "]").encode() for k in range(0, len(toks), 48)]
+    i = np.arange(len(vals))
+    log = RecordLog(vals, i % 4, i // 4)
+    check(log, JsonArray(torch.float32, max_len=48), 16)
+    check(log, JsonArray(torch.float64, max_len=48), 16)
+
+
 def test_random_decimal_strings_float64():
     import random
     rng = random.Random(11)

@@ -89,6 +89,8 @@ _SIGNATURES = {
     "tk_process_slot": (C.c_int, [C.c_void_p, C.c_int, _p(TkJob), C.c_void_p]),
     "tk_compact_noalloc": (C.c_int, [C.c_void_p, C.c_uint32, C.c_uint32, C.c_uint32, C.c_void_p,
                                      C.c_void_p, C.c_void_p]),
+    "tk_ctx_set_timing": (C.c_int, [C.c_void_p, C.c_int]),
+    "tk_slot_decode_ms": (C.c_int, [C.c_void_p, C.c_int, _p(C.c_float)]),
     "tk_slot_fetch_result": (C.c_int, [C.c_void_p, C.c_int, C.c_void_p]),
     "tk_slot_result": (C.c_int, [C.c_void_p, C.c_int, _p(_p(TkResult)), _p(_p(C.c_uint32)),
                                  _p(_p(C.c_uint32)), _p(_p(C.c_int64)), _p(C.c_uint32)]),

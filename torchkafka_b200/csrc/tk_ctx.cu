@@ -162,6 +162,8 @@ static void free_slot(tk_slot& s) {
     if (s.ev_h2d) cudaEventDestroy(s.ev_h2d);
     if (s.ev_free) cudaEventDestroy(s.ev_free);
     if (s.ev_result) cudaEventDestroy(s.ev_result);
+    if (s.ev_dec0) cudaEventDestroy(s.ev_dec0);
+    if (s.ev_dec1) cudaEventDestroy(s.ev_dec1);
 }
 
 extern "C" int tk_ctx_destroy(tk_ctx* ctx) {
@@ -225,6 +227,8 @@ static int create_impl(tk_ctx* ctx) {
         TK_CUDA(cudaEventCreateWithFlags(&s.ev_h2d, cudaEventDisableTiming));
         TK_CUDA(cudaEventCreateWithFlags(&s.ev_free, cudaEventDisableTiming));
         TK_CUDA(cudaEventCreateWithFlags(&s.ev_result, cudaEventDisableTiming));
+        TK_CUDA(cudaEventCreate(&s.ev_dec0));
+        TK_CUDA(cudaEventCreate(&s.ev_dec1));
     }
     return tk_ctx_reset(ctx, nullptr);
 }
@@ -235,7 +239,7 @@ extern "C" int tk_ctx_create(int device, uint64_t slot_bytes, uint32_t slot_reco
     *out = nullptr;
     TK_REQUIRE(slot_bytes > 0 && slot_bytes < (1ull << 32) - TK_BYTES_PAD,
                "slot_bytes must be in (0, 4 GiB): CSR offsets are 32-bit");
-    TK_REQUIRE(slot_records > 0 && n_slots > 0 && n_slots <= 64 && max_batches > 0 && n_partitions > 0,
+    TK_REQUIRE(slot_records > 0 && slot_records < (1u << 30) && n_slots > 0 && n_slots <= 64 && max_batches > 0 && n_partitions > 0,
                "bad context geometry");
     tk_ctx* ctx = new (std::nothrow) tk_ctx;
     TK_REQUIRE(ctx, "out of host memory");

@@ -67,6 +67,8 @@ struct tk_slot {
     cudaEvent_t  ev_h2d;      // H2D landed
     cudaEvent_t  ev_free;     // kernels finished reading the device copy
     cudaEvent_t  ev_result;   // result block is in pinned memory
+    cudaEvent_t  ev_dec0, ev_dec1;   // timing events around the decode / collate kernels (tk_ctx_set_timing)
+    bool         dec_timed;
     bool         free_recorded;
 };
 
@@ -88,6 +90,7 @@ struct tk_ctx {
     int       image_channels;
     int       image_fma;       // 1: fused multiply-add reproduces the exact table for all 256 x C inputs
     float     image_a[4], image_b[4];   // y = fma(float(x), a[c], b[c])
+    int       timing;          // tk_ctx_set_timing
     tk_slot*  slots;
 };
 

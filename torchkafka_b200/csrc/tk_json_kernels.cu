@@ -34,6 +34,11 @@ __device__ __forceinline__ uint32_t comma4(uint32_t x) {
     return ~(((y & 0x7F7F7F7Fu) + 0x7F7F7F7Fu) | y) & 0x80808080u;
 }
 
+// flags in the record field of a token entry
+#define TOK_LAST 0x80000000u     // last element of its record
+#define TOK_TAIL 0x40000000u     // ... and the record's final byte is ']'
+#define TOK_REC_MASK 0x3FFFFFFFu
+
 struct scan_args {
     const uint8_t*  bytes;
     const tk_rec_t* recs;
@@ -70,6 +75,10 @@ __global__ void __launch_bounds__(256) k_json_scan(const scan_args a) {
     for (uint32_t i = warp; i < a.n; i += nwarps) {
         const uint32_t start = a.recs[i].start, end = a.recs[i + 1].start;
         const uint32_t base0 = start & ~15u;
+        // what the last element's entry carries: the parse kernel takes its fast lane only when the
+        // record ends in ']' right behind the last number (trailing white space: scalar grammar)
+        const uint32_t last_flags =
+            TOK_LAST | ((end > start && __ldg(a.bytes + end - 1) == ']') ? TOK_TAIL : 0u);
         // ---- pass 1: comma masks (kept in registers for short records) and their count
         uint32_t commas = 0;
         uint32_t kept_mask[SCAN_KEEP / 2];
@@ -127,7 +136,7 @@ __global__ void __launch_bounds__(256) k_json_scan(const scan_args a) {
             a.rec_kidx[i] = (status == TK_OK && len >= a.min_size) ? 0 : -1;
             if (len) {
                 t0 = atomicAdd(a.tok_count, len);
-                if (t0 < a.tok_cap) tok[t0] = make_uint2(head ? start : first, i);
+                if (t0 < a.tok_cap) tok[t0] = make_uint2(head ? start : first, i | (len == 1 ? last_flags : 0u));
             }
             a.rec_tok[i] = t0;
         }
@@ -136,6 +145,7 @@ __global__ void __launch_bounds__(256) k_json_scan(const scan_args a) {
         if (len <= 1) continue;
         // ---- pass 2: element e (>= 1) starts right after the e-th comma
         uint32_t seen = 0;
+        const uint32_t t_last = t0 + len - 1;
         auto emit = [&](uint32_t cm, uint32_t pos) {
             // exclusive prefix of the per-lane comma counts: one ballot per count level
             const uint32_t cnt = __popc(cm);
@@ -150,7 +160,7 @@ __global__ void __launch_bounds__(256) k_json_scan(const scan_args a) {
             while (cm) {
                 const int b = __ffs(cm) - 1;
                 cm &= cm - 1;
-                if (t < a.tok_cap) tok[t] = make_uint2(pos + b + 1, i);
+                if (t < a.tok_cap) tok[t] = make_uint2(pos + b + 1, i | (t == t_last ? last_flags : 0u));
                 ++t;
             }
             seen += total;
@@ -259,109 +269,217 @@ __global__ void __launch_bounds__(256) k_json_rows(const flat_args a) {
     }
 }
 
-// unaligned 8-byte window out of global memory (L1-resident: neighbouring threads read
-// neighbouring tokens)
-__device__ __forceinline__ Window8 global_load8(const uint8_t* bytes, uint32_t pos) {
-    const uint32_t* w32 = reinterpret_cast<const uint32_t*>(bytes) + (pos >> 2);
-    const uint32_t w0 = __ldg(w32), w1 = __ldg(w32 + 1), w2 = __ldg(w32 + 2);
-    const uint32_t sh = (pos & 3u) * 8u;
-    Window8 w;
-    w.lo = __funnelshift_r(w0, w1, sh);
-    w.hi = __funnelshift_r(w1, w2, sh);
-    return w;
+// ---- per-block lookup tables of the parse kernel.  Shared memory, not __constant__: the index
+// differs from lane to lane (number of fraction digits), which a constant-bank read serialises.
+struct parse_tables {
+    ulonglong2 pow5[20];     // 128-bit normalised 5^-k (k = 0..19): rows 342-k of the Eisel-Lemire table
+    uint64_t   pow10w[17];   // 10^k, k = 0..16
+    double     inv10[17];    // 10^-k correctly rounded, k = 0..16
+    uint32_t   pow10[9];     // 10^m for the digit-group accumulation  F = g1 * 10^m + g2
+};
+static __device__ const double g_inv10[17] = {1e0, 1e-1, 1e-2, 1e-3, 1e-4, 1e-5, 1e-6, 1e-7, 1e-8,
+                                              1e-9, 1e-10, 1e-11, 1e-12, 1e-13, 1e-14, 1e-15, 1e-16};
+static __device__ const uint64_t g_pow10w[17] = {
+    1ull, 10ull, 100ull, 1000ull, 10000ull, 100000ull, 1000000ull, 10000000ull, 100000000ull,
+    1000000000ull, 10000000000ull, 100000000000ull, 1000000000000ull, 10000000000000ull,
+    100000000000000ull, 1000000000000000ull, 10000000000000000ull};
+
+__device__ __forceinline__ void parse_tables_init(parse_tables& tb) {
+    const uint32_t i = threadIdx.x;
+    if (i < 20) tb.pow5[i] = make_ulonglong2(TK_POW5_TABLE[342 - i][0], TK_POW5_TABLE[342 - i][1]);
+    else if (i >= 32 && i < 49) { tb.pow10w[i - 32] = g_pow10w[i - 32]; tb.inv10[i - 32] = g_inv10[i - 32]; }
+    else if (i >= 64 && i < 73) tb.pow10[i - 64] = c_pow10[i - 64];
+    __syncthreads();
 }
 
-// fast_token24 for the flat path: bytes come from global memory, one leading space is skipped,
-// and the separator that ends the segment must simply be ','.
-__device__ __forceinline__ bool flat_token24(const uint8_t* bytes, uint32_t pos, uint32_t end, tk_token* out) {
-    if (pos >= end) return false;
-    if (bytes[pos] == ' ') ++pos;
-    if (pos >= end) return false;
-    const uint32_t avail = end - pos;
-    const uint32_t* w32 = reinterpret_cast<const uint32_t*>(bytes) + (pos >> 2);
-    const uint32_t sh = (pos & 3u) * 8u;
-    uint32_t a[7];
+// Eisel-Lemire for  w * 10^-k,  w != 0,  0 <= k <= 19.  Same arithmetic as tk_eisel_lemire
+// (tk_number.cuh) with the arms that cannot be reached here removed: 1 <= w < 2^64 and
+// 10^-19 <= 10^-k <= 1 keep the result a normal double, far from overflow and underflow.
+__device__ __forceinline__ uint64_t el_small_neg_exp(uint64_t w, uint32_t k, const ulonglong2* pow5) {
+    const int lz = __clzll((long long)w);
+    w <<= lz;
+    const ulonglong2 p = pow5[k];
+    uint64_t hi = __umul64hi(w, p.x), lo = w * p.x;
+    if ((hi & 0x1FFu) == 0x1FFu) {                              // 55 bits not settled: second product
+        const uint64_t second = __umul64hi(w, p.y);
+        lo += second;
+        if (second > lo) ++hi;
+    }
+    const uint32_t upperbit = (uint32_t)(hi >> 63);
+    const uint32_t shift = upperbit + 9u;                      // 64 - 52 - 3
+    uint64_t mant = hi >> shift;
+    // exactly halfway between two doubles: only when 5^k fits 64 bits (k <= 4 on this side)
+    if (k <= 4u && lo <= 1u && (mant & 3u) == 1u && (mant << shift) == hi) mant &= ~1ull;
+    mant = (mant + (mant & 1u)) >> 1;                           // 2^52 <= mant <= 2^53
+    // floor(log2(10^-k)) + 63 + 1023, then the implicit bit of mant carries into the exponent
+    // (and a mantissa that rounded up to 2^53 carries once more)
+    const int32_t power2 = ((-(int32_t)(217706u * k)) >> 16) + 63 + 1023 + (int32_t)upperbit - lz;
+    return ((uint64_t)(uint32_t)(power2 - 1) << 52) + mant;
+}
+
+// Fast lane of the parse kernel.  Accepts exactly
+//     [' '] ['-'] d{1,8} ['.' d{1,16}]        at most 19 digits, no leading zero,
+// ending at byte `stop` (the ',' the scan found, or the record's final ']'), which is what
+// json.dumps writes for every int below 10^8 and every float without exponent.  Everything
+// else (exponents, other white space, long literals, specials, garbage) returns false and is
+// handled -- or rejected -- by the scalar grammar.  Out: I = the integer digits, F = the L2
+// digits after the point (as integers), neg.
+__device__ __forceinline__ bool fast_number(const uint8_t* bytes, uint32_t pos, uint32_t stop,
+                                            const uint32_t* pow10, uint32_t* I_out, uint64_t* F_out,
+                                            uint32_t* L2_out, uint32_t* neg_out) {
+    // 28 bytes from the aligned word the token starts in (the slot buffer is padded: tk_internal.h)
+    const uint32_t* w32 = reinterpret_cast<const uint32_t*>(bytes + (pos & ~3u));
+    uint32_t r[7];
 #pragma unroll
-    for (int k = 0; k < 7; ++k) a[k] = __ldg(w32 + k);
-    uint32_t W[6];
+    for (int k = 0; k < 7; ++k) r[k] = __ldg(w32 + k);
+    uint32_t sh = (pos & 3u) * 8u;
+    const uint32_t sp = ((r[0] >> sh) & 0xFFu) == ' ' ? 1u : 0u;      // json.dumps: ", "
+    sh += 8u * sp;                                                    // 0..32: clamped funnel shift
+    pos += sp;
+    uint32_t W[6];                                                    // 24 bytes of token text
 #pragma unroll
-    for (int k = 0; k < 6; ++k) W[k] = __funnelshift_r(a[k], a[k + 1], sh);
-    uint32_t nd = 0xFF000000u;
+    for (int k = 0; k < 6; ++k) W[k] = __funnelshift_rc(r[k], r[k + 1], sh);
+    uint32_t nd = 0xFF000000u;                                        // bit i: byte i is not a digit
 #pragma unroll
     for (int k = 0; k < 6; ++k) {
         const uint32_t u = W[k] ^ 0x30303030u;
         const uint32_t t = (imad(u & 0x7F7F7F7Fu, 1u, 0x76767676u) | u) & 0x80808080u;
         nd = imad(hibits_to_nibble(t), 1u << (4 * k), nd);
     }
-    if (avail < 24) nd |= 0xFFFFFFFFu << avail;
     const uint32_t neg = (W[0] & 0xFFu) == '-' ? 1u : 0u;
-    const uint32_t p = neg;
-    const uint32_t L1 = __ffs(nd >> p) - 1;
-    if (L1 == 0 || L1 > 8) return false;
-    const Window8 wi = {__funnelshift_r(W[0], W[1], 8 * p), __funnelshift_r(W[1], W[2], 8 * p)};
+    const uint32_t L1 = __ffs(nd >> neg) - 1;                         // integer digits
+    if (L1 - 1u > 7u) return false;
+    const Window8 wi = {__funnelshift_r(W[0], W[1], 8 * neg), __funnelshift_r(W[1], W[2], 8 * neg)};
     if (L1 > 1 && (wi.lo & 0xFFu) == '0') return false;
-    const uint32_t tpos = p + L1;
-    const uint32_t tword = tpos < 4 ? W[0] : (tpos < 8 ? W[1] : W[2]);
-    const uint32_t tc = (tword >> (8 * (tpos & 3u))) & 0xFFu;
+    const uint32_t tpos = neg + L1;                                   // 1..9: byte after the integer part
+    const uint32_t tc = (tpos < 8 ? __byte_perm(W[0], W[1], tpos) : __byte_perm(W[2], 0u, tpos - 8u)) & 0xFFu;
+    const uint32_t I = parse_upto8(wi, L1);
+    uint64_t F = 0;
     uint32_t L2 = 0, endp = tpos;
-    uint64_t w = parse_upto8(wi, L1);
     if (tc == '.') {
         const uint32_t q0 = tpos + 1;
-        L2 = __ffs(nd >> q0) - 1;
-        if (L2 == 0 || L2 > 16 || L1 + L2 > 19) return false;
-        endp = q0 + L2;
-        if (endp > 23) return false;
-        const uint32_t m0 = L2 < 8 ? L2 : 8, m1 = L2 - m0;
-        w = w * c_pow10[m0] + parse_upto8(global_load8(bytes, pos + q0), m0);
-        if (m1) w = w * c_pow10[m1] + parse_upto8(global_load8(bytes, pos + q0 + 8), m1);
+        L2 = __ffs(nd >> q0) - 1;                                     // fraction digits
+        if (L2 - 1u > 15u || L1 + L2 > 19u) return false;
+        endp = q0 + L2;                                               // <= 21: inside the 24 bytes
+        // the fraction as two 8-byte windows, re-read at its own alignment (L1 hits)
+        const uint32_t fpos = pos + q0;
+        const uint32_t* f32 = reinterpret_cast<const uint32_t*>(bytes + (fpos & ~3u));
+        uint32_t f[5];
+#pragma unroll
+        for (int k = 0; k < 5; ++k) f[k] = __ldg(f32 + k);
+        const uint32_t fsh = (fpos & 3u) * 8u;
+        const Window8 x0 = {__funnelshift_r(f[0], f[1], fsh), __funnelshift_r(f[1], f[2], fsh)};
+        const uint32_t m0 = min(L2, 8u), m1 = L2 - m0;
+        const uint32_t g1 = parse_upto8(x0, m0);
+        F = g1;
+        if (m1) {
+            const Window8 x1 = {__funnelshift_r(f[2], f[3], fsh), __funnelshift_r(f[3], f[4], fsh)};
+            F = (uint64_t)g1 * pow10[m1] + parse_upto8(x1, m1);
+        }
     }
-    if (endp >= avail) return false;
-    {
-        // the segment ends at the next ',' -- or, for the last element, at the closing ']' that is
-        // also the last byte of the record; anything else (ws, exponent, garbage): general path
-        const uint32_t g = bytes[pos + endp];
-        if (g != ',' && !(g == ']' && endp + 1 == avail)) return false;
-    }
-    tk_token t;
-    t.w = w; t.q = -(int32_t)L2; t.end = pos + endp; t.dig_begin = pos + p; t.exp10 = 0;
-    t.neg = (uint8_t)neg; t.is_int = L2 == 0; t.truncated = 0; t.special = 0; t.err = TK_OK;
-    t.nsig = (int32_t)(L1 + L2); t.frac_digits = (int32_t)L2;
-    *out = t;
+    if (pos + endp != stop) return false;
+    *I_out = I; *F_out = F; *L2_out = L2; *neg_out = neg;
     return true;
 }
 
+// Token entry written by k_json_scan: .x = byte position of the element, .y = record index with
+// TOK_LAST on the record's last element and TOK_TAIL when the record's final byte is ']'.
 template <int KIND>
 __global__ void __launch_bounds__(256) k_json_parse(const flat_args a) {
     typedef typename tk_elem<KIND>::type T;
+    __shared__ parse_tables tb;
+    parse_tables_init(tb);
     const uint32_t n_tok = min(*a.tok_count, a.tok_cap);
-    const uint64_t B = a.res->batch_size;
+    const uint32_t B = a.res->batch_size;
     T* values = reinterpret_cast<T*>(a.values.base);
-    for (uint32_t t = blockIdx.x * blockDim.x + threadIdx.x; t < n_tok; t += gridDim.x * blockDim.x) {
-        const uint2 tk = __ldg(a.tok + t);
-        const uint32_t pos = tk.x, rec = tk.y;
+    // Persistent grid, software-pipelined two elements deep: the token entry of iteration i + 2
+    // is requested and the text of element i + 1 is prefetched into L1 while element i is parsed,
+    // so neither of the two dependent DRAM round trips (entry -> text) is waited for.
+    const uint32_t stride = gridDim.x * blockDim.x;
+    uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
+    uint2 tk = make_uint2(0, 0), tk1 = make_uint2(0, 0);
+    uint32_t next_pos = 0, next_pos1 = 0;
+    if (t < n_tok) { tk = __ldg(a.tok + t); next_pos = __ldg(&a.tok[t + 1].x); }   // one spare entry behind the array
+    if (t + stride < n_tok) { tk1 = __ldg(a.tok + t + stride); next_pos1 = __ldg(&a.tok[t + stride + 1].x); }
+    uint2 tk2 = make_uint2(0, 0);
+    uint32_t next_pos2 = 0;
+    for (; t < n_tok; t += stride, tk = tk1, next_pos = next_pos1, tk1 = tk2, next_pos1 = next_pos2) {
+        {
+            const uint32_t t2 = t + 2 * stride;
+            const uint8_t* ahead = a.bytes + tk1.x;
+            asm volatile("prefetch.global.L1 [%0];" ::"l"(ahead));
+            asm volatile("prefetch.global.L1 [%0];" ::"l"(ahead + 27));
+            if (t2 < n_tok) { tk2 = __ldg(a.tok + t2); next_pos2 = __ldg(&a.tok[t2 + 1].x); }
+        }
+        const uint32_t pos = tk.x, rec = tk.y & TOK_REC_MASK, flags = tk.y & ~TOK_REC_MASK;
         const uint32_t end = a.recs[rec + 1].start;
-        GlobalReader rd{a.bytes, end};
+        const int32_t kidx = a.rec_kidx[rec];
+        const uint32_t e = t - a.rec_tok[rec];                   // element index inside the record
+        // the element ends at the next ',' -- or, for the last one, at the ']' that closes the record
+        const uint32_t stop = (flags ? end : next_pos) - 1u;
         T v;
-        int st;
-        tk_token tok;
-        if (flat_token24(a.bytes, pos, end, &tok)) {
-            if (KIND == TK_F32 || KIND == TK_F64) {
-                double d;
-                st = tk_token_to_f64(rd, tok, &d);
-                v = (T)d;
+        int st = TK_OK;
+        uint64_t F;
+        uint32_t I, L2, neg;
+        bool fast = flags != TOK_LAST && fast_number(a.bytes, pos, stop, tb.pow10, &I, &F, &L2, &neg);
+        if (fast) {
+            // torch.tensor(json.loads(..)): an int literal is a Python int ("-0" is +0.0), a float
+            // literal keeps its sign ("-0.0" is -0.0)
+            const bool minus = neg && (I | L2 | (uint32_t)F | (uint32_t)(F >> 32));
+            if (KIND == TK_F32) {
+                // The reference rounds twice: text -> double (json.loads), double -> float
+                // (torch.tensor).  d = I + F * 10^-L2 in one fused multiply-add is within 2.5 ulp
+                // (double) of the exact value x: F -> double and the rounded 10^-L2 contribute a
+                // relative 2^-52 of the fraction (< 1), the final rounding half an ulp.  The
+                // correctly rounded double y is within 3.5 ulp of d, so unless a float rounding
+                // boundary (low 29 mantissa bits = 0x10000000) lies within 8 ulp of d, float(d)
+                // == float(y) bit for bit.  Otherwise (2^-25 of the inputs): exact conversion.
+                double d = (double)I;
+                if (L2) d = fma((double)F, tb.inv10[L2], d);
+                const uint32_t low = (uint32_t)__double_as_longlong(d) & 0x1FFFFFFFu;
+                if (low - (0x10000000u - 8u) <= 16u) {
+                    const uint64_t w = (uint64_t)I * tb.pow10w[L2] + F;
+                    d = __longlong_as_double((long long)(w ? el_small_neg_exp(w, L2, tb.pow5) : 0ull));
+                }
+                const float f = (float)d;
+                v = (T)(minus ? -f : f);
+            } else if (KIND == TK_F64) {
+                const uint64_t w = (uint64_t)I * tb.pow10w[L2] + F;
+                uint64_t bits = w ? el_small_neg_exp(w, L2, tb.pow5) : 0ull;
+                if (minus) bits |= 0x8000000000000000ull;
+                v = (T)__longlong_as_double((long long)bits);
+            } else if (L2 == 0) {
+                v = (T)(neg ? -(int32_t)I : (int32_t)I);         // < 10^8: fits every integer target
             } else {
-                int64_t x = 0;
-                st = tk_token_to_i64(rd, tok, KIND == TK_I32 ? 32 : 64, &x);
-                v = (T)x;
+                fast = false;                                    // float literal, integer target
             }
-        } else {
+        }
+        if (!fast) {
+            GlobalReader rd{a.bytes, end};
             st = tk_json_element_flat<KIND>(rd, pos, &v);
         }
         if (st) { flag_record(a.rec_status, a.res, rec, st); continue; }
-        const int32_t kidx = a.rec_kidx[rec];
-        const uint32_t e = t - a.rec_tok[rec];               // element index inside the record
-        if (kidx >= 0 && e < a.max_len) values[(B + (uint32_t)kidx) * a.max_len + e] = v;
+        if (kidx >= 0 && e < a.max_len) values[(uint64_t)(B + (uint32_t)kidx) * a.max_len + e] = v;
     }
+}
+
+// one wave of resident blocks (no tail wave): SMs x blocks per SM of the kernel, asked once
+static uint32_t parse_grid(int dtype) {
+    static uint32_t cached[4] = {0, 0, 0, 0};
+    const int k = dtype - TK_DTYPE_F32;
+    if (!cached[k]) {
+        int per_sm = 0, sms = 0, dev = 0;
+        const void* fn = k == 0 ? (const void*)k_json_parse<TK_F32> : k == 1 ? (const void*)k_json_parse<TK_F64>
+                       : k == 2 ? (const void*)k_json_parse<TK_I32> : (const void*)k_json_parse<TK_I64>;
+        if (cudaGetDevice(&dev) != cudaSuccess ||
+            cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess ||
+            cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, fn, 256, 0) != cudaSuccess || per_sm < 1 || sms < 1) {
+            cudaGetLastError();
+            per_sm = 6; sms = 148;
+        }
+        cached[k] = (uint32_t)(per_sm * sms);
+    }
+    return cached[k];
 }
 
 extern "C" int tk_json_decode(tk_ctx* ctx, int slot, int dtype, uint32_t max_len, uint32_t fixed_len,
@@ -393,7 +511,7 @@ extern "C" int tk_json_decode(tk_ctx* ctx, int slot, int dtype, uint32_t max_len
     // the element count lives on the device; size the grid for the worst case this slot allows
     // (an element needs two bytes) and let surplus blocks exit at once
     const uint64_t max_tok = (uint64_t)s.n_bytes / 2 + n;
-    const uint32_t pblocks = (uint32_t)min((max_tok + 255) / 256, (uint64_t)148 * 32);
+    const uint32_t pblocks = (uint32_t)min((max_tok + 255) / 256, (uint64_t)parse_grid(dtype));
     switch (dtype) {
         case TK_DTYPE_F32: k_json_parse<TK_F32><<<pblocks, 256, 0, st>>>(a); break;
         case TK_DTYPE_F64: k_json_parse<TK_F64><<<pblocks, 256, 0, st>>>(a); break;

@@ -20,6 +20,9 @@ extern "C" int tk_process_slot(tk_ctx* ctx, int slot, const tk_job_t* job, void*
     if (rc) return rc;
     rc = tk_compact(ctx, slot, job->batch_size, stream); if (rc) return rc;
     rc = tk_commit_offsets(ctx, slot, stream); if (rc) return rc;
+    tk_slot& s = ctx->slots[slot];
+    s.dec_timed = false;
+    if (ctx->timing) TK_CUDA(cudaEventRecord(s.ev_dec0, (cudaStream_t)stream));
     switch (job->schema) {
         case TK_SCHEMA_JSON:
             rc = tk_json_decode(ctx, slot, job->dtype, job->max_len, job->fixed_len, &job->cur[0],
@@ -37,5 +40,22 @@ extern "C" int tk_process_slot(tk_ctx* ctx, int slot, const tk_job_t* job, void*
             TK_REQUIRE(false, "unknown schema %d", job->schema);
     }
     if (rc) return rc;
+    if (ctx->timing) { TK_CUDA(cudaEventRecord(s.ev_dec1, (cudaStream_t)stream)); s.dec_timed = true; }
     return tk_slot_fetch_result(ctx, slot, stream);
+}
+
+extern "C" int tk_ctx_set_timing(tk_ctx* ctx, int enabled) {
+    TK_REQUIRE(ctx, "null context");
+    ctx->timing = enabled ? 1 : 0;
+    return 0;
+}
+
+extern "C" int tk_slot_decode_ms(tk_ctx* ctx, int slot, float* ms) {
+    TK_ENTER(ctx, slot);
+    TK_REQUIRE(ms, "ms is null");
+    tk_slot& s = ctx->slots[slot];
+    TK_REQUIRE(s.dec_timed, "slot %d was not processed with timing enabled", slot);
+    TK_CUDA(cudaEventSynchronize(s.ev_dec1));
+    TK_CUDA(cudaEventElapsedTime(ms, s.ev_dec0, s.ev_dec1));
+    return 0;
 }

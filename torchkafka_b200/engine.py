@@ -310,6 +310,16 @@ class SlotEngine:
             out.done.record(self.stream)
         return out
 
+    def set_timing(self, enabled: bool):
+        """Bracket the decode / collate kernels of every following ``process`` call with CUDA
+        events inside the library (``decode_ms`` reads them)."""
+        _native.check(self.lib.tk_ctx_set_timing(self.ctx, 1 if enabled else 0))
+
+    def decode_ms(self, slot: int) -> float:
+        ms = C.c_float()
+        _native.check(self.lib.tk_slot_decode_ms(self.ctx, slot, C.byref(ms)))
+        return float(ms.value)
+
     def publish(self, out: "SlotOutput"):
         """Make the slot's tensors safe to use on the caller's current stream."""
         cur = torch.cuda.current_stream(self.device)

@@ -13,8 +13,8 @@ passes covering exactly K batches.
     e2e     the same metric through the public API (auto_commit(DataLoader(dataset))) from
             host ConsumerRecord objects: poll -> pack into pinned memory -> H2D -> kernels ->
             result D2H, plus a D2H read of each batch's checksum
-    roofline  dominant kernel (k_json_parse, timed together with the small k_json_rows that precedes
-              it inside tk_json_decode) against the measured HBM copy bandwidth
+    roofline  dominant kernel (k_json_parse: pad/length/mask rows + thread-per-element parse,
+              the one kernel of tk_json_decode) against the measured HBM copy bandwidth
     cpu_baseline  the oracle (reference algorithm: json.loads + torch.tensor + pad collate)
                   timed on this box's host cores on a bounded sample
 
@@ -489,7 +489,7 @@ def main_gpu(args):
             "gpu_launches": dev["launches"],
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
                          "frac": achieved / peak, "traffic": traffic,
-                         "kernel": "tk_json_decode = k_json_parse<f32> (thread per element; dominant) + k_json_rows",
+                         "kernel": "tk_json_decode = k_json_parse<f32> (thread per element parse + pad/length/mask rows, one kernel)",
                          "share_of_step": dev["decode_ms_total"] / dev["ms"],
                          "peak_source": peak_src, "launches_timed": dev["decode_launches"]},
             "clocks": clocks,

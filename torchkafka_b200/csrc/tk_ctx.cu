@@ -266,7 +266,9 @@ int tk_ensure_token_arrays(tk_ctx* ctx) {
     for (int i = 0; i < ctx->n_slots; ++i) {
         tk_slot& s = ctx->slots[i];
         TK_CUDA(cudaMalloc(&s.d.tok_pos, sizeof(uint32_t) * 2 * cap));       // uint2 {position, record}
-        TK_CUDA(cudaMalloc(&s.d.tok_count, sizeof(uint32_t)));
+        TK_CUDA(cudaMalloc(&s.d.tok_count, 2 * sizeof(uint32_t)));
+        TK_CUDA(cudaMemset(s.d.tok_count, 0, 2 * sizeof(uint32_t)));
+        s.tok_use = 0;
     }
     ctx->tok_cap = cap;
     return 0;

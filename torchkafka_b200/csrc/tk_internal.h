@@ -43,7 +43,8 @@ struct tk_slot_dev {
     unsigned long long* blk_sum;   // per-tile (kept << 40 | elements) for the compaction scan
     uint32_t*    rec_tok;      // [slot_records] index of each record's first element in the token array
     uint32_t*    tok_pos;      // [tok_cap] token array of the flat decode path: uint2 {byte position, record}
-    uint32_t*    tok_count;    // elements emitted so far (token array allocation cursor)
+    uint32_t*    tok_count;    // [2] elements emitted so far (token array allocation cursor): two
+                               // counters used alternately, each scan zeroes the one of the next
     uint8_t*     block;        // one allocation: header | batch_end | batch_lmax | commit
     tk_result_t* result;       // header
     uint32_t*    batch_end;    // [max_batches + 1]
@@ -69,6 +70,7 @@ struct tk_slot {
     cudaEvent_t  ev_result;   // result block is in pinned memory
     cudaEvent_t  ev_dec0, ev_dec1;   // timing events around the decode / collate kernels (tk_ctx_set_timing)
     bool         dec_timed;
+    uint32_t     tok_use;     // tk_json_scan calls on this slot: selects the token counter
     bool         free_recorded;
 };
 
@@ -108,6 +110,36 @@ static inline int tk_check_slot(tk_ctx* ctx, int slot) {
     } while (0)
 
 #define TK_LAUNCH_CHECK() TK_CUDA(cudaGetLastError())
+
+// Programmatic dependent launch (sm_90+).  The kernels of a slot form a chain on one stream, each
+// a few microseconds to a few tens of microseconds long, so the launch latency between them is
+// a visible share of the slot.  Every kernel of the chain
+//   - calls tk_pdl_launch_dependents() first: the next kernel of the stream may be scheduled (its
+//     blocks become resident, read their parameters, run any prologue that touches no data of
+//     earlier kernels) as soon as every block of this one has started;
+//   - calls tk_pdl_wait() before its first access to global memory: returns once every earlier
+//     kernel of the chain has completed and flushed its writes (transitively: the predecessor
+//     itself only completes after its own wait).
+// Both are no-ops in a kernel launched without the attribute.
+#if defined(__CUDACC__)
+__device__ __forceinline__ void tk_pdl_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;"); }
+__device__ __forceinline__ void tk_pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+
+#define TK_LAUNCH_PDL(kernel, grid, block, strm__, ...)                                         \
+    do {                                                                                        \
+        cudaLaunchConfig_t cfg__ = {};                                                          \
+        cfg__.gridDim = dim3(grid);                                                             \
+        cfg__.blockDim = dim3(block);                                                           \
+        cfg__.dynamicSmemBytes = 0;                                                             \
+        cfg__.stream = (strm__);                                                                \
+        cudaLaunchAttribute attr__[1];                                                          \
+        attr__[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;                      \
+        attr__[0].val.programmaticStreamSerializationAllowed = 1;                               \
+        cfg__.attrs = attr__;                                                                   \
+        cfg__.numAttrs = 1;                                                                     \
+        TK_CUDA(cudaLaunchKernelEx(&cfg__, kernel, __VA_ARGS__));                               \
+    } while (0)
+#endif
 
 int tk_ensure_token_arrays(tk_ctx* ctx);
 

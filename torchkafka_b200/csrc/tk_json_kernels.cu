@@ -49,6 +49,7 @@ struct scan_args {
     uint32_t*       rec_tok;
     uint32_t*       tok;          // uint2 {byte position, record} per element
     uint32_t*       tok_count;
+    uint32_t*       tok_count_next;   // counter of the slot's next scan: zeroed here
     uint32_t        tok_cap;
 };
 
@@ -67,6 +68,9 @@ __device__ __forceinline__ uint32_t comma_mask16(const uint4 v, uint32_t pos, ui
 #define SCAN_KEEP 12     // 512-byte steps whose comma masks stay in registers between the passes
 
 __global__ void __launch_bounds__(256) k_json_scan(const scan_args a) {
+    tk_pdl_launch_dependents();
+    tk_pdl_wait();
+    if (blockIdx.x == 0 && threadIdx.x == 0) *a.tok_count_next = 0;
     const uint32_t lane = threadIdx.x & 31;
     const uint32_t lt_mask = (1u << lane) - 1u;
     const uint32_t warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
@@ -185,25 +189,26 @@ extern "C" int tk_json_scan(tk_ctx* ctx, int slot, uint32_t max_len, uint32_t mi
     int rc = tk_ensure_token_arrays(ctx);
     if (rc) return rc;
     cudaStream_t st = (cudaStream_t)stream;
-    TK_CUDA(cudaMemsetAsync(s.d.tok_count, 0, sizeof(uint32_t), st));
     if (!n) return 0;
     scan_args a;
     a.bytes = s.d.bytes; a.recs = s.d.recs; a.n = n; a.max_len = max_len; a.min_size = min_size;
     a.rec_len = s.d.rec_len; a.rec_status = s.d.rec_status; a.rec_kidx = s.d.rec_kidx; a.rec_tok = s.d.rec_tok;
-    a.tok = s.d.tok_pos; a.tok_count = s.d.tok_count;
+    // the counter of this use was zeroed by the previous scan of the slot (or at allocation)
+    s.tok_use++;
+    a.tok = s.d.tok_pos; a.tok_count = s.d.tok_count + (s.tok_use & 1u); a.tok_count_next = s.d.tok_count + ((s.tok_use + 1) & 1u);
     a.tok_cap = (uint32_t)(ctx->tok_cap > 0xFFFFFFFFull ? 0xFFFFFFFFull : ctx->tok_cap);
     const uint32_t blocks = (n + 7) / 8;                   // one warp per record
-    k_json_scan<<<blocks, 256, 0, st>>>(a);
-    TK_LAUNCH_CHECK();
+    TK_LAUNCH_PDL(k_json_scan, blocks, 256, st, a);
     return 0;
 }
 
 // ================================================================ flat decode path
 // After k_json_scan (token array) and the compaction (row of every kept record):
-//   k_json_rows      (warp per record) reports the records the scan rejected, checks fixed_len,
-//                    and writes pad, length and mask of every kept record's row;
-//   k_json_parse<T>  (thread per element) parses one token each: perfectly balanced, every
-//                    lane busy whatever the record lengths are, no shared memory.
+// k_json_parse<T>, one persistent grid, two parts per block:
+//   rows   (warp per record) reports the records the scan rejected, checks fixed_len, and writes
+//          pad, length and mask of every kept record's row;
+//   parse  (thread per element) parses one token each: perfectly balanced, every lane busy
+//          whatever the record lengths are.
 // The grammar is checked with the comma-split decomposition (tk_json_gap_flat in tk_json.cuh).
 struct flat_args {
     const uint8_t*  bytes;
@@ -226,44 +231,79 @@ __device__ __forceinline__ void flag_record(int32_t* rec_status, tk_result_t* re
     if (atomicCAS(&rec_status[rec], 0, code) == 0) report_error(res, rec, code);   // count a record once
 }
 
+// 4 mask bytes (1 = real element) for elements e .. e+3 of a record with `len` elements
+__device__ __forceinline__ uint32_t mask_word(uint32_t len, uint32_t e) {
+    const int left = (int)len - (int)e;
+    return left >= 4 ? 0x01010101u : (left <= 0 ? 0u : (0x01010101u >> (8 * (4 - left))));
+}
+
+// Rows part of the decode kernel: reports what the scan rejected, checks fixed_len, and writes
+// pad, length and mask of every kept record's row -- store-only work, 16 bytes per lane where
+// the planes allow it.  A warp takes ROWS_GROUP records at a time: their metadata comes in with
+// one load per array (lanes 0..ROWS_GROUP-1), then the rows are written one after the other
+// without a dependent load in between, so the warp spends its time issuing stores that drain
+// while the block goes on to parse numbers.
+#define ROWS_GROUP 8
 template <int ELEM_BYTES>
-__global__ void __launch_bounds__(256) k_json_rows(const flat_args a) {
-    const uint32_t lane = threadIdx.x & 31;
-    const uint32_t warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
-    const uint32_t nwarps = (gridDim.x * blockDim.x) >> 5;
+__device__ __forceinline__ void json_rows_part(const flat_args& a, uint32_t warp, uint32_t nwarps, uint32_t lane) {
+    constexpr uint32_t PER16 = 16 / ELEM_BYTES;                 // elements per 16-byte store
     const uint32_t B = a.res->batch_size;
-    for (uint32_t i = warp; i < a.n; i += nwarps) {
-        const int32_t kidx = a.rec_kidx[i];
-        const uint32_t len = (uint32_t)a.rec_len[i];
-        if (lane == 0) {
+    const bool vec_values = ((a.values.row_bytes | (uintptr_t)a.values.base) & 15u) == 0;
+    const bool vec_mask = a.mask.base && ((a.mask.row_bytes | (uintptr_t)a.mask.base | a.max_len) & 15u) == 0;
+    for (uint32_t g = warp * ROWS_GROUP; g < a.n; g += nwarps * ROWS_GROUP) {
+        int32_t my_kidx = -1;
+        uint32_t my_len = 0;
+        if (lane < ROWS_GROUP && g + lane < a.n) {
+            const uint32_t i = g + lane;
+            my_kidx = a.rec_kidx[i];
+            my_len = (uint32_t)a.rec_len[i];
             const int pre = a.rec_status[i];                  // head / TOO_LONG verdict of the scan
             if (pre) report_error(a.res, i, pre);
-            else if (kidx >= 0 && a.fixed_len && len != a.fixed_len)
+            else if (my_kidx >= 0 && a.fixed_len && my_len != a.fixed_len)
                 flag_record(a.rec_status, a.res, i, TK_ERR_RAGGED);
         }
-        if (kidx < 0) continue;
-        const uint64_t row = (uint64_t)B + (uint32_t)kidx;
-        const uint32_t fill_from = min(len, a.max_len);
-        uint8_t* vrow = (uint8_t*)a.values.base + row * a.values.row_bytes;
-        if (ELEM_BYTES == 4) {
-            uint32_t* p = reinterpret_cast<uint32_t*>(vrow);
-            for (uint32_t e = fill_from + lane; e < a.max_len; e += 32) p[e] = 0u;
-        } else {
-            unsigned long long* p = reinterpret_cast<unsigned long long*>(vrow);
-            for (uint32_t e = fill_from + lane; e < a.max_len; e += 32) p[e] = 0ull;
-        }
-        if (a.lengths.base && lane == 0)
-            *reinterpret_cast<int32_t*>((uint8_t*)a.lengths.base + row * a.lengths.row_bytes) = (int32_t)len;
-        if (a.mask.base) {
-            uint8_t* m = (uint8_t*)a.mask.base + row * a.mask.row_bytes;
-            if ((a.max_len & 3u) == 0 && ((uintptr_t)m & 3u) == 0) {
-                uint32_t* m32 = reinterpret_cast<uint32_t*>(m);
-                for (uint32_t w = lane; w < a.max_len / 4; w += 32) {
-                    const int left = (int)len - (int)(w * 4);
-                    m32[w] = left >= 4 ? 0x01010101u : (left <= 0 ? 0u : (0x01010101u >> (8 * (4 - left))));
+#pragma unroll 1
+        for (uint32_t r = 0; r < ROWS_GROUP; ++r) {
+            const int32_t kidx = __shfl_sync(0xffffffffu, my_kidx, r);
+            const uint32_t len = __shfl_sync(0xffffffffu, my_len, r);
+            if (kidx < 0) continue;
+            const uint64_t row = (uint64_t)B + (uint32_t)kidx;
+            const uint32_t fill_from = min(len, a.max_len);
+            uint8_t* vrow = (uint8_t*)a.values.base + row * a.values.row_bytes;
+            // pad [fill_from, max_len): scalar stores up to the next 16-byte boundary, then 16 bytes per lane
+            uint32_t e0 = fill_from;
+            if (vec_values) {
+                const uint32_t up = min((fill_from + PER16 - 1) & ~(PER16 - 1), a.max_len);
+                if (fill_from + lane < up) {
+                    if (ELEM_BYTES == 4) reinterpret_cast<uint32_t*>(vrow)[fill_from + lane] = 0u;
+                    else reinterpret_cast<unsigned long long*>(vrow)[fill_from + lane] = 0ull;
                 }
+                const uint32_t vend = a.max_len & ~(PER16 - 1);
+                for (uint32_t e = up + lane * PER16; e < vend; e += 32 * PER16)
+                    *reinterpret_cast<uint4*>(vrow + (size_t)e * ELEM_BYTES) = make_uint4(0, 0, 0, 0);
+                e0 = max(up, vend);
+            }
+            if (ELEM_BYTES == 4) {
+                uint32_t* p = reinterpret_cast<uint32_t*>(vrow);
+                for (uint32_t e = e0 + lane; e < a.max_len; e += 32) p[e] = 0u;
             } else {
-                for (uint32_t e = lane; e < a.max_len; e += 32) m[e] = e < len ? 1 : 0;
+                unsigned long long* p = reinterpret_cast<unsigned long long*>(vrow);
+                for (uint32_t e = e0 + lane; e < a.max_len; e += 32) p[e] = 0ull;
+            }
+            if (a.lengths.base && lane == 0)
+                *reinterpret_cast<int32_t*>((uint8_t*)a.lengths.base + row * a.lengths.row_bytes) = (int32_t)len;
+            if (a.mask.base) {
+                uint8_t* m = (uint8_t*)a.mask.base + row * a.mask.row_bytes;
+                if (vec_mask) {
+                    for (uint32_t e = lane * 16; e < a.max_len; e += 32 * 16)
+                        *reinterpret_cast<uint4*>(m + e) = make_uint4(mask_word(len, e), mask_word(len, e + 4),
+                                                                      mask_word(len, e + 8), mask_word(len, e + 12));
+                } else if ((a.max_len & 3u) == 0 && ((uintptr_t)m & 3u) == 0) {
+                    uint32_t* m32 = reinterpret_cast<uint32_t*>(m);
+                    for (uint32_t w = lane; w < a.max_len / 4; w += 32) m32[w] = mask_word(len, w * 4);
+                } else {
+                    for (uint32_t e = lane; e < a.max_len; e += 32) m[e] = e < len ? 1 : 0;
+                }
             }
         }
     }
@@ -385,10 +425,14 @@ __device__ __forceinline__ bool fast_number(const uint8_t* bytes, uint32_t pos, 
 // Token entry written by k_json_scan: .x = byte position of the element, .y = record index with
 // TOK_LAST on the record's last element and TOK_TAIL when the record's final byte is ']'.
 template <int KIND>
-__global__ void __launch_bounds__(256) k_json_parse(const flat_args a) {
+__global__ void __launch_bounds__(256, 6) k_json_parse(const flat_args a) {
     typedef typename tk_elem<KIND>::type T;
     __shared__ parse_tables tb;
-    parse_tables_init(tb);
+    tk_pdl_launch_dependents();
+    parse_tables_init(tb);                  // constants only: overlaps the tail of the previous kernel
+    tk_pdl_wait();
+    json_rows_part<sizeof(T)>(a, (blockIdx.x * blockDim.x + threadIdx.x) >> 5, (gridDim.x * blockDim.x) >> 5,
+                              threadIdx.x & 31);
     const uint32_t n_tok = min(*a.tok_count, a.tok_cap);
     const uint32_t B = a.res->batch_size;
     T* values = reinterpret_cast<T*>(a.values.base);
@@ -498,26 +542,22 @@ extern "C" int tk_json_decode(tk_ctx* ctx, int slot, int dtype, uint32_t max_len
     a.bytes = s.d.bytes; a.recs = s.d.recs; a.n = n; a.max_len = max_len; a.fixed_len = fixed_len;
     a.rec_kidx = s.d.rec_kidx; a.rec_len = s.d.rec_len; a.rec_status = s.d.rec_status;
     a.rec_tok = s.d.rec_tok; a.res = s.d.result;
-    a.tok = reinterpret_cast<const uint2*>(s.d.tok_pos); a.tok_count = s.d.tok_count;
+    a.tok = reinterpret_cast<const uint2*>(s.d.tok_pos); a.tok_count = s.d.tok_count + (s.tok_use & 1u);
     a.tok_cap = (uint32_t)(ctx->tok_cap > 0xFFFFFFFFull ? 0xFFFFFFFFull : ctx->tok_cap);
     tk_plane_t z; z.base = nullptr; z.row_bytes = 0;
     a.values = *values;
     a.lengths = lengths ? *lengths : z;
     a.mask = mask ? *mask : z;
-    const uint32_t rblocks = min((n + 7) / 8, 148u * 16u);
-    if (dtype == TK_DTYPE_F32 || dtype == TK_DTYPE_I32) k_json_rows<4><<<rblocks, 256, 0, st>>>(a);
-    else k_json_rows<8><<<rblocks, 256, 0, st>>>(a);
-    TK_LAUNCH_CHECK();
     // the element count lives on the device; size the grid for the worst case this slot allows
     // (an element needs two bytes) and let surplus blocks exit at once
     const uint64_t max_tok = (uint64_t)s.n_bytes / 2 + n;
-    const uint32_t pblocks = (uint32_t)min((max_tok + 255) / 256, (uint64_t)parse_grid(dtype));
+    // (the rows part wants a warp per ~record too: never fewer blocks than records / 8 would use)
+    const uint32_t pblocks = (uint32_t)min(max((max_tok + 255) / 256, ((uint64_t)n + 7) / 8), (uint64_t)parse_grid(dtype));
     switch (dtype) {
-        case TK_DTYPE_F32: k_json_parse<TK_F32><<<pblocks, 256, 0, st>>>(a); break;
-        case TK_DTYPE_F64: k_json_parse<TK_F64><<<pblocks, 256, 0, st>>>(a); break;
-        case TK_DTYPE_I32: k_json_parse<TK_I32><<<pblocks, 256, 0, st>>>(a); break;
-        default:           k_json_parse<TK_I64><<<pblocks, 256, 0, st>>>(a); break;
+        case TK_DTYPE_F32: TK_LAUNCH_PDL(k_json_parse<TK_F32>, pblocks, 256, st, a); break;
+        case TK_DTYPE_F64: TK_LAUNCH_PDL(k_json_parse<TK_F64>, pblocks, 256, st, a); break;
+        case TK_DTYPE_I32: TK_LAUNCH_PDL(k_json_parse<TK_I32>, pblocks, 256, st, a); break;
+        default:           TK_LAUNCH_PDL(k_json_parse<TK_I64>, pblocks, 256, st, a); break;
     }
-    TK_LAUNCH_CHECK();
     return 0;
 }

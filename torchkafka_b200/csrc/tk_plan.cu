@@ -81,6 +81,8 @@ __global__ void __launch_bounds__(CMP_THREADS) k_compact_count(const int32_t* __
                                                                  const int32_t* __restrict__ rec_len, uint32_t n,
                                                                  unsigned long long* __restrict__ blk_sum) {
     __shared__ unsigned long long tot;
+    tk_pdl_launch_dependents();
+    tk_pdl_wait();
     const uint32_t base = blockIdx.x * CMP_TILE + threadIdx.x * CMP_ITEMS;
     unsigned long long c = 0;
 #pragma unroll
@@ -98,8 +100,13 @@ __global__ void __launch_bounds__(1024) k_compact_scan(unsigned long long* __res
                                                        uint32_t max_batches, tk_state* state,
                                                        tk_result_t* __restrict__ res,
                                                        uint32_t* __restrict__ batch_end,
-                                                       uint32_t* __restrict__ batch_lmax) {
+                                                       uint32_t* __restrict__ batch_lmax,
+                                                       int64_t* __restrict__ commit, uint32_t commit_elems) {
     __shared__ unsigned long long tot;
+    tk_pdl_launch_dependents();
+    tk_pdl_wait();
+    // commit matrix starts at -1 ("partition not seen"); filled by the apply pass
+    for (uint32_t x = threadIdx.x; x < commit_elems; x += blockDim.x) commit[x] = -1;
     unsigned long long running = 0;
     for (uint32_t base = 0; base < nblk; base += blockDim.x) {
         uint32_t i = base + threadIdx.x;
@@ -148,6 +155,8 @@ __global__ void __launch_bounds__(CMP_THREADS) k_compact_apply(int32_t* __restri
                                                                  int64_t* __restrict__ commit, uint32_t pitch,
                                                                  uint32_t n_partitions) {
     __shared__ unsigned long long tot;
+    tk_pdl_launch_dependents();
+    tk_pdl_wait();
     const uint32_t base = blockIdx.x * CMP_TILE + threadIdx.x * CMP_ITEMS;
     int keep[CMP_ITEMS];
     uint32_t lens[CMP_ITEMS];
@@ -217,21 +226,13 @@ extern "C" int tk_compact(tk_ctx* ctx, int slot, uint32_t batch_size, void* stre
                "slot with %u records can close more than max_batches=%u batches of %u", n, ctx->max_batches, batch_size);
     ctx->batch_size = batch_size;
     const uint32_t nblk = (n + CMP_TILE - 1) / CMP_TILE;
-    // commit matrix starts at -1 ("partition not seen"); filled by the apply pass below
-    TK_CUDA(cudaMemsetAsync(s.d.commit, 0xFF, sizeof(int64_t) * (size_t)ctx->n_partitions * ctx->commit_pitch, st));
-    if (nblk) {
-        k_compact_count<<<nblk, CMP_THREADS, 0, st>>>(s.d.rec_kidx, s.d.rec_len, n, s.d.blk_sum);
-        TK_LAUNCH_CHECK();
-    }
-    k_compact_scan<<<1, 1024, 0, st>>>(s.d.blk_sum, nblk, n, batch_size, ctx->max_batches, ctx->d_state,
-                                       s.d.result, s.d.batch_end, s.d.batch_lmax);
-    TK_LAUNCH_CHECK();
-    if (nblk) {
-        k_compact_apply<<<nblk, CMP_THREADS, 0, st>>>(s.d.rec_kidx, s.d.rec_len, n, s.d.blk_sum, s.d.result,
-                                                     s.d.batch_end, s.d.batch_lmax, s.d.recs, s.d.commit,
-                                                     ctx->commit_pitch, ctx->n_partitions);
-        TK_LAUNCH_CHECK();
-    }
+    if (nblk) TK_LAUNCH_PDL(k_compact_count, nblk, CMP_THREADS, st, s.d.rec_kidx, s.d.rec_len, n, s.d.blk_sum);
+    TK_LAUNCH_PDL(k_compact_scan, 1, 1024, st, s.d.blk_sum, nblk, n, batch_size, ctx->max_batches, ctx->d_state,
+                  s.d.result, s.d.batch_end, s.d.batch_lmax, s.d.commit,
+                  (uint32_t)(ctx->n_partitions * ctx->commit_pitch));
+    if (nblk)
+        TK_LAUNCH_PDL(k_compact_apply, nblk, CMP_THREADS, st, s.d.rec_kidx, s.d.rec_len, n, s.d.blk_sum, s.d.result,
+                      s.d.batch_end, s.d.batch_lmax, s.d.recs, s.d.commit, ctx->commit_pitch, ctx->n_partitions);
     return 0;
 }
 
@@ -243,6 +244,8 @@ __global__ void __launch_bounds__(128) k_commit_scan(int64_t* __restrict__ commi
                                                       const tk_result_t* __restrict__ res,
                                                       int64_t* __restrict__ positions) {
     __shared__ long long chunk_max[128];
+    tk_pdl_launch_dependents();
+    tk_pdl_wait();
     const uint32_t p = blockIdx.x;
     const uint32_t nb = res->n_closed + 1;                 // closed batches + the open one
     int64_t* row = commit + (size_t)p * pitch;
@@ -273,8 +276,7 @@ extern "C" int tk_commit_offsets(tk_ctx* ctx, int slot, void* stream) {
     TK_ENTER(ctx, slot);
     tk_slot& s = ctx->slots[slot];
     cudaStream_t st = (cudaStream_t)stream;
-    k_commit_scan<<<ctx->n_partitions, 128, 0, st>>>(s.d.commit, ctx->commit_pitch, s.d.result, ctx->d_positions);
-    TK_LAUNCH_CHECK();
+    TK_LAUNCH_PDL(k_commit_scan, ctx->n_partitions, 128, st, s.d.commit, ctx->commit_pitch, s.d.result, ctx->d_positions);
     return 0;
 }
 
@@ -289,6 +291,8 @@ struct carry_args {
 };
 
 __global__ void __launch_bounds__(256) k_carry_rows(const tk_result_t* __restrict__ prev_res, const carry_args a) {
+    tk_pdl_launch_dependents();
+    tk_pdl_wait();
     const uint64_t co = prev_res->carry_out;
     if (co == 0) return;
     const uint64_t B = prev_res->batch_size, nk = prev_res->n_kept;
@@ -323,7 +327,6 @@ extern "C" int tk_carry_rows(tk_ctx* ctx, int prev_slot, int n_planes, const tk_
         a.prev[k] = prev[k];
         a.cur[k] = cur[k];
     }
-    k_carry_rows<<<148 * 2, 256, 0, (cudaStream_t)stream>>>(ctx->slots[prev_slot].d.result, a);
-    TK_LAUNCH_CHECK();
+    TK_LAUNCH_PDL(k_carry_rows, 148 * 2, 256, (cudaStream_t)stream, ctx->slots[prev_slot].d.result, a);
     return 0;
 }

@@ -18,6 +18,8 @@ __device__ __forceinline__ void raw_report_error(tk_result_t* res, uint32_t rec,
 __global__ void __launch_bounds__(256) k_raw_scan(const tk_rec_t* __restrict__ recs, uint32_t n,
                                                    uint64_t record_bytes, int32_t* __restrict__ rec_len,
                                                    int32_t* __restrict__ rec_status, int32_t* __restrict__ rec_kidx) {
+    tk_pdl_launch_dependents();
+    tk_pdl_wait();
     const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
     const uint32_t len = recs[i + 1].start - recs[i].start;
@@ -32,9 +34,8 @@ extern "C" int tk_raw_scan(tk_ctx* ctx, int slot, uint64_t record_bytes, void* s
     tk_slot& s = ctx->slots[slot];
     const uint32_t n = s.n_records;
     if (!n) return 0;
-    k_raw_scan<<<(n + 255) / 256, 256, 0, (cudaStream_t)stream>>>(s.d.recs, n, record_bytes, s.d.rec_len,
-                                                                  s.d.rec_status, s.d.rec_kidx);
-    TK_LAUNCH_CHECK();
+    TK_LAUNCH_PDL(k_raw_scan, (n + 255) / 256, 256, (cudaStream_t)stream, s.d.recs, n, record_bytes, s.d.rec_len,
+                  s.d.rec_status, s.d.rec_kidx);
     return 0;
 }
 
@@ -51,6 +52,8 @@ __global__ void __launch_bounds__(256) k_collate_raw(const uint8_t* __restrict__
                                                       const int32_t* __restrict__ rec_kidx,
                                                       const int32_t* __restrict__ rec_status,
                                                       tk_result_t* res, tk_plane_t out) {
+    tk_pdl_launch_dependents();
+    tk_pdl_wait();
     const uint32_t total = n * chunks_per_rec;
     for (uint32_t x = blockIdx.x * blockDim.x + threadIdx.x; x < total; x += gridDim.x * blockDim.x) {
         const uint32_t i = x / chunks_per_rec;
@@ -85,9 +88,8 @@ extern "C" int tk_collate_raw(tk_ctx* ctx, int slot, uint64_t record_bytes, cons
         TK_REQUIRE(total < (1ull << 32) && record_bytes < (1ull << 32), "slot too large for 32-bit chunk indexing");
         const uint64_t want = (total + 255) / 256;
         const uint32_t blocks = (uint32_t)(want < 148ull * 32 ? want : 148ull * 32);
-        k_collate_raw<<<blocks, 256, 0, st>>>(s.d.bytes, s.d.recs, n, (uint32_t)record_bytes, (uint32_t)cpr,
-                                              s.d.rec_kidx, s.d.rec_status, s.d.result, *out);
-        TK_LAUNCH_CHECK();
+        TK_LAUNCH_PDL(k_collate_raw, blocks, 256, st, s.d.bytes, s.d.recs, n, (uint32_t)record_bytes, (uint32_t)cpr,
+                      s.d.rec_kidx, s.d.rec_status, s.d.result, *out);
     }
     return 0;
 }
@@ -172,6 +174,8 @@ __global__ void __launch_bounds__(IMG_THREADS) k_collate_image(const uint8_t* __
                                                                tk_result_t* res, tk_plane_t out) {
     __shared__ __align__(16) uint8_t s_in[IMG_PIX * C];
     __shared__ uint32_t s_lut[C * 32 * 32];
+    tk_pdl_launch_dependents();
+    tk_pdl_wait();
     // table: word (c*32 + row)*32 + 4*g + q holds entries x = 8*row + 2*q (low half) and x + 1 (high half)
     for (uint32_t w = threadIdx.x; w < C * 32 * 32; w += IMG_THREADS) {
         const uint32_t col = w & 31u, row = (w >> 5) & 31u, c = w >> 10;
@@ -251,6 +255,8 @@ __global__ void __launch_bounds__(IMG_THREADS) k_collate_image_fma(const uint8_t
                                                                    const img_consts k,
                                                                    tk_result_t* res, tk_plane_t out) {
     __shared__ __align__(16) uint8_t s_in[IMG_PIX * C];
+    tk_pdl_launch_dependents();
+    tk_pdl_wait();
     const uint32_t total_tiles = n * tiles_per_img;
     for (uint32_t job = blockIdx.x; job < total_tiles; job += gridDim.x) {
         const uint32_t i = job / tiles_per_img;
@@ -323,11 +329,11 @@ extern "C" int tk_collate_image_u8_bf16_nchw(tk_ctx* ctx, int slot, uint32_t hei
         for (int c = 0; c < 4; ++c) { kc.a[c] = ctx->image_a[c]; kc.b[c] = ctx->image_b[c]; }
 #define TK_IMG_LAUNCH(CC)                                                                                   \
     if (ctx->image_fma)                                                                                     \
-        k_collate_image_fma<CC><<<blocks, IMG_THREADS, 0, st>>>(s.d.bytes, s.d.recs, n, npix, tiles,       \
-                                                                s.d.rec_kidx, s.d.rec_status, kc, s.d.result, *out); \
+        TK_LAUNCH_PDL(k_collate_image_fma<CC>, blocks, IMG_THREADS, st, s.d.bytes, s.d.recs, n, npix, tiles, \
+                      s.d.rec_kidx, s.d.rec_status, kc, s.d.result, *out);                                  \
     else                                                                                                    \
-        k_collate_image<CC><<<blocks, IMG_THREADS, 0, st>>>(s.d.bytes, s.d.recs, n, npix, tiles, s.d.rec_kidx, \
-                                                            s.d.rec_status, ctx->d_image_lut, s.d.result, *out)
+        TK_LAUNCH_PDL(k_collate_image<CC>, blocks, IMG_THREADS, st, s.d.bytes, s.d.recs, n, npix, tiles,    \
+                      s.d.rec_kidx, s.d.rec_status, (const uint16_t*)ctx->d_image_lut, s.d.result, *out)
         switch (channels) {
             case 1: TK_IMG_LAUNCH(1); break;
             case 2: TK_IMG_LAUNCH(2); break;
@@ -336,7 +342,6 @@ extern "C" int tk_collate_image_u8_bf16_nchw(tk_ctx* ctx, int slot, uint32_t hei
             default: TK_REQUIRE(false, "1..4 channels supported");
         }
 #undef TK_IMG_LAUNCH
-        TK_LAUNCH_CHECK();
     }
     return 0;
 }

@@ -31,9 +31,9 @@ REC_DTYPE = np.dtype([("start", "<u4"), ("partition", "<i4"), ("offset", "<i8")]
 
 #: a slot never closes more batches than this (bounds the commit matrix)
 MAX_BATCHES_CAP = 16384
-#: kernels launched per slot by ``process`` (JSON: carry, scan, 3x compact, commit scan, rows,
-#: parse; raw: carry, scan, 3x compact, commit scan, collate; memsets are not counted)
-LAUNCHES_PER_SLOT_JSON = 8
+#: kernels launched per slot by ``process`` (JSON: carry, scan, 3x compact, commit scan, decode
+#: (rows + parse in one kernel); raw: carry, scan, 3x compact, commit scan, collate)
+LAUNCHES_PER_SLOT_JSON = 7
 LAUNCHES_PER_SLOT_RAW = 7
 
 

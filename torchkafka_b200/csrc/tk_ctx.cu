@@ -157,7 +157,8 @@ static void free_slot(tk_slot& s) {
     if (s.h_recs) cudaFreeHost(s.h_recs);
     if (s.h_block) cudaFreeHost(s.h_block);
     cudaFree(s.d.bytes); cudaFree(s.d.recs); cudaFree(s.d.rec_len); cudaFree(s.d.rec_status);
-    cudaFree(s.d.rec_kidx); cudaFree(s.d.blk_sum); cudaFree(s.d.block);
+    cudaFree(s.d.rec_kidx); cudaFree(s.d.tile_agg); cudaFree(s.d.tile_incl); cudaFree(s.d.tile_flag);
+    cudaFree(s.d.plan_ctr); cudaFree(s.d.block);
     cudaFree(s.d.rec_tok); cudaFree(s.d.tok_pos); cudaFree(s.d.tok_count);
     if (s.ev_h2d) cudaEventDestroy(s.ev_h2d);
     if (s.ev_free) cudaEventDestroy(s.ev_free);
@@ -216,7 +217,12 @@ static int create_impl(tk_ctx* ctx) {
         TK_CUDA(cudaMalloc(&s.d.rec_len, sizeof(int32_t) * nrec));
         TK_CUDA(cudaMalloc(&s.d.rec_status, sizeof(int32_t) * nrec));
         TK_CUDA(cudaMalloc(&s.d.rec_kidx, sizeof(int32_t) * nrec));
-        TK_CUDA(cudaMalloc(&s.d.blk_sum, sizeof(unsigned long long) * nblk));
+        TK_CUDA(cudaMalloc(&s.d.tile_agg, sizeof(unsigned long long) * nblk));
+        TK_CUDA(cudaMalloc(&s.d.tile_incl, sizeof(unsigned long long) * nblk));
+        TK_CUDA(cudaMalloc(&s.d.tile_flag, sizeof(uint32_t) * nblk));
+        TK_CUDA(cudaMemset(s.d.tile_flag, 0, sizeof(uint32_t) * nblk));
+        TK_CUDA(cudaMalloc(&s.d.plan_ctr, 2 * sizeof(uint32_t)));
+        TK_CUDA(cudaMemset(s.d.plan_ctr, 0, 2 * sizeof(uint32_t)));
         TK_CUDA(cudaMalloc(&s.d.rec_tok, sizeof(uint32_t) * (nrec + 1)));
         // token arrays of the JSON path are allocated on first use (tk_ensure_token_arrays)
         TK_CUDA(cudaMalloc(&s.d.block, ctx->block_bytes));

@@ -40,7 +40,14 @@ struct tk_slot_dev {
     int32_t*     rec_len;      // element count (JSON) / byte count (raw)
     int32_t*     rec_status;   // tk_status_t
     int32_t*     rec_kidx;     // index among kept records of this slot, -1 if skipped
-    unsigned long long* blk_sum;   // per-tile (kept << 40 | elements) for the compaction scan
+    // single-pass compaction scan (tk_plan.cu): per tile of CMP_TILE records the packed sum
+    // (kept << 40 | elements) of the tile alone and of everything up to and including it, a
+    // status word (epoch << 2 | 1: tile sum valid, | 2: inclusive sum valid), and two counters
+    // (tile ticket, finished tiles) that the last block resets
+    unsigned long long* tile_agg;
+    unsigned long long* tile_incl;
+    uint32_t*    tile_flag;
+    uint32_t*    plan_ctr;
     uint32_t*    rec_tok;      // [slot_records] index of each record's first element in the token array
     uint32_t*    tok_pos;      // [tok_cap] token array of the flat decode path: uint2 {byte position, record}
     uint32_t*    tok_count;    // [2] elements emitted so far (token array allocation cursor): two
@@ -71,6 +78,7 @@ struct tk_slot {
     cudaEvent_t  ev_dec0, ev_dec1;   // timing events around the decode / collate kernels (tk_ctx_set_timing)
     bool         dec_timed;
     uint32_t     tok_use;     // tk_json_scan calls on this slot: selects the token counter
+    uint32_t     plan_epoch;  // tk_compact calls on this slot: tags the tile status words
     bool         free_recorded;
 };
 
@@ -142,6 +150,8 @@ __device__ __forceinline__ void tk_pdl_wait() { asm volatile("griddepcontrol.wai
 #endif
 
 int tk_ensure_token_arrays(tk_ctx* ctx);
+// K4 second half; wait_for_prior = 0 only behind a kernel that released its dependents after its own wait
+int tk_commit_final(tk_ctx* ctx, int slot, int wait_for_prior, void* stream);
 
 // bytes the kernels may over-read past n_bytes (aligned vector loads of the last tile)
 #define TK_BYTES_PAD 4096

@@ -197,8 +197,11 @@ extern "C" int tk_json_scan(tk_ctx* ctx, int slot, uint32_t max_len, uint32_t mi
     s.tok_use++;
     a.tok = s.d.tok_pos; a.tok_count = s.d.tok_count + (s.tok_use & 1u); a.tok_count_next = s.d.tok_count + ((s.tok_use + 1) & 1u);
     a.tok_cap = (uint32_t)(ctx->tok_cap > 0xFFFFFFFFull ? 0xFFFFFFFFull : ctx->tok_cap);
-    const uint32_t blocks = (n + 7) / 8;                   // one warp per record
-    TK_LAUNCH_PDL(k_json_scan, blocks, 256, st, a);
+    // one warp per record; 4-warp blocks: records differ in length, and a block holds its
+    // slots until its longest record is done
+    const uint32_t threads = 128, wpb = threads / 32;
+    const uint32_t blocks = (n + wpb - 1) / wpb;
+    TK_LAUNCH_PDL(k_json_scan, blocks, threads, st, a);
     return 0;
 }
 
@@ -428,9 +431,9 @@ template <int KIND>
 __global__ void __launch_bounds__(256, 6) k_json_parse(const flat_args a) {
     typedef typename tk_elem<KIND>::type T;
     __shared__ parse_tables tb;
-    tk_pdl_launch_dependents();
     parse_tables_init(tb);                  // constants only: overlaps the tail of the previous kernel
     tk_pdl_wait();
+    tk_pdl_launch_dependents();             // after the wait: see k_commit_final (tk_plan.cu)
     json_rows_part<sizeof(T)>(a, (blockIdx.x * blockDim.x + threadIdx.x) >> 5, (gridDim.x * blockDim.x) >> 5,
                               threadIdx.x & 31);
     const uint32_t n_tok = min(*a.tok_count, a.tok_cap);

@@ -76,101 +76,124 @@ __device__ __forceinline__ unsigned long long block_excl_scan64(unsigned long lo
     return r;
 }
 
-// pass 1: kept count per tile of CMP_TILE records
-__global__ void __launch_bounds__(CMP_THREADS) k_compact_count(const int32_t* __restrict__ rec_kidx,
-                                                                 const int32_t* __restrict__ rec_len, uint32_t n,
-                                                                 unsigned long long* __restrict__ blk_sum) {
-    __shared__ unsigned long long tot;
-    tk_pdl_launch_dependents();
-    tk_pdl_wait();
-    const uint32_t base = blockIdx.x * CMP_TILE + threadIdx.x * CMP_ITEMS;
-    unsigned long long c = 0;
-#pragma unroll
-    for (int k = 0; k < CMP_ITEMS; ++k) {
-        uint32_t i = base + k;
-        if (i < n) c += ((unsigned long long)(rec_kidx[i] >= 0 ? 1 : 0) << PACK_SHIFT) + (uint32_t)rec_len[i];
-    }
-    block_excl_scan64(c, &tot);
-    if (threadIdx.x == 0) blk_sum[blockIdx.x] = tot;
-}
-
-// pass 2: one block scans the tile sums, fills the result header, advances the carry
-__global__ void __launch_bounds__(1024) k_compact_scan(unsigned long long* __restrict__ blk_sum, uint32_t nblk,
-                                                       uint32_t n, uint32_t batch_size,
-                                                       uint32_t max_batches, tk_state* state,
-                                                       tk_result_t* __restrict__ res,
-                                                       uint32_t* __restrict__ batch_end,
-                                                       uint32_t* __restrict__ batch_lmax,
-                                                       int64_t* __restrict__ commit, uint32_t commit_elems) {
-    __shared__ unsigned long long tot;
-    tk_pdl_launch_dependents();
-    tk_pdl_wait();
-    // commit matrix starts at -1 ("partition not seen"); filled by the apply pass
-    for (uint32_t x = threadIdx.x; x < commit_elems; x += blockDim.x) commit[x] = -1;
-    unsigned long long running = 0;
-    for (uint32_t base = 0; base < nblk; base += blockDim.x) {
-        uint32_t i = base + threadIdx.x;
-        unsigned long long v = i < nblk ? blk_sum[i] : 0;
-        unsigned long long ex = block_excl_scan64(v, &tot);
-        if (i < nblk) blk_sum[i] = running + ex;
-        running += tot;
-        __syncthreads();
-    }
-    const uint32_t n_kept = (uint32_t)(running >> PACK_SHIFT);
-    const unsigned long long n_tokens = running & ((1ull << PACK_SHIFT) - 1);
-    const uint32_t c = state->carry_rows;
-    const uint32_t n_closed = (c + n_kept) / batch_size;
-    for (uint32_t j = threadIdx.x; j <= max_batches; j += blockDim.x) {
-        batch_end[j] = n ? n - 1 : 0;
-        batch_lmax[j] = 0;
-    }
-    __syncthreads();
-    if (threadIdx.x == 0) {
-        res->n_records = n;
-        res->n_kept = n_kept;
-        res->carry_in = c;
-        res->carry_out = (c + n_kept) % batch_size;
-        res->n_closed = n_closed;
-        res->batch_size = batch_size;
-        res->n_errors = 0;
-        res->first_error_rec = 0xFFFFFFFFu;
-        res->first_error_status = 0;
-        res->reserved[0] = (uint32_t)(n_tokens > 0xFFFFFFFFull ? 0xFFFFFFFFu : n_tokens);   // elements in the slot
-        state->carry_rows = (c + n_kept) % batch_size;
-    }
-}
-
-// pass 3: final index of every record.
+// ------------------------------------------------------------------------ K2 + K4, one kernel
+// Single-pass scan with decoupled look-back: every block takes the next tile of CMP_TILE
+// records (ticket counter, so a tile's predecessors are always running or done), publishes the
+// tile's packed sum, looks back over the predecessors' published sums for its exclusive prefix,
+// publishes its inclusive sum, and applies:
 //   kept record    -> rec_kidx = k            (k = kept records before it in this slot)
 //   skipped record -> rec_kidx = -1 - k
-// and per batch: the longest kept record (one atomic per warp when the warp lies inside one
-// batch, which is the common case) and the index of the record that closed it.
-__global__ void __launch_bounds__(CMP_THREADS) k_compact_apply(int32_t* __restrict__ rec_kidx,
-                                                                 const int32_t* __restrict__ rec_len,
-                                                                 uint32_t n, const unsigned long long* __restrict__ blk_sum,
-                                                                 const tk_result_t* __restrict__ res,
-                                                                 uint32_t* __restrict__ batch_end,
-                                                                 uint32_t* __restrict__ batch_lmax,
-                                                                 const tk_rec_t* __restrict__ recs,
-                                                                 int64_t* __restrict__ commit, uint32_t pitch,
-                                                                 uint32_t n_partitions) {
-    __shared__ unsigned long long tot;
+//   per batch: longest kept record, index of the closing record
+//   K4 first half: segmented max of (offset + 1) per (batch, partition) into the commit matrix.
+// The block that finishes last writes the result header and advances the carry.  K4's second
+// half (running max along the batch axis) is k_commit_final below.
+// Tile 0 initialises the per-batch arrays and the commit matrix before it publishes anything;
+// every other tile reaches its apply phase only after (transitively) seeing tile 0's flag.
+struct plan_args {
+    int32_t*        rec_kidx;
+    const int32_t*  rec_len;
+    const tk_rec_t* recs;
+    uint32_t        n, n_tiles;
+    uint32_t        batch_size, max_batches;
+    uint32_t        pitch, n_partitions;
+    uint32_t        epoch;
+    tk_state*       state;
+    tk_result_t*    res;
+    uint32_t*       batch_end;
+    uint32_t*       batch_lmax;
+    int64_t*        commit;
+    int64_t*        positions;
+    unsigned long long* tile_agg;
+    unsigned long long* tile_incl;
+    uint32_t*       tile_flag;
+    uint32_t*       ctr;          // [0] tile ticket, [1] finished tiles
+};
+
+__device__ __forceinline__ uint32_t ld_acquire_u32(const uint32_t* p) {
+    uint32_t v;
+    asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    return v;
+}
+__device__ __forceinline__ void st_release_u32(uint32_t* p, uint32_t v) {
+    asm volatile("st.release.gpu.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+__device__ __forceinline__ unsigned long long warp_sum64(unsigned long long v) {
+#pragma unroll
+    for (int d = 16; d > 0; d >>= 1) v += __shfl_xor_sync(0xffffffffu, v, d);
+    return v;
+}
+
+// exclusive prefix of tile `tile` (warp 0 of the block; result valid in every lane)
+__device__ __forceinline__ unsigned long long plan_lookback(const plan_args& a, uint32_t tile, uint32_t lane) {
+    unsigned long long excl = 0;
+    int p = (int)tile - 1;
+    while (p >= 0) {
+        const int q = p - (int)lane;                      // lane 0 looks at the nearest predecessor
+        uint32_t st = 2;                                  // tiles before 0: "inclusive sum 0"
+        if (q >= 0) {
+            uint32_t f;
+            do { f = ld_acquire_u32(a.tile_flag + q); } while ((f >> 2) != a.epoch);
+            st = f & 3u;
+        }
+        const uint32_t full = __ballot_sync(0xffffffffu, st == 2);
+        const uint32_t first = full ? (uint32_t)__ffs(full) - 1 : 32u;      // nearest inclusive sum
+        unsigned long long v = 0;
+        if (q >= 0 && lane <= first) v = lane == first ? a.tile_incl[q] : a.tile_agg[q];
+        excl += warp_sum64(v);
+        if (full) break;
+        p -= 32;
+    }
+    return excl;
+}
+
+__global__ void __launch_bounds__(CMP_THREADS) k_plan(const plan_args a) {
+    __shared__ unsigned long long tot, s_excl;
+    __shared__ uint32_t s_tile, s_last;
     tk_pdl_launch_dependents();
     tk_pdl_wait();
-    const uint32_t base = blockIdx.x * CMP_TILE + threadIdx.x * CMP_ITEMS;
+    if (threadIdx.x == 0) s_tile = atomicAdd(&a.ctr[0], 1u);
+    __syncthreads();
+    const uint32_t tile = s_tile, lane = threadIdx.x & 31;
+    const uint32_t base = tile * CMP_TILE + threadIdx.x * CMP_ITEMS;
+    const uint32_t n = a.n, B = a.batch_size;
     int keep[CMP_ITEMS];
     uint32_t lens[CMP_ITEMS];
     unsigned long long c = 0;
 #pragma unroll
     for (int k = 0; k < CMP_ITEMS; ++k) {
-        uint32_t i = base + k;
-        keep[k] = (i < n && rec_kidx[i] >= 0) ? 1 : 0;
-        lens[k] = i < n ? (uint32_t)rec_len[i] : 0u;
+        const uint32_t i = base + k;
+        keep[k] = (i < n && a.rec_kidx[i] >= 0) ? 1 : 0;
+        lens[k] = i < n ? (uint32_t)a.rec_len[i] : 0u;
         c += ((unsigned long long)keep[k] << PACK_SHIFT) + lens[k];
     }
-    const unsigned long long ex64 = block_excl_scan64(c, &tot) + blk_sum[blockIdx.x];
-    uint32_t ex = (uint32_t)(ex64 >> PACK_SHIFT);
-    const uint32_t carry = res->carry_in, B = res->batch_size;
+    const unsigned long long in_tile = block_excl_scan64(c, &tot);
+    if (tile == 0) {
+        for (uint32_t j = threadIdx.x; j <= a.max_batches; j += blockDim.x) {
+            a.batch_end[j] = n ? n - 1 : 0;
+            a.batch_lmax[j] = 0;
+        }
+        for (uint32_t x = threadIdx.x; x < a.n_partitions * a.pitch; x += blockDim.x) a.commit[x] = -1;
+        __threadfence();
+        __syncthreads();
+    }
+    if (threadIdx.x < 32) {
+        if (lane == 0) {
+            a.tile_agg[tile] = tot;
+            if (tile == 0) a.tile_incl[0] = tot;
+            st_release_u32(a.tile_flag + tile, (a.epoch << 2) | (tile == 0 ? 2u : 1u));
+        }
+        const unsigned long long excl = tile ? plan_lookback(a, tile, lane) : 0ull;
+        if (lane == 0) {
+            if (tile) {
+                a.tile_incl[tile] = excl + tot;
+                st_release_u32(a.tile_flag + tile, (a.epoch << 2) | 2u);
+            }
+            s_excl = excl;
+        }
+    }
+    __syncthreads();
+    uint32_t ex = (uint32_t)((in_tile + s_excl) >> PACK_SHIFT);
+    const uint32_t carry = a.state->carry_rows;
 #pragma unroll
     for (int k = 0; k < CMP_ITEMS; ++k) {
         const uint32_t i = base + k;
@@ -179,39 +202,66 @@ __global__ void __launch_bounds__(CMP_THREADS) k_compact_apply(int32_t* __restri
         uint32_t len = 0;
         if (live) {
             if (keep[k]) {
-                rec_kidx[i] = (int32_t)ex;
+                a.rec_kidx[i] = (int32_t)ex;
                 len = lens[k];
-                if ((carry + ex + 1) % B == 0) batch_end[j] = i;
+                if ((carry + ex + 1) % B == 0) a.batch_end[j] = i;
             } else {
-                rec_kidx[i] = -1 - (int32_t)ex;
+                a.rec_kidx[i] = -1 - (int32_t)ex;
             }
         }
-        // longest kept record of the batch
+        // longest kept record of the batch: one atomic per warp when the warp lies inside one batch
         const uint32_t j0 = __shfl_sync(0xffffffffu, j, 0);
         if (__all_sync(0xffffffffu, j == j0)) {
             const uint32_t m = __reduce_max_sync(0xffffffffu, len);
-            if ((threadIdx.x & 31) == 0 && m > *(volatile uint32_t*)&batch_lmax[j0]) atomicMax(&batch_lmax[j0], m);
-        } else if (len > *(volatile uint32_t*)&batch_lmax[j]) {
-            atomicMax(&batch_lmax[j], len);
+            if (lane == 0 && m) atomicMax(&a.batch_lmax[j0], m);
+        } else if (len) {
+            atomicMax(&a.batch_lmax[j], len);
         }
-        // K4, first half: segmented max of (offset + 1) per (batch, partition).  Lanes of the warp
-        // that share a key elect one lane that issues the group's only atomic.
+        // K4, first half.  Lanes of the warp that share a (batch, partition) key elect one lane
+        // that issues the group's only atomic.
         uint32_t key = 0xFFFFFFFFu, p = 0;
         long long val = 0;
         if (live) {
-            const uint4 raw = __ldg(reinterpret_cast<const uint4*>(recs) + i);
+            const uint4 raw = __ldg(reinterpret_cast<const uint4*>(a.recs) + i);
             p = raw.y;
             val = (long long)(((uint64_t)raw.w << 32) | raw.z) + 1;
-            if (p < n_partitions) key = j * n_partitions + p;
+            if (p < a.n_partitions) key = j * a.n_partitions + p;
         }
         const unsigned peers = __match_any_sync(0xffffffffu, key);
         const uint32_t vhi = (uint32_t)((unsigned long long)val >> 32), vlo = (uint32_t)val;
         const uint32_t mh = __reduce_max_sync(peers, vhi);
         const uint32_t ml = __reduce_max_sync(peers, vhi == mh ? vlo : 0u);
-        if (key != 0xFFFFFFFFu && (int)(threadIdx.x & 31) == __ffs(peers) - 1)
-            atomicMax(reinterpret_cast<long long*>(&commit[(size_t)p * pitch + j]),
+        if (key != 0xFFFFFFFFu && (int)lane == __ffs(peers) - 1)
+            atomicMax(reinterpret_cast<long long*>(&a.commit[(size_t)p * a.pitch + j]),
                       (long long)(((unsigned long long)mh << 32) | ml));
         if (live && keep[k]) ++ex;
+    }
+    // ---- the last block to get here finishes the plan
+    __threadfence();
+    __syncthreads();
+    if (threadIdx.x == 0) s_last = atomicAdd(&a.ctr[1], 1u) == a.n_tiles - 1 ? 1u : 0u;
+    __syncthreads();
+    if (!s_last) return;
+    __threadfence();
+    const unsigned long long total = *(volatile unsigned long long*)&a.tile_incl[a.n_tiles - 1];
+    const uint32_t n_kept = (uint32_t)(total >> PACK_SHIFT);
+    const unsigned long long n_tokens = total & ((1ull << PACK_SHIFT) - 1);
+    const uint32_t n_closed = (carry + n_kept) / B;
+    if (threadIdx.x == 0) {
+        tk_result_t* res = a.res;
+        res->n_records = n;
+        res->n_kept = n_kept;
+        res->carry_in = carry;
+        res->carry_out = (carry + n_kept) % B;
+        res->n_closed = n_closed;
+        res->batch_size = B;
+        res->n_errors = 0;
+        res->first_error_rec = 0xFFFFFFFFu;
+        res->first_error_status = 0;
+        res->reserved[0] = (uint32_t)(n_tokens > 0xFFFFFFFFull ? 0xFFFFFFFFu : n_tokens);   // elements in the slot
+        a.state->carry_rows = (carry + n_kept) % B;
+        a.ctr[0] = 0;
+        a.ctr[1] = 0;
     }
 }
 
@@ -225,59 +275,95 @@ extern "C" int tk_compact(tk_ctx* ctx, int slot, uint32_t batch_size, void* stre
     TK_REQUIRE(((uint64_t)n + batch_size - 1) / batch_size <= ctx->max_batches,
                "slot with %u records can close more than max_batches=%u batches of %u", n, ctx->max_batches, batch_size);
     ctx->batch_size = batch_size;
-    const uint32_t nblk = (n + CMP_TILE - 1) / CMP_TILE;
-    if (nblk) TK_LAUNCH_PDL(k_compact_count, nblk, CMP_THREADS, st, s.d.rec_kidx, s.d.rec_len, n, s.d.blk_sum);
-    TK_LAUNCH_PDL(k_compact_scan, 1, 1024, st, s.d.blk_sum, nblk, n, batch_size, ctx->max_batches, ctx->d_state,
-                  s.d.result, s.d.batch_end, s.d.batch_lmax, s.d.commit,
-                  (uint32_t)(ctx->n_partitions * ctx->commit_pitch));
-    if (nblk)
-        TK_LAUNCH_PDL(k_compact_apply, nblk, CMP_THREADS, st, s.d.rec_kidx, s.d.rec_len, n, s.d.blk_sum, s.d.result,
-                      s.d.batch_end, s.d.batch_lmax, s.d.recs, s.d.commit, ctx->commit_pitch, ctx->n_partitions);
+    plan_args a;
+    a.rec_kidx = s.d.rec_kidx; a.rec_len = s.d.rec_len; a.recs = s.d.recs;
+    a.n = n; a.n_tiles = n ? (n + CMP_TILE - 1) / CMP_TILE : 1;
+    a.batch_size = batch_size; a.max_batches = ctx->max_batches;
+    a.pitch = ctx->commit_pitch; a.n_partitions = ctx->n_partitions;
+    s.plan_epoch = (s.plan_epoch + 1) & 0x3FFFFFFFu;
+    if (!s.plan_epoch) s.plan_epoch = 1;                   // 0 is the state of a fresh allocation
+    a.epoch = s.plan_epoch;
+    a.state = ctx->d_state; a.res = s.d.result; a.batch_end = s.d.batch_end; a.batch_lmax = s.d.batch_lmax;
+    a.commit = s.d.commit; a.positions = ctx->d_positions;
+    a.tile_agg = s.d.tile_agg; a.tile_incl = s.d.tile_incl; a.tile_flag = s.d.tile_flag; a.ctr = s.d.plan_ctr;
+    TK_LAUNCH_PDL(k_plan, a.n_tiles, CMP_THREADS, st, a);
     return 0;
 }
 
-// ------------------------------------------------------------------------ K4
-// First half (segmented max per (batch, partition)) runs inside k_compact_apply, where the
-// batch index of every record is at hand.  Second half:
-// Running max along the batch axis, one block per partition.
-__global__ void __launch_bounds__(128) k_commit_scan(int64_t* __restrict__ commit, uint32_t pitch,
-                                                      const tk_result_t* __restrict__ res,
-                                                      int64_t* __restrict__ positions) {
-    __shared__ long long chunk_max[128];
+// ------------------------------------------------------------------------ K4, second half
+// Running max along the batch axis of every partition, seeded with the positions earlier slots
+// left behind.  One block; the (partition, batch) matrix is staged through shared memory in
+// chunks: one round of independent loads, then thread p runs the max along the batch axis of
+// partition p out of shared memory, then one round of stores -- three memory latencies per
+// chunk instead of one per partition.
+//
+// Nothing on the device consumes the result (the host reads it with the slot's result block), so
+// tk_process_slot launches this kernel *behind* the decode kernel with wait_for_prior = 0: the
+// decode kernel releases its dependents only after its own griddepcontrol.wait, i.e. once the
+// plan is complete and visible, and this block then runs next to the decode kernel's blocks
+// instead of in front of them.
+#define PLAN_STAGE 4096u      // int64 entries of the staging buffer (32 KiB)
+__global__ void __launch_bounds__(256) k_commit_final(int64_t* __restrict__ commit, uint32_t pitch,
+                                                       uint32_t n_partitions, const tk_result_t* __restrict__ res,
+                                                       int64_t* __restrict__ positions, int wait_for_prior) {
+    __shared__ long long s_stage[PLAN_STAGE];
     tk_pdl_launch_dependents();
-    tk_pdl_wait();
-    const uint32_t p = blockIdx.x;
-    const uint32_t nb = res->n_closed + 1;                 // closed batches + the open one
-    int64_t* row = commit + (size_t)p * pitch;
-    const uint32_t per = (nb + blockDim.x - 1) / blockDim.x;
-    const uint32_t a = threadIdx.x * per;
-    const uint32_t b = min(a + per, nb);
-    long long m = -1;
-    for (uint32_t j = a; j < b; ++j) { long long v = row[j]; m = v > m ? v : m; }
-    chunk_max[threadIdx.x] = m;
-    __syncthreads();
-    long long run = positions[p];
-    for (uint32_t t = 0; t < threadIdx.x; ++t) { long long v = chunk_max[t]; run = v > run ? v : run; }
-    for (uint32_t j = a; j < b; ++j) {
-        long long v = row[j];
-        run = v > run ? v : run;
-        row[j] = run;
+    if (wait_for_prior) tk_pdl_wait();
+    const uint32_t nb = __ldcg(&res->n_closed) + 1;                  // closed batches + the open one
+    for (uint32_t p0 = 0; p0 < n_partitions; p0 += blockDim.x) {
+        const uint32_t pg = min(blockDim.x, n_partitions - p0);
+        const uint32_t J = max(1u, PLAN_STAGE / pg - 1u);   // batches per chunk (row stride J | 1 <= J + 1)
+        long long run = threadIdx.x < pg ? positions[p0 + threadIdx.x] : -1;
+        for (uint32_t j0 = 0; j0 < nb; j0 += J) {
+            const uint32_t jn = min(J, nb - j0), stride = jn | 1u;
+            // (ld.cg: the maxima were produced by atomics of other SMs and live in L2.)  Eight loads
+            // per thread are issued before the first is used.
+            const uint32_t total = pg * jn;
+            for (uint32_t x0 = threadIdx.x; x0 < total; x0 += blockDim.x * 8) {
+                long long v[8];
+#pragma unroll
+                for (int k = 0; k < 8; ++k) {
+                    const uint32_t x = x0 + k * blockDim.x;
+                    const uint32_t pp = x / jn, jj = x - pp * jn;
+                    v[k] = x < total ? __ldcg(reinterpret_cast<const long long*>(&commit[(size_t)(p0 + pp) * pitch + j0 + jj])) : 0;
+                }
+#pragma unroll
+                for (int k = 0; k < 8; ++k) {
+                    const uint32_t x = x0 + k * blockDim.x;
+                    const uint32_t pp = x / jn, jj = x - pp * jn;
+                    if (x < total) s_stage[pp * stride + jj] = v[k];
+                }
+            }
+            __syncthreads();
+            if (threadIdx.x < pg) {
+                long long* row = s_stage + threadIdx.x * stride;
+                for (uint32_t jj = 0; jj < jn; ++jj) {
+                    const long long v = row[jj];
+                    run = v > run ? v : run;
+                    row[jj] = run;
+                }
+            }
+            __syncthreads();
+            for (uint32_t x = threadIdx.x; x < pg * jn; x += blockDim.x) {
+                const uint32_t pp = x / jn, jj = x - pp * jn;
+                commit[(size_t)(p0 + pp) * pitch + j0 + jj] = s_stage[pp * stride + jj];
+            }
+            __syncthreads();
+        }
+        if (threadIdx.x < pg) positions[p0 + threadIdx.x] = run;
     }
-    __syncthreads();
-    if (threadIdx.x == blockDim.x - 1) {
-        // last thread's run covers every chunk only if it owned the tail; recompute the global max
-        long long g = positions[p];
-        for (uint32_t t = 0; t < blockDim.x; ++t) { long long v = chunk_max[t]; g = v > g ? v : g; }
-        positions[p] = g;
-    }
+}
+
+int tk_commit_final(tk_ctx* ctx, int slot, int wait_for_prior, void* stream) {
+    TK_ENTER(ctx, slot);
+    tk_slot& s = ctx->slots[slot];
+    TK_LAUNCH_PDL(k_commit_final, 1, 256, (cudaStream_t)stream, s.d.commit, ctx->commit_pitch, ctx->n_partitions,
+                  (const tk_result_t*)s.d.result, ctx->d_positions, wait_for_prior);
+    return 0;
 }
 
 extern "C" int tk_commit_offsets(tk_ctx* ctx, int slot, void* stream) {
-    TK_ENTER(ctx, slot);
-    tk_slot& s = ctx->slots[slot];
-    cudaStream_t st = (cudaStream_t)stream;
-    TK_LAUNCH_PDL(k_commit_scan, ctx->n_partitions, 128, st, s.d.commit, ctx->commit_pitch, s.d.result, ctx->d_positions);
-    return 0;
+    return tk_commit_final(ctx, slot, 1, stream);
 }
 
 // ------------------------------------------------------------------------ carry

@@ -19,7 +19,6 @@ extern "C" int tk_process_slot(tk_ctx* ctx, int slot, const tk_job_t* job, void*
     else rc = tk_raw_scan(ctx, slot, job->record_bytes, stream);
     if (rc) return rc;
     rc = tk_compact(ctx, slot, job->batch_size, stream); if (rc) return rc;
-    rc = tk_commit_offsets(ctx, slot, stream); if (rc) return rc;
     tk_slot& s = ctx->slots[slot];
     s.dec_timed = false;
     if (ctx->timing) TK_CUDA(cudaEventRecord(s.ev_dec0, (cudaStream_t)stream));
@@ -41,6 +40,11 @@ extern "C" int tk_process_slot(tk_ctx* ctx, int slot, const tk_job_t* job, void*
     }
     if (rc) return rc;
     if (ctx->timing) { TK_CUDA(cudaEventRecord(s.ev_dec1, (cudaStream_t)stream)); s.dec_timed = true; }
+    // commit offsets, second half: next to the decode kernel, not in front of it (tk_plan.cu).  With
+    // no records there was no decode kernel to order it behind the plan, and with timing events in
+    // between the chain is cut anyway: wait then.
+    rc = tk_commit_final(ctx, slot, (s.n_records == 0 || ctx->timing) ? 1 : 0, stream);
+    if (rc) return rc;
     return tk_slot_fetch_result(ctx, slot, stream);
 }
 

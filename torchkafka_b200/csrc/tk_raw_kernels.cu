@@ -52,8 +52,8 @@ __global__ void __launch_bounds__(256) k_collate_raw(const uint8_t* __restrict__
                                                       const int32_t* __restrict__ rec_kidx,
                                                       const int32_t* __restrict__ rec_status,
                                                       tk_result_t* res, tk_plane_t out) {
-    tk_pdl_launch_dependents();
     tk_pdl_wait();
+    tk_pdl_launch_dependents();             // after the wait: see k_commit_final (tk_plan.cu)
     const uint32_t total = n * chunks_per_rec;
     for (uint32_t x = blockIdx.x * blockDim.x + threadIdx.x; x < total; x += gridDim.x * blockDim.x) {
         const uint32_t i = x / chunks_per_rec;
@@ -174,8 +174,8 @@ __global__ void __launch_bounds__(IMG_THREADS) k_collate_image(const uint8_t* __
                                                                tk_result_t* res, tk_plane_t out) {
     __shared__ __align__(16) uint8_t s_in[IMG_PIX * C];
     __shared__ uint32_t s_lut[C * 32 * 32];
-    tk_pdl_launch_dependents();
     tk_pdl_wait();
+    tk_pdl_launch_dependents();             // after the wait: see k_commit_final (tk_plan.cu)
     // table: word (c*32 + row)*32 + 4*g + q holds entries x = 8*row + 2*q (low half) and x + 1 (high half)
     for (uint32_t w = threadIdx.x; w < C * 32 * 32; w += IMG_THREADS) {
         const uint32_t col = w & 31u, row = (w >> 5) & 31u, c = w >> 10;
@@ -255,8 +255,8 @@ __global__ void __launch_bounds__(IMG_THREADS) k_collate_image_fma(const uint8_t
                                                                    const img_consts k,
                                                                    tk_result_t* res, tk_plane_t out) {
     __shared__ __align__(16) uint8_t s_in[IMG_PIX * C];
-    tk_pdl_launch_dependents();
     tk_pdl_wait();
+    tk_pdl_launch_dependents();             // after the wait: see k_commit_final (tk_plan.cu)
     const uint32_t total_tiles = n * tiles_per_img;
     for (uint32_t job = blockIdx.x; job < total_tiles; job += gridDim.x) {
         const uint32_t i = job / tiles_per_img;

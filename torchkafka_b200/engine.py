@@ -31,10 +31,10 @@ REC_DTYPE = np.dtype([("start", "<u4"), ("partition", "<i4"), ("offset", "<i8")]
 
 #: a slot never closes more batches than this (bounds the commit matrix)
 MAX_BATCHES_CAP = 16384
-#: kernels launched per slot by ``process`` (JSON: carry, scan, 3x compact, commit scan, decode
-#: (rows + parse in one kernel); raw: carry, scan, 3x compact, commit scan, collate)
-LAUNCHES_PER_SLOT_JSON = 7
-LAUNCHES_PER_SLOT_RAW = 7
+#: kernels launched per slot by ``process``: carry rows, scan, plan (compaction + commit maxima,
+#: one kernel), decode / collate (one kernel), commit running max (one block, beside the decode)
+LAUNCHES_PER_SLOT_JSON = 5
+LAUNCHES_PER_SLOT_RAW = 5
 
 
 def _np_view(ptr: int, nbytes: int, dtype) -> np.ndarray:

@@ -129,7 +129,10 @@ int tk_raw_scan(tk_ctx* ctx, int slot, uint64_t record_bytes, void* stream);
  * replaces `if data is not None: yield data` (src/kafka_dataset.py:161-162) and
  * the batch_size loop of _IterableDatasetFetcher.fetch (fetch.py:33-38) */
 /* (the same pass also accumulates, per (batch, partition), the largest offset + 1 it sees:
- * the segmented-max half of K4, done here because the batch index of each record is at hand) */
+ * the segmented-max half of K4, done here because the batch index of each record is at hand)
+ * Call order per slot pass: one scan (tk_json_scan or tk_raw_scan -- it also resets the
+ * per-batch outputs this call accumulates into), then tk_compact, then tk_commit_offsets and
+ * the decode / collate call in either order. */
 int tk_compact(tk_ctx* ctx, int slot, uint32_t batch_size, void* stream);
 
 /* ---- K4: per batch, per partition: max(offset)+1 over every record consumed up

@@ -133,6 +133,23 @@ static inline int tk_check_slot(tk_ctx* ctx, int slot) {
 __device__ __forceinline__ void tk_pdl_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;"); }
 __device__ __forceinline__ void tk_pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
 
+// Outputs of the plan kernel (tk_plan.cu) that accumulate with atomics start from a clean state:
+// commit matrix -1 ("partition not seen"), per-batch longest record 0, closing record n - 1.
+// The scan kernels do this (grid-stride, every thread a few entries) because they run before
+// the plan and every thread of a large grid is at hand; tk_compact relies on it.
+struct tk_plan_reset {
+    int64_t*  commit;
+    uint32_t* batch_end;
+    uint32_t* batch_lmax;
+    uint32_t  commit_elems;    // n_partitions * commit_pitch
+    uint32_t  n_batches;       // max_batches + 1
+    uint32_t  last_record;     // n ? n - 1 : 0
+};
+__device__ __forceinline__ void tk_plan_reset_run(const tk_plan_reset& r, uint32_t gtid, uint32_t nthreads) {
+    for (uint32_t x = gtid; x < r.commit_elems; x += nthreads) r.commit[x] = -1;
+    for (uint32_t j = gtid; j < r.n_batches; j += nthreads) { r.batch_end[j] = r.last_record; r.batch_lmax[j] = 0; }
+}
+
 #define TK_LAUNCH_PDL(kernel, grid, block, strm__, ...)                                         \
     do {                                                                                        \
         cudaLaunchConfig_t cfg__ = {};                                                          \
@@ -150,6 +167,7 @@ __device__ __forceinline__ void tk_pdl_wait() { asm volatile("griddepcontrol.wai
 #endif
 
 int tk_ensure_token_arrays(tk_ctx* ctx);
+tk_plan_reset tk_plan_reset_args(tk_ctx* ctx, int slot);
 // K4 second half; wait_for_prior = 0 only behind a kernel that released its dependents after its own wait
 int tk_commit_final(tk_ctx* ctx, int slot, int wait_for_prior, void* stream);
 

@@ -51,6 +51,7 @@ struct scan_args {
     uint32_t*       tok_count;
     uint32_t*       tok_count_next;   // counter of the slot's next scan: zeroed here
     uint32_t        tok_cap;
+    tk_plan_reset   reset;
 };
 
 // comma bits of one 16-byte chunk restricted to the record
@@ -71,6 +72,7 @@ __global__ void __launch_bounds__(256) k_json_scan(const scan_args a) {
     tk_pdl_launch_dependents();
     tk_pdl_wait();
     if (blockIdx.x == 0 && threadIdx.x == 0) *a.tok_count_next = 0;
+    tk_plan_reset_run(a.reset, blockIdx.x * blockDim.x + threadIdx.x, gridDim.x * blockDim.x);
     const uint32_t lane = threadIdx.x & 31;
     const uint32_t lt_mask = (1u << lane) - 1u;
     const uint32_t warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
@@ -189,18 +191,18 @@ extern "C" int tk_json_scan(tk_ctx* ctx, int slot, uint32_t max_len, uint32_t mi
     int rc = tk_ensure_token_arrays(ctx);
     if (rc) return rc;
     cudaStream_t st = (cudaStream_t)stream;
-    if (!n) return 0;
-    scan_args a;
+    scan_args a;                                           // (an empty slot still resets the plan outputs)
     a.bytes = s.d.bytes; a.recs = s.d.recs; a.n = n; a.max_len = max_len; a.min_size = min_size;
     a.rec_len = s.d.rec_len; a.rec_status = s.d.rec_status; a.rec_kidx = s.d.rec_kidx; a.rec_tok = s.d.rec_tok;
     // the counter of this use was zeroed by the previous scan of the slot (or at allocation)
     s.tok_use++;
     a.tok = s.d.tok_pos; a.tok_count = s.d.tok_count + (s.tok_use & 1u); a.tok_count_next = s.d.tok_count + ((s.tok_use + 1) & 1u);
     a.tok_cap = (uint32_t)(ctx->tok_cap > 0xFFFFFFFFull ? 0xFFFFFFFFull : ctx->tok_cap);
+    a.reset = tk_plan_reset_args(ctx, slot);
     // one warp per record; 4-warp blocks: records differ in length, and a block holds its
     // slots until its longest record is done
     const uint32_t threads = 128, wpb = threads / 32;
-    const uint32_t blocks = (n + wpb - 1) / wpb;
+    const uint32_t blocks = max((n + wpb - 1) / wpb, 1u);
     TK_LAUNCH_PDL(k_json_scan, blocks, threads, st, a);
     return 0;
 }

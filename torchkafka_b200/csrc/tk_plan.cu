@@ -87,8 +87,8 @@ __device__ __forceinline__ unsigned long long block_excl_scan64(unsigned long lo
 //   K4 first half: segmented max of (offset + 1) per (batch, partition) into the commit matrix.
 // The block that finishes last writes the result header and advances the carry.  K4's second
 // half (running max along the batch axis) is k_commit_final below.
-// Tile 0 initialises the per-batch arrays and the commit matrix before it publishes anything;
-// every other tile reaches its apply phase only after (transitively) seeing tile 0's flag.
+// The per-batch arrays and the commit matrix were reset by the scan kernel of the slot
+// (tk_plan_reset, tk_internal.h).
 struct plan_args {
     int32_t*        rec_kidx;
     const int32_t*  rec_len;
@@ -167,15 +167,6 @@ __global__ void __launch_bounds__(CMP_THREADS) k_plan(const plan_args a) {
         c += ((unsigned long long)keep[k] << PACK_SHIFT) + lens[k];
     }
     const unsigned long long in_tile = block_excl_scan64(c, &tot);
-    if (tile == 0) {
-        for (uint32_t j = threadIdx.x; j <= a.max_batches; j += blockDim.x) {
-            a.batch_end[j] = n ? n - 1 : 0;
-            a.batch_lmax[j] = 0;
-        }
-        for (uint32_t x = threadIdx.x; x < a.n_partitions * a.pitch; x += blockDim.x) a.commit[x] = -1;
-        __threadfence();
-        __syncthreads();
-    }
     if (threadIdx.x < 32) {
         if (lane == 0) {
             a.tile_agg[tile] = tot;
@@ -354,12 +345,62 @@ __global__ void __launch_bounds__(256) k_commit_final(int64_t* __restrict__ comm
     }
 }
 
+// Many batches per slot (small batch sizes): one block per partition, every thread a contiguous
+// chunk of the batch axis, two passes (chunk maxima, then the running max).
+__global__ void __launch_bounds__(128) k_commit_rows(int64_t* __restrict__ commit, uint32_t pitch,
+                                                      const tk_result_t* __restrict__ res,
+                                                      int64_t* __restrict__ positions, int wait_for_prior) {
+    __shared__ long long chunk_max[128];
+    tk_pdl_launch_dependents();
+    if (wait_for_prior) tk_pdl_wait();
+    const uint32_t p = blockIdx.x;
+    const uint32_t nb = __ldcg(&res->n_closed) + 1;
+    long long* row = reinterpret_cast<long long*>(commit) + (size_t)p * pitch;
+    const uint32_t per = (nb + blockDim.x - 1) / blockDim.x;
+    const uint32_t a = threadIdx.x * per;
+    const uint32_t b = min(a + per, nb);
+    long long m = -1;
+    for (uint32_t j = a; j < b; ++j) { const long long v = __ldcg(row + j); m = v > m ? v : m; }
+    chunk_max[threadIdx.x] = m;
+    __syncthreads();
+    long long run = positions[p];
+    for (uint32_t t = 0; t < threadIdx.x; ++t) { const long long v = chunk_max[t]; run = v > run ? v : run; }
+    for (uint32_t j = a; j < b; ++j) {
+        const long long v = __ldcg(row + j);
+        run = v > run ? v : run;
+        row[j] = run;
+    }
+    __syncthreads();
+    if (threadIdx.x == blockDim.x - 1) {
+        long long g = positions[p];
+        for (uint32_t t = 0; t < blockDim.x; ++t) { const long long v = chunk_max[t]; g = v > g ? v : g; }
+        positions[p] = g;
+    }
+}
+
 int tk_commit_final(tk_ctx* ctx, int slot, int wait_for_prior, void* stream) {
     TK_ENTER(ctx, slot);
     tk_slot& s = ctx->slots[slot];
-    TK_LAUNCH_PDL(k_commit_final, 1, 256, (cudaStream_t)stream, s.d.commit, ctx->commit_pitch, ctx->n_partitions,
-                  (const tk_result_t*)s.d.result, ctx->d_positions, wait_for_prior);
+    // upper bound of the batches this slot can touch: carry < B, kept <= n
+    const uint32_t B = ctx->batch_size ? ctx->batch_size : 1;
+    const uint64_t nb_bound = ((uint64_t)s.n_records + B - 1) / B + 1;
+    if (nb_bound <= 64)
+        TK_LAUNCH_PDL(k_commit_final, 1, 256, (cudaStream_t)stream, s.d.commit, ctx->commit_pitch, ctx->n_partitions,
+                      (const tk_result_t*)s.d.result, ctx->d_positions, wait_for_prior);
+    else
+        TK_LAUNCH_PDL(k_commit_rows, ctx->n_partitions, 128, (cudaStream_t)stream, s.d.commit, ctx->commit_pitch,
+                      (const tk_result_t*)s.d.result, ctx->d_positions, wait_for_prior);
     return 0;
+}
+
+tk_plan_reset tk_plan_reset_args(tk_ctx* ctx, int slot) {
+    tk_slot& s = ctx->slots[slot];
+    tk_plan_reset r;
+    r.commit = s.d.commit; r.batch_end = s.d.batch_end; r.batch_lmax = s.d.batch_lmax;
+    r.commit_elems = (uint32_t)(ctx->n_partitions * ctx->commit_pitch);
+    r.n_batches = ctx->max_batches + 1;
+    r.last_record = s.n_records ? s.n_records - 1 : 0;
+    return r;
 }
 
 extern "C" int tk_commit_offsets(tk_ctx* ctx, int slot, void* stream) {

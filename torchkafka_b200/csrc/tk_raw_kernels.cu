@@ -17,10 +17,12 @@ __device__ __forceinline__ void raw_report_error(tk_result_t* res, uint32_t rec,
 // every record is kept; a record of the wrong size is an error
 __global__ void __launch_bounds__(256) k_raw_scan(const tk_rec_t* __restrict__ recs, uint32_t n,
                                                    uint64_t record_bytes, int32_t* __restrict__ rec_len,
-                                                   int32_t* __restrict__ rec_status, int32_t* __restrict__ rec_kidx) {
+                                                   int32_t* __restrict__ rec_status, int32_t* __restrict__ rec_kidx,
+                                                   const tk_plan_reset reset) {
     tk_pdl_launch_dependents();
     tk_pdl_wait();
     const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    tk_plan_reset_run(reset, i, gridDim.x * blockDim.x);
     if (i >= n) return;
     const uint32_t len = recs[i + 1].start - recs[i].start;
     rec_len[i] = (int32_t)len;
@@ -32,10 +34,9 @@ __global__ void __launch_bounds__(256) k_raw_scan(const tk_rec_t* __restrict__ r
 extern "C" int tk_raw_scan(tk_ctx* ctx, int slot, uint64_t record_bytes, void* stream) {
     TK_ENTER(ctx, slot);
     tk_slot& s = ctx->slots[slot];
-    const uint32_t n = s.n_records;
-    if (!n) return 0;
-    TK_LAUNCH_PDL(k_raw_scan, (n + 255) / 256, 256, (cudaStream_t)stream, s.d.recs, n, record_bytes, s.d.rec_len,
-                  s.d.rec_status, s.d.rec_kidx);
+    const uint32_t n = s.n_records;                        // (an empty slot still resets the plan outputs)
+    TK_LAUNCH_PDL(k_raw_scan, max((n + 255) / 256, 1u), 256, (cudaStream_t)stream, s.d.recs, n, record_bytes, s.d.rec_len,
+                  s.d.rec_status, s.d.rec_kidx, tk_plan_reset_args(ctx, slot));
     return 0;
 }
 

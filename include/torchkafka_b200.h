@@ -57,7 +57,8 @@ typedef enum {
     TK_STATUS_TOO_LONG = 3,     /* more than max_len elements */
     TK_STATUS_UNSUPPORTED = 4,  /* valid JSON outside the numeric-array schema */
     TK_STATUS_SIZE = 5,         /* raw record with the wrong byte count */
-    TK_STATUS_RAGGED = 6        /* fixed_len schema, other length (torch.stack raises) */
+    TK_STATUS_RAGGED = 6,       /* fixed_len schema, other length (torch.stack raises) */
+    TK_STATUS_CORRUPT = 7       /* record batch failed its CRC or framing (kafka CorruptRecordException) */
 } tk_status_t;
 
 /* Per-slot result header, written by the kernels, fetched with tk_slot_fetch_result. */
@@ -217,6 +218,55 @@ int tk_process_slot(tk_ctx* ctx, int slot, const tk_job_t* job, void* stream);
 #define TK_NOALLOC_MAX_RECORDS (1u << 20)
 int tk_compact_noalloc(const int32_t* d_keep, uint32_t n, uint32_t batch_size, uint32_t carry_in,
                        int32_t* d_kidx, tk_result_t* d_result, void* stream);
+
+/* ---- Kafka RecordBatch v2 blobs -> slot -----------------------
+ * The step before the path on real topics.  The host copies each fetched partition's
+ * `records` field (a sequence of RecordBatch v2, magic 2, as kafka-python's fetcher receives
+ * it; kafka/record/default_records.py and kafka/consumer/fetcher.py of the reference's
+ * dependency kafka-python >= 2.0.2, setup.py:9) unparsed into the slot's pinned byte buffer
+ * (tk_slot_host_ptrs) and describes the blobs; the device validates every batch (CRC-32C),
+ * splits it at its varint record framing and builds the slot's CSR.  Replaces, per record,
+ * the ConsumerRecord that `for record in self._consumer` (src/kafka_dataset.py:156) yields.
+ *   - a batch that is cut off by the end of its blob is ignored (fetch responses end so)
+ *   - records with offset < fetch_offset are skipped (batches are returned whole)
+ *   - control batches are skipped; compressed batches and null values surface as
+ *     TK_STATUS_UNSUPPORTED, CRC / framing errors as TK_STATUS_CORRUPT on the first record
+ *     of the batch, when the batch that contains it is delivered
+ *   - offset_delta is added to every offset (0 for real fetch responses; lets a test log be
+ *     replayed at higher offsets without re-encoding) */
+typedef struct tk_blob {
+    uint32_t start;          /* first byte of the blob in the slot's byte buffer */
+    uint32_t length;
+    int32_t  partition;      /* dense partition index, as in tk_rec_t */
+    uint32_t reserved;
+    int64_t  fetch_offset;
+    int64_t  offset_delta;
+} tk_blob_t;
+typedef struct tk_rb_summary {
+    uint32_t n_records;      /* records in the slot, including skipped ones */
+    uint32_t n_batches;
+    uint64_t n_bytes;        /* value bytes in the slot */
+    uint32_t status;         /* TK_RB_* */
+    uint32_t reserved;
+} tk_rb_summary_t;
+enum { TK_RB_OK = 0, TK_RB_TOO_MANY_BATCHES = 1, TK_RB_TOO_MANY_RECORDS = 2, TK_RB_TOO_MANY_BYTES = 3 };
+#define TK_MAX_BLOBS 1024u
+/* flags the split leaves in tk_rec_t.partition (the scans act on them) */
+#define TK_REC_DROPPED     0x40000000   /* below the fetch offset / control batch: not consumed */
+#define TK_REC_CORRUPT     0x20000000
+#define TK_REC_UNSUPPORTED 0x10000000
+#define TK_REC_FLAGS       0x70000000
+/* raw bytes are in the slot's pinned buffer [0, n_bytes); asynchronous (H2D + kernels on the
+ * library's copy stream); tk_process_slot / tk_slot_wait order behind it as behind tk_slot_submit */
+int tk_slot_submit_recordbatches(tk_ctx* ctx, int slot, uint64_t n_bytes, const tk_blob_t* blobs,
+                                 uint32_t n_blobs);
+/* wait for the split; the slot then holds summary->n_records records.  A non-zero
+ * summary->status means the slot geometry was too small and nothing was written. */
+int tk_slot_recordbatch_result(tk_ctx* ctx, int slot, tk_rb_summary_t* summary);
+/* one record header of the device twin (error reports) */
+int tk_slot_record(tk_ctx* ctx, int slot, uint32_t index, tk_rec_t* out);
+/* host-side CRC-32C (Castagnoli) for integrators that build or check batches themselves */
+uint32_t tk_crc32c(const void* data, uint64_t n, uint32_t crc);
 
 /* Measurement aid (no counterpart in the reference): with timing enabled, tk_process_slot
  * brackets the decode / collate kernels of every slot with two CUDA events on `stream`;

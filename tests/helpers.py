@@ -16,8 +16,9 @@ from torchkafka_b200.testing import stub_kafka as sk  # noqa: E402
 from oracle import reference_path as ref  # noqa: E402
 
 
-def make_dataset(log, schema, slot_bytes=None, use_packed=True, **attrs):
+def make_dataset(log, schema, slot_bytes=None, use_packed=True, consumer_kwargs=None, **attrs):
     _Consumer = sk.KafkaConsumer if use_packed else sk.PollOnlyConsumer
+    extra = dict(consumer_kwargs or {})
 
     class DS(KafkaDataset):
         payload_schema = schema
@@ -25,7 +26,7 @@ def make_dataset(log, schema, slot_bytes=None, use_packed=True, **attrs):
         @classmethod
         def new_consumer(cls, *a, **k):
             k.pop("enable_auto_commit", None)
-            return _Consumer(*a, log=log, **k)
+            return _Consumer(*a, log=log, **extra, **k)
 
     if slot_bytes is not None:
         DS.device_slot_bytes = slot_bytes

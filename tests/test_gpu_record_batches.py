@@ -1,0 +1,201 @@
+"""GPU parity of the record-batch input: the same log served as RecordBatch v2
+blobs (`poll_raw`, CRC-32C + varint framing on the device) must give bit-identical batches and
+commits to the oracle iterating ConsumerRecords; malformed batches surface like kafka-python's
+CorruptRecordException would, at the batch that contains them."""
+import json
+
+import numpy as np
+import pytest
+import torch
+
+from helpers import assert_same, make_dataset, run_gpu, run_oracle
+from oracle import record_batch as orb
+from torchkafka_b200.engine import SlotEngine
+from torchkafka_b200.schema import ImageU8, JsonArray, PayloadError, RawBytes, TokenList
+from torchkafka_b200.testing import record_batch as rb
+from torchkafka_b200.testing import synthetic as syn
+from torchkafka_b200.testing.stub_kafka import RecordLog
+
+pytestmark = pytest.mark.gpu
+
+
+def check_raw(log, schema, batch_size, batch_bytes=16384, **kw):
+    gpu = run_gpu(log, schema, batch_size, device_input="raw",
+                  consumer_kwargs={"raw_batch_bytes": batch_bytes}, **kw)
+    cpu = run_oracle(log, schema, batch_size)
+    assert_same(gpu, cpu, schema)
+    return gpu
+
+
+@pytest.mark.parametrize("layout,chunk,batch_bytes", [("chunked", 500, 16384), ("chunked", 37, 3000),
+                                                      ("roundrobin", 1, 16384), ("chunked", 500, 1 << 20)])
+def test_cfg2_from_record_batches(layout, chunk, batch_bytes):
+    log = syn.make_log(2, 6000, seed=21, partitions=8, layout=layout, chunk=chunk)
+    check_raw(log, JsonArray(torch.float32, max_len=256, min_size=32), 256, batch_bytes=batch_bytes)
+
+
+def test_cfg2_small_slots_many_fetches():
+    log = syn.make_log(2, 3000, seed=22, partitions=4, layout="chunked", chunk=100)
+    check_raw(log, JsonArray(torch.float32, max_len=256, min_size=32), 64, slot_bytes=200_000, batch_bytes=8192)
+
+
+def test_cfg3_tokens_from_record_batches():
+    log = syn.make_log(3, 800, seed=23, partitions=8, layout="chunked", chunk=50)
+    check_raw(log, TokenList(torch.int32, max_len=2048), 32, batch_bytes=65536)
+
+
+def test_cfg5_small_records_from_record_batches():
+    log = syn.make_log(5, 20000, seed=24, partitions=16, layout="chunked", chunk=500)
+    check_raw(log, RawBytes((64,), torch.uint8), 256)
+
+
+def test_cfg4_images_from_record_batches():
+    log = syn.make_log(4, 24, seed=25, partitions=4, layout="chunked", chunk=3)
+    check_raw(log, ImageU8(224, 224, 3), 8, batch_bytes=1 << 20, slot_bytes=24 * 150528 + (1 << 20))
+
+
+# ---------------------------------------------------------------- the split itself, blob by blob
+def split_on_gpu(blobs, slot_bytes=1 << 20, slot_records=4096, schema=None):
+    """blobs: [(partition, bytes, fetch_offset, offset_delta)] -> (engine, n, nbytes) after the split."""
+    eng = SlotEngine(schema or RawBytes((1,), torch.uint8), 4, slot_bytes=slot_bytes, slot_records=slot_records,
+                     n_slots=2, device=0, n_partitions=16)
+    hb, _ = eng.host_views(0)
+    pos, desc = 0, []
+    for p, data, fo, delta in blobs:
+        hb[pos:pos + len(data)] = np.frombuffer(data, dtype=np.uint8)
+        desc.append((pos, len(data), p, fo, delta))
+        pos += len(data)
+    eng.submit_recordbatches(0, pos, desc)
+    n, nbytes, nbatches = eng.recordbatch_result(0)
+    return eng, n, nbytes, nbatches
+
+
+def device_records(eng, n, nbytes):
+    """(start, partition with flags, offset) of every record header of slot 0's device twin, plus
+    the closing entry."""
+    from torchkafka_b200 import _native
+    import ctypes as C
+    recs = []
+    for i in range(n + 1):
+        r = _native.TkRec()
+        _native.check(eng.lib.tk_slot_record(eng.ctx, 0, i, C.byref(r)))
+        recs.append((int(r.start), int(r.partition), int(r.offset)))
+    return recs
+
+
+def test_split_headers_match_the_oracle():
+    rng = np.random.default_rng(5)
+    vals = [bytes(rng.integers(0, 256, int(k), dtype=np.uint8)) for k in rng.integers(0, 700, 300)]
+    blob_a = b"".join(rb.encode_batch(100 + 50 * j, vals[50 * j:50 * j + 50]) for j in range(3))
+    blob_b = rb.encode_batch(7, vals[150:300], keys=[b"key%d" % i if i % 3 else None for i in range(150)],
+                             headers=[[(b"h", b"x" * (i % 5))] if i % 4 == 0 else [] for i in range(150)])
+    cut = blob_a + rb.encode_batch(250, [b"never complete"])[:-3]          # response ends mid-batch
+    blobs = [(3, cut, 120, 0), (5, blob_b, 0, 1000)]
+    eng, n, nbytes, nbatches = split_on_gpu(blobs)
+    want = []
+    for p, data, fo, delta in blobs:
+        # the device keeps skipped records as flagged entries; the oracle drops them
+        want += [(r.partition, r.offset, r.value) for r in orb.split_blob(data, p, 0, delta)]
+    assert nbatches == 4 and n == len(want) == 300
+    recs = device_records(eng, n, nbytes)
+    from torchkafka_b200 import _native
+    kept_bytes = 0
+    for (start, part, off), (p, o, v), nxt in zip(recs, want, recs[1:]):
+        dropped = p == 3 and o < 120
+        assert part == (p | (0x40000000 if dropped else 0)) and off == o
+        assert nxt[0] - start == (0 if dropped else len(v))
+        kept_bytes += 0 if dropped else len(v)
+    assert recs[-1][0] == nbytes == kept_bytes
+    eng.close()
+
+
+def run_blobs(blobs, schema, batch_size):
+    """Drive the public API with a consumer that serves exactly these blobs in one fetch."""
+    from torchkafka_b200.testing import stub_kafka as sk
+
+    class OneFetch(sk.KafkaConsumer):
+        def poll_raw(self, max_bytes, max_records):
+            if getattr(self, "_served", False):
+                return None
+            self._served = True
+            return sk.RawFetch([(p, np.frombuffer(d, dtype=np.uint8), fo, delta) for p, d, fo, delta in blobs])
+
+    from torchkafka_b200 import KafkaDataset, auto_commit
+    from torch.utils.data import DataLoader
+
+    class DS(KafkaDataset):
+        payload_schema = schema
+        device_input = "raw"
+
+        @classmethod
+        def new_consumer(cls, *a, **k):
+            k.pop("enable_auto_commit", None)
+            return OneFetch(*a, log=RecordLog([], [], []), **k)
+
+    ds = DS("topic", group_id="g")
+    out = [b for b in auto_commit(DataLoader(ds, batch_size=batch_size))]
+    commits = list(ds._consumer.committed_log)
+    ds.close()
+    return out, commits
+
+
+def jvals(lo, hi):
+    return [json.dumps([float(i), i + 0.5]).encode() for i in range(lo, hi)]
+
+
+def test_fetch_offset_skips_records_and_control_batches_are_invisible():
+    blob = (rb.encode_batch(10, jvals(10, 16)) + rb.encode_batch(16, [b"\x00\x00\x00\x01"], attributes=0x20) +
+            rb.encode_batch(17, jvals(17, 20)))
+    out, commits = run_blobs([(2, blob, 13, 0)], JsonArray(torch.float32, fixed_len=2), 3)
+    got = torch.cat([b.cpu() for b in out])
+    assert got[:, 0].tolist() == [13.0, 14.0, 15.0, 17.0, 18.0, 19.0]
+    assert commits == [{2: 16}, {2: 20}]
+
+
+@pytest.mark.parametrize("damage,status", [("crc", 7), ("varint", 7), ("magic", 7), ("count", 7), ("codec", 4), ("null", 4)])
+def test_broken_batches_raise_at_their_batch(damage, status):
+    good = rb.encode_batch(0, jvals(0, 4))
+    bad = bytearray(rb.encode_batch(4, jvals(4, 8)))
+    if damage == "crc":
+        bad[70] ^= 0x40
+    elif damage == "magic":
+        bad[16] = 1
+    elif damage == "codec":
+        bad = bytearray(rb.encode_batch(4, jvals(4, 8), attributes=3))
+    elif damage == "null":
+        bad = bytearray(rb.encode_batch(4, [jvals(4, 5)[0], None, jvals(6, 7)[0]]))
+    elif damage == "varint":                                  # framing broken, CRC recomputed to match
+        bad[61] = 0xFF
+        bad[17:21] = rb.crc32c(bytes(bad[21:])).to_bytes(4, "big")
+    elif damage == "count":
+        bad[57:61] = (9).to_bytes(4, "big")
+        bad[17:21] = rb.crc32c(bytes(bad[21:])).to_bytes(4, "big")
+    blob = good + bytes(bad) + rb.encode_batch(8, jvals(8, 12))
+    from torchkafka_b200.testing import stub_kafka as sk   # noqa: F401
+    with pytest.raises(PayloadError) as ei:
+        run_blobs([(1, blob, 0, 0)], JsonArray(torch.float32, fixed_len=2), 2)
+    assert ei.value.status == status and ei.value.partition == 1
+    assert ei.value.offset == (5 if damage == "null" else 4 if damage != "magic" else 0)
+
+
+def test_large_and_tiny_batches_and_unaligned_blobs():
+    """CRC over > 512-byte rows, exact multiples, short tails; blobs starting at odd addresses."""
+    rng = np.random.default_rng(8)
+    blobs, want = [], []
+    for p, nrec, size in [(0, 1, 0), (1, 1, 1), (2, 3, 450), (3, 1, 512 - 69), (4, 2, 1024), (5, 40, 3000), (6, 1, 300000)]:
+        vals = [bytes(rng.integers(0, 256, size, dtype=np.uint8)) for _ in range(nrec)]
+        blobs.append((p, rb.encode_batch(1000 * p, vals), 0, 0))
+        want += vals
+    eng, n, nbytes, nbatches = split_on_gpu(blobs, slot_bytes=2 << 20)
+    assert (n, nbatches, nbytes) == (len(want), len(blobs), sum(map(len, want)))
+    recs = device_records(eng, n, nbytes)
+    assert all(not (part & 0x70000000) for _, part, _ in recs[:-1])      # every CRC verified
+    assert [b[0] - a[0] for a, b in zip(recs, recs[1:])] == [len(v) for v in want]
+    eng.close()
+
+
+def test_slot_too_small_is_reported():
+    blob = rb.encode_batch(0, [b"x" * 100] * 50)
+    from torchkafka_b200 import _native
+    with pytest.raises(_native.NativeError, match="more records than slot_records"):
+        split_on_gpu([(0, blob, 0, 0)], slot_records=10)

@@ -1,0 +1,139 @@
+"""CPU tests of the record-batch step: the oracle restatement of the RecordBatch v2
+format against the format's published known answers, the stub broker's encoder against the
+oracle, and the library's host-side CRC-32C.  No GPU."""
+import random
+import struct
+
+import numpy as np
+import pytest
+
+import helpers  # noqa: F401  (sys.path)
+from oracle import record_batch as orb
+from torchkafka_b200.testing import record_batch as rb
+from torchkafka_b200.testing import stub_kafka as sk
+from torchkafka_b200.testing import synthetic as syn
+
+# RFC 3720 (iSCSI) appendix B.4 CRC-32C test vectors + the classic check value
+CRC_KAT = [
+    (b"123456789", 0xE3069283),
+    (bytes(32), 0x8A9136AA),
+    (b"\xff" * 32, 0x62A8AB43),
+    (bytes(range(32)), 0x46DD794E),
+    (bytes(range(31, -1, -1)), 0x113FDB5C),
+    (b"", 0x00000000),
+]
+
+
+@pytest.mark.parametrize("data,want", CRC_KAT)
+def test_crc32c_known_answers(data, want):
+    assert orb.crc32c(data) == want
+    assert rb.crc32c(data) == want
+
+
+def test_crc32c_host_library_matches_oracle_on_random_data_and_continues():
+    rng = random.Random(3)
+    for n in [1, 7, 8, 9, 63, 64, 65, 1000, 4099]:
+        data = bytes(rng.getrandbits(8) for _ in range(n))
+        assert rb.crc32c(data) == orb.crc32c(data)
+        k = rng.randrange(n + 1)
+        assert rb.crc32c(data[k:], rb.crc32c(data[:k])) == orb.crc32c(data)      # incremental form
+        # unaligned start
+        arr = np.frombuffer(b"x" + data, dtype=np.uint8)[1:]
+        assert rb.crc32c(arr) == orb.crc32c(data)
+
+
+# zig-zag varints: the examples of the protobuf encoding guide (sint32/sint64)
+VARINT_KAT = [(0, b"\x00"), (-1, b"\x01"), (1, b"\x02"), (-2, b"\x03"), (2147483647, b"\xfe\xff\xff\xff\x0f"),
+              (-2147483648, b"\xff\xff\xff\xff\x0f"), (150, b"\xac\x02"), (-64, b"\x7f"), (64, b"\x80\x01")]
+
+
+@pytest.mark.parametrize("value,wire", VARINT_KAT)
+def test_varint_known_answers(value, wire):
+    assert rb.zigzag_varint(value) == wire
+    assert orb.read_varint(wire, 0, len(wire)) == (value, len(wire))
+
+
+def test_varint_errors():
+    with pytest.raises(orb.CorruptRecordError):
+        orb.read_varint(b"\x80\x80", 0, 2)                     # runs off the end
+    with pytest.raises(orb.CorruptRecordError):
+        orb.read_varint(b"\xff" * 11, 0, 11)                   # more than 10 bytes
+
+
+def test_batch_layout_matches_the_protocol_guide():
+    """Field offsets of the 61-byte header (Kafka protocol guide, Record Batch, magic 2)."""
+    blob = rb.encode_batch(1234567890123, [b"ab", b"cde"])
+    base, length, epoch, magic, crc = struct.unpack_from(">qiibI", blob, 0)
+    attrs, last, t0, t1, pid, pepoch, seq, count = struct.unpack_from(">hiqqqhii", blob, 21)
+    assert (base, magic, attrs, last, count) == (1234567890123, 2, 0, 1, 2)
+    assert length == len(blob) - 12 and (pid, pepoch, seq) == (-1, -1, -1)
+    assert crc == orb.crc32c(blob[21:])
+    # first record: length 8, attributes 0, timestampDelta 0, offsetDelta 0, key null, value "ab", no headers
+    assert blob[61:70] == bytes([2 * 8, 0, 0, 0, 1, 2 * 2]) + b"ab" + b"\x00"
+
+
+def test_roundtrip_with_keys_headers_nulls_and_offset_gaps():
+    rng = random.Random(9)
+    values = [None if rng.random() < 0.1 else bytes(rng.getrandbits(8) for _ in range(rng.choice([0, 1, 5, 200, 5000])))
+              for _ in range(40)]
+    keys = [None if rng.random() < 0.5 else b"k" * rng.randrange(0, 300) for _ in values]
+    headers = [[(b"h", b"v" * rng.randrange(3)), (b"n", None)] if rng.random() < 0.3 else [] for _ in values]
+    deltas = sorted(rng.sample(range(200), len(values)))        # compacted topic: gaps
+    blob = rb.encode_batch(1000, values, offset_deltas=deltas, keys=keys, headers=headers)
+    recs = orb.split_blob(blob, 5)
+    assert [r.value for r in recs] == values
+    assert [r.offset for r in recs] == [1000 + d for d in deltas]
+    assert all(r.partition == 5 for r in recs)
+
+
+def test_fetch_offset_partial_tail_control_and_errors():
+    a = rb.encode_batch(10, [b"a", b"b", b"c"])
+    b = rb.encode_batch(13, [b"d"])
+    ctl = rb.encode_batch(14, [b"\x00\x00\x00\x00"], attributes=0x20)
+    c = rb.encode_batch(15, [b"e"])
+    blob = a + b + ctl + c
+    assert [r.value for r in orb.split_blob(blob, 0)] == [b"a", b"b", b"c", b"d", b"e"]
+    assert [r.offset for r in orb.split_blob(blob, 0, fetch_offset=12)] == [12, 13, 15]
+    assert [r.offset for r in orb.split_blob(blob, 0, offset_delta=100)] == [110, 111, 112, 113, 115]
+    for cut in (1, 11, 12, 30, len(c) - 1):                     # response cut inside the last batch
+        assert [r.value for r in orb.split_blob(blob[:len(blob) - cut], 0)] == [b"a", b"b", b"c", b"d"]
+    bad = bytearray(blob)
+    bad[len(a) + 63] ^= 1                                      # inside the second batch's record
+    with pytest.raises(orb.CorruptRecordError):
+        orb.split_blob(bytes(bad), 0)
+    with pytest.raises(orb.UnsupportedBatch):
+        orb.split_blob(rb.encode_batch(0, [b"x"], attributes=2), 0)
+    v1 = bytearray(a)
+    v1[16] = 1
+    with pytest.raises(orb.CorruptRecordError):
+        orb.split_blob(bytes(v1), 0)
+
+
+@pytest.mark.parametrize("layout,chunk", [("chunked", 7), ("roundrobin", 1), ("chunked", 500)])
+def test_poll_raw_serves_the_log_in_iteration_order(layout, chunk):
+    log = syn.make_log(2, 400, seed=2, partitions=5, layout=layout, chunk=chunk)
+    c = sk.KafkaConsumer("topic", log=log, repeat=2, raw_batch_bytes=6000)
+    got = []
+    while True:
+        f = c.poll_raw(50000, 64)
+        if f is None:
+            break
+        assert len({p for p, *_ in f.blobs}) == len(f.blobs)    # a partition at most once per fetch
+        for p, data, fetch_offset, delta in f.blobs:
+            got += orb.split_blob(bytes(data), p, fetch_offset, delta)
+    it = sk.KafkaConsumer("topic", log=log, repeat=2)
+    want = list(it)
+    assert [(r.partition, r.offset, r.value) for r in got] == [(r.partition, r.offset, r.value) for r in want]
+    assert c._positions == it._positions
+
+
+def test_poll_raw_after_partial_consumption_returns_the_batch_whole():
+    log = syn.make_log(2, 60, seed=4, partitions=1, layout="chunked", chunk=60)
+    c = sk.KafkaConsumer("topic", log=log, raw_batch_bytes=1 << 20)      # one batch
+    first = [next(c) for _ in range(25)]
+    f = c.poll_raw(1 << 22, 1000)
+    (p, data, fetch_offset, delta), = f.blobs
+    assert fetch_offset == first[-1].offset + 1
+    recs = orb.split_blob(bytes(data), p, fetch_offset, delta)
+    assert [r.offset for r in recs] == list(range(25, 60))
+    assert len(orb.split_blob(bytes(data), p, 0, delta)) == 60

@@ -45,6 +45,23 @@ class TkJob(C.Structure):
     ]
 
 
+class TkBlob(C.Structure):
+    _fields_ = [("start", C.c_uint32), ("length", C.c_uint32), ("partition", C.c_int32),
+                ("reserved", C.c_uint32), ("fetch_offset", C.c_int64), ("offset_delta", C.c_int64)]
+
+
+class TkRbSummary(C.Structure):
+    _fields_ = [("n_records", C.c_uint32), ("n_batches", C.c_uint32), ("n_bytes", C.c_uint64),
+                ("status", C.c_uint32), ("reserved", C.c_uint32)]
+
+
+RB_STATUS_NAMES = {
+    1: "more record batches than slot_records",
+    2: "more records than slot_records",
+    3: "more value bytes than slot_bytes",
+}
+REC_FLAGS = 0x70000000
+
 STATUS_NAMES = {
     0: "ok",
     1: "not a JSON array of numbers (json.JSONDecodeError in the reference)",
@@ -53,6 +70,7 @@ STATUS_NAMES = {
     4: "valid JSON outside the numeric-array schema (true/false/null, strings, nesting)",
     5: "raw record has the wrong byte count",
     6: "record length differs from the schema's fixed_len (torch.stack would raise)",
+    7: "record batch failed its CRC-32C or its record framing (CorruptRecordException in kafka-python)",
 }
 
 _p = C.POINTER
@@ -89,6 +107,10 @@ _SIGNATURES = {
     "tk_process_slot": (C.c_int, [C.c_void_p, C.c_int, _p(TkJob), C.c_void_p]),
     "tk_compact_noalloc": (C.c_int, [C.c_void_p, C.c_uint32, C.c_uint32, C.c_uint32, C.c_void_p,
                                      C.c_void_p, C.c_void_p]),
+    "tk_slot_submit_recordbatches": (C.c_int, [C.c_void_p, C.c_int, C.c_uint64, _p(TkBlob), C.c_uint32]),
+    "tk_slot_recordbatch_result": (C.c_int, [C.c_void_p, C.c_int, _p(TkRbSummary)]),
+    "tk_slot_record": (C.c_int, [C.c_void_p, C.c_int, C.c_uint32, _p(TkRec)]),
+    "tk_crc32c": (C.c_uint32, [C.c_void_p, C.c_uint64, C.c_uint32]),
     "tk_ctx_set_timing": (C.c_int, [C.c_void_p, C.c_int]),
     "tk_slot_decode_ms": (C.c_int, [C.c_void_p, C.c_int, _p(C.c_float)]),
     "tk_slot_fetch_result": (C.c_int, [C.c_void_p, C.c_int, C.c_void_p]),

@@ -33,6 +33,19 @@ struct tk_state {
     uint32_t pad;
 };
 
+// One RecordBatch of a raw slot (tk_recordbatch.cu)
+struct tk_rb_batch {
+    uint32_t start, end;       // byte range of the batch in the raw buffer
+    int32_t  partition;
+    uint32_t status;           // tk_status_t: the batch could not be split
+    int64_t  base_offset;      // + blob offset_delta
+    int64_t  fetch_offset;
+    uint32_t n_rec;            // records (1 pseudo-record if status != 0)
+    uint32_t value_bytes;      // bytes the batch contributes to the slot
+    uint32_t rec_base;         // first record / first value byte of the batch in the slot
+    uint32_t byte_base;
+};
+
 // Per-slot device scratch ("plan"): everything the kernels hand to one another.
 struct tk_slot_dev {
     uint8_t*     bytes;        // [slot_bytes + pad]
@@ -52,6 +65,11 @@ struct tk_slot_dev {
     uint32_t*    tok_pos;      // [tok_cap] token array of the flat decode path: uint2 {byte position, record}
     uint32_t*    tok_count;    // [2] elements emitted so far (token array allocation cursor): two
                                // counters used alternately, each scan zeroes the one of the next
+    // raw record-batch input (allocated on first tk_slot_submit_recordbatches)
+    uint8_t*     raw;          // [slot_bytes + pad]
+    tk_blob_t*   blobs;        // [TK_MAX_BLOBS]
+    tk_rb_batch* rb_batches;   // [slot_records]
+    tk_rb_summary_t* rb_summary;
     uint8_t*     block;        // one allocation: header | batch_end | batch_lmax | commit
     tk_result_t* result;       // header
     uint32_t*    batch_end;    // [max_batches + 1]
@@ -75,6 +93,8 @@ struct tk_slot {
     cudaEvent_t  ev_h2d;      // H2D landed
     cudaEvent_t  ev_free;     // kernels finished reading the device copy
     cudaEvent_t  ev_result;   // result block is in pinned memory
+    tk_blob_t*   h_blobs;     // pinned
+    tk_rb_summary_t* h_rb_summary;   // pinned
     cudaEvent_t  ev_dec0, ev_dec1;   // timing events around the decode / collate kernels (tk_ctx_set_timing)
     bool         dec_timed;
     uint32_t     tok_use;     // tk_json_scan calls on this slot: selects the token counter

@@ -80,6 +80,19 @@ __global__ void __launch_bounds__(256) k_json_scan(const scan_args a) {
     uint2* tok = reinterpret_cast<uint2*>(a.tok);
     for (uint32_t i = warp; i < a.n; i += nwarps) {
         const uint32_t start = a.recs[i].start, end = a.recs[i + 1].start;
+        // records the record-batch split flagged (tk_recordbatch.cu): skipped ones were never
+        // consumed, broken ones carry their batch's error; neither has a payload to look at
+        const int32_t pflags = a.recs[i].partition & TK_REC_FLAGS;
+        if (pflags) {
+            if (lane == 0) {
+                a.rec_len[i] = 0;
+                a.rec_status[i] = (pflags & TK_REC_CORRUPT) ? TK_STATUS_CORRUPT
+                                : (pflags & TK_REC_UNSUPPORTED) ? TK_STATUS_UNSUPPORTED : TK_STATUS_OK;
+                a.rec_kidx[i] = -1;
+                a.rec_tok[i] = 0;
+            }
+            continue;
+        }
         const uint32_t base0 = start & ~15u;
         // what the last element's entry carries: the parse kernel takes its fast lane only when the
         // record ends in ']' right behind the last number (trailing white space: scalar grammar)

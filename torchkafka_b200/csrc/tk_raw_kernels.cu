@@ -26,6 +26,13 @@ __global__ void __launch_bounds__(256) k_raw_scan(const tk_rec_t* __restrict__ r
     if (i >= n) return;
     const uint32_t len = recs[i + 1].start - recs[i].start;
     rec_len[i] = (int32_t)len;
+    const int32_t pflags = recs[i].partition & TK_REC_FLAGS;    // set by the record-batch split
+    if (pflags) {
+        rec_status[i] = (pflags & TK_REC_CORRUPT) ? TK_STATUS_CORRUPT
+                      : (pflags & TK_REC_UNSUPPORTED) ? TK_STATUS_UNSUPPORTED : TK_STATUS_OK;
+        rec_kidx[i] = -1;
+        return;
+    }
     const bool ok = len == record_bytes;
     rec_status[i] = ok ? TK_STATUS_OK : TK_STATUS_SIZE;
     rec_kidx[i] = ok ? 0 : -1;

@@ -397,11 +397,41 @@ class SlotEngine:
             batches.append(sc.wrap(v, ln, m))
         return batches
 
-    def error_for(self, slot: int, res: SlotResult, partitions, offsets) -> PayloadError:
+    def error_for(self, slot: int, res: SlotResult, partitions=None, offsets=None) -> PayloadError:
+        """The error of the slot's first bad record.  ``partitions`` / ``offsets`` are the host's
+        copy of the record coordinates; a slot split on the device (record batches) has none and
+        the record's header is read back instead."""
         e = int(res.first_error_rec)
         _, status, _ = self.record_debug(slot, res.n_records)
         code = int(status[e])
+        if partitions is None:
+            rec = _native.TkRec()
+            _native.check(self.lib.tk_slot_record(self.ctx, slot, e, C.byref(rec)))
+            part, off = int(rec.partition) & ~_native.REC_FLAGS, int(rec.offset)
+        else:
+            part, off = int(partitions[e]), int(offsets[e])
         return PayloadError(
-            f"record {e} of the slot (partition index {int(partitions[e])}, offset {int(offsets[e])}): "
+            f"record {e} of the slot (partition index {part}, offset {off}): "
             f"{_native.STATUS_NAMES.get(code, code)}",
-            partition=int(partitions[e]), offset=int(offsets[e]), status=code)
+            partition=part, offset=off, status=code)
+
+    # ------------------------------------------------------------------ record batches
+    def submit_recordbatches(self, slot: int, n_bytes: int, blobs) -> None:
+        """Raw RecordBatch v2 bytes are in the slot's pinned buffer ``[0, n_bytes)``; ``blobs`` is a
+        sequence of (start, length, dense partition, fetch_offset, offset_delta).  Asynchronous."""
+        arr = (_native.TkBlob * max(len(blobs), 1))()
+        for k, (start, length, part, fetch_offset, delta) in enumerate(blobs):
+            b = arr[k]
+            b.start, b.length, b.partition = int(start), int(length), int(part)
+            b.fetch_offset, b.offset_delta = int(fetch_offset), int(delta)
+        _native.check(self.lib.tk_slot_submit_recordbatches(self.ctx, slot, C.c_uint64(int(n_bytes)), arr, len(blobs)))
+
+    def recordbatch_result(self, slot: int):
+        """Wait for the split of ``slot``; returns (n_records, n_value_bytes, n_batches)."""
+        r = _native.TkRbSummary()
+        _native.check(self.lib.tk_slot_recordbatch_result(self.ctx, slot, C.byref(r)))
+        if r.status:
+            raise _native.NativeError(
+                f"record batches do not fit the slot: {_native.RB_STATUS_NAMES.get(int(r.status), int(r.status))} "
+                f"(slot_records={self.slot_records}, slot_bytes={self.slot_bytes})")
+        return int(r.n_records), int(r.n_bytes), int(r.n_batches)

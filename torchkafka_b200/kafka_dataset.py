@@ -100,6 +100,10 @@ class KafkaDataset(IterableDataset):
     #: send every assigned partition with each commit (reference behaviour) instead of only the
     #: partitions whose position moved since the previous commit (same broker state, cheaper)
     commit_all_partitions = False
+    #: how records reach the GPU: "auto" (``poll_packed()`` if the consumer has it, else
+    #: ``poll()``), "records", "packed", or "raw" (``poll_raw()``: RecordBatch v2 blobs of the
+    #: fetch response, CRC-checked and split on the device)
+    device_input = "auto"
 
     def __init__(self, *args, **kwargs):
         self._worker_id = None          # set by init_worker inside a DataLoader worker
@@ -235,7 +239,7 @@ class KafkaDataset(IterableDataset):
             slot_bytes=self.device_slot_bytes, n_slots=self.device_slots,
             device=self.device_index, max_partitions=self.max_partitions,
             threaded=self.device_producer_thread, n_producers=self.device_producers,
-            commit_all_partitions=self.commit_all_partitions,
+            commit_all_partitions=self.commit_all_partitions, input_mode=self.device_input,
         )
         return self._pipeline
 

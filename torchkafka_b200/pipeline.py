@@ -72,7 +72,7 @@ class IngestPipeline:
                  slot_bytes: int = 64 << 20, n_slots: int = 3, device: Optional[int] = None,
                  max_partitions: int = 64, poll_timeout_ms: int = 100,
                  threaded: bool = True, commit_all_partitions: bool = False,
-                 n_producers: int = 2):
+                 n_producers: int = 2, input_mode: str = "auto"):
         self.consumer = consumer
         self.schema = schema
         self.batch_size = int(batch_size)
@@ -99,7 +99,22 @@ class IngestPipeline:
         self._tp_cls = _tp_struct()
         self._tp_of: Dict[int, object] = {}        # dense partition index -> TopicPartition
         self._dense_of: Dict[object, int] = {}     # TopicPartition -> dense index
-        self._packed = hasattr(consumer, "poll_packed")
+        # how records reach the slot:
+        #   "records"  consumer.poll() -> ConsumerRecord objects (kafka-python as it is)
+        #   "packed"   consumer.poll_packed() -> flat arrays (additive protocol)
+        #   "raw"      consumer.poll_raw() -> RecordBatch v2 blobs of the fetch response, split on
+        #              the GPU (additive protocol)
+        #   "auto"     packed if the consumer offers it, else records
+        if input_mode not in ("auto", "records", "packed", "raw"):
+            raise ValueError(f"unknown input_mode {input_mode!r}")
+        if input_mode == "auto":
+            input_mode = "packed" if hasattr(consumer, "poll_packed") else "records"
+        if input_mode == "packed" and not hasattr(consumer, "poll_packed"):
+            raise TypeError("input_mode='packed' needs a consumer with poll_packed()")
+        if input_mode == "raw" and not hasattr(consumer, "poll_raw"):
+            raise TypeError("input_mode='raw' needs a consumer with poll_raw()")
+        self.input_mode = input_mode
+        self._packed = input_mode == "packed"
         self._leftover = []                        # (tp, records) polled but not fitting the last slot
         self._field_idx = {}                       # record type -> (value index, offset index)
         self.n_producers = max(1, int(n_producers))
@@ -183,6 +198,59 @@ class IngestPipeline:
         n, nbytes = self.engine.fill_packed(slot, run.values, run.starts, parts, run.offsets)
         self.stats["t_pack"] += time.perf_counter() - t0
         return parts, np.asarray(run.offsets)
+
+    def _gather_raw(self, slot: int, scratch):
+        """Next fetch as RecordBatch v2 blobs: no per-record work on the host at all."""
+        eng = self.engine
+        idle_since = None
+        while True:
+            t0 = time.perf_counter()
+            with self.consumer_lock:
+                fetch = self.consumer.poll_raw(eng.slot_bytes, eng.slot_records)
+            self.stats["t_poll"] += time.perf_counter() - t0
+            if fetch is not None and len(fetch.blobs):
+                break
+            if idle_since is None:
+                idle_since = time.monotonic()
+            if self._stop.is_set() or time.monotonic() - idle_since >= self.idle_timeout_s:
+                return 0, 0, None
+            time.sleep(min(self.poll_timeout_ms, 50) / 1e3)
+        topic = getattr(fetch, "topic", None) or "topic"
+        nbytes = 0
+        for p, data, _fo, _delta in fetch.blobs:
+            p = int(p)
+            if p not in self._tp_of:                       # dense index == partition id (single topic)
+                if not 0 <= p < eng.n_partitions:
+                    raise RuntimeError(f"partition {p} outside [0, max_partitions={eng.n_partitions})")
+                tp = self._tp_cls(topic, p)
+                self._tp_of[p] = tp
+                self._dense_of[tp] = p
+            nbytes += len(data)
+        if nbytes > eng.slot_bytes:
+            raise ValueError(f"a fetch of {nbytes} bytes exceeds the slot size ({eng.slot_bytes} bytes)")
+        # n is not known before the device has split the batches: report blobs, fix up in _pack_raw
+        return len(fetch.blobs), nbytes, fetch
+
+    def _pack_raw(self, slot: int, scratch, n_blobs: int, fetch):
+        """Blobs -> pinned buffer (multi-threaded gather), H2D + split kernels, wait for the counts."""
+        eng = self.engine
+        t0 = time.perf_counter()
+        k = len(fetch.blobs)
+        ptrs = np.fromiter((b[1].ctypes.data for b in fetch.blobs), dtype=np.uint64, count=k)
+        lens = np.fromiter((len(b[1]) for b in fetch.blobs), dtype=np.uint32, count=k)
+        parts = np.fromiter((int(b[0]) for b in fetch.blobs), dtype=np.int32, count=k)
+        fetch_offsets = np.fromiter((int(b[2]) for b in fetch.blobs), dtype=np.int64, count=k)
+        eng.pack_pointers(slot, ptrs, lens, parts, fetch_offsets, k)      # bytes back to back
+        starts = np.zeros(k + 1, dtype=np.int64)
+        np.cumsum(lens, out=starts[1:])
+        eng.submit_recordbatches(slot, int(starts[k]),
+                                 [(int(starts[i]), int(lens[i]), int(parts[i]), int(fetch_offsets[i]),
+                                   int(fetch.blobs[i][3])) for i in range(k)])
+        self.stats["t_pack"] += time.perf_counter() - t0
+        t0 = time.perf_counter()
+        n, nbytes, _ = eng.recordbatch_result(slot)
+        self.stats["t_split_wait"] = self.stats.get("t_split_wait", 0.0) + time.perf_counter() - t0
+        return n, nbytes
 
     def _indices(self, rec):
         """(value index, offset index) for tuple-like records, (-1, -1) for attribute access."""
@@ -300,9 +368,10 @@ class IngestPipeline:
     def _produce(self, free_q, deliver):
         """Producer thread.  Gather (consumer calls, serialised, defines the slot order) then
         pack + submit (parallel across producer threads)."""
-        gather = self._gather_packed if self._packed else self._gather_poll
-        pack = self._pack_packed if self._packed else self._pack_poll
-        scratch = self._new_scratch() if not self._packed else None
+        raw = self.input_mode == "raw"
+        gather = self._gather_raw if raw else self._gather_packed if self._packed else self._gather_poll
+        pack = self._pack_raw if raw else self._pack_packed if self._packed else self._pack_poll
+        scratch = self._new_scratch() if self.input_mode == "records" else None
         try:
             while not self._stop.is_set():
                 slot = free_q.get()
@@ -320,6 +389,11 @@ class IngestPipeline:
                 if n == 0:
                     deliver(seq, None)
                     return
+                if raw:
+                    # the device splits the batches: record coordinates stay there
+                    n, nbytes = pack(slot, scratch, n, token)
+                    deliver(seq, (slot, n, nbytes, None, None))
+                    continue
                 parts, offs = pack(slot, scratch, n, token)
                 self.engine.submit(slot, n, nbytes)
                 deliver(seq, (slot, n, nbytes, parts, offs))
@@ -335,9 +409,10 @@ class IngestPipeline:
         self._seq = 0
         self._eof = False
         if not self.threaded:
-            gather = self._gather_packed if self._packed else self._gather_poll
-            pack = self._pack_packed if self._packed else self._pack_poll
-            scratch = self._new_scratch() if not self._packed else None
+            raw = self.input_mode == "raw"
+            gather = self._gather_raw if raw else self._gather_packed if self._packed else self._gather_poll
+            pack = self._pack_raw if raw else self._pack_packed if self._packed else self._pack_poll
+            scratch = self._new_scratch() if self.input_mode == "records" else None
             free = collections.deque(range(eng.n_slots))
 
             def gen():
@@ -346,6 +421,10 @@ class IngestPipeline:
                     n, nbytes, token = gather(slot, scratch)
                     if n == 0:
                         return
+                    if raw:
+                        n, nbytes = pack(slot, scratch, n, token)
+                        yield slot, n, nbytes, None, None
+                        continue
                     parts, offs = pack(slot, scratch, n, token)
                     eng.submit(slot, n, nbytes)
                     yield slot, n, nbytes, parts, offs

@@ -1,0 +1,125 @@
+"""Kafka RecordBatch v2 encoder for the in-memory stub broker (tests and benchmarks).
+
+What a broker would put into the `records` field of a fetch response for one partition:
+uncompressed, non-transactional batches (Apache Kafka protocol guide, "Record Batch", magic 2).
+Record keys are null, headers empty, timestamps zero -- the reference's `_process` hook only
+reads `record.value`, `.partition` and `.offset`.
+
+The checksum comes from the library's host-side `tk_crc32c` (include/torchkafka_b200.h).
+"""
+from __future__ import annotations
+
+import ctypes as C
+import struct
+from typing import List, Optional, Sequence
+
+import numpy as np
+
+HEADER_BYTES = 61
+CRC_FROM = 21
+
+
+def zigzag_varint(v: int) -> bytes:
+    """Signed integer -> zig-zag base-128 varint."""
+    u = (v << 1) ^ (v >> 63)
+    u &= (1 << 64) - 1
+    out = bytearray()
+    while True:
+        b = u & 0x7F
+        u >>= 7
+        if u:
+            out.append(b | 0x80)
+        else:
+            out.append(b)
+            return bytes(out)
+
+
+_VARINT_SMALL = [zigzag_varint(i) for i in range(4096)]
+_VARINT_M1 = zigzag_varint(-1)
+
+
+def _vi(v: int) -> bytes:
+    return _VARINT_SMALL[v] if 0 <= v < 4096 else zigzag_varint(v)
+
+
+def crc32c(data, crc: int = 0) -> int:
+    from .. import _native
+    lib = _native.load()
+    buf = np.frombuffer(data, dtype=np.uint8) if not isinstance(data, np.ndarray) else data
+    return int(lib.tk_crc32c(C.c_void_p(buf.ctypes.data), C.c_uint64(buf.size), C.c_uint32(crc)))
+
+
+def encode_record(offset_delta: int, value: Optional[bytes], key: Optional[bytes] = None,
+                  timestamp_delta: int = 0, headers: Sequence = ()) -> bytes:
+    body = bytearray(b"\x00")                                  # attributes
+    body += _vi(timestamp_delta) if timestamp_delta >= 0 else zigzag_varint(timestamp_delta)
+    body += _vi(offset_delta)
+    if key is None:
+        body += _VARINT_M1
+    else:
+        body += _vi(len(key)) + key
+    if value is None:
+        body += _VARINT_M1
+    else:
+        body += _vi(len(value))
+        body += value
+    body += _vi(len(headers))
+    for hk, hv in headers:
+        body += _vi(len(hk)) + hk
+        body += _VARINT_M1 if hv is None else _vi(len(hv)) + hv
+    return _vi(len(body)) + bytes(body)
+
+
+def encode_batch(base_offset: int, values: Sequence[Optional[bytes]], attributes: int = 0,
+                 offset_deltas: Optional[Sequence[int]] = None, keys: Optional[Sequence] = None,
+                 headers: Optional[Sequence] = None, crc: Optional[int] = None) -> bytes:
+    """One RecordBatch v2.  `offset_deltas` default to 0, 1, 2, ... (a compacted topic has gaps)."""
+    n = len(values)
+    deltas = list(range(n)) if offset_deltas is None else list(offset_deltas)
+    recs = b"".join(encode_record(deltas[k], values[k], None if keys is None else keys[k], 0,
+                                  () if headers is None else headers[k]) for k in range(n))
+    last = deltas[-1] if n else 0
+    tail = struct.pack(">hiqqqhii", attributes, last, 0, 0, -1, -1, -1, n) + recs    # from byte 21 on
+    if crc is None:
+        crc = crc32c(tail)
+    batch_len = (HEADER_BYTES - 12) + len(recs)
+    return struct.pack(">qiibI", base_offset, batch_len, 0, 2, crc) + tail
+
+
+class EncodedLog:
+    """A RecordLog as record batches: every run of same-partition records of the log becomes one
+    or more batches of at most `batch_bytes` of payload (at least one record)."""
+
+    def __init__(self, log, batch_bytes: int = 16384):
+        values = log._byte_values            # noqa: SLF001 (test helper of the same package)
+        parts = log.partitions
+        offs = log.offsets
+        n = len(log)
+        chunks: List[bytes] = []
+        first_rec, part_of, pos_of = [], [], []
+        pos = 0
+        i = 0
+        while i < n:
+            p = int(parts[i])
+            j, size = i, 0
+            # a batch: consecutive records of one partition with consecutive offsets
+            while j < n and int(parts[j]) == p and (j == i or (int(offs[j]) == int(offs[j - 1]) + 1
+                                                               and size + len(values[j]) <= batch_bytes)):
+                size += len(values[j])
+                j += 1
+            blob = encode_batch(int(offs[i]), values[i:j])
+            chunks.append(blob)
+            first_rec.append(i)
+            part_of.append(p)
+            pos_of.append(pos)
+            pos += len(blob)
+            i = j
+        self.data = np.frombuffer(b"".join(chunks), dtype=np.uint8) if chunks else np.zeros(0, np.uint8)
+        self.first_rec = np.asarray(first_rec + [n], dtype=np.int64)      # batch b holds records [first_rec[b], first_rec[b+1])
+        self.partition = np.asarray(part_of, dtype=np.int32)
+        self.start = np.asarray(pos_of + [pos], dtype=np.int64)
+        self.n_batches = len(part_of)
+
+    @property
+    def nbytes(self) -> int:
+        return int(self.start[-1])

@@ -80,6 +80,22 @@ class PackedRecords:
         return int(self.starts[-1]) - int(self.starts[0]) if len(self.starts) else 0
 
 
+class RawFetch:
+    """A fetch response as the wire delivers it: per partition one blob of RecordBatch v2 bytes.
+
+    ``blobs`` is a list of ``(partition, uint8 array, fetch_offset, offset_delta)``; the array
+    is a view of the broker's log segment, ``fetch_offset`` the consumer's position in that
+    partition (records below it are to be skipped), ``offset_delta`` is added to every offset
+    (0 on a real broker; the stub uses it to serve the same bytes again at higher offsets).
+    """
+
+    __slots__ = ("blobs", "topic")
+
+    def __init__(self, blobs, topic="topic"):
+        self.blobs = blobs
+        self.topic = topic
+
+
 class RecordLog:
     """An immutable, ordered log of records shared by stub consumers.
 
@@ -155,6 +171,14 @@ class RecordLog:
             self._bounds = (np.flatnonzero(p[1:] != p[:-1]) + 1) if len(p) > 1 else np.zeros(0, np.int64)
         return self._bounds
 
+    def encoded(self, batch_bytes: int = 16384):
+        """The log as RecordBatch v2 bytes (``testing.record_batch.EncodedLog``), cached."""
+        cache = self.__dict__.setdefault("_encoded", {})
+        if batch_bytes not in cache:
+            from .record_batch import EncodedLog
+            cache[batch_bytes] = EncodedLog(self, batch_bytes)
+        return cache[batch_bytes]
+
     def select_partitions(self, keep) -> "RecordLog":
         """Sub-log holding only partitions for which ``keep(p)`` is true."""
         idx = [i for i, p in enumerate(self.partitions) if keep(int(p))]
@@ -173,7 +197,7 @@ class KafkaConsumer:
     """
 
     def __init__(self, *topics, log: Optional[RecordLog] = None, block_at_end: bool = False,
-                 fail_commits: bool = False, repeat: int = 1, **configs):
+                 fail_commits: bool = False, repeat: int = 1, raw_batch_bytes: int = 16384, **configs):
         self.topics = topics
         self.config = dict(configs)
         # the end of the in-memory log is the end of the stream, unless the stub is told to
@@ -184,6 +208,7 @@ class KafkaConsumer:
         self._rep = 0                  # current repetition of the log (see ``repeat``)
         self._repeat = max(1, int(repeat))
         self._block_at_end = block_at_end
+        self._raw_batch_bytes = int(raw_batch_bytes)
         self._fail_commits = fail_commits
         self._positions: Dict[int, int] = {}
         self.committed_log: List[Dict[int, int]] = []
@@ -282,6 +307,58 @@ class KafkaConsumer:
         return PackedRecords(self._log.values[base:starts[b]],
                              (starts[a:b + 1] - base).astype(np.uint32),
                              parts, offs, self._log.topic)
+
+    # -- raw fast path (additive) --------------------------------------------
+    def poll_raw(self, max_bytes: int, max_records: int) -> Optional[RawFetch]:
+        """Next fetch response as RecordBatch v2 blobs (no parsing on the host).
+
+        Whole batches only, every partition at most once per response, blobs in consumption
+        order.  If the cursor stands inside a batch (earlier records of the batch were already
+        handed out through ``poll()`` / iteration), the batch is returned whole with
+        ``fetch_offset`` = the position, as a broker does.  Returns ``None`` at the end of the log.
+        """
+        n = len(self._log)
+        if not self._roll():
+            return None
+        enc = self._log.encoded(self._raw_batch_bytes)
+        first = enc.first_rec
+        b = int(np.searchsorted(first, self._cursor, side="right")) - 1      # batch holding the cursor
+        offs = self._log.rep_offsets(self._rep)
+        delta_of = (self._rep * self._log.per_partition_count()) if self._rep else None
+        blobs = []
+        seen = set()
+        nbytes = nrec = 0
+        cursor = self._cursor
+        while b < enc.n_batches:
+            p = int(enc.partition[b])
+            if p in seen:
+                break                                    # would re-open a partition
+            # extend over the following batches of the same partition
+            e = b
+            size = count = 0
+            while e < enc.n_batches and int(enc.partition[e]) == p:
+                bsz = int(enc.start[e + 1] - enc.start[e])
+                bcnt = int(first[e + 1] - first[e])
+                if (blobs or e > b) and (nbytes + size + bsz > max_bytes or nrec + count + bcnt > max_records):
+                    break
+                size += bsz
+                count += bcnt
+                e += 1
+            if e == b:
+                break
+            data = enc.data[int(enc.start[b]):int(enc.start[e])]
+            delta = int(delta_of[p]) if delta_of is not None else 0
+            blobs.append((p, data, int(offs[cursor]), delta))
+            seen.add(p)
+            nbytes += size
+            nrec += count
+            cursor = int(first[e])
+            self._positions[p] = int(offs[cursor - 1]) + 1
+            b = e
+            if nbytes >= max_bytes or nrec >= max_records:
+                break
+        self._cursor = cursor
+        return RawFetch(blobs, self._log.topic)
 
     # -- offsets -------------------------------------------------------------
     def position(self, tp):

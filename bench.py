@@ -243,12 +243,17 @@ def run_device_resident(base_log, steps, warmup, device):
     return info
 
 
+RAW_BATCH_BYTES = int(os.environ.get("RAW_BATCH_BYTES", str(64 << 10)))   # producer batch.size of the raw arm
+
+
 def make_dataset_cls(log, packed, repeat=1):
+    """packed: False = poll() objects, True = poll_packed() arrays, "raw" = poll_raw() record batches."""
     import torch
     from torchkafka_b200 import KafkaDataset
     from torchkafka_b200.schema import JsonArray
     from torchkafka_b200.testing import stub_kafka as sk
     consumer_cls = sk.KafkaConsumer if packed else sk.PollOnlyConsumer
+    mode = "raw" if packed == "raw" else "auto"
 
     class Cfg2Dataset(KafkaDataset):
         payload_schema = JsonArray(torch.float32, max_len=MAX_LEN, min_size=MIN_SIZE)
@@ -256,11 +261,12 @@ def make_dataset_cls(log, packed, repeat=1):
         device_slots = 3
         device_producers = int(os.environ.get("TK_PRODUCERS", "2"))
         max_partitions = PARTITIONS
+        device_input = mode
 
         @classmethod
         def new_consumer(cls, *a, **k):
             k.pop("enable_auto_commit", None)
-            return consumer_cls(*a, log=log, repeat=repeat, **k)
+            return consumer_cls(*a, log=log, repeat=repeat, raw_batch_bytes=RAW_BATCH_BYTES, **k)
 
     return Cfg2Dataset
 
@@ -296,7 +302,7 @@ def run_e2e(log, steps, warmup, device, packed, repeat=1):
     assert t1 is not None, f"log too short: {seen} batches for warmup {warmup} + steps {steps}"
     stats = dict(ds._pipeline.stats) if ds._pipeline is not None else dict(ds.last_pipeline_stats)
     print("e2e total", round(t1 - t0, 4), "checksum", checksum, file=sys.stderr)
-    print("e2e", "packed" if packed else "poll", {k: (round(v, 4) if isinstance(v, float) else v) for k, v in stats.items()}, file=sys.stderr, flush=True)
+    print("e2e", packed if packed == "raw" else "packed" if packed else "poll", {k: (round(v, 4) if isinstance(v, float) else v) for k, v in stats.items()}, file=sys.stderr, flush=True)
     ds.close()
     return {"seconds": t1 - t0, "checksum": checksum, "stats": stats}
 
@@ -447,20 +453,25 @@ def main_gpu(args):
             base.rep_records(r)          # exactly as they do for the CPU arm
     barrier()
     if args.skip_e2e:
-        e2e_poll = e2e_packed = {"seconds": float("nan")}
+        e2e_poll = e2e_packed = e2e_raw = {"seconds": float("nan")}
+        raw_bytes_per_step = float("nan")
     else:
         e2e_poll = run_e2e(base, steps, max(warmup, 3), device, packed=False, repeat=reps)
         barrier()
         e2e_packed = run_e2e(base, steps, max(warmup, 3), device, packed=True, repeat=reps)
+        barrier()
+        enc = base.encoded(RAW_BATCH_BYTES)          # the broker's log segment exists before the clock starts
+        raw_bytes_per_step = enc.nbytes / SLOT_BATCHES
+        e2e_raw = run_e2e(base, steps, max(warmup, 3), device, packed="raw", repeat=reps)
     barrier()
 
     rec_per_step = len(base) / SLOT_BATCHES
     bytes_per_step = (base.nbytes + 16 * len(base)) / SLOT_BATCHES
-    t = torch.tensor([dev["ms"], e2e_poll["seconds"], e2e_packed["seconds"]], dtype=torch.float64)
+    t = torch.tensor([dev["ms"], e2e_poll["seconds"], e2e_packed["seconds"], e2e_raw["seconds"]], dtype=torch.float64)
     if world > 1:
         import torch.distributed as dist
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
-    ms, e2e_poll_s, e2e_packed_s = [float(x) for x in t.tolist()]
+    ms, e2e_poll_s, e2e_packed_s, e2e_raw_s = [float(x) for x in t.tolist()]
     total_records = dev["records"] * world
     value = total_records / (ms / 1e3)
 
@@ -500,6 +511,11 @@ def main_gpu(args):
             "e2e_packed": {"value": steps * rec_per_step * world / e2e_packed_s, "unit": "records/s",
                            "path": "same API over consumer.poll_packed() (flat arrays, no per-record objects)",
                            "link_frac": steps * bytes_per_step / e2e_packed_s / 1e9 / dev["h2d_peak_gbs"]},
+            "e2e_raw": {"value": steps * rec_per_step * world / e2e_raw_s, "unit": "records/s",
+                        "path": "same API over consumer.poll_raw(): RecordBatch v2 blobs of the fetch response, "
+                                f"batch.size {RAW_BATCH_BYTES}; CRC-32C, varint framing and value gather on the GPU",
+                        "h2d_bytes_per_step": None if raw_bytes_per_step != raw_bytes_per_step else int(raw_bytes_per_step),
+                        "link_frac": steps * raw_bytes_per_step / e2e_raw_s / 1e9 / dev["h2d_peak_gbs"]},
             "gpu_launches": dev["launches"],
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
                          "frac": achieved / peak, "traffic": traffic,

@@ -12,15 +12,15 @@
 //
 // Kernels (all on the slot's copy stream, behind the H2D of the raw bytes):
 //   k_rb_headers  one block: thread per partition blob walks the chain of batch headers (twice:
-//                 count, block scan, emit) -> batch descriptors in consumption order
+//                 count, block scan, emit) -> batch descriptors in consumption order, each with
+//                 the index of its first record (sum of the headers' record counts)
 //   k_rb_check    warp per batch: CRC-32C of the batch (strided slicing-by-4, lanes own one 16-byte
 //                 chunk of every 512-byte row; lane states combined by carry-less multiplication),
-//                 then lane 0 walks the records (bytes now in L1/L2): count, value bytes, framing
-//   k_rb_prefix   one block: exclusive scan over the batches -> first record / first value byte of
-//                 each batch, totals, capacity checks
-//   k_rb_emit     warp per batch: lane 0 walks the records again, the warp copies each value to
-//                 its place in the slot's byte buffer (aligned destination words, funnel-shifted
-//                 source) and writes the record's tk_rec_t
+//                 then lane 0 walks the records (bytes now in L1/L2): framing checks, record
+//                 headers (partition, offset), one copy descriptor per record
+//   k_rb_prefix   one block: exclusive scan of the batches' value bytes, capacity check
+//   k_rb_copy     warp per record: the value moves to its place in the slot's byte buffer (aligned
+//                 destination words, funnel-shifted source)
 // Big-endian header fields, zig-zag varints.  Uncompressed batches only (codecs: SURVEY §8f-2).
 #include "tk_internal.h"
 #include <mutex>
@@ -90,6 +90,7 @@ struct rb_args {
     tk_rb_batch*     batches;
     uint32_t         max_batches;
     tk_rb_summary_t* summary;
+    uint4*           temp;            // [slot_records] per-record copy descriptors (rb_temp)
     uint8_t*         bytes;           // slot byte buffer (destination)
     tk_rec_t*        recs;            // slot record headers (destination)
     uint32_t         slot_records;
@@ -99,70 +100,95 @@ struct rb_args {
 // ---------------------------------------------------------------- k_rb_headers
 // One step of the header chain of a blob.  A blob ends at its first incomplete batch (fetch
 // responses are cut at max_bytes); a header that cannot be trusted ends the blob with one
-// descriptor of status CORRUPT, because the next boundary cannot be found.
+// descriptor of status CORRUPT, because the next boundary cannot be found.  The three fields a
+// step needs (batchLength, magic, recordCount) are requested together: one memory round trip.
 struct rb_hdr {
-    uint32_t start, end, status;
+    uint32_t start, end, status, count;
 };
 __device__ __forceinline__ bool rb_next_header(const uint8_t* raw, uint32_t pos, uint32_t blob_end, rb_hdr& h) {
     if (blob_end - pos < 12u) return false;
     const uint32_t blen = rb_be32(raw + pos + 8);
+    const uint32_t magic = raw[pos + 16];                 // (inside the padded buffer even if cut)
+    const uint32_t count = rb_be32(raw + pos + 57);
     h.start = pos;
+    h.count = 1;
     if ((int32_t)blen < (int32_t)(RB_HEADER - 12u)) { h.end = blob_end; h.status = TK_STATUS_CORRUPT; return true; }
     if (blen > blob_end - pos - 12u) return false;                    // partial trailing batch
     h.end = pos + 12u + blen;
-    h.status = raw[pos + 16] == 2 ? TK_STATUS_OK : TK_STATUS_CORRUPT;
-    if (h.status) h.end = blob_end;
+    // a record is at least 7 bytes: a larger count cannot be true (the checksum would say so too,
+    // but the count sizes the slot before the checksum is looked at)
+    h.status = (magic == 2 && count <= (h.end - pos - RB_HEADER) / 7u + 1u) ? TK_STATUS_OK : TK_STATUS_CORRUPT;
+    if (magic != 2) h.end = blob_end;
+    if (!h.status) h.count = count;
     return true;
 }
 
+// exclusive scan of one packed (batches << 40 | records) value per thread of a 1024-thread block
+__device__ __forceinline__ unsigned long long rb_block_scan(unsigned long long v, unsigned long long* warp_tot,
+                                                            unsigned long long* total) {
+    const uint32_t t = threadIdx.x, lane = t & 31;
+    unsigned long long incl = v;
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+        const unsigned long long o = __shfl_up_sync(0xffffffffu, incl, d);
+        if (lane >= (uint32_t)d) incl += o;
+    }
+    if (lane == 31) warp_tot[t >> 5] = incl;
+    __syncthreads();
+    if (t < 32) {
+        const unsigned long long w = warp_tot[t];
+        unsigned long long wi = w;
+#pragma unroll
+        for (int d = 1; d < 32; d <<= 1) {
+            const unsigned long long o = __shfl_up_sync(0xffffffffu, wi, d);
+            if (t >= (uint32_t)d) wi += o;
+        }
+        warp_tot[t] = wi - w;
+        if (t == 31) *total = wi;
+    }
+    __syncthreads();
+    return warp_tot[t >> 5] + incl - v;
+}
+
+// One block: thread per partition blob walks the chain of batch headers (count, block scan,
+// walk again and emit).  The record counts of the headers give every batch its first record
+// index in the slot, so the next kernel can write record headers while it validates.
 __global__ void __launch_bounds__(1024) k_rb_headers(const rb_args a) {
-    __shared__ uint32_t warp_tot[32];
-    __shared__ uint32_t s_total;
+    __shared__ unsigned long long warp_tot[32];
+    __shared__ unsigned long long s_total;
     const uint32_t t = threadIdx.x;
-    uint32_t count = 0, blob_start = 0, blob_end = 0;
+    unsigned long long mine = 0;
+    uint32_t blob_start = 0, blob_end = 0;
     if (t < a.n_blobs) {
         blob_start = a.blobs[t].start;
         blob_end = blob_start + a.blobs[t].length;
         rb_hdr h;
-        for (uint32_t pos = blob_start; rb_next_header(a.raw, pos, blob_end, h); pos = h.end) ++count;
+        for (uint32_t pos = blob_start; rb_next_header(a.raw, pos, blob_end, h); pos = h.end)
+            mine += (1ull << 40) + h.count;
     }
-    // exclusive scan of the per-blob batch counts (blobs <= 1024: one value per thread)
-    uint32_t incl = count;
-#pragma unroll
-    for (int d = 1; d < 32; d <<= 1) {
-        const uint32_t o = __shfl_up_sync(0xffffffffu, incl, d);
-        if ((t & 31) >= d) incl += o;
-    }
-    if ((t & 31) == 31) warp_tot[t >> 5] = incl;
-    __syncthreads();
-    if (t < 32) {
-        uint32_t w = warp_tot[t], wi = w;
-#pragma unroll
-        for (int d = 1; d < 32; d <<= 1) {
-            const uint32_t o = __shfl_up_sync(0xffffffffu, wi, d);
-            if (t >= d) wi += o;
-        }
-        warp_tot[t] = wi - w;
-        if (t == 31) s_total = wi;
-    }
-    __syncthreads();
-    uint32_t idx = warp_tot[t >> 5] + incl - count;
+    const unsigned long long excl = rb_block_scan(mine, warp_tot, &s_total);
+    const unsigned long long n_batches = s_total >> 40, n_records = s_total & 0xFFFFFFFFFFull;
+    uint32_t status = TK_RB_OK;
+    if (n_batches > a.max_batches) status = TK_RB_TOO_MANY_BATCHES;
+    else if (n_records > a.slot_records) status = TK_RB_TOO_MANY_RECORDS;
     if (t == 0) {
-        a.summary->n_batches = min(s_total, a.max_batches);
-        a.summary->status = s_total > a.max_batches ? TK_RB_TOO_MANY_BATCHES : TK_RB_OK;
+        a.summary->n_batches = status ? 0u : (uint32_t)n_batches;
+        a.summary->n_records = (uint32_t)min(n_records, 0xFFFFFFFFull);
+        a.summary->n_bytes = 0;
+        a.summary->status = status;
     }
-    if (t < a.n_blobs) {
-        const tk_blob_t blob = a.blobs[t];
-        rb_hdr h;
-        for (uint32_t pos = blob_start; rb_next_header(a.raw, pos, blob_end, h); pos = h.end, ++idx) {
-            if (idx >= a.max_batches) break;
-            tk_rb_batch b;
-            b.start = h.start; b.end = h.end; b.partition = blob.partition; b.status = h.status;
-            b.base_offset = h.status ? 0 : (int64_t)rb_be64(a.raw + h.start) + blob.offset_delta;
-            b.fetch_offset = blob.fetch_offset;
-            b.n_rec = 0; b.value_bytes = 0; b.rec_base = 0; b.byte_base = 0;
-            a.batches[idx] = b;
-        }
+    if (status || t >= a.n_blobs) return;
+    const tk_blob_t blob = a.blobs[t];
+    uint32_t idx = (uint32_t)(excl >> 40), rec = (uint32_t)(excl & 0xFFFFFFFFFFull);
+    rb_hdr h;
+    for (uint32_t pos = blob_start; rb_next_header(a.raw, pos, blob_end, h); pos = h.end, ++idx) {
+        tk_rb_batch b;
+        b.start = h.start; b.end = h.end; b.partition = blob.partition; b.status = h.status;
+        b.base_offset = h.status ? 0 : (int64_t)rb_be64(a.raw + h.start) + blob.offset_delta;
+        b.fetch_offset = blob.fetch_offset;
+        b.n_rec = h.count; b.value_bytes = 0; b.rec_base = rec; b.byte_base = 0;
+        a.batches[idx] = b;
+        rec += h.count;
     }
 }
 
@@ -277,101 +303,101 @@ __device__ __forceinline__ bool rb_decode_record(const uint8_t* raw, uint32_t p,
 }
 
 // ---------------------------------------------------------------- k_rb_check
+// Per record, between the kernels: where its value sits in the raw buffer, how long it is, where
+// it goes inside its batch's share of the slot, and which batch that is.
+struct rb_temp {
+    uint32_t src, len, rel, batch;
+};
+
+// Warp per batch: checksum, then lane 0 walks the records (their bytes are in L1/L2 now) and
+// writes each one's header (partition, offset) and copy descriptor.  A batch that fails keeps its
+// record slots: the first carries the error, the others are marked skipped.
 __global__ void __launch_bounds__(256) k_rb_check(const rb_args a) {
     __shared__ rb_tables tb;
     rb_tables_init(tb);
     const uint32_t lane = threadIdx.x & 31;
     const uint32_t warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, nwarps = (gridDim.x * blockDim.x) >> 5;
     const uint32_t n_batches = a.summary->n_batches;
+    rb_temp* temp = reinterpret_cast<rb_temp*>(a.temp);
     for (uint32_t i = warp; i < n_batches; i += nwarps) {
-        tk_rb_batch b = a.batches[i];
-        uint32_t status = b.status, n_rec = 1, value_bytes = 0;
+        const tk_rb_batch b = a.batches[i];
+        uint32_t status = b.status, value_bytes = 0;
         if (!status) {
             const uint32_t want = rb_be32(a.raw + b.start + 17);
             const uint32_t got = rb_crc32c_warp(tb, a.raw, b.start + RB_CRC_FROM, b.end, lane);
             if (got != want) status = TK_STATUS_CORRUPT;
         }
-        if (!status && lane == 0) {
-            const uint32_t attributes = ((uint32_t)a.raw[b.start + 21] << 8) | a.raw[b.start + 22];
-            const int32_t count = (int32_t)rb_be32(a.raw + b.start + 57);
-            const bool control = attributes & 0x20u;
-            if (attributes & 0x07u) status = TK_STATUS_UNSUPPORTED;              // compressed
-            else if (count < 0 || (uint32_t)count > (b.end - b.start)) status = TK_STATUS_CORRUPT;
-            else {
+        if (lane == 0) {
+            if (!status) {
+                const uint32_t attributes = ((uint32_t)a.raw[b.start + 21] << 8) | a.raw[b.start + 22];
+                const bool control = attributes & 0x20u;
+                if (attributes & 0x07u) status = TK_STATUS_UNSUPPORTED;          // compressed
                 uint32_t p = b.start + RB_HEADER;
                 rb_record r;
-                for (int32_t k = 0; k < count; ++k) {
+                for (uint32_t k = 0; !status && k < b.n_rec; ++k) {
                     if (!rb_decode_record(a.raw, p, b.end, r)) { status = TK_STATUS_CORRUPT; break; }
-                    const bool dropped = control || b.base_offset + r.offset_delta < b.fetch_offset;
-                    if (!dropped && r.value_len > 0) value_bytes += (uint32_t)r.value_len;
+                    const long long offset = b.base_offset + r.offset_delta;
+                    const bool dropped = control || offset < b.fetch_offset;
+                    const uint32_t n = (!dropped && r.value_len > 0) ? (uint32_t)r.value_len : 0u;
+                    rb_temp tmp;
+                    tmp.src = r.value_pos; tmp.len = n; tmp.rel = value_bytes; tmp.batch = i;
+                    temp[b.rec_base + k] = tmp;
+                    tk_rec_t rec;
+                    rec.start = 0;
+                    rec.partition = b.partition | (dropped ? TK_REC_DROPPED : (r.value_len < 0 ? TK_REC_UNSUPPORTED : 0));
+                    rec.offset = offset;
+                    a.recs[b.rec_base + k] = rec;
+                    value_bytes += n;
                     p = r.next;
                 }
                 if (!status && p != b.end) status = TK_STATUS_CORRUPT;
-                if (!status) n_rec = (uint32_t)count;
             }
-        }
-        status = __shfl_sync(0xffffffffu, status, 0);
-        if (lane == 0) {
-            // a batch that cannot be split is carried as one pseudo-record that holds the error
+            if (status) {
+                value_bytes = 0;
+                for (uint32_t k = 0; k < b.n_rec; ++k) {
+                    rb_temp tmp;
+                    tmp.src = 0; tmp.len = 0; tmp.rel = 0; tmp.batch = i;
+                    temp[b.rec_base + k] = tmp;
+                    tk_rec_t rec;
+                    rec.start = 0;
+                    rec.partition = b.partition | (k ? TK_REC_DROPPED
+                                                     : status == TK_STATUS_UNSUPPORTED ? TK_REC_UNSUPPORTED : TK_REC_CORRUPT);
+                    rec.offset = b.base_offset;
+                    a.recs[b.rec_base + k] = rec;
+                }
+            }
             a.batches[i].status = status;
-            a.batches[i].n_rec = status ? 1u : n_rec;
-            a.batches[i].value_bytes = status ? 0u : value_bytes;
+            a.batches[i].value_bytes = value_bytes;
         }
     }
 }
 
 // ---------------------------------------------------------------- k_rb_prefix
+// One block: exclusive scan of the batches' value bytes -> first byte of each batch in the slot.
 __global__ void __launch_bounds__(1024) k_rb_prefix(const rb_args a) {
     __shared__ unsigned long long warp_tot[32];
-    __shared__ unsigned long long s_run;
-    const uint32_t t = threadIdx.x, lane = t & 31;
+    __shared__ unsigned long long s_total, s_run;
+    const uint32_t t = threadIdx.x;
     const uint32_t n_batches = a.summary->n_batches;
     if (t == 0) s_run = 0;
     __syncthreads();
     for (uint32_t base = 0; base < n_batches; base += blockDim.x) {
         const uint32_t i = base + t;
-        unsigned long long v = 0;
-        if (i < n_batches) v = ((unsigned long long)a.batches[i].n_rec << 40) | a.batches[i].value_bytes;
-        unsigned long long incl = v;
-#pragma unroll
-        for (int d = 1; d < 32; d <<= 1) {
-            const unsigned long long o = __shfl_up_sync(0xffffffffu, incl, d);
-            if (lane >= (uint32_t)d) incl += o;
-        }
-        if (lane == 31) warp_tot[t >> 5] = incl;
+        const unsigned long long v = i < n_batches ? a.batches[i].value_bytes : 0ull;
+        const unsigned long long excl = s_run + rb_block_scan(v, warp_tot, &s_total);
+        if (i < n_batches) a.batches[i].byte_base = (uint32_t)excl;
         __syncthreads();
-        if (t < 32) {
-            unsigned long long w = warp_tot[t], wi = w;
-#pragma unroll
-            for (int d = 1; d < 32; d <<= 1) {
-                const unsigned long long o = __shfl_up_sync(0xffffffffu, wi, d);
-                if (t >= (uint32_t)d) wi += o;
-            }
-            warp_tot[t] = wi - w;
-        }
-        __syncthreads();
-        const unsigned long long excl = s_run + warp_tot[t >> 5] + incl - v;
-        if (i < n_batches) {
-            a.batches[i].rec_base = (uint32_t)(excl >> 40);
-            a.batches[i].byte_base = (uint32_t)(excl & 0xFFFFFFFFFFull);
-        }
-        __syncthreads();
-        if (t == blockDim.x - 1) s_run = excl + v;
+        if (t == 0) s_run += s_total;
         __syncthreads();
     }
-    if (t == 0) {
-        const unsigned long long n_rec = s_run >> 40, n_bytes = s_run & 0xFFFFFFFFFFull;
-        a.summary->n_records = (uint32_t)min(n_rec, 0xFFFFFFFFull);
-        a.summary->n_bytes = n_bytes;
-        if (a.summary->status == TK_RB_OK) {
-            if (n_rec > a.slot_records) a.summary->status = TK_RB_TOO_MANY_RECORDS;
-            else if (n_bytes > a.slot_bytes) a.summary->status = TK_RB_TOO_MANY_BYTES;
-            else a.recs[n_rec].start = (uint32_t)n_bytes;          // closes the CSR
-        }
+    if (t == 0 && a.summary->status == TK_RB_OK) {
+        a.summary->n_bytes = s_run;
+        if (s_run > a.slot_bytes) a.summary->status = TK_RB_TOO_MANY_BYTES;
+        else a.recs[a.summary->n_records].start = (uint32_t)s_run;      // closes the CSR
     }
 }
 
-// ---------------------------------------------------------------- k_rb_emit
+// ---------------------------------------------------------------- k_rb_copy
 // dst[0, len) = src[0, len), whole warp; destination words aligned, source funnel-shifted
 __device__ __forceinline__ void rb_warp_copy(uint8_t* dst, const uint8_t* src, uint32_t len, uint32_t lane) {
     const uint32_t head = min((4u - ((uint32_t)(uintptr_t)dst & 3u)) & 3u, len);
@@ -386,45 +412,19 @@ __device__ __forceinline__ void rb_warp_copy(uint8_t* dst, const uint8_t* src, u
     if (done + lane < len) dst[done + lane] = src[done + lane];
 }
 
-__global__ void __launch_bounds__(256) k_rb_emit(const rb_args a) {
+// Warp per record: the value moves to its place in the slot's byte buffer, the record header gets
+// its start.
+__global__ void __launch_bounds__(256) k_rb_copy(const rb_args a) {
     if (a.summary->status != TK_RB_OK) return;
     const uint32_t lane = threadIdx.x & 31;
     const uint32_t warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, nwarps = (gridDim.x * blockDim.x) >> 5;
-    const uint32_t n_batches = a.summary->n_batches;
-    for (uint32_t i = warp; i < n_batches; i += nwarps) {
-        const tk_rb_batch b = a.batches[i];
-        if (b.status) {
-            if (lane == 0) {
-                tk_rec_t rec;
-                rec.start = b.byte_base;
-                rec.partition = b.partition | (b.status == TK_STATUS_UNSUPPORTED ? TK_REC_UNSUPPORTED : TK_REC_CORRUPT);
-                rec.offset = b.base_offset;
-                a.recs[b.rec_base] = rec;
-            }
-            continue;
-        }
-        const bool control = a.raw[b.start + 22] & 0x20u;
-        uint32_t p = b.start + RB_HEADER, dst = b.byte_base;
-        for (uint32_t k = 0; k < b.n_rec; ++k) {
-            rb_record r;
-            r.value_pos = 0; r.value_len = 0; r.offset_delta = 0; r.next = 0;
-            if (lane == 0) rb_decode_record(a.raw, p, b.end, r);       // validated by k_rb_check
-            const uint32_t vpos = __shfl_sync(0xffffffffu, r.value_pos, 0);
-            const int32_t vlen = __shfl_sync(0xffffffffu, r.value_len, 0);
-            p = __shfl_sync(0xffffffffu, r.next, 0);
-            const long long offset = b.base_offset + __shfl_sync(0xffffffffu, (long long)r.offset_delta, 0);
-            const bool dropped = control || offset < b.fetch_offset;
-            const uint32_t n = (!dropped && vlen > 0) ? (uint32_t)vlen : 0u;
-            if (n) rb_warp_copy(a.bytes + dst, a.raw + vpos, n, lane);
-            if (lane == 0) {
-                tk_rec_t rec;
-                rec.start = dst;
-                rec.partition = b.partition | (dropped ? TK_REC_DROPPED : (vlen < 0 ? TK_REC_UNSUPPORTED : 0));
-                rec.offset = offset;
-                a.recs[b.rec_base + k] = rec;
-            }
-            dst += n;
-        }
+    const uint32_t n = a.summary->n_records;
+    const uint4* temp = reinterpret_cast<const uint4*>(a.temp);
+    for (uint32_t i = warp; i < n; i += nwarps) {
+        const uint4 t = __ldg(temp + i);                      // {src, len, rel, batch}
+        const uint32_t dst = a.batches[t.w].byte_base + t.z;
+        if (lane == 0) a.recs[i].start = dst;
+        if (t.y) rb_warp_copy(a.bytes + dst, a.raw + t.x, t.y, lane);
     }
 }
 
@@ -441,6 +441,7 @@ static int rb_ensure(tk_ctx* ctx) {
         TK_CUDA(cudaMalloc(&s.d.blobs, sizeof(tk_blob_t) * TK_MAX_BLOBS));
         TK_CUDA(cudaMalloc(&s.d.rb_batches, sizeof(tk_rb_batch) * (size_t)ctx->slot_records));
         TK_CUDA(cudaMalloc(&s.d.rb_summary, sizeof(tk_rb_summary_t)));
+        TK_CUDA(cudaMalloc(&s.d.rb_temp, sizeof(uint4) * (size_t)ctx->slot_records));
         TK_CUDA(cudaHostAlloc(&s.h_blobs, sizeof(tk_blob_t) * TK_MAX_BLOBS, cudaHostAllocDefault));
         TK_CUDA(cudaHostAlloc(&s.h_rb_summary, sizeof(tk_rb_summary_t), cudaHostAllocDefault));
     }
@@ -469,12 +470,12 @@ extern "C" int tk_slot_submit_recordbatches(tk_ctx* ctx, int slot, uint64_t n_by
     if (n_blobs) TK_CUDA(cudaMemcpyAsync(s.d.blobs, s.h_blobs, sizeof(tk_blob_t) * n_blobs, cudaMemcpyHostToDevice, st));
     rb_args a;
     a.raw = s.d.raw; a.blobs = s.d.blobs; a.n_blobs = n_blobs; a.batches = s.d.rb_batches;
-    a.max_batches = ctx->slot_records; a.summary = s.d.rb_summary; a.bytes = s.d.bytes; a.recs = s.d.recs;
+    a.max_batches = ctx->slot_records; a.summary = s.d.rb_summary; a.temp = s.d.rb_temp; a.bytes = s.d.bytes; a.recs = s.d.recs;
     a.slot_records = ctx->slot_records; a.slot_bytes = ctx->slot_bytes;
     k_rb_headers<<<1, 1024, 0, st>>>(a);
     k_rb_check<<<148 * 4, 256, 0, st>>>(a);
     k_rb_prefix<<<1, 1024, 0, st>>>(a);
-    k_rb_emit<<<148 * 4, 256, 0, st>>>(a);
+    k_rb_copy<<<148 * 8, 256, 0, st>>>(a);
     TK_LAUNCH_CHECK();
     TK_CUDA(cudaMemcpyAsync(s.h_rb_summary, s.d.rb_summary, sizeof(tk_rb_summary_t), cudaMemcpyDeviceToHost, st));
     TK_CUDA(cudaEventRecord(s.ev_h2d, st));

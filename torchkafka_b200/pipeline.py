@@ -247,8 +247,13 @@ class IngestPipeline:
                                  [(int(starts[i]), int(lens[i]), int(parts[i]), int(fetch_offsets[i]),
                                    int(fetch.blobs[i][3])) for i in range(k)])
         self.stats["t_pack"] += time.perf_counter() - t0
+        # the record count is known once the device has split the batches; the consuming thread
+        # asks for it right before it launches the slot's kernels (_split_result)
+        return None, int(starts[k])
+
+    def _split_result(self, slot: int):
         t0 = time.perf_counter()
-        n, nbytes, _ = eng.recordbatch_result(slot)
+        n, nbytes, _ = self.engine.recordbatch_result(slot)
         self.stats["t_split_wait"] = self.stats.get("t_split_wait", 0.0) + time.perf_counter() - t0
         return n, nbytes
 
@@ -515,6 +520,9 @@ class IngestPipeline:
         for slot, n, nbytes, parts, offs in slots:
             t0 = time.perf_counter()
             self.stats["t_wait_slot"] += t0 - t_get
+            if n is None:                          # record batches: split on the device
+                n, nbytes = self._split_result(slot)
+                t0 = time.perf_counter()
             out = eng.process(slot, n, prev_slot, prev_out)
             self.stats["t_launch"] += time.perf_counter() - t0
             pending.append(_Pending(slot, n, out, parts, offs))

@@ -119,6 +119,11 @@ class EncodedLog:
         self.partition = np.asarray(part_of, dtype=np.int32)
         self.start = np.asarray(pos_of + [pos], dtype=np.int64)
         self.n_batches = len(part_of)
+        # run_end[b]: index of the first batch after b that belongs to another partition
+        nbt = self.n_batches
+        change = np.flatnonzero(self.partition[1:] != self.partition[:-1]) + 1 if nbt > 1 else np.zeros(0, np.int64)
+        ends = np.concatenate([change, [nbt]]).astype(np.int64)
+        self.run_end = ends[np.searchsorted(ends, np.arange(nbt), side="right")] if nbt else np.zeros(0, np.int64)
 
     @property
     def nbytes(self) -> int:

@@ -317,11 +317,11 @@ class KafkaConsumer:
         handed out through ``poll()`` / iteration), the batch is returned whole with
         ``fetch_offset`` = the position, as a broker does.  Returns ``None`` at the end of the log.
         """
-        n = len(self._log)
         if not self._roll():
             return None
         enc = self._log.encoded(self._raw_batch_bytes)
-        first = enc.first_rec
+        first, start, part = enc.first_rec, enc.start, enc.partition
+        run_end = enc.run_end                    # run_end[b] = first batch after b of another partition
         b = int(np.searchsorted(first, self._cursor, side="right")) - 1      # batch holding the cursor
         offs = self._log.rep_offsets(self._rep)
         delta_of = (self._rep * self._log.per_partition_count()) if self._rep else None
@@ -329,33 +329,34 @@ class KafkaConsumer:
         seen = set()
         nbytes = nrec = 0
         cursor = self._cursor
-        while b < enc.n_batches:
-            p = int(enc.partition[b])
+        nb = enc.n_batches
+        while b < nb:
+            p = int(part[b])
             if p in seen:
                 break                                    # would re-open a partition
-            # extend over the following batches of the same partition
-            e = b
-            size = count = 0
-            while e < enc.n_batches and int(enc.partition[e]) == p:
-                bsz = int(enc.start[e + 1] - enc.start[e])
-                bcnt = int(first[e + 1] - first[e])
-                if (blobs or e > b) and (nbytes + size + bsz > max_bytes or nrec + count + bcnt > max_records):
-                    break
-                size += bsz
-                count += bcnt
-                e += 1
-            if e == b:
-                break
-            data = enc.data[int(enc.start[b]):int(enc.start[e])]
+            # whole batches of this partition's run, as many as the limits allow (at least one if
+            # the response is still empty)
+            e = int(run_end[b])
+            byte_room = max_bytes - nbytes
+            rec_room = max_records - nrec
+            if int(start[e] - start[b]) > byte_room or int(first[e] - first[b]) > rec_room:
+                e = min(int(np.searchsorted(start, start[b] + byte_room, side="right")) - 1,
+                        int(np.searchsorted(first, first[b] + rec_room, side="right")) - 1, e)
+                if e <= b:
+                    if blobs:
+                        break
+                    e = b + 1
+            data = enc.data[int(start[b]):int(start[e])]
             delta = int(delta_of[p]) if delta_of is not None else 0
             blobs.append((p, data, int(offs[cursor]), delta))
             seen.add(p)
-            nbytes += size
-            nrec += count
+            nbytes += int(start[e] - start[b])
+            nrec += int(first[e] - first[b])
             cursor = int(first[e])
             self._positions[p] = int(offs[cursor - 1]) + 1
+            partial = e < int(run_end[b])
             b = e
-            if nbytes >= max_bytes or nrec >= max_records:
+            if partial or nbytes >= max_bytes or nrec >= max_records:
                 break
         self._cursor = cursor
         return RawFetch(blobs, self._log.topic)

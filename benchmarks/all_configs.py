@@ -79,18 +79,23 @@ def device_resident(cfg, log, passes=24):
             "payload_GBps": (log.nbytes + 16 * len(log)) / ms / 1e6}, peak
 
 
+RAW_BATCH_BYTES = 64 << 10
+
+
 def e2e(cfg, log, packed, repeat, batches_timed, warm):
+    """packed: False = poll() objects, True = poll_packed() arrays, "raw" = poll_raw() record batches."""
     consumer_cls = sk.KafkaConsumer if packed else sk.PollOnlyConsumer
 
     class DS(KafkaDataset):
         payload_schema = cfg["schema"]
-        device_slot_bytes = cfg["slot_bytes"]
+        device_slot_bytes = cfg["slot_bytes"] + (cfg["slot_bytes"] >> 2 if packed == "raw" else 0)   # framing
         device_slots = 3
+        device_input = "raw" if packed == "raw" else "auto"
 
         @classmethod
         def new_consumer(cls, *a, **k):
             k.pop("enable_auto_commit", None)
-            return consumer_cls(*a, log=log, repeat=repeat, **k)
+            return consumer_cls(*a, log=log, repeat=repeat, raw_batch_bytes=max(RAW_BATCH_BYTES, 2 * cfg.get("record_bytes", 0)), **k)
 
     from torch.utils.data import DataLoader
     ds = DS("topic", group_id="cfg")
@@ -157,11 +162,16 @@ def main():
         warm = max(3, nb // 8)
         row = {"config": c, "name": cfg["name"], "records": len(log), "avg_value_bytes": log.nbytes / len(log),
                "link_bytes_per_record": link_bytes, "device": dev, "h2d_peak_GBps": peak}
-        for packed in (False, True):
+        for packed in (False, True, "raw"):
+            if packed == "raw":
+                enc = log.encoded(max(RAW_BATCH_BYTES, 2 * cfg.get("record_bytes", 0)))   # before the clock
+                lb = enc.nbytes / len(log)
+            else:
+                lb = link_bytes
             rps = e2e(cfg, log, packed, repeat, nb - warm, warm)
-            row["e2e_packed" if packed else "e2e_poll"] = {
-                "records_per_s": rps, "link_GBps": rps * link_bytes / 1e9,
-                "link_frac": rps * link_bytes / 1e9 / peak}
+            row["e2e_raw" if packed == "raw" else "e2e_packed" if packed else "e2e_poll"] = {
+                "records_per_s": rps, "link_GBps": rps * lb / 1e9,
+                "link_frac": rps * lb / 1e9 / peak}
         if not args.no_cpu:
             row["cpu_oracle_1core_records_per_s"] = cpu_oracle(cfg, log)
         rows.append(row)

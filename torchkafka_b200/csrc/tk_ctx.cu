@@ -375,19 +375,26 @@ extern "C" int tk_slot_pack(tk_ctx* ctx, int slot, uint32_t first_record, uint64
     if (total < (1u << 20) || n_threads == 1) {
         for (uint32_t i = 0; i < n; ++i) memcpy(s.h_bytes + s.h_recs[first_record + i].start, values[i], lengths[i]);
     } else {
-        // record ranges of similar byte volume, one range per part
-        std::vector<uint32_t> cut(n_threads + 1, n);
-        cut[0] = 0;
-        uint32_t a = 0;
-        for (int t = 1; t < n_threads; ++t) {
-            const uint64_t want = first_byte + total * (uint64_t)t / n_threads;
-            while (a < n && s.h_recs[first_record + a].start < want) ++a;
-            cut[t] = a;
-        }
+        // equal byte ranges, one per part; a range may start and end inside a value (a fetch
+        // response can be a handful of multi-megabyte blobs)
         tk_slot* sp = &s;
         copy_pool(n_threads)->run(n_threads, [=](int t) {
-            for (uint32_t i = cut[t]; i < cut[t + 1]; ++i)
-                stream_copy(sp->h_bytes + sp->h_recs[first_record + i].start, values[i], lengths[i]);
+            const uint64_t lo = first_byte + total * (uint64_t)t / n_threads;
+            const uint64_t hi = first_byte + total * (uint64_t)(t + 1) / n_threads;
+            if (hi <= lo) return;
+            // first record whose end lies behind lo
+            uint32_t a = 0, b = n;
+            while (a < b) {
+                const uint32_t m = (a + b) / 2;
+                if ((uint64_t)sp->h_recs[first_record + m + 1].start <= lo) a = m + 1; else b = m;
+            }
+            for (uint32_t i = a; i < n; ++i) {
+                const uint64_t rs = sp->h_recs[first_record + i].start;
+                if (rs >= hi) break;
+                const uint64_t re = rs + lengths[i];
+                const uint64_t from = rs > lo ? rs : lo, to = re < hi ? re : hi;
+                if (to > from) stream_copy(sp->h_bytes + from, values[i] + (from - rs), to - from);
+            }
             stream_fence();
         });
     }

@@ -107,9 +107,17 @@ struct rb_hdr {
 };
 __device__ __forceinline__ bool rb_next_header(const uint8_t* raw, uint32_t pos, uint32_t blob_end, rb_hdr& h) {
     if (blob_end - pos < 12u) return false;
-    const uint32_t blen = rb_be32(raw + pos + 8);
-    const uint32_t magic = raw[pos + 16];                 // (inside the padded buffer even if cut)
-    const uint32_t count = rb_be32(raw + pos + 57);
+    // (volatile asm: the compiler would otherwise sink each load below the branch that first needs
+    // it and turn one round trip into three; all addresses lie inside the padded buffer)
+    uint32_t hb[9];
+#pragma unroll
+    for (int k = 0; k < 9; ++k) {
+        const uint8_t* q = raw + pos + (k < 4 ? 8 + k : k == 4 ? 16 : 57 + (k - 5));
+        asm volatile("ld.global.u8 %0, [%1];" : "=r"(hb[k]) : "l"(q));
+    }
+    const uint32_t blen = (hb[0] << 24) | (hb[1] << 16) | (hb[2] << 8) | hb[3];
+    const uint32_t magic = hb[4];
+    const uint32_t count = (hb[5] << 24) | (hb[6] << 16) | (hb[7] << 8) | hb[8];
     h.start = pos;
     h.count = 1;
     if ((int32_t)blen < (int32_t)(RB_HEADER - 12u)) { h.end = blob_end; h.status = TK_STATUS_CORRUPT; return true; }
@@ -242,10 +250,33 @@ __device__ __forceinline__ uint32_t rb_crc32c_warp(const rb_tables& tb, const ui
     if (rows) {
         uint32_t s = lane == 0 ? c : 0u;
         const uint4* src = reinterpret_cast<const uint4*>(raw + pos) + lane;
-        uint4 v = __ldg(src);
-        for (uint32_t r = 0; r < rows; ++r) {
-            const uint4 cur = v;
-            if (r + 1 < rows) v = __ldg(src + (size_t)(r + 1) * 32);
+        uint32_t r = 0;
+        if (rows >= 8) {
+            // four row streams per lane (quarters of the rows): the table walk of one stream is a
+            // chain of dependent shared-memory lookups, four of them in flight hide its latency
+            const uint32_t q = rows / 4;
+            uint32_t s1 = 0, s2 = 0, s3 = 0;
+            const uint4 *p0 = src, *p1 = src + (size_t)q * 32, *p2 = src + (size_t)2 * q * 32, *p3 = src + (size_t)3 * q * 32;
+            for (uint32_t i = 0; i < q; ++i) {
+                const uint4 v0 = __ldg(p0 + (size_t)i * 32), v1 = __ldg(p1 + (size_t)i * 32);
+                const uint4 v2 = __ldg(p2 + (size_t)i * 32), v3 = __ldg(p3 + (size_t)i * 32);
+                if (i) { s = crc_skip496(tb, s); s1 = crc_skip496(tb, s1); s2 = crc_skip496(tb, s2); s3 = crc_skip496(tb, s3); }
+                s = crc_word(tb, s, v0.x); s1 = crc_word(tb, s1, v1.x); s2 = crc_word(tb, s2, v2.x); s3 = crc_word(tb, s3, v3.x);
+                s = crc_word(tb, s, v0.y); s1 = crc_word(tb, s1, v1.y); s2 = crc_word(tb, s2, v2.y); s3 = crc_word(tb, s3, v3.y);
+                s = crc_word(tb, s, v0.z); s1 = crc_word(tb, s1, v1.z); s2 = crc_word(tb, s2, v2.z); s3 = crc_word(tb, s3, v3.z);
+                s = crc_word(tb, s, v0.w); s1 = crc_word(tb, s1, v1.w); s2 = crc_word(tb, s2, v2.w); s3 = crc_word(tb, s3, v3.w);
+            }
+            // join: every stream is advanced over the q rows of each stream behind it
+            uint32_t mq = 0x80000000u;                                  // x^0
+            for (uint32_t j = 0, k = q; k; ++j, k >>= 1)
+                if (k & 1u) mq = crc_mul(mq, tk_crc32c_dev_xrow[j]);
+            s = crc_mul(s, mq) ^ s1;
+            s = crc_mul(s, mq) ^ s2;
+            s = crc_mul(s, mq) ^ s3;
+            r = 4 * q;
+        }
+        for (; r < rows; ++r) {
+            const uint4 cur = __ldg(src + (size_t)r * 32);
             if (r) s = crc_skip496(tb, s);
             s = crc_word(tb, s, cur.x);
             s = crc_word(tb, s, cur.y);

@@ -148,7 +148,9 @@ def main():
     rows = []
     for c in [int(x) for x in args.configs.split(",")]:
         cfg = CONFIGS[c]
-        log = syn.make_log(c, cfg["n"], seed=100 + c, partitions=64, layout="chunked", chunk=500)
+        # runs of 500 records per partition; images (150 KB each) in runs of 4 so that a fetch of one
+        # slot still spans all 64 partitions, as a real fetch response does
+        log = syn.make_log(c, cfg["n"], seed=100 + c, partitions=64, layout="chunked", chunk=4 if c == 4 else 500)
         dev, peak = device_resident(cfg, log)
         link_bytes = (log.nbytes + 16 * len(log)) / len(log)
         slot_recs = max(1, min(len(log), int(cfg["slot_bytes"] // max(log.nbytes / len(log), 1))))

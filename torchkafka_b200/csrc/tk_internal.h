@@ -71,6 +71,7 @@ struct tk_slot_dev {
     tk_rb_batch* rb_batches;   // [slot_records]
     tk_rb_summary_t* rb_summary;
     uint4*       rb_temp;      // [slot_records] per-record copy descriptors
+    uint32_t*    rb_bigq;      // records copied piecewise
     uint8_t*     block;        // one allocation: header | batch_end | batch_lmax | commit
     tk_result_t* result;       // header
     uint32_t*    batch_end;    // [max_batches + 1]

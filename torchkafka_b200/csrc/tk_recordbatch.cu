@@ -16,11 +16,13 @@
 //                 the index of its first record (sum of the headers' record counts)
 //   k_rb_check    warp per batch: CRC-32C of the batch (strided slicing-by-4, lanes own one 16-byte
 //                 chunk of every 512-byte row; lane states combined by carry-less multiplication),
-//                 then lane 0 walks the records (bytes now in L1/L2): framing checks, record
-//                 headers (partition, offset), one copy descriptor per record
+//                 then the record walk (bytes now in L1/L2): lane 0 follows the chain of record
+//                 lengths, 32 at a time, and every lane decodes one record: framing checks,
+//                 record header (partition, offset), copy descriptor
 //   k_rb_prefix   one block: exclusive scan of the batches' value bytes, capacity check
 //   k_rb_copy     warp per record: the value moves to its place in the slot's byte buffer (aligned
-//                 destination words, funnel-shifted source)
+//                 destination words, funnel-shifted source); values above 16 KiB are queued and
+//                 copied in 4 KiB pieces by all warps (k_rb_copy_big)
 // Big-endian header fields, zig-zag varints.  Uncompressed batches only (codecs: SURVEY §8f-2).
 #include "tk_internal.h"
 #include <mutex>
@@ -91,6 +93,7 @@ struct rb_args {
     uint32_t         max_batches;
     tk_rb_summary_t* summary;
     uint4*           temp;            // [slot_records] per-record copy descriptors (rb_temp)
+    uint32_t*        bigq;            // records longer than RB_BIG, copied piecewise by k_rb_copy_big
     uint8_t*         bytes;           // slot byte buffer (destination)
     tk_rec_t*        recs;            // slot record headers (destination)
     uint32_t         slot_records;
@@ -184,6 +187,7 @@ __global__ void __launch_bounds__(1024) k_rb_headers(const rb_args a) {
         a.summary->n_records = (uint32_t)min(n_records, 0xFFFFFFFFull);
         a.summary->n_bytes = 0;
         a.summary->status = status;
+        a.summary->reserved = 0;                          // length of the big-record queue
     }
     if (status || t >= a.n_blobs) return;
     const tk_blob_t blob = a.blobs[t];
@@ -340,13 +344,16 @@ struct rb_temp {
     uint32_t src, len, rel, batch;
 };
 
-// Warp per batch: checksum, then lane 0 walks the records (their bytes are in L1/L2 now) and
-// writes each one's header (partition, offset) and copy descriptor.  A batch that fails keeps its
-// record slots: the first carries the error, the others are marked skipped.
+// Warp per batch: checksum, then the record walk (the batch's bytes are in L1/L2 now).  Only the
+// chain of record lengths is sequential: lane 0 follows it for 32 records at a time (one varint and
+// one add per record), then every lane decodes one record completely and writes its header
+// (partition, offset) and copy descriptor.  A batch that fails keeps its record slots: the first
+// carries the error, the others are marked skipped.
 __global__ void __launch_bounds__(256) k_rb_check(const rb_args a) {
     __shared__ rb_tables tb;
+    __shared__ uint32_t s_pos[8][33];
     rb_tables_init(tb);
-    const uint32_t lane = threadIdx.x & 31;
+    const uint32_t lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
     const uint32_t warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, nwarps = (gridDim.x * blockDim.x) >> 5;
     const uint32_t n_batches = a.summary->n_batches;
     rb_temp* temp = reinterpret_cast<rb_temp*>(a.temp);
@@ -358,45 +365,81 @@ __global__ void __launch_bounds__(256) k_rb_check(const rb_args a) {
             const uint32_t got = rb_crc32c_warp(tb, a.raw, b.start + RB_CRC_FROM, b.end, lane);
             if (got != want) status = TK_STATUS_CORRUPT;
         }
-        if (lane == 0) {
-            if (!status) {
-                const uint32_t attributes = ((uint32_t)a.raw[b.start + 21] << 8) | a.raw[b.start + 22];
-                const bool control = attributes & 0x20u;
-                if (attributes & 0x07u) status = TK_STATUS_UNSUPPORTED;          // compressed
-                uint32_t p = b.start + RB_HEADER;
+        bool control = false;
+        if (!status) {
+            const uint32_t attributes = ((uint32_t)a.raw[b.start + 21] << 8) | a.raw[b.start + 22];
+            control = attributes & 0x20u;
+            if (attributes & 0x07u) status = TK_STATUS_UNSUPPORTED;              // compressed
+        }
+        uint32_t p = b.start + RB_HEADER;                                        // lane 0's cursor
+        for (uint32_t k0 = 0; !status && k0 < b.n_rec; k0 += 32) {
+            const uint32_t m = min(32u, b.n_rec - k0);
+            if (lane == 0) {
+                uint32_t bad = 0;
+                for (uint32_t j = 0; j < m; ++j) {
+                    s_pos[wib][j] = p;
+                    long long length;
+                    uint32_t q = p;
+                    if (!rb_varint(a.raw, q, b.end, length) || length < 1 || (unsigned long long)length > b.end - q) {
+                        bad = 1;
+                        break;
+                    }
+                    p = q + (uint32_t)length;
+                }
+                s_pos[wib][32] = bad;
+            }
+            __syncwarp();
+            if (s_pos[wib][32]) status = TK_STATUS_CORRUPT;
+            uint32_t n = 0;
+            if (!status && lane < m) {
                 rb_record r;
-                for (uint32_t k = 0; !status && k < b.n_rec; ++k) {
-                    if (!rb_decode_record(a.raw, p, b.end, r)) { status = TK_STATUS_CORRUPT; break; }
+                if (!rb_decode_record(a.raw, s_pos[wib][lane], b.end, r)) {
+                    status = TK_STATUS_CORRUPT;
+                } else {
                     const long long offset = b.base_offset + r.offset_delta;
                     const bool dropped = control || offset < b.fetch_offset;
-                    const uint32_t n = (!dropped && r.value_len > 0) ? (uint32_t)r.value_len : 0u;
-                    rb_temp tmp;
-                    tmp.src = r.value_pos; tmp.len = n; tmp.rel = value_bytes; tmp.batch = i;
-                    temp[b.rec_base + k] = tmp;
+                    n = (!dropped && r.value_len > 0) ? (uint32_t)r.value_len : 0u;
                     tk_rec_t rec;
                     rec.start = 0;
                     rec.partition = b.partition | (dropped ? TK_REC_DROPPED : (r.value_len < 0 ? TK_REC_UNSUPPORTED : 0));
                     rec.offset = offset;
-                    a.recs[b.rec_base + k] = rec;
-                    value_bytes += n;
-                    p = r.next;
-                }
-                if (!status && p != b.end) status = TK_STATUS_CORRUPT;
-            }
-            if (status) {
-                value_bytes = 0;
-                for (uint32_t k = 0; k < b.n_rec; ++k) {
-                    rb_temp tmp;
-                    tmp.src = 0; tmp.len = 0; tmp.rel = 0; tmp.batch = i;
-                    temp[b.rec_base + k] = tmp;
-                    tk_rec_t rec;
-                    rec.start = 0;
-                    rec.partition = b.partition | (k ? TK_REC_DROPPED
-                                                     : status == TK_STATUS_UNSUPPORTED ? TK_REC_UNSUPPORTED : TK_REC_CORRUPT);
-                    rec.offset = b.base_offset;
-                    a.recs[b.rec_base + k] = rec;
+                    a.recs[b.rec_base + k0 + lane] = rec;
+                    // .src now, .rel after the warp scan below
+                    temp[b.rec_base + k0 + lane].src = r.value_pos;
                 }
             }
+            if (__any_sync(0xffffffffu, status != 0)) { status = TK_STATUS_CORRUPT; break; }
+            uint32_t incl = n;
+#pragma unroll
+            for (int d = 1; d < 32; d <<= 1) {
+                const uint32_t o = __shfl_up_sync(0xffffffffu, incl, d);
+                if (lane >= (uint32_t)d) incl += o;
+            }
+            if (lane < m) {
+                rb_temp* t = &temp[b.rec_base + k0 + lane];
+                t->len = n; t->rel = value_bytes + incl - n; t->batch = i;
+            }
+            value_bytes += __shfl_sync(0xffffffffu, incl, 31);
+            __syncwarp();
+        }
+        // the cursor must land on the end of the batch
+        const uint32_t p_end = __shfl_sync(0xffffffffu, p, 0);
+        if (!status && p_end != b.end) status = TK_STATUS_CORRUPT;
+        if (status) {
+            value_bytes = 0;
+            for (uint32_t k = lane; k < b.n_rec; k += 32) {
+                rb_temp tmp;
+                tmp.src = 0; tmp.len = 0; tmp.rel = 0; tmp.batch = i;
+                temp[b.rec_base + k] = tmp;
+                tk_rec_t rec;
+                rec.start = 0;
+                rec.partition = b.partition | (k ? TK_REC_DROPPED
+                                                 : status == TK_STATUS_UNSUPPORTED ? TK_REC_UNSUPPORTED : TK_REC_CORRUPT);
+                rec.offset = b.base_offset;
+                a.recs[b.rec_base + k] = rec;
+            }
+        }
+        if (lane == 0) {
             a.batches[i].status = status;
             a.batches[i].value_bytes = value_bytes;
         }
@@ -444,7 +487,11 @@ __device__ __forceinline__ void rb_warp_copy(uint8_t* dst, const uint8_t* src, u
 }
 
 // Warp per record: the value moves to its place in the slot's byte buffer, the record header gets
-// its start.
+// its start.  Values longer than RB_BIG are only queued here: one warp per multi-megabyte value
+// would leave the rest of the GPU idle, so k_rb_copy_big spreads their RB_PIECE-byte pieces over
+// all warps.
+#define RB_BIG 16384u
+#define RB_PIECE 4096u
 __global__ void __launch_bounds__(256) k_rb_copy(const rb_args a) {
     if (a.summary->status != TK_RB_OK) return;
     const uint32_t lane = threadIdx.x & 31;
@@ -454,8 +501,39 @@ __global__ void __launch_bounds__(256) k_rb_copy(const rb_args a) {
     for (uint32_t i = warp; i < n; i += nwarps) {
         const uint4 t = __ldg(temp + i);                      // {src, len, rel, batch}
         const uint32_t dst = a.batches[t.w].byte_base + t.z;
-        if (lane == 0) a.recs[i].start = dst;
-        if (t.y) rb_warp_copy(a.bytes + dst, a.raw + t.x, t.y, lane);
+        if (lane == 0) {
+            a.recs[i].start = dst;
+            if (t.y > RB_BIG) a.bigq[atomicAdd(&a.summary->reserved, 1u)] = i;
+        }
+        if (t.y && t.y <= RB_BIG) rb_warp_copy(a.bytes + dst, a.raw + t.x, t.y, lane);
+    }
+}
+
+__global__ void __launch_bounds__(256) k_rb_copy_big(const rb_args a) {
+    if (a.summary->status != TK_RB_OK) return;
+    const uint32_t count = a.summary->reserved;
+    if (!count) return;
+    const uint32_t lane = threadIdx.x & 31;
+    const uint32_t warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, nwarps = (gridDim.x * blockDim.x) >> 5;
+    const uint4* temp = reinterpret_cast<const uint4*>(a.temp);
+    uint32_t piece0 = 0;                                      // global index of the entry's first piece
+    for (uint32_t e = 0; e < count; ++e) {
+        const uint4 t = __ldg(temp + a.bigq[e]);
+        const uint32_t pieces = (t.y + RB_PIECE - 1) / RB_PIECE;
+        // first piece of this entry that belongs to this warp: global index == warp (mod nwarps)
+        uint32_t k = (warp + nwarps - piece0 % nwarps) % nwarps;
+        if (k < pieces) {
+            const uint32_t dst = a.batches[t.w].byte_base + t.z;
+            // pieces are cut at 4-byte boundaries of the destination so that every piece but the
+            // first starts on an aligned word
+            const uint32_t lead = (4u - (dst & 3u)) & 3u;
+            for (; k < pieces; k += nwarps) {
+                const uint32_t from = k ? k * RB_PIECE + lead : 0u;
+                const uint32_t to = min((k + 1) * RB_PIECE + lead, t.y);
+                if (from < to) rb_warp_copy(a.bytes + dst + from, a.raw + t.x + from, to - from, lane);
+            }
+        }
+        piece0 += pieces;
     }
 }
 
@@ -473,6 +551,7 @@ static int rb_ensure(tk_ctx* ctx) {
         TK_CUDA(cudaMalloc(&s.d.rb_batches, sizeof(tk_rb_batch) * (size_t)ctx->slot_records));
         TK_CUDA(cudaMalloc(&s.d.rb_summary, sizeof(tk_rb_summary_t)));
         TK_CUDA(cudaMalloc(&s.d.rb_temp, sizeof(uint4) * (size_t)ctx->slot_records));
+        TK_CUDA(cudaMalloc(&s.d.rb_bigq, sizeof(uint32_t) * ((size_t)(ctx->slot_bytes / RB_BIG) + 2)));
         TK_CUDA(cudaHostAlloc(&s.h_blobs, sizeof(tk_blob_t) * TK_MAX_BLOBS, cudaHostAllocDefault));
         TK_CUDA(cudaHostAlloc(&s.h_rb_summary, sizeof(tk_rb_summary_t), cudaHostAllocDefault));
     }
@@ -501,12 +580,13 @@ extern "C" int tk_slot_submit_recordbatches(tk_ctx* ctx, int slot, uint64_t n_by
     if (n_blobs) TK_CUDA(cudaMemcpyAsync(s.d.blobs, s.h_blobs, sizeof(tk_blob_t) * n_blobs, cudaMemcpyHostToDevice, st));
     rb_args a;
     a.raw = s.d.raw; a.blobs = s.d.blobs; a.n_blobs = n_blobs; a.batches = s.d.rb_batches;
-    a.max_batches = ctx->slot_records; a.summary = s.d.rb_summary; a.temp = s.d.rb_temp; a.bytes = s.d.bytes; a.recs = s.d.recs;
+    a.max_batches = ctx->slot_records; a.summary = s.d.rb_summary; a.temp = s.d.rb_temp; a.bigq = s.d.rb_bigq; a.bytes = s.d.bytes; a.recs = s.d.recs;
     a.slot_records = ctx->slot_records; a.slot_bytes = ctx->slot_bytes;
     k_rb_headers<<<1, 1024, 0, st>>>(a);
     k_rb_check<<<148 * 4, 256, 0, st>>>(a);
     k_rb_prefix<<<1, 1024, 0, st>>>(a);
     k_rb_copy<<<148 * 8, 256, 0, st>>>(a);
+    k_rb_copy_big<<<148 * 8, 256, 0, st>>>(a);
     TK_LAUNCH_CHECK();
     TK_CUDA(cudaMemcpyAsync(s.h_rb_summary, s.d.rb_summary, sizeof(tk_rb_summary_t), cudaMemcpyDeviceToHost, st));
     TK_CUDA(cudaEventRecord(s.ev_h2d, st));

@@ -246,22 +246,25 @@ typedef struct tk_rb_summary {
     uint32_t n_records;      /* records in the slot, including skipped ones */
     uint32_t n_batches;
     uint64_t n_bytes;        /* value bytes in the slot */
-    uint32_t status;         /* TK_RB_* */
+    uint32_t status;         /* TK_RB_OK */
     uint32_t reserved;
 } tk_rb_summary_t;
-enum { TK_RB_OK = 0, TK_RB_TOO_MANY_BATCHES = 1, TK_RB_TOO_MANY_RECORDS = 2, TK_RB_TOO_MANY_BYTES = 3 };
+enum { TK_RB_OK = 0 };
 #define TK_MAX_BLOBS 1024u
 /* flags the split leaves in tk_rec_t.partition (the scans act on them) */
 #define TK_REC_DROPPED     0x40000000   /* below the fetch offset / control batch: not consumed */
 #define TK_REC_CORRUPT     0x20000000
 #define TK_REC_UNSUPPORTED 0x10000000
 #define TK_REC_FLAGS       0x70000000
-/* raw bytes are in the slot's pinned buffer [0, n_bytes); asynchronous (H2D + kernels on the
- * library's copy stream); tk_process_slot / tk_slot_wait order behind it as behind tk_slot_submit */
+/* Raw bytes are in the slot's pinned buffer [0, n_bytes).  The call follows the chain of batch
+ * headers of every blob on the host (one read per batch) and returns the number of record
+ * entries the slot will hold in *n_records (skipped records included: their entries stay, flagged);
+ * the H2D copy and the split kernels (CRC-32C, record framing, value gather) are asynchronous on
+ * the library's copy stream; tk_process_slot / tk_slot_wait order behind them as behind
+ * tk_slot_submit.  Fails at once if the slot geometry (slot_records) is too small. */
 int tk_slot_submit_recordbatches(tk_ctx* ctx, int slot, uint64_t n_bytes, const tk_blob_t* blobs,
-                                 uint32_t n_blobs);
-/* wait for the split; the slot then holds summary->n_records records.  A non-zero
- * summary->status means the slot geometry was too small and nothing was written. */
+                                 uint32_t n_blobs, uint32_t* n_records);
+/* optional: wait for the split and read its totals (value bytes, batches) */
 int tk_slot_recordbatch_result(tk_ctx* ctx, int slot, tk_rb_summary_t* summary);
 /* one record header of the device twin (error reports) */
 int tk_slot_record(tk_ctx* ctx, int slot, uint32_t index, tk_rec_t* out);

@@ -65,8 +65,9 @@ def split_on_gpu(blobs, slot_bytes=1 << 20, slot_records=4096, schema=None):
         hb[pos:pos + len(data)] = np.frombuffer(data, dtype=np.uint8)
         desc.append((pos, len(data), p, fo, delta))
         pos += len(data)
-    eng.submit_recordbatches(0, pos, desc)
+    n_host = eng.submit_recordbatches(0, pos, desc)
     n, nbytes, nbatches = eng.recordbatch_result(0)
+    assert n == n_host
     return eng, n, nbytes, nbatches
 
 
@@ -197,5 +198,5 @@ def test_large_and_tiny_batches_and_unaligned_blobs():
 def test_slot_too_small_is_reported():
     blob = rb.encode_batch(0, [b"x" * 100] * 50)
     from torchkafka_b200 import _native
-    with pytest.raises(_native.NativeError, match="more records than slot_records"):
+    with pytest.raises(_native.NativeError, match="more records in the slot than slot_records"):
         split_on_gpu([(0, blob, 0, 0)], slot_records=10)

@@ -55,11 +55,6 @@ class TkRbSummary(C.Structure):
                 ("status", C.c_uint32), ("reserved", C.c_uint32)]
 
 
-RB_STATUS_NAMES = {
-    1: "more record batches than slot_records",
-    2: "more records than slot_records",
-    3: "more value bytes than slot_bytes",
-}
 REC_FLAGS = 0x70000000
 
 STATUS_NAMES = {
@@ -107,7 +102,8 @@ _SIGNATURES = {
     "tk_process_slot": (C.c_int, [C.c_void_p, C.c_int, _p(TkJob), C.c_void_p]),
     "tk_compact_noalloc": (C.c_int, [C.c_void_p, C.c_uint32, C.c_uint32, C.c_uint32, C.c_void_p,
                                      C.c_void_p, C.c_void_p]),
-    "tk_slot_submit_recordbatches": (C.c_int, [C.c_void_p, C.c_int, C.c_uint64, _p(TkBlob), C.c_uint32]),
+    "tk_slot_submit_recordbatches": (C.c_int, [C.c_void_p, C.c_int, C.c_uint64, _p(TkBlob), C.c_uint32,
+                                             _p(C.c_uint32)]),
     "tk_slot_recordbatch_result": (C.c_int, [C.c_void_p, C.c_int, _p(TkRbSummary)]),
     "tk_slot_record": (C.c_int, [C.c_void_p, C.c_int, C.c_uint32, _p(TkRec)]),
     "tk_crc32c": (C.c_uint32, [C.c_void_p, C.c_uint64, C.c_uint32]),

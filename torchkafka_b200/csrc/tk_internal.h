@@ -67,7 +67,6 @@ struct tk_slot_dev {
                                // counters used alternately, each scan zeroes the one of the next
     // raw record-batch input (allocated on first tk_slot_submit_recordbatches)
     uint8_t*     raw;          // [slot_bytes + pad]
-    tk_blob_t*   blobs;        // [TK_MAX_BLOBS]
     tk_rb_batch* rb_batches;   // [slot_records]
     tk_rb_summary_t* rb_summary;
     uint4*       rb_temp;      // [slot_records] per-record copy descriptors
@@ -95,7 +94,7 @@ struct tk_slot {
     cudaEvent_t  ev_h2d;      // H2D landed
     cudaEvent_t  ev_free;     // kernels finished reading the device copy
     cudaEvent_t  ev_result;   // result block is in pinned memory
-    tk_blob_t*   h_blobs;     // pinned
+    tk_rb_batch* h_rb_batches;   // pinned, [slot_records]: written by the host's header walk
     tk_rb_summary_t* h_rb_summary;   // pinned
     cudaEvent_t  ev_dec0, ev_dec1;   // timing events around the decode / collate kernels (tk_ctx_set_timing)
     bool         dec_timed;

@@ -10,10 +10,9 @@
 // kafka-python is a dependency of the reference (setup.py:9, >= 2.0.2) and not part of its tree;
 // the format implemented here is the published one (Kafka protocol guide, "Record Batch", magic 2).
 //
-// Kernels (all on the slot's copy stream, behind the H2D of the raw bytes):
-//   k_rb_headers  one block: thread per partition blob walks the chain of batch headers (twice:
-//                 count, block scan, emit) -> batch descriptors in consumption order, each with
-//                 the index of its first record (sum of the headers' record counts)
+// Host (tk_slot_submit_recordbatches): follows the chain of batch headers of every blob -> batch
+// descriptors in consumption order, each with the index of its first record; returns the record
+// count of the slot.  Kernels (on the slot's copy stream, behind the H2D of the raw bytes):
 //   k_rb_check    warp per batch: CRC-32C of the batch (strided slicing-by-4, lanes own one 16-byte
 //                 chunk of every 512-byte row; lane states combined by carry-less multiplication),
 //                 then the record walk (bytes now in L1/L2): lane 0 follows the chain of record
@@ -87,10 +86,8 @@ __device__ __forceinline__ bool rb_varint(const uint8_t* raw, uint32_t& p, uint3
 
 struct rb_args {
     const uint8_t*   raw;
-    const tk_blob_t* blobs;
-    uint32_t         n_blobs;
     tk_rb_batch*     batches;
-    uint32_t         max_batches;
+    uint32_t         n_batches, n_records;    // from the host's header walk
     tk_rb_summary_t* summary;
     uint4*           temp;            // [slot_records] per-record copy descriptors (rb_temp)
     uint32_t*        bigq;            // records longer than RB_BIG, copied piecewise by k_rb_copy_big
@@ -100,38 +97,64 @@ struct rb_args {
     uint64_t         slot_bytes;
 };
 
-// ---------------------------------------------------------------- k_rb_headers
-// One step of the header chain of a blob.  A blob ends at its first incomplete batch (fetch
-// responses are cut at max_bytes); a header that cannot be trusted ends the blob with one
-// descriptor of status CORRUPT, because the next boundary cannot be found.  The three fields a
-// step needs (batchLength, magic, recordCount) are requested together: one memory round trip.
-struct rb_hdr {
-    uint32_t start, end, status, count;
-};
-__device__ __forceinline__ bool rb_next_header(const uint8_t* raw, uint32_t pos, uint32_t blob_end, rb_hdr& h) {
-    if (blob_end - pos < 12u) return false;
-    // (volatile asm: the compiler would otherwise sink each load below the branch that first needs
-    // it and turn one round trip into three; all addresses lie inside the padded buffer)
-    uint32_t hb[9];
-#pragma unroll
-    for (int k = 0; k < 9; ++k) {
-        const uint8_t* q = raw + pos + (k < 4 ? 8 + k : k == 4 ? 16 : 57 + (k - 5));
-        asm volatile("ld.global.u8 %0, [%1];" : "=r"(hb[k]) : "l"(q));
+// ---------------------------------------------------------------- batch headers (host)
+// The chain of batch headers of a blob is followed on the host, in tk_slot_submit_recordbatches:
+// it is one dependent read per batch (tens of kilobytes apart) of memory the host has just
+// written, a few dozen per blob -- a latency chain that would occupy one GPU thread per blob for
+// tens of microseconds, and whose result (the record count of the slot) the host needs before it
+// can size the output tensors.  Everything that is proportional to the bytes or to the records
+// (checksum, record framing, value gather) runs on the device.
+//
+// A blob ends at its first incomplete batch (fetch responses are cut at max_bytes); a header that
+// cannot be trusted ends the blob with one descriptor of status CORRUPT, because the next boundary
+// cannot be found.  The header's record count gives every batch its first record index in the
+// slot; a batch that fails later keeps its record slots (first one carries the error).
+static inline uint32_t rb_host_be32(const uint8_t* p) {
+    return ((uint32_t)p[0] << 24) | ((uint32_t)p[1] << 16) | ((uint32_t)p[2] << 8) | p[3];
+}
+static int rb_walk_host(const uint8_t* raw, const tk_blob_t* blobs, uint32_t n_blobs, tk_rb_batch* out,
+                        uint32_t max_batches, uint32_t max_records, uint32_t* n_batches_out, uint32_t* n_records_out) {
+    uint32_t nb = 0;
+    uint64_t nrec = 0;
+    for (uint32_t t = 0; t < n_blobs; ++t) {
+        const tk_blob_t& blob = blobs[t];
+        const uint32_t blob_end = blob.start + blob.length;
+        uint32_t pos = blob.start;
+        while (blob_end - pos >= 12u) {
+            const uint32_t blen = rb_host_be32(raw + pos + 8);
+            uint32_t end, status = TK_STATUS_OK, count = 1;
+            if ((int32_t)blen < (int32_t)(RB_HEADER - 12u)) {
+                end = blob_end; status = TK_STATUS_CORRUPT;
+            } else {
+                if (blen > blob_end - pos - 12u) break;                   // partial trailing batch
+                end = pos + 12u + blen;
+                const uint32_t magic = raw[pos + 16];
+                const uint32_t c = rb_host_be32(raw + pos + 57);
+                // a record is at least 7 bytes: a larger count cannot be true (the checksum would
+                // say so too, but the count sizes the slot before the checksum is looked at)
+                if (magic != 2) { status = TK_STATUS_CORRUPT; end = blob_end; }
+                else if (c > (end - pos - RB_HEADER) / 7u + 1u) status = TK_STATUS_CORRUPT;
+                else count = c;
+            }
+            TK_REQUIRE(nb < max_batches, "more record batches in the slot than slot_records (%u)", max_batches);
+            tk_rb_batch& b = out[nb++];
+            b.start = pos; b.end = end; b.partition = blob.partition; b.status = status;
+            int64_t base = 0;
+            if (!status) {
+                uint64_t u = ((uint64_t)rb_host_be32(raw + pos) << 32) | rb_host_be32(raw + pos + 4);
+                base = (int64_t)u + blob.offset_delta;
+            }
+            b.base_offset = base;
+            b.fetch_offset = blob.fetch_offset;
+            b.n_rec = count; b.value_bytes = 0; b.rec_base = (uint32_t)nrec; b.byte_base = 0;
+            nrec += count;
+            TK_REQUIRE(nrec <= max_records, "more records in the slot than slot_records (%u)", max_records);
+            pos = end;
+        }
     }
-    const uint32_t blen = (hb[0] << 24) | (hb[1] << 16) | (hb[2] << 8) | hb[3];
-    const uint32_t magic = hb[4];
-    const uint32_t count = (hb[5] << 24) | (hb[6] << 16) | (hb[7] << 8) | hb[8];
-    h.start = pos;
-    h.count = 1;
-    if ((int32_t)blen < (int32_t)(RB_HEADER - 12u)) { h.end = blob_end; h.status = TK_STATUS_CORRUPT; return true; }
-    if (blen > blob_end - pos - 12u) return false;                    // partial trailing batch
-    h.end = pos + 12u + blen;
-    // a record is at least 7 bytes: a larger count cannot be true (the checksum would say so too,
-    // but the count sizes the slot before the checksum is looked at)
-    h.status = (magic == 2 && count <= (h.end - pos - RB_HEADER) / 7u + 1u) ? TK_STATUS_OK : TK_STATUS_CORRUPT;
-    if (magic != 2) h.end = blob_end;
-    if (!h.status) h.count = count;
-    return true;
+    *n_batches_out = nb;
+    *n_records_out = (uint32_t)nrec;
+    return 0;
 }
 
 // exclusive scan of one packed (batches << 40 | records) value per thread of a 1024-thread block
@@ -159,49 +182,6 @@ __device__ __forceinline__ unsigned long long rb_block_scan(unsigned long long v
     }
     __syncthreads();
     return warp_tot[t >> 5] + incl - v;
-}
-
-// One block: thread per partition blob walks the chain of batch headers (count, block scan,
-// walk again and emit).  The record counts of the headers give every batch its first record
-// index in the slot, so the next kernel can write record headers while it validates.
-__global__ void __launch_bounds__(1024) k_rb_headers(const rb_args a) {
-    __shared__ unsigned long long warp_tot[32];
-    __shared__ unsigned long long s_total;
-    const uint32_t t = threadIdx.x;
-    unsigned long long mine = 0;
-    uint32_t blob_start = 0, blob_end = 0;
-    if (t < a.n_blobs) {
-        blob_start = a.blobs[t].start;
-        blob_end = blob_start + a.blobs[t].length;
-        rb_hdr h;
-        for (uint32_t pos = blob_start; rb_next_header(a.raw, pos, blob_end, h); pos = h.end)
-            mine += (1ull << 40) + h.count;
-    }
-    const unsigned long long excl = rb_block_scan(mine, warp_tot, &s_total);
-    const unsigned long long n_batches = s_total >> 40, n_records = s_total & 0xFFFFFFFFFFull;
-    uint32_t status = TK_RB_OK;
-    if (n_batches > a.max_batches) status = TK_RB_TOO_MANY_BATCHES;
-    else if (n_records > a.slot_records) status = TK_RB_TOO_MANY_RECORDS;
-    if (t == 0) {
-        a.summary->n_batches = status ? 0u : (uint32_t)n_batches;
-        a.summary->n_records = (uint32_t)min(n_records, 0xFFFFFFFFull);
-        a.summary->n_bytes = 0;
-        a.summary->status = status;
-        a.summary->reserved = 0;                          // length of the big-record queue
-    }
-    if (status || t >= a.n_blobs) return;
-    const tk_blob_t blob = a.blobs[t];
-    uint32_t idx = (uint32_t)(excl >> 40), rec = (uint32_t)(excl & 0xFFFFFFFFFFull);
-    rb_hdr h;
-    for (uint32_t pos = blob_start; rb_next_header(a.raw, pos, blob_end, h); pos = h.end, ++idx) {
-        tk_rb_batch b;
-        b.start = h.start; b.end = h.end; b.partition = blob.partition; b.status = h.status;
-        b.base_offset = h.status ? 0 : (int64_t)rb_be64(a.raw + h.start) + blob.offset_delta;
-        b.fetch_offset = blob.fetch_offset;
-        b.n_rec = h.count; b.value_bytes = 0; b.rec_base = rec; b.byte_base = 0;
-        a.batches[idx] = b;
-        rec += h.count;
-    }
 }
 
 // ---------------------------------------------------------------- CRC-32C on the device
@@ -355,7 +335,7 @@ __global__ void __launch_bounds__(256) k_rb_check(const rb_args a) {
     rb_tables_init(tb);
     const uint32_t lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
     const uint32_t warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, nwarps = (gridDim.x * blockDim.x) >> 5;
-    const uint32_t n_batches = a.summary->n_batches;
+    const uint32_t n_batches = a.n_batches;
     rb_temp* temp = reinterpret_cast<rb_temp*>(a.temp);
     for (uint32_t i = warp; i < n_batches; i += nwarps) {
         const tk_rb_batch b = a.batches[i];
@@ -452,7 +432,7 @@ __global__ void __launch_bounds__(1024) k_rb_prefix(const rb_args a) {
     __shared__ unsigned long long warp_tot[32];
     __shared__ unsigned long long s_total, s_run;
     const uint32_t t = threadIdx.x;
-    const uint32_t n_batches = a.summary->n_batches;
+    const uint32_t n_batches = a.n_batches;
     if (t == 0) s_run = 0;
     __syncthreads();
     for (uint32_t base = 0; base < n_batches; base += blockDim.x) {
@@ -464,10 +444,14 @@ __global__ void __launch_bounds__(1024) k_rb_prefix(const rb_args a) {
         if (t == 0) s_run += s_total;
         __syncthreads();
     }
-    if (t == 0 && a.summary->status == TK_RB_OK) {
+    if (t == 0) {
+        // (the values are a subset of the raw bytes, which fit the slot: no capacity check needed)
+        a.summary->n_records = a.n_records;
+        a.summary->n_batches = n_batches;
         a.summary->n_bytes = s_run;
-        if (s_run > a.slot_bytes) a.summary->status = TK_RB_TOO_MANY_BYTES;
-        else a.recs[a.summary->n_records].start = (uint32_t)s_run;      // closes the CSR
+        a.summary->status = TK_RB_OK;
+        a.summary->reserved = 0;                              // length of the big-record queue
+        a.recs[a.n_records].start = (uint32_t)s_run;          // closes the CSR
     }
 }
 
@@ -493,10 +477,9 @@ __device__ __forceinline__ void rb_warp_copy(uint8_t* dst, const uint8_t* src, u
 #define RB_BIG 16384u
 #define RB_PIECE 4096u
 __global__ void __launch_bounds__(256) k_rb_copy(const rb_args a) {
-    if (a.summary->status != TK_RB_OK) return;
     const uint32_t lane = threadIdx.x & 31;
     const uint32_t warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, nwarps = (gridDim.x * blockDim.x) >> 5;
-    const uint32_t n = a.summary->n_records;
+    const uint32_t n = a.n_records;
     const uint4* temp = reinterpret_cast<const uint4*>(a.temp);
     for (uint32_t i = warp; i < n; i += nwarps) {
         const uint4 t = __ldg(temp + i);                      // {src, len, rel, batch}
@@ -510,7 +493,6 @@ __global__ void __launch_bounds__(256) k_rb_copy(const rb_args a) {
 }
 
 __global__ void __launch_bounds__(256) k_rb_copy_big(const rb_args a) {
-    if (a.summary->status != TK_RB_OK) return;
     const uint32_t count = a.summary->reserved;
     if (!count) return;
     const uint32_t lane = threadIdx.x & 31;
@@ -547,19 +529,18 @@ static int rb_ensure(tk_ctx* ctx) {
         if (s.d.raw) continue;
         TK_CUDA(cudaMalloc(&s.d.raw, ctx->slot_bytes + TK_BYTES_PAD));
         TK_CUDA(cudaMemset(s.d.raw, 0, ctx->slot_bytes + TK_BYTES_PAD));
-        TK_CUDA(cudaMalloc(&s.d.blobs, sizeof(tk_blob_t) * TK_MAX_BLOBS));
         TK_CUDA(cudaMalloc(&s.d.rb_batches, sizeof(tk_rb_batch) * (size_t)ctx->slot_records));
         TK_CUDA(cudaMalloc(&s.d.rb_summary, sizeof(tk_rb_summary_t)));
         TK_CUDA(cudaMalloc(&s.d.rb_temp, sizeof(uint4) * (size_t)ctx->slot_records));
         TK_CUDA(cudaMalloc(&s.d.rb_bigq, sizeof(uint32_t) * ((size_t)(ctx->slot_bytes / RB_BIG) + 2)));
-        TK_CUDA(cudaHostAlloc(&s.h_blobs, sizeof(tk_blob_t) * TK_MAX_BLOBS, cudaHostAllocDefault));
+        TK_CUDA(cudaHostAlloc(&s.h_rb_batches, sizeof(tk_rb_batch) * (size_t)ctx->slot_records, cudaHostAllocDefault));
         TK_CUDA(cudaHostAlloc(&s.h_rb_summary, sizeof(tk_rb_summary_t), cudaHostAllocDefault));
     }
     return 0;
 }
 
 extern "C" int tk_slot_submit_recordbatches(tk_ctx* ctx, int slot, uint64_t n_bytes, const tk_blob_t* blobs,
-                                            uint32_t n_blobs) {
+                                            uint32_t n_blobs, uint32_t* n_records) {
     TK_ENTER(ctx, slot);
     TK_REQUIRE(n_bytes <= ctx->slot_bytes, "n_bytes %llu exceeds slot_bytes %llu", (unsigned long long)n_bytes,
                (unsigned long long)ctx->slot_bytes);
@@ -571,18 +552,20 @@ extern "C" int tk_slot_submit_recordbatches(tk_ctx* ctx, int slot, uint64_t n_by
     int rc = rb_ensure(ctx); if (rc) return rc;
     tk_slot& s = ctx->slots[slot];
     cudaStream_t st = ctx->copy_stream;
-    // until the result is read the slot's geometry is unknown: an upper bound keeps checks sane
-    s.n_records = 0;
-    s.n_bytes = 0;
-    if (n_blobs) memcpy(s.h_blobs, blobs, sizeof(tk_blob_t) * n_blobs);
+    uint32_t n_batches = 0, n_rec = 0;
+    rc = rb_walk_host(s.h_bytes, blobs, n_blobs, s.h_rb_batches, ctx->slot_records, ctx->slot_records, &n_batches, &n_rec);
+    if (rc) return rc;
+    s.n_records = n_rec;
+    s.n_bytes = n_bytes;                     // upper bound of the value bytes (sizes grids only)
+    if (n_records) *n_records = n_rec;
     if (s.free_recorded) TK_CUDA(cudaStreamWaitEvent(st, s.ev_free, 0));
     if (n_bytes) TK_CUDA(cudaMemcpyAsync(s.d.raw, s.h_bytes, n_bytes, cudaMemcpyHostToDevice, st));
-    if (n_blobs) TK_CUDA(cudaMemcpyAsync(s.d.blobs, s.h_blobs, sizeof(tk_blob_t) * n_blobs, cudaMemcpyHostToDevice, st));
+    if (n_batches)
+        TK_CUDA(cudaMemcpyAsync(s.d.rb_batches, s.h_rb_batches, sizeof(tk_rb_batch) * n_batches, cudaMemcpyHostToDevice, st));
     rb_args a;
-    a.raw = s.d.raw; a.blobs = s.d.blobs; a.n_blobs = n_blobs; a.batches = s.d.rb_batches;
-    a.max_batches = ctx->slot_records; a.summary = s.d.rb_summary; a.temp = s.d.rb_temp; a.bigq = s.d.rb_bigq; a.bytes = s.d.bytes; a.recs = s.d.recs;
+    a.raw = s.d.raw; a.batches = s.d.rb_batches; a.n_batches = n_batches; a.n_records = n_rec;
+    a.summary = s.d.rb_summary; a.temp = s.d.rb_temp; a.bigq = s.d.rb_bigq; a.bytes = s.d.bytes; a.recs = s.d.recs;
     a.slot_records = ctx->slot_records; a.slot_bytes = ctx->slot_bytes;
-    k_rb_headers<<<1, 1024, 0, st>>>(a);
     k_rb_check<<<148 * 4, 256, 0, st>>>(a);
     k_rb_prefix<<<1, 1024, 0, st>>>(a);
     k_rb_copy<<<148 * 8, 256, 0, st>>>(a);
@@ -598,12 +581,7 @@ extern "C" int tk_slot_recordbatch_result(tk_ctx* ctx, int slot, tk_rb_summary_t
     tk_slot& s = ctx->slots[slot];
     TK_REQUIRE(s.h_rb_summary, "no record batches were submitted on this context");
     TK_CUDA(cudaEventSynchronize(s.ev_h2d));
-    const tk_rb_summary_t r = *s.h_rb_summary;
-    if (summary) *summary = r;
-    if (r.status == TK_RB_OK) {
-        s.n_records = r.n_records;
-        s.n_bytes = r.n_bytes;
-    }
+    if (summary) *summary = *s.h_rb_summary;
     return 0;
 }
 

@@ -416,22 +416,23 @@ class SlotEngine:
             partition=part, offset=off, status=code)
 
     # ------------------------------------------------------------------ record batches
-    def submit_recordbatches(self, slot: int, n_bytes: int, blobs) -> None:
+    def submit_recordbatches(self, slot: int, n_bytes: int, blobs) -> int:
         """Raw RecordBatch v2 bytes are in the slot's pinned buffer ``[0, n_bytes)``; ``blobs`` is a
-        sequence of (start, length, dense partition, fetch_offset, offset_delta).  Asynchronous."""
+        sequence of (start, length, dense partition, fetch_offset, offset_delta).  Returns the
+        number of record entries of the slot (known from the batch headers); the copy to the
+        device and the split kernels are asynchronous."""
         arr = (_native.TkBlob * max(len(blobs), 1))()
         for k, (start, length, part, fetch_offset, delta) in enumerate(blobs):
             b = arr[k]
             b.start, b.length, b.partition = int(start), int(length), int(part)
             b.fetch_offset, b.offset_delta = int(fetch_offset), int(delta)
-        _native.check(self.lib.tk_slot_submit_recordbatches(self.ctx, slot, C.c_uint64(int(n_bytes)), arr, len(blobs)))
+        n = C.c_uint32()
+        _native.check(self.lib.tk_slot_submit_recordbatches(self.ctx, slot, C.c_uint64(int(n_bytes)), arr,
+                                                            len(blobs), C.byref(n)))
+        return int(n.value)
 
     def recordbatch_result(self, slot: int):
         """Wait for the split of ``slot``; returns (n_records, n_value_bytes, n_batches)."""
         r = _native.TkRbSummary()
         _native.check(self.lib.tk_slot_recordbatch_result(self.ctx, slot, C.byref(r)))
-        if r.status:
-            raise _native.NativeError(
-                f"record batches do not fit the slot: {_native.RB_STATUS_NAMES.get(int(r.status), int(r.status))} "
-                f"(slot_records={self.slot_records}, slot_bytes={self.slot_bytes})")
         return int(r.n_records), int(r.n_bytes), int(r.n_batches)

@@ -232,7 +232,8 @@ class IngestPipeline:
         return len(fetch.blobs), nbytes, fetch
 
     def _pack_raw(self, slot: int, scratch, n_blobs: int, fetch):
-        """Blobs -> pinned buffer (multi-threaded gather), H2D + split kernels, wait for the counts."""
+        """Blobs -> pinned buffer (multi-threaded gather); the batch headers give the record count;
+        H2D and the split kernels are queued.  Returns (record entries, raw bytes)."""
         eng = self.engine
         t0 = time.perf_counter()
         k = len(fetch.blobs)
@@ -243,19 +244,11 @@ class IngestPipeline:
         eng.pack_pointers(slot, ptrs, lens, parts, fetch_offsets, k)      # bytes back to back
         starts = np.zeros(k + 1, dtype=np.int64)
         np.cumsum(lens, out=starts[1:])
-        eng.submit_recordbatches(slot, int(starts[k]),
-                                 [(int(starts[i]), int(lens[i]), int(parts[i]), int(fetch_offsets[i]),
-                                   int(fetch.blobs[i][3])) for i in range(k)])
+        n = eng.submit_recordbatches(slot, int(starts[k]),
+                                     [(int(starts[i]), int(lens[i]), int(parts[i]), int(fetch_offsets[i]),
+                                       int(fetch.blobs[i][3])) for i in range(k)])
         self.stats["t_pack"] += time.perf_counter() - t0
-        # the record count is known once the device has split the batches; the consuming thread
-        # asks for it right before it launches the slot's kernels (_split_result)
-        return None, int(starts[k])
-
-    def _split_result(self, slot: int):
-        t0 = time.perf_counter()
-        n, nbytes, _ = self.engine.recordbatch_result(slot)
-        self.stats["t_split_wait"] = self.stats.get("t_split_wait", 0.0) + time.perf_counter() - t0
-        return n, nbytes
+        return n, int(starts[k])
 
     def _indices(self, rec):
         """(value index, offset index) for tuple-like records, (-1, -1) for attribute access."""
@@ -520,9 +513,6 @@ class IngestPipeline:
         for slot, n, nbytes, parts, offs in slots:
             t0 = time.perf_counter()
             self.stats["t_wait_slot"] += t0 - t_get
-            if n is None:                          # record batches: split on the device
-                n, nbytes = self._split_result(slot)
-                t0 = time.perf_counter()
             out = eng.process(slot, n, prev_slot, prev_out)
             self.stats["t_launch"] += time.perf_counter() - t0
             pending.append(_Pending(slot, n, out, parts, offs))

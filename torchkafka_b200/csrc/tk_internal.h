@@ -94,6 +94,7 @@ struct tk_slot {
     cudaEvent_t  ev_h2d;      // H2D landed
     cudaEvent_t  ev_free;     // kernels finished reading the device copy
     cudaEvent_t  ev_result;   // result block is in pinned memory
+    cudaEvent_t  ev_raw;      // raw record-batch bytes landed (created with the raw buffers)
     tk_rb_batch* h_rb_batches;   // pinned, [slot_records]: written by the host's header walk
     tk_rb_summary_t* h_rb_summary;   // pinned
     cudaEvent_t  ev_dec0, ev_dec1;   // timing events around the decode / collate kernels (tk_ctx_set_timing)
@@ -115,6 +116,7 @@ struct tk_ctx {
     size_t    tok_cap;         // entries of the token array (a token needs >= 2 bytes)
     uint32_t  batch_size;      // of the last tk_compact
     cudaStream_t copy_stream;
+    cudaStream_t split_stream;   // record-batch split kernels (created on first use): the next slot's H2D overlaps them
     tk_state* d_state;
     int64_t*  d_positions;     // [n_partitions] running max(offset)+1, -1 = never seen
     uint16_t* d_image_lut;     // [4][256] bf16 bit patterns

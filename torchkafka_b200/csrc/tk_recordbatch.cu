@@ -524,6 +524,7 @@ __global__ void __launch_bounds__(256) k_rb_copy_big(const rb_args a) {
 static std::mutex g_rb_mutex;
 static int rb_ensure(tk_ctx* ctx) {
     std::lock_guard<std::mutex> lock(g_rb_mutex);
+    if (!ctx->split_stream) TK_CUDA(cudaStreamCreateWithFlags(&ctx->split_stream, cudaStreamNonBlocking));
     for (int i = 0; i < ctx->n_slots; ++i) {
         tk_slot& s = ctx->slots[i];
         if (s.d.raw) continue;
@@ -535,6 +536,7 @@ static int rb_ensure(tk_ctx* ctx) {
         TK_CUDA(cudaMalloc(&s.d.rb_bigq, sizeof(uint32_t) * ((size_t)(ctx->slot_bytes / RB_BIG) + 2)));
         TK_CUDA(cudaHostAlloc(&s.h_rb_batches, sizeof(tk_rb_batch) * (size_t)ctx->slot_records, cudaHostAllocDefault));
         TK_CUDA(cudaHostAlloc(&s.h_rb_summary, sizeof(tk_rb_summary_t), cudaHostAllocDefault));
+        TK_CUDA(cudaEventCreateWithFlags(&s.ev_raw, cudaEventDisableTiming));
     }
     return 0;
 }
@@ -558,20 +560,29 @@ extern "C" int tk_slot_submit_recordbatches(tk_ctx* ctx, int slot, uint64_t n_by
     s.n_records = n_rec;
     s.n_bytes = n_bytes;                     // upper bound of the value bytes (sizes grids only)
     if (n_records) *n_records = n_rec;
-    if (s.free_recorded) TK_CUDA(cudaStreamWaitEvent(st, s.ev_free, 0));
+    // copies on the copy stream, kernels on the split stream: the H2D of the next slot runs while
+    // this one is split
+    cudaStream_t ks = ctx->split_stream;
+    if (s.free_recorded) {
+        TK_CUDA(cudaStreamWaitEvent(st, s.ev_free, 0));
+        TK_CUDA(cudaStreamWaitEvent(ks, s.ev_free, 0));
+    }
     if (n_bytes) TK_CUDA(cudaMemcpyAsync(s.d.raw, s.h_bytes, n_bytes, cudaMemcpyHostToDevice, st));
     if (n_batches)
         TK_CUDA(cudaMemcpyAsync(s.d.rb_batches, s.h_rb_batches, sizeof(tk_rb_batch) * n_batches, cudaMemcpyHostToDevice, st));
+    TK_CUDA(cudaEventRecord(s.ev_raw, st));
+    TK_CUDA(cudaStreamWaitEvent(ks, s.ev_raw, 0));
     rb_args a;
     a.raw = s.d.raw; a.batches = s.d.rb_batches; a.n_batches = n_batches; a.n_records = n_rec;
     a.summary = s.d.rb_summary; a.temp = s.d.rb_temp; a.bigq = s.d.rb_bigq; a.bytes = s.d.bytes; a.recs = s.d.recs;
     a.slot_records = ctx->slot_records; a.slot_bytes = ctx->slot_bytes;
-    k_rb_check<<<148 * 4, 256, 0, st>>>(a);
-    k_rb_prefix<<<1, 1024, 0, st>>>(a);
-    k_rb_copy<<<148 * 8, 256, 0, st>>>(a);
-    k_rb_copy_big<<<148 * 8, 256, 0, st>>>(a);
+    k_rb_check<<<148 * 4, 256, 0, ks>>>(a);
+    k_rb_prefix<<<1, 1024, 0, ks>>>(a);
+    k_rb_copy<<<148 * 8, 256, 0, ks>>>(a);
+    k_rb_copy_big<<<148 * 8, 256, 0, ks>>>(a);
     TK_LAUNCH_CHECK();
-    TK_CUDA(cudaMemcpyAsync(s.h_rb_summary, s.d.rb_summary, sizeof(tk_rb_summary_t), cudaMemcpyDeviceToHost, st));
+    TK_CUDA(cudaMemcpyAsync(s.h_rb_summary, s.d.rb_summary, sizeof(tk_rb_summary_t), cudaMemcpyDeviceToHost, ks));
+    st = ks;
     TK_CUDA(cudaEventRecord(s.ev_h2d, st));
     return 0;
 }

@@ -116,6 +116,7 @@ class IngestPipeline:
         self.input_mode = input_mode
         self._packed = input_mode == "packed"
         self._leftover = []                        # (tp, records) polled but not fitting the last slot
+        self._mean_len = 0.0                       # running mean of the value size (poll sizing)
         self._field_idx = {}                       # record type -> (value index, offset index)
         self.n_producers = max(1, int(n_producers))
         self._threads = []
@@ -281,9 +282,14 @@ class IngestPipeline:
                 items, self._leftover = self._leftover, []
             else:
                 t0 = time.perf_counter()
+                # ask for about as many records as still fit (mean value size seen so far): records
+                # polled beyond the slot's byte budget would be harvested twice
+                want = eng.slot_records - n
+                if self._mean_len:
+                    want = min(want, int((eng.slot_bytes - nbytes) / self._mean_len * 1.02) + 16)
                 with self.consumer_lock:
                     polled = self.consumer.poll(timeout_ms=self.poll_timeout_ms,
-                                                max_records=min(eng.slot_records - n, 1 << 16))
+                                                max_records=max(1, min(want, 1 << 16)))
                 self.stats["t_poll"] += time.perf_counter() - t0
                 if not polled:
                     # a partly filled slot is shipped as soon as the stream pauses (bounded
@@ -312,6 +318,9 @@ class IngestPipeline:
                 hold.append(keep)
             n += taken
             nbytes += tot
+            if taken:
+                m = tot / taken
+                self._mean_len = m if not self._mean_len else 0.75 * self._mean_len + 0.25 * m
             if g_done < len(items):
                 # the slot is full inside group g_done: records cannot be un-polled, so the
                 # rest waits, in consumption order, for the next slot

@@ -13,7 +13,10 @@ Semantics restated from kafka-python's fetcher:
   * a batch that is not completely inside the blob (fetch responses end mid-batch) is ignored;
   * records whose offset is below the fetch position are skipped (batches are returned whole);
   * CRC mismatch, magic != 2, malformed varints raise CorruptRecordError;
-  * compressed batches are outside this restatement (SURVEY §8f-2) and raise UnsupportedBatch;
+  * LZ4-compressed batches (codec 3) are decompressed with the restatement of the LZ4 frame and
+    block formats below (lz4_Frame_format.md / lz4_Block_format.md of the LZ4 project; xxHash
+    checksums are skipped, the batch CRC covers the same bytes); the other codecs (gzip, snappy,
+    zstd: SURVEY §8f-2) raise UnsupportedBatch;
   * control batches (attributes bit 5) carry no user records and are skipped.
 Pure Python, byte at a time: for small cases.
 """
@@ -68,6 +71,83 @@ def read_varint(buf: bytes, pos: int, end: int) -> Tuple[int, int]:
     return (raw >> 1) ^ -(raw & 1), pos
 
 
+def lz4_block_decode(src: bytes, out: bytearray, window_start: int) -> None:
+    """Append the decoded LZ4 block `src` to `out`; matches may reach back to out[window_start:]."""
+    ip, n = 0, len(src)
+    while ip < n:
+        token = src[ip]
+        ip += 1
+        lit = token >> 4
+        if lit == 15:
+            while True:
+                if ip >= n:
+                    raise CorruptRecordError("lz4: literal length runs past the block")
+                b = src[ip]
+                ip += 1
+                lit += b
+                if b != 255:
+                    break
+        if ip + lit > n:
+            raise CorruptRecordError("lz4: literals run past the block")
+        out += src[ip:ip + lit]
+        ip += lit
+        if ip >= n:
+            break                                    # the last sequence has no match
+        if ip + 2 > n:
+            raise CorruptRecordError("lz4: truncated offset")
+        offset = src[ip] | (src[ip + 1] << 8)
+        ip += 2
+        if offset == 0 or offset > len(out) - window_start:
+            raise CorruptRecordError("lz4: offset outside the window")
+        mlen = token & 15
+        if mlen == 15:
+            while True:
+                if ip >= n:
+                    raise CorruptRecordError("lz4: match length runs past the block")
+                b = src[ip]
+                ip += 1
+                mlen += b
+                if b != 255:
+                    break
+        mlen += 4
+        start = len(out) - offset
+        for i in range(mlen):                        # byte by byte: the match may overlap its output
+            out.append(out[start + i])
+
+
+def lz4_frame_decode(src: bytes) -> bytes:
+    """One LZ4 frame (what Kafka writes per compressed batch) -> the bytes it holds."""
+    if len(src) < 7 or src[:4] != b"\x04\x22\x4d\x18":
+        raise CorruptRecordError("lz4: bad frame magic")
+    flg, _bd = src[4], src[5]
+    if flg >> 6 != 1:
+        raise CorruptRecordError("lz4: unknown frame version")
+    if flg & 1:
+        raise UnsupportedBatch("lz4: dictionary frames")
+    independent, block_checksum = bool(flg & 0x20), bool(flg & 0x10)
+    pos = 6 + (8 if flg & 0x08 else 0) + 1            # content size, header checksum
+    out = bytearray()
+    while True:
+        if pos + 4 > len(src):
+            raise CorruptRecordError("lz4: truncated frame")
+        (size,) = struct.unpack_from("<I", src, pos)
+        pos += 4
+        if size == 0:
+            break
+        raw_block, size = bool(size >> 31), size & 0x7FFFFFFF
+        if pos + size > len(src):
+            raise CorruptRecordError("lz4: block runs past the frame")
+        if raw_block:
+            out += src[pos:pos + size]
+        else:
+            lz4_block_decode(src[pos:pos + size], out, len(out) if independent else 0)
+        pos += size + (4 if block_checksum else 0)
+    pos += 4 if flg & 0x04 else 0                     # content checksum
+    if pos != len(src):
+        raise CorruptRecordError("lz4: bytes behind the frame")
+    return bytes(out)
+
+
 class Record(NamedTuple):
     partition: int
     offset: int
@@ -94,32 +174,37 @@ def split_blob(blob: bytes, partition: int, fetch_offset: int = 0, offset_delta:
             raise CorruptRecordError(f"CRC mismatch in the batch at byte {pos}")
         (attributes,) = struct.unpack_from(">h", blob, pos + 21)
         (count,) = struct.unpack_from(">i", blob, pos + 57)
-        if attributes & 0x07:
-            raise UnsupportedBatch(f"compression codec {attributes & 7}")
+        codec = attributes & 0x07
+        if codec == 3:
+            body = lz4_frame_decode(bytes(blob[pos + HEADER_BYTES:end]))
+        elif codec:
+            raise UnsupportedBatch(f"compression codec {codec}")
+        else:
+            body = blob[pos + HEADER_BYTES:end]
         control = bool(attributes & 0x20)
-        p = pos + HEADER_BYTES
+        p, body_end = 0, len(body)
         if count < 0:
             raise CorruptRecordError("negative record count")
         for _ in range(count):
-            length, p = read_varint(blob, p, end)
-            if length < 0 or p + length > end:
+            length, p = read_varint(body, p, body_end)
+            if length < 0 or p + length > body_end:
                 raise CorruptRecordError("record length outside the batch")
             rec_end = p + length
             q = p + 1                                # attributes (int8)
-            _ts, q = read_varint(blob, q, rec_end)
-            od, q = read_varint(blob, q, rec_end)
-            klen, q = read_varint(blob, q, rec_end)
+            _ts, q = read_varint(body, q, rec_end)
+            od, q = read_varint(body, q, rec_end)
+            klen, q = read_varint(body, q, rec_end)
             if klen > 0:
                 q += klen
-            vlen, q = read_varint(blob, q, rec_end)
+            vlen, q = read_varint(body, q, rec_end)
             if q > rec_end or (vlen > 0 and q + vlen > rec_end):
                 raise CorruptRecordError("record fields outside the record")
-            value = None if vlen < 0 else bytes(blob[q:q + vlen])
+            value = None if vlen < 0 else bytes(body[q:q + vlen])
             offset = base_offset + od + offset_delta
             if not control and offset >= fetch_offset:
                 out.append(Record(partition, offset, value))
             p = rec_end
-        if p != end:
+        if p != body_end:
             raise CorruptRecordError("records do not fill the batch")
         pos = end
     return out

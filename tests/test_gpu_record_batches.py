@@ -19,9 +19,9 @@ from torchkafka_b200.testing.stub_kafka import RecordLog
 pytestmark = pytest.mark.gpu
 
 
-def check_raw(log, schema, batch_size, batch_bytes=16384, **kw):
+def check_raw(log, schema, batch_size, batch_bytes=16384, codec=0, **kw):
     gpu = run_gpu(log, schema, batch_size, device_input="raw",
-                  consumer_kwargs={"raw_batch_bytes": batch_bytes}, **kw)
+                  consumer_kwargs={"raw_batch_bytes": batch_bytes, "raw_codec": codec}, **kw)
     cpu = run_oracle(log, schema, batch_size)
     assert_same(gpu, cpu, schema)
     return gpu
@@ -162,7 +162,7 @@ def test_broken_batches_raise_at_their_batch(damage, status):
     elif damage == "magic":
         bad[16] = 1
     elif damage == "codec":
-        bad = bytearray(rb.encode_batch(4, jvals(4, 8), attributes=3))
+        bad = bytearray(rb.encode_batch(4, jvals(4, 8), attributes=2))        # snappy: not built
     elif damage == "null":
         bad = bytearray(rb.encode_batch(4, [jvals(4, 5)[0], None, jvals(6, 7)[0]]))
     elif damage == "varint":                                  # framing broken, CRC recomputed to match
@@ -200,3 +200,49 @@ def test_slot_too_small_is_reported():
     from torchkafka_b200 import _native
     with pytest.raises(_native.NativeError, match="more records in the slot than slot_records"):
         split_on_gpu([(0, blob, 0, 0)], slot_records=10)
+
+
+# ---------------------------------------------------------------- LZ4-compressed batches (§8f-2)
+@pytest.mark.parametrize("cfg,n,batch_bytes", [(2, 3000, 16384), (2, 3000, 200000), (3, 600, 65536), (5, 20000, 16384)])
+def test_lz4_batches_match_the_oracle(cfg, n, batch_bytes):
+    """cfg2/cfg3: text (matches, several 64 KiB blocks per frame with batch_bytes 200000: dependent
+    blocks); cfg5: random bytes (stored blocks, tiny matches)."""
+    log = syn.make_log(cfg, n, seed=31 + cfg, partitions=8, layout="chunked", chunk=100)
+    schema = {2: JsonArray(torch.float32, max_len=256, min_size=32), 3: TokenList(torch.int32, max_len=2048),
+              5: RawBytes((64,), torch.uint8)}[cfg]
+    check_raw(log, schema, 128, batch_bytes=batch_bytes, codec=3)
+
+
+def test_lz4_mixed_with_plain_batches_and_long_overlapping_matches():
+    vals_a = [json.dumps([1.5] * 200).encode() for _ in range(40)]          # one long period-5 match
+    vals_b = jvals(0, 50)
+    wide = [json.dumps([float(i % 7)] * 120).encode() for i in range(300)]   # > 64 KiB: window wrap
+    blob = (rb.encode_batch(0, vals_a, codec=3) + rb.encode_batch(40, vals_b) + rb.encode_batch(90, wide, codec=3))
+    out, commits = run_blobs([(4, blob, 0, 0)], JsonArray(torch.float32, max_len=256), 64)
+    want = [json.loads(v) for v in vals_a + vals_b + wide]
+    got = []
+    for b in out:
+        vals, lens = b.values.cpu(), b.lengths.cpu()
+        got += [vals[i, :int(lens[i])].tolist() for i in range(len(lens))]
+    assert got == want and commits[-1] == {4: 390}
+
+
+@pytest.mark.parametrize("damage", ["magic", "offset", "truncated", "size"])
+def test_broken_lz4_frames_raise_at_their_batch(damage):
+    good = rb.encode_batch(0, jvals(0, 4), codec=3)
+    bad = bytearray(rb.encode_batch(4, [json.dumps([0.5] * 60).encode()] * 4, codec=3))
+    if damage == "magic":
+        bad[61] ^= 0xFF
+    elif damage == "offset":                         # first match reaches before the start of the output
+        k = 61 + 7 + 4                               # frame header, block size -> first token
+        lit = bad[k] >> 4
+        assert lit < 15
+        bad[k + 1 + lit:k + 3 + lit] = (60000).to_bytes(2, "little")
+    elif damage == "truncated":
+        bad[61 + 7:61 + 11] = (len(bad)).to_bytes(4, "little")      # block longer than the batch
+    elif damage == "size":
+        bad[-4:] = b"\x01\x00\x00\x00"                              # garbage instead of the end mark
+    bad[17:21] = rb.crc32c(bytes(bad[21:])).to_bytes(4, "big")
+    with pytest.raises(PayloadError) as ei:
+        run_blobs([(1, good + bytes(bad), 0, 0)], JsonArray(torch.float32, max_len=64), 2)
+    assert ei.value.status == 7 and ei.value.partition == 1 and ei.value.offset == 4

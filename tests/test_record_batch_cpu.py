@@ -137,3 +137,49 @@ def test_poll_raw_after_partial_consumption_returns_the_batch_whole():
     recs = orb.split_blob(bytes(data), p, fetch_offset, delta)
     assert [r.offset for r in recs] == list(range(25, 60))
     assert len(orb.split_blob(bytes(data), p, 0, delta)) == 60
+
+
+# ---------------------------------------------------------------- LZ4 (codec 3)
+def test_lz4_oracle_decodes_frames_of_an_independent_compressor():
+    """The oracle's LZ4 frame/block restatement against frames written by pyarrow's liblz4:
+    incompressible data (stored blocks), long overlapping matches, text, several blocks."""
+    import os
+    rng = random.Random(6)
+    cases = [b"", b"a", os.urandom(200_000), b"abc" * 70_000, b"\x00" * 300_000,
+             json_like(rng, 150_000), os.urandom(10) * 9_000 + os.urandom(5_000)]
+    for data in cases:
+        assert orb.lz4_frame_decode(rb.lz4_frame(data)) == data
+
+
+def json_like(rng, n):
+    import json
+    out = json.dumps([rng.randrange(128000) for _ in range(n // 6)]).encode()
+    return out[:n]
+
+
+def test_lz4_errors():
+    z = bytearray(rb.lz4_frame(b"hello world, hello world, hello world" * 20))
+    with pytest.raises(orb.CorruptRecordError):
+        orb.lz4_frame_decode(bytes(z[:-1]))
+    bad = bytearray(z)
+    bad[0] ^= 1
+    with pytest.raises(orb.CorruptRecordError):
+        orb.lz4_frame_decode(bytes(bad))
+    with pytest.raises(orb.CorruptRecordError):                  # offset beyond the start of the output
+        orb.lz4_frame_decode(b"\x04\x22\x4d\x18\x60\x40\x82" + (7).to_bytes(4, "little") + b"\x10a\x05\x00\x50bc" + bytes(4))
+
+
+def test_lz4_batches_roundtrip_through_the_oracle():
+    log = syn.make_log(3, 120, seed=8, partitions=3, layout="chunked", chunk=20)
+    c = sk.KafkaConsumer("topic", log=log, raw_batch_bytes=30000, raw_codec=3)
+    got = []
+    while True:
+        f = c.poll_raw(1 << 22, 1000)
+        if f is None:
+            break
+        for p, data, fetch_offset, delta in f.blobs:
+            assert bytes(data[21:23]) == b"\x00\x03"            # attributes: LZ4
+            got += orb.split_blob(bytes(data), p, fetch_offset, delta)
+    want = list(sk.KafkaConsumer("topic", log=log))
+    assert [(r.partition, r.offset, r.value) for r in got] == [(r.partition, r.offset, r.value) for r in want]
+    assert log.encoded(30000, 3).nbytes < 0.9 * log.encoded(30000).nbytes

@@ -44,6 +44,10 @@ struct tk_rb_batch {
     uint32_t value_bytes;      // bytes the batch contributes to the slot
     uint32_t rec_base;         // first record / first value byte of the batch in the slot
     uint32_t byte_base;
+    uint32_t codec;            // attributes & 7: 0 plain, 3 LZ4 (decompressed on the device), others unsupported
+    uint32_t rec_start, rec_end;   // the records: [start + 61, end) of the raw bytes, or the batch's
+                                   // region of the decompressed buffer
+    uint32_t unc_bytes;        // decompressed size of the records (codec != 0)
 };
 
 // Per-slot device scratch ("plan"): everything the kernels hand to one another.
@@ -67,6 +71,7 @@ struct tk_slot_dev {
                                // counters used alternately, each scan zeroes the one of the next
     // raw record-batch input (allocated on first tk_slot_submit_recordbatches)
     uint8_t*     raw;          // [slot_bytes + pad]
+    uint8_t*     raw2;         // [slot_bytes + pad] decompressed records of compressed batches (first use)
     tk_rb_batch* rb_batches;   // [slot_records]
     tk_rb_summary_t* rb_summary;
     uint4*       rb_temp;      // [slot_records] per-record copy descriptors

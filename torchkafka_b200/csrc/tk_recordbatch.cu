@@ -84,8 +84,11 @@ __device__ __forceinline__ bool rb_varint(const uint8_t* raw, uint32_t& p, uint3
     return false;
 }
 
+#define RB_SRC2 0x80000000u       // copy descriptor: the value lies in the decompressed buffer
+
 struct rb_args {
     const uint8_t*   raw;
+    uint8_t*         raw2;            // decompressed records of compressed batches
     tk_rb_batch*     batches;
     uint32_t         n_batches, n_records;    // from the host's header walk
     tk_rb_summary_t* summary;
@@ -113,8 +116,10 @@ static inline uint32_t rb_host_be32(const uint8_t* p) {
     return ((uint32_t)p[0] << 24) | ((uint32_t)p[1] << 16) | ((uint32_t)p[2] << 8) | p[3];
 }
 static int rb_walk_host(const uint8_t* raw, const tk_blob_t* blobs, uint32_t n_blobs, tk_rb_batch* out,
-                        uint32_t max_batches, uint32_t max_records, uint32_t* n_batches_out, uint32_t* n_records_out) {
+                        uint32_t max_batches, uint32_t max_records, uint32_t* n_batches_out, uint32_t* n_records_out,
+                        uint32_t* n_lz4_out) {
     uint32_t nb = 0;
+    *n_lz4_out = 0;
     uint64_t nrec = 0;
     for (uint32_t t = 0; t < n_blobs; ++t) {
         const tk_blob_t& blob = blobs[t];
@@ -122,7 +127,7 @@ static int rb_walk_host(const uint8_t* raw, const tk_blob_t* blobs, uint32_t n_b
         uint32_t pos = blob.start;
         while (blob_end - pos >= 12u) {
             const uint32_t blen = rb_host_be32(raw + pos + 8);
-            uint32_t end, status = TK_STATUS_OK, count = 1;
+            uint32_t end, status = TK_STATUS_OK, count = 1, codec = 0;
             if ((int32_t)blen < (int32_t)(RB_HEADER - 12u)) {
                 end = blob_end; status = TK_STATUS_CORRUPT;
             } else {
@@ -130,10 +135,13 @@ static int rb_walk_host(const uint8_t* raw, const tk_blob_t* blobs, uint32_t n_b
                 end = pos + 12u + blen;
                 const uint32_t magic = raw[pos + 16];
                 const uint32_t c = rb_host_be32(raw + pos + 57);
-                // a record is at least 7 bytes: a larger count cannot be true (the checksum would
-                // say so too, but the count sizes the slot before the checksum is looked at)
+                codec = raw[pos + 22] & 7u;
+                // a record is at least 7 bytes (LZ4 expands at most 255-fold): a larger count cannot
+                // be true (the checksum would say so too, but the count sizes the slot before the
+                // checksum is looked at)
+                const uint64_t room = (uint64_t)(end - pos - RB_HEADER) * (codec == 3 ? 255u : 1u);
                 if (magic != 2) { status = TK_STATUS_CORRUPT; end = blob_end; }
-                else if (c > (end - pos - RB_HEADER) / 7u + 1u) status = TK_STATUS_CORRUPT;
+                else if (c > room / 7u + 1u) status = TK_STATUS_CORRUPT;
                 else count = c;
             }
             TK_REQUIRE(nb < max_batches, "more record batches in the slot than slot_records (%u)", max_batches);
@@ -147,6 +155,8 @@ static int rb_walk_host(const uint8_t* raw, const tk_blob_t* blobs, uint32_t n_b
             b.base_offset = base;
             b.fetch_offset = blob.fetch_offset;
             b.n_rec = count; b.value_bytes = 0; b.rec_base = (uint32_t)nrec; b.byte_base = 0;
+            b.codec = status ? 0u : codec; b.rec_start = pos + RB_HEADER; b.rec_end = end; b.unc_bytes = 0;
+            if (b.codec == 3) ++*n_lz4_out;
             nrec += count;
             TK_REQUIRE(nrec <= max_records, "more records in the slot than slot_records (%u)", max_records);
             pos = end;
@@ -349,9 +359,12 @@ __global__ void __launch_bounds__(256) k_rb_check(const rb_args a) {
         if (!status) {
             const uint32_t attributes = ((uint32_t)a.raw[b.start + 21] << 8) | a.raw[b.start + 22];
             control = attributes & 0x20u;
-            if (attributes & 0x07u) status = TK_STATUS_UNSUPPORTED;              // compressed
+            if (b.codec != 0u && b.codec != 3u) status = TK_STATUS_UNSUPPORTED;  // gzip, snappy, zstd
         }
-        uint32_t p = b.start + RB_HEADER;                                        // lane 0's cursor
+        // the records: behind the header, or (LZ4) in the batch's region of the decompressed buffer
+        const uint8_t* rbase = b.codec == 3u ? a.raw2 : a.raw;
+        const uint32_t rend = b.rec_end, src_flag = b.codec == 3u ? RB_SRC2 : 0u;
+        uint32_t p = b.rec_start;                                                // lane 0's cursor
         for (uint32_t k0 = 0; !status && k0 < b.n_rec; k0 += 32) {
             const uint32_t m = min(32u, b.n_rec - k0);
             if (lane == 0) {
@@ -360,7 +373,7 @@ __global__ void __launch_bounds__(256) k_rb_check(const rb_args a) {
                     s_pos[wib][j] = p;
                     long long length;
                     uint32_t q = p;
-                    if (!rb_varint(a.raw, q, b.end, length) || length < 1 || (unsigned long long)length > b.end - q) {
+                    if (!rb_varint(rbase, q, rend, length) || length < 1 || (unsigned long long)length > rend - q) {
                         bad = 1;
                         break;
                     }
@@ -373,7 +386,7 @@ __global__ void __launch_bounds__(256) k_rb_check(const rb_args a) {
             uint32_t n = 0;
             if (!status && lane < m) {
                 rb_record r;
-                if (!rb_decode_record(a.raw, s_pos[wib][lane], b.end, r)) {
+                if (!rb_decode_record(rbase, s_pos[wib][lane], rend, r)) {
                     status = TK_STATUS_CORRUPT;
                 } else {
                     const long long offset = b.base_offset + r.offset_delta;
@@ -385,7 +398,7 @@ __global__ void __launch_bounds__(256) k_rb_check(const rb_args a) {
                     rec.offset = offset;
                     a.recs[b.rec_base + k0 + lane] = rec;
                     // .src now, .rel after the warp scan below
-                    temp[b.rec_base + k0 + lane].src = r.value_pos;
+                    temp[b.rec_base + k0 + lane].src = r.value_pos | src_flag;
                 }
             }
             if (__any_sync(0xffffffffu, status != 0)) { status = TK_STATUS_CORRUPT; break; }
@@ -404,7 +417,7 @@ __global__ void __launch_bounds__(256) k_rb_check(const rb_args a) {
         }
         // the cursor must land on the end of the batch
         const uint32_t p_end = __shfl_sync(0xffffffffu, p, 0);
-        if (!status && p_end != b.end) status = TK_STATUS_CORRUPT;
+        if (!status && p_end != rend) status = TK_STATUS_CORRUPT;
         if (status) {
             value_bytes = 0;
             for (uint32_t k = lane; k < b.n_rec; k += 32) {
@@ -488,7 +501,8 @@ __global__ void __launch_bounds__(256) k_rb_copy(const rb_args a) {
             a.recs[i].start = dst;
             if (t.y > RB_BIG) a.bigq[atomicAdd(&a.summary->reserved, 1u)] = i;
         }
-        if (t.y && t.y <= RB_BIG) rb_warp_copy(a.bytes + dst, a.raw + t.x, t.y, lane);
+        if (t.y && t.y <= RB_BIG)
+            rb_warp_copy(a.bytes + dst, ((t.x & RB_SRC2) ? a.raw2 : a.raw) + (t.x & ~RB_SRC2), t.y, lane);
     }
 }
 
@@ -512,10 +526,222 @@ __global__ void __launch_bounds__(256) k_rb_copy_big(const rb_args a) {
             for (; k < pieces; k += nwarps) {
                 const uint32_t from = k ? k * RB_PIECE + lead : 0u;
                 const uint32_t to = min((k + 1) * RB_PIECE + lead, t.y);
-                if (from < to) rb_warp_copy(a.bytes + dst + from, a.raw + t.x + from, to - from, lane);
+                if (from < to)
+                    rb_warp_copy(a.bytes + dst + from, ((t.x & RB_SRC2) ? a.raw2 : a.raw) + (t.x & ~RB_SRC2) + from,
+                                 to - from, lane);
             }
         }
         piece0 += pieces;
+    }
+}
+
+// ---------------------------------------------------------------- LZ4
+// Compressed batches (attributes & 7 == 3) hold one LZ4 frame behind the 61-byte header
+// (lz4_Frame_format.md: magic, FLG, BD, [content size], [dictionary id], header checksum, blocks
+// {u32 size, data, [checksum]}, end mark, [content checksum]; blocks per lz4_Block_format.md).
+// Replaces kafka-python's `lz4_decode` (kafka/codec.py, called from DefaultRecordBatch
+// ._maybe_uncompress).  The xxHash checksums are not verified: the batch's CRC-32C covers the same
+// bytes.  Two passes, because the decompressed size is written nowhere:
+//   k_lz4_size    thread per batch: walks the sequences without copying -> decompressed size
+//   k_lz4_prefix  one block: places every batch's records in the decompressed buffer
+//   k_lz4_decode  warp per batch: lane 0 reads the tokens, the warp copies literals and matches;
+//                 the last 64 KiB of output (the LZ4 window) live in a shared-memory ring, so a
+//                 match never waits for global memory; every byte is also stored to its final
+//                 place.  Frames with dependent blocks decode in order by construction.
+#define LZ4_RING 65536u
+
+struct lz4_frame {
+    uint32_t pos;          // first block header
+    bool independent, block_checksum, content_checksum;
+};
+// header of the frame at [p, end); false if it is not a frame this decoder handles
+__device__ __forceinline__ bool lz4_frame_header(const uint8_t* raw, uint32_t p, uint32_t end, lz4_frame& f, uint32_t& status) {
+    if (end - p < 7u || raw[p] != 0x04 || raw[p + 1] != 0x22 || raw[p + 2] != 0x4D || raw[p + 3] != 0x18) {
+        status = TK_STATUS_CORRUPT; return false;
+    }
+    const uint32_t flg = raw[p + 4];
+    if ((flg >> 6) != 1u) { status = TK_STATUS_CORRUPT; return false; }
+    if (flg & 1u) { status = TK_STATUS_UNSUPPORTED; return false; }        // dictionary
+    f.independent = flg & 0x20u; f.block_checksum = flg & 0x10u; f.content_checksum = flg & 0x04u;
+    f.pos = p + 6u + ((flg & 0x08u) ? 8u : 0u) + 1u;
+    if (f.pos > end) { status = TK_STATUS_CORRUPT; return false; }
+    return true;
+}
+__device__ __forceinline__ uint32_t lz4_le32(const uint8_t* p) {
+    return (uint32_t)p[0] | ((uint32_t)p[1] << 8) | ((uint32_t)p[2] << 16) | ((uint32_t)p[3] << 24);
+}
+// length with its 255-extension bytes; false if it runs past `end`
+__device__ __forceinline__ bool lz4_length(const uint8_t* raw, uint32_t& p, uint32_t end, uint32_t nibble, uint32_t& len) {
+    len = nibble;
+    if (nibble == 15u) {
+        uint32_t b;
+        do {
+            if (p >= end) return false;
+            b = raw[p++];
+            len += b;
+            if (len > 0x7FFFFFFFu) return false;
+        } while (b == 255u);
+    }
+    return true;
+}
+
+__global__ void __launch_bounds__(128) k_lz4_size(const rb_args a) {
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < a.n_batches; i += gridDim.x * blockDim.x) {
+        const tk_rb_batch b = a.batches[i];
+        if (b.status || b.codec != 3u) continue;
+        const uint8_t* raw = a.raw;
+        const uint32_t end = b.end;
+        uint32_t status = TK_STATUS_OK;
+        uint64_t out = 0;
+        lz4_frame f;
+        if (lz4_frame_header(raw, b.start + RB_HEADER, end, f, status)) {
+            uint32_t p = f.pos;
+            for (;;) {
+                if (end - p < 4u) { status = TK_STATUS_CORRUPT; break; }
+                uint32_t size = lz4_le32(raw + p);
+                p += 4;
+                if (size == 0) break;
+                const bool stored = size >> 31;
+                size &= 0x7FFFFFFFu;
+                if (size > end - p) { status = TK_STATUS_CORRUPT; break; }
+                const uint32_t bend = p + size;
+                if (stored) out += size;
+                else {
+                    while (p < bend) {
+                        const uint32_t token = raw[p++];
+                        uint32_t lit, mlen;
+                        if (!lz4_length(raw, p, bend, token >> 4, lit) || lit > bend - p) { status = TK_STATUS_CORRUPT; break; }
+                        p += lit; out += lit;
+                        if (p >= bend) break;
+                        if (bend - p < 2u) { status = TK_STATUS_CORRUPT; break; }
+                        p += 2;
+                        if (!lz4_length(raw, p, bend, token & 15u, mlen)) { status = TK_STATUS_CORRUPT; break; }
+                        out += mlen + 4u;
+                    }
+                    if (status) break;
+                }
+                p = bend + (f.block_checksum ? 4u : 0u);
+                if (p > end) { status = TK_STATUS_CORRUPT; break; }
+            }
+            if (!status && p + (f.content_checksum ? 4u : 0u) != end) status = TK_STATUS_CORRUPT;
+            if (!status && out > 0x7FFFFFFFull) status = TK_STATUS_UNSUPPORTED;
+        }
+        a.batches[i].status = status;
+        a.batches[i].unc_bytes = status ? 0u : (uint32_t)out;
+    }
+}
+
+__global__ void __launch_bounds__(1024) k_lz4_prefix(const rb_args a) {
+    __shared__ unsigned long long warp_tot[32];
+    __shared__ unsigned long long s_total, s_run;
+    const uint32_t t = threadIdx.x;
+    if (t == 0) s_run = 0;
+    __syncthreads();
+    for (uint32_t base = 0; base < a.n_batches; base += blockDim.x) {
+        const uint32_t i = base + t;
+        const bool mine = i < a.n_batches && a.batches[i].codec == 3u && !a.batches[i].status;
+        const unsigned long long v = mine ? a.batches[i].unc_bytes : 0ull;
+        const unsigned long long excl = s_run + rb_block_scan(v, warp_tot, &s_total);
+        if (mine) {
+            if (excl + v > a.slot_bytes) a.batches[i].status = TK_STATUS_UNSUPPORTED;   // does not fit the slot
+            else { a.batches[i].rec_start = (uint32_t)excl; a.batches[i].rec_end = (uint32_t)(excl + v); }
+        }
+        __syncthreads();
+        if (t == 0) s_run += s_total;
+        __syncthreads();
+    }
+}
+
+// one 32-thread block per batch at a time, 64 KiB of dynamic shared memory (the window)
+__global__ void __launch_bounds__(32) k_lz4_decode(const rb_args a) {
+    extern __shared__ uint8_t ring[];
+    const uint32_t lane = threadIdx.x;
+    for (uint32_t i = blockIdx.x; i < a.n_batches; i += gridDim.x) {
+        const tk_rb_batch b = a.batches[i];
+        if (b.status || b.codec != 3u) continue;
+        const uint8_t* raw = a.raw;
+        uint8_t* out = a.raw2 + b.rec_start;
+        const uint32_t cap = b.rec_end - b.rec_start, end = b.end;
+        uint32_t status = TK_STATUS_OK, op = 0;
+        lz4_frame f;
+        lz4_frame_header(raw, b.start + RB_HEADER, end, f, status);      // validated by k_lz4_size
+        uint32_t p = f.pos;
+        while (!status) {
+            uint32_t size = lz4_le32(raw + p);
+            p += 4;
+            if (size == 0) break;
+            const bool stored = size >> 31;
+            size &= 0x7FFFFFFFu;
+            const uint32_t bend = p + size;
+            const uint32_t window = f.independent ? op : 0u;             // matches reach back to here
+            if (stored) {
+                if (size > cap - op) { status = TK_STATUS_CORRUPT; break; }
+                for (uint32_t k = lane; k < size; k += 32) {
+                    const uint8_t v = raw[p + k];
+                    ring[(op + k) & (LZ4_RING - 1)] = v;
+                    out[op + k] = v;
+                }
+                op += size;
+                __syncwarp();
+            } else {
+                while (p < bend) {
+                    // lane 0 reads the sequence header, everybody copies
+                    uint32_t token = 0, lit = 0, lit_at = 0, ok = 1;
+                    if (lane == 0) {
+                        token = raw[p];
+                        lit_at = p + 1;
+                        ok = lz4_length(raw, lit_at, bend, token >> 4, lit) && lit <= bend - lit_at && lit <= cap - op;
+                    }
+                    ok = __shfl_sync(0xffffffffu, ok, 0);
+                    if (!ok) { status = TK_STATUS_CORRUPT; break; }
+                    token = __shfl_sync(0xffffffffu, token, 0);
+                    lit = __shfl_sync(0xffffffffu, lit, 0);
+                    lit_at = __shfl_sync(0xffffffffu, lit_at, 0);
+                    for (uint32_t k = lane; k < lit; k += 32) {
+                        const uint8_t v = raw[lit_at + k];
+                        ring[(op + k) & (LZ4_RING - 1)] = v;
+                        out[op + k] = v;
+                    }
+                    op += lit;
+                    p = lit_at + lit;
+                    if (p >= bend) break;
+                    uint32_t offset = 0, mlen = 0, next = 0;
+                    if (lane == 0) {
+                        offset = (uint32_t)raw[p] | ((uint32_t)raw[p + 1] << 8);
+                        next = p + 2;
+                        ok = bend - p >= 2u && lz4_length(raw, next, bend, token & 15u, mlen);
+                        mlen += 4u;
+                        ok = ok && offset != 0 && offset <= op - window && mlen <= cap - op;
+                    }
+                    ok = __shfl_sync(0xffffffffu, ok, 0);
+                    if (!ok) { status = TK_STATUS_CORRUPT; break; }
+                    offset = __shfl_sync(0xffffffffu, offset, 0);
+                    mlen = __shfl_sync(0xffffffffu, mlen, 0);
+                    p = __shfl_sync(0xffffffffu, next, 0);
+                    __syncwarp();                                  // the literals are in the ring
+                    // out[op + k] = out[op - offset + k]; where the match overlaps its own output the
+                    // source repeats with period `offset`, so every byte comes from before `op`.
+                    // Chunks of half a ring: a long match must not overwrite its own source.
+                    while (mlen) {
+                        const uint32_t n = min(mlen, LZ4_RING / 2);
+                        for (uint32_t k = lane; k < n; k += 32) {
+                            const uint32_t from = op - offset + (offset >= n ? k : k % offset);
+                            const uint8_t v = ring[from & (LZ4_RING - 1)];
+                            out[op + k] = v;
+                            ring[(op + k) & (LZ4_RING - 1)] = v;
+                        }
+                        __syncwarp();
+                        op += n;
+                        mlen -= n;
+                    }
+                }
+                if (status) break;
+            }
+            p = bend + (f.block_checksum ? 4u : 0u);
+        }
+        if (!status && op != cap) status = TK_STATUS_CORRUPT;
+        if (status && lane == 0) a.batches[i].status = status;
+        __syncwarp();
     }
 }
 
@@ -541,6 +767,21 @@ static int rb_ensure(tk_ctx* ctx) {
     return 0;
 }
 
+// the decompressed buffer and the decoder's 64 KiB of dynamic shared memory: first compressed batch
+static int rb_ensure_lz4(tk_ctx* ctx) {
+    std::lock_guard<std::mutex> lock(g_rb_mutex);
+    TK_REQUIRE(ctx->slot_bytes < (1ull << 31), "compressed record batches need slot_bytes < 2 GiB");
+    if (ctx->n_slots && ctx->slots[ctx->n_slots - 1].d.raw2) return 0;
+    TK_CUDA(cudaFuncSetAttribute(k_lz4_decode, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)LZ4_RING));
+    for (int i = 0; i < ctx->n_slots; ++i) {
+        tk_slot& s = ctx->slots[i];
+        if (s.d.raw2) continue;
+        TK_CUDA(cudaMalloc(&s.d.raw2, ctx->slot_bytes + TK_BYTES_PAD));
+        TK_CUDA(cudaMemset(s.d.raw2, 0, ctx->slot_bytes + TK_BYTES_PAD));
+    }
+    return 0;
+}
+
 extern "C" int tk_slot_submit_recordbatches(tk_ctx* ctx, int slot, uint64_t n_bytes, const tk_blob_t* blobs,
                                             uint32_t n_blobs, uint32_t* n_records) {
     TK_ENTER(ctx, slot);
@@ -554,9 +795,11 @@ extern "C" int tk_slot_submit_recordbatches(tk_ctx* ctx, int slot, uint64_t n_by
     int rc = rb_ensure(ctx); if (rc) return rc;
     tk_slot& s = ctx->slots[slot];
     cudaStream_t st = ctx->copy_stream;
-    uint32_t n_batches = 0, n_rec = 0;
-    rc = rb_walk_host(s.h_bytes, blobs, n_blobs, s.h_rb_batches, ctx->slot_records, ctx->slot_records, &n_batches, &n_rec);
+    uint32_t n_batches = 0, n_rec = 0, n_lz4 = 0;
+    rc = rb_walk_host(s.h_bytes, blobs, n_blobs, s.h_rb_batches, ctx->slot_records, ctx->slot_records, &n_batches,
+                      &n_rec, &n_lz4);
     if (rc) return rc;
+    if (n_lz4) { rc = rb_ensure_lz4(ctx); if (rc) return rc; }
     s.n_records = n_rec;
     s.n_bytes = n_bytes;                     // upper bound of the value bytes (sizes grids only)
     if (n_records) *n_records = n_rec;
@@ -573,9 +816,14 @@ extern "C" int tk_slot_submit_recordbatches(tk_ctx* ctx, int slot, uint64_t n_by
     TK_CUDA(cudaEventRecord(s.ev_raw, st));
     TK_CUDA(cudaStreamWaitEvent(ks, s.ev_raw, 0));
     rb_args a;
-    a.raw = s.d.raw; a.batches = s.d.rb_batches; a.n_batches = n_batches; a.n_records = n_rec;
+    a.raw = s.d.raw; a.raw2 = s.d.raw2; a.batches = s.d.rb_batches; a.n_batches = n_batches; a.n_records = n_rec;
     a.summary = s.d.rb_summary; a.temp = s.d.rb_temp; a.bigq = s.d.rb_bigq; a.bytes = s.d.bytes; a.recs = s.d.recs;
     a.slot_records = ctx->slot_records; a.slot_bytes = ctx->slot_bytes;
+    if (n_lz4) {
+        k_lz4_size<<<(n_batches + 127) / 128, 128, 0, ks>>>(a);
+        k_lz4_prefix<<<1, 1024, 0, ks>>>(a);
+        k_lz4_decode<<<min(n_batches, 148u * 3u), 32, LZ4_RING, ks>>>(a);
+    }
     k_rb_check<<<148 * 4, 256, 0, ks>>>(a);
     k_rb_prefix<<<1, 1024, 0, ks>>>(a);
     k_rb_copy<<<148 * 8, 256, 0, ks>>>(a);

@@ -70,15 +70,27 @@ def encode_record(offset_delta: int, value: Optional[bytes], key: Optional[bytes
     return _vi(len(body)) + bytes(body)
 
 
+def lz4_frame(data: bytes) -> bytes:
+    """LZ4 frame of `data` (pyarrow's codec: test infrastructure, as the oracle is)."""
+    import pyarrow as pa
+    return pa.Codec("lz4").compress(data, asbytes=True)
+
+
 def encode_batch(base_offset: int, values: Sequence[Optional[bytes]], attributes: int = 0,
                  offset_deltas: Optional[Sequence[int]] = None, keys: Optional[Sequence] = None,
-                 headers: Optional[Sequence] = None, crc: Optional[int] = None) -> bytes:
-    """One RecordBatch v2.  `offset_deltas` default to 0, 1, 2, ... (a compacted topic has gaps)."""
+                 headers: Optional[Sequence] = None, crc: Optional[int] = None, codec: int = 0) -> bytes:
+    """One RecordBatch v2.  `offset_deltas` default to 0, 1, 2, ... (a compacted topic has gaps).
+    `codec` 3 compresses the records with LZ4 (frame format) and sets the attribute bits."""
     n = len(values)
     deltas = list(range(n)) if offset_deltas is None else list(offset_deltas)
     recs = b"".join(encode_record(deltas[k], values[k], None if keys is None else keys[k], 0,
                                   () if headers is None else headers[k]) for k in range(n))
     last = deltas[-1] if n else 0
+    if codec == 3:
+        recs = lz4_frame(recs)
+        attributes |= 3
+    elif codec:
+        raise ValueError("the stub broker compresses with LZ4 only")
     tail = struct.pack(">hiqqqhii", attributes, last, 0, 0, -1, -1, -1, n) + recs    # from byte 21 on
     if crc is None:
         crc = crc32c(tail)
@@ -90,7 +102,7 @@ class EncodedLog:
     """A RecordLog as record batches: every run of same-partition records of the log becomes one
     or more batches of at most `batch_bytes` of payload (at least one record)."""
 
-    def __init__(self, log, batch_bytes: int = 16384):
+    def __init__(self, log, batch_bytes: int = 16384, codec: int = 0):
         values = log._byte_values            # noqa: SLF001 (test helper of the same package)
         parts = log.partitions
         offs = log.offsets
@@ -107,7 +119,7 @@ class EncodedLog:
                                                                and size + len(values[j]) <= batch_bytes)):
                 size += len(values[j])
                 j += 1
-            blob = encode_batch(int(offs[i]), values[i:j])
+            blob = encode_batch(int(offs[i]), values[i:j], codec=codec)
             chunks.append(blob)
             first_rec.append(i)
             part_of.append(p)

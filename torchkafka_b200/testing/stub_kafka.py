@@ -171,13 +171,14 @@ class RecordLog:
             self._bounds = (np.flatnonzero(p[1:] != p[:-1]) + 1) if len(p) > 1 else np.zeros(0, np.int64)
         return self._bounds
 
-    def encoded(self, batch_bytes: int = 16384):
-        """The log as RecordBatch v2 bytes (``testing.record_batch.EncodedLog``), cached."""
+    def encoded(self, batch_bytes: int = 16384, codec: int = 0):
+        """The log as RecordBatch v2 bytes (``testing.record_batch.EncodedLog``), cached.
+        ``codec`` 3 = LZ4-compressed batches."""
         cache = self.__dict__.setdefault("_encoded", {})
-        if batch_bytes not in cache:
+        if (batch_bytes, codec) not in cache:
             from .record_batch import EncodedLog
-            cache[batch_bytes] = EncodedLog(self, batch_bytes)
-        return cache[batch_bytes]
+            cache[(batch_bytes, codec)] = EncodedLog(self, batch_bytes, codec)
+        return cache[(batch_bytes, codec)]
 
     def select_partitions(self, keep) -> "RecordLog":
         """Sub-log holding only partitions for which ``keep(p)`` is true."""
@@ -197,7 +198,8 @@ class KafkaConsumer:
     """
 
     def __init__(self, *topics, log: Optional[RecordLog] = None, block_at_end: bool = False,
-                 fail_commits: bool = False, repeat: int = 1, raw_batch_bytes: int = 16384, **configs):
+                 fail_commits: bool = False, repeat: int = 1, raw_batch_bytes: int = 16384,
+                 raw_codec: int = 0, **configs):
         self.topics = topics
         self.config = dict(configs)
         # the end of the in-memory log is the end of the stream, unless the stub is told to
@@ -209,6 +211,7 @@ class KafkaConsumer:
         self._repeat = max(1, int(repeat))
         self._block_at_end = block_at_end
         self._raw_batch_bytes = int(raw_batch_bytes)
+        self._raw_codec = int(raw_codec)
         self._fail_commits = fail_commits
         self._positions: Dict[int, int] = {}
         self.committed_log: List[Dict[int, int]] = []
@@ -319,7 +322,7 @@ class KafkaConsumer:
         """
         if not self._roll():
             return None
-        enc = self._log.encoded(self._raw_batch_bytes)
+        enc = self._log.encoded(self._raw_batch_bytes, self._raw_codec)
         first, start, part = enc.first_rec, enc.start, enc.partition
         run_end = enc.run_end                    # run_end[b] = first batch after b of another partition
         b = int(np.searchsorted(first, self._cursor, side="right")) - 1      # batch holding the cursor

@@ -79,7 +79,8 @@ def device_resident(cfg, log, passes=24):
             "payload_GBps": (log.nbytes + 16 * len(log)) / ms / 1e6}, peak
 
 
-RAW_BATCH_BYTES = 64 << 10
+RAW_BATCH_BYTES = int(os.environ.get("RAW_BATCH_BYTES", str(64 << 10)))
+RAW_CODEC = int(os.environ.get("RAW_CODEC", "0"))      # 3: the raw arm serves LZ4-compressed batches
 
 
 def e2e(cfg, log, packed, repeat, batches_timed, warm):
@@ -95,7 +96,8 @@ def e2e(cfg, log, packed, repeat, batches_timed, warm):
         @classmethod
         def new_consumer(cls, *a, **k):
             k.pop("enable_auto_commit", None)
-            return consumer_cls(*a, log=log, repeat=repeat, raw_batch_bytes=max(RAW_BATCH_BYTES, 2 * cfg.get("record_bytes", 0)), **k)
+            return consumer_cls(*a, log=log, repeat=repeat, raw_codec=RAW_CODEC,
+                                raw_batch_bytes=max(RAW_BATCH_BYTES, 2 * cfg.get("record_bytes", 0)), **k)
 
     from torch.utils.data import DataLoader
     ds = DS("topic", group_id="cfg")
@@ -166,7 +168,7 @@ def main():
                "link_bytes_per_record": link_bytes, "device": dev, "h2d_peak_GBps": peak}
         for packed in (False, True, "raw"):
             if packed == "raw":
-                enc = log.encoded(max(RAW_BATCH_BYTES, 2 * cfg.get("record_bytes", 0)))   # before the clock
+                enc = log.encoded(max(RAW_BATCH_BYTES, 2 * cfg.get("record_bytes", 0)), RAW_CODEC)   # before the clock
                 lb = enc.nbytes / len(log)
             else:
                 lb = link_bytes

@@ -542,13 +542,12 @@ __global__ void __launch_bounds__(256) k_rb_copy_big(const rb_args a) {
 // Replaces kafka-python's `lz4_decode` (kafka/codec.py, called from DefaultRecordBatch
 // ._maybe_uncompress).  The xxHash checksums are not verified: the batch's CRC-32C covers the same
 // bytes.  Two passes, because the decompressed size is written nowhere:
-//   k_lz4_size    thread per batch: walks the sequences without copying -> decompressed size
+//   k_lz4_size    warp per batch: walks the sequences without copying -> decompressed size
 //   k_lz4_prefix  one block: places every batch's records in the decompressed buffer
-//   k_lz4_decode  warp per batch: lane 0 reads the tokens, the warp copies literals and matches;
-//                 the last 64 KiB of output (the LZ4 window) live in a shared-memory ring, so a
-//                 match never waits for global memory; every byte is also stored to its final
-//                 place.  Frames with dependent blocks decode in order by construction.
-#define LZ4_RING 65536u
+//   k_lz4_decode  warp per batch: every lane parses the sequences out of a shuffled 128-byte window
+//                 of the compressed bytes, the warp copies literals and matches;
+//                 matches are read back from the batch's own output through L1.  Frames with
+//                 dependent blocks decode in order by construction.
 
 struct lz4_frame {
     uint32_t pos;          // first block header
@@ -570,14 +569,34 @@ __device__ __forceinline__ bool lz4_frame_header(const uint8_t* raw, uint32_t p,
 __device__ __forceinline__ uint32_t lz4_le32(const uint8_t* p) {
     return (uint32_t)p[0] | ((uint32_t)p[1] << 8) | ((uint32_t)p[2] << 16) | ((uint32_t)p[3] << 24);
 }
+// The compressed bytes are read through a 128-byte window held by the warp (4 bytes per lane, one
+// coalesced load per ~100 bytes consumed): a sequence is 5-10 bytes long and its fields depend on
+// one another, so reading them from memory one at a time would cost a cache round trip each.
+// Every lane runs the same parse on bytes fetched by shuffle; nothing is broadcast from a leader.
+struct lz4_window {
+    const uint8_t* raw;
+    uint32_t at;          // position of the window's first byte (multiple of 4)
+    uint32_t word;        // this lane's 4 bytes
+};
+__device__ __forceinline__ void lz4_window_load(lz4_window& w, uint32_t pos, uint32_t lane) {
+    w.at = pos & ~3u;
+    w.word = *reinterpret_cast<const uint32_t*>(w.raw + w.at + 4u * lane);    // inside the padded buffer
+}
+// byte at `pos` (same in every lane)
+__device__ __forceinline__ uint32_t lz4_byte(lz4_window& w, uint32_t pos, uint32_t lane) {
+    if (pos - w.at >= 128u) lz4_window_load(w, pos, lane);
+    const uint32_t j = pos - w.at;
+    return (__shfl_sync(0xffffffffu, w.word, j >> 2) >> ((j & 3u) * 8u)) & 0xFFu;
+}
 // length with its 255-extension bytes; false if it runs past `end`
-__device__ __forceinline__ bool lz4_length(const uint8_t* raw, uint32_t& p, uint32_t end, uint32_t nibble, uint32_t& len) {
+__device__ __forceinline__ bool lz4_length(lz4_window& w, uint32_t lane, uint32_t& p, uint32_t end, uint32_t nibble,
+                                           uint32_t& len) {
     len = nibble;
     if (nibble == 15u) {
         uint32_t b;
         do {
             if (p >= end) return false;
-            b = raw[p++];
+            b = lz4_byte(w, p++, lane);
             len += b;
             if (len > 0x7FFFFFFFu) return false;
         } while (b == 255u);
@@ -585,49 +604,106 @@ __device__ __forceinline__ bool lz4_length(const uint8_t* raw, uint32_t& p, uint
     return true;
 }
 
-__global__ void __launch_bounds__(128) k_lz4_size(const rb_args a) {
-    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < a.n_batches; i += gridDim.x * blockDim.x) {
+// One frame, whole warp.  EMIT = false: only the decompressed size is computed (*out_size);
+// EMIT = true: the bytes are written to `out` (capacity `cap`).
+template <bool EMIT>
+__device__ __forceinline__ uint32_t lz4_frame_run(const uint8_t* raw, uint32_t start, uint32_t end, uint32_t lane,
+                                                  uint8_t* out, uint32_t cap, uint64_t* out_size) {
+    uint32_t status = TK_STATUS_OK;
+    lz4_frame f;
+    if (!lz4_frame_header(raw, start, end, f, status)) return status;
+    lz4_window w;
+    w.raw = raw;
+    uint32_t p = f.pos;
+    lz4_window_load(w, p, lane);
+    uint64_t total = 0;
+    uint32_t op = 0;
+    for (;;) {
+        if (end - p < 4u) return TK_STATUS_CORRUPT;
+        uint32_t size = lz4_byte(w, p, lane) | (lz4_byte(w, p + 1, lane) << 8) | (lz4_byte(w, p + 2, lane) << 16) |
+                        (lz4_byte(w, p + 3, lane) << 24);
+        p += 4;
+        if (size == 0) break;
+        const bool stored = size >> 31;
+        size &= 0x7FFFFFFFu;
+        if (size > end - p) return TK_STATUS_CORRUPT;
+        const uint32_t bend = p + size;
+        const uint32_t window = f.independent ? op : 0u;             // matches reach back to here
+        if (stored) {
+            total += size;
+            if (EMIT) {
+                if (size > cap - op) return TK_STATUS_CORRUPT;
+                for (uint32_t k = lane; k < size; k += 32) {
+                    out[op + k] = raw[p + k];
+                }
+                op += size;
+                __syncwarp();
+            }
+        } else {
+            while (p < bend) {
+                const uint32_t token = lz4_byte(w, p, lane);
+                uint32_t lit, lit_at = p + 1;
+                if (!lz4_length(w, lane, lit_at, bend, token >> 4, lit) || lit > bend - lit_at) return TK_STATUS_CORRUPT;
+                total += lit;
+                if (EMIT) {
+                    if (lit > cap - op) return TK_STATUS_CORRUPT;
+                    if (lit <= 32u && lit_at - w.at + 32u <= 128u) {          // literals are in the window
+                        const uint32_t j = lit_at - w.at + lane;
+                        const uint8_t v = (uint8_t)(__shfl_sync(0xffffffffu, w.word, (j >> 2) & 31u) >> ((j & 3u) * 8u));
+                        if (lane < lit) out[op + lane] = v;
+                    } else {
+                        for (uint32_t k = lane; k < lit; k += 32) {
+                            out[op + k] = raw[lit_at + k];
+                        }
+                    }
+                    op += lit;
+                }
+                p = lit_at + lit;
+                if (p >= bend) break;                                 // the last sequence has no match
+                if (bend - p < 2u) return TK_STATUS_CORRUPT;
+                const uint32_t offset = lz4_byte(w, p, lane) | (lz4_byte(w, p + 1, lane) << 8);
+                p += 2;
+                uint32_t mlen;
+                if (!lz4_length(w, lane, p, bend, token & 15u, mlen)) return TK_STATUS_CORRUPT;
+                mlen += 4u;
+                total += mlen;
+                if (EMIT) {
+                    if (offset == 0 || offset > op - window || mlen > cap - op) return TK_STATUS_CORRUPT;
+                    // out[op + k] = out[op - offset + k]; where the match overlaps its own output the
+                    // source repeats with period `offset`, so every byte comes from before `op`: the
+                    // lanes never read what this match writes.  The bytes were written by other lanes
+                    // of this warp: __syncwarp orders them, and they are read back through the L1 of
+                    // the same SM (the decompressed region belongs to this warp alone).
+                    __syncwarp();
+                    for (uint32_t k = lane; k < mlen; k += 32)
+                        out[op + k] = out[op - offset + (offset >= mlen ? k : k % offset)];
+                    __syncwarp();
+                    op += mlen;
+                }
+            }
+        }
+        p = bend + (f.block_checksum ? 4u : 0u);
+        if (p > end) return TK_STATUS_CORRUPT;
+    }
+    if (p + (f.content_checksum ? 4u : 0u) != end) return TK_STATUS_CORRUPT;
+    if (EMIT && op != cap) return TK_STATUS_CORRUPT;
+    *out_size = total;
+    return TK_STATUS_OK;
+}
+
+__global__ void __launch_bounds__(256) k_lz4_size(const rb_args a) {
+    const uint32_t lane = threadIdx.x & 31;
+    const uint32_t warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, nwarps = (gridDim.x * blockDim.x) >> 5;
+    for (uint32_t i = warp; i < a.n_batches; i += nwarps) {
         const tk_rb_batch b = a.batches[i];
         if (b.status || b.codec != 3u) continue;
-        const uint8_t* raw = a.raw;
-        const uint32_t end = b.end;
-        uint32_t status = TK_STATUS_OK;
         uint64_t out = 0;
-        lz4_frame f;
-        if (lz4_frame_header(raw, b.start + RB_HEADER, end, f, status)) {
-            uint32_t p = f.pos;
-            for (;;) {
-                if (end - p < 4u) { status = TK_STATUS_CORRUPT; break; }
-                uint32_t size = lz4_le32(raw + p);
-                p += 4;
-                if (size == 0) break;
-                const bool stored = size >> 31;
-                size &= 0x7FFFFFFFu;
-                if (size > end - p) { status = TK_STATUS_CORRUPT; break; }
-                const uint32_t bend = p + size;
-                if (stored) out += size;
-                else {
-                    while (p < bend) {
-                        const uint32_t token = raw[p++];
-                        uint32_t lit, mlen;
-                        if (!lz4_length(raw, p, bend, token >> 4, lit) || lit > bend - p) { status = TK_STATUS_CORRUPT; break; }
-                        p += lit; out += lit;
-                        if (p >= bend) break;
-                        if (bend - p < 2u) { status = TK_STATUS_CORRUPT; break; }
-                        p += 2;
-                        if (!lz4_length(raw, p, bend, token & 15u, mlen)) { status = TK_STATUS_CORRUPT; break; }
-                        out += mlen + 4u;
-                    }
-                    if (status) break;
-                }
-                p = bend + (f.block_checksum ? 4u : 0u);
-                if (p > end) { status = TK_STATUS_CORRUPT; break; }
-            }
-            if (!status && p + (f.content_checksum ? 4u : 0u) != end) status = TK_STATUS_CORRUPT;
-            if (!status && out > 0x7FFFFFFFull) status = TK_STATUS_UNSUPPORTED;
+        uint32_t status = lz4_frame_run<false>(a.raw, b.start + RB_HEADER, b.end, lane, nullptr, 0, &out);
+        if (!status && out > 0x7FFFFFFFull) status = TK_STATUS_UNSUPPORTED;
+        if (lane == 0) {
+            a.batches[i].status = status;
+            a.batches[i].unc_bytes = status ? 0u : (uint32_t)out;
         }
-        a.batches[i].status = status;
-        a.batches[i].unc_bytes = status ? 0u : (uint32_t)out;
     }
 }
 
@@ -652,96 +728,17 @@ __global__ void __launch_bounds__(1024) k_lz4_prefix(const rb_args a) {
     }
 }
 
-// one 32-thread block per batch at a time, 64 KiB of dynamic shared memory (the window)
-__global__ void __launch_bounds__(32) k_lz4_decode(const rb_args a) {
-    extern __shared__ uint8_t ring[];
-    const uint32_t lane = threadIdx.x;
-    for (uint32_t i = blockIdx.x; i < a.n_batches; i += gridDim.x) {
+// warp per batch
+__global__ void __launch_bounds__(128) k_lz4_decode(const rb_args a) {
+    const uint32_t lane = threadIdx.x & 31;
+    const uint32_t warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, nwarps = (gridDim.x * blockDim.x) >> 5;
+    for (uint32_t i = warp; i < a.n_batches; i += nwarps) {
         const tk_rb_batch b = a.batches[i];
         if (b.status || b.codec != 3u) continue;
-        const uint8_t* raw = a.raw;
-        uint8_t* out = a.raw2 + b.rec_start;
-        const uint32_t cap = b.rec_end - b.rec_start, end = b.end;
-        uint32_t status = TK_STATUS_OK, op = 0;
-        lz4_frame f;
-        lz4_frame_header(raw, b.start + RB_HEADER, end, f, status);      // validated by k_lz4_size
-        uint32_t p = f.pos;
-        while (!status) {
-            uint32_t size = lz4_le32(raw + p);
-            p += 4;
-            if (size == 0) break;
-            const bool stored = size >> 31;
-            size &= 0x7FFFFFFFu;
-            const uint32_t bend = p + size;
-            const uint32_t window = f.independent ? op : 0u;             // matches reach back to here
-            if (stored) {
-                if (size > cap - op) { status = TK_STATUS_CORRUPT; break; }
-                for (uint32_t k = lane; k < size; k += 32) {
-                    const uint8_t v = raw[p + k];
-                    ring[(op + k) & (LZ4_RING - 1)] = v;
-                    out[op + k] = v;
-                }
-                op += size;
-                __syncwarp();
-            } else {
-                while (p < bend) {
-                    // lane 0 reads the sequence header, everybody copies
-                    uint32_t token = 0, lit = 0, lit_at = 0, ok = 1;
-                    if (lane == 0) {
-                        token = raw[p];
-                        lit_at = p + 1;
-                        ok = lz4_length(raw, lit_at, bend, token >> 4, lit) && lit <= bend - lit_at && lit <= cap - op;
-                    }
-                    ok = __shfl_sync(0xffffffffu, ok, 0);
-                    if (!ok) { status = TK_STATUS_CORRUPT; break; }
-                    token = __shfl_sync(0xffffffffu, token, 0);
-                    lit = __shfl_sync(0xffffffffu, lit, 0);
-                    lit_at = __shfl_sync(0xffffffffu, lit_at, 0);
-                    for (uint32_t k = lane; k < lit; k += 32) {
-                        const uint8_t v = raw[lit_at + k];
-                        ring[(op + k) & (LZ4_RING - 1)] = v;
-                        out[op + k] = v;
-                    }
-                    op += lit;
-                    p = lit_at + lit;
-                    if (p >= bend) break;
-                    uint32_t offset = 0, mlen = 0, next = 0;
-                    if (lane == 0) {
-                        offset = (uint32_t)raw[p] | ((uint32_t)raw[p + 1] << 8);
-                        next = p + 2;
-                        ok = bend - p >= 2u && lz4_length(raw, next, bend, token & 15u, mlen);
-                        mlen += 4u;
-                        ok = ok && offset != 0 && offset <= op - window && mlen <= cap - op;
-                    }
-                    ok = __shfl_sync(0xffffffffu, ok, 0);
-                    if (!ok) { status = TK_STATUS_CORRUPT; break; }
-                    offset = __shfl_sync(0xffffffffu, offset, 0);
-                    mlen = __shfl_sync(0xffffffffu, mlen, 0);
-                    p = __shfl_sync(0xffffffffu, next, 0);
-                    __syncwarp();                                  // the literals are in the ring
-                    // out[op + k] = out[op - offset + k]; where the match overlaps its own output the
-                    // source repeats with period `offset`, so every byte comes from before `op`.
-                    // Chunks of half a ring: a long match must not overwrite its own source.
-                    while (mlen) {
-                        const uint32_t n = min(mlen, LZ4_RING / 2);
-                        for (uint32_t k = lane; k < n; k += 32) {
-                            const uint32_t from = op - offset + (offset >= n ? k : k % offset);
-                            const uint8_t v = ring[from & (LZ4_RING - 1)];
-                            out[op + k] = v;
-                            ring[(op + k) & (LZ4_RING - 1)] = v;
-                        }
-                        __syncwarp();
-                        op += n;
-                        mlen -= n;
-                    }
-                }
-                if (status) break;
-            }
-            p = bend + (f.block_checksum ? 4u : 0u);
-        }
-        if (!status && op != cap) status = TK_STATUS_CORRUPT;
+        uint64_t total = 0;
+        const uint32_t status = lz4_frame_run<true>(a.raw, b.start + RB_HEADER, b.end, lane, a.raw2 + b.rec_start,
+                                                    b.rec_end - b.rec_start, &total);
         if (status && lane == 0) a.batches[i].status = status;
-        __syncwarp();
     }
 }
 
@@ -767,12 +764,11 @@ static int rb_ensure(tk_ctx* ctx) {
     return 0;
 }
 
-// the decompressed buffer and the decoder's 64 KiB of dynamic shared memory: first compressed batch
+// the decompressed buffer: first compressed batch
 static int rb_ensure_lz4(tk_ctx* ctx) {
     std::lock_guard<std::mutex> lock(g_rb_mutex);
     TK_REQUIRE(ctx->slot_bytes < (1ull << 31), "compressed record batches need slot_bytes < 2 GiB");
     if (ctx->n_slots && ctx->slots[ctx->n_slots - 1].d.raw2) return 0;
-    TK_CUDA(cudaFuncSetAttribute(k_lz4_decode, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)LZ4_RING));
     for (int i = 0; i < ctx->n_slots; ++i) {
         tk_slot& s = ctx->slots[i];
         if (s.d.raw2) continue;
@@ -820,9 +816,9 @@ extern "C" int tk_slot_submit_recordbatches(tk_ctx* ctx, int slot, uint64_t n_by
     a.summary = s.d.rb_summary; a.temp = s.d.rb_temp; a.bigq = s.d.rb_bigq; a.bytes = s.d.bytes; a.recs = s.d.recs;
     a.slot_records = ctx->slot_records; a.slot_bytes = ctx->slot_bytes;
     if (n_lz4) {
-        k_lz4_size<<<(n_batches + 127) / 128, 128, 0, ks>>>(a);
+        k_lz4_size<<<min((n_batches + 7) / 8, 148u * 8u), 256, 0, ks>>>(a);
         k_lz4_prefix<<<1, 1024, 0, ks>>>(a);
-        k_lz4_decode<<<min(n_batches, 148u * 3u), 32, LZ4_RING, ks>>>(a);
+        k_lz4_decode<<<min((n_batches + 3) / 4, 148u * 16u), 128, 0, ks>>>(a);
     }
     k_rb_check<<<148 * 4, 256, 0, ks>>>(a);
     k_rb_prefix<<<1, 1024, 0, ks>>>(a);

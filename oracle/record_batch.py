@@ -15,8 +15,9 @@ Semantics restated from kafka-python's fetcher:
   * CRC mismatch, magic != 2, malformed varints raise CorruptRecordError;
   * LZ4-compressed batches (codec 3) are decompressed with the restatement of the LZ4 frame and
     block formats below (lz4_Frame_format.md / lz4_Block_format.md of the LZ4 project; xxHash
-    checksums are skipped, the batch CRC covers the same bytes); the other codecs (gzip, snappy,
-    zstd: SURVEY §8f-2) raise UnsupportedBatch;
+    checksums are skipped, the batch CRC covers the same bytes); snappy batches (codec 2) with the
+    restatement of snappy's format_description.txt, raw or in snappy-java's xerial framing (what
+    kafka-python's snappy_decode accepts); gzip and zstd raise UnsupportedBatch;
   * control batches (attributes bit 5) carry no user records and are skipped.
 Pure Python, byte at a time: for small cases.
 """
@@ -148,6 +149,78 @@ def lz4_frame_decode(src: bytes) -> bytes:
     return bytes(out)
 
 
+def snappy_block_decode(src: bytes) -> bytes:
+    """One raw snappy block: varint32 length, then literal / copy elements."""
+    n, ip, shift, want = len(src), 0, 0, 0
+    while True:
+        if ip >= n or shift > 28:
+            raise CorruptRecordError("snappy: bad length preamble")
+        b = src[ip]
+        ip += 1
+        want |= (b & 0x7F) << shift
+        if not b & 0x80:
+            break
+        shift += 7
+    out = bytearray()
+    while ip < n:
+        tag = src[ip]
+        ip += 1
+        kind = tag & 3
+        if kind == 0:
+            length = tag >> 2
+            if length >= 60:
+                nb = length - 59
+                if ip + nb > n:
+                    raise CorruptRecordError("snappy: truncated literal length")
+                length = int.from_bytes(src[ip:ip + nb], "little")
+                ip += nb
+            length += 1
+            if ip + length > n:
+                raise CorruptRecordError("snappy: literal runs past the block")
+            out += src[ip:ip + length]
+            ip += length
+            continue
+        if kind == 1:
+            if ip >= n:
+                raise CorruptRecordError("snappy: truncated copy")
+            length, offset = 4 + ((tag >> 2) & 7), ((tag >> 5) << 8) | src[ip]
+            ip += 1
+        else:
+            nb = 2 if kind == 2 else 4
+            if ip + nb > n:
+                raise CorruptRecordError("snappy: truncated copy")
+            length, offset = 1 + (tag >> 2), int.from_bytes(src[ip:ip + nb], "little")
+            ip += nb
+        if offset == 0 or offset > len(out):
+            raise CorruptRecordError("snappy: offset outside the output")
+        start = len(out) - offset
+        for i in range(length):
+            out.append(out[start + i])
+    if len(out) != want:
+        raise CorruptRecordError("snappy: length differs from the preamble")
+    return bytes(out)
+
+
+XERIAL_MAGIC = b"\x82SNAPPY\x00"
+
+
+def snappy_decode(src: bytes) -> bytes:
+    """Raw snappy block, or snappy-java ("xerial") framing: magic, two int32, {int32 length, block}*."""
+    if src[:8] == XERIAL_MAGIC and len(src) >= 16:
+        pos, out = 16, bytearray()
+        while pos < len(src):
+            if pos + 4 > len(src):
+                raise CorruptRecordError("snappy: truncated chunk header")
+            (size,) = struct.unpack_from(">I", src, pos)
+            pos += 4
+            if pos + size > len(src):
+                raise CorruptRecordError("snappy: chunk runs past the batch")
+            out += snappy_block_decode(src[pos:pos + size])
+            pos += size
+        return bytes(out)
+    return snappy_block_decode(src)
+
+
 class Record(NamedTuple):
     partition: int
     offset: int
@@ -177,6 +250,8 @@ def split_blob(blob: bytes, partition: int, fetch_offset: int = 0, offset_delta:
         codec = attributes & 0x07
         if codec == 3:
             body = lz4_frame_decode(bytes(blob[pos + HEADER_BYTES:end]))
+        elif codec == 2:
+            body = snappy_decode(bytes(blob[pos + HEADER_BYTES:end]))
         elif codec:
             raise UnsupportedBatch(f"compression codec {codec}")
         else:

@@ -162,7 +162,7 @@ def test_broken_batches_raise_at_their_batch(damage, status):
     elif damage == "magic":
         bad[16] = 1
     elif damage == "codec":
-        bad = bytearray(rb.encode_batch(4, jvals(4, 8), attributes=2))        # snappy: not built
+        bad = bytearray(rb.encode_batch(4, jvals(4, 8), attributes=1))        # gzip: not built
     elif damage == "null":
         bad = bytearray(rb.encode_batch(4, [jvals(4, 5)[0], None, jvals(6, 7)[0]]))
     elif damage == "varint":                                  # framing broken, CRC recomputed to match
@@ -203,21 +203,25 @@ def test_slot_too_small_is_reported():
 
 
 # ---------------------------------------------------------------- LZ4-compressed batches (§8f-2)
+@pytest.mark.parametrize("codec", [3, "lz4i", "lz4ic", 2, "snappy_raw"])
 @pytest.mark.parametrize("cfg,n,batch_bytes", [(2, 3000, 16384), (2, 3000, 200000), (3, 600, 65536), (5, 20000, 16384)])
-def test_lz4_batches_match_the_oracle(cfg, n, batch_bytes):
-    """cfg2/cfg3: text (matches, several 64 KiB blocks per frame with batch_bytes 200000: dependent
-    blocks); cfg5: random bytes (stored blocks, tiny matches)."""
+def test_compressed_batches_match_the_oracle(cfg, n, batch_bytes, codec):
+    """LZ4 frames with dependent blocks (liblz4's default), with independent blocks and checksums
+    (Kafka's Java client), snappy in xerial framing and raw.  cfg2/cfg3: text (matches; several
+    blocks / chunks per batch with batch_bytes 200000); cfg5: random bytes (stored blocks, tiny
+    matches)."""
     log = syn.make_log(cfg, n, seed=31 + cfg, partitions=8, layout="chunked", chunk=100)
     schema = {2: JsonArray(torch.float32, max_len=256, min_size=32), 3: TokenList(torch.int32, max_len=2048),
               5: RawBytes((64,), torch.uint8)}[cfg]
-    check_raw(log, schema, 128, batch_bytes=batch_bytes, codec=3)
+    check_raw(log, schema, 128, batch_bytes=batch_bytes, codec=codec)
 
 
-def test_lz4_mixed_with_plain_batches_and_long_overlapping_matches():
+@pytest.mark.parametrize("ca,cb", [(3, "lz4i"), (2, "snappy_raw"), ("lz4ic", 2)])
+def test_codecs_mixed_with_plain_batches_and_long_overlapping_matches(ca, cb):
     vals_a = [json.dumps([1.5] * 200).encode() for _ in range(40)]          # one long period-5 match
     vals_b = jvals(0, 50)
-    wide = [json.dumps([float(i % 7)] * 120).encode() for i in range(300)]   # > 64 KiB: window wrap
-    blob = (rb.encode_batch(0, vals_a, codec=3) + rb.encode_batch(40, vals_b) + rb.encode_batch(90, wide, codec=3))
+    wide = [json.dumps([float(i % 7)] * 120).encode() for i in range(300)]   # > 64 KiB of records
+    blob = (rb.encode_batch(0, vals_a, codec=ca) + rb.encode_batch(40, vals_b) + rb.encode_batch(90, wide, codec=cb))
     out, commits = run_blobs([(4, blob, 0, 0)], JsonArray(torch.float32, max_len=256), 64)
     want = [json.loads(v) for v in vals_a + vals_b + wide]
     got = []
@@ -242,6 +246,32 @@ def test_broken_lz4_frames_raise_at_their_batch(damage):
         bad[61 + 7:61 + 11] = (len(bad)).to_bytes(4, "little")      # block longer than the batch
     elif damage == "size":
         bad[-4:] = b"\x01\x00\x00\x00"                              # garbage instead of the end mark
+    bad[17:21] = rb.crc32c(bytes(bad[21:])).to_bytes(4, "big")
+    with pytest.raises(PayloadError) as ei:
+        run_blobs([(1, good + bytes(bad), 0, 0)], JsonArray(torch.float32, max_len=64), 2)
+    assert ei.value.status == 7 and ei.value.partition == 1 and ei.value.offset == 4
+
+
+@pytest.mark.parametrize("damage", ["preamble", "offset", "chunk"])
+def test_broken_snappy_batches_raise_at_their_batch(damage):
+    good = rb.encode_batch(0, jvals(0, 4), codec=2)
+    bad = bytearray(rb.encode_batch(4, [json.dumps([0.5] * 60).encode()] * 4, codec=2))
+    k = 61 + 16 + 4                                  # xerial header, chunk length -> the snappy block
+    if damage == "preamble":
+        bad[k] ^= 0x01                               # announces another length than it decodes to
+    elif damage == "chunk":
+        bad[61 + 16:61 + 20] = (len(bad)).to_bytes(4, "big")
+    elif damage == "offset":
+        pre = 1 if bad[k] < 0x80 else 2
+        tag = bad[k + pre]
+        assert tag & 3 == 0 and (tag >> 2) < 60      # a short literal first, then a copy
+        c = k + pre + 1 + (tag >> 2) + 1
+        assert bad[c] & 3 in (1, 2)
+        if bad[c] & 3 == 1:
+            bad[c] |= 0xE0
+            bad[c + 1] = 0xFF
+        else:
+            bad[c + 1:c + 3] = b"\xff\xff"
     bad[17:21] = rb.crc32c(bytes(bad[21:])).to_bytes(4, "big")
     with pytest.raises(PayloadError) as ei:
         run_blobs([(1, good + bytes(bad), 0, 0)], JsonArray(torch.float32, max_len=64), 2)

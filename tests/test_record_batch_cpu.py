@@ -102,7 +102,7 @@ def test_fetch_offset_partial_tail_control_and_errors():
     with pytest.raises(orb.CorruptRecordError):
         orb.split_blob(bytes(bad), 0)
     with pytest.raises(orb.UnsupportedBatch):
-        orb.split_blob(rb.encode_batch(0, [b"x"], attributes=2), 0)
+        orb.split_blob(rb.encode_batch(0, [b"x"], attributes=1), 0)
     v1 = bytearray(a)
     v1[16] = 1
     with pytest.raises(orb.CorruptRecordError):
@@ -183,3 +183,46 @@ def test_lz4_batches_roundtrip_through_the_oracle():
     want = list(sk.KafkaConsumer("topic", log=log))
     assert [(r.partition, r.offset, r.value) for r in got] == [(r.partition, r.offset, r.value) for r in want]
     assert log.encoded(30000, 3).nbytes < 0.9 * log.encoded(30000).nbytes
+
+
+def test_independent_block_frames_are_valid_lz4_frames():
+    """The stub's Kafka-style frame writer (independent blocks, optional xxHash checksums) against
+    liblz4 itself (pyarrow), which verifies the header and content checksums."""
+    import os
+    import pyarrow as pa
+    rng = random.Random(12)
+    for data in [json_like(rng, 200_000), os.urandom(70_000), b"xyz" * 50_000]:
+        for kw in ({}, {"block_checksum": True, "content_checksum": True}):
+            z = rb.lz4_frame_independent(data, **kw)
+            assert pa.Codec("lz4").decompress(z, decompressed_size=len(data)).to_pybytes() == data
+            assert orb.lz4_frame_decode(z) == data
+
+
+def test_snappy_oracle_decodes_blocks_of_an_independent_compressor():
+    import os
+    rng = random.Random(13)
+    cases = [b"", b"a", os.urandom(100_000), b"abc" * 70_000, b"\x00" * 200_000, json_like(rng, 150_000)]
+    for data in cases:
+        assert orb.snappy_decode(rb.snappy_raw(data)) == data
+        assert orb.snappy_decode(rb.snappy_xerial(data)) == data
+    # format_description.txt: literal "abcd" then a copy of 4 bytes at offset 4 (tag 01, length 4)
+    assert orb.snappy_block_decode(bytes([8, 0x0C]) + b"abcd" + bytes([0x01, 0x04])) == b"abcdabcd"
+    with pytest.raises(orb.CorruptRecordError):
+        orb.snappy_block_decode(bytes([8, 0x0C]) + b"abcd" + bytes([0x01, 0x05]))     # offset before the start
+    with pytest.raises(orb.CorruptRecordError):
+        orb.snappy_block_decode(bytes([9, 0x0C]) + b"abcd" + bytes([0x01, 0x04]))     # length mismatch
+
+
+@pytest.mark.parametrize("codec", [2, "snappy_raw", "lz4i", "lz4ic"])
+def test_compressed_batches_roundtrip_through_the_oracle(codec):
+    log = syn.make_log(2, 200, seed=9, partitions=2, layout="chunked", chunk=50)
+    c = sk.KafkaConsumer("topic", log=log, raw_batch_bytes=100000, raw_codec=codec)
+    got = []
+    while True:
+        f = c.poll_raw(1 << 22, 1000)
+        if f is None:
+            break
+        for p, data, fetch_offset, delta in f.blobs:
+            got += orb.split_blob(bytes(data), p, fetch_offset, delta)
+    want = list(sk.KafkaConsumer("topic", log=log))
+    assert [(r.partition, r.offset, r.value) for r in got] == [(r.partition, r.offset, r.value) for r in want]

@@ -1,0 +1,392 @@
+// tk_codecs.cu -- compressed record batches: LZ4 (attributes & 7 == 3) and
+// snappy (== 2) are decompressed on the device, between the H2D copy of the raw fetch bytes and
+// the record split of tk_recordbatch.cu.
+//
+// Replaces kafka-python's `lz4_decode` / `snappy_decode` (kafka/codec.py, called from
+// DefaultRecordBatch._maybe_uncompress in kafka/record/default_records.py; dependency of the
+// reference, setup.py:9, not in its tree).  Formats: lz4_Frame_format.md and lz4_Block_format.md of
+// the LZ4 project; format_description.txt of snappy and the xerial framing of snappy-java
+// (8-byte magic "\x82SNAPPY\0", two int32, then {int32 length, snappy block} chunks).  The xxHash
+// checksums of LZ4 frames are not verified: the batch's CRC-32C covers the same bytes.
+//
+// Work split:
+//   host    tk_codec_units_host: follows the codec's framing (a few header reads per batch) and
+//           cuts every batch into independently decodable *units*: LZ4 blocks of a
+//           block-independent frame (what Kafka's Java client writes), the whole block chain of a
+//           block-dependent frame (liblz4's default), stored blocks, snappy blocks (xerial chunks)
+//   device  k_unit_size    warp per LZ4 unit: walks the sequences without copying -> decompressed
+//                          size (LZ4 writes it nowhere; snappy blocks start with it)
+//           k_unit_place   one block: exclusive scan of the sizes -> place of every unit and of
+//                          every batch's records in the decompressed buffer
+//           k_unit_decode  warp per unit
+// Decoders: every lane runs the same element parse on bytes fetched by shuffle from a 128-byte
+// window of the compressed stream held by the warp (one coalesced load per ~100 bytes consumed:
+// the fields of an element depend on one another, a cache round trip each would dominate);
+// literals and matches are copied by the whole warp, overlapping matches by repeating the source
+// with period `offset`; matches are read back from the unit's own output through L1.
+#include "tk_rb.h"
+
+// ---------------------------------------------------------------- host: units
+static inline uint32_t cu_le32(const uint8_t* p) {
+    return (uint32_t)p[0] | ((uint32_t)p[1] << 8) | ((uint32_t)p[2] << 16) | ((uint32_t)p[3] << 24);
+}
+static inline uint32_t cu_be32(const uint8_t* p) {
+    return ((uint32_t)p[0] << 24) | ((uint32_t)p[1] << 16) | ((uint32_t)p[2] << 8) | p[3];
+}
+
+struct unit_sink {
+    tk_rb_unit* units;
+    uint32_t max_units, n, batch;
+    bool full;
+    void add(uint32_t src, uint32_t len, uint32_t kind, uint32_t unc_len) {
+        if (n >= max_units) { full = true; return; }
+        tk_rb_unit& u = units[n++];
+        u.src = src; u.src_len = len; u.batch = batch; u.kind = kind; u.unc_len = unc_len; u.out = 0;
+    }
+};
+
+// LZ4 frame at [p, end) -> units; returns a tk_status_t
+static uint32_t lz4_units(const uint8_t* raw, uint32_t p, uint32_t end, unit_sink& sink) {
+    if (end - p < 7u || cu_le32(raw + p) != 0x184D2204u) return TK_STATUS_CORRUPT;
+    const uint32_t flg = raw[p + 4];
+    if ((flg >> 6) != 1u) return TK_STATUS_CORRUPT;
+    if (flg & 1u) return TK_STATUS_UNSUPPORTED;                              // dictionary
+    const bool independent = flg & 0x20u, block_checksum = flg & 0x10u, content_checksum = flg & 0x04u;
+    p += 6u + ((flg & 0x08u) ? 8u : 0u) + 1u;                                // content size, header checksum
+    if (p > end) return TK_STATUS_CORRUPT;
+    if (!independent) {
+        // blocks may refer to the output of earlier blocks: one unit decodes the chain in order
+        sink.add(p, end - p, RB_UNIT_LZ4_CHAIN | (block_checksum ? RB_UNIT_BLOCK_CHECKSUM : 0u) |
+                                 (content_checksum ? RB_UNIT_CONTENT_CHECKSUM : 0u), 0);
+        return TK_STATUS_OK;
+    }
+    for (;;) {
+        if (end - p < 4u) return TK_STATUS_CORRUPT;
+        uint32_t size = cu_le32(raw + p);
+        p += 4;
+        if (size == 0) break;
+        const bool stored = size >> 31;
+        size &= 0x7FFFFFFFu;
+        if (size > end - p) return TK_STATUS_CORRUPT;
+        if (stored) sink.add(p, size, RB_UNIT_STORED | RB_UNIT_SIZED, size);
+        else sink.add(p, size, RB_UNIT_LZ4_BLOCK, 0);
+        p += size + (block_checksum ? 4u : 0u);
+        if (p > end) return TK_STATUS_CORRUPT;
+    }
+    return p + (content_checksum ? 4u : 0u) == end ? TK_STATUS_OK : TK_STATUS_CORRUPT;
+}
+
+// decompressed length a snappy block announces (varint32 preamble); false if malformed
+static bool snappy_preamble(const uint8_t* raw, uint32_t p, uint32_t end, uint32_t* len) {
+    uint64_t v = 0;
+    for (int shift = 0; shift < 35; shift += 7) {
+        if (p >= end) return false;
+        const uint32_t b = raw[p++];
+        v |= (uint64_t)(b & 0x7Fu) << shift;
+        if (!(b & 0x80u)) { *len = (uint32_t)v; return v <= 0x7FFFFFFFull; }
+    }
+    return false;
+}
+
+static uint32_t snappy_units(const uint8_t* raw, uint32_t p, uint32_t end, unit_sink& sink) {
+    static const uint8_t magic[8] = {0x82, 'S', 'N', 'A', 'P', 'P', 'Y', 0};
+    uint32_t len;
+    if (end - p >= 16u && memcmp(raw + p, magic, 8) == 0) {                   // xerial framing
+        p += 16;
+        while (p < end) {
+            if (end - p < 4u) return TK_STATUS_CORRUPT;
+            const uint32_t size = cu_be32(raw + p);
+            p += 4;
+            if (size > end - p || !snappy_preamble(raw, p, p + size, &len)) return TK_STATUS_CORRUPT;
+            sink.add(p, size, RB_UNIT_SNAPPY | RB_UNIT_SIZED, len);
+            p += size;
+        }
+        return TK_STATUS_OK;
+    }
+    if (!snappy_preamble(raw, p, end, &len)) return TK_STATUS_CORRUPT;
+    sink.add(p, end - p, RB_UNIT_SNAPPY | RB_UNIT_SIZED, len);
+    return TK_STATUS_OK;
+}
+
+int tk_codec_units_host(const uint8_t* raw, tk_rb_batch& b, uint32_t batch_index, tk_rb_unit* units,
+                        uint32_t max_units, uint32_t* n_units) {
+    unit_sink sink = {units, max_units, *n_units, batch_index, false};
+    const uint32_t first = sink.n;
+    const uint32_t status = b.codec == 3u ? lz4_units(raw, b.start + RB_HEADER, b.end, sink)
+                                          : snappy_units(raw, b.start + RB_HEADER, b.end, sink);
+    TK_REQUIRE(!sink.full, "more compressed blocks in the slot than the unit table holds (%u)", max_units);
+    if (status) {
+        b.status = status;
+        sink.n = first;
+    }
+    b.unit_first = first;
+    b.unit_count = sink.n - first;
+    *n_units = sink.n;
+    return 0;
+}
+
+// ---------------------------------------------------------------- device: the shuffled window
+struct cz_window {
+    const uint8_t* raw;
+    uint32_t at;          // position of the window's first byte (multiple of 4)
+    uint32_t word;        // this lane's 4 bytes
+};
+__device__ __forceinline__ void cz_load(cz_window& w, uint32_t pos, uint32_t lane) {
+    w.at = pos & ~3u;
+    w.word = *reinterpret_cast<const uint32_t*>(w.raw + w.at + 4u * lane);    // inside the padded buffer
+}
+// byte at `pos` (same in every lane)
+__device__ __forceinline__ uint32_t cz_byte(cz_window& w, uint32_t pos, uint32_t lane) {
+    if (pos - w.at >= 128u) cz_load(w, pos, lane);
+    const uint32_t j = pos - w.at;
+    return (__shfl_sync(0xffffffffu, w.word, j >> 2) >> ((j & 3u) * 8u)) & 0xFFu;
+}
+// out[op, op + n) = raw[from, from + n): from the window when it holds them, else from memory
+__device__ __forceinline__ void cz_literals(cz_window& w, uint32_t lane, uint32_t from, uint32_t n, uint8_t* out,
+                                            uint32_t op) {
+    if (n <= 32u && from - w.at + 32u <= 128u) {
+        const uint32_t j = from - w.at + lane;
+        const uint8_t v = (uint8_t)(__shfl_sync(0xffffffffu, w.word, (j >> 2) & 31u) >> ((j & 3u) * 8u));
+        if (lane < n) out[op + lane] = v;
+    } else {
+        for (uint32_t k = lane; k < n; k += 32) out[op + k] = w.raw[from + k];
+    }
+}
+// out[op + k] = out[op - offset + k], k < n.  Where the match overlaps its own output the source
+// repeats with period `offset`, so every byte comes from before `op`: the lanes never read what
+// this match writes.  The bytes were written by other lanes of this warp: __syncwarp orders them,
+// and they are read back through the L1 of the same SM (the region belongs to this warp alone).
+__device__ __forceinline__ void cz_match(uint8_t* out, uint32_t op, uint32_t offset, uint32_t n, uint32_t lane) {
+    __syncwarp();
+    for (uint32_t k = lane; k < n; k += 32) out[op + k] = out[op - offset + (offset >= n ? k : k % offset)];
+    __syncwarp();
+}
+
+// ---------------------------------------------------------------- LZ4
+// length with its 255-extension bytes; false if it runs past `end`
+__device__ __forceinline__ bool lz4_length(cz_window& w, uint32_t lane, uint32_t& p, uint32_t end, uint32_t nibble,
+                                           uint32_t& len) {
+    len = nibble;
+    if (nibble == 15u) {
+        uint32_t b;
+        do {
+            if (p >= end) return false;
+            b = cz_byte(w, p++, lane);
+            len += b;
+            if (len > 0x7FFFFFFFu) return false;
+        } while (b == 255u);
+    }
+    return true;
+}
+
+// The sequences of one block [p, bend).  EMIT = false: only counts (op advances); EMIT = true: writes
+// out[op...] (capacity cap); matches may reach back to out[window].
+template <bool EMIT>
+__device__ __forceinline__ uint32_t lz4_block_run(cz_window& w, uint32_t lane, uint32_t p, uint32_t bend, uint8_t* out,
+                                                  uint32_t cap, uint32_t window, uint32_t& op) {
+    while (p < bend) {
+        const uint32_t token = cz_byte(w, p, lane);
+        uint32_t lit, lit_at = p + 1;
+        if (!lz4_length(w, lane, lit_at, bend, token >> 4, lit) || lit > bend - lit_at) return TK_STATUS_CORRUPT;
+        if (lit > cap - op) return EMIT ? TK_STATUS_CORRUPT : TK_STATUS_UNSUPPORTED;
+        if (EMIT) cz_literals(w, lane, lit_at, lit, out, op);
+        op += lit;
+        p = lit_at + lit;
+        if (p >= bend) break;                                 // the last sequence has no match
+        if (bend - p < 2u) return TK_STATUS_CORRUPT;
+        const uint32_t offset = cz_byte(w, p, lane) | (cz_byte(w, p + 1, lane) << 8);
+        p += 2;
+        uint32_t mlen;
+        if (!lz4_length(w, lane, p, bend, token & 15u, mlen)) return TK_STATUS_CORRUPT;
+        mlen += 4u;
+        if (offset == 0 || offset > op - window) return TK_STATUS_CORRUPT;
+        if (mlen > cap - op) return EMIT ? TK_STATUS_CORRUPT : TK_STATUS_UNSUPPORTED;
+        if (EMIT) cz_match(out, op, offset, mlen, lane);
+        op += mlen;
+    }
+    return TK_STATUS_OK;
+}
+
+// The block chain of a block-dependent frame: {u32 size, data, [checksum]} ... end mark, [checksum]
+template <bool EMIT>
+__device__ __forceinline__ uint32_t lz4_chain_run(cz_window& w, uint32_t lane, uint32_t p, uint32_t end, uint32_t kind,
+                                                  uint8_t* out, uint32_t cap, uint32_t& op) {
+    for (;;) {
+        if (end - p < 4u) return TK_STATUS_CORRUPT;
+        uint32_t size = cz_byte(w, p, lane) | (cz_byte(w, p + 1, lane) << 8) | (cz_byte(w, p + 2, lane) << 16) |
+                        (cz_byte(w, p + 3, lane) << 24);
+        p += 4;
+        if (size == 0) break;
+        const bool stored = size >> 31;
+        size &= 0x7FFFFFFFu;
+        if (size > end - p) return TK_STATUS_CORRUPT;
+        if (stored) {
+            if (size > cap - op) return EMIT ? TK_STATUS_CORRUPT : TK_STATUS_UNSUPPORTED;
+            if (EMIT) {
+                for (uint32_t k = lane; k < size; k += 32) out[op + k] = w.raw[p + k];
+                __syncwarp();
+            }
+            op += size;
+        } else {
+            const uint32_t st = lz4_block_run<EMIT>(w, lane, p, p + size, out, cap, 0u, op);
+            if (st) return st;
+        }
+        p += size + ((kind & RB_UNIT_BLOCK_CHECKSUM) ? 4u : 0u);
+        if (p > end) return TK_STATUS_CORRUPT;
+    }
+    return p + ((kind & RB_UNIT_CONTENT_CHECKSUM) ? 4u : 0u) == end ? TK_STATUS_OK : TK_STATUS_CORRUPT;
+}
+
+// ---------------------------------------------------------------- snappy
+// One block: varint32 length, then elements; tag & 3: 0 literal (length - 1 in the upper 6 bits, 60..63:
+// in the next 1..4 bytes), 1 copy (length 4..11, 11-bit offset), 2 copy (length 1..64, 16-bit offset),
+// 3 copy (32-bit offset).
+__device__ __forceinline__ uint32_t snappy_run(cz_window& w, uint32_t lane, uint32_t p, uint32_t end, uint8_t* out,
+                                               uint32_t cap, uint32_t& op) {
+    uint32_t b;
+    do {                                                    // preamble (validated on the host)
+        if (p >= end) return TK_STATUS_CORRUPT;
+        b = cz_byte(w, p++, lane);
+    } while (b & 0x80u);
+    while (p < end) {
+        const uint32_t tag = cz_byte(w, p++, lane);
+        if ((tag & 3u) == 0u) {
+            uint32_t len = tag >> 2;
+            if (len >= 60u) {
+                const uint32_t nb = len - 59u;
+                if (end - p < nb) return TK_STATUS_CORRUPT;
+                len = 0;
+                for (uint32_t k = 0; k < nb; ++k) len |= cz_byte(w, p + k, lane) << (8u * k);
+                p += nb;
+            }
+            if (len >= 0x7FFFFFFFu) return TK_STATUS_CORRUPT;
+            len += 1u;
+            if (len > end - p || len > cap - op) return TK_STATUS_CORRUPT;
+            cz_literals(w, lane, p, len, out, op);
+            op += len;
+            p += len;
+        } else {
+            uint32_t len, offset;
+            if ((tag & 3u) == 1u) {
+                if (p >= end) return TK_STATUS_CORRUPT;
+                len = 4u + ((tag >> 2) & 7u);
+                offset = ((tag >> 5) << 8) | cz_byte(w, p, lane);
+                p += 1;
+            } else if ((tag & 3u) == 2u) {
+                if (end - p < 2u) return TK_STATUS_CORRUPT;
+                len = 1u + (tag >> 2);
+                offset = cz_byte(w, p, lane) | (cz_byte(w, p + 1, lane) << 8);
+                p += 2;
+            } else {
+                if (end - p < 4u) return TK_STATUS_CORRUPT;
+                len = 1u + (tag >> 2);
+                offset = cz_byte(w, p, lane) | (cz_byte(w, p + 1, lane) << 8) | (cz_byte(w, p + 2, lane) << 16) |
+                         (cz_byte(w, p + 3, lane) << 24);
+                p += 4;
+            }
+            if (offset == 0 || offset > op || len > cap - op) return TK_STATUS_CORRUPT;
+            cz_match(out, op, offset, len, lane);
+            op += len;
+        }
+    }
+    return TK_STATUS_OK;
+}
+
+// ---------------------------------------------------------------- kernels
+__global__ void __launch_bounds__(256) k_unit_size(const rb_args a) {
+    const uint32_t lane = threadIdx.x & 31;
+    const uint32_t warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, nwarps = (gridDim.x * blockDim.x) >> 5;
+    for (uint32_t i = warp; i < a.n_units; i += nwarps) {
+        const tk_rb_unit u = a.units[i];
+        if (u.kind & RB_UNIT_SIZED) continue;
+        cz_window w;
+        w.raw = a.raw;
+        cz_load(w, u.src, lane);
+        uint32_t op = 0, st;
+        if ((u.kind & 0xFFu) == RB_UNIT_LZ4_BLOCK)
+            st = lz4_block_run<false>(w, lane, u.src, u.src + u.src_len, nullptr, 0x7FFFFFFFu, 0u, op);
+        else
+            st = lz4_chain_run<false>(w, lane, u.src, u.src + u.src_len, u.kind, nullptr, 0x7FFFFFFFu, op);
+        if (lane == 0) {
+            a.units[i].unc_len = st ? 0u : op;
+            if (st) a.units[i].kind = u.kind | RB_UNIT_FAILED;
+        }
+    }
+}
+
+// One block: place of every unit (exclusive scan of the sizes), then of every batch's records.
+__global__ void __launch_bounds__(1024) k_unit_place(const rb_args a) {
+    __shared__ unsigned long long warp_tot[32];
+    __shared__ unsigned long long s_total, s_run;
+    const uint32_t t = threadIdx.x;
+    if (t == 0) s_run = 0;
+    __syncthreads();
+    for (uint32_t base = 0; base < a.n_units; base += blockDim.x) {
+        const uint32_t i = base + t;
+        const unsigned long long v = i < a.n_units ? a.units[i].unc_len : 0ull;
+        const unsigned long long excl = s_run + rb_block_scan(v, warp_tot, &s_total);
+        // (past the buffer: the batch is rejected below, the unit is never decoded)
+        if (i < a.n_units) a.units[i].out = (uint32_t)min(excl, 0xFFFFFFFFull);
+        __syncthreads();
+        if (t == 0) s_run += s_total;
+        __syncthreads();
+    }
+    for (uint32_t i = t; i < a.n_batches; i += blockDim.x) {
+        tk_rb_batch& b = a.batches[i];
+        if (b.status || !b.codec || !b.unit_count) {
+            if (!b.status && b.codec) { b.rec_start = 0; b.rec_end = 0; }     // a frame without blocks
+            continue;
+        }
+        unsigned long long total = 0;
+        bool failed = false;
+        for (uint32_t k = 0; k < b.unit_count; ++k) {
+            const tk_rb_unit u = a.units[b.unit_first + k];
+            failed |= (u.kind & RB_UNIT_FAILED) != 0;
+            total += u.unc_len;
+        }
+        const unsigned long long first = a.units[b.unit_first].out;
+        if (failed) b.status = TK_STATUS_CORRUPT;
+        else if (first + total > a.slot_bytes) b.status = TK_STATUS_UNSUPPORTED;   // does not fit the slot
+        else { b.rec_start = (uint32_t)first; b.rec_end = (uint32_t)(first + total); }
+    }
+}
+
+__global__ void __launch_bounds__(128) k_unit_decode(const rb_args a) {
+    const uint32_t lane = threadIdx.x & 31;
+    const uint32_t warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, nwarps = (gridDim.x * blockDim.x) >> 5;
+    for (uint32_t i = warp; i < a.n_units; i += nwarps) {
+        const tk_rb_unit u = a.units[i];
+        if (a.batches[u.batch].status) continue;           // rejected by the size pass or the placement
+        uint8_t* out = a.raw2 + u.out;
+        const uint32_t kind = u.kind & 0xFFu;
+        uint32_t op = 0, st = TK_STATUS_OK;
+        if (kind == RB_UNIT_STORED) {
+            for (uint32_t k = lane; k < u.src_len; k += 32) out[k] = a.raw[u.src + k];
+            op = u.src_len;
+        } else {
+            cz_window w;
+            w.raw = a.raw;
+            cz_load(w, u.src, lane);
+            if (kind == RB_UNIT_LZ4_BLOCK) st = lz4_block_run<true>(w, lane, u.src, u.src + u.src_len, out, u.unc_len, 0u, op);
+            else if (kind == RB_UNIT_LZ4_CHAIN) st = lz4_chain_run<true>(w, lane, u.src, u.src + u.src_len, u.kind, out, u.unc_len, op);
+            else st = snappy_run(w, lane, u.src, u.src + u.src_len, out, u.unc_len, op);
+        }
+        if (!st && op != u.unc_len) st = TK_STATUS_CORRUPT;
+        // (k_rb_check runs behind this kernel and turns the status into the batch's error entry)
+        if (st && lane == 0) a.batches[u.batch].status = TK_STATUS_CORRUPT;
+    }
+}
+
+int tk_codec_launch(const rb_args& a, cudaStream_t stream) {
+    if (!a.n_units) {
+        // compressed batches without a single block: their (empty) record ranges still need setting
+        k_unit_place<<<1, 1024, 0, stream>>>(a);
+        TK_LAUNCH_CHECK();
+        return 0;
+    }
+    k_unit_size<<<min((a.n_units + 7) / 8, 148u * 8u), 256, 0, stream>>>(a);
+    k_unit_place<<<1, 1024, 0, stream>>>(a);
+    k_unit_decode<<<min((a.n_units + 3) / 4, 148u * 16u), 128, 0, stream>>>(a);
+    TK_LAUNCH_CHECK();
+    return 0;
+}

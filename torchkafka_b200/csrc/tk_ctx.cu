@@ -157,8 +157,9 @@ static void free_slot(tk_slot& s) {
     if (s.h_recs) cudaFreeHost(s.h_recs);
     if (s.h_block) cudaFreeHost(s.h_block);
     if (s.h_rb_batches) cudaFreeHost(s.h_rb_batches);
+    if (s.h_rb_units) cudaFreeHost(s.h_rb_units);
     if (s.h_rb_summary) cudaFreeHost(s.h_rb_summary);
-    cudaFree(s.d.raw); cudaFree(s.d.raw2); cudaFree(s.d.rb_batches); cudaFree(s.d.rb_summary); cudaFree(s.d.rb_temp); cudaFree(s.d.rb_bigq);
+    cudaFree(s.d.raw); cudaFree(s.d.raw2); cudaFree(s.d.rb_batches); cudaFree(s.d.rb_units); cudaFree(s.d.rb_summary); cudaFree(s.d.rb_temp); cudaFree(s.d.rb_bigq);
     cudaFree(s.d.bytes); cudaFree(s.d.recs); cudaFree(s.d.rec_len); cudaFree(s.d.rec_status);
     cudaFree(s.d.rec_kidx); cudaFree(s.d.tile_agg); cudaFree(s.d.tile_incl); cudaFree(s.d.tile_flag);
     cudaFree(s.d.plan_ctr); cudaFree(s.d.block);

@@ -44,11 +44,13 @@ struct tk_rb_batch {
     uint32_t value_bytes;      // bytes the batch contributes to the slot
     uint32_t rec_base;         // first record / first value byte of the batch in the slot
     uint32_t byte_base;
-    uint32_t codec;            // attributes & 7: 0 plain, 3 LZ4 (decompressed on the device), others unsupported
+    uint32_t codec;            // attributes & 7: 0 plain, 2 snappy / 3 LZ4 (decompressed on the device), others unsupported
     uint32_t rec_start, rec_end;   // the records: [start + 61, end) of the raw bytes, or the batch's
                                    // region of the decompressed buffer
-    uint32_t unc_bytes;        // decompressed size of the records (codec != 0)
+    uint32_t unit_first, unit_count;   // its decompression units (tk_rb.h)
+    uint32_t reserved;
 };
+struct tk_rb_unit;
 
 // Per-slot device scratch ("plan"): everything the kernels hand to one another.
 struct tk_slot_dev {
@@ -73,6 +75,7 @@ struct tk_slot_dev {
     uint8_t*     raw;          // [slot_bytes + pad]
     uint8_t*     raw2;         // [slot_bytes + pad] decompressed records of compressed batches (first use)
     tk_rb_batch* rb_batches;   // [slot_records]
+    tk_rb_unit*  rb_units;     // decompression units (first compressed batch)
     tk_rb_summary_t* rb_summary;
     uint4*       rb_temp;      // [slot_records] per-record copy descriptors
     uint32_t*    rb_bigq;      // records copied piecewise
@@ -101,6 +104,7 @@ struct tk_slot {
     cudaEvent_t  ev_result;   // result block is in pinned memory
     cudaEvent_t  ev_raw;      // raw record-batch bytes landed (created with the raw buffers)
     tk_rb_batch* h_rb_batches;   // pinned, [slot_records]: written by the host's header walk
+    tk_rb_unit*  h_rb_units;     // pinned: decompression units of compressed batches
     tk_rb_summary_t* h_rb_summary;   // pinned
     cudaEvent_t  ev_dec0, ev_dec1;   // timing events around the decode / collate kernels (tk_ctx_set_timing)
     bool         dec_timed;

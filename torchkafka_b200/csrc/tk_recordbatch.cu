@@ -22,8 +22,9 @@
 //   k_rb_copy     warp per record: the value moves to its place in the slot's byte buffer (aligned
 //                 destination words, funnel-shifted source); values above 16 KiB are queued and
 //                 copied in 4 KiB pieces by all warps (k_rb_copy_big)
-// Big-endian header fields, zig-zag varints.  Uncompressed batches only (codecs: SURVEY §8f-2).
-#include "tk_internal.h"
+// Big-endian header fields, zig-zag varints.  LZ4 and snappy batches are decompressed first
+// (tk_codecs.cu); gzip and zstd batches are reported as unsupported.
+#include "tk_rb.h"
 #include <mutex>
 
 // ---------------------------------------------------------------- CRC-32C tables
@@ -59,8 +60,6 @@ extern "C" uint32_t tk_crc32c(const void* data, uint64_t n, uint32_t crc) {
 }
 
 // ---------------------------------------------------------------- device helpers
-#define RB_HEADER 61u
-#define RB_CRC_FROM 21u
 
 __device__ __forceinline__ uint32_t rb_be32(const uint8_t* p) {
     return ((uint32_t)p[0] << 24) | ((uint32_t)p[1] << 16) | ((uint32_t)p[2] << 8) | p[3];
@@ -84,22 +83,6 @@ __device__ __forceinline__ bool rb_varint(const uint8_t* raw, uint32_t& p, uint3
     return false;
 }
 
-#define RB_SRC2 0x80000000u       // copy descriptor: the value lies in the decompressed buffer
-
-struct rb_args {
-    const uint8_t*   raw;
-    uint8_t*         raw2;            // decompressed records of compressed batches
-    tk_rb_batch*     batches;
-    uint32_t         n_batches, n_records;    // from the host's header walk
-    tk_rb_summary_t* summary;
-    uint4*           temp;            // [slot_records] per-record copy descriptors (rb_temp)
-    uint32_t*        bigq;            // records longer than RB_BIG, copied piecewise by k_rb_copy_big
-    uint8_t*         bytes;           // slot byte buffer (destination)
-    tk_rec_t*        recs;            // slot record headers (destination)
-    uint32_t         slot_records;
-    uint64_t         slot_bytes;
-};
-
 // ---------------------------------------------------------------- batch headers (host)
 // The chain of batch headers of a blob is followed on the host, in tk_slot_submit_recordbatches:
 // it is one dependent read per batch (tens of kilobytes apart) of memory the host has just
@@ -117,9 +100,10 @@ static inline uint32_t rb_host_be32(const uint8_t* p) {
 }
 static int rb_walk_host(const uint8_t* raw, const tk_blob_t* blobs, uint32_t n_blobs, tk_rb_batch* out,
                         uint32_t max_batches, uint32_t max_records, uint32_t* n_batches_out, uint32_t* n_records_out,
-                        uint32_t* n_lz4_out) {
+                        tk_rb_unit* units, uint32_t max_units, uint32_t* n_units_out, uint32_t* n_coded_out) {
     uint32_t nb = 0;
-    *n_lz4_out = 0;
+    *n_units_out = 0;
+    *n_coded_out = 0;
     uint64_t nrec = 0;
     for (uint32_t t = 0; t < n_blobs; ++t) {
         const tk_blob_t& blob = blobs[t];
@@ -136,10 +120,10 @@ static int rb_walk_host(const uint8_t* raw, const tk_blob_t* blobs, uint32_t n_b
                 const uint32_t magic = raw[pos + 16];
                 const uint32_t c = rb_host_be32(raw + pos + 57);
                 codec = raw[pos + 22] & 7u;
-                // a record is at least 7 bytes (LZ4 expands at most 255-fold): a larger count cannot
+                // a record is at least 7 bytes (the codecs expand at most ~255-fold): a larger count cannot
                 // be true (the checksum would say so too, but the count sizes the slot before the
                 // checksum is looked at)
-                const uint64_t room = (uint64_t)(end - pos - RB_HEADER) * (codec == 3 ? 255u : 1u);
+                const uint64_t room = (uint64_t)(end - pos - RB_HEADER) * (codec ? 255u : 1u);
                 if (magic != 2) { status = TK_STATUS_CORRUPT; end = blob_end; }
                 else if (c > room / 7u + 1u) status = TK_STATUS_CORRUPT;
                 else count = c;
@@ -155,8 +139,13 @@ static int rb_walk_host(const uint8_t* raw, const tk_blob_t* blobs, uint32_t n_b
             b.base_offset = base;
             b.fetch_offset = blob.fetch_offset;
             b.n_rec = count; b.value_bytes = 0; b.rec_base = (uint32_t)nrec; b.byte_base = 0;
-            b.codec = status ? 0u : codec; b.rec_start = pos + RB_HEADER; b.rec_end = end; b.unc_bytes = 0;
-            if (b.codec == 3) ++*n_lz4_out;
+            b.codec = status ? 0u : codec; b.rec_start = pos + RB_HEADER; b.rec_end = end;
+            b.unit_first = 0; b.unit_count = 0; b.reserved = 0;
+            if (b.codec == 2u || b.codec == 3u) {            // snappy, LZ4: cut into decodable units
+                ++*n_coded_out;
+                const int rc = tk_codec_units_host(raw, b, nb - 1, units, max_units, n_units_out);
+                if (rc) return rc;
+            }
             nrec += count;
             TK_REQUIRE(nrec <= max_records, "more records in the slot than slot_records (%u)", max_records);
             pos = end;
@@ -165,33 +154,6 @@ static int rb_walk_host(const uint8_t* raw, const tk_blob_t* blobs, uint32_t n_b
     *n_batches_out = nb;
     *n_records_out = (uint32_t)nrec;
     return 0;
-}
-
-// exclusive scan of one packed (batches << 40 | records) value per thread of a 1024-thread block
-__device__ __forceinline__ unsigned long long rb_block_scan(unsigned long long v, unsigned long long* warp_tot,
-                                                            unsigned long long* total) {
-    const uint32_t t = threadIdx.x, lane = t & 31;
-    unsigned long long incl = v;
-#pragma unroll
-    for (int d = 1; d < 32; d <<= 1) {
-        const unsigned long long o = __shfl_up_sync(0xffffffffu, incl, d);
-        if (lane >= (uint32_t)d) incl += o;
-    }
-    if (lane == 31) warp_tot[t >> 5] = incl;
-    __syncthreads();
-    if (t < 32) {
-        const unsigned long long w = warp_tot[t];
-        unsigned long long wi = w;
-#pragma unroll
-        for (int d = 1; d < 32; d <<= 1) {
-            const unsigned long long o = __shfl_up_sync(0xffffffffu, wi, d);
-            if (t >= (uint32_t)d) wi += o;
-        }
-        warp_tot[t] = wi - w;
-        if (t == 31) *total = wi;
-    }
-    __syncthreads();
-    return warp_tot[t >> 5] + incl - v;
 }
 
 // ---------------------------------------------------------------- CRC-32C on the device
@@ -359,11 +321,11 @@ __global__ void __launch_bounds__(256) k_rb_check(const rb_args a) {
         if (!status) {
             const uint32_t attributes = ((uint32_t)a.raw[b.start + 21] << 8) | a.raw[b.start + 22];
             control = attributes & 0x20u;
-            if (b.codec != 0u && b.codec != 3u) status = TK_STATUS_UNSUPPORTED;  // gzip, snappy, zstd
+            if (b.codec != 0u && b.codec != 2u && b.codec != 3u) status = TK_STATUS_UNSUPPORTED;  // gzip, zstd
         }
-        // the records: behind the header, or (LZ4) in the batch's region of the decompressed buffer
-        const uint8_t* rbase = b.codec == 3u ? a.raw2 : a.raw;
-        const uint32_t rend = b.rec_end, src_flag = b.codec == 3u ? RB_SRC2 : 0u;
+        // the records: behind the header, or (compressed) in the batch's region of the decompressed buffer
+        const uint8_t* rbase = b.codec ? a.raw2 : a.raw;
+        const uint32_t rend = b.rec_end, src_flag = b.codec ? RB_SRC2 : 0u;
         uint32_t p = b.rec_start;                                                // lane 0's cursor
         for (uint32_t k0 = 0; !status && k0 < b.n_rec; k0 += 32) {
             const uint32_t m = min(32u, b.n_rec - k0);
@@ -535,214 +497,11 @@ __global__ void __launch_bounds__(256) k_rb_copy_big(const rb_args a) {
     }
 }
 
-// ---------------------------------------------------------------- LZ4
-// Compressed batches (attributes & 7 == 3) hold one LZ4 frame behind the 61-byte header
-// (lz4_Frame_format.md: magic, FLG, BD, [content size], [dictionary id], header checksum, blocks
-// {u32 size, data, [checksum]}, end mark, [content checksum]; blocks per lz4_Block_format.md).
-// Replaces kafka-python's `lz4_decode` (kafka/codec.py, called from DefaultRecordBatch
-// ._maybe_uncompress).  The xxHash checksums are not verified: the batch's CRC-32C covers the same
-// bytes.  Two passes, because the decompressed size is written nowhere:
-//   k_lz4_size    warp per batch: walks the sequences without copying -> decompressed size
-//   k_lz4_prefix  one block: places every batch's records in the decompressed buffer
-//   k_lz4_decode  warp per batch: every lane parses the sequences out of a shuffled 128-byte window
-//                 of the compressed bytes, the warp copies literals and matches;
-//                 matches are read back from the batch's own output through L1.  Frames with
-//                 dependent blocks decode in order by construction.
-
-struct lz4_frame {
-    uint32_t pos;          // first block header
-    bool independent, block_checksum, content_checksum;
-};
-// header of the frame at [p, end); false if it is not a frame this decoder handles
-__device__ __forceinline__ bool lz4_frame_header(const uint8_t* raw, uint32_t p, uint32_t end, lz4_frame& f, uint32_t& status) {
-    if (end - p < 7u || raw[p] != 0x04 || raw[p + 1] != 0x22 || raw[p + 2] != 0x4D || raw[p + 3] != 0x18) {
-        status = TK_STATUS_CORRUPT; return false;
-    }
-    const uint32_t flg = raw[p + 4];
-    if ((flg >> 6) != 1u) { status = TK_STATUS_CORRUPT; return false; }
-    if (flg & 1u) { status = TK_STATUS_UNSUPPORTED; return false; }        // dictionary
-    f.independent = flg & 0x20u; f.block_checksum = flg & 0x10u; f.content_checksum = flg & 0x04u;
-    f.pos = p + 6u + ((flg & 0x08u) ? 8u : 0u) + 1u;
-    if (f.pos > end) { status = TK_STATUS_CORRUPT; return false; }
-    return true;
-}
-__device__ __forceinline__ uint32_t lz4_le32(const uint8_t* p) {
-    return (uint32_t)p[0] | ((uint32_t)p[1] << 8) | ((uint32_t)p[2] << 16) | ((uint32_t)p[3] << 24);
-}
-// The compressed bytes are read through a 128-byte window held by the warp (4 bytes per lane, one
-// coalesced load per ~100 bytes consumed): a sequence is 5-10 bytes long and its fields depend on
-// one another, so reading them from memory one at a time would cost a cache round trip each.
-// Every lane runs the same parse on bytes fetched by shuffle; nothing is broadcast from a leader.
-struct lz4_window {
-    const uint8_t* raw;
-    uint32_t at;          // position of the window's first byte (multiple of 4)
-    uint32_t word;        // this lane's 4 bytes
-};
-__device__ __forceinline__ void lz4_window_load(lz4_window& w, uint32_t pos, uint32_t lane) {
-    w.at = pos & ~3u;
-    w.word = *reinterpret_cast<const uint32_t*>(w.raw + w.at + 4u * lane);    // inside the padded buffer
-}
-// byte at `pos` (same in every lane)
-__device__ __forceinline__ uint32_t lz4_byte(lz4_window& w, uint32_t pos, uint32_t lane) {
-    if (pos - w.at >= 128u) lz4_window_load(w, pos, lane);
-    const uint32_t j = pos - w.at;
-    return (__shfl_sync(0xffffffffu, w.word, j >> 2) >> ((j & 3u) * 8u)) & 0xFFu;
-}
-// length with its 255-extension bytes; false if it runs past `end`
-__device__ __forceinline__ bool lz4_length(lz4_window& w, uint32_t lane, uint32_t& p, uint32_t end, uint32_t nibble,
-                                           uint32_t& len) {
-    len = nibble;
-    if (nibble == 15u) {
-        uint32_t b;
-        do {
-            if (p >= end) return false;
-            b = lz4_byte(w, p++, lane);
-            len += b;
-            if (len > 0x7FFFFFFFu) return false;
-        } while (b == 255u);
-    }
-    return true;
-}
-
-// One frame, whole warp.  EMIT = false: only the decompressed size is computed (*out_size);
-// EMIT = true: the bytes are written to `out` (capacity `cap`).
-template <bool EMIT>
-__device__ __forceinline__ uint32_t lz4_frame_run(const uint8_t* raw, uint32_t start, uint32_t end, uint32_t lane,
-                                                  uint8_t* out, uint32_t cap, uint64_t* out_size) {
-    uint32_t status = TK_STATUS_OK;
-    lz4_frame f;
-    if (!lz4_frame_header(raw, start, end, f, status)) return status;
-    lz4_window w;
-    w.raw = raw;
-    uint32_t p = f.pos;
-    lz4_window_load(w, p, lane);
-    uint64_t total = 0;
-    uint32_t op = 0;
-    for (;;) {
-        if (end - p < 4u) return TK_STATUS_CORRUPT;
-        uint32_t size = lz4_byte(w, p, lane) | (lz4_byte(w, p + 1, lane) << 8) | (lz4_byte(w, p + 2, lane) << 16) |
-                        (lz4_byte(w, p + 3, lane) << 24);
-        p += 4;
-        if (size == 0) break;
-        const bool stored = size >> 31;
-        size &= 0x7FFFFFFFu;
-        if (size > end - p) return TK_STATUS_CORRUPT;
-        const uint32_t bend = p + size;
-        const uint32_t window = f.independent ? op : 0u;             // matches reach back to here
-        if (stored) {
-            total += size;
-            if (EMIT) {
-                if (size > cap - op) return TK_STATUS_CORRUPT;
-                for (uint32_t k = lane; k < size; k += 32) {
-                    out[op + k] = raw[p + k];
-                }
-                op += size;
-                __syncwarp();
-            }
-        } else {
-            while (p < bend) {
-                const uint32_t token = lz4_byte(w, p, lane);
-                uint32_t lit, lit_at = p + 1;
-                if (!lz4_length(w, lane, lit_at, bend, token >> 4, lit) || lit > bend - lit_at) return TK_STATUS_CORRUPT;
-                total += lit;
-                if (EMIT) {
-                    if (lit > cap - op) return TK_STATUS_CORRUPT;
-                    if (lit <= 32u && lit_at - w.at + 32u <= 128u) {          // literals are in the window
-                        const uint32_t j = lit_at - w.at + lane;
-                        const uint8_t v = (uint8_t)(__shfl_sync(0xffffffffu, w.word, (j >> 2) & 31u) >> ((j & 3u) * 8u));
-                        if (lane < lit) out[op + lane] = v;
-                    } else {
-                        for (uint32_t k = lane; k < lit; k += 32) {
-                            out[op + k] = raw[lit_at + k];
-                        }
-                    }
-                    op += lit;
-                }
-                p = lit_at + lit;
-                if (p >= bend) break;                                 // the last sequence has no match
-                if (bend - p < 2u) return TK_STATUS_CORRUPT;
-                const uint32_t offset = lz4_byte(w, p, lane) | (lz4_byte(w, p + 1, lane) << 8);
-                p += 2;
-                uint32_t mlen;
-                if (!lz4_length(w, lane, p, bend, token & 15u, mlen)) return TK_STATUS_CORRUPT;
-                mlen += 4u;
-                total += mlen;
-                if (EMIT) {
-                    if (offset == 0 || offset > op - window || mlen > cap - op) return TK_STATUS_CORRUPT;
-                    // out[op + k] = out[op - offset + k]; where the match overlaps its own output the
-                    // source repeats with period `offset`, so every byte comes from before `op`: the
-                    // lanes never read what this match writes.  The bytes were written by other lanes
-                    // of this warp: __syncwarp orders them, and they are read back through the L1 of
-                    // the same SM (the decompressed region belongs to this warp alone).
-                    __syncwarp();
-                    for (uint32_t k = lane; k < mlen; k += 32)
-                        out[op + k] = out[op - offset + (offset >= mlen ? k : k % offset)];
-                    __syncwarp();
-                    op += mlen;
-                }
-            }
-        }
-        p = bend + (f.block_checksum ? 4u : 0u);
-        if (p > end) return TK_STATUS_CORRUPT;
-    }
-    if (p + (f.content_checksum ? 4u : 0u) != end) return TK_STATUS_CORRUPT;
-    if (EMIT && op != cap) return TK_STATUS_CORRUPT;
-    *out_size = total;
-    return TK_STATUS_OK;
-}
-
-__global__ void __launch_bounds__(256) k_lz4_size(const rb_args a) {
-    const uint32_t lane = threadIdx.x & 31;
-    const uint32_t warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, nwarps = (gridDim.x * blockDim.x) >> 5;
-    for (uint32_t i = warp; i < a.n_batches; i += nwarps) {
-        const tk_rb_batch b = a.batches[i];
-        if (b.status || b.codec != 3u) continue;
-        uint64_t out = 0;
-        uint32_t status = lz4_frame_run<false>(a.raw, b.start + RB_HEADER, b.end, lane, nullptr, 0, &out);
-        if (!status && out > 0x7FFFFFFFull) status = TK_STATUS_UNSUPPORTED;
-        if (lane == 0) {
-            a.batches[i].status = status;
-            a.batches[i].unc_bytes = status ? 0u : (uint32_t)out;
-        }
-    }
-}
-
-__global__ void __launch_bounds__(1024) k_lz4_prefix(const rb_args a) {
-    __shared__ unsigned long long warp_tot[32];
-    __shared__ unsigned long long s_total, s_run;
-    const uint32_t t = threadIdx.x;
-    if (t == 0) s_run = 0;
-    __syncthreads();
-    for (uint32_t base = 0; base < a.n_batches; base += blockDim.x) {
-        const uint32_t i = base + t;
-        const bool mine = i < a.n_batches && a.batches[i].codec == 3u && !a.batches[i].status;
-        const unsigned long long v = mine ? a.batches[i].unc_bytes : 0ull;
-        const unsigned long long excl = s_run + rb_block_scan(v, warp_tot, &s_total);
-        if (mine) {
-            if (excl + v > a.slot_bytes) a.batches[i].status = TK_STATUS_UNSUPPORTED;   // does not fit the slot
-            else { a.batches[i].rec_start = (uint32_t)excl; a.batches[i].rec_end = (uint32_t)(excl + v); }
-        }
-        __syncthreads();
-        if (t == 0) s_run += s_total;
-        __syncthreads();
-    }
-}
-
-// warp per batch
-__global__ void __launch_bounds__(128) k_lz4_decode(const rb_args a) {
-    const uint32_t lane = threadIdx.x & 31;
-    const uint32_t warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, nwarps = (gridDim.x * blockDim.x) >> 5;
-    for (uint32_t i = warp; i < a.n_batches; i += nwarps) {
-        const tk_rb_batch b = a.batches[i];
-        if (b.status || b.codec != 3u) continue;
-        uint64_t total = 0;
-        const uint32_t status = lz4_frame_run<true>(a.raw, b.start + RB_HEADER, b.end, lane, a.raw2 + b.rec_start,
-                                                    b.rec_end - b.rec_start, &total);
-        if (status && lane == 0) a.batches[i].status = status;
-    }
-}
-
 // ---------------------------------------------------------------- entry points
+// compressed blocks a slot can hold: one per record plus one per 4 KiB (snappy-java chunks are 32 KiB,
+// LZ4 blocks 64 KiB and more)
+static inline size_t rb_max_units(const tk_ctx* ctx) { return (size_t)ctx->slot_records + ctx->slot_bytes / 4096 + 16; }
+
 // (producer threads submit concurrently: the first-use allocation is serialised)
 static std::mutex g_rb_mutex;
 static int rb_ensure(tk_ctx* ctx) {
@@ -759,13 +518,14 @@ static int rb_ensure(tk_ctx* ctx) {
         TK_CUDA(cudaMalloc(&s.d.rb_bigq, sizeof(uint32_t) * ((size_t)(ctx->slot_bytes / RB_BIG) + 2)));
         TK_CUDA(cudaHostAlloc(&s.h_rb_batches, sizeof(tk_rb_batch) * (size_t)ctx->slot_records, cudaHostAllocDefault));
         TK_CUDA(cudaHostAlloc(&s.h_rb_summary, sizeof(tk_rb_summary_t), cudaHostAllocDefault));
+        TK_CUDA(cudaHostAlloc(&s.h_rb_units, sizeof(tk_rb_unit) * rb_max_units(ctx), cudaHostAllocDefault));
         TK_CUDA(cudaEventCreateWithFlags(&s.ev_raw, cudaEventDisableTiming));
     }
     return 0;
 }
 
-// the decompressed buffer: first compressed batch
-static int rb_ensure_lz4(tk_ctx* ctx) {
+// the decompressed buffer and the device unit table: first compressed batch
+static int rb_ensure_codecs(tk_ctx* ctx) {
     std::lock_guard<std::mutex> lock(g_rb_mutex);
     TK_REQUIRE(ctx->slot_bytes < (1ull << 31), "compressed record batches need slot_bytes < 2 GiB");
     if (ctx->n_slots && ctx->slots[ctx->n_slots - 1].d.raw2) return 0;
@@ -774,6 +534,7 @@ static int rb_ensure_lz4(tk_ctx* ctx) {
         if (s.d.raw2) continue;
         TK_CUDA(cudaMalloc(&s.d.raw2, ctx->slot_bytes + TK_BYTES_PAD));
         TK_CUDA(cudaMemset(s.d.raw2, 0, ctx->slot_bytes + TK_BYTES_PAD));
+        TK_CUDA(cudaMalloc(&s.d.rb_units, sizeof(tk_rb_unit) * rb_max_units(ctx)));
     }
     return 0;
 }
@@ -791,11 +552,11 @@ extern "C" int tk_slot_submit_recordbatches(tk_ctx* ctx, int slot, uint64_t n_by
     int rc = rb_ensure(ctx); if (rc) return rc;
     tk_slot& s = ctx->slots[slot];
     cudaStream_t st = ctx->copy_stream;
-    uint32_t n_batches = 0, n_rec = 0, n_lz4 = 0;
+    uint32_t n_batches = 0, n_rec = 0, n_units = 0, n_coded = 0;
     rc = rb_walk_host(s.h_bytes, blobs, n_blobs, s.h_rb_batches, ctx->slot_records, ctx->slot_records, &n_batches,
-                      &n_rec, &n_lz4);
+                      &n_rec, s.h_rb_units, (uint32_t)rb_max_units(ctx), &n_units, &n_coded);
     if (rc) return rc;
-    if (n_lz4) { rc = rb_ensure_lz4(ctx); if (rc) return rc; }
+    if (n_coded) { rc = rb_ensure_codecs(ctx); if (rc) return rc; }
     s.n_records = n_rec;
     s.n_bytes = n_bytes;                     // upper bound of the value bytes (sizes grids only)
     if (n_records) *n_records = n_rec;
@@ -809,17 +570,16 @@ extern "C" int tk_slot_submit_recordbatches(tk_ctx* ctx, int slot, uint64_t n_by
     if (n_bytes) TK_CUDA(cudaMemcpyAsync(s.d.raw, s.h_bytes, n_bytes, cudaMemcpyHostToDevice, st));
     if (n_batches)
         TK_CUDA(cudaMemcpyAsync(s.d.rb_batches, s.h_rb_batches, sizeof(tk_rb_batch) * n_batches, cudaMemcpyHostToDevice, st));
+    if (n_units)
+        TK_CUDA(cudaMemcpyAsync(s.d.rb_units, s.h_rb_units, sizeof(tk_rb_unit) * n_units, cudaMemcpyHostToDevice, st));
     TK_CUDA(cudaEventRecord(s.ev_raw, st));
     TK_CUDA(cudaStreamWaitEvent(ks, s.ev_raw, 0));
     rb_args a;
     a.raw = s.d.raw; a.raw2 = s.d.raw2; a.batches = s.d.rb_batches; a.n_batches = n_batches; a.n_records = n_rec;
+    a.units = s.d.rb_units; a.n_units = n_units;
     a.summary = s.d.rb_summary; a.temp = s.d.rb_temp; a.bigq = s.d.rb_bigq; a.bytes = s.d.bytes; a.recs = s.d.recs;
     a.slot_records = ctx->slot_records; a.slot_bytes = ctx->slot_bytes;
-    if (n_lz4) {
-        k_lz4_size<<<min((n_batches + 7) / 8, 148u * 8u), 256, 0, ks>>>(a);
-        k_lz4_prefix<<<1, 1024, 0, ks>>>(a);
-        k_lz4_decode<<<min((n_batches + 3) / 4, 148u * 16u), 128, 0, ks>>>(a);
-    }
+    if (n_coded) { rc = tk_codec_launch(a, ks); if (rc) return rc; }
     k_rb_check<<<148 * 4, 256, 0, ks>>>(a);
     k_rb_prefix<<<1, 1024, 0, ks>>>(a);
     k_rb_copy<<<148 * 8, 256, 0, ks>>>(a);

@@ -71,26 +71,77 @@ def encode_record(offset_delta: int, value: Optional[bytes], key: Optional[bytes
 
 
 def lz4_frame(data: bytes) -> bytes:
-    """LZ4 frame of `data` (pyarrow's codec: test infrastructure, as the oracle is)."""
+    """LZ4 frame of `data` as liblz4 writes it by default: block-dependent, 64 KiB blocks, no
+    checksums (pyarrow's codec: test infrastructure, as the oracle is)."""
     import pyarrow as pa
     return pa.Codec("lz4").compress(data, asbytes=True)
+
+
+def lz4_frame_independent(data: bytes, block_bytes: int = 65536, block_checksum: bool = False,
+                          content_checksum: bool = False) -> bytes:
+    """LZ4 frame with independent blocks, the way Kafka's Java client writes it
+    (KafkaLZ4BlockOutputStream: FLG = version 01 | block independence, BD = 64 KiB)."""
+    import pyarrow as pa
+    import xxhash
+    raw = pa.Codec("lz4_raw")
+    flg = 0x60 | (0x10 if block_checksum else 0) | (0x04 if content_checksum else 0)
+    bd = {65536: 0x40, 262144: 0x50, 1 << 20: 0x60, 4 << 20: 0x70}[block_bytes]
+    head = bytes([flg, bd])
+    out = bytearray(b"\x04\x22\x4d\x18" + head + bytes([(xxhash.xxh32(head, seed=0).intdigest() >> 8) & 0xFF]))
+    for k in range(0, len(data), block_bytes):
+        chunk = data[k:k + block_bytes]
+        z = raw.compress(chunk, asbytes=True)
+        if len(z) >= len(chunk):                               # stored block
+            out += struct.pack("<I", len(chunk) | 0x80000000) + chunk
+            z = chunk
+        else:
+            out += struct.pack("<I", len(z)) + z
+        if block_checksum:
+            out += struct.pack("<I", xxhash.xxh32(z, seed=0).intdigest())
+    out += b"\x00\x00\x00\x00"
+    if content_checksum:
+        out += struct.pack("<I", xxhash.xxh32(data, seed=0).intdigest())
+    return bytes(out)
+
+
+def snappy_raw(data: bytes) -> bytes:
+    import pyarrow as pa
+    return pa.Codec("snappy").compress(data, asbytes=True)
+
+
+def snappy_xerial(data: bytes, chunk_bytes: int = 32768) -> bytes:
+    """snappy-java framing (what Kafka's Java client writes): magic, version, compatible version,
+    then {int32 length, raw snappy block} per 32 KiB of input."""
+    out = bytearray(b"\x82SNAPPY\x00" + struct.pack(">ii", 1, 1))
+    for k in range(0, len(data), chunk_bytes):
+        z = snappy_raw(data[k:k + chunk_bytes])
+        out += struct.pack(">i", len(z)) + z
+    return bytes(out)
+
+
+#: codec argument of encode_batch -> (attribute bits, compressor)
+CODECS = {
+    3: (3, lz4_frame), "lz4": (3, lz4_frame), "lz4i": (3, lz4_frame_independent),
+    "lz4ic": (3, lambda d: lz4_frame_independent(d, block_checksum=True, content_checksum=True)),
+    2: (2, snappy_xerial), "snappy": (2, snappy_xerial), "snappy_raw": (2, snappy_raw),
+}
 
 
 def encode_batch(base_offset: int, values: Sequence[Optional[bytes]], attributes: int = 0,
                  offset_deltas: Optional[Sequence[int]] = None, keys: Optional[Sequence] = None,
                  headers: Optional[Sequence] = None, crc: Optional[int] = None, codec: int = 0) -> bytes:
     """One RecordBatch v2.  `offset_deltas` default to 0, 1, 2, ... (a compacted topic has gaps).
-    `codec` 3 compresses the records with LZ4 (frame format) and sets the attribute bits."""
+    `codec` (a key of CODECS: 3 / "lz4", "lz4i", "lz4ic", 2 / "snappy", "snappy_raw") compresses the
+    records and sets the attribute bits."""
     n = len(values)
     deltas = list(range(n)) if offset_deltas is None else list(offset_deltas)
     recs = b"".join(encode_record(deltas[k], values[k], None if keys is None else keys[k], 0,
                                   () if headers is None else headers[k]) for k in range(n))
     last = deltas[-1] if n else 0
-    if codec == 3:
-        recs = lz4_frame(recs)
-        attributes |= 3
-    elif codec:
-        raise ValueError("the stub broker compresses with LZ4 only")
+    if codec:
+        bits, compress = CODECS[codec]
+        recs = compress(recs)
+        attributes |= bits
     tail = struct.pack(">hiqqqhii", attributes, last, 0, 0, -1, -1, -1, n) + recs    # from byte 21 on
     if crc is None:
         crc = crc32c(tail)

@@ -199,7 +199,7 @@ class KafkaConsumer:
 
     def __init__(self, *topics, log: Optional[RecordLog] = None, block_at_end: bool = False,
                  fail_commits: bool = False, repeat: int = 1, raw_batch_bytes: int = 16384,
-                 raw_codec: int = 0, **configs):
+                 raw_codec=0, **configs):
         self.topics = topics
         self.config = dict(configs)
         # the end of the in-memory log is the end of the stream, unless the stub is told to
@@ -211,7 +211,7 @@ class KafkaConsumer:
         self._repeat = max(1, int(repeat))
         self._block_at_end = block_at_end
         self._raw_batch_bytes = int(raw_batch_bytes)
-        self._raw_codec = int(raw_codec)
+        self._raw_codec = raw_codec
         self._fail_commits = fail_commits
         self._positions: Dict[int, int] = {}
         self.committed_log: List[Dict[int, int]] = []

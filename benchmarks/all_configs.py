@@ -80,7 +80,8 @@ def device_resident(cfg, log, passes=24):
 
 
 RAW_BATCH_BYTES = int(os.environ.get("RAW_BATCH_BYTES", str(64 << 10)))
-RAW_CODEC = int(os.environ.get("RAW_CODEC", "0"))      # 3: the raw arm serves LZ4-compressed batches
+_rc = os.environ.get("RAW_CODEC", "0")                  # codec of the raw arm: 0, 2 (snappy), 3 (LZ4), "lz4i", ...
+RAW_CODEC = int(_rc) if _rc.isdigit() else _rc
 
 
 def e2e(cfg, log, packed, repeat, batches_timed, warm):
@@ -90,7 +91,8 @@ def e2e(cfg, log, packed, repeat, batches_timed, warm):
     class DS(KafkaDataset):
         payload_schema = cfg["schema"]
         device_slot_bytes = cfg["slot_bytes"] + (cfg["slot_bytes"] >> 2 if packed == "raw" else 0)   # framing
-        device_slots = 3
+        device_slots = int(os.environ.get("DEVICE_SLOTS", "3"))
+        device_producers = int(os.environ.get("TK_PRODUCERS", "2"))
         device_input = "raw" if packed == "raw" else "auto"
 
         @classmethod

@@ -168,6 +168,7 @@ static void free_slot(tk_slot& s) {
     if (s.ev_free) cudaEventDestroy(s.ev_free);
     if (s.ev_result) cudaEventDestroy(s.ev_result);
     if (s.ev_raw) cudaEventDestroy(s.ev_raw);
+    if (s.split_stream) cudaStreamDestroy(s.split_stream);
     if (s.ev_dec0) cudaEventDestroy(s.ev_dec0);
     if (s.ev_dec1) cudaEventDestroy(s.ev_dec1);
 }
@@ -184,7 +185,6 @@ extern "C" int tk_ctx_destroy(tk_ctx* ctx) {
     cudaFree(ctx->d_positions);
     cudaFree(ctx->d_image_lut);
     if (ctx->copy_stream) cudaStreamDestroy(ctx->copy_stream);
-    if (ctx->split_stream) cudaStreamDestroy(ctx->split_stream);
     delete ctx;
     return 0;
 }

@@ -103,6 +103,8 @@ struct tk_slot {
     cudaEvent_t  ev_free;     // kernels finished reading the device copy
     cudaEvent_t  ev_result;   // result block is in pinned memory
     cudaEvent_t  ev_raw;      // raw record-batch bytes landed (created with the raw buffers)
+    cudaStream_t split_stream;   // this slot's decompression + split kernels: they overlap the next
+                                 // slot's H2D and the kernels of the other slots (latency-bound decoders)
     tk_rb_batch* h_rb_batches;   // pinned, [slot_records]: written by the host's header walk
     tk_rb_unit*  h_rb_units;     // pinned: decompression units of compressed batches
     tk_rb_summary_t* h_rb_summary;   // pinned
@@ -125,7 +127,6 @@ struct tk_ctx {
     size_t    tok_cap;         // entries of the token array (a token needs >= 2 bytes)
     uint32_t  batch_size;      // of the last tk_compact
     cudaStream_t copy_stream;
-    cudaStream_t split_stream;   // record-batch split kernels (created on first use): the next slot's H2D overlaps them
     tk_state* d_state;
     int64_t*  d_positions;     // [n_partitions] running max(offset)+1, -1 = never seen
     uint16_t* d_image_lut;     // [4][256] bf16 bit patterns

@@ -506,7 +506,6 @@ static inline size_t rb_max_units(const tk_ctx* ctx) { return (size_t)ctx->slot_
 static std::mutex g_rb_mutex;
 static int rb_ensure(tk_ctx* ctx) {
     std::lock_guard<std::mutex> lock(g_rb_mutex);
-    if (!ctx->split_stream) TK_CUDA(cudaStreamCreateWithFlags(&ctx->split_stream, cudaStreamNonBlocking));
     for (int i = 0; i < ctx->n_slots; ++i) {
         tk_slot& s = ctx->slots[i];
         if (s.d.raw) continue;
@@ -520,6 +519,7 @@ static int rb_ensure(tk_ctx* ctx) {
         TK_CUDA(cudaHostAlloc(&s.h_rb_summary, sizeof(tk_rb_summary_t), cudaHostAllocDefault));
         TK_CUDA(cudaHostAlloc(&s.h_rb_units, sizeof(tk_rb_unit) * rb_max_units(ctx), cudaHostAllocDefault));
         TK_CUDA(cudaEventCreateWithFlags(&s.ev_raw, cudaEventDisableTiming));
+        TK_CUDA(cudaStreamCreateWithFlags(&s.split_stream, cudaStreamNonBlocking));
     }
     return 0;
 }
@@ -560,9 +560,9 @@ extern "C" int tk_slot_submit_recordbatches(tk_ctx* ctx, int slot, uint64_t n_by
     s.n_records = n_rec;
     s.n_bytes = n_bytes;                     // upper bound of the value bytes (sizes grids only)
     if (n_records) *n_records = n_rec;
-    // copies on the copy stream, kernels on the split stream: the H2D of the next slot runs while
-    // this one is split
-    cudaStream_t ks = ctx->split_stream;
+    // copies on the copy stream, kernels on the slot's own stream: the H2D of the next slot and
+    // the kernels of the other slots run while this one is decompressed and split
+    cudaStream_t ks = s.split_stream;
     if (s.free_recorded) {
         TK_CUDA(cudaStreamWaitEvent(st, s.ev_free, 0));
         TK_CUDA(cudaStreamWaitEvent(ks, s.ev_free, 0));

@@ -229,11 +229,12 @@ int tk_compact_noalloc(const int32_t* d_keep, uint32_t n, uint32_t batch_size, u
  * the ConsumerRecord that `for record in self._consumer` (src/kafka_dataset.py:156) yields.
  *   - a batch that is cut off by the end of its blob is ignored (fetch responses end so)
  *   - records with offset < fetch_offset are skipped (batches are returned whole)
- *   - LZ4-compressed batches (attributes & 7 == 3; kafka/codec.py lz4_decode) are decompressed
- *     on the device (LZ4 frame + block format; xxHash checksums skipped, the batch CRC covers
- *     the same bytes); gzip / snappy / zstd batches surface as TK_STATUS_UNSUPPORTED
+ *   - LZ4 and snappy batches (attributes & 7 == 3 / 2; kafka/codec.py lz4_decode,
+ *     snappy_decode) are decompressed on the device (LZ4 frame + block format, xxHash checksums
+ *     skipped: the batch CRC covers the same bytes; snappy blocks, raw or in snappy-java's xerial
+ *     framing); gzip / zstd batches surface as TK_STATUS_UNSUPPORTED
  *   - control batches are skipped; null values surface as TK_STATUS_UNSUPPORTED, CRC /
- *     framing / LZ4 stream errors as TK_STATUS_CORRUPT on the first record of the batch, when
+ *     framing / compressed-stream errors as TK_STATUS_CORRUPT on the first record of the batch, when
  *     the batch that contains it is delivered
  *   - offset_delta is added to every offset (0 for real fetch responses; lets a test log be
  *     replayed at higher offsets without re-encoding) */

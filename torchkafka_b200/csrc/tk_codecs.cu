@@ -158,7 +158,12 @@ __device__ __forceinline__ void cz_literals(cz_window& w, uint32_t lane, uint32_
 // and they are read back through the L1 of the same SM (the region belongs to this warp alone).
 __device__ __forceinline__ void cz_match(uint8_t* out, uint32_t op, uint32_t offset, uint32_t n, uint32_t lane) {
     __syncwarp();
-    for (uint32_t k = lane; k < n; k += 32) out[op + k] = out[op - offset + (offset >= n ? k : k % offset)];
+    const uint8_t* src = out + op - offset;
+    if (offset >= n) {
+        for (uint32_t k = lane; k < n; k += 32) out[op + k] = src[k];
+    } else {
+        for (uint32_t k = lane; k < n; k += 32) out[op + k] = src[k % offset];
+    }
     __syncwarp();
 }
 
@@ -181,21 +186,58 @@ __device__ __forceinline__ bool lz4_length(cz_window& w, uint32_t lane, uint32_t
 
 // The sequences of one block [p, bend).  EMIT = false: only counts (op advances); EMIT = true: writes
 // out[op...] (capacity cap); matches may reach back to out[window].
+// One sequence at p, general form (every field through the checked window).  *last: the block ended
+// with this sequence's literals.
+template <bool EMIT>
+__device__ __forceinline__ uint32_t lz4_sequence(cz_window& w, uint32_t lane, uint32_t& p, uint32_t bend, uint8_t* out,
+                                                 uint32_t cap, uint32_t window, uint32_t& op, bool* last) {
+    const uint32_t token = cz_byte(w, p, lane);
+    uint32_t lit, lit_at = p + 1;
+    if (!lz4_length(w, lane, lit_at, bend, token >> 4, lit) || lit > bend - lit_at) return TK_STATUS_CORRUPT;
+    if (lit > cap - op) return EMIT ? TK_STATUS_CORRUPT : TK_STATUS_UNSUPPORTED;
+    if (EMIT) cz_literals(w, lane, lit_at, lit, out, op);
+    op += lit;
+    p = lit_at + lit;
+    if (p >= bend) { *last = true; return TK_STATUS_OK; }       // the last sequence has no match
+    if (bend - p < 2u) return TK_STATUS_CORRUPT;
+    const uint32_t offset = cz_byte(w, p, lane) | (cz_byte(w, p + 1, lane) << 8);
+    p += 2;
+    uint32_t mlen;
+    if (!lz4_length(w, lane, p, bend, token & 15u, mlen)) return TK_STATUS_CORRUPT;
+    mlen += 4u;
+    if (offset == 0 || offset > op - window) return TK_STATUS_CORRUPT;
+    if (mlen > cap - op) return EMIT ? TK_STATUS_CORRUPT : TK_STATUS_UNSUPPORTED;
+    if (EMIT) cz_match(out, op, offset, mlen, lane);
+    op += mlen;
+    return TK_STATUS_OK;
+}
+
+// The sequences of one block [p, bend).  EMIT = false: only counts (op advances); EMIT = true: writes
+// out[op...] (capacity cap); matches may reach back to out[window].
+// Fast lane (literal run < 15, the usual case in text): lane i takes byte p + i out of the window
+// with one shuffle; the token is lane 0's byte, the literals are the bytes of lanes 1..lit (stored
+// straight from the register), the offset the bytes of lanes lit+1, lit+2.
 template <bool EMIT>
 __device__ __forceinline__ uint32_t lz4_block_run(cz_window& w, uint32_t lane, uint32_t p, uint32_t bend, uint8_t* out,
                                                   uint32_t cap, uint32_t window, uint32_t& op) {
     while (p < bend) {
-        const uint32_t token = cz_byte(w, p, lane);
-        uint32_t lit, lit_at = p + 1;
-        if (!lz4_length(w, lane, lit_at, bend, token >> 4, lit) || lit > bend - lit_at) return TK_STATUS_CORRUPT;
+        if (p - w.at > 96u) cz_load(w, p, lane);              // [p, p + 32) is inside the window
+        const uint32_t jj = p - w.at + lane;
+        const uint32_t mine = (__shfl_sync(0xffffffffu, w.word, jj >> 2) >> ((jj & 3u) * 8u)) & 0xFFu;
+        const uint32_t token = __shfl_sync(0xffffffffu, mine, 0);
+        const uint32_t lit = token >> 4;
+        if (lit == 15u || bend - p < 32u) {                   // long literal run / end of the block
+            bool last = false;
+            const uint32_t st = lz4_sequence<EMIT>(w, lane, p, bend, out, cap, window, op, &last);
+            if (st) return st;
+            if (last) break;
+            continue;
+        }
         if (lit > cap - op) return EMIT ? TK_STATUS_CORRUPT : TK_STATUS_UNSUPPORTED;
-        if (EMIT) cz_literals(w, lane, lit_at, lit, out, op);
+        if (EMIT && lane - 1u < lit) out[op + lane - 1u] = (uint8_t)mine;
         op += lit;
-        p = lit_at + lit;
-        if (p >= bend) break;                                 // the last sequence has no match
-        if (bend - p < 2u) return TK_STATUS_CORRUPT;
-        const uint32_t offset = cz_byte(w, p, lane) | (cz_byte(w, p + 1, lane) << 8);
-        p += 2;
+        const uint32_t offset = __shfl_sync(0xffffffffu, mine, lit + 1u) | (__shfl_sync(0xffffffffu, mine, lit + 2u) << 8);
+        p += lit + 3u;
         uint32_t mlen;
         if (!lz4_length(w, lane, p, bend, token & 15u, mlen)) return TK_STATUS_CORRUPT;
         mlen += 4u;

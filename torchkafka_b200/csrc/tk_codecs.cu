@@ -291,6 +291,33 @@ __device__ __forceinline__ uint32_t snappy_run(cz_window& w, uint32_t lane, uint
         b = cz_byte(w, p++, lane);
     } while (b & 0x80u);
     while (p < end) {
+        if (end - p >= 32u) {
+            // fast lane: lane i takes byte p + i with one shuffle; tag = lane 0's byte, a short
+            // literal is the bytes of lanes 1..len, a copy's offset the bytes of lanes 1 (, 2)
+            if (p - w.at > 96u) cz_load(w, p, lane);
+            const uint32_t jj = p - w.at + lane;
+            const uint32_t mine = (__shfl_sync(0xffffffffu, w.word, jj >> 2) >> ((jj & 3u) * 8u)) & 0xFFu;
+            const uint32_t tag = __shfl_sync(0xffffffffu, mine, 0);
+            const uint32_t kind = tag & 3u;
+            if (kind == 0u && (tag >> 2) < 31u) {
+                const uint32_t len = (tag >> 2) + 1u;
+                if (len > cap - op) return TK_STATUS_CORRUPT;
+                if (lane - 1u < len) out[op + lane - 1u] = (uint8_t)mine;
+                op += len;
+                p += 1u + len;
+                continue;
+            }
+            if (kind == 1u || kind == 2u) {
+                const uint32_t b1 = __shfl_sync(0xffffffffu, mine, 1), b2 = __shfl_sync(0xffffffffu, mine, 2);
+                const uint32_t len = kind == 1u ? 4u + ((tag >> 2) & 7u) : 1u + (tag >> 2);
+                const uint32_t offset = kind == 1u ? (((tag >> 5) << 8) | b1) : (b1 | (b2 << 8));
+                if (offset == 0 || offset > op || len > cap - op) return TK_STATUS_CORRUPT;
+                cz_match(out, op, offset, len, lane);
+                op += len;
+                p += kind == 1u ? 2u : 3u;
+                continue;
+            }
+        }
         const uint32_t tag = cz_byte(w, p++, lane);
         if ((tag & 3u) == 0u) {
             uint32_t len = tag >> 2;

@@ -236,12 +236,13 @@ __device__ __forceinline__ uint32_t lz4_block_run(cz_window& w, uint32_t lane, u
         if (lit > cap - op) return EMIT ? TK_STATUS_CORRUPT : TK_STATUS_UNSUPPORTED;
         if (EMIT && lane - 1u < lit) out[op + lane - 1u] = (uint8_t)mine;
         op += lit;
-        const uint32_t offset = __shfl_sync(0xffffffffu, mine, lit + 1u) | (__shfl_sync(0xffffffffu, mine, lit + 2u) << 8);
+        uint32_t offset = 1;                                 // (the size pass leaves offsets to the decode pass)
+        if (EMIT) offset = __shfl_sync(0xffffffffu, mine, lit + 1u) | (__shfl_sync(0xffffffffu, mine, lit + 2u) << 8);
         p += lit + 3u;
         uint32_t mlen;
         if (!lz4_length(w, lane, p, bend, token & 15u, mlen)) return TK_STATUS_CORRUPT;
         mlen += 4u;
-        if (offset == 0 || offset > op - window) return TK_STATUS_CORRUPT;
+        if (EMIT && (offset == 0 || offset > op - window)) return TK_STATUS_CORRUPT;
         if (mlen > cap - op) return EMIT ? TK_STATUS_CORRUPT : TK_STATUS_UNSUPPORTED;
         if (EMIT) cz_match(out, op, offset, mlen, lane);
         op += mlen;

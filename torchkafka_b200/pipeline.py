@@ -372,6 +372,29 @@ class IngestPipeline:
         vals = column[idx].tolist()
         return {tp_of[p]: mk(v) for p, v in zip(idx.tolist(), vals)}
 
+    def _offsets_maps(self, cols: np.ndarray):
+        """``_offsets_map`` for every row of ``cols`` (one row per closed batch of a slot) at once:
+        one vectorised comparison per slot instead of a handful of numpy calls per batch, which is
+        what the host spends its time on when batches are small."""
+        nc = cols.shape[0]
+        if nc == 0:
+            return []
+        prev = self._last_column
+        if prev is None or self.commit_all_partitions:
+            head = cols[:1] >= 0
+            changed = np.concatenate([head, (cols[1:] >= 0) if self.commit_all_partitions
+                                      else (cols[1:] != cols[:-1])], axis=0)
+        else:
+            changed = np.concatenate([cols[:1] != prev[None, :], cols[1:] != cols[:-1]], axis=0)
+        self._last_column = cols[nc - 1]
+        rows, parts = np.nonzero(changed)
+        vals = cols[rows, parts].tolist()
+        parts = parts.tolist()
+        cut = np.searchsorted(rows, np.arange(nc + 1)).tolist()
+        mk = self._mk_offset
+        tp_of = self._tp_of
+        return [{tp_of[parts[k]]: mk(vals[k]) for k in range(cut[j], cut[j + 1])} for j in range(nc)]
+
     def _produce(self, free_q, deliver):
         """Producer thread.  Gather (consumer calls, serialised, defines the slot order) then
         pack + submit (parallel across producer threads)."""
@@ -505,12 +528,14 @@ class IngestPipeline:
                 lmax = res.batch_lmax[:nc].copy()
                 lmax[0] = max(int(lmax[0]), open_lmax)
                 views = eng.batch_views(item.out, first, nc, lmax)
-                commit_cols = np.ascontiguousarray(res.commit.T)
-                for j in range(nc):
-                    if err_rec is not None and res.batch_end[j] >= err_rec:
-                        raise self._error(item, res)
-                    self.stats["batches"] += 1
-                    yield views[j], self._offsets_map(commit_cols[j])
+                commit_cols = np.ascontiguousarray(res.commit.T[:nc])
+                # batches in front of the first bad record are delivered, the one holding it raises
+                good = nc if err_rec is None else int(np.searchsorted(res.batch_end[:nc], err_rec, side="left"))
+                maps = self._offsets_maps(commit_cols[:good])
+                self.stats["batches"] += good
+                yield from zip(views[:good], maps)
+                if good < nc:
+                    raise self._error(item, res)
             if err_rec is not None:
                 # bad record sits in the still-open batch: it surfaces with that batch
                 raise self._error(item, res)

@@ -443,7 +443,7 @@ __device__ __forceinline__ bool fast_number(const uint8_t* bytes, uint32_t pos, 
 // Token entry written by k_json_scan: .x = byte position of the element, .y = record index with
 // TOK_LAST on the record's last element and TOK_TAIL when the record's final byte is ']'.
 template <int KIND>
-__global__ void __launch_bounds__(256, 6) k_json_parse(const flat_args a) {
+__global__ void __launch_bounds__(256, 5) k_json_parse(const flat_args a) {
     typedef typename tk_elem<KIND>::type T;
     __shared__ parse_tables tb;
     parse_tables_init(tb);                  // constants only: overlaps the tail of the previous kernel

@@ -169,6 +169,12 @@ int tk_json_decode_warp(tk_ctx* ctx, int slot, int dtype, uint32_t max_len, uint
 /* ---- K1c + K3: fixed-layout bytes -> rows (torch.frombuffer + torch.stack) -- */
 int tk_collate_raw(tk_ctx* ctx, int slot, uint64_t record_bytes, const tk_plane_t* out,
                    void* stream);
+/* fixed-layout struct records: bytes [field_offset, field_offset + field_bytes) of
+ * every kept record -> row of `out` (row_bytes == field_bytes); one call per field.  What a
+ * `_process` returning a tuple of torch.frombuffer views + default_collate's per-field
+ * torch.stack (collate.py:275 via the tuple branch) compute. */
+int tk_collate_field(tk_ctx* ctx, int slot, uint64_t record_bytes, uint32_t field_offset, uint32_t field_bytes,
+                     const tk_plane_t* out, void* stream);
 /* HWC uint8 -> normalised bfloat16 CHW:  bf16(((x / 255) - mean[c]) / std[c]) in
  * float32 with IEEE division, the op order of SURVEY.md §8c */
 int tk_image_set_norm(tk_ctx* ctx, int channels, const float* mean, const float* std, void* stream);
@@ -180,7 +186,8 @@ int tk_collate_image_u8_bf16_nchw(tk_ctx* ctx, int slot, uint32_t height, uint32
  * tk_slot_fetch_result, enqueued on `stream`.  What a host plugin binds in place of
  * the per-record loop KafkaDataset.__iter__ (src/kafka_dataset.py:147-171) + the
  * DataLoader fetch/collate (fetch.py:27-45) + auto_commit's commit (auto_commit.py:55-58). */
-typedef enum { TK_SCHEMA_JSON = 0, TK_SCHEMA_RAW = 1, TK_SCHEMA_IMAGE = 2 } tk_schema_t;
+typedef enum { TK_SCHEMA_JSON = 0, TK_SCHEMA_RAW = 1, TK_SCHEMA_IMAGE = 2, TK_SCHEMA_STRUCT = 3 } tk_schema_t;
+#define TK_MAX_PLANES 8
 typedef struct tk_job {
     int32_t    schema;        /* tk_schema_t */
     int32_t    dtype;         /* JSON: tk_dtype_t */
@@ -189,10 +196,12 @@ typedef struct tk_job {
     uint64_t   record_bytes;                            /* raw / image input bytes per record */
     uint32_t   batch_size;
     int32_t    prev_slot;     /* slot processed just before this one, -1 if none */
-    int32_t    n_planes;      /* 1 (values) or 3 (values, lengths, mask) */
+    int32_t    n_planes;      /* 1 (values), 3 (values, lengths, mask), or one per struct field */
     int32_t    resident;      /* non-zero: device copy already valid, skip the H2D wait */
-    tk_plane_t prev[3];       /* planes of the previous slot's tensors (carry source) */
-    tk_plane_t cur[3];        /* planes of this slot's tensors */
+    tk_plane_t prev[TK_MAX_PLANES];       /* planes of the previous slot's tensors (carry source) */
+    tk_plane_t cur[TK_MAX_PLANES];        /* planes of this slot's tensors */
+    uint32_t   field_offset[TK_MAX_PLANES];   /* struct: byte offset of field k inside the record ... */
+    uint32_t   field_bytes[TK_MAX_PLANES];    /* ... and its size (== row_bytes of plane k) */
 } tk_job_t;
 int tk_process_slot(tk_ctx* ctx, int slot, const tk_job_t* job, void* stream);
 

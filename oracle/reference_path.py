@@ -59,6 +59,35 @@ def process_raw(shape, dtype=torch.uint8):
     return _process
 
 
+def process_struct(fields):
+    """Fixed-layout struct: one torch.frombuffer view per field, returned as a
+    tuple; default_collate stacks every position of the tuple (collate.py tuple branch -> :275).
+    A record of the wrong size raises, as frombuffer / view would."""
+    layout, off = [], 0
+    for _name, dtype, shape in fields:
+        count = 1
+        for k in shape:
+            count *= k
+        layout.append((dtype, count, off, tuple(shape)))
+        off += count * torch.empty((), dtype=dtype).element_size()
+    total = off
+
+    def _process(record):
+        buf = bytearray(record.value)
+        if len(buf) != total:
+            raise ValueError(f"record of {len(buf)} bytes, struct of {total}")
+        out = []
+        for dtype, count, o, shape in layout:
+            # frombuffer needs the offset aligned to the element size: copy the field out first
+            out.append(torch.frombuffer(bytearray(buf[o:o + count * torch.empty((), dtype=dtype).element_size()]),
+                                        dtype=dtype, count=count).view(*shape) if shape else
+                       torch.frombuffer(bytearray(buf[o:o + torch.empty((), dtype=dtype).element_size()]),
+                                        dtype=dtype, count=1).view(()))
+        return tuple(out)
+
+    return _process
+
+
 def process_image(h=224, w=224, c=3, mean=IMAGENET_MEAN, std=IMAGENET_STD):
     """HWC u8 -> CHW float /255 -> (x-mean)/std in f32 -> bf16 (RNE)."""
     mean_t = torch.tensor(mean, dtype=torch.float32).view(c, 1, 1)

@@ -11,7 +11,7 @@ if ROOT not in sys.path:
     sys.path.insert(0, ROOT)
 
 from torchkafka_b200 import KafkaDataset, auto_commit  # noqa: E402
-from torchkafka_b200.schema import ImageU8, JsonArray, RawBytes  # noqa: E402
+from torchkafka_b200.schema import ImageU8, JsonArray, RawBytes, StructBytes  # noqa: E402
 from torchkafka_b200.testing import stub_kafka as sk  # noqa: E402
 from oracle import reference_path as ref  # noqa: E402
 
@@ -67,6 +67,8 @@ def oracle_process(schema):
         return ref.process_image(schema.height, schema.width, schema.channels, schema.mean, schema.std)
     if isinstance(schema, RawBytes):
         return ref.process_raw(schema.shape, schema.dtype)
+    if isinstance(schema, StructBytes):
+        return ref.process_struct(schema.fields)
     raise TypeError(schema)
 
 
@@ -87,6 +89,10 @@ def assert_same(gpu, cpu, schema):
             assert bit_equal(gb[0], vals), f"batch {k}: values differ"
             assert torch.equal(gb[1], lengths), f"batch {k}: lengths differ"
             assert torch.equal(gb[2], mask), f"batch {k}: mask differs"
+        elif isinstance(schema, StructBytes):
+            assert len(gb) == len(cb) == len(schema.fields)
+            for (name, _, _), g, c in zip(schema.fields, gb, cb):
+                assert bit_equal(g, c), f"batch {k}: field {name} differs"
         else:
             assert gb.shape == cb.shape, (k, gb.shape, cb.shape)
             assert gb.dtype == cb.dtype

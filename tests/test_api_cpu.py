@@ -201,3 +201,16 @@ def test_finite_stream_with_workers_does_not_kill_the_workers():
                         worker_init_fn=DS.init_worker("topic", group_id="g"))
     rows = sum(b.shape[0] for b in auto_commit(loader))
     assert rows == len(base)
+
+
+def test_struct_schema_layout():
+    import torch
+    from torchkafka_b200.schema import StructBytes
+    sc = StructBytes((("x", torch.float32, (3,)), ("flag", torch.uint8, ()), ("y", torch.int64, 1), ("h", torch.float16, (2, 2))))
+    assert sc.field_bytes == (12, 1, 8, 8) and sc.field_offsets == (0, 12, 13, 21) and sc.record_bytes == 29
+    assert sc.fields[2][2] == (1,)
+    b = sc.wrap(1, 2, 3, 4)
+    assert b._fields == ("x", "flag", "y", "h")
+    import pytest
+    with pytest.raises(ValueError):
+        StructBytes(tuple(("f%d" % i, torch.uint8, ()) for i in range(9)))

@@ -309,3 +309,41 @@ def test_images_table_fallback_when_fma_is_not_exact():
     # odd shapes: single channel, width that breaks the 16-byte store alignment
     log1 = syn.make_log(4, 9, seed=52, h=13, w=7, c=1)
     check(log1, ImageU8(13, 7, 1, mean=(0.5,), std=(0.25,)), 4)
+
+
+# ---------------------------------------------------------------- fixed-layout structs (§8f-4)
+def struct_log(schema, n, seed, partitions=4, bad_at=None):
+    rng = np.random.default_rng(seed)
+    vals = []
+    for i in range(n):
+        parts = []
+        for _, dtype, shape in schema.fields:
+            count = int(np.prod(shape)) if shape else 1
+            nb = count * torch.empty((), dtype=dtype).element_size()
+            parts.append(rng.integers(0, 256, nb, dtype=np.uint8).tobytes())
+        v = b"".join(parts)
+        if bad_at is not None and i == bad_at:
+            v = v[:-1]
+        vals.append(v)
+    i = np.arange(n)
+    return RecordLog(vals, i % partitions, i // partitions)
+
+
+def test_struct_records_mixed_dtypes_and_odd_offsets():
+    from torchkafka_b200.schema import StructBytes
+    # offsets 0, 12, 13, 21, 29: word copies from unaligned sources, a 1-byte and a 3-byte field
+    schema = StructBytes((("x", torch.float32, (3,)), ("flag", torch.uint8, ()), ("label", torch.int64, ()),
+                          ("h", torch.float16, (2, 2)), ("rgb", torch.uint8, (3,)), ("w", torch.int32, (5,))))
+    log = struct_log(schema, 1000, seed=41)
+    gpu = check(log, schema, 64)
+    assert type(gpu[0][0]).__name__ == "StructBatch" and gpu[0][0].h.shape == (64, 2, 2)
+    check(log, schema, 7, slot_bytes=schema.record_bytes * 50)          # many slots, carried rows of every field
+
+
+def test_struct_record_of_wrong_size_raises():
+    from torchkafka_b200.schema import StructBytes
+    schema = StructBytes((("a", torch.int32, (4,)), ("b", torch.float64, ())))
+    log = struct_log(schema, 40, seed=42, bad_at=17)
+    with pytest.raises(PayloadError) as ei:
+        run_gpu(log, schema, 8)
+    assert ei.value.status == 5 and (ei.value.partition, ei.value.offset) == (17 % 4, 17 // 4)

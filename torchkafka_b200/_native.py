@@ -41,7 +41,8 @@ class TkJob(C.Structure):
         ("height", C.c_uint32), ("width", C.c_uint32), ("channels", C.c_uint32),
         ("record_bytes", C.c_uint64), ("batch_size", C.c_uint32), ("prev_slot", C.c_int32),
         ("n_planes", C.c_int32), ("resident", C.c_int32),
-        ("prev", TkPlane * 3), ("cur", TkPlane * 3),
+        ("prev", TkPlane * 8), ("cur", TkPlane * 8),
+        ("field_offset", C.c_uint32 * 8), ("field_bytes", C.c_uint32 * 8),
     ]
 
 
@@ -96,6 +97,7 @@ _SIGNATURES = {
     "tk_json_decode_warp": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_uint32, C.c_uint32, _p(TkPlane),
                                       _p(TkPlane), _p(TkPlane), C.c_void_p]),
     "tk_collate_raw": (C.c_int, [C.c_void_p, C.c_int, C.c_uint64, _p(TkPlane), C.c_void_p]),
+    "tk_collate_field": (C.c_int, [C.c_void_p, C.c_int, C.c_uint64, C.c_uint32, C.c_uint32, _p(TkPlane), C.c_void_p]),
     "tk_image_set_norm": (C.c_int, [C.c_void_p, C.c_int, _p(C.c_float), _p(C.c_float), C.c_void_p]),
     "tk_collate_image_u8_bf16_nchw": (C.c_int, [C.c_void_p, C.c_int, C.c_uint32, C.c_uint32, C.c_uint32,
                                                 _p(TkPlane), C.c_void_p]),

@@ -412,8 +412,8 @@ extern "C" int tk_commit_offsets(tk_ctx* ctx, int slot, void* stream) {
 // that slot's tensor: rows [B + n_kept - carry_out, B + n_kept).  Copy them to
 // rows [B - carry_out, B) of the current tensor (the end of its head region).
 struct carry_args {
-    tk_plane_t prev[4];
-    tk_plane_t cur[4];
+    tk_plane_t prev[TK_MAX_PLANES];
+    tk_plane_t cur[TK_MAX_PLANES];
     int n_planes;
 };
 
@@ -446,7 +446,7 @@ __global__ void __launch_bounds__(256) k_carry_rows(const tk_result_t* __restric
 extern "C" int tk_carry_rows(tk_ctx* ctx, int prev_slot, int n_planes, const tk_plane_t* prev,
                              const tk_plane_t* cur, void* stream) {
     TK_ENTER(ctx, prev_slot);
-    TK_REQUIRE(n_planes >= 1 && n_planes <= 4 && prev && cur, "1..4 planes");
+    TK_REQUIRE(n_planes >= 1 && n_planes <= TK_MAX_PLANES && prev && cur, "1..%d planes", TK_MAX_PLANES);
     carry_args a;
     a.n_planes = n_planes;
     for (int k = 0; k < n_planes; ++k) {

@@ -31,6 +31,12 @@ extern "C" int tk_process_slot(tk_ctx* ctx, int slot, const tk_job_t* job, void*
         case TK_SCHEMA_RAW:
             rc = tk_collate_raw(ctx, slot, job->record_bytes, &job->cur[0], stream);
             break;
+        case TK_SCHEMA_STRUCT:
+            TK_REQUIRE(job->n_planes >= 1 && job->n_planes <= TK_MAX_PLANES, "1..%d struct fields", TK_MAX_PLANES);
+            for (int k = 0; k < job->n_planes && !rc; ++k)
+                rc = tk_collate_field(ctx, slot, job->record_bytes, job->field_offset[k], job->field_bytes[k],
+                                      &job->cur[k], stream);
+            break;
         case TK_SCHEMA_IMAGE:
             rc = tk_collate_image_u8_bf16_nchw(ctx, slot, job->height, job->width, job->channels,
                                                &job->cur[0], stream);

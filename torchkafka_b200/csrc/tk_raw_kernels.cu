@@ -102,6 +102,60 @@ extern "C" int tk_collate_raw(tk_ctx* ctx, int slot, uint64_t record_bytes, cons
     return 0;
 }
 
+// One field of fixed-layout struct records: thread per 4-byte word of the destination row (aligned
+// store; the source is read as two aligned words and funnel-shifted: records and fields sit at
+// arbitrary byte offsets), thread per byte when the field is not a multiple of 4 bytes.
+__global__ void __launch_bounds__(256) k_collate_field(const uint8_t* __restrict__ bytes,
+                                                        const tk_rec_t* __restrict__ recs, uint32_t n,
+                                                        uint32_t field_offset, uint32_t field_bytes, uint32_t units_per_rec,
+                                                        uint32_t unit_bytes, const int32_t* __restrict__ rec_kidx,
+                                                        const int32_t* __restrict__ rec_status, int report,
+                                                        tk_result_t* res, tk_plane_t out) {
+    tk_pdl_wait();
+    tk_pdl_launch_dependents();             // after the wait: see k_commit_final (tk_plan.cu)
+    const uint32_t total = n * units_per_rec;
+    for (uint32_t x = blockIdx.x * blockDim.x + threadIdx.x; x < total; x += gridDim.x * blockDim.x) {
+        const uint32_t i = x / units_per_rec;
+        const uint32_t u = x - i * units_per_rec;
+        const int32_t kidx = rec_kidx[i];
+        if (kidx < 0) {
+            if (u == 0 && report) raw_report_error(res, i, rec_status[i]);
+            continue;
+        }
+        const uint8_t* src = bytes + recs[i].start + field_offset + u * unit_bytes;
+        uint8_t* dst = row_ptr(res, out, (uint32_t)kidx) + u * unit_bytes;
+        if (unit_bytes == 4u) {
+            const uint32_t sh = ((uint32_t)(uintptr_t)src & 3u) * 8u;
+            const uint32_t* s32 = reinterpret_cast<const uint32_t*>(src - ((uintptr_t)src & 3u));
+            *reinterpret_cast<uint32_t*>(dst) = __funnelshift_r(__ldg(s32), __ldg(s32 + 1), sh);
+        } else {
+            *dst = *src;
+        }
+    }
+}
+
+extern "C" int tk_collate_field(tk_ctx* ctx, int slot, uint64_t record_bytes, uint32_t field_offset, uint32_t field_bytes,
+                                const tk_plane_t* out, void* stream) {
+    TK_ENTER(ctx, slot);
+    tk_slot& s = ctx->slots[slot];
+    TK_REQUIRE(out && out->base, "output plane is required");
+    TK_REQUIRE(field_bytes > 0 && (uint64_t)field_offset + field_bytes <= record_bytes, "field outside the record");
+    TK_REQUIRE(out->row_bytes == field_bytes, "row_bytes must equal field_bytes");
+    const uint32_t n = s.n_records;
+    if (n) {
+        const bool words = (field_bytes & 3u) == 0 && ((uintptr_t)out->base & 3u) == 0;
+        const uint32_t unit = words ? 4u : 1u, upr = field_bytes / unit;
+        const uint64_t total = (uint64_t)n * upr;
+        TK_REQUIRE(total < (1ull << 32), "slot too large for 32-bit indexing");
+        const uint64_t want = (total + 255) / 256;
+        const uint32_t blocks = (uint32_t)(want < 148ull * 32 ? want : 148ull * 32);
+        // (records of the wrong size are reported once, by the field at offset 0)
+        TK_LAUNCH_PDL(k_collate_field, blocks, 256, (cudaStream_t)stream, s.d.bytes, s.d.recs, n, field_offset,
+                      field_bytes, upr, unit, s.d.rec_kidx, s.d.rec_status, field_offset == 0 ? 1 : 0, s.d.result, *out);
+    }
+    return 0;
+}
+
 // ---------------------------------------------------------------------- images
 // The normalisation has only 256 x C distinct inputs, so it is evaluated once,
 // exactly (IEEE float32 division and subtraction, round-to-nearest-even bf16),

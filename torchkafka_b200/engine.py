@@ -24,7 +24,7 @@ import numpy as np
 import torch
 
 from . import _native
-from .schema import ImageU8, JsonArray, PayloadError, RawBytes
+from .schema import ImageU8, JsonArray, PayloadError, RawBytes, StructBytes
 
 # one packed record header: tk_rec_t in include/torchkafka_b200.h
 REC_DTYPE = np.dtype([("start", "<u4"), ("partition", "<i4"), ("offset", "<i8")])
@@ -93,7 +93,7 @@ class SlotEngine:
         self.n_slots = int(n_slots)
         self.n_partitions = int(n_partitions)
         self.slot_bytes = int(slot_bytes)
-        if isinstance(schema, (RawBytes, ImageU8)):
+        if isinstance(schema, (RawBytes, ImageU8, StructBytes)):
             rb = schema.record_bytes
             if self.slot_bytes < rb:
                 self.slot_bytes = rb
@@ -227,6 +227,9 @@ class SlotEngine:
             out = torch.empty((rows,) + sc.shape, dtype=sc.dtype, device=dev)
             tensors = [out]
             planes = [(out.data_ptr(), sc.record_bytes)]
+        elif isinstance(sc, StructBytes):
+            tensors = [torch.empty((rows,) + sh, dtype=d, device=dev) for _, d, sh in sc.fields]
+            planes = [(t.data_ptr(), nb) for t, nb in zip(tensors, sc.field_bytes)]
         else:
             raise TypeError(f"unsupported schema {sc!r}")
         arr = (_native.TkPlane * len(planes))()
@@ -245,6 +248,11 @@ class SlotEngine:
             job.schema = 2
             job.height, job.width, job.channels = sc.height, sc.width, sc.channels
             job.record_bytes = sc.record_bytes
+        elif isinstance(sc, StructBytes):
+            job.schema = 3
+            job.record_bytes = sc.record_bytes
+            for k, (off, nb) in enumerate(zip(sc.field_offsets, sc.field_bytes)):
+                job.field_offset[k], job.field_bytes[k] = off, nb
         else:
             job.schema = 1
             job.record_bytes = sc.record_bytes
@@ -298,6 +306,9 @@ class SlotEngine:
                 elif isinstance(sc, ImageU8):
                     _native.check(lib.tk_collate_image_u8_bf16_nchw(ctx, slot, sc.height, sc.width,
                                                                     sc.channels, C.byref(P[0]), st))
+                elif isinstance(sc, StructBytes):
+                    for k, (off, nb) in enumerate(zip(sc.field_offsets, sc.field_bytes)):
+                        _native.check(lib.tk_collate_field(ctx, slot, sc.record_bytes, off, nb, C.byref(P[k]), st))
                 else:
                     _native.check(lib.tk_collate_raw(ctx, slot, sc.record_bytes, C.byref(P[0]), st))
                 ev1.record()
@@ -305,7 +316,7 @@ class SlotEngine:
                     timers.append((ev0, ev1))
                 _native.check(lib.tk_slot_fetch_result(ctx, slot, st))
             self.launches += (LAUNCHES_PER_SLOT_JSON if is_json else LAUNCHES_PER_SLOT_RAW) \
-                - (1 if prev_out is None else 0)
+                - (1 if prev_out is None else 0) + (len(out.planes) - 1 if isinstance(sc, StructBytes) else 0)
             out.done = torch.cuda.Event()
             out.done.record(self.stream)
         return out
@@ -377,6 +388,8 @@ class SlotEngine:
             return sc.wrap(t[0][first_row:first_row + n_rows, :width],
                            t[1][first_row:first_row + n_rows],
                            t[2][first_row:first_row + n_rows, :width])
+        if isinstance(sc, StructBytes):
+            return sc.wrap(*[p[first_row:first_row + n_rows] for p in t])
         return t[0][first_row:first_row + n_rows]
 
     def batch_views(self, out: SlotOutput, first_row: int, n_batches: int, lmax):
@@ -386,6 +399,8 @@ class SlotEngine:
         sc = self.schema
         planes = [p[first_row:first_row + n_batches * B].unflatten(0, (n_batches, B)).unbind(0)
                   for p in out.tensors]
+        if isinstance(sc, StructBytes):
+            return [sc.wrap(*fields) for fields in zip(*planes)]
         if not (isinstance(sc, JsonArray) and sc.fixed_len is None):
             return list(planes[0])
         batches = []

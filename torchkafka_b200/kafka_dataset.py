@@ -275,7 +275,7 @@ class KafkaDataset(IterableDataset):
         to the GPU); ``default_collate`` then stacks them.  Correct but slow:
         ``auto_commit(dataloader)`` or ``device_batches()`` deliver whole batches.
         """
-        from .schema import JsonArray
+        from .schema import JsonArray, StructBytes
         schema = self.payload_schema
         if self.device_batch_size:
             yield from self.device_batches(int(self.device_batch_size), False)
@@ -284,6 +284,8 @@ class KafkaDataset(IterableDataset):
             if isinstance(schema, JsonArray) and schema.fixed_len is None:
                 n = int(batch.lengths[0])
                 yield batch[0][0, :n]
+            elif isinstance(schema, StructBytes):
+                yield tuple(f[0] for f in batch)
             else:
                 yield batch[0]
 

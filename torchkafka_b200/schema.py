@@ -19,6 +19,9 @@ schema           equivalent reference ``_process`` + collate
                  ``input_ids / lengths / attention_mask``
 ``RawBytes``     ``torch.frombuffer(record.value, dtype=dtype).view(shape)``;
                  batches are ``torch.stack``
+``StructBytes``  fixed-layout struct: field k is ``torch.frombuffer(value, dtype_k,
+                 count_k, offset_k).view(shape_k)``; ``_process`` returns the tuple,
+                 ``default_collate`` stacks every field
 ``ImageU8``      HWC uint8 -> ``permute(2,0,1).float().div(255)`` ->
                  ``(x - mean) / std`` in float32 -> ``bfloat16``; batches are
                  ``torch.stack`` ([B, C, H, W])
@@ -132,6 +135,49 @@ class RawBytes:
         for s in self.shape:
             n *= s
         return n * torch.empty((), dtype=self.dtype).element_size()
+
+
+@dataclasses.dataclass(frozen=True)
+class StructBytes:
+    """Fixed-layout binary record made of typed fields laid out back to back (a packed C struct,
+    a numpy structured dtype without padding): ``fields`` is a sequence of
+    ``(name, dtype, shape)``.  Batches are namedtuples with one ``[B, *shape]`` tensor per field.
+    Byte order is the machine's (little endian), as with ``torch.frombuffer``."""
+
+    fields: Sequence[Tuple[str, torch.dtype, Tuple[int, ...]]] = (("x", torch.float32, (1,)),)
+
+    def __post_init__(self):
+        norm = tuple((str(n), d, tuple(int(k) for k in (sh if isinstance(sh, (tuple, list)) else (sh,))))
+                     for n, d, sh in self.fields)
+        if not 1 <= len(norm) <= 8:
+            raise ValueError("1 to 8 fields supported")
+        object.__setattr__(self, "fields", norm)
+        object.__setattr__(self, "_batch_type", collections.namedtuple("StructBatch", [n for n, _, _ in norm]))
+
+    @property
+    def field_bytes(self) -> Tuple[int, ...]:
+        out = []
+        for _, d, sh in self.fields:
+            n = 1
+            for k in sh:
+                n *= k
+            out.append(n * torch.empty((), dtype=d).element_size())
+        return tuple(out)
+
+    @property
+    def field_offsets(self) -> Tuple[int, ...]:
+        off, out = 0, []
+        for b in self.field_bytes:
+            out.append(off)
+            off += b
+        return tuple(out)
+
+    @property
+    def record_bytes(self) -> int:
+        return sum(self.field_bytes)
+
+    def wrap(self, *tensors):
+        return self._batch_type(*tensors)
 
 
 @dataclasses.dataclass(frozen=True)

@@ -15,18 +15,22 @@ from torchkafka_b200.testing import synthetic as syn
 pytestmark = pytest.mark.gpu
 
 
-def run(log, schema, batch_size, repeat, slot_bytes, packed, producers=2):
+def run(log, schema, batch_size, repeat, slot_bytes, packed, producers=2, raw_codec=None, raw_batch_bytes=65536):
+    """packed: False = poll() objects, True = poll_packed() arrays; raw_codec not None: poll_raw()
+    record batches (0 plain, 3 / "lz4i" LZ4, 2 snappy)."""
     consumer_cls = sk.KafkaConsumer if packed else sk.PollOnlyConsumer
 
     class DS(KafkaDataset):
         payload_schema = schema
         device_slot_bytes = slot_bytes
         device_producers = producers
+        device_input = "auto" if raw_codec is None else "raw"
 
         @classmethod
         def new_consumer(cls, *a, **k):
             k.pop("enable_auto_commit", None)
-            return consumer_cls(*a, log=log, repeat=repeat, **k)
+            return consumer_cls(*a, log=log, repeat=repeat, raw_codec=raw_codec or 0,
+                                raw_batch_bytes=raw_batch_bytes, **k)
 
     ds = DS("topic", group_id="prop")
     sums, rows, n_batches = [], 0, 0
@@ -87,3 +91,17 @@ def test_cfg5_raw_records_commit_equals_log_positions():
     assert a[3] == expected_positions(base, 5)
     total = int(np.frombuffer(base.values, np.uint8).astype(np.int64).sum()) * 5
     assert int(a[0].sum()) == total                    # checksum of checksums over all bytes
+
+
+def test_cfg2_record_batches_and_codecs_give_the_same_batches():
+    """The stream served as ConsumerRecord arrays, as RecordBatch v2 bytes, and as LZ4 / snappy
+    compressed batches (~160 MB of JSON): every batch and the final commit must be identical."""
+    base = syn.make_log(2, 20000, seed=34, layout="chunked", chunk=300)
+    repeat, B = 3, 1024
+    sc = JsonArray(torch.float32, max_len=256, min_size=32)
+    ref = run(base, sc, B, repeat, 48 << 20, packed=True)
+    for codec, bb in [(0, 65536), (0, 1 << 20), ("lz4i", 16384), (3, 65536), (2, 65536)]:
+        got = run(base, sc, B, repeat, 56 << 20, packed=True, raw_codec=codec, raw_batch_bytes=bb)
+        assert got[1] == ref[1] and got[2] == ref[2], codec
+        assert np.array_equal(got[0], ref[0]), codec
+        assert got[3] == ref[3] == expected_positions(base, repeat)

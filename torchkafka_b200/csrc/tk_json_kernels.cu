@@ -10,8 +10,8 @@
 //
 //   k_json_scan      warp per record: element count, head check, keep flag, token array
 //   (compaction and commit offsets: tk_plan.cu)
-//   k_json_rows      warp per kept record: pad, length, mask
-//   k_json_parse<T>  thread per element: text -> value, stored in the record's row
+//   k_json_parse<T>  rows part (pad, length, mask of the kept records) + thread per element:
+//                    text -> value, stored in the record's row
 #include "tk_swar.cuh"
 
 // ---------------------------------------------------------------- K1 phase 1

@@ -18,35 +18,7 @@
 #define CMP_ITEMS 2
 #define CMP_TILE (CMP_THREADS * CMP_ITEMS)
 
-__device__ __forceinline__ uint32_t warp_incl_scan(uint32_t v) {
-#pragma unroll
-    for (int d = 1; d < 32; d <<= 1) {
-        uint32_t t = __shfl_up_sync(0xffffffffu, v, d);
-        if ((threadIdx.x & 31) >= d) v += t;
-    }
-    return v;
-}
-
-// block-wide exclusive scan of one value per thread (blockDim.x <= 1024); returns total via *total
-__device__ __forceinline__ uint32_t block_excl_scan(uint32_t v, uint32_t* total) {
-    __shared__ uint32_t warp_tot[32];
-    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
-    uint32_t incl = warp_incl_scan(v);
-    if (lane == 31) warp_tot[wid] = incl;
-    __syncthreads();
-    if (wid == 0) {
-        uint32_t w = lane < (int)((blockDim.x + 31) >> 5) ? warp_tot[lane] : 0;
-        uint32_t wi = warp_incl_scan(w);
-        warp_tot[lane] = wi - w;                       // exclusive warp offsets
-        if (lane == 31) warp_tot[31] = wi - w, *total = wi;
-    }
-    __syncthreads();
-    uint32_t r = warp_tot[wid] + incl - v;
-    __syncthreads();
-    return r;
-}
-
-// 64-bit variants: the compaction scans two quantities at once, packed as
+// The compaction scans two quantities at once, packed as
 // (kept records << 40) | elements: the second sum is the number of elements in the slot, which
 // sizes the thread-per-element parse kernel of the flat decode path.
 #define PACK_SHIFT 40

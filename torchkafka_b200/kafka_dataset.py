@@ -84,7 +84,7 @@ class KafkaDataset(IterableDataset):
 
     _COMMIT_SIGNAL = _commit_signal()
 
-    #: optional schema (``JsonArray`` / ``TokenList`` / ``RawBytes`` / ``ImageU8``)
+    #: optional schema (``JsonArray`` / ``TokenList`` / ``RawBytes`` / ``StructBytes`` / ``ImageU8``)
     payload_schema = None
     #: GPU-path tuning knobs (bytes per staging slot, slots in flight, device index)
     device_slot_bytes = 64 << 20

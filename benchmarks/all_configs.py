@@ -26,7 +26,7 @@ import torch            # noqa: E402
 
 from torchkafka_b200 import KafkaDataset, auto_commit                                   # noqa: E402
 from torchkafka_b200.engine import SlotEngine                                           # noqa: E402
-from torchkafka_b200.schema import ImageU8, JsonArray, RawBytes, TokenList              # noqa: E402
+from torchkafka_b200.schema import ImageU8, JsonArray, JsonObject, RawBytes, TokenList  # noqa: E402
 from torchkafka_b200.testing import stub_kafka as sk                                    # noqa: E402
 from torchkafka_b200.testing import synthetic as syn                                    # noqa: E402
 
@@ -41,6 +41,9 @@ CONFIGS = {
             n=256, slot_bytes=256 * 150528),
     5: dict(name="cfg5 64-byte records, commit offsets", schema=RawBytes((64,), torch.uint8), batch=256,
             n=262144, slot_bytes=17 << 20),
+    # not a BASELINE config: SURVEY §8f-4, JSON objects with 8 named numeric members + 2 ignored ones
+    6: dict(name="objects, 8 named members of 10", schema=JsonObject(syn.OBJECT_FIELDS, torch.float32), batch=1024,
+            n=65536, slot_bytes=20 << 20),
 }
 
 

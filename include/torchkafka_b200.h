@@ -58,7 +58,8 @@ typedef enum {
     TK_STATUS_UNSUPPORTED = 4,  /* valid JSON outside the numeric-array schema */
     TK_STATUS_SIZE = 5,         /* raw record with the wrong byte count */
     TK_STATUS_RAGGED = 6,       /* fixed_len schema, other length (torch.stack raises) */
-    TK_STATUS_CORRUPT = 7       /* record batch failed its CRC or framing (kafka CorruptRecordException) */
+    TK_STATUS_CORRUPT = 7,      /* record batch failed its CRC or framing (kafka CorruptRecordException) */
+    TK_STATUS_MISSING_KEY = 8   /* JSON object without one of the named fields (KeyError) */
 } tk_status_t;
 
 /* Per-slot result header, written by the kernels, fetched with tk_slot_fetch_result. */
@@ -122,7 +123,9 @@ int tk_h2d_peak_gbs(int device, uint64_t bytes, int iters, double* gbs_out);
  * replaces `len(json.loads(record.value)) < min_size -> None`
  * (README.md:74-77; src/kafka_dataset.py:161-162) */
 int tk_json_scan(tk_ctx* ctx, int slot, uint32_t max_len, uint32_t min_size, void* stream);
-/* raw payloads: every record is kept; wrong byte count -> TK_STATUS_SIZE */
+/* raw payloads: every record is kept; wrong byte count -> TK_STATUS_SIZE
+ * (record_bytes == TK_ANY_RECORD_BYTES: any size; the scan of the JSON-object schema) */
+#define TK_ANY_RECORD_BYTES 0xFFFFFFFFFFFFFFFFull
 int tk_raw_scan(tk_ctx* ctx, int slot, uint64_t record_bytes, void* stream);
 
 /* ---- K2: stream compaction of the keep flags -> row of every kept record,
@@ -175,6 +178,23 @@ int tk_collate_raw(tk_ctx* ctx, int slot, uint64_t record_bytes, const tk_plane_
  * torch.stack (collate.py:275 via the tuple branch) compute. */
 int tk_collate_field(tk_ctx* ctx, int slot, uint64_t record_bytes, uint32_t field_offset, uint32_t field_bytes,
                      const tk_plane_t* out, void* stream);
+/* ---- K1 + K3: JSON objects with named numeric fields ---------
+ * replaces a `_process` of the shape of README.md:72-79 over a dict payload,
+ *     d = json.loads(record.value); torch.tensor([d[k] for k in fields], dtype=...)
+ * and default_collate/torch.stack (collate.py:275): row = the named members in schema order.
+ * The whole record must be what json.loads accepts (other members may hold any JSON value);
+ * a named member must be a number or true/false, the last of duplicate members counts,
+ * a missing one is TK_STATUS_MISSING_KEY.  Reported as TK_STATUS_UNSUPPORTED rather than
+ * decoded: member names written with backslash escapes, nesting deeper than 32, UTF-16/32.
+ * tk_ctx_set_object_fields (synchronous, once per context): `names` = the UTF-8 field names
+ * back to back, name f = [name_offsets[f], name_offsets[f + 1]).  Scan: tk_raw_scan with
+ * TK_ANY_RECORD_BYTES.  values: row_bytes = n_fields * element size. */
+#define TK_MAX_OBJECT_FIELDS 64
+#define TK_MAX_OBJECT_NAME_BYTES 2048
+int tk_ctx_set_object_fields(tk_ctx* ctx, const uint8_t* names, const uint32_t* name_offsets,
+                             uint32_t n_fields, void* stream);
+int tk_json_object_decode(tk_ctx* ctx, int slot, int dtype, const tk_plane_t* values, void* stream);
+
 /* HWC uint8 -> normalised bfloat16 CHW:  bf16(((x / 255) - mean[c]) / std[c]) in
  * float32 with IEEE division, the op order of SURVEY.md §8c */
 int tk_image_set_norm(tk_ctx* ctx, int channels, const float* mean, const float* std, void* stream);
@@ -186,11 +206,12 @@ int tk_collate_image_u8_bf16_nchw(tk_ctx* ctx, int slot, uint32_t height, uint32
  * tk_slot_fetch_result, enqueued on `stream`.  What a host plugin binds in place of
  * the per-record loop KafkaDataset.__iter__ (src/kafka_dataset.py:147-171) + the
  * DataLoader fetch/collate (fetch.py:27-45) + auto_commit's commit (auto_commit.py:55-58). */
-typedef enum { TK_SCHEMA_JSON = 0, TK_SCHEMA_RAW = 1, TK_SCHEMA_IMAGE = 2, TK_SCHEMA_STRUCT = 3 } tk_schema_t;
+typedef enum { TK_SCHEMA_JSON = 0, TK_SCHEMA_RAW = 1, TK_SCHEMA_IMAGE = 2, TK_SCHEMA_STRUCT = 3,
+               TK_SCHEMA_OBJECT = 4 } tk_schema_t;
 #define TK_MAX_PLANES 8
 typedef struct tk_job {
     int32_t    schema;        /* tk_schema_t */
-    int32_t    dtype;         /* JSON: tk_dtype_t */
+    int32_t    dtype;         /* JSON array / object: tk_dtype_t */
     uint32_t   max_len, min_size, fixed_len;            /* JSON */
     uint32_t   height, width, channels;                 /* image */
     uint64_t   record_bytes;                            /* raw / image input bytes per record */

@@ -52,6 +52,18 @@ def process_json(dtype, min_size: int = 0):
     return _process
 
 
+def process_object(fields, dtype):
+    """JSON object with named numeric fields: the README.md:72-79 body with a
+    dict payload -- json.loads, then the named members in schema order as one tensor."""
+    fields = tuple(fields)
+
+    def _process(record):
+        d = json.loads(record.value)
+        return torch.tensor([d[k] for k in fields], dtype=dtype)
+
+    return _process
+
+
 def process_raw(shape, dtype=torch.uint8):
     def _process(record):
         return torch.frombuffer(bytearray(record.value), dtype=dtype).view(*shape)

@@ -7,7 +7,7 @@
 // (tests/test_number_host.py).  Nothing in torchkafka_b200/ loads this library.
 #include <stdint.h>
 #include <string.h>
-#include "../../torchkafka_b200/csrc/tk_json.cuh"
+#include "../../torchkafka_b200/csrc/tk_json_object.cuh"
 
 struct HostReader {
     const uint8_t* p;
@@ -117,4 +117,18 @@ extern "C" int tk_host_strtod_many(const uint8_t* buf, const uint32_t* starts, u
         status[i] = (uint8_t)tk_host_strtod(buf + starts[i], starts[i + 1] - starts[i], &bits[i]);
     }
     return 0;
+}
+
+// One JSON object with named numeric fields (tk_json_object.cuh): row[f] per field, status.
+extern "C" int tk_host_decode_object(const uint8_t* buf, uint32_t len, int kind, const uint8_t* names,
+                                     const uint32_t* name_off, uint32_t n_fields, void* row) {
+    HostReader rd{buf, len};
+    tk_obj_fields ft{names, name_off, n_fields};
+    switch (kind) {
+        case TK_F32: return tk_json_object_record<TK_F32>(rd, 0, ft, (float*)row);
+        case TK_F64: return tk_json_object_record<TK_F64>(rd, 0, ft, (double*)row);
+        case TK_I32: return tk_json_object_record<TK_I32>(rd, 0, ft, (int32_t*)row);
+        case TK_I64: return tk_json_object_record<TK_I64>(rd, 0, ft, (int64_t*)row);
+    }
+    return -1;
 }

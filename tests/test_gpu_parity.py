@@ -347,3 +347,86 @@ def test_struct_record_of_wrong_size_raises():
     with pytest.raises(PayloadError) as ei:
         run_gpu(log, schema, 8)
     assert ei.value.status == 5 and (ei.value.partition, ei.value.offset) == (17 % 4, 17 // 4)
+
+
+# ---------------------------------------------------------------- JSON objects with named fields (§8f-4)
+OBJ_FIELDS = ("x", "y", "z", "w", "vx", "vy", "vz", "t")
+
+
+def object_log(n, seed, partitions=4, **kw):
+    vals = syn.object_values(n, seed, OBJ_FIELDS, **kw)
+    i = np.arange(n)
+    return RecordLog(vals, i % partitions, i // partitions)
+
+
+@pytest.mark.parametrize("dtype", [torch.float32, torch.float64, torch.int32, torch.int64])
+def test_object_records_every_dtype(dtype):
+    from torchkafka_b200.schema import JsonObject
+    log = object_log(3000, seed=51)
+    gpu = check(log, JsonObject(OBJ_FIELDS, dtype), 64)
+    assert gpu[0][0].shape == (64, len(OBJ_FIELDS)) and gpu[0][0].dtype == dtype
+
+
+def test_object_records_small_slots_subset_of_fields_and_reordered_columns():
+    from torchkafka_b200.schema import JsonObject
+    log = object_log(2000, seed=52)
+    check(log, JsonObject(("t", "x", "vz"), torch.float32), 7, slot_bytes=6000)     # many slots, carried rows
+
+
+def test_object_records_layouts_the_scanner_must_get_right():
+    """White space, member order, duplicates, bools, ignored members of every kind, non-ASCII,
+    records longer than a warp's window (scanned from global memory), empty strings."""
+    from torchkafka_b200.schema import JsonObject
+    rng = np.random.default_rng(53)
+    vals = [
+        b'{"a": 1.5, "b": -2, "c": 3e4}',
+        b'\xef\xbb\xbf \r\n{ "c" : 3 ,\t"b" : 2 , "a" : 1 } \n',
+        b'{"a": 1, "a": "x", "a": 2.25, "b": true, "c": false}',
+        b'{"a": 1e999, "a": 7, "b": 0, "c": -0.0, "b": -0}',
+        '{"s": "h\\u00e9llo \\"q\\" \\\\ 世界 \U0001F600", "a": 1.0000000596046448, "n": null, "b": 16777217, '
+        '"l": [1, [2, {"k": []}], {}], "c": 1152921573326323713, "": {"a": "not this one"}}'.encode(),
+        b'{"pad": "' + b"x" * 7000 + b'", "a": 1, "b": 2, "c": 3}',                 # longer than the window
+        b'{"a": NaN, "b": -Infinity, "c": 8.41e21, "big": ' + b"9" * 4300 + b"}",
+        b'{"a":0.1,"b":1e23,"c":4.9e-324}',
+    ]
+    vals += [json.dumps({"pad": "y" * int(rng.integers(0, 3000)), "c": float(rng.normal()), "a": int(rng.integers(-99, 99)),
+                         "b": float(rng.uniform(-1, 1))}).encode() for _ in range(200)]
+    i = np.arange(len(vals))
+    log = RecordLog(vals, i % 3, i // 3)
+    for dtype in (torch.float32, torch.float64):
+        check(log, JsonObject(("a", "b", "c"), dtype), 5)
+
+
+OBJ_BAD = [(b'{"a": 1, "b": 2}', 8), (b'{"a": 1, "b": 2, "c": null}', 4), (b'{"a": 1, "b": 2, "c": [3]}', 4),
+           (b'{"a": 1, "b": 2, "c": "3"}', 4), (b'{"a": 1, "b": 2, "c": 3,}', 1), (b'{"a": 1, "b": 2, "c": 3} x', 1),
+           (b'[1, 2, 3]', 4), (b'', 1), (b'{"a": 1, "b": 2, "c": 3, "s": "\\x"}', 1),
+           (b'{"a": 1, "b": 2, "c": 3, "s": "\xc0\xaf"}', 1), (b'{"a": 1, "b": 2, "c": 01}', 1),
+           (b'{"a": 1, "b": 2, "c": 3', 1), (b'{"a": 1, "b": 2, "c": ' + b"9" * 400 + b'}', 2)]
+
+
+@pytest.mark.parametrize("bad,status", OBJ_BAD)
+def test_object_bad_payload_raises_like_reference(bad, status):
+    from torchkafka_b200.schema import JsonObject
+    good = [b'{"a": 1, "b": 2, "c": 3}'] * 5
+    vals = good[:3] + [bad] + good[3:]
+    i = np.arange(len(vals))
+    log = RecordLog(vals, i % 2, i // 2)
+    sc = JsonObject(("a", "b", "c"), torch.float32)
+    with pytest.raises(Exception):
+        run_oracle(log, sc, 2)
+    with pytest.raises(PayloadError) as ei:
+        run_gpu(log, sc, 2)
+    assert (ei.value.partition, ei.value.offset, ei.value.status) == (1, 1, status)
+
+
+def test_object_int_targets_overflow_and_truncation():
+    from torchkafka_b200.schema import JsonObject
+    sc = JsonObject(("a", "b"), torch.int32)
+    check(RecordLog([b'{"a": 1.5, "b": -2147483648}', b'{"b": true, "a": 2147483647}'], [0, 0], [0, 1]), sc, 2)
+    for bad in (b'{"a": 2147483648, "b": 0}', b'{"a": NaN, "b": 0}', b'{"a": 1e30, "b": 0}'):
+        log = RecordLog([bad], [0], [0])
+        with pytest.raises(Exception):
+            run_oracle(log, sc, 1)
+        with pytest.raises(PayloadError) as ei:
+            run_gpu(log, sc, 1)
+        assert ei.value.status == 2

@@ -153,6 +153,28 @@ def test_fetch_offset_skips_records_and_control_batches_are_invisible():
     assert commits == [{2: 16}, {2: 20}]
 
 
+def test_fetch_offset_skips_records_of_raw_and_struct_schemas_too():
+    """Records below the fetch position are not errors for the collate kernels either."""
+    from torchkafka_b200.schema import StructBytes
+    vals = [bytes([i]) * 8 for i in range(10, 20)]
+    blob = rb.encode_batch(10, vals[:6]) + rb.encode_batch(16, vals[6:])
+    out, commits = run_blobs([(2, blob, 13, 0)], RawBytes((8,), torch.uint8), 3)
+    assert torch.cat([b.cpu() for b in out])[:, 0].tolist() == [13, 14, 15, 16, 17, 18, 19]
+    assert commits == [{2: 16}, {2: 19}, {2: 20}]
+    out, _ = run_blobs([(2, blob, 13, 0)], StructBytes((("a", torch.uint8, (3,)), ("b", torch.uint8, (5,)))), 4)
+    assert torch.cat([b.b.cpu() for b in out])[:, 4].tolist() == [13, 14, 15, 16, 17, 18, 19]
+
+
+def test_objects_from_record_batches():
+    from torchkafka_b200.schema import JsonObject
+    fields = ("x", "y", "z", "w", "vx", "vy", "vz", "t")
+    vals = syn.object_values(4000, 26, fields)
+    part, off = syn._coords(4000, 8, "chunked", 50)         # noqa: SLF001
+    log = RecordLog(vals, part, off)
+    check_raw(log, JsonObject(fields, torch.float32), 128)
+    check_raw(log, JsonObject(("t", "x"), torch.int64), 100, batch_bytes=4096, codec="lz4i")
+
+
 @pytest.mark.parametrize("damage,status", [("crc", 7), ("varint", 7), ("magic", 7), ("count", 7), ("codec", 4), ("null", 4)])
 def test_broken_batches_raise_at_their_batch(damage, status):
     good = rb.encode_batch(0, jvals(0, 4))

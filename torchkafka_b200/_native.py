@@ -67,6 +67,7 @@ STATUS_NAMES = {
     5: "raw record has the wrong byte count",
     6: "record length differs from the schema's fixed_len (torch.stack would raise)",
     7: "record batch failed its CRC-32C or its record framing (CorruptRecordException in kafka-python)",
+    8: "JSON object without one of the schema's fields (KeyError in the reference)",
 }
 
 _p = C.POINTER
@@ -98,6 +99,8 @@ _SIGNATURES = {
                                       _p(TkPlane), _p(TkPlane), C.c_void_p]),
     "tk_collate_raw": (C.c_int, [C.c_void_p, C.c_int, C.c_uint64, _p(TkPlane), C.c_void_p]),
     "tk_collate_field": (C.c_int, [C.c_void_p, C.c_int, C.c_uint64, C.c_uint32, C.c_uint32, _p(TkPlane), C.c_void_p]),
+    "tk_ctx_set_object_fields": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint32, C.c_void_p]),
+    "tk_json_object_decode": (C.c_int, [C.c_void_p, C.c_int, C.c_int, _p(TkPlane), C.c_void_p]),
     "tk_image_set_norm": (C.c_int, [C.c_void_p, C.c_int, _p(C.c_float), _p(C.c_float), C.c_void_p]),
     "tk_collate_image_u8_bf16_nchw": (C.c_int, [C.c_void_p, C.c_int, C.c_uint32, C.c_uint32, C.c_uint32,
                                                 _p(TkPlane), C.c_void_p]),

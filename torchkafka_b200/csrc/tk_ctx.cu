@@ -184,6 +184,7 @@ extern "C" int tk_ctx_destroy(tk_ctx* ctx) {
     cudaFree(ctx->d_state);
     cudaFree(ctx->d_positions);
     cudaFree(ctx->d_image_lut);
+    cudaFree(ctx->d_obj_table);
     if (ctx->copy_stream) cudaStreamDestroy(ctx->copy_stream);
     delete ctx;
     return 0;

@@ -134,6 +134,9 @@ struct tk_ctx {
     int       image_fma;       // 1: fused multiply-add reproduces the exact table for all 256 x C inputs
     float     image_a[4], image_b[4];   // y = fma(float(x), a[c], b[c])
     int       timing;          // tk_ctx_set_timing
+    uint8_t*  d_obj_table;     // JSON-object schema: name offsets [65] then the names (tk_json_object.cu)
+    uint32_t  obj_fields;      // 0: no field table set
+    uint32_t  obj_name_bytes;
     tk_slot*  slots;
 };
 

@@ -1,0 +1,179 @@
+// tk_json_object.cu -- K1 + K3 for JSON objects with named numeric fields.
+//
+// Replaces, per record, a user hook of the shape of README.md:72-79 with a dict payload
+//     d = json.loads(record.value)
+//     return torch.tensor([d[k] for k in fields], dtype=...)
+// and, per batch, default_collate -> torch.stack (collate.py:275): row k of the batch holds the
+// named members of kept record k in schema order.  Grammar and conversions: tk_json_object.cuh.
+//
+//   (scan: tk_raw_scan with TK_ANY_RECORD_BYTES -- every record is kept; compaction and commit
+//    offsets: tk_plan.cu)
+//   k_json_object<T>  thread per record.  An object is a chain of dependent decisions (string
+//                     ends, member names, nesting), so a record is scanned sequentially; the
+//                     parallelism is across records.  A warp takes the next run of consecutive
+//                     records that fits its shared-memory window (they lie back to back in the
+//                     slot's byte buffer), brings the run in with coalesced 16-byte loads, and
+//                     every lane scans its own record out of shared memory and writes its row.
+//                     A record larger than the window is scanned from global memory by one lane.
+#include "tk_swar.cuh"
+#include "tk_json_object.cuh"
+
+#define OBJ_THREADS 128
+#define OBJ_WARPS (OBJ_THREADS / 32)
+#define OBJ_WINDOW 6144u                                   // bytes of shared memory per warp
+#define OBJ_TABLE_OFFSETS ((TK_OBJ_MAX_FIELDS + 1) * 4)    // device table: offsets, then names
+
+struct ObjSharedReader {
+    const uint8_t* win;
+    uint32_t base, end;
+    __device__ __forceinline__ int operator()(uint32_t pos) const { return pos < end ? (int)win[pos - base] : -1; }
+};
+struct ObjGlobalReader {
+    const uint8_t* bytes;
+    uint32_t end;
+    __device__ __forceinline__ int operator()(uint32_t pos) const { return pos < end ? (int)bytes[pos] : -1; }
+};
+
+struct obj_args {
+    const uint8_t*  bytes;
+    const tk_rec_t* recs;
+    uint32_t        n;
+    const int32_t*  rec_kidx;
+    int32_t*        rec_status;
+    tk_result_t*    res;
+    const uint8_t*  table;
+    uint32_t        n_fields, name_bytes;
+    tk_plane_t      values;
+};
+
+template <int KIND>
+__global__ void __launch_bounds__(OBJ_THREADS) k_json_object(const obj_args a) {
+    typedef typename tk_elem<KIND>::type T;
+    __shared__ __align__(16) uint8_t win[OBJ_WARPS][OBJ_WINDOW];
+    __shared__ uint32_t s_off[TK_OBJ_MAX_FIELDS + 1];
+    __shared__ uint8_t s_names[TK_MAX_OBJECT_NAME_BYTES];
+    // the field table was written by tk_ctx_set_object_fields (synchronous): not data of the chain
+    for (uint32_t k = threadIdx.x; k <= a.n_fields; k += OBJ_THREADS) s_off[k] = reinterpret_cast<const uint32_t*>(a.table)[k];
+    for (uint32_t k = threadIdx.x; k < a.name_bytes; k += OBJ_THREADS) s_names[k] = a.table[OBJ_TABLE_OFFSETS + k];
+    __syncthreads();
+    tk_pdl_wait();
+    tk_pdl_launch_dependents();             // after the wait: see k_commit_final (tk_plan.cu)
+    const tk_obj_fields ft = {s_names, s_off, a.n_fields};
+    const uint32_t B = a.res->batch_size;
+    const uint32_t lane = threadIdx.x & 31;
+    const uint32_t warp = (blockIdx.x * OBJ_THREADS + threadIdx.x) >> 5;
+    const uint32_t nwarps = (gridDim.x * OBJ_THREADS) >> 5;
+    uint8_t* w = win[threadIdx.x >> 5];
+    for (uint32_t g0 = warp * 32; g0 < a.n; g0 += nwarps * 32) {
+        const uint32_t gend = min(g0 + 32u, a.n);
+        uint32_t g = g0;
+        while (g < gend) {                                  // warp-uniform
+            const uint32_t i = g + lane;
+            const bool have = i < gend;
+            uint32_t my_start = 0, my_end = 0;
+            int32_t kidx = -1;
+            if (have) {
+                my_start = a.recs[i].start;
+                my_end = a.recs[i + 1].start;
+                kidx = a.rec_kidx[i];
+            }
+            const uint32_t base = __shfl_sync(0xffffffffu, my_start, 0) & ~15u;
+            const uint32_t fits = __ballot_sync(0xffffffffu, have && my_end - base <= OBJ_WINDOW);
+            const uint32_t k = fits == 0xffffffffu ? 32u : (uint32_t)__ffs((int)~fits) - 1u;   // leading records that fit
+            int st = TK_OK;
+            bool mine = false;
+            if (k == 0) {
+                // the first record alone exceeds the window
+                if (lane == 0 && kidx >= 0) {
+                    const ObjGlobalReader rd = {a.bytes, my_end};
+                    T* row = reinterpret_cast<T*>((uint8_t*)a.values.base + ((uint64_t)B + (uint32_t)kidx) * a.values.row_bytes);
+                    st = tk_json_object_record<KIND>(rd, my_start, ft, row);
+                }
+                mine = lane == 0;
+                g += 1;
+            } else {
+                const uint32_t span_end = __shfl_sync(0xffffffffu, my_end, (int)k - 1);
+                for (uint32_t off = lane * 16; base + off < span_end; off += 512)      // (the slot buffer is padded)
+                    *reinterpret_cast<uint4*>(w + off) = __ldg(reinterpret_cast<const uint4*>(a.bytes + base + off));
+                __syncwarp();
+                mine = lane < k;
+                if (mine && kidx >= 0) {
+                    const ObjSharedReader rd = {w, base, my_end};
+                    T* row = reinterpret_cast<T*>((uint8_t*)a.values.base + ((uint64_t)B + (uint32_t)kidx) * a.values.row_bytes);
+                    st = tk_json_object_record<KIND>(rd, my_start, ft, row);
+                }
+                __syncwarp();                               // the window is reused by the next run
+                g += k;
+            }
+            if (mine) {
+                if (st) { a.rec_status[i] = st; report_error(a.res, i, st); }
+                else if (kidx < 0) {                        // flagged by the record-batch split
+                    const int pre = a.rec_status[i];
+                    if (pre) report_error(a.res, i, pre);
+                }
+            }
+        }
+    }
+}
+
+// Field names of the object schema: `names` holds the UTF-8 names back to back, name f is
+// [name_offsets[f], name_offsets[f + 1]).  Synchronous (set once per context, before the first slot).
+extern "C" int tk_ctx_set_object_fields(tk_ctx* ctx, const uint8_t* names, const uint32_t* name_offsets,
+                                        uint32_t n_fields, void* stream) {
+    TK_REQUIRE(ctx, "null context");
+    TK_CUDA(cudaSetDevice(ctx->device));
+    TK_REQUIRE(names && name_offsets, "names / name_offsets are null");
+    TK_REQUIRE(n_fields >= 1 && n_fields <= TK_OBJ_MAX_FIELDS, "1..%d fields", TK_OBJ_MAX_FIELDS);
+    TK_REQUIRE(name_offsets[0] == 0, "name_offsets must start at 0");
+    for (uint32_t f = 0; f < n_fields; ++f)
+        TK_REQUIRE(name_offsets[f + 1] >= name_offsets[f], "name_offsets must not decrease");
+    const uint32_t nb = name_offsets[n_fields];
+    TK_REQUIRE(nb <= TK_MAX_OBJECT_NAME_BYTES, "field names take %u bytes, at most %d", nb, TK_MAX_OBJECT_NAME_BYTES);
+    for (uint32_t f = 0; f < n_fields; ++f)
+        for (uint32_t g = f + 1; g < n_fields; ++g) {
+            const uint32_t lf = name_offsets[f + 1] - name_offsets[f], lg = name_offsets[g + 1] - name_offsets[g];
+            TK_REQUIRE(lf != lg || memcmp(names + name_offsets[f], names + name_offsets[g], lf) != 0,
+                       "fields %u and %u have the same name", f, g);
+        }
+    uint8_t host[OBJ_TABLE_OFFSETS + TK_MAX_OBJECT_NAME_BYTES];
+    memset(host, 0, sizeof(host));
+    memcpy(host, name_offsets, sizeof(uint32_t) * (n_fields + 1));
+    memcpy(host + OBJ_TABLE_OFFSETS, names, nb);
+    cudaStream_t st = (cudaStream_t)stream;
+    TK_CUDA(cudaStreamSynchronize(st));                      // kernels still reading the previous table
+    if (!ctx->d_obj_table) TK_CUDA(cudaMalloc(&ctx->d_obj_table, sizeof(host)));
+    TK_CUDA(cudaMemcpyAsync(ctx->d_obj_table, host, sizeof(host), cudaMemcpyHostToDevice, st));
+    TK_CUDA(cudaStreamSynchronize(st));
+    ctx->obj_fields = n_fields;
+    ctx->obj_name_bytes = nb;
+    return 0;
+}
+
+extern "C" int tk_json_object_decode(tk_ctx* ctx, int slot, int dtype, const tk_plane_t* values, void* stream) {
+    TK_ENTER(ctx, slot);
+    tk_slot& s = ctx->slots[slot];
+    TK_REQUIRE(values && values->base, "values plane is required");
+    TK_REQUIRE(dtype >= TK_DTYPE_F32 && dtype <= TK_DTYPE_I64, "unknown dtype %d", dtype);
+    TK_REQUIRE(ctx->obj_fields, "tk_ctx_set_object_fields must be called first");
+    const uint32_t esize = (dtype == TK_DTYPE_F32 || dtype == TK_DTYPE_I32) ? 4u : 8u;
+    TK_REQUIRE(values->row_bytes == (uint64_t)ctx->obj_fields * esize && ((uintptr_t)values->base & (esize - 1)) == 0,
+               "values rows must hold %u elements of %u bytes", ctx->obj_fields, esize);
+    const uint32_t n = s.n_records;
+    if (!n) return 0;
+    obj_args a;
+    a.bytes = s.d.bytes; a.recs = s.d.recs; a.n = n;
+    a.rec_kidx = s.d.rec_kidx; a.rec_status = s.d.rec_status; a.res = s.d.result;
+    a.table = ctx->d_obj_table; a.n_fields = ctx->obj_fields;
+    a.name_bytes = ctx->obj_name_bytes;
+    a.values = *values;
+    const uint32_t warps = (n + 31) / 32;
+    const uint32_t blocks = min((warps + OBJ_WARPS - 1) / OBJ_WARPS, 148u * 8u);
+    cudaStream_t st = (cudaStream_t)stream;
+    switch (dtype) {
+        case TK_DTYPE_F32: TK_LAUNCH_PDL(k_json_object<TK_F32>, blocks, OBJ_THREADS, st, a); break;
+        case TK_DTYPE_F64: TK_LAUNCH_PDL(k_json_object<TK_F64>, blocks, OBJ_THREADS, st, a); break;
+        case TK_DTYPE_I32: TK_LAUNCH_PDL(k_json_object<TK_I32>, blocks, OBJ_THREADS, st, a); break;
+        default:           TK_LAUNCH_PDL(k_json_object<TK_I64>, blocks, OBJ_THREADS, st, a); break;
+    }
+    return 0;
+}

@@ -9,6 +9,7 @@
 #include "tk_internal.h"
 
 __device__ __forceinline__ void raw_report_error(tk_result_t* res, uint32_t rec, int status) {
+    if (status == TK_STATUS_OK) return;      // not kept and no error: skipped by the record-batch split
     atomicAdd(&res->n_errors, 1u);
     const uint32_t prev = atomicMin(&res->first_error_rec, rec);
     if (rec < prev) res->first_error_status = (uint32_t)status;
@@ -33,7 +34,7 @@ __global__ void __launch_bounds__(256) k_raw_scan(const tk_rec_t* __restrict__ r
         rec_kidx[i] = -1;
         return;
     }
-    const bool ok = len == record_bytes;
+    const bool ok = len == record_bytes || record_bytes == TK_ANY_RECORD_BYTES;
     rec_status[i] = ok ? TK_STATUS_OK : TK_STATUS_SIZE;
     rec_kidx[i] = ok ? 0 : -1;
 }

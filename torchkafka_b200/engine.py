@@ -12,7 +12,8 @@ Kernel sequence per slot (all on the caller's current CUDA stream):
     tk_json_scan | tk_raw_scan      element count / size check, keep flag (K1 phase 1)
     tk_compact          filter compaction, batch boundaries (K2)
     tk_commit_offsets   per batch, per partition commit offsets (K4)
-    tk_json_decode | tk_collate_raw | tk_collate_image_u8_bf16_nchw   (K1 phase 2 + K3)
+    tk_json_decode | tk_json_object_decode | tk_collate_raw | tk_collate_field |
+    tk_collate_image_u8_bf16_nchw   (K1 phase 2 + K3)
     tk_slot_fetch_result            async D2H of the small result block
 """
 from __future__ import annotations
@@ -24,7 +25,7 @@ import numpy as np
 import torch
 
 from . import _native
-from .schema import ImageU8, JsonArray, PayloadError, RawBytes, StructBytes
+from .schema import ImageU8, JsonArray, JsonObject, PayloadError, RawBytes, StructBytes
 
 # one packed record header: tk_rec_t in include/torchkafka_b200.h
 REC_DTYPE = np.dtype([("start", "<u4"), ("partition", "<i4"), ("offset", "<i8")])
@@ -121,6 +122,13 @@ class SlotEngine:
             with torch.cuda.device(self.device):
                 _native.check(self.lib.tk_image_set_norm(self.ctx, schema.channels, mean, std,
                                                          self._stream()))
+        if isinstance(schema, JsonObject):
+            names, offs = schema.name_table()
+            blob = np.frombuffer(names, dtype=np.uint8).copy()
+            off = np.asarray(offs, dtype=np.uint32)
+            with torch.cuda.device(self.device):
+                _native.check(self.lib.tk_ctx_set_object_fields(self.ctx, blob.ctypes.data, off.ctypes.data,
+                                                                len(schema.fields), self._stream()))
         self.launches = 0
         #: use the earlier warp-per-record decode kernel (tk_json_decode_warp) instead of the flat
         #: token-array path; kept for cross-checks and comparison runs
@@ -219,6 +227,10 @@ class SlotEngine:
                 mask = torch.empty((rows, sc.max_len), dtype=torch.bool, device=dev)
                 tensors += [lengths, mask]
                 planes += [(lengths.data_ptr(), 4), (mask.data_ptr(), sc.max_len)]
+        elif isinstance(sc, JsonObject):
+            values = torch.empty((rows, len(sc.fields)), dtype=sc.dtype, device=dev)
+            tensors = [values]
+            planes = [(values.data_ptr(), len(sc.fields) * values.element_size())]
         elif isinstance(sc, ImageU8):
             out = torch.empty((rows, sc.channels, sc.height, sc.width), dtype=torch.bfloat16, device=dev)
             tensors = [out]
@@ -244,6 +256,8 @@ class SlotEngine:
         if isinstance(sc, JsonArray):
             job.schema, job.dtype = 0, sc.kind
             job.max_len, job.min_size, job.fixed_len = sc.max_len, sc.min_size, sc.fixed_len or 0
+        elif isinstance(sc, JsonObject):
+            job.schema, job.dtype = 4, sc.kind
         elif isinstance(sc, ImageU8):
             job.schema = 2
             job.height, job.width, job.channels = sc.height, sc.width, sc.channels
@@ -289,6 +303,8 @@ class SlotEngine:
                                                     out.planes, st))
                 if is_json:
                     _native.check(lib.tk_json_scan(ctx, slot, sc.max_len, sc.min_size, st))
+                elif isinstance(sc, JsonObject):
+                    _native.check(lib.tk_raw_scan(ctx, slot, 0xFFFFFFFFFFFFFFFF, st))     # TK_ANY_RECORD_BYTES
                 else:
                     _native.check(lib.tk_raw_scan(ctx, slot, sc.record_bytes, st))
                 _native.check(lib.tk_compact(ctx, slot, self.batch_size, st))
@@ -303,6 +319,8 @@ class SlotEngine:
                     _native.check(decode(
                         ctx, slot, sc.kind, sc.max_len, sc.fixed_len or 0, C.byref(P[0]),
                         C.byref(P[1]) if variable else None, C.byref(P[2]) if variable else None, st))
+                elif isinstance(sc, JsonObject):
+                    _native.check(lib.tk_json_object_decode(ctx, slot, sc.kind, C.byref(P[0]), st))
                 elif isinstance(sc, ImageU8):
                     _native.check(lib.tk_collate_image_u8_bf16_nchw(ctx, slot, sc.height, sc.width,
                                                                     sc.channels, C.byref(P[0]), st))

@@ -17,6 +17,9 @@ schema           equivalent reference ``_process`` + collate
                  cannot batch ragged samples)
 ``TokenList``    ``JsonArray`` with an integer dtype, batches named
                  ``input_ids / lengths / attention_mask``
+``JsonObject``   ``d = json.loads(record.value)``;
+                 ``torch.tensor([d[k] for k in fields], dtype=dtype)``; batches are
+                 ``torch.stack`` ([B, len(fields)])
 ``RawBytes``     ``torch.frombuffer(record.value, dtype=dtype).view(shape)``;
                  batches are ``torch.stack``
 ``StructBytes``  fixed-layout struct: field k is ``torch.frombuffer(value, dtype_k,
@@ -117,6 +120,50 @@ class TokenList(JsonArray):
         if self.fixed_len is not None:
             return values
         return TokenBatch(values, lengths, mask)
+
+
+@dataclasses.dataclass(frozen=True)
+class JsonObject:
+    """A JSON object whose named members are numbers: ``fields`` are the member names, in the
+    order of the columns of the ``[B, len(fields)]`` batch.
+
+    The whole record must be valid JSON as ``json.loads`` sees it; members not named in
+    ``fields`` may hold anything and are ignored.  A named member must be a number (or
+    ``true`` / ``false``, which ``torch.tensor`` stores as 1 / 0); of duplicate members the last
+    one counts; a missing one is an error (``KeyError`` in the reference).  Reported as errors
+    rather than decoded: member names written with backslash escapes, values nested deeper
+    than 32 levels, UTF-16/32 payloads.
+    """
+
+    fields: Sequence[str] = ("x",)
+    dtype: torch.dtype = torch.float32
+
+    def __post_init__(self):
+        if self.dtype not in _JSON_DTYPES:
+            raise TypeError(f"JsonObject does not support dtype {self.dtype}")
+        names = tuple(str(f) for f in self.fields)
+        if not 1 <= len(names) <= 64:
+            raise ValueError("1 to 64 fields supported")
+        if len(set(names)) != len(names):
+            raise ValueError("field names must be distinct")
+        for f in names:
+            if '"' in f or "\\" in f or any(ord(ch) < 0x20 for ch in f):
+                raise ValueError(f"field name {f!r} cannot appear unescaped in JSON")
+        if sum(len(f.encode("utf-8", "surrogatepass")) for f in names) > 2048:
+            raise ValueError("field names take more than 2048 bytes")
+        object.__setattr__(self, "fields", names)
+
+    @property
+    def kind(self) -> int:
+        return _JSON_DTYPES[self.dtype]
+
+    def name_table(self):
+        """(names back to back as bytes, offsets) for tk_ctx_set_object_fields."""
+        enc = [f.encode("utf-8", "surrogatepass") for f in self.fields]
+        offs = [0]
+        for b in enc:
+            offs.append(offs[-1] + len(b))
+        return b"".join(enc), offs
 
 
 @dataclasses.dataclass(frozen=True)

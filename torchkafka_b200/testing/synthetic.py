@@ -74,12 +74,33 @@ def cfg5_values(n: int, seed: int = 0, size: int = 64) -> List[bytes]:
     return [blob[i * size:(i + 1) * size] for i in range(n)]
 
 
-_GEN = {1: cfg1_values, 2: cfg2_values, 3: cfg3_values, 4: cfg4_values, 5: cfg5_values}
+def object_values(n: int, seed: int = 0, fields=("x", "y", "z", "w", "vx", "vy", "vz", "t"),
+                  extras: bool = True) -> List[bytes]:
+    """JSON objects with named numeric members: floats uniform(-1e3, 1e3) and a
+    few ints under `fields`, plus (``extras``) an id string and a tag list the schema ignores."""
+    rng = random.Random(seed)
+    u = rng.uniform
+    out = []
+    for i in range(n):
+        d = {}
+        if extras:
+            d["id"] = "sensor-%06d" % rng.randrange(10 ** 6)
+        for k, f in enumerate(fields):
+            d[f] = rng.randrange(-1000, 1000) if k % 4 == 3 else u(-1e3, 1e3)
+        if extras:
+            d["tags"] = ["a", {"n": i % 7}]
+        out.append(json.dumps(d).encode())
+    return out
+
+
+OBJECT_FIELDS = ("x", "y", "z", "w", "vx", "vy", "vz", "t")
+_GEN = {1: cfg1_values, 2: cfg2_values, 3: cfg3_values, 4: cfg4_values, 5: cfg5_values, 6: object_values}
 
 
 def make_log(cfg: int, n: int, seed: int = 0, partitions: int = 64,
              layout: str = "roundrobin", chunk: int = 500, **kw) -> RecordLog:
-    """RecordLog for BASELINE config ``cfg`` (1..5) with ``n`` records."""
+    """RecordLog for BASELINE config ``cfg`` (1..5) with ``n`` records (6: JSON objects with the
+    named numeric members OBJECT_FIELDS, SURVEY.md §8f-4 -- not a BASELINE config)."""
     return _log(_GEN[cfg](n, seed, **kw), partitions, layout, chunk)
 
 

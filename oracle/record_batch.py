@@ -17,7 +17,8 @@ Semantics restated from kafka-python's fetcher:
     block formats below (lz4_Frame_format.md / lz4_Block_format.md of the LZ4 project; xxHash
     checksums are skipped, the batch CRC covers the same bytes); snappy batches (codec 2) with the
     restatement of snappy's format_description.txt, raw or in snappy-java's xerial framing (what
-    kafka-python's snappy_decode accepts); gzip and zstd raise UnsupportedBatch;
+    kafka-python's snappy_decode accepts); gzip batches (codec 1) with CPython's own gzip module,
+    which is what kafka-python's gzip_decode calls; zstd raises UnsupportedBatch;
   * control batches (attributes bit 5) carry no user records and are skipped.
 Pure Python, byte at a time: for small cases.
 """
@@ -252,6 +253,12 @@ def split_blob(blob: bytes, partition: int, fetch_offset: int = 0, offset_delta:
             body = lz4_frame_decode(bytes(blob[pos + HEADER_BYTES:end]))
         elif codec == 2:
             body = snappy_decode(bytes(blob[pos + HEADER_BYTES:end]))
+        elif codec == 1:
+            import gzip
+            try:
+                body = gzip.decompress(bytes(blob[pos + HEADER_BYTES:end]))
+            except Exception as e:                           # noqa: BLE001 (zlib.error, BadGzipFile, EOFError)
+                raise CorruptRecordError(f"gzip: {e}") from e
         elif codec:
             raise UnsupportedBatch(f"compression codec {codec}")
         else:

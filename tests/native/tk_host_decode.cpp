@@ -8,6 +8,7 @@
 #include <stdint.h>
 #include <string.h>
 #include "../../torchkafka_b200/csrc/tk_json_object.cuh"
+#include "../../torchkafka_b200/csrc/tk_inflate.cuh"
 
 struct HostReader {
     const uint8_t* p;
@@ -131,4 +132,23 @@ extern "C" int tk_host_decode_object(const uint8_t* buf, uint32_t len, int kind,
         case TK_I64: return tk_json_object_record<TK_I64>(rd, 0, ft, (int64_t*)row);
     }
     return -1;
+}
+
+// One raw DEFLATE stream (tk_inflate.cuh) with the match copy done serially: 0 ok, 1 error.
+extern "C" int tk_host_inflate(const uint8_t* in, uint32_t len, uint8_t* out, uint32_t cap, uint32_t* out_len,
+                               uint32_t* consumed) {
+    tk_inflate_state s;
+    tk_inflate_tables tb;
+    tk_inflate_init(s, in, 0, len);
+    uint32_t op = 0, mlen = 0, mdist = 0;
+    for (;;) {
+        const int ev = tk_inflate_next(s, tb, out, cap, op, &mlen, &mdist);
+        if (ev == TK_INF_ERROR) return 1;
+        if (ev == TK_INF_DONE) break;
+        for (uint32_t k = 0; k < mlen; ++k) out[op + k] = out[op - mdist + k];
+        op += mlen;
+    }
+    *out_len = op;
+    *consumed = tk_inf_consumed(s);
+    return 0;
 }

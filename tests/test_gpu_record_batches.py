@@ -184,7 +184,7 @@ def test_broken_batches_raise_at_their_batch(damage, status):
     elif damage == "magic":
         bad[16] = 1
     elif damage == "codec":
-        bad = bytearray(rb.encode_batch(4, jvals(4, 8), attributes=1))        # gzip: not built
+        bad = bytearray(rb.encode_batch(4, jvals(4, 8), attributes=4))        # zstd: not built
     elif damage == "null":
         bad = bytearray(rb.encode_batch(4, [jvals(4, 5)[0], None, jvals(6, 7)[0]]))
     elif damage == "varint":                                  # framing broken, CRC recomputed to match
@@ -225,20 +225,21 @@ def test_slot_too_small_is_reported():
 
 
 # ---------------------------------------------------------------- LZ4-compressed batches (§8f-2)
-@pytest.mark.parametrize("codec", [3, "lz4i", "lz4ic", 2, "snappy_raw"])
+@pytest.mark.parametrize("codec", [3, "lz4i", "lz4ic", 2, "snappy_raw", 1, "gzipx", "gzip0"])
 @pytest.mark.parametrize("cfg,n,batch_bytes", [(2, 3000, 16384), (2, 3000, 200000), (3, 600, 65536), (5, 20000, 16384)])
 def test_compressed_batches_match_the_oracle(cfg, n, batch_bytes, codec):
     """LZ4 frames with dependent blocks (liblz4's default), with independent blocks and checksums
     (Kafka's Java client), snappy in xerial framing and raw.  cfg2/cfg3: text (matches; several
     blocks / chunks per batch with batch_bytes 200000); cfg5: random bytes (stored blocks, tiny
-    matches)."""
+    matches).  gzip: one member per batch, dynamic and fixed Huffman blocks, with the optional
+    header fields ("gzipx"), stored blocks only ("gzip0")."""
     log = syn.make_log(cfg, n, seed=31 + cfg, partitions=8, layout="chunked", chunk=100)
     schema = {2: JsonArray(torch.float32, max_len=256, min_size=32), 3: TokenList(torch.int32, max_len=2048),
               5: RawBytes((64,), torch.uint8)}[cfg]
     check_raw(log, schema, 128, batch_bytes=batch_bytes, codec=codec)
 
 
-@pytest.mark.parametrize("ca,cb", [(3, "lz4i"), (2, "snappy_raw"), ("lz4ic", 2)])
+@pytest.mark.parametrize("ca,cb", [(3, "lz4i"), (2, "snappy_raw"), ("lz4ic", 2), (1, "gzipx"), ("gzip", 3)])
 def test_codecs_mixed_with_plain_batches_and_long_overlapping_matches(ca, cb):
     vals_a = [json.dumps([1.5] * 200).encode() for _ in range(40)]          # one long period-5 match
     vals_b = jvals(0, 50)
@@ -272,6 +273,32 @@ def test_broken_lz4_frames_raise_at_their_batch(damage):
     with pytest.raises(PayloadError) as ei:
         run_blobs([(1, good + bytes(bad), 0, 0)], JsonArray(torch.float32, max_len=64), 2)
     assert ei.value.status == 7 and ei.value.partition == 1 and ei.value.offset == 4
+
+
+@pytest.mark.parametrize("damage", ["magic", "method", "blocktype", "isize", "truncated", "two-members"])
+def test_broken_gzip_batches_raise_at_their_batch(damage):
+    good = rb.encode_batch(0, jvals(0, 4), codec=1)
+    bad = bytearray(rb.encode_batch(4, [json.dumps([0.5 + i] * 60).encode() for i in range(4)], codec=1))
+    status = 7
+    if damage == "magic":
+        bad[61] ^= 0xFF
+    elif damage == "method":
+        bad[63] = 7
+        status = 4
+    elif damage == "blocktype":
+        bad[61 + 10] |= 0x06                         # first block header: reserved block type 3
+    elif damage == "isize":
+        bad[-4:] = (int.from_bytes(bad[-4:], "little") + 1).to_bytes(4, "little")
+    elif damage == "truncated":
+        del bad[-12:-8]                              # the stream loses its last bytes
+        bad[8:12] = (len(bad) - 12).to_bytes(4, "big")
+    elif damage == "two-members":                    # gzip allows it, this decoder follows one member
+        bad += rb.gzip_member(b"")
+        bad[8:12] = (len(bad) - 12).to_bytes(4, "big")
+    bad[17:21] = rb.crc32c(bytes(bad[21:])).to_bytes(4, "big")
+    with pytest.raises(PayloadError) as ei:
+        run_blobs([(1, good + bytes(bad), 0, 0)], JsonArray(torch.float32, max_len=64), 2)
+    assert ei.value.status == status and ei.value.partition == 1 and ei.value.offset == 4
 
 
 @pytest.mark.parametrize("damage", ["preamble", "offset", "chunk"])

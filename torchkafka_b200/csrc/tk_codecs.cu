@@ -1,30 +1,35 @@
-// tk_codecs.cu -- compressed record batches: LZ4 (attributes & 7 == 3) and
-// snappy (== 2) are decompressed on the device, between the H2D copy of the raw fetch bytes and
-// the record split of tk_recordbatch.cu.
+// tk_codecs.cu -- compressed record batches: LZ4 (attributes & 7 == 3), snappy
+// (== 2) and gzip (== 1) are decompressed on the device, between the H2D copy of the raw fetch
+// bytes and the record split of tk_recordbatch.cu.
 //
-// Replaces kafka-python's `lz4_decode` / `snappy_decode` (kafka/codec.py, called from
+// Replaces kafka-python's `lz4_decode` / `snappy_decode` / `gzip_decode` (kafka/codec.py, called from
 // DefaultRecordBatch._maybe_uncompress in kafka/record/default_records.py; dependency of the
 // reference, setup.py:9, not in its tree).  Formats: lz4_Frame_format.md and lz4_Block_format.md of
 // the LZ4 project; format_description.txt of snappy and the xerial framing of snappy-java
 // (8-byte magic "\x82SNAPPY\0", two int32, then {int32 length, snappy block} chunks).  The xxHash
-// checksums of LZ4 frames are not verified: the batch's CRC-32C covers the same bytes.
+// checksums of LZ4 frames are not verified: the batch's CRC-32C covers the same bytes.  gzip: RFC
+// 1952 member header, DEFLATE (RFC 1951, tk_inflate.cuh), CRC-32 (not verified, same reason) and
+// ISIZE trailer; one member per batch (what java.util.zip.GZIPOutputStream writes).
 //
 // Work split:
 //   host    tk_codec_units_host: follows the codec's framing (a few header reads per batch) and
 //           cuts every batch into independently decodable *units*: LZ4 blocks of a
 //           block-independent frame (what Kafka's Java client writes), the whole block chain of a
-//           block-dependent frame (liblz4's default), stored blocks, snappy blocks (xerial chunks)
+//           block-dependent frame (liblz4's default), stored blocks, snappy blocks (xerial chunks),
+//           the DEFLATE stream of a gzip member (its size is the ISIZE trailer)
 //   device  k_unit_size    warp per LZ4 unit: walks the sequences without copying -> decompressed
 //                          size (LZ4 writes it nowhere; snappy blocks start with it)
 //           k_unit_place   one block: exclusive scan of the sizes -> place of every unit and of
 //                          every batch's records in the decompressed buffer
 //           k_unit_decode  warp per unit
-// Decoders: every lane runs the same element parse on bytes fetched by shuffle from a 128-byte
+// DEFLATE is one chain of dependent bit fields: lane 0 walks it (Huffman tables in shared memory)
+// and writes the literals, the warp copies the matches.  LZ4 / snappy decoders: every lane runs the same element parse on bytes fetched by shuffle from a 128-byte
 // window of the compressed stream held by the warp (one coalesced load per ~100 bytes consumed:
 // the fields of an element depend on one another, a cache round trip each would dominate);
 // literals and matches are copied by the whole warp, overlapping matches by repeating the source
 // with period `offset`; matches are read back from the unit's own output through L1.
 #include "tk_rb.h"
+#include "tk_inflate.cuh"
 
 // ---------------------------------------------------------------- host: units
 static inline uint32_t cu_le32(const uint8_t* p) {
@@ -108,12 +113,38 @@ static uint32_t snappy_units(const uint8_t* raw, uint32_t p, uint32_t end, unit_
     return TK_STATUS_OK;
 }
 
+// gzip member at [p, end): header (RFC 1952), DEFLATE stream, CRC-32, ISIZE
+static uint32_t gzip_units(const uint8_t* raw, uint32_t p, uint32_t end, unit_sink& sink) {
+    if (end - p < 18u || raw[p] != 0x1Fu || raw[p + 1] != 0x8Bu) return TK_STATUS_CORRUPT;
+    if (raw[p + 2] != 8u) return TK_STATUS_UNSUPPORTED;                      // compression method
+    const uint32_t flg = raw[p + 3];
+    if (flg & 0xE0u) return TK_STATUS_CORRUPT;                               // reserved bits
+    p += 10;
+    if (flg & 4u) {                                                          // FEXTRA
+        if (end - p < 2u) return TK_STATUS_CORRUPT;
+        const uint32_t xlen = raw[p] | ((uint32_t)raw[p + 1] << 8);
+        if (xlen > end - p - 2u) return TK_STATUS_CORRUPT;
+        p += 2u + xlen;
+    }
+    for (uint32_t bit = 8u; bit <= 16u; bit <<= 1)                           // FNAME, FCOMMENT: zero-terminated
+        if (flg & bit) {
+            while (p < end && raw[p]) ++p;
+            if (p >= end) return TK_STATUS_CORRUPT;
+            ++p;
+        }
+    if (flg & 2u) p += 2;                                                    // FHCRC
+    if (p > end || end - p < 8u) return TK_STATUS_CORRUPT;
+    sink.add(p, end - 8u - p, RB_UNIT_DEFLATE | RB_UNIT_SIZED, cu_le32(raw + end - 4));
+    return TK_STATUS_OK;
+}
+
 int tk_codec_units_host(const uint8_t* raw, tk_rb_batch& b, uint32_t batch_index, tk_rb_unit* units,
                         uint32_t max_units, uint32_t* n_units) {
     unit_sink sink = {units, max_units, *n_units, batch_index, false};
     const uint32_t first = sink.n;
     const uint32_t status = b.codec == 3u ? lz4_units(raw, b.start + RB_HEADER, b.end, sink)
-                                          : snappy_units(raw, b.start + RB_HEADER, b.end, sink);
+                          : b.codec == 2u ? snappy_units(raw, b.start + RB_HEADER, b.end, sink)
+                                          : gzip_units(raw, b.start + RB_HEADER, b.end, sink);
     TK_REQUIRE(!sink.full, "more compressed blocks in the slot than the unit table holds (%u)", max_units);
     if (status) {
         b.status = status;
@@ -362,6 +393,30 @@ __device__ __forceinline__ uint32_t snappy_run(cz_window& w, uint32_t lane, uint
     return TK_STATUS_OK;
 }
 
+// ---------------------------------------------------------------- DEFLATE (gzip)
+// Lane 0 owns the decoder state and runs tk_inflate_next up to the next match; its literals are
+// plain stores of lane 0 (ordered before the warp's reads by the __syncwarp in cz_match).
+__device__ __forceinline__ uint32_t inflate_run(const uint8_t* raw, uint32_t lane, uint32_t p, uint32_t end, uint8_t* out,
+                                                uint32_t cap, uint32_t& op, tk_inflate_tables& tb) {
+    tk_inflate_state s;
+    tk_inflate_init(s, raw, p, end);
+    for (;;) {
+        uint32_t ev = TK_INF_DONE, mlen = 0, mdist = 0;
+        if (lane == 0) ev = (uint32_t)tk_inflate_next(s, tb, out, cap, op, &mlen, &mdist);
+        ev = __shfl_sync(0xffffffffu, ev, 0);
+        if (ev == TK_INF_ERROR) return TK_STATUS_CORRUPT;
+        op = __shfl_sync(0xffffffffu, op, 0);
+        if (ev == TK_INF_DONE) break;
+        mlen = __shfl_sync(0xffffffffu, mlen, 0);
+        mdist = __shfl_sync(0xffffffffu, mdist, 0);
+        cz_match(out, op, mdist, mlen, lane);
+        op += mlen;
+    }
+    // the stream must end where the trailer begins (a second member behind it is not followed)
+    const uint32_t used = __shfl_sync(0xffffffffu, tk_inf_consumed(s), 0);
+    return used == end ? TK_STATUS_OK : TK_STATUS_CORRUPT;
+}
+
 // ---------------------------------------------------------------- kernels
 __global__ void __launch_bounds__(256) k_unit_size(const rb_args a) {
     const uint32_t lane = threadIdx.x & 31;
@@ -422,6 +477,7 @@ __global__ void __launch_bounds__(1024) k_unit_place(const rb_args a) {
 }
 
 __global__ void __launch_bounds__(128) k_unit_decode(const rb_args a) {
+    __shared__ tk_inflate_tables inf_tables[4];
     const uint32_t lane = threadIdx.x & 31;
     const uint32_t warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, nwarps = (gridDim.x * blockDim.x) >> 5;
     for (uint32_t i = warp; i < a.n_units; i += nwarps) {
@@ -439,6 +495,7 @@ __global__ void __launch_bounds__(128) k_unit_decode(const rb_args a) {
             cz_load(w, u.src, lane);
             if (kind == RB_UNIT_LZ4_BLOCK) st = lz4_block_run<true>(w, lane, u.src, u.src + u.src_len, out, u.unc_len, 0u, op);
             else if (kind == RB_UNIT_LZ4_CHAIN) st = lz4_chain_run<true>(w, lane, u.src, u.src + u.src_len, u.kind, out, u.unc_len, op);
+            else if (kind == RB_UNIT_DEFLATE) st = inflate_run(a.raw, lane, u.src, u.src + u.src_len, out, u.unc_len, op, inf_tables[threadIdx.x >> 5]);
             else st = snappy_run(w, lane, u.src, u.src + u.src_len, out, u.unc_len, op);
         }
         if (!st && op != u.unc_len) st = TK_STATUS_CORRUPT;

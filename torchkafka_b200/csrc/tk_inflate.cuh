@@ -1,0 +1,206 @@
+// tk_inflate.cuh -- DEFLATE (RFC 1951) decoder for gzip-compressed record batches
+// (attributes & 7 == 1).  Replaces kafka-python's `gzip_decode`
+// (kafka/codec.py: gzip.GzipFile(...).read(), i.e. zlib's inflate), called from
+// DefaultRecordBatch._maybe_uncompress; dependency of the reference (setup.py:9), not in its tree.
+//
+// A DEFLATE stream is one chain of dependent bit fields, so one thread walks it: it decodes
+// symbols, writes literals itself, and hands every match (length, distance) to its caller, which
+// copies it -- on the device with the whole warp (tk_codecs.cu), on the host in a plain loop
+// (tests/native, differential test against zlib).  Host+device code (TK_HD).
+// Huffman decoding is canonical: per code length the number of codes and the symbols in code
+// order; a code is walked one bit at a time until it falls into the range of its length.
+#pragma once
+#include "tk_number.cuh"      // TK_HD
+
+enum { TK_INF_MATCH = 0, TK_INF_DONE = 1, TK_INF_ERROR = 2 };
+enum { TK_INF_HEADER = 0, TK_INF_CODES = 1, TK_INF_END = 2 };
+
+struct tk_inflate_tables {
+    uint16_t lit_count[16], lit_symbol[288];
+    uint16_t dist_count[16], dist_symbol[32];
+    uint16_t lengths[320];         // scratch: code lengths of a dynamic block
+};
+
+struct tk_inflate_state {
+    const uint8_t* in;
+    uint32_t pos, end;             // next input byte; pos may run past end (zeros are fed, checked later)
+    uint64_t buf;                  // bit buffer, least significant bit first
+    int      cnt;                  // bits in buf
+    int      mode, last;
+};
+
+TK_HD void tk_inflate_init(tk_inflate_state& s, const uint8_t* in, uint32_t pos, uint32_t end) {
+    s.in = in; s.pos = pos; s.end = end; s.buf = 0; s.cnt = 0; s.mode = TK_INF_HEADER; s.last = 0;
+}
+TK_HD void tk_inf_refill(tk_inflate_state& s) {
+    while (s.cnt <= 56) {
+        const uint64_t b = s.pos < s.end ? s.in[s.pos] : 0u;
+        ++s.pos;
+        s.buf |= b << s.cnt;
+        s.cnt += 8;
+    }
+}
+TK_HD uint32_t tk_inf_bits(tk_inflate_state& s, int n) {          // n <= 16, buffer holds them
+    const uint32_t v = (uint32_t)s.buf & ((1u << n) - 1u);
+    s.buf >>= n;
+    s.cnt -= n;
+    return v;
+}
+// bytes of input consumed so far (whole bytes still in the buffer do not count)
+TK_HD uint32_t tk_inf_consumed(const tk_inflate_state& s) { return s.pos - (uint32_t)(s.cnt >> 3); }
+
+// Canonical code from code lengths.  Returns 0 for a complete code, > 0 for an incomplete one
+// (that many codes of the longest length are unused), < 0 for an over-subscribed one.
+TK_HD int tk_huff_build(uint16_t* count, uint16_t* symbol, const uint16_t* length, int n) {
+    for (int l = 0; l < 16; ++l) count[l] = 0;
+    for (int i = 0; i < n; ++i) count[length[i]]++;
+    if (count[0] == n) return 0;                       // no codes at all: nothing can be decoded
+    int left = 1;
+    for (int l = 1; l < 16; ++l) {
+        left <<= 1;
+        left -= count[l];
+        if (left < 0) return left;
+    }
+    uint16_t offs[16];
+    offs[1] = 0;
+    for (int l = 1; l < 15; ++l) offs[l + 1] = (uint16_t)(offs[l] + count[l]);
+    for (int i = 0; i < n; ++i)
+        if (length[i]) symbol[offs[length[i]]++] = (uint16_t)i;
+    return left;
+}
+
+// Next symbol (the buffer holds at least 15 bits), -1 if the bits are no code.
+TK_HD int tk_huff_decode(tk_inflate_state& s, const uint16_t* count, const uint16_t* symbol) {
+    uint32_t bits = (uint32_t)s.buf;
+    int code = 0, first = 0, index = 0;
+    for (int len = 1; len < 16; ++len) {
+        code |= (int)(bits & 1u);
+        bits >>= 1;
+        const int c = count[len];
+        if (code - c < first) {
+            s.buf >>= len;
+            s.cnt -= len;
+            return symbol[index + (code - first)];
+        }
+        index += c;
+        first = (first + c) << 1;
+        code <<= 1;
+    }
+    return -1;
+}
+
+TK_HD bool tk_inf_fixed_tables(tk_inflate_tables& tb) {
+    for (int i = 0; i < 288; ++i) tb.lengths[i] = (uint16_t)(i < 144 ? 8 : i < 256 ? 9 : i < 280 ? 7 : 8);
+    tk_huff_build(tb.lit_count, tb.lit_symbol, tb.lengths, 288);
+    for (int i = 0; i < 30; ++i) tb.lengths[i] = 5;
+    tk_huff_build(tb.dist_count, tb.dist_symbol, tb.lengths, 30);
+    return true;
+}
+
+TK_HD bool tk_inf_dynamic_tables(tk_inflate_state& s, tk_inflate_tables& tb) {
+    tk_inf_refill(s);
+    const int nlen = (int)tk_inf_bits(s, 5) + 257, ndist = (int)tk_inf_bits(s, 5) + 1, ncode = (int)tk_inf_bits(s, 4) + 4;
+    if (nlen > 286 || ndist > 30) return false;
+    const char* order = "\x10\x11\x12\x00\x08\x07\x09\x06\x0a\x05\x0b\x04\x0c\x03\x0d\x02\x0e\x01\x0f";
+    for (int i = 0; i < 19; ++i) tb.lengths[i] = 0;
+    for (int i = 0; i < ncode; ++i) {
+        tk_inf_refill(s);
+        tb.lengths[(int)order[i]] = (uint16_t)tk_inf_bits(s, 3);
+    }
+    // the code of the code lengths lives in the literal table for the moment
+    if (tk_huff_build(tb.lit_count, tb.lit_symbol, tb.lengths, 19) != 0) return false;      // must be complete
+    int i = 0;
+    while (i < nlen + ndist) {
+        tk_inf_refill(s);
+        const int sym = tk_huff_decode(s, tb.lit_count, tb.lit_symbol);
+        if (sym < 0) return false;
+        if (sym < 16) { tb.lengths[i++] = (uint16_t)sym; continue; }
+        int rep, val = 0;
+        if (sym == 16) {
+            if (i == 0) return false;
+            val = tb.lengths[i - 1];
+            rep = 3 + (int)tk_inf_bits(s, 2);
+        } else if (sym == 17) {
+            rep = 3 + (int)tk_inf_bits(s, 3);
+        } else {
+            rep = 11 + (int)tk_inf_bits(s, 7);
+        }
+        if (i + rep > nlen + ndist) return false;
+        while (rep--) tb.lengths[i++] = (uint16_t)val;
+    }
+    if (tk_inf_consumed(s) > s.end) return false;
+    if (tb.lengths[256] == 0) return false;                    // no end-of-block code
+    // distance lengths first (building the literal table overwrites nothing they need, but the
+    // literal build reads lengths[0, nlen) which must stay intact: build dist from its own range)
+    int err = tk_huff_build(tb.dist_count, tb.dist_symbol, tb.lengths + nlen, ndist);
+    if (err && (err < 0 || ndist != tb.dist_count[0] + tb.dist_count[1])) return false;   // incomplete: only a single 1-bit code
+    err = tk_huff_build(tb.lit_count, tb.lit_symbol, tb.lengths, nlen);
+    if (err && (err < 0 || nlen != tb.lit_count[0] + tb.lit_count[1])) return false;
+    return true;
+}
+
+// Decodes on from the current state: literals go to out[op++] (capacity cap); returns at the next
+// match with *mlen / *mdist set (the caller copies out[op - dist ..] and advances op by mlen; both
+// are checked against op and cap here), at the end of the stream, or on an error.
+TK_HD int tk_inflate_next(tk_inflate_state& s, tk_inflate_tables& tb, uint8_t* out, uint32_t cap, uint32_t& op,
+                          uint32_t* mlen, uint32_t* mdist) {
+    for (;;) {
+        if (s.mode == TK_INF_HEADER) {
+            if (s.last) { s.mode = TK_INF_END; return TK_INF_DONE; }
+            tk_inf_refill(s);
+            s.last = (int)tk_inf_bits(s, 1);
+            const uint32_t type = tk_inf_bits(s, 2);
+            if (type == 0) {                                    // stored
+                tk_inf_bits(s, s.cnt & 7);                      // to the byte boundary
+                tk_inf_refill(s);
+                const uint32_t len = tk_inf_bits(s, 16), nlen = tk_inf_bits(s, 16);
+                if ((len ^ nlen) != 0xFFFFu || len > cap - op) return TK_INF_ERROR;
+                for (uint32_t k = 0; k < len; ++k) {
+                    tk_inf_refill(s);
+                    out[op++] = (uint8_t)tk_inf_bits(s, 8);
+                }
+                if (tk_inf_consumed(s) > s.end) return TK_INF_ERROR;
+                continue;
+            }
+            if (type == 1) tk_inf_fixed_tables(tb);
+            else if (type == 2) { if (!tk_inf_dynamic_tables(s, tb)) return TK_INF_ERROR; }
+            else return TK_INF_ERROR;
+            s.mode = TK_INF_CODES;
+        }
+        if (s.mode == TK_INF_END) return TK_INF_DONE;
+        for (;;) {
+            tk_inf_refill(s);                                   // >= 57 bits: literal/length 15 + 5, distance 15 + 13
+            if (tk_inf_consumed(s) > s.end) return TK_INF_ERROR;
+            int sym = tk_huff_decode(s, tb.lit_count, tb.lit_symbol);
+            if (sym < 0) return TK_INF_ERROR;
+            if (sym < 256) {
+                if (op >= cap) return TK_INF_ERROR;
+                out[op++] = (uint8_t)sym;
+                continue;
+            }
+            if (sym == 256) { s.mode = TK_INF_HEADER; break; }
+            sym -= 257;
+            if (sym >= 29) return TK_INF_ERROR;
+            uint32_t len;
+            if (sym < 8) len = 3u + (uint32_t)sym;
+            else if (sym == 28) len = 258u;
+            else {
+                const int k = sym - 4, e = k >> 2;              // 1..5 extra bits
+                len = ((4u + (uint32_t)(k & 3)) << e) + 3u + tk_inf_bits(s, e);
+            }
+            const int dsym = tk_huff_decode(s, tb.dist_count, tb.dist_symbol);
+            if (dsym < 0 || dsym >= 30) return TK_INF_ERROR;
+            uint32_t dist;
+            if (dsym < 4) dist = (uint32_t)dsym + 1u;
+            else {
+                const int e = (dsym >> 1) - 1;                  // 1..13 extra bits
+                dist = ((2u + (uint32_t)(dsym & 1)) << e) + 1u + tk_inf_bits(s, e);
+            }
+            if (tk_inf_consumed(s) > s.end) return TK_INF_ERROR;
+            if (dist > op || len > cap - op) return TK_INF_ERROR;
+            *mlen = len;
+            *mdist = dist;
+            return TK_INF_MATCH;
+        }
+    }
+}

@@ -119,8 +119,31 @@ def snappy_xerial(data: bytes, chunk_bytes: int = 32768) -> bytes:
     return bytes(out)
 
 
+def gzip_member(data: bytes, level: int = 6, name: bytes = None, extra: bytes = None, comment: bytes = None,
+                header_crc: bool = False) -> bytes:
+    """One gzip member (RFC 1952); without the optional fields this is what
+    java.util.zip.GZIPOutputStream (Kafka's Java client) writes."""
+    import zlib
+    flg = (2 if header_crc else 0) | (4 if extra is not None else 0) | (8 if name is not None else 0) | \
+        (16 if comment is not None else 0)
+    head = bytearray(b"\x1f\x8b\x08" + bytes([flg]) + b"\x00\x00\x00\x00\x00\x00")
+    if extra is not None:
+        head += struct.pack("<H", len(extra)) + extra
+    if name is not None:
+        head += name + b"\x00"
+    if comment is not None:
+        head += comment + b"\x00"
+    if header_crc:
+        head += struct.pack("<H", zlib.crc32(bytes(head)) & 0xFFFF)
+    co = zlib.compressobj(level, zlib.DEFLATED, -15)
+    body = co.compress(data) + co.flush()
+    return bytes(head) + body + struct.pack("<II", zlib.crc32(data) & 0xFFFFFFFF, len(data) & 0xFFFFFFFF)
+
+
 #: codec argument of encode_batch -> (attribute bits, compressor)
 CODECS = {
+    1: (1, gzip_member), "gzip": (1, gzip_member), "gzip0": (1, lambda d: gzip_member(d, level=0)),
+    "gzipx": (1, lambda d: gzip_member(d, 9, name=b"records.bin", extra=b"\x01\x02\x03", comment=b"c", header_crc=True)),
     3: (3, lz4_frame), "lz4": (3, lz4_frame), "lz4i": (3, lz4_frame_independent),
     "lz4ic": (3, lambda d: lz4_frame_independent(d, block_checksum=True, content_checksum=True)),
     2: (2, snappy_xerial), "snappy": (2, snappy_xerial), "snappy_raw": (2, snappy_raw),
@@ -131,7 +154,8 @@ def encode_batch(base_offset: int, values: Sequence[Optional[bytes]], attributes
                  offset_deltas: Optional[Sequence[int]] = None, keys: Optional[Sequence] = None,
                  headers: Optional[Sequence] = None, crc: Optional[int] = None, codec: int = 0) -> bytes:
     """One RecordBatch v2.  `offset_deltas` default to 0, 1, 2, ... (a compacted topic has gaps).
-    `codec` (a key of CODECS: 3 / "lz4", "lz4i", "lz4ic", 2 / "snappy", "snappy_raw") compresses the
+    `codec` (a key of CODECS: 3 / "lz4", "lz4i", "lz4ic", 2 / "snappy", "snappy_raw", 1 / "gzip", "gzip0",
+    "gzipx") compresses the
     records and sets the attribute bits."""
     n = len(values)
     deltas = list(range(n)) if offset_deltas is None else list(offset_deltas)

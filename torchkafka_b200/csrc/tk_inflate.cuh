@@ -8,17 +8,23 @@
 // copies it -- on the device with the whole warp (tk_codecs.cu), on the host in a plain loop
 // (tests/native, differential test against zlib).  Host+device code (TK_HD).
 // Huffman decoding is canonical: per code length the number of codes and the symbols in code
-// order; a code is walked one bit at a time until it falls into the range of its length.
+// order.  Codes of up to TK_INF_LIT_FAST / TK_INF_DIST_FAST bits are found with one lookup of the
+// next bits in a table of (symbol << 4 | length); longer ones are walked one bit at a time until
+// they fall into the range of their length.
 #pragma once
+#include <string.h>
 #include "tk_number.cuh"      // TK_HD
 
 enum { TK_INF_MATCH = 0, TK_INF_DONE = 1, TK_INF_ERROR = 2 };
 enum { TK_INF_HEADER = 0, TK_INF_CODES = 1, TK_INF_END = 2 };
 
+#define TK_INF_LIT_FAST 10
+#define TK_INF_DIST_FAST 8
 struct tk_inflate_tables {
     uint16_t lit_count[16], lit_symbol[288];
     uint16_t dist_count[16], dist_symbol[32];
     uint16_t lengths[320];         // scratch: code lengths of a dynamic block
+    uint16_t lit_fast[1 << TK_INF_LIT_FAST], dist_fast[1 << TK_INF_DIST_FAST];   // 0: longer code
 };
 
 struct tk_inflate_state {
@@ -29,14 +35,30 @@ struct tk_inflate_state {
     int      mode, last;
 };
 
+// Brings the buffer to at least 33 bits with one aligned 4-byte load (every field group of the
+// format needs at most 32: see the callers).  Past the end of the input zeros are fed; the position
+// check (tk_inf_consumed) catches a stream that used them.
+TK_HD void tk_inf_refill(tk_inflate_state& s) {
+    if (s.cnt > 32) return;
+    uint32_t w = 0;
+    if (s.pos < s.end && s.end - s.pos >= 4u) {
+#if defined(__CUDA_ARCH__)
+        w = *reinterpret_cast<const uint32_t*>(s.in + s.pos);      // aligned: tk_inflate_init
+#else
+        memcpy(&w, s.in + s.pos, 4);
+#endif
+    } else {
+        for (uint32_t k = 0; k < 4; ++k)
+            if (s.pos + k < s.end) w |= (uint32_t)s.in[s.pos + k] << (8 * k);
+    }
+    s.pos += 4;
+    s.buf |= (uint64_t)w << s.cnt;
+    s.cnt += 32;
+}
 TK_HD void tk_inflate_init(tk_inflate_state& s, const uint8_t* in, uint32_t pos, uint32_t end) {
     s.in = in; s.pos = pos; s.end = end; s.buf = 0; s.cnt = 0; s.mode = TK_INF_HEADER; s.last = 0;
-}
-TK_HD void tk_inf_refill(tk_inflate_state& s) {
-    while (s.cnt <= 56) {
-        const uint64_t b = s.pos < s.end ? s.in[s.pos] : 0u;
-        ++s.pos;
-        s.buf |= b << s.cnt;
+    while (((uintptr_t)(in + s.pos) & 3u) && s.pos < end) {         // up to the first aligned word
+        s.buf |= (uint64_t)in[s.pos++] << s.cnt;
         s.cnt += 8;
     }
 }
@@ -69,8 +91,33 @@ TK_HD int tk_huff_build(uint16_t* count, uint16_t* symbol, const uint16_t* lengt
     return left;
 }
 
+// Lookup table of the codes of at most `fast_bits` bits (call right after tk_huff_build, same
+// lengths): entry at every index whose low bits are the code, first bit of the code lowest.
+TK_HD void tk_huff_fast(uint16_t* fast, int fast_bits, const uint16_t* count, const uint16_t* length, int n) {
+    uint32_t next[16];
+    next[1] = 0;
+    for (int l = 1; l < 15; ++l) next[l + 1] = (next[l] + count[l]) << 1;
+    for (int k = 0; k < (1 << fast_bits); ++k) fast[k] = 0;
+    for (int i = 0; i < n; ++i) {
+        const int l = length[i];
+        if (!l) continue;
+        const uint32_t code = next[l]++;
+        if (l > fast_bits) continue;
+        uint32_t rev = 0;
+        for (int b = 0; b < l; ++b) rev |= ((code >> b) & 1u) << (l - 1 - b);
+        for (uint32_t k = rev; k < (1u << fast_bits); k += 1u << l) fast[k] = (uint16_t)((i << 4) | l);
+    }
+}
+
 // Next symbol (the buffer holds at least 15 bits), -1 if the bits are no code.
-TK_HD int tk_huff_decode(tk_inflate_state& s, const uint16_t* count, const uint16_t* symbol) {
+TK_HD int tk_huff_decode(tk_inflate_state& s, const uint16_t* count, const uint16_t* symbol, const uint16_t* fast,
+                         int fast_bits) {
+    const uint32_t e = fast[(uint32_t)s.buf & ((1u << fast_bits) - 1u)];
+    if (e) {
+        s.buf >>= (e & 15u);
+        s.cnt -= (int)(e & 15u);
+        return (int)(e >> 4);
+    }
     uint32_t bits = (uint32_t)s.buf;
     int code = 0, first = 0, index = 0;
     for (int len = 1; len < 16; ++len) {
@@ -92,8 +139,10 @@ TK_HD int tk_huff_decode(tk_inflate_state& s, const uint16_t* count, const uint1
 TK_HD bool tk_inf_fixed_tables(tk_inflate_tables& tb) {
     for (int i = 0; i < 288; ++i) tb.lengths[i] = (uint16_t)(i < 144 ? 8 : i < 256 ? 9 : i < 280 ? 7 : 8);
     tk_huff_build(tb.lit_count, tb.lit_symbol, tb.lengths, 288);
+    tk_huff_fast(tb.lit_fast, TK_INF_LIT_FAST, tb.lit_count, tb.lengths, 288);
     for (int i = 0; i < 30; ++i) tb.lengths[i] = 5;
     tk_huff_build(tb.dist_count, tb.dist_symbol, tb.lengths, 30);
+    tk_huff_fast(tb.dist_fast, TK_INF_DIST_FAST, tb.dist_count, tb.lengths, 30);
     return true;
 }
 
@@ -107,12 +156,13 @@ TK_HD bool tk_inf_dynamic_tables(tk_inflate_state& s, tk_inflate_tables& tb) {
         tk_inf_refill(s);
         tb.lengths[(int)order[i]] = (uint16_t)tk_inf_bits(s, 3);
     }
-    // the code of the code lengths lives in the literal table for the moment
+    // the code of the code lengths lives in the literal table for the moment (codes of <= 7 bits)
     if (tk_huff_build(tb.lit_count, tb.lit_symbol, tb.lengths, 19) != 0) return false;      // must be complete
+    tk_huff_fast(tb.dist_fast, 7, tb.lit_count, tb.lengths, 19);
     int i = 0;
     while (i < nlen + ndist) {
         tk_inf_refill(s);
-        const int sym = tk_huff_decode(s, tb.lit_count, tb.lit_symbol);
+        const int sym = tk_huff_decode(s, tb.lit_count, tb.lit_symbol, tb.dist_fast, 7);
         if (sym < 0) return false;
         if (sym < 16) { tb.lengths[i++] = (uint16_t)sym; continue; }
         int rep, val = 0;
@@ -134,8 +184,10 @@ TK_HD bool tk_inf_dynamic_tables(tk_inflate_state& s, tk_inflate_tables& tb) {
     // literal build reads lengths[0, nlen) which must stay intact: build dist from its own range)
     int err = tk_huff_build(tb.dist_count, tb.dist_symbol, tb.lengths + nlen, ndist);
     if (err && (err < 0 || ndist != tb.dist_count[0] + tb.dist_count[1])) return false;   // incomplete: only a single 1-bit code
+    tk_huff_fast(tb.dist_fast, TK_INF_DIST_FAST, tb.dist_count, tb.lengths + nlen, ndist);
     err = tk_huff_build(tb.lit_count, tb.lit_symbol, tb.lengths, nlen);
     if (err && (err < 0 || nlen != tb.lit_count[0] + tb.lit_count[1])) return false;
+    tk_huff_fast(tb.lit_fast, TK_INF_LIT_FAST, tb.lit_count, tb.lengths, nlen);
     return true;
 }
 
@@ -146,7 +198,10 @@ TK_HD int tk_inflate_next(tk_inflate_state& s, tk_inflate_tables& tb, uint8_t* o
                           uint32_t* mlen, uint32_t* mdist) {
     for (;;) {
         if (s.mode == TK_INF_HEADER) {
-            if (s.last) { s.mode = TK_INF_END; return TK_INF_DONE; }
+            if (s.last) {
+                s.mode = TK_INF_END;
+                return tk_inf_consumed(s) > s.end ? TK_INF_ERROR : TK_INF_DONE;   // ended on bits that are not there
+            }
             tk_inf_refill(s);
             s.last = (int)tk_inf_bits(s, 1);
             const uint32_t type = tk_inf_bits(s, 2);
@@ -169,9 +224,9 @@ TK_HD int tk_inflate_next(tk_inflate_state& s, tk_inflate_tables& tb, uint8_t* o
         }
         if (s.mode == TK_INF_END) return TK_INF_DONE;
         for (;;) {
-            tk_inf_refill(s);                                   // >= 57 bits: literal/length 15 + 5, distance 15 + 13
+            tk_inf_refill(s);                                   // >= 33 bits: literal/length code 15 + 5 extra
             if (tk_inf_consumed(s) > s.end) return TK_INF_ERROR;
-            int sym = tk_huff_decode(s, tb.lit_count, tb.lit_symbol);
+            int sym = tk_huff_decode(s, tb.lit_count, tb.lit_symbol, tb.lit_fast, TK_INF_LIT_FAST);
             if (sym < 0) return TK_INF_ERROR;
             if (sym < 256) {
                 if (op >= cap) return TK_INF_ERROR;
@@ -188,7 +243,8 @@ TK_HD int tk_inflate_next(tk_inflate_state& s, tk_inflate_tables& tb, uint8_t* o
                 const int k = sym - 4, e = k >> 2;              // 1..5 extra bits
                 len = ((4u + (uint32_t)(k & 3)) << e) + 3u + tk_inf_bits(s, e);
             }
-            const int dsym = tk_huff_decode(s, tb.dist_count, tb.dist_symbol);
+            tk_inf_refill(s);                                   // distance code 15 + 13 extra
+            const int dsym = tk_huff_decode(s, tb.dist_count, tb.dist_symbol, tb.dist_fast, TK_INF_DIST_FAST);
             if (dsym < 0 || dsym >= 30) return TK_INF_ERROR;
             uint32_t dist;
             if (dsym < 4) dist = (uint32_t)dsym + 1u;

@@ -9,6 +9,7 @@
 #include <string.h>
 #include "../../torchkafka_b200/csrc/tk_json_object.cuh"
 #include "../../torchkafka_b200/csrc/tk_inflate.cuh"
+#include "../../torchkafka_b200/csrc/tk_zstd.cuh"
 
 struct HostReader {
     const uint8_t* p;
@@ -150,5 +151,29 @@ extern "C" int tk_host_inflate(const uint8_t* in, uint32_t len, uint8_t* out, ui
     }
     *out_len = op;
     *consumed = tk_inf_consumed(s);
+    return 0;
+}
+
+// Zstandard payload (tk_zstd.cuh) with the copies done serially.  emit = 0: size pass only.
+// Returns 0 ok, else the decoder's status; *out_len = bytes produced.
+extern "C" int tk_host_zstd(const uint8_t* in, uint32_t len, uint8_t* out, uint32_t cap, int emit, uint32_t* out_len) {
+    static tk_zstd_tables tb;
+    tk_zstd_state s;
+    tk_zstd_init(s, tb, in, 0, len);
+    uint32_t op = 0;
+    tk_zstd_event ev;
+    for (;;) {
+        const int st = tk_zstd_next(s, tb, out, emit ? cap : 0x7FFFFFFFu, op, emit != 0, &ev);
+        if (st == TK_ZS_DONE) break;
+        if (st != TK_ZS_COPY) return st;
+        if (emit) {
+            if (ev.lit_kind == TK_ZL_INPUT) memmove(out + op, in + ev.lit_src, ev.lit_len);
+            else if (ev.lit_kind == TK_ZL_RLE) memset(out + op, (int)ev.lit_src, ev.lit_len);
+            else for (uint32_t k = 0; k < ev.lit_len; ++k) out[op + k] = out[ev.lit_src + k];
+            for (uint32_t k = 0; k < ev.mlen; ++k) out[op + ev.lit_len + k] = out[op + ev.lit_len - ev.offset + k];
+        }
+        op += ev.lit_len + ev.mlen;
+    }
+    *out_len = op;
     return 0;
 }

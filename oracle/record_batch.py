@@ -18,7 +18,8 @@ Semantics restated from kafka-python's fetcher:
     checksums are skipped, the batch CRC covers the same bytes); snappy batches (codec 2) with the
     restatement of snappy's format_description.txt, raw or in snappy-java's xerial framing (what
     kafka-python's snappy_decode accepts); gzip batches (codec 1) with CPython's own gzip module,
-    which is what kafka-python's gzip_decode calls; zstd raises UnsupportedBatch;
+    which is what kafka-python's gzip_decode calls; zstd batches (codec 4) with libzstd (through
+    pyarrow's stream reader; kafka-python calls the same library through `zstandard`);
   * control batches (attributes bit 5) carry no user records and are skipped.
 Pure Python, byte at a time: for small cases.
 """
@@ -259,6 +260,12 @@ def split_blob(blob: bytes, partition: int, fetch_offset: int = 0, offset_delta:
                 body = gzip.decompress(bytes(blob[pos + HEADER_BYTES:end]))
             except Exception as e:                           # noqa: BLE001 (zlib.error, BadGzipFile, EOFError)
                 raise CorruptRecordError(f"gzip: {e}") from e
+        elif codec == 4:
+            import pyarrow as pa
+            try:
+                body = pa.CompressedInputStream(pa.BufferReader(bytes(blob[pos + HEADER_BYTES:end])), "zstd").read()
+            except Exception as e:                           # noqa: BLE001
+                raise CorruptRecordError(f"zstd: {e}") from e
         elif codec:
             raise UnsupportedBatch(f"compression codec {codec}")
         else:

@@ -184,7 +184,7 @@ def test_broken_batches_raise_at_their_batch(damage, status):
     elif damage == "magic":
         bad[16] = 1
     elif damage == "codec":
-        bad = bytearray(rb.encode_batch(4, jvals(4, 8), attributes=4))        # zstd: not built
+        bad = bytearray(rb.encode_batch(4, jvals(4, 8), attributes=5))        # no such codec
     elif damage == "null":
         bad = bytearray(rb.encode_batch(4, [jvals(4, 5)[0], None, jvals(6, 7)[0]]))
     elif damage == "varint":                                  # framing broken, CRC recomputed to match
@@ -225,21 +225,22 @@ def test_slot_too_small_is_reported():
 
 
 # ---------------------------------------------------------------- LZ4-compressed batches (§8f-2)
-@pytest.mark.parametrize("codec", [3, "lz4i", "lz4ic", 2, "snappy_raw", 1, "gzipx", "gzip0"])
+@pytest.mark.parametrize("codec", [3, "lz4i", "lz4ic", 2, "snappy_raw", 1, "gzipx", "gzip0", 4, "zstds", "zstd19"])
 @pytest.mark.parametrize("cfg,n,batch_bytes", [(2, 3000, 16384), (2, 3000, 200000), (3, 600, 65536), (5, 20000, 16384)])
 def test_compressed_batches_match_the_oracle(cfg, n, batch_bytes, codec):
     """LZ4 frames with dependent blocks (liblz4's default), with independent blocks and checksums
     (Kafka's Java client), snappy in xerial framing and raw.  cfg2/cfg3: text (matches; several
     blocks / chunks per batch with batch_bytes 200000); cfg5: random bytes (stored blocks, tiny
     matches).  gzip: one member per batch, dynamic and fixed Huffman blocks, with the optional
-    header fields ("gzipx"), stored blocks only ("gzip0")."""
+    header fields ("gzipx"), stored blocks only ("gzip0").  zstd: frames without a content size
+    (the streaming form, size pass on the device), with one ("zstds"), level 19 ("zstd19")."""
     log = syn.make_log(cfg, n, seed=31 + cfg, partitions=8, layout="chunked", chunk=100)
     schema = {2: JsonArray(torch.float32, max_len=256, min_size=32), 3: TokenList(torch.int32, max_len=2048),
               5: RawBytes((64,), torch.uint8)}[cfg]
     check_raw(log, schema, 128, batch_bytes=batch_bytes, codec=codec)
 
 
-@pytest.mark.parametrize("ca,cb", [(3, "lz4i"), (2, "snappy_raw"), ("lz4ic", 2), (1, "gzipx"), ("gzip", 3)])
+@pytest.mark.parametrize("ca,cb", [(3, "lz4i"), (2, "snappy_raw"), ("lz4ic", 2), (1, "gzipx"), ("gzip", 3), (4, "zstds"), ("zstd19", 1)])
 def test_codecs_mixed_with_plain_batches_and_long_overlapping_matches(ca, cb):
     vals_a = [json.dumps([1.5] * 200).encode() for _ in range(40)]          # one long period-5 match
     vals_b = jvals(0, 50)
@@ -295,6 +296,37 @@ def test_broken_gzip_batches_raise_at_their_batch(damage):
     elif damage == "two-members":                    # gzip allows it, this decoder follows one member
         bad += rb.gzip_member(b"")
         bad[8:12] = (len(bad) - 12).to_bytes(4, "big")
+    bad[17:21] = rb.crc32c(bytes(bad[21:])).to_bytes(4, "big")
+    with pytest.raises(PayloadError) as ei:
+        run_blobs([(1, good + bytes(bad), 0, 0)], JsonArray(torch.float32, max_len=64), 2)
+    assert ei.value.status == status and ei.value.partition == 1 and ei.value.offset == 4
+
+
+@pytest.mark.parametrize("damage", ["magic", "blocktype", "truncated", "dictionary", "size"])
+@pytest.mark.parametrize("codec", [4, "zstds"])
+def test_broken_zstd_batches_raise_at_their_batch(damage, codec):
+    good = rb.encode_batch(0, jvals(0, 4), codec=codec)
+    bad = bytearray(rb.encode_batch(4, [json.dumps([0.5 + i] * 60).encode() for i in range(4)], codec=codec))
+    status = 7
+    head = 61 + (6 if codec == 4 else 5 + (1 if bad[61 + 4] >> 6 == 0 else 2))       # first block header
+    if damage == "magic":
+        bad[61] ^= 0xFF
+    elif damage == "blocktype":
+        bad[head] |= 0x06                            # reserved block type 3
+    elif damage == "truncated":
+        del bad[-3:]
+        bad[8:12] = (len(bad) - 12).to_bytes(4, "big")
+    elif damage == "dictionary":
+        if codec != 4:
+            pytest.skip("header layout of the sized frame")
+        bad[61 + 4] |= 0x01
+        bad[61 + 6:61 + 6] = b"\x09"
+        bad[8:12] = (len(bad) - 12).to_bytes(4, "big")
+        status = 4
+    elif damage == "size":
+        if codec == 4:
+            pytest.skip("no content size in this frame")
+        bad[61 + 5] ^= 0x01                          # Frame_Content_Size says another length
     bad[17:21] = rb.crc32c(bytes(bad[21:])).to_bytes(4, "big")
     with pytest.raises(PayloadError) as ei:
         run_blobs([(1, good + bytes(bad), 0, 0)], JsonArray(torch.float32, max_len=64), 2)

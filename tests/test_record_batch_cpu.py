@@ -102,7 +102,7 @@ def test_fetch_offset_partial_tail_control_and_errors():
     with pytest.raises(orb.CorruptRecordError):
         orb.split_blob(bytes(bad), 0)
     with pytest.raises(orb.UnsupportedBatch):
-        orb.split_blob(rb.encode_batch(0, [b"x"], attributes=4), 0)         # zstd
+        orb.split_blob(rb.encode_batch(0, [b"x"], attributes=5), 0)         # no such codec
     v1 = bytearray(a)
     v1[16] = 1
     with pytest.raises(orb.CorruptRecordError):
@@ -213,7 +213,7 @@ def test_snappy_oracle_decodes_blocks_of_an_independent_compressor():
         orb.snappy_block_decode(bytes([9, 0x0C]) + b"abcd" + bytes([0x01, 0x04]))     # length mismatch
 
 
-@pytest.mark.parametrize("codec", [2, "snappy_raw", "lz4i", "lz4ic", 1, "gzipx"])
+@pytest.mark.parametrize("codec", [2, "snappy_raw", "lz4i", "lz4ic", 1, "gzipx", 4, "zstds"])
 def test_compressed_batches_roundtrip_through_the_oracle(codec):
     log = syn.make_log(2, 200, seed=9, partitions=2, layout="chunked", chunk=50)
     c = sk.KafkaConsumer("topic", log=log, raw_batch_bytes=100000, raw_codec=codec)

@@ -1,35 +1,38 @@
 // tk_codecs.cu -- compressed record batches: LZ4 (attributes & 7 == 3), snappy
-// (== 2) and gzip (== 1) are decompressed on the device, between the H2D copy of the raw fetch
+// (== 2), gzip (== 1) and zstd (== 4) are decompressed on the device, between the H2D copy of the raw fetch
 // bytes and the record split of tk_recordbatch.cu.
 //
-// Replaces kafka-python's `lz4_decode` / `snappy_decode` / `gzip_decode` (kafka/codec.py, called from
+// Replaces kafka-python's `lz4_decode` / `snappy_decode` / `gzip_decode` / `zstd_decode` (kafka/codec.py, called from
 // DefaultRecordBatch._maybe_uncompress in kafka/record/default_records.py; dependency of the
 // reference, setup.py:9, not in its tree).  Formats: lz4_Frame_format.md and lz4_Block_format.md of
 // the LZ4 project; format_description.txt of snappy and the xerial framing of snappy-java
 // (8-byte magic "\x82SNAPPY\0", two int32, then {int32 length, snappy block} chunks).  The xxHash
 // checksums of LZ4 frames are not verified: the batch's CRC-32C covers the same bytes.  gzip: RFC
 // 1952 member header, DEFLATE (RFC 1951, tk_inflate.cuh), CRC-32 (not verified, same reason) and
-// ISIZE trailer; one member per batch (what java.util.zip.GZIPOutputStream writes).
+// ISIZE trailer; one member per batch (what java.util.zip.GZIPOutputStream writes).  zstd: RFC 8878
+// (tk_zstd.cuh); frames usually carry no content size, so they take the size pass.
 //
 // Work split:
 //   host    tk_codec_units_host: follows the codec's framing (a few header reads per batch) and
 //           cuts every batch into independently decodable *units*: LZ4 blocks of a
 //           block-independent frame (what Kafka's Java client writes), the whole block chain of a
 //           block-dependent frame (liblz4's default), stored blocks, snappy blocks (xerial chunks),
-//           the DEFLATE stream of a gzip member (its size is the ISIZE trailer)
+//           the DEFLATE stream of a gzip member (its size is the ISIZE trailer), the zstd frames
+//           of a batch (block headers walked; sized when every frame states its content size)
 //   device  k_unit_size    warp per LZ4 unit: walks the sequences without copying -> decompressed
 //                          size (LZ4 writes it nowhere; snappy blocks start with it)
 //           k_unit_place   one block: exclusive scan of the sizes -> place of every unit and of
 //                          every batch's records in the decompressed buffer
 //           k_unit_decode  warp per unit
-// DEFLATE is one chain of dependent bit fields: lane 0 walks it (Huffman tables in shared memory)
-// and writes the literals, the warp copies the matches.  LZ4 / snappy decoders: every lane runs the same element parse on bytes fetched by shuffle from a 128-byte
+// DEFLATE and zstd are chains of dependent bit fields: lane 0 walks them (tables in shared memory),
+// the warp copies literal runs and matches (k_unit_size_zstd / k_unit_decode_serial).  LZ4 / snappy decoders: every lane runs the same element parse on bytes fetched by shuffle from a 128-byte
 // window of the compressed stream held by the warp (one coalesced load per ~100 bytes consumed:
 // the fields of an element depend on one another, a cache round trip each would dominate);
 // literals and matches are copied by the whole warp, overlapping matches by repeating the source
 // with period `offset`; matches are read back from the unit's own output through L1.
 #include "tk_rb.h"
 #include "tk_inflate.cuh"
+#include "tk_zstd.cuh"
 
 // ---------------------------------------------------------------- host: units
 static inline uint32_t cu_le32(const uint8_t* p) {
@@ -138,13 +141,72 @@ static uint32_t gzip_units(const uint8_t* raw, uint32_t p, uint32_t end, unit_si
     return TK_STATUS_OK;
 }
 
+// zstd frames at [p, end): frame headers and block headers are followed (a few reads per 128 KiB);
+// the unit is the whole payload, sized when every frame announces its content size
+static uint32_t zstd_units(const uint8_t* raw, uint32_t p, uint32_t end, unit_sink& sink) {
+    const uint32_t start = p;
+    uint64_t total = 0;
+    bool sized = true;
+    uint32_t frames = 0;
+    while (p < end) {
+        if (end - p < 4u) return TK_STATUS_CORRUPT;
+        const uint32_t magic = cu_le32(raw + p);
+        if ((magic & 0xFFFFFFF0u) == 0x184D2A50u) {                          // skippable frame
+            if (end - p < 8u || cu_le32(raw + p + 4) > end - p - 8u) return TK_STATUS_CORRUPT;
+            p += 8u + cu_le32(raw + p + 4);
+            continue;
+        }
+        if (magic != 0xFD2FB528u || end - p < 5u) return TK_STATUS_CORRUPT;
+        const uint32_t fhd = raw[p + 4];
+        if (fhd & 0x08u) return TK_STATUS_CORRUPT;
+        const uint32_t single = (fhd >> 5) & 1u, fcs = fhd >> 6, did = fhd & 3u;
+        const uint32_t did_bytes = did == 3u ? 4u : did;
+        const uint32_t fcs_bytes = fcs == 0 ? single : fcs == 1u ? 2u : fcs == 2u ? 4u : 8u;
+        p += 5u;
+        const uint32_t head = (single ? 0u : 1u) + did_bytes + fcs_bytes;
+        if (head > end - p) return TK_STATUS_CORRUPT;
+        const uint8_t* f = raw + p + (single ? 0u : 1u);
+        for (uint32_t k = 0; k < did_bytes; ++k)
+            if (f[k]) return TK_STATUS_UNSUPPORTED;                          // dictionary
+        f += did_bytes;
+        if (!fcs_bytes) sized = false;
+        else {
+            uint64_t v = 0;
+            for (uint32_t k = 0; k < fcs_bytes; ++k) v |= (uint64_t)f[k] << (8u * k);
+            total += v + (fcs_bytes == 2u ? 256u : 0u);
+        }
+        p += head;
+        for (;;) {                                                           // blocks
+            if (end - p < 3u) return TK_STATUS_CORRUPT;
+            const uint32_t bh = raw[p] | ((uint32_t)raw[p + 1] << 8) | ((uint32_t)raw[p + 2] << 16);
+            p += 3u;
+            const uint32_t type = (bh >> 1) & 3u, size = bh >> 3;
+            if (type == 3u) return TK_STATUS_CORRUPT;
+            const uint32_t body = type == 1u ? 1u : size;
+            if (body > end - p) return TK_STATUS_CORRUPT;
+            p += body;
+            if (bh & 1u) break;
+        }
+        if (fhd & 0x04u) {                                                   // content checksum
+            if (end - p < 4u) return TK_STATUS_CORRUPT;
+            p += 4u;
+        }
+        ++frames;
+    }
+    if (total > 0x7FFFFFFFull) return TK_STATUS_UNSUPPORTED;
+    sized = sized && frames > 0;
+    sink.add(start, end - start, RB_UNIT_ZSTD | (sized ? RB_UNIT_SIZED : 0u), sized ? (uint32_t)total : 0u);
+    return TK_STATUS_OK;
+}
+
 int tk_codec_units_host(const uint8_t* raw, tk_rb_batch& b, uint32_t batch_index, tk_rb_unit* units,
                         uint32_t max_units, uint32_t* n_units) {
     unit_sink sink = {units, max_units, *n_units, batch_index, false};
     const uint32_t first = sink.n;
     const uint32_t status = b.codec == 3u ? lz4_units(raw, b.start + RB_HEADER, b.end, sink)
                           : b.codec == 2u ? snappy_units(raw, b.start + RB_HEADER, b.end, sink)
-                                          : gzip_units(raw, b.start + RB_HEADER, b.end, sink);
+                          : b.codec == 1u ? gzip_units(raw, b.start + RB_HEADER, b.end, sink)
+                                          : zstd_units(raw, b.start + RB_HEADER, b.end, sink);
     TK_REQUIRE(!sink.full, "more compressed blocks in the slot than the unit table holds (%u)", max_units);
     if (status) {
         b.status = status;
@@ -423,7 +485,7 @@ __global__ void __launch_bounds__(256) k_unit_size(const rb_args a) {
     const uint32_t warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, nwarps = (gridDim.x * blockDim.x) >> 5;
     for (uint32_t i = warp; i < a.n_units; i += nwarps) {
         const tk_rb_unit u = a.units[i];
-        if (u.kind & RB_UNIT_SIZED) continue;
+        if ((u.kind & RB_UNIT_SIZED) || (u.kind & 0xFFu) > RB_UNIT_LZ4_CHAIN) continue;
         cz_window w;
         w.raw = a.raw;
         cz_load(w, u.src, lane);
@@ -477,14 +539,14 @@ __global__ void __launch_bounds__(1024) k_unit_place(const rb_args a) {
 }
 
 __global__ void __launch_bounds__(128) k_unit_decode(const rb_args a) {
-    __shared__ tk_inflate_tables inf_tables[4];
     const uint32_t lane = threadIdx.x & 31;
     const uint32_t warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, nwarps = (gridDim.x * blockDim.x) >> 5;
     for (uint32_t i = warp; i < a.n_units; i += nwarps) {
         const tk_rb_unit u = a.units[i];
+        const uint32_t kind = u.kind & 0xFFu;
+        if (kind >= RB_UNIT_DEFLATE) continue;             // k_unit_decode_serial
         if (a.batches[u.batch].status) continue;           // rejected by the size pass or the placement
         uint8_t* out = a.raw2 + u.out;
-        const uint32_t kind = u.kind & 0xFFu;
         uint32_t op = 0, st = TK_STATUS_OK;
         if (kind == RB_UNIT_STORED) {
             for (uint32_t k = lane; k < u.src_len; k += 32) out[k] = a.raw[u.src + k];
@@ -495,7 +557,6 @@ __global__ void __launch_bounds__(128) k_unit_decode(const rb_args a) {
             cz_load(w, u.src, lane);
             if (kind == RB_UNIT_LZ4_BLOCK) st = lz4_block_run<true>(w, lane, u.src, u.src + u.src_len, out, u.unc_len, 0u, op);
             else if (kind == RB_UNIT_LZ4_CHAIN) st = lz4_chain_run<true>(w, lane, u.src, u.src + u.src_len, u.kind, out, u.unc_len, op);
-            else if (kind == RB_UNIT_DEFLATE) st = inflate_run(a.raw, lane, u.src, u.src + u.src_len, out, u.unc_len, op, inf_tables[threadIdx.x >> 5]);
             else st = snappy_run(w, lane, u.src, u.src + u.src_len, out, u.unc_len, op);
         }
         if (!st && op != u.unc_len) st = TK_STATUS_CORRUPT;
@@ -504,16 +565,107 @@ __global__ void __launch_bounds__(128) k_unit_decode(const rb_args a) {
     }
 }
 
-int tk_codec_launch(const rb_args& a, cudaStream_t stream) {
-    if (!a.n_units) {
-        // compressed batches without a single block: their (empty) record ranges still need setting
-        k_unit_place<<<1, 1024, 0, stream>>>(a);
-        TK_LAUNCH_CHECK();
-        return 0;
+// ---------------------------------------------------------------- serial formats: gzip, zstd
+union unit_tables {
+    tk_inflate_tables inflate;
+    tk_zstd_tables    zstd;
+};
+
+// Lane 0 owns the decoder state and produces copy events; the warp executes them.  Literals that
+// lane 0 decoded itself (Huffman) are parked at the end of the unit's output and move down from
+// there: the destination is below the source, so chunks of 32 bytes go load, barrier, store.
+__device__ __forceinline__ uint32_t zstd_run(const uint8_t* raw, uint32_t lane, uint32_t p, uint32_t end, uint8_t* out,
+                                             uint32_t cap, uint32_t& op, tk_zstd_tables& tb) {
+    tk_zstd_state s;
+    if (lane == 0) tk_zstd_init(s, tb, raw, p, end);
+    for (;;) {
+        tk_zstd_event ev;
+        ev.lit_len = ev.lit_kind = ev.lit_src = ev.mlen = ev.offset = 0;
+        uint32_t st = TK_ZS_DONE;
+        if (lane == 0) st = (uint32_t)tk_zstd_next(s, tb, out, cap, op, true, &ev);
+        __syncwarp();                                       // lane 0's literal stores before the warp reads them
+        st = __shfl_sync(0xffffffffu, st, 0);
+        if (st == TK_ZS_DONE) return TK_STATUS_OK;
+        if (st != TK_ZS_COPY) return st == TK_ZS_UNSUPPORTED ? TK_STATUS_UNSUPPORTED : TK_STATUS_CORRUPT;
+        const uint32_t n = __shfl_sync(0xffffffffu, ev.lit_len, 0), kind = __shfl_sync(0xffffffffu, ev.lit_kind, 0);
+        const uint32_t src = __shfl_sync(0xffffffffu, ev.lit_src, 0);
+        const uint32_t mlen = __shfl_sync(0xffffffffu, ev.mlen, 0), offset = __shfl_sync(0xffffffffu, ev.offset, 0);
+        if (kind == TK_ZL_INPUT) {
+            for (uint32_t k = lane; k < n; k += 32) out[op + k] = raw[src + k];
+        } else if (kind == TK_ZL_RLE) {
+            for (uint32_t k = lane; k < n; k += 32) out[op + k] = (uint8_t)src;
+        } else if (src != op) {
+            for (uint32_t base = 0; base < n; base += 32) {
+                const uint32_t k = base + lane;
+                const uint8_t v = k < n ? out[src + k] : 0;
+                __syncwarp();
+                if (k < n) out[op + k] = v;
+            }
+        }
+        op += n;
+        if (mlen) cz_match(out, op, offset, mlen, lane);
+        op += mlen;
     }
-    k_unit_size<<<min((a.n_units + 7) / 8, 148u * 8u), 256, 0, stream>>>(a);
+}
+
+// Size pass of zstd units without a content size: lane 0 walks the sequences, nothing is written.
+__global__ void __launch_bounds__(128) k_unit_size_zstd(const rb_args a) {
+    __shared__ unit_tables tables[4];
+    const uint32_t lane = threadIdx.x & 31;
+    const uint32_t warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, nwarps = (gridDim.x * blockDim.x) >> 5;
+    for (uint32_t i = warp; i < a.n_units; i += nwarps) {
+        const tk_rb_unit u = a.units[i];
+        if ((u.kind & 0xFFu) != RB_UNIT_ZSTD || (u.kind & RB_UNIT_SIZED)) continue;
+        if (lane == 0) {
+            tk_zstd_tables& tb = tables[threadIdx.x >> 5].zstd;
+            tk_zstd_state s;
+            tk_zstd_init(s, tb, a.raw, u.src, u.src + u.src_len);
+            tk_zstd_event ev;
+            uint32_t op = 0, st;
+            while ((st = (uint32_t)tk_zstd_next(s, tb, nullptr, 0x7FFFFFFFu, op, false, &ev)) == TK_ZS_COPY)
+                op += ev.lit_len + ev.mlen;
+            a.units[i].unc_len = st == TK_ZS_DONE ? op : 0u;
+            if (st != TK_ZS_DONE) a.units[i].kind = u.kind | RB_UNIT_FAILED;
+        }
+        __syncwarp();
+    }
+}
+
+__global__ void __launch_bounds__(128) k_unit_decode_serial(const rb_args a) {
+    __shared__ unit_tables tables[4];
+    const uint32_t lane = threadIdx.x & 31;
+    const uint32_t warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, nwarps = (gridDim.x * blockDim.x) >> 5;
+    for (uint32_t i = warp; i < a.n_units; i += nwarps) {
+        const tk_rb_unit u = a.units[i];
+        const uint32_t kind = u.kind & 0xFFu;
+        if (kind < RB_UNIT_DEFLATE || a.batches[u.batch].status) continue;
+        uint8_t* out = a.raw2 + u.out;
+        uint32_t op = 0, st;
+        if (kind == RB_UNIT_DEFLATE)
+            st = inflate_run(a.raw, lane, u.src, u.src + u.src_len, out, u.unc_len, op, tables[threadIdx.x >> 5].inflate);
+        else
+            st = zstd_run(a.raw, lane, u.src, u.src + u.src_len, out, u.unc_len, op, tables[threadIdx.x >> 5].zstd);
+        if (!st && op != u.unc_len) st = TK_STATUS_CORRUPT;
+        if (st && lane == 0) a.batches[u.batch].status = st;
+        __syncwarp();                                       // the tables are reused by the warp's next unit
+    }
+}
+
+int tk_codec_launch(const rb_args& a, const tk_rb_unit* h_units, cudaStream_t stream) {
+    // which kernels this slot needs
+    uint32_t lz_unsized = 0, zs_unsized = 0, warp_units = 0, serial_units = 0;
+    for (uint32_t i = 0; i < a.n_units; ++i) {
+        const uint32_t kind = h_units[i].kind & 0xFFu;
+        const bool sized = h_units[i].kind & RB_UNIT_SIZED;
+        if (kind >= RB_UNIT_DEFLATE) { ++serial_units; if (kind == RB_UNIT_ZSTD && !sized) ++zs_unsized; }
+        else { ++warp_units; if (!sized) ++lz_unsized; }
+    }
+    if (lz_unsized) k_unit_size<<<min((a.n_units + 7) / 8, 148u * 8u), 256, 0, stream>>>(a);
+    if (zs_unsized) k_unit_size_zstd<<<min((a.n_units + 3) / 4, 148u * 5u), 128, 0, stream>>>(a);
+    // (also sets the empty record ranges of compressed batches without a single block)
     k_unit_place<<<1, 1024, 0, stream>>>(a);
-    k_unit_decode<<<min((a.n_units + 3) / 4, 148u * 16u), 128, 0, stream>>>(a);
+    if (warp_units) k_unit_decode<<<min((a.n_units + 3) / 4, 148u * 16u), 128, 0, stream>>>(a);
+    if (serial_units) k_unit_decode_serial<<<min((a.n_units + 3) / 4, 148u * 5u), 128, 0, stream>>>(a);
     TK_LAUNCH_CHECK();
     return 0;
 }

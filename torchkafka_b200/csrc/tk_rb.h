@@ -10,9 +10,10 @@
 // One independently decodable piece of a compressed batch, found by the host's walk over the
 // codec's framing (tk_codec_units_host): an LZ4 block of a block-independent frame, the whole
 // block chain of a block-dependent frame, a stored (uncompressed) block, a snappy block (the
-// whole batch, or one chunk of xerial framing), the DEFLATE stream of a gzip member.  Units of a batch are consecutive and decode
+// whole batch, or one chunk of xerial framing), the DEFLATE stream of a gzip member, the
+// Zstandard frames of a batch.  Units of a batch are consecutive and decode
 // into consecutive ranges of the decompressed buffer.
-enum { RB_UNIT_LZ4_BLOCK = 1, RB_UNIT_LZ4_CHAIN = 2, RB_UNIT_STORED = 3, RB_UNIT_SNAPPY = 4, RB_UNIT_DEFLATE = 5 };
+enum { RB_UNIT_LZ4_BLOCK = 1, RB_UNIT_LZ4_CHAIN = 2, RB_UNIT_STORED = 3, RB_UNIT_SNAPPY = 4, RB_UNIT_DEFLATE = 5, RB_UNIT_ZSTD = 6 };
 #define RB_UNIT_BLOCK_CHECKSUM 0x100u    // LZ4 chain: 4 checksum bytes behind every block
 #define RB_UNIT_CONTENT_CHECKSUM 0x200u  // LZ4 chain: 4 checksum bytes behind the end mark
 #define RB_UNIT_SIZED 0x400u             // unc_len is known from the framing (no size pass)
@@ -42,11 +43,12 @@ struct rb_args {
 };
 
 // host: units of batch `b` appended to units[*n_units...]; sets b.unit_first /
-// b.unit_count, or b.status when the framing is broken or not handled (codec 1, 2 or 3)
+// b.unit_count, or b.status when the framing is broken or not handled (codec 1 .. 4)
 int tk_codec_units_host(const uint8_t* raw, tk_rb_batch& b, uint32_t batch_index, tk_rb_unit* units,
                         uint32_t max_units, uint32_t* n_units);
-// device: size pass, placement, decode of a.units on `stream`
-int tk_codec_launch(const rb_args& a, cudaStream_t stream);
+// device: size pass, placement, decode of a.units on `stream`; h_units = the host's copy (which
+// kernels are needed)
+int tk_codec_launch(const rb_args& a, const tk_rb_unit* h_units, cudaStream_t stream);
 
 #if defined(__CUDACC__)
 // exclusive scan of one 64-bit value per thread of a 1024-thread block; *total = block sum

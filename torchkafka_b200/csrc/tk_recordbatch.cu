@@ -23,7 +23,7 @@
 //                 destination words, funnel-shifted source); values above 16 KiB are queued and
 //                 copied in 4 KiB pieces by all warps (k_rb_copy_big)
 // Big-endian header fields, zig-zag varints.  LZ4 and snappy batches are decompressed first
-// (tk_codecs.cu), gzip batches too (tk_inflate.cuh); zstd batches are reported as unsupported.
+// (tk_codecs.cu), gzip and zstd batches too (tk_inflate.cuh, tk_zstd.cuh).
 #include "tk_rb.h"
 #include <mutex>
 
@@ -120,10 +120,10 @@ static int rb_walk_host(const uint8_t* raw, const tk_blob_t* blobs, uint32_t n_b
                 const uint32_t magic = raw[pos + 16];
                 const uint32_t c = rb_host_be32(raw + pos + 57);
                 codec = raw[pos + 22] & 7u;
-                // a record is at least 7 bytes (LZ4 and snappy expand at most ~255-fold, DEFLATE 1032-fold): a larger count cannot
+                // a record is at least 7 bytes (LZ4 and snappy expand at most ~255-fold, DEFLATE 1032-fold, zstd's RLE blocks far more): a larger count cannot
                 // be true (the checksum would say so too, but the count sizes the slot before the
                 // checksum is looked at)
-                const uint64_t room = (uint64_t)(end - pos - RB_HEADER) * (codec == 1u ? 1032u : codec ? 255u : 1u);
+                const uint64_t room = (uint64_t)(end - pos - RB_HEADER) * (codec == 4u ? 65536u : codec == 1u ? 1032u : codec ? 255u : 1u);
                 if (magic != 2) { status = TK_STATUS_CORRUPT; end = blob_end; }
                 else if (c > room / 7u + 1u) status = TK_STATUS_CORRUPT;
                 else count = c;
@@ -141,7 +141,7 @@ static int rb_walk_host(const uint8_t* raw, const tk_blob_t* blobs, uint32_t n_b
             b.n_rec = count; b.value_bytes = 0; b.rec_base = (uint32_t)nrec; b.byte_base = 0;
             b.codec = status ? 0u : codec; b.rec_start = pos + RB_HEADER; b.rec_end = end;
             b.unit_first = 0; b.unit_count = 0; b.reserved = 0;
-            if (b.codec >= 1u && b.codec <= 3u) {            // gzip, snappy, LZ4: cut into decodable units
+            if (b.codec >= 1u && b.codec <= 4u) {            // gzip, snappy, LZ4, zstd: cut into decodable units
                 ++*n_coded_out;
                 const int rc = tk_codec_units_host(raw, b, nb - 1, units, max_units, n_units_out);
                 if (rc) return rc;
@@ -321,7 +321,7 @@ __global__ void __launch_bounds__(256) k_rb_check(const rb_args a) {
         if (!status) {
             const uint32_t attributes = ((uint32_t)a.raw[b.start + 21] << 8) | a.raw[b.start + 22];
             control = attributes & 0x20u;
-            if (b.codec > 3u) status = TK_STATUS_UNSUPPORTED;  // zstd
+            if (b.codec > 4u) status = TK_STATUS_UNSUPPORTED;  // no such codec
         }
         // the records: behind the header, or (compressed) in the batch's region of the decompressed buffer
         const uint8_t* rbase = b.codec ? a.raw2 : a.raw;
@@ -579,7 +579,7 @@ extern "C" int tk_slot_submit_recordbatches(tk_ctx* ctx, int slot, uint64_t n_by
     a.units = s.d.rb_units; a.n_units = n_units;
     a.summary = s.d.rb_summary; a.temp = s.d.rb_temp; a.bigq = s.d.rb_bigq; a.bytes = s.d.bytes; a.recs = s.d.recs;
     a.slot_records = ctx->slot_records; a.slot_bytes = ctx->slot_bytes;
-    if (n_coded) { rc = tk_codec_launch(a, ks); if (rc) return rc; }
+    if (n_coded) { rc = tk_codec_launch(a, s.h_rb_units, ks); if (rc) return rc; }
     k_rb_check<<<148 * 4, 256, 0, ks>>>(a);
     k_rb_prefix<<<1, 1024, 0, ks>>>(a);
     k_rb_copy<<<148 * 8, 256, 0, ks>>>(a);

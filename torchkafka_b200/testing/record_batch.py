@@ -140,8 +140,26 @@ def gzip_member(data: bytes, level: int = 6, name: bytes = None, extra: bytes = 
     return bytes(head) + body + struct.pack("<II", zlib.crc32(data) & 0xFFFFFFFF, len(data) & 0xFFFFFFFF)
 
 
+def zstd_frame(data: bytes, level: int = 3, content_size: bool = False) -> bytes:
+    """One Zstandard frame (libzstd through pyarrow).  Kafka's Java client compresses through a
+    stream and so writes no Frame_Content_Size: that is the default here -- the field is taken
+    out of the one-shot frame and a window descriptor put in place of the single-segment flag
+    (the frame header carries no checksum)."""
+    import pyarrow as pa
+    z = pa.Codec("zstd", compression_level=level).compress(data, asbytes=True)
+    if content_size:
+        return z
+    fhd = z[4]
+    single, fcs, did = (fhd >> 5) & 1, fhd >> 6, fhd & 3
+    pos = 5 + (0 if single else 1) + (4 if did == 3 else did)
+    fcs_bytes = (1 if single else 0) if fcs == 0 else (2, 4, 8)[fcs - 1]
+    return z[:4] + bytes([fhd & 0x07, (27 - 10) << 3]) + z[5 + (0 if single else 1):pos] + z[pos + fcs_bytes:]
+
+
 #: codec argument of encode_batch -> (attribute bits, compressor)
 CODECS = {
+    4: (4, zstd_frame), "zstd": (4, zstd_frame), "zstds": (4, lambda d: zstd_frame(d, 1, content_size=True)),
+    "zstd19": (4, lambda d: zstd_frame(d, 19)),
     1: (1, gzip_member), "gzip": (1, gzip_member), "gzip0": (1, lambda d: gzip_member(d, level=0)),
     "gzipx": (1, lambda d: gzip_member(d, 9, name=b"records.bin", extra=b"\x01\x02\x03", comment=b"c", header_crc=True)),
     3: (3, lz4_frame), "lz4": (3, lz4_frame), "lz4i": (3, lz4_frame_independent),
@@ -155,7 +173,7 @@ def encode_batch(base_offset: int, values: Sequence[Optional[bytes]], attributes
                  headers: Optional[Sequence] = None, crc: Optional[int] = None, codec: int = 0) -> bytes:
     """One RecordBatch v2.  `offset_deltas` default to 0, 1, 2, ... (a compacted topic has gaps).
     `codec` (a key of CODECS: 3 / "lz4", "lz4i", "lz4ic", 2 / "snappy", "snappy_raw", 1 / "gzip", "gzip0",
-    "gzipx") compresses the
+    "gzipx", 4 / "zstd", "zstds", "zstd19") compresses the
     records and sets the attribute bits."""
     n = len(values)
     deltas = list(range(n)) if offset_deltas is None else list(offset_deltas)

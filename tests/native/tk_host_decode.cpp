@@ -165,6 +165,11 @@ extern "C" int tk_host_zstd(const uint8_t* in, uint32_t len, uint8_t* out, uint3
     for (;;) {
         const int st = tk_zstd_next(s, tb, out, emit ? cap : 0x7FFFFFFFu, op, emit != 0, &ev);
         if (st == TK_ZS_DONE) break;
+        if (st == TK_ZS_HUF) {
+            for (uint32_t k = 0; k < ev.h_streams; ++k)
+                if (!tk_huf_stream(in, ev.h_lo[k], ev.h_hi[k], tb.huf, (int)ev.h_log, out + ev.h_dst[k], ev.h_n[k])) return TK_ZS_ERROR;
+            continue;
+        }
         if (st != TK_ZS_COPY) return st;
         if (emit) {
             if (ev.lit_kind == TK_ZL_INPUT) memmove(out + op, in + ev.lit_src, ev.lit_len);

@@ -575,21 +575,25 @@ union unit_tables {
 // lane 0 decoded itself (Huffman) are parked at the end of the unit's output and move down from
 // there: the destination is below the source, so chunks of 32 bytes go load, barrier, store.
 __device__ __forceinline__ uint32_t zstd_run(const uint8_t* raw, uint32_t lane, uint32_t p, uint32_t end, uint8_t* out,
-                                             uint32_t cap, uint32_t& op, tk_zstd_tables& tb) {
+                                             uint32_t cap, uint32_t& op, tk_zstd_tables& tb, tk_zstd_event& ev) {
     tk_zstd_state s;
     if (lane == 0) tk_zstd_init(s, tb, raw, p, end);
     for (;;) {
-        tk_zstd_event ev;
-        ev.lit_len = ev.lit_kind = ev.lit_src = ev.mlen = ev.offset = 0;
         uint32_t st = TK_ZS_DONE;
         if (lane == 0) st = (uint32_t)tk_zstd_next(s, tb, out, cap, op, true, &ev);
-        __syncwarp();                                       // lane 0's literal stores before the warp reads them
+        __syncwarp();                                       // the event (shared memory) and the tables are written
         st = __shfl_sync(0xffffffffu, st, 0);
         if (st == TK_ZS_DONE) return TK_STATUS_OK;
+        if (st == TK_ZS_HUF) {                              // the block's literals: one Huffman stream per lane
+            bool ok = true;
+            if (lane < ev.h_streams)
+                ok = tk_huf_stream(raw, ev.h_lo[lane], ev.h_hi[lane], tb.huf, (int)ev.h_log, out + ev.h_dst[lane], ev.h_n[lane]);
+            if (!__all_sync(0xffffffffu, ok)) return TK_STATUS_CORRUPT;
+            __syncwarp();                                   // literals stored, event read by every lane
+            continue;
+        }
         if (st != TK_ZS_COPY) return st == TK_ZS_UNSUPPORTED ? TK_STATUS_UNSUPPORTED : TK_STATUS_CORRUPT;
-        const uint32_t n = __shfl_sync(0xffffffffu, ev.lit_len, 0), kind = __shfl_sync(0xffffffffu, ev.lit_kind, 0);
-        const uint32_t src = __shfl_sync(0xffffffffu, ev.lit_src, 0);
-        const uint32_t mlen = __shfl_sync(0xffffffffu, ev.mlen, 0), offset = __shfl_sync(0xffffffffu, ev.offset, 0);
+        const uint32_t n = ev.lit_len, kind = ev.lit_kind, src = ev.lit_src, mlen = ev.mlen, offset = ev.offset;
         if (kind == TK_ZL_INPUT) {
             for (uint32_t k = lane; k < n; k += 32) out[op + k] = raw[src + k];
         } else if (kind == TK_ZL_RLE) {
@@ -605,6 +609,7 @@ __device__ __forceinline__ uint32_t zstd_run(const uint8_t* raw, uint32_t lane, 
         op += n;
         if (mlen) cz_match(out, op, offset, mlen, lane);
         op += mlen;
+        __syncwarp();                                       // every lane has read the event
     }
 }
 
@@ -633,6 +638,7 @@ __global__ void __launch_bounds__(128) k_unit_size_zstd(const rb_args a) {
 
 __global__ void __launch_bounds__(128) k_unit_decode_serial(const rb_args a) {
     __shared__ unit_tables tables[4];
+    __shared__ tk_zstd_event events[4];
     const uint32_t lane = threadIdx.x & 31;
     const uint32_t warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, nwarps = (gridDim.x * blockDim.x) >> 5;
     for (uint32_t i = warp; i < a.n_units; i += nwarps) {
@@ -644,7 +650,8 @@ __global__ void __launch_bounds__(128) k_unit_decode_serial(const rb_args a) {
         if (kind == RB_UNIT_DEFLATE)
             st = inflate_run(a.raw, lane, u.src, u.src + u.src_len, out, u.unc_len, op, tables[threadIdx.x >> 5].inflate);
         else
-            st = zstd_run(a.raw, lane, u.src, u.src + u.src_len, out, u.unc_len, op, tables[threadIdx.x >> 5].zstd);
+            st = zstd_run(a.raw, lane, u.src, u.src + u.src_len, out, u.unc_len, op, tables[threadIdx.x >> 5].zstd,
+                          events[threadIdx.x >> 5]);
         if (!st && op != u.unc_len) st = TK_STATUS_CORRUPT;
         if (st && lane == 0) a.batches[u.batch].status = st;
         __syncwarp();                                       // the tables are reused by the warp's next unit

@@ -17,14 +17,18 @@
 #include <string.h>
 #include "tk_number.cuh"      // TK_HD
 
-enum { TK_ZS_COPY = 0, TK_ZS_DONE = 1, TK_ZS_ERROR = 2, TK_ZS_UNSUPPORTED = 3 };
+enum { TK_ZS_COPY = 0, TK_ZS_DONE = 1, TK_ZS_ERROR = 2, TK_ZS_UNSUPPORTED = 3, TK_ZS_HUF = 4 };
 enum { TK_ZL_INPUT = 0, TK_ZL_OUTPUT = 1, TK_ZL_RLE = 2 };
 
 // One step of the output: lit_len literal bytes (from the input at lit_src, from the output
 // buffer at lit_src -- Huffman-decoded literals are parked at its end --, or lit_len copies of the
 // byte lit_src), then mlen bytes from `offset` bytes back.
+// TK_ZS_HUF instead: the block's literals are h_streams (1 or 4) independent Huffman streams,
+// stream k = in[h_lo[k], h_hi[k]) -> h_n[k] bytes at out + h_dst[k] (tk_huf_stream with the
+// decoder's current tree, longest code h_log); the caller decodes them -- the device one per lane.
 struct tk_zstd_event {
     uint32_t lit_len, lit_kind, lit_src, mlen, offset;
+    uint32_t h_streams, h_log, h_lo[4], h_hi[4], h_dst[4], h_n[4];
 };
 
 struct tk_fse_entry {
@@ -43,9 +47,11 @@ struct tk_zstd_tables {
 };
 
 TK_HD int tk_zs_highbit(uint32_t x) {                  // index of the highest set bit, x != 0
-    int n = 0;
-    while (x >>= 1) ++n;
-    return n;
+#if defined(__CUDA_ARCH__)
+    return 31 - __clz((int)x);
+#else
+    return 31 - __builtin_clz(x);
+#endif
 }
 
 // n <= 32 bits starting at bit `bitpos` of the little-endian bit array in[lo, hi); bits outside
@@ -274,13 +280,13 @@ TK_HD bool tk_huf_stream(const uint8_t* in, uint32_t lo, uint32_t hi, const uint
 }
 
 // ---------------------------------------------------------------- frames, blocks, sequences
-enum { TK_ZM_FRAME = 0, TK_ZM_BLOCK = 1, TK_ZM_SEQ = 2 };
+enum { TK_ZM_FRAME = 0, TK_ZM_BLOCK = 1, TK_ZM_SEQ = 2, TK_ZM_SEQHDR = 3 };
 #define TK_ZS_BLOCK_MAX (128u << 10)
 
 struct tk_zstd_state {
     const uint8_t* in;
     uint32_t pos, end;             // cursor in the batch payload
-    uint32_t rep[3];               // repeat offsets of the frame
+    uint32_t rep0, rep1, rep2;     // repeat offsets of the frame (scalars: the state stays in registers)
     int      ll_log, ml_log, of_log;   // accuracy logs of the current sequence tables, -1: none yet
     int      huf_log;              // longest code of the current literals tree, 0: none yet
     int      mode, last_block, checksum;
@@ -342,8 +348,9 @@ TK_HD int tk_zstd_seq_table(tk_zstd_state& s, tk_zstd_tables& tb, uint32_t mode,
     return TK_ZS_COPY;
 }
 
-// Literals section and sequences header of the compressed block at s.pos .. s.block_end.
-TK_HD int tk_zstd_block_start(tk_zstd_state& s, tk_zstd_tables& tb, uint8_t* out, uint32_t cap, uint32_t op, bool emit) {
+// Literals section of the compressed block at s.pos .. s.block_end.  TK_ZS_HUF: *ev describes the
+// Huffman streams the caller has to decode before it goes on.
+TK_HD int tk_zstd_literals(tk_zstd_state& s, tk_zstd_tables& tb, uint32_t cap, uint32_t op, bool emit, tk_zstd_event* ev) {
     const uint8_t* in = s.in;
     const uint32_t bend = s.block_end;
     if (bend - s.pos < 2u) return TK_ZS_ERROR;
@@ -393,8 +400,10 @@ TK_HD int tk_zstd_block_start(tk_zstd_state& s, tk_zstd_tables& tb, uint8_t* out
             if (regen > cap - op) return TK_ZS_ERROR;
             const uint32_t dst = cap - regen;
             s.lit_src = dst;
+            ev->h_streams = streams;
+            ev->h_log = (uint32_t)s.huf_log;
             if (streams == 1u) {
-                if (!tk_huf_stream(in, lo, hi, tb.huf, s.huf_log, out + dst, regen)) return TK_ZS_ERROR;
+                ev->h_lo[0] = lo; ev->h_hi[0] = hi; ev->h_dst[0] = dst; ev->h_n[0] = regen;
             } else {
                 if (hi - lo < 6u) return TK_ZS_ERROR;
                 const uint32_t z1 = tk_zs_le(in + lo, 2), z2 = tk_zs_le(in + lo + 2, 2), z3 = tk_zs_le(in + lo + 4, 2);
@@ -402,16 +411,24 @@ TK_HD int tk_zstd_block_start(tk_zstd_state& s, tk_zstd_tables& tb, uint8_t* out
                 if ((uint64_t)z1 + z2 + z3 > hi - lo) return TK_ZS_ERROR;
                 const uint32_t per = (regen + 3u) / 4u;
                 if (3u * per > regen) return TK_ZS_ERROR;
-                if (!tk_huf_stream(in, lo, lo + z1, tb.huf, s.huf_log, out + dst, per) ||
-                    !tk_huf_stream(in, lo + z1, lo + z1 + z2, tb.huf, s.huf_log, out + dst + per, per) ||
-                    !tk_huf_stream(in, lo + z1 + z2, lo + z1 + z2 + z3, tb.huf, s.huf_log, out + dst + 2u * per, per) ||
-                    !tk_huf_stream(in, lo + z1 + z2 + z3, hi, tb.huf, s.huf_log, out + dst + 3u * per, regen - 3u * per))
-                    return TK_ZS_ERROR;
+                ev->h_lo[0] = lo;           ev->h_hi[0] = lo + z1;
+                ev->h_lo[1] = lo + z1;      ev->h_hi[1] = lo + z1 + z2;
+                ev->h_lo[2] = lo + z1 + z2; ev->h_hi[2] = lo + z1 + z2 + z3;
+                ev->h_lo[3] = lo + z1 + z2 + z3; ev->h_hi[3] = hi;
+                for (uint32_t k = 0; k < 4u; ++k) { ev->h_dst[k] = dst + k * per; ev->h_n[k] = k < 3u ? per : regen - 3u * per; }
             }
+            s.lit_left = regen;
+            return regen ? TK_ZS_HUF : TK_ZS_COPY;
         }
     }
     s.lit_left = regen;
-    // ---- sequences header
+    return TK_ZS_COPY;
+}
+
+// Sequences header of the block (behind its literals section): count, tables, initial states.
+TK_HD int tk_zstd_seq_header(tk_zstd_state& s, tk_zstd_tables& tb) {
+    const uint8_t* in = s.in;
+    const uint32_t bend = s.block_end;
     if (s.pos >= bend) return TK_ZS_ERROR;
     uint32_t nseq = in[s.pos++];
     if (nseq >= 128u) {
@@ -479,7 +496,7 @@ TK_HD int tk_zstd_next(tk_zstd_state& s, tk_zstd_tables& tb, uint8_t* out, uint3
             if (head > s.end - s.pos) return TK_ZS_ERROR;
             if (did_bytes && tk_zs_le(in + s.pos + (single ? 0u : 1u), (int)did_bytes) != 0) return TK_ZS_UNSUPPORTED;
             s.pos += head;
-            s.rep[0] = 1; s.rep[1] = 4; s.rep[2] = 8;
+            s.rep0 = 1; s.rep1 = 4; s.rep2 = 8;
             s.ll_log = s.ml_log = s.of_log = -1;
             s.huf_log = 0;
             s.last_block = 0;
@@ -513,7 +530,12 @@ TK_HD int tk_zstd_next(tk_zstd_state& s, tk_zstd_tables& tb, uint8_t* out, uint3
             }
             if (size > s.end - s.pos) return TK_ZS_ERROR;
             s.block_end = s.pos + size;
-            const int st = tk_zstd_block_start(s, tb, out, cap, op, emit);
+            const int st = tk_zstd_literals(s, tb, cap, op, emit, ev);
+            s.mode = TK_ZM_SEQHDR;
+            if (st) return st;                                       // TK_ZS_HUF: back here once the caller decoded them
+        }
+        if (s.mode == TK_ZM_SEQHDR) {
+            const int st = tk_zstd_seq_header(s, tb);
             if (st) return st;
             s.mode = TK_ZM_SEQ;
         }
@@ -538,16 +560,16 @@ TK_HD int tk_zstd_next(tk_zstd_state& s, tk_zstd_tables& tb, uint8_t* out, uint3
         uint32_t offset;
         if (ov > 3u) {
             offset = ov - 3u;
-            s.rep[2] = s.rep[1]; s.rep[1] = s.rep[0]; s.rep[0] = offset;
+            s.rep2 = s.rep1; s.rep1 = s.rep0; s.rep0 = offset;
         } else {
             const uint32_t idx = ov - 1u + (llen == 0 ? 1u : 0u);
             if (idx == 0) {
-                offset = s.rep[0];
+                offset = s.rep0;
             } else {
-                offset = idx < 3u ? s.rep[idx] : s.rep[0] - 1u;
-                if (idx > 1u) s.rep[2] = s.rep[1];
-                s.rep[1] = s.rep[0];
-                s.rep[0] = offset;
+                offset = idx == 1u ? s.rep1 : idx == 2u ? s.rep2 : s.rep0 - 1u;
+                if (idx > 1u) s.rep2 = s.rep1;
+                s.rep1 = s.rep0;
+                s.rep0 = offset;
             }
         }
         if (--s.seq_left) {

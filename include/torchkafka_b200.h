@@ -259,10 +259,12 @@ int tk_compact_noalloc(const int32_t* d_keep, uint32_t n, uint32_t batch_size, u
  * the ConsumerRecord that `for record in self._consumer` (src/kafka_dataset.py:156) yields.
  *   - a batch that is cut off by the end of its blob is ignored (fetch responses end so)
  *   - records with offset < fetch_offset are skipped (batches are returned whole)
- *   - LZ4 and snappy batches (attributes & 7 == 3 / 2; kafka/codec.py lz4_decode,
- *     snappy_decode) are decompressed on the device (LZ4 frame + block format, xxHash checksums
- *     skipped: the batch CRC covers the same bytes; snappy blocks, raw or in snappy-java's xerial
- *     framing); gzip / zstd batches surface as TK_STATUS_UNSUPPORTED
+ *   - compressed batches (attributes & 7: 1 gzip, 2 snappy, 3 LZ4, 4 zstd; kafka/codec.py
+ *     gzip_decode, snappy_decode, lz4_decode, zstd_decode) are decompressed on the device: gzip
+ *     member + DEFLATE; snappy blocks, raw or in snappy-java's xerial framing; LZ4 frame + block
+ *     format; Zstandard frames without dictionary (one with a dictionary id surfaces as
+ *     TK_STATUS_UNSUPPORTED).  The inner checksums (CRC-32, xxHash) are not verified: the
+ *     batch's CRC-32C covers the same bytes
  *   - control batches are skipped; null values surface as TK_STATUS_UNSUPPORTED, CRC /
  *     framing / compressed-stream errors as TK_STATUS_CORRUPT on the first record of the batch, when
  *     the batch that contains it is delivered

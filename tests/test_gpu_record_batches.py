@@ -302,6 +302,19 @@ def test_broken_gzip_batches_raise_at_their_batch(damage):
     assert ei.value.status == status and ei.value.partition == 1 and ei.value.offset == 4
 
 
+def test_zstd_frames_without_content_size_placed_by_bound_or_sized_first(monkeypatch):
+    """Frames without a content size: placed by their upper bound when the slot's bounds fit the
+    decompressed buffer (which grows for them), otherwise sized by a first pass; both must agree
+    with the oracle.  Small slots with many small batches exceed the bound budget on their own."""
+    log = syn.make_log(2, 3000, seed=36, partitions=8, layout="chunked", chunk=100)
+    schema = JsonArray(torch.float32, max_len=256, min_size=32)
+    check_raw(log, schema, 128, batch_bytes=16384, codec=4)                       # bounds fit
+    check_raw(log, schema, 128, batch_bytes=2048, codec=4, slot_bytes=300_000)    # 128 KiB bound per 2.6 KB batch: size pass
+    monkeypatch.setenv("TK_ZSTD_SIZE_PASS", "1")
+    check_raw(log, schema, 128, batch_bytes=16384, codec=4)
+    check_raw(log, schema, 128, batch_bytes=200000, codec="zstd19")
+
+
 @pytest.mark.parametrize("damage", ["magic", "blocktype", "truncated", "dictionary", "size"])
 @pytest.mark.parametrize("codec", [4, "zstds"])
 def test_broken_zstd_batches_raise_at_their_batch(damage, codec):

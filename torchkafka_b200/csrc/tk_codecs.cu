@@ -145,7 +145,7 @@ static uint32_t gzip_units(const uint8_t* raw, uint32_t p, uint32_t end, unit_si
 // the unit is the whole payload, sized when every frame announces its content size
 static uint32_t zstd_units(const uint8_t* raw, uint32_t p, uint32_t end, unit_sink& sink) {
     const uint32_t start = p;
-    uint64_t total = 0;
+    uint64_t total = 0, bound = 0;
     bool sized = true;
     uint32_t frames = 0;
     while (p < end) {
@@ -185,6 +185,7 @@ static uint32_t zstd_units(const uint8_t* raw, uint32_t p, uint32_t end, unit_si
             const uint32_t body = type == 1u ? 1u : size;
             if (body > end - p) return TK_STATUS_CORRUPT;
             p += body;
+            bound += type == 2u ? TK_ZS_BLOCK_MAX : size;                    // a compressed block holds at most 128 KiB
             if (bh & 1u) break;
         }
         if (fhd & 0x04u) {                                                   // content checksum
@@ -195,7 +196,10 @@ static uint32_t zstd_units(const uint8_t* raw, uint32_t p, uint32_t end, unit_si
     }
     if (total > 0x7FFFFFFFull) return TK_STATUS_UNSUPPORTED;
     sized = sized && frames > 0;
-    sink.add(start, end - start, RB_UNIT_ZSTD | (sized ? RB_UNIT_SIZED : 0u), sized ? (uint32_t)total : 0u);
+    // without a content size: the upper bound (the caller decides between it and the size pass)
+    const bool bounded = !sized && bound <= 0x7FFFFFFFull;
+    sink.add(start, end - start, RB_UNIT_ZSTD | (sized ? RB_UNIT_SIZED : bounded ? RB_UNIT_BOUND : 0u),
+             sized ? (uint32_t)total : bounded ? (uint32_t)bound : 0u);
     return TK_STATUS_OK;
 }
 
@@ -533,7 +537,7 @@ __global__ void __launch_bounds__(1024) k_unit_place(const rb_args a) {
         }
         const unsigned long long first = a.units[b.unit_first].out;
         if (failed) b.status = TK_STATUS_CORRUPT;
-        else if (first + total > a.slot_bytes) b.status = TK_STATUS_UNSUPPORTED;   // does not fit the slot
+        else if (first + total > a.raw2_bytes) b.status = TK_STATUS_UNSUPPORTED;   // does not fit the buffer
         else { b.rec_start = (uint32_t)first; b.rec_end = (uint32_t)(first + total); }
     }
 }
@@ -620,7 +624,7 @@ __global__ void __launch_bounds__(128) k_unit_size_zstd(const rb_args a) {
     const uint32_t warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, nwarps = (gridDim.x * blockDim.x) >> 5;
     for (uint32_t i = warp; i < a.n_units; i += nwarps) {
         const tk_rb_unit u = a.units[i];
-        if ((u.kind & 0xFFu) != RB_UNIT_ZSTD || (u.kind & RB_UNIT_SIZED)) continue;
+        if ((u.kind & 0xFFu) != RB_UNIT_ZSTD || (u.kind & (RB_UNIT_SIZED | RB_UNIT_BOUND))) continue;
         if (lane == 0) {
             tk_zstd_tables& tb = tables[threadIdx.x >> 5].zstd;
             tk_zstd_state s;
@@ -652,7 +656,11 @@ __global__ void __launch_bounds__(128) k_unit_decode_serial(const rb_args a) {
         else
             st = zstd_run(a.raw, lane, u.src, u.src + u.src_len, out, u.unc_len, op, tables[threadIdx.x >> 5].zstd,
                           events[threadIdx.x >> 5]);
-        if (!st && op != u.unc_len) st = TK_STATUS_CORRUPT;
+        if (u.kind & RB_UNIT_BOUND) {                       // placed by its upper bound: the records end here
+            if (!st && lane == 0) a.batches[u.batch].rec_end = a.batches[u.batch].rec_start + op;
+        } else if (!st && op != u.unc_len) {
+            st = TK_STATUS_CORRUPT;
+        }
         if (st && lane == 0) a.batches[u.batch].status = st;
         __syncwarp();                                       // the tables are reused by the warp's next unit
     }
@@ -663,7 +671,7 @@ int tk_codec_launch(const rb_args& a, const tk_rb_unit* h_units, cudaStream_t st
     uint32_t lz_unsized = 0, zs_unsized = 0, warp_units = 0, serial_units = 0;
     for (uint32_t i = 0; i < a.n_units; ++i) {
         const uint32_t kind = h_units[i].kind & 0xFFu;
-        const bool sized = h_units[i].kind & RB_UNIT_SIZED;
+        const bool sized = h_units[i].kind & (RB_UNIT_SIZED | RB_UNIT_BOUND);
         if (kind >= RB_UNIT_DEFLATE) { ++serial_units; if (kind == RB_UNIT_ZSTD && !sized) ++zs_unsized; }
         else { ++warp_units; if (!sized) ++lz_unsized; }
     }

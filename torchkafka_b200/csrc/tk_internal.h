@@ -73,7 +73,8 @@ struct tk_slot_dev {
                                // counters used alternately, each scan zeroes the one of the next
     // raw record-batch input (allocated on first tk_slot_submit_recordbatches)
     uint8_t*     raw;          // [slot_bytes + pad]
-    uint8_t*     raw2;         // [slot_bytes + pad] decompressed records of compressed batches (first use)
+    uint8_t*     raw2;         // [raw2_bytes + pad] decompressed records of compressed batches (first use)
+    uint64_t     raw2_bytes;   // slot_bytes, more once zstd units were placed by their upper bounds
     tk_rb_batch* rb_batches;   // [slot_records]
     tk_rb_unit*  rb_units;     // decompression units (first compressed batch)
     tk_rb_summary_t* rb_summary;

@@ -26,6 +26,7 @@
 // (tk_codecs.cu), gzip and zstd batches too (tk_inflate.cuh, tk_zstd.cuh).
 #include "tk_rb.h"
 #include <mutex>
+#include <stdlib.h>
 
 // ---------------------------------------------------------------- CRC-32C tables
 #define TK_CRC_QUAL const
@@ -534,8 +535,44 @@ static int rb_ensure_codecs(tk_ctx* ctx) {
         if (s.d.raw2) continue;
         TK_CUDA(cudaMalloc(&s.d.raw2, ctx->slot_bytes + TK_BYTES_PAD));
         TK_CUDA(cudaMemset(s.d.raw2, 0, ctx->slot_bytes + TK_BYTES_PAD));
+        s.d.raw2_bytes = ctx->slot_bytes;
         TK_CUDA(cudaMalloc(&s.d.rb_units, sizeof(tk_rb_unit) * rb_max_units(ctx)));
     }
+    return 0;
+}
+
+// zstd frames without a content size are placed in the decompressed buffer by their upper bound
+// (128 KiB per compressed block), which saves the size pass -- as long as the bounds of the slot
+// fit a buffer of at most RB_BOUND_FACTOR x slot_bytes (below the 2 GiB the copy descriptors
+// address); the buffer grows to what the largest slot so far needed.  Otherwise (or with
+// TK_ZSTD_SIZE_PASS=1 in the environment, for tests and comparisons) the units go back to the
+// size pass.
+#define RB_BOUND_FACTOR 16ull
+static int rb_place_by_bounds(tk_ctx* ctx, tk_slot& s, tk_rb_unit* units, uint32_t n_units) {
+    uint64_t need = 0;
+    bool any = false;
+    for (uint32_t i = 0; i < n_units; ++i) {
+        if (units[i].kind & (RB_UNIT_SIZED | RB_UNIT_BOUND)) need += units[i].unc_len;
+        else need += 255ull * units[i].src_len;              // LZ4 unit before its size pass: worst case
+        any |= (units[i].kind & RB_UNIT_BOUND) != 0;
+    }
+    if (!any) return 0;
+    const char* force = getenv("TK_ZSTD_SIZE_PASS");
+    const bool size_pass = force && force[0] == '1';
+    if (!size_pass && need <= s.d.raw2_bytes) return 0;
+    const uint64_t limit = min(RB_BOUND_FACTOR * ctx->slot_bytes, 0x7F000000ull);
+    if (!size_pass && need <= limit) {
+        std::lock_guard<std::mutex> lock(g_rb_mutex);
+        const uint64_t bytes = min(limit, need + need / 4);
+        TK_CUDA(cudaFree(s.d.raw2));                          // (waits for the device: nobody reads the old buffer)
+        s.d.raw2 = nullptr;
+        TK_CUDA(cudaMalloc(&s.d.raw2, bytes + TK_BYTES_PAD));
+        TK_CUDA(cudaMemset(s.d.raw2, 0, bytes + TK_BYTES_PAD));
+        s.d.raw2_bytes = bytes;
+        return 0;
+    }
+    for (uint32_t i = 0; i < n_units; ++i)
+        if (units[i].kind & RB_UNIT_BOUND) { units[i].kind &= ~RB_UNIT_BOUND; units[i].unc_len = 0; }
     return 0;
 }
 
@@ -556,7 +593,10 @@ extern "C" int tk_slot_submit_recordbatches(tk_ctx* ctx, int slot, uint64_t n_by
     rc = rb_walk_host(s.h_bytes, blobs, n_blobs, s.h_rb_batches, ctx->slot_records, ctx->slot_records, &n_batches,
                       &n_rec, s.h_rb_units, (uint32_t)rb_max_units(ctx), &n_units, &n_coded);
     if (rc) return rc;
-    if (n_coded) { rc = rb_ensure_codecs(ctx); if (rc) return rc; }
+    if (n_coded) {
+        rc = rb_ensure_codecs(ctx); if (rc) return rc;
+        rc = rb_place_by_bounds(ctx, s, s.h_rb_units, n_units); if (rc) return rc;
+    }
     s.n_records = n_rec;
     s.n_bytes = n_bytes;                     // upper bound of the value bytes (sizes grids only)
     if (n_records) *n_records = n_rec;
@@ -575,7 +615,7 @@ extern "C" int tk_slot_submit_recordbatches(tk_ctx* ctx, int slot, uint64_t n_by
     TK_CUDA(cudaEventRecord(s.ev_raw, st));
     TK_CUDA(cudaStreamWaitEvent(ks, s.ev_raw, 0));
     rb_args a;
-    a.raw = s.d.raw; a.raw2 = s.d.raw2; a.batches = s.d.rb_batches; a.n_batches = n_batches; a.n_records = n_rec;
+    a.raw = s.d.raw; a.raw2 = s.d.raw2; a.raw2_bytes = s.d.raw2_bytes; a.batches = s.d.rb_batches; a.n_batches = n_batches; a.n_records = n_rec;
     a.units = s.d.rb_units; a.n_units = n_units;
     a.summary = s.d.rb_summary; a.temp = s.d.rb_temp; a.bigq = s.d.rb_bigq; a.bytes = s.d.bytes; a.recs = s.d.recs;
     a.slot_records = ctx->slot_records; a.slot_bytes = ctx->slot_bytes;

@@ -117,6 +117,12 @@ class IngestPipeline:
         self._packed = input_mode == "packed"
         self._leftover = []                        # (tp, records) polled but not fitting the last slot
         self._mean_len = 0.0                       # running mean of the value size (poll sizing)
+        # raw input: decompressed bytes per fetched byte.  A slot must hold the records of its fetch
+        # *after* decompression, so fetches of compressed topics ask for less than a slot; until
+        # the first slot came back the codec is unknown and the budget is conservative.
+        self._raw_expansion = 4.0
+        self._raw_seen = False
+        self._raw_bytes_of = {}
         self._field_idx = {}                       # record type -> (value index, offset index)
         self.n_producers = max(1, int(n_producers))
         self._threads = []
@@ -206,8 +212,11 @@ class IngestPipeline:
         idle_since = None
         while True:
             t0 = time.perf_counter()
+            budget = eng.slot_bytes
+            if self._raw_expansion > 1.0:
+                budget = max(int(eng.slot_bytes / (self._raw_expansion * 1.15)), min(eng.slot_bytes, 4096))
             with self.consumer_lock:
-                fetch = self.consumer.poll_raw(eng.slot_bytes, eng.slot_records)
+                fetch = self.consumer.poll_raw(budget, eng.slot_records)
             self.stats["t_poll"] += time.perf_counter() - t0
             if fetch is not None and len(fetch.blobs):
                 break
@@ -249,7 +258,21 @@ class IngestPipeline:
                                      [(int(starts[i]), int(lens[i]), int(parts[i]), int(fetch_offsets[i]),
                                        int(fetch.blobs[i][3])) for i in range(k)])
         self.stats["t_pack"] += time.perf_counter() - t0
+        self._raw_bytes_of[slot] = int(starts[k])
         return n, int(starts[k])
+
+    def _note_raw_expansion(self, slot: int, n_records: int):
+        """Feedback for the fetch budget (the split of this slot is done: no waiting here)."""
+        raw = self._raw_bytes_of.get(slot, 0)
+        if not raw:
+            return
+        _, value_bytes, _ = self.engine.recordbatch_result(slot)
+        decompressed = value_bytes + 12 * n_records          # values + record framing, roughly
+        obs = decompressed / raw if decompressed > raw * 1.02 else 1.0
+        if not self._raw_seen:
+            self._raw_expansion, self._raw_seen = obs, True
+        else:
+            self._raw_expansion = max(obs, 0.9 * self._raw_expansion + 0.1 * obs)
 
     def _indices(self, rec):
         """(value index, offset index) for tuple-like records, (-1, -1) for attribute access."""
@@ -517,6 +540,8 @@ class IngestPipeline:
             t0 = time.perf_counter()
             res = eng.result(item.slot)
             self.stats["t_wait_result"] += time.perf_counter() - t0
+            if self.input_mode == "raw":
+                self._note_raw_expansion(item.slot, res.n_records)
             release(item.slot)         # pinned memory is reusable: H2D and kernels are done
             eng.publish(item.out)      # caller's stream waits for this slot only
             self.stats["records"] += res.n_records

@@ -214,3 +214,60 @@ def test_struct_schema_layout():
     import pytest
     with pytest.raises(ValueError):
         StructBytes(tuple(("f%d" % i, torch.uint8, ()) for i in range(9)))
+
+
+def test_workers_commit_what_was_delivered_not_their_read_ahead(tmp_path):
+    """with the reference a worker commits its consumer's position, which is
+    ahead of the delivered batches by the DataLoader's prefetch, and signals go round-robin even
+    after a worker's stream ended.  Here every commit a worker makes is the position at the end of
+    one of *its* delivered batches -- the table single-process iteration over its partitions
+    commits -- and never beyond what the main process received from it."""
+    import json as _json
+    from oracle import reference_path as ref
+    base = build_log(CASES["cfg5_raw64"])
+    B = 8
+
+    def process(record):
+        return torch.frombuffer(bytearray(record.value), dtype=torch.uint8)
+
+    class Logged(sk.KafkaConsumer):
+        def commit(self, offsets=None):
+            super().commit(offsets)
+            with open(self.log_path, "a") as f:
+                f.write(_json.dumps({str(k): v for k, v in self.committed_log[-1].items()}) + "\n")
+
+    def sub_log(worker, n_workers):
+        # uneven split: worker 0 owns one partition in four, so its stream ends long before worker 1's
+        return base.select_partitions(lambda p: (p % 4 == 0) == (worker == 0))
+
+    class DS(KafkaDataset):
+        @classmethod
+        def new_consumer(cls, *a, **k):
+            from torch.utils.data import get_worker_info
+            info = get_worker_info()
+            k.pop("enable_auto_commit", None)
+            c = Logged(*a, log=sub_log(info.id, info.num_workers), **k)
+            c.log_path = str(tmp_path / f"worker{info.id}.jsonl")
+            return c
+
+        def _process(self, record):
+            return process(record)
+
+    loader = DataLoader(DS.placeholder(), batch_size=B, num_workers=2, prefetch_factor=2,
+                        worker_init_fn=DS.init_worker("topic", group_id="g"))
+    rows = sum(b.shape[0] for b in auto_commit(loader))
+    assert rows == len(base)
+    total = 0
+    for w in range(2):
+        want = [{str(k): v for k, v in committed.items()}
+                for _, committed in ref.run(sk.KafkaConsumer("topic", log=sub_log(w, 2)), process, B)]
+        path = tmp_path / f"worker{w}.jsonl"
+        got = [_json.loads(line) for line in path.read_text().splitlines()] if path.exists() else []
+        assert got, f"worker {w} never committed"
+        k = -1
+        for table in got:                                  # each one a batch boundary, in order
+            k = want.index(table, k + 1)
+        # the first commit of a worker: the reference is already two prefetched batches ahead
+        assert got[0] in want[:2]
+        total += len(got)
+    assert total >= 4

@@ -8,8 +8,11 @@ facts in SURVEY.md §4.1-6/9):
 * ``num_workers == 0``            -> yield the batch, then ``dataset.commit()``
   (so commit *k* runs when batch *k+1* is requested; breaking out of the loop
   leaves the last batch uncommitted: at-least-once)
-* ``num_workers > 0``             -> workers are signalled round-robin after
-  each batch (``commit_worker``)
+* ``num_workers > 0``             -> the worker that produced a batch is signalled after it
+  (``commit_worker``).  Two fixes over the reference: the worker is
+  the one the DataLoader says the batch came from (the reference assumes round-robin, which
+  breaks once a worker's stream ended), and it commits the offsets of the batches the main
+  process has received, not its read-ahead position (``commit_delivered_only``)
 
 New, for datasets that declare a ``payload_schema``: the DataLoader's per-sample
 ``next()`` loop (``torch/utils/data/_utils/fetch.py:27-45``) is bypassed; the
@@ -20,7 +23,9 @@ commits in single-process mode.
 """
 from __future__ import annotations
 
+import ctypes
 import itertools
+import multiprocessing
 
 from torch.utils.data import DataLoader
 
@@ -57,11 +62,31 @@ def auto_commit(dataloader: DataLoader):
             yield batch
             dataset.commit()
         return
-    # Multi-process: the iterator owns the worker processes; tasks are handed
-    # out round-robin, so batch i came from worker i % num_workers (holds while
-    # all workers are alive and in_order=True).
+    # Multi-process: the iterator owns the worker processes.  Every worker keeps the positions at
+    # the end of each batch it produced; the count of batches received from it lives in shared
+    # memory (set up before the workers are forked), the signal only says "look at it".
+    delivered = None
+    if dataset.commit_delivered_only:
+        delivered = multiprocessing.Array(ctypes.c_longlong, dataloader.num_workers, lock=False)
+        dataset._delivered = delivered                              # pylint: disable=protected-access
+        dataset._delivered_batch_size = dataloader.batch_size or 1  # pylint: disable=protected-access
     batches = iter(dataloader)
-    owners = itertools.cycle(batches._workers)  # pylint: disable=protected-access
-    for worker, batch in zip(owners, batches):
+    workers = batches._workers  # pylint: disable=protected-access
+    # which worker a batch came from: the iterator passes it to _process_data (torch >= 1.8);
+    # without that hook fall back to the reference's round-robin assumption
+    source = {}
+    inner = getattr(batches, "_process_data", None)
+    if inner is not None:
+        def spy(data, *args, **kwargs):
+            source["worker"] = args[0] if args else kwargs.get("worker_idx")
+            return inner(data, *args, **kwargs)
+        batches._process_data = spy  # pylint: disable=protected-access
+    fallback = itertools.cycle(range(len(workers)))
+    for batch in batches:
+        w = source.pop("worker", None)
+        if w is None:
+            w = next(fallback)
         yield batch
-        dataset.commit_worker(worker)
+        if delivered is not None:
+            delivered[w] += 1
+        dataset.commit_worker(workers[w])

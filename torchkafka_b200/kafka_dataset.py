@@ -27,6 +27,7 @@ Two things differ from the reference on purpose, both on the schema path only:
 """
 from __future__ import annotations
 
+import collections
 import contextlib
 import logging
 import os
@@ -104,10 +105,19 @@ class KafkaDataset(IterableDataset):
     #: ``poll()``), "records", "packed", or "raw" (``poll_raw()``: RecordBatch v2 blobs of the
     #: fetch response, CRC-checked and split on the device)
     device_input = "auto"
+    #: multi-worker CPU path: a worker commits the offsets of the batches the main process has
+    #: *received* from it (explicit offsets, same values as single-process iteration), not its
+    #: consumer's position, which runs ahead by the DataLoader's prefetched batches and would lose
+    #: them on a crash.  False = the reference's behaviour.
+    commit_delivered_only = True
 
     def __init__(self, *args, **kwargs):
         self._worker_id = None          # set by init_worker inside a DataLoader worker
         self._commit_required = False   # raised by the signal handler, cleared after each commit
+        self._delivered = None          # shared per-worker count of delivered batches (auto_commit)
+        self._delivered_batch_size = None
+        self._snapshots = None          # worker: positions at the end of every batch it produced
+        self._snapshot_base = 0         # worker: batches whose snapshots were already dropped
         self._explicit_offsets = None   # {TopicPartition: OffsetAndMetadata} of the last device batch
         self._pipeline = None
         self.last_pipeline_stats = {}
@@ -166,7 +176,9 @@ class KafkaDataset(IterableDataset):
         else:
             _logger.debug("Committing offsets.")
         try:
-            if self._explicit_offsets is not None:
+            if in_worker and self._snapshots is not None:
+                self._commit_delivered()
+            elif self._explicit_offsets is not None:
                 # GPU path: exactly the records up to the delivered batch, never the read-ahead;
                 # serialised with the producer thread's poll() (the consumer is not thread safe)
                 pipe = self._pipeline
@@ -192,6 +204,19 @@ class KafkaDataset(IterableDataset):
         finally:
             self._commit_required = False
 
+    def _commit_delivered(self):
+        """Worker: commit the positions at the end of the last batch the main process received
+        from this worker (its count sits in shared memory: signals may coalesce, counts do not)."""
+        from .structs import _offset_struct, _tp_struct
+        target = int(self._delivered[self._worker_id])
+        snap = None
+        while self._snapshots and self._snapshot_base < target:
+            snap = self._snapshots.popleft()
+            self._snapshot_base += 1
+        if snap:
+            tp, off = _tp_struct(), _offset_struct()
+            self._consumer.commit({tp(t, p): off(o) for (t, p), o in snap.items()})
+
     # ------------------------------------------------------------------ iteration
     def __iter__(self):
         if self._consumer is None:
@@ -203,8 +228,23 @@ class KafkaDataset(IterableDataset):
         if in_worker:
             signal.signal(self._COMMIT_SIGNAL, self.commit)
         process = self._process
+        track = in_worker and self.commit_delivered_only and self._delivered is not None
+        if track:
+            # batch boundaries as the DataLoader's fetcher draws them (fetch.py:27-45): a batch
+            # closes on its B-th kept sample; records skipped behind it belong to the next one
+            per_batch = int(self._delivered_batch_size or 1)
+            self._snapshots = collections.deque()
+            self._snapshot_base = 0
+            positions = {}
+            kept = 0
         for record in self._consumer:
             sample = process(record)
+            if track:
+                positions[(getattr(record, "topic", None), record.partition)] = record.offset + 1
+                if sample is not None:
+                    kept += 1
+                    if kept % per_batch == 0:
+                        self._snapshots.append(dict(positions))
             if sample is not None:
                 yield sample
             if in_worker:
@@ -217,6 +257,8 @@ class KafkaDataset(IterableDataset):
             # kills it ("DataLoader worker is killed by signal").  A finished
             # worker instead honours a pending commit request once more and then ignores further
             # signals.
+            if track and kept % per_batch:
+                self._snapshots.append(dict(positions))     # the short tail batch
             self._commit_if_required()
             signal.signal(self._COMMIT_SIGNAL, signal.SIG_IGN)
 

@@ -30,30 +30,7 @@ from .engine import SlotEngine
 from .schema import PayloadError
 
 
-def _offset_struct():
-    """OffsetAndMetadata constructor of kafka-python if present, else of the stub."""
-    mod = sys.modules.get("kafka.structs")
-    cls = getattr(mod, "OffsetAndMetadata", None) if mod is not None else None
-    if cls is None:
-        try:
-            from kafka.structs import OffsetAndMetadata as cls  # type: ignore
-        except Exception:
-            from .testing.stub_kafka import OffsetAndMetadata as cls
-    nfields = len(getattr(cls, "_fields", ("offset", "metadata")))
-    if nfields >= 3:        # kafka-python >= 2.1 added leader_epoch
-        return lambda off: cls(off, "", -1)
-    return lambda off: cls(off, "")
-
-
-def _tp_struct():
-    mod = sys.modules.get("kafka.structs")
-    cls = getattr(mod, "TopicPartition", None) if mod is not None else None
-    if cls is None:
-        try:
-            from kafka.structs import TopicPartition as cls  # type: ignore
-        except Exception:
-            from .testing.stub_kafka import TopicPartition as cls
-    return cls
+from .structs import _offset_struct, _tp_struct  # noqa: E402  (kafka-python's structs, or the stub's)
 
 
 class _Pending:

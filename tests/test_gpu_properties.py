@@ -8,7 +8,7 @@ import torch
 from torch.utils.data import DataLoader
 
 from torchkafka_b200 import KafkaDataset, auto_commit
-from torchkafka_b200.schema import JsonArray, RawBytes
+from torchkafka_b200.schema import JsonArray, JsonObject, RawBytes
 from torchkafka_b200.testing import stub_kafka as sk
 from torchkafka_b200.testing import synthetic as syn
 
@@ -94,14 +94,64 @@ def test_cfg5_raw_records_commit_equals_log_positions():
 
 
 def test_cfg2_record_batches_and_codecs_give_the_same_batches():
-    """The stream served as ConsumerRecord arrays, as RecordBatch v2 bytes, and as LZ4 / snappy
-    compressed batches (~160 MB of JSON): every batch and the final commit must be identical."""
+    """The stream served as ConsumerRecord arrays, as RecordBatch v2 bytes, and as LZ4 / snappy /
+    gzip / zstd compressed batches (~160 MB of JSON): every batch and the final commit must be
+    identical."""
     base = syn.make_log(2, 20000, seed=34, layout="chunked", chunk=300)
     repeat, B = 3, 1024
     sc = JsonArray(torch.float32, max_len=256, min_size=32)
     ref = run(base, sc, B, repeat, 48 << 20, packed=True)
-    for codec, bb in [(0, 65536), (0, 1 << 20), ("lz4i", 16384), (3, 65536), (2, 65536)]:
+    for codec, bb in [(0, 65536), (0, 1 << 20), ("lz4i", 16384), (3, 65536), (2, 65536), (1, 16384), (4, 16384),
+                      ("zstds", 65536)]:
         got = run(base, sc, B, repeat, 56 << 20, packed=True, raw_codec=codec, raw_batch_bytes=bb)
         assert got[1] == ref[1] and got[2] == ref[2], codec
         assert np.array_equal(got[0], ref[0]), codec
         assert got[3] == ref[3] == expected_positions(base, repeat)
+
+
+def test_objects_half_a_million_records_round_trip_the_generated_numbers():
+    """JSON objects at a size the oracle would need minutes for: the numbers the
+    generator wrote (`repr` of float64, i.e. shortest round-trip text) must come back bit for bit in
+    float64, in schema order whatever the member order, and as their float32 rounding in float32;
+    the final commit must equal the log's positions."""
+    import json
+    rng = np.random.default_rng(35)
+    n, F = 50000, 6
+    names = ["f%d" % k for k in range(F)]
+    table = rng.uniform(-1e6, 1e6, (n, F))
+    table[:, 5] = np.round(table[:, 5]) + 0.0                        # whole numbers written as ints (no -0.0)
+    vals = []
+    for i in range(n):
+        order = names if i % 3 else names[::-1]
+        d = {"id": "r%07d" % i}
+        for k in order:
+            j = int(k[1:])
+            d[k] = int(table[i, j]) if j == 5 else float(table[i, j])
+        d["tags"] = [i % 5, {"k": None}]
+        vals.append(json.dumps(d).encode())
+    i = np.arange(n)
+    base = sk.RecordLog(vals, i % 16, i // 16)
+    repeat, B = 10, 512
+
+    def rows(dtype):
+        class DS(KafkaDataset):
+            payload_schema = JsonObject(names, dtype)
+            device_slot_bytes = 24 << 20
+
+            @classmethod
+            def new_consumer(cls, *a, **k):
+                k.pop("enable_auto_commit", None)
+                return sk.KafkaConsumer(*a, log=base, repeat=repeat, **k)
+
+        ds = DS("topic", group_id="prop")
+        out = torch.cat([b for b in auto_commit(DataLoader(ds, batch_size=B))]).cpu().numpy()
+        committed = dict(ds._consumer.committed_log[-1])
+        ds.close()
+        return out, committed
+
+    got64, committed = rows(torch.float64)
+    assert got64.shape == (n * repeat, F)
+    assert np.array_equal(got64.view(np.uint64), np.tile(table, (repeat, 1)).view(np.uint64))
+    assert committed == expected_positions(base, repeat)
+    got32, _ = rows(torch.float32)
+    assert np.array_equal(got32.view(np.uint32), np.tile(table.astype(np.float32), (repeat, 1)).view(np.uint32))

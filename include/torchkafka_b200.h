@@ -194,6 +194,14 @@ int tk_collate_field(tk_ctx* ctx, int slot, uint64_t record_bytes, uint32_t fiel
 int tk_ctx_set_object_fields(tk_ctx* ctx, const uint8_t* names, const uint32_t* name_offsets,
                              uint32_t n_fields, void* stream);
 int tk_json_object_decode(tk_ctx* ctx, int slot, int dtype, const tk_plane_t* values, void* stream);
+/* nested arrays of a fixed shape: the record is arrays nested ndim deep with
+ * extents dims[0..ndim), numbers at the leaves -- `torch.tensor(json.loads(record.value),
+ * dtype=...)` of that shape; row = the leaves in C order (row_bytes = prod(dims) * element
+ * size), batches [B, *dims] by torch.stack.  Another depth or extent: TK_STATUS_RAGGED.
+ * Scan: tk_raw_scan with TK_ANY_RECORD_BYTES. */
+#define TK_MAX_NESTED_DIMS 4
+int tk_json_nested_decode(tk_ctx* ctx, int slot, int dtype, uint32_t ndim, const uint32_t* dims,
+                          const tk_plane_t* values, void* stream);
 
 /* HWC uint8 -> normalised bfloat16 CHW:  bf16(((x / 255) - mean[c]) / std[c]) in
  * float32 with IEEE division, the op order of SURVEY.md §8c */
@@ -207,12 +215,13 @@ int tk_collate_image_u8_bf16_nchw(tk_ctx* ctx, int slot, uint32_t height, uint32
  * the per-record loop KafkaDataset.__iter__ (src/kafka_dataset.py:147-171) + the
  * DataLoader fetch/collate (fetch.py:27-45) + auto_commit's commit (auto_commit.py:55-58). */
 typedef enum { TK_SCHEMA_JSON = 0, TK_SCHEMA_RAW = 1, TK_SCHEMA_IMAGE = 2, TK_SCHEMA_STRUCT = 3,
-               TK_SCHEMA_OBJECT = 4 } tk_schema_t;
+               TK_SCHEMA_OBJECT = 4, TK_SCHEMA_NESTED = 5 } tk_schema_t;
 #define TK_MAX_PLANES 8
 typedef struct tk_job {
     int32_t    schema;        /* tk_schema_t */
     int32_t    dtype;         /* JSON array / object: tk_dtype_t */
-    uint32_t   max_len, min_size, fixed_len;            /* JSON */
+    uint32_t   max_len, min_size, fixed_len;            /* JSON arrays; nested arrays: max_len = number of
+                                                           dimensions, their extents in field_bytes[] */
     uint32_t   height, width, channels;                 /* image */
     uint64_t   record_bytes;                            /* raw / image input bytes per record */
     uint32_t   batch_size;

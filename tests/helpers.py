@@ -11,7 +11,7 @@ if ROOT not in sys.path:
     sys.path.insert(0, ROOT)
 
 from torchkafka_b200 import KafkaDataset, auto_commit  # noqa: E402
-from torchkafka_b200.schema import ImageU8, JsonArray, JsonObject, RawBytes, StructBytes  # noqa: E402
+from torchkafka_b200.schema import ImageU8, JsonArray, JsonNested, JsonObject, RawBytes, StructBytes  # noqa: E402
 from torchkafka_b200.testing import stub_kafka as sk  # noqa: E402
 from oracle import reference_path as ref  # noqa: E402
 
@@ -65,6 +65,8 @@ def oracle_process(schema):
         return ref.process_json(schema.dtype, schema.min_size)
     if isinstance(schema, JsonObject):
         return ref.process_object(schema.fields, schema.dtype)
+    if isinstance(schema, JsonNested):
+        return ref.process_json(schema.dtype, 0)           # torch.tensor(json.loads(v)) as it is
     if isinstance(schema, ImageU8):
         return ref.process_image(schema.height, schema.width, schema.channels, schema.mean, schema.std)
     if isinstance(schema, RawBytes):

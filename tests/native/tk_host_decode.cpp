@@ -182,3 +182,16 @@ extern "C" int tk_host_zstd(const uint8_t* in, uint32_t len, uint8_t* out, uint3
     *out_len = op;
     return 0;
 }
+
+// Nested arrays of a fixed shape (tk_json_object.cuh): leaves in C order, status.
+extern "C" int tk_host_decode_nested(const uint8_t* buf, uint32_t len, int kind, const uint32_t* dims, uint32_t ndim,
+                                     void* row) {
+    HostReader rd{buf, len};
+    switch (kind) {
+        case TK_F32: return tk_json_nested_record<TK_F32>(rd, 0, dims, ndim, (float*)row);
+        case TK_F64: return tk_json_nested_record<TK_F64>(rd, 0, dims, ndim, (double*)row);
+        case TK_I32: return tk_json_nested_record<TK_I32>(rd, 0, dims, ndim, (int32_t*)row);
+        case TK_I64: return tk_json_nested_record<TK_I64>(rd, 0, dims, ndim, (int64_t*)row);
+    }
+    return -1;
+}

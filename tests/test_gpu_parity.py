@@ -430,3 +430,41 @@ def test_object_int_targets_overflow_and_truncation():
         with pytest.raises(PayloadError) as ei:
             run_gpu(log, sc, 1)
         assert ei.value.status == 2
+
+
+# ---------------------------------------------------------------- nested arrays of a fixed shape (§8f-4)
+def nested_log(n, shape, seed, partitions=4, ints=False):
+    rng = np.random.default_rng(seed)
+    vals = []
+    for _ in range(n):
+        a = rng.integers(-10 ** 6, 10 ** 6, shape) if ints else rng.uniform(-1e3, 1e3, shape)
+        vals.append(json.dumps(a.tolist()).encode())
+    i = np.arange(n)
+    return RecordLog(vals, i % partitions, i // partitions)
+
+
+@pytest.mark.parametrize("shape,dtype", [((4, 3), torch.float32), ((2, 3, 4), torch.float64), ((16,), torch.int32),
+                                         ((2, 2, 2, 2), torch.int64), ((64, 24), torch.float32)])
+def test_nested_arrays_match_torch_tensor(shape, dtype):
+    from torchkafka_b200.schema import JsonNested
+    log = nested_log(1500 if np.prod(shape) < 100 else 200, shape, seed=61, ints=not dtype.is_floating_point)
+    gpu = check(log, JsonNested(shape, dtype), 32)
+    assert gpu[0][0].shape == (32,) + shape and gpu[0][0].dtype == dtype
+    check(log, JsonNested(shape, dtype), 5, slot_bytes=40000)           # many slots, carried rows
+
+
+@pytest.mark.parametrize("bad", [b"[[1, 2, 3], [4, 5]]", b"[[1, 2, 3]]", b"[1, 2, 3]", b"[[[1, 2, 3], [4, 5, 6]]]",
+                                 b"[[1, 2, 3], [4, 5, 6]] x", b"[[1, 2, 3], [4, 5, null]]",
+                                 b"[[1, 2, 3], [4, 5, " + b"9" * 400 + b"]]"])
+def test_nested_arrays_of_another_shape_raise(bad):
+    from torchkafka_b200.schema import JsonNested
+    good = [b"[[1, 2, 3], [4, 5, 6]]"] * 5
+    vals = good[:3] + [bad] + good[3:]
+    i = np.arange(len(vals))
+    log = RecordLog(vals, i % 2, i // 2)
+    sc = JsonNested((2, 3), torch.float32)
+    with pytest.raises(Exception):
+        run_oracle(log, sc, 2)          # torch.tensor on the ragged one, or torch.stack on the odd shape
+    with pytest.raises(PayloadError) as ei:
+        run_gpu(log, sc, 2)
+    assert (ei.value.partition, ei.value.offset) == (1, 1)

@@ -206,3 +206,76 @@ def test_many_fields_and_schema_order(lib):
             rng.shuffle(order)
         payload = json.dumps({k: rng.uniform(-10, 10) for k in order}).encode()
         check(lib, payload, fields, kinds=(0, 1))
+
+
+# ---------------------------------------------------------------- nested arrays of a fixed shape
+def decode_nested(lib, payload: bytes, shape, kind: int):
+    dims = np.asarray(shape, np.uint32)
+    row = np.zeros(int(np.prod(shape)), DTYPES[kind][1])
+    st = lib.tk_host_decode_nested(payload, len(payload), kind, dims.ctypes.data_as(ctypes.c_void_p), len(shape),
+                                   row.ctypes.data_as(ctypes.c_void_p))
+    return st, row.reshape(shape)
+
+
+def check_nested(lib, payload, shape, kinds=(0, 1, 2, 3)):
+    for kind in kinds:
+        try:
+            want = torch.tensor(json.loads(payload), dtype=DTYPES[kind][0])
+            if tuple(want.shape) != tuple(shape):
+                want = None                               # a tensor, but not a sample of this schema
+        except Exception:                                 # noqa: BLE001
+            want = None
+        st, got = decode_nested(lib, payload, shape, kind)
+        if want is None:
+            assert st != 0, (payload, shape, kind)
+        else:
+            assert st == 0, (payload, shape, kind, st)
+            bits = DTYPES[kind][2]
+            assert np.array_equal(got.view(bits), want.numpy().view(bits)), (payload, kind)
+
+
+def test_nested_arrays_known_records(lib):
+    for payload, shape, status in [
+        (b"[[1, 2, 3], [4, 5, 6]]", (2, 3), 0),
+        (b"\xef\xbb\xbf [ [1.5,-2e3 ,true] ,\r\n[NaN, -0, -0.0]\t] ", (2, 3), None),
+        (b"[[[1], [2]], [[3], [4]], [[5], [6]]]", (3, 2, 1), 0),
+        (b"[1, 2, 3, 4]", (4,), 0),
+        (b"[[[[7]]]]", (1, 1, 1, 1), 0),
+        (b"[[1, 2, 3], [4, 5]]", (2, 3), 6),              # ragged: torch.tensor raises
+        (b"[[1, 2, 3], [4, 5, 6, 7]]", (2, 3), 6),
+        (b"[[1, 2, 3]]", (2, 3), 6),                      # another shape: torch.stack would raise
+        (b"[[1, 2, 3], [4, 5, 6], [7, 8, 9]]", (2, 3), 6),
+        (b"[1, 2, 3]", (1, 3), 6),                        # not deep enough
+        (b"[[[1, 2, 3]]]", (1, 3), 6),                    # too deep
+        (b"[[1, 2, 3], [4, 5, 6]] x", (2, 3), 1),
+        (b"[[1, 2, 3], [4, 5, 6]", (2, 3), 1),
+        (b"[[1, 2, 3] [4, 5, 6]]", (2, 3), 1),
+        (b"[[1, 2, 3], [4, 5, 6],]", (2, 3), 6),
+        (b"[[1, 2, null], [4, 5, 6]]", (2, 3), 4),
+        (b'[[1, 2, "3"], [4, 5, 6]]', (2, 3), 6),
+        (b"[[1, 2, 1e999], [4, 5, 6]]", (2, 3), None),
+        (b"", (2, 3), 1),
+        (b"{}", (2, 3), 6),
+    ]:
+        check_nested(lib, payload, shape)
+        if status is not None:
+            assert decode_nested(lib, payload, shape, 0)[0] == status, payload
+
+
+def test_nested_arrays_random_records(lib):
+    rng = random.Random(43)
+    for it in range(3000):
+        shape = tuple(rng.randint(1, 4) for _ in range(rng.randint(1, 4)))
+        true_shape = shape if rng.random() < 0.8 else tuple(rng.randint(1, 4) for _ in range(rng.randint(1, 4)))
+
+        def build(dims):
+            if not dims:
+                tok = gen_number(rng)
+                return tok if not tok.startswith(("[", "{")) or rng.random() < 0.02 else "7"
+            sep = rng.choice([",", ", ", " ,\n"])
+            return "[" + rng.choice(["", " "]) + sep.join(build(dims[1:]) for _ in range(dims[0])) + "]"
+        payload = (rng.choice(["", " ", "﻿"]) + build(true_shape) + rng.choice(["", "\n"])).encode()
+        if rng.random() < 0.15:
+            cut = rng.randrange(len(payload) + 1)
+            payload = payload[:cut] + rng.choice([b"", b",", b"]", b"[", b"x", b"1"]) + payload[cut + rng.randint(0, 1):]
+        check_nested(lib, payload, shape, kinds=(it % 4,))

@@ -7,11 +7,11 @@ error there (no CPU fallback).
 """
 from .kafka_dataset import KafkaDataset
 from .auto_commit import auto_commit
-from .schema import (ImageU8, JsonArray, JsonObject, PaddedBatch, PayloadError, RawBytes, StructBytes, TokenBatch,
+from .schema import (ImageU8, JsonArray, JsonNested, JsonObject, PaddedBatch, PayloadError, RawBytes, StructBytes, TokenBatch,
                      TokenList)
 
 __all__ = [
-    "KafkaDataset", "auto_commit", "JsonArray", "JsonObject", "TokenList", "RawBytes", "StructBytes", "ImageU8",
+    "KafkaDataset", "auto_commit", "JsonArray", "JsonObject", "JsonNested", "TokenList", "RawBytes", "StructBytes", "ImageU8",
     "PaddedBatch", "TokenBatch", "PayloadError",
 ]
 __version__ = "0.1.0"

@@ -65,7 +65,7 @@ STATUS_NAMES = {
     3: "more elements than the schema's max_len",
     4: "valid JSON outside the numeric-array schema (true/false/null, strings, nesting)",
     5: "raw record has the wrong byte count",
-    6: "record length differs from the schema's fixed_len (torch.stack would raise)",
+    6: "record length or shape differs from the schema's (torch.tensor / torch.stack would raise)",
     7: "record batch failed its CRC-32C or its record framing (CorruptRecordException in kafka-python)",
     8: "JSON object without one of the schema's fields (KeyError in the reference)",
 }
@@ -101,6 +101,7 @@ _SIGNATURES = {
     "tk_collate_field": (C.c_int, [C.c_void_p, C.c_int, C.c_uint64, C.c_uint32, C.c_uint32, _p(TkPlane), C.c_void_p]),
     "tk_ctx_set_object_fields": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint32, C.c_void_p]),
     "tk_json_object_decode": (C.c_int, [C.c_void_p, C.c_int, C.c_int, _p(TkPlane), C.c_void_p]),
+    "tk_json_nested_decode": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_uint32, C.c_void_p, _p(TkPlane), C.c_void_p]),
     "tk_image_set_norm": (C.c_int, [C.c_void_p, C.c_int, _p(C.c_float), _p(C.c_float), C.c_void_p]),
     "tk_collate_image_u8_bf16_nchw": (C.c_int, [C.c_void_p, C.c_int, C.c_uint32, C.c_uint32, C.c_uint32,
                                                 _p(TkPlane), C.c_void_p]),

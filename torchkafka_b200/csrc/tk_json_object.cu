@@ -1,10 +1,14 @@
-// tk_json_object.cu -- K1 + K3 for JSON objects with named numeric fields.
+// tk_json_object.cu -- K1 + K3 for JSON objects with named numeric fields and for nested arrays of
+// a fixed shape.
 //
 // Replaces, per record, a user hook of the shape of README.md:72-79 with a dict payload
 //     d = json.loads(record.value)
 //     return torch.tensor([d[k] for k in fields], dtype=...)
 // and, per batch, default_collate -> torch.stack (collate.py:275): row k of the batch holds the
 // named members of kept record k in schema order.  Grammar and conversions: tk_json_object.cuh.
+//
+// Nested arrays: `torch.tensor(json.loads(record.value), dtype=...)` of a declared shape
+// (dims[0..ndim)), batches [B, *shape]; same kernel, other record grammar (tk_json_nested_record).
 //
 //   (scan: tk_raw_scan with TK_ANY_RECORD_BYTES -- every record is kept; compaction and commit
 //    offsets: tk_plan.cu)
@@ -43,8 +47,16 @@ struct obj_args {
     tk_result_t*    res;
     const uint8_t*  table;
     uint32_t        n_fields, name_bytes;
+    uint32_t        ndim, dims[TK_NESTED_MAX_DIMS];   // ndim > 0: nested arrays instead of an object
     tk_plane_t      values;
 };
+
+template <int KIND, class R>
+__device__ __forceinline__ int obj_parse_record(const obj_args& a, const R& rd, uint32_t pos, const tk_obj_fields& ft,
+                                                typename tk_elem<KIND>::type* row) {
+    if (a.ndim) return tk_json_nested_record<KIND>(rd, pos, a.dims, a.ndim, row);
+    return tk_json_object_record<KIND>(rd, pos, ft, row);
+}
 
 template <int KIND>
 __global__ void __launch_bounds__(OBJ_THREADS) k_json_object(const obj_args a) {
@@ -53,7 +65,7 @@ __global__ void __launch_bounds__(OBJ_THREADS) k_json_object(const obj_args a) {
     __shared__ uint32_t s_off[TK_OBJ_MAX_FIELDS + 1];
     __shared__ uint8_t s_names[TK_MAX_OBJECT_NAME_BYTES];
     // the field table was written by tk_ctx_set_object_fields (synchronous): not data of the chain
-    for (uint32_t k = threadIdx.x; k <= a.n_fields; k += OBJ_THREADS) s_off[k] = reinterpret_cast<const uint32_t*>(a.table)[k];
+    for (uint32_t k = threadIdx.x; a.n_fields && k <= a.n_fields; k += OBJ_THREADS) s_off[k] = reinterpret_cast<const uint32_t*>(a.table)[k];
     for (uint32_t k = threadIdx.x; k < a.name_bytes; k += OBJ_THREADS) s_names[k] = a.table[OBJ_TABLE_OFFSETS + k];
     __syncthreads();
     tk_pdl_wait();
@@ -87,7 +99,7 @@ __global__ void __launch_bounds__(OBJ_THREADS) k_json_object(const obj_args a) {
                 if (lane == 0 && kidx >= 0) {
                     const ObjGlobalReader rd = {a.bytes, my_end};
                     T* row = reinterpret_cast<T*>((uint8_t*)a.values.base + ((uint64_t)B + (uint32_t)kidx) * a.values.row_bytes);
-                    st = tk_json_object_record<KIND>(rd, my_start, ft, row);
+                    st = obj_parse_record<KIND>(a, rd, my_start, ft, row);
                 }
                 mine = lane == 0;
                 g += 1;
@@ -100,7 +112,7 @@ __global__ void __launch_bounds__(OBJ_THREADS) k_json_object(const obj_args a) {
                 if (mine && kidx >= 0) {
                     const ObjSharedReader rd = {w, base, my_end};
                     T* row = reinterpret_cast<T*>((uint8_t*)a.values.base + ((uint64_t)B + (uint32_t)kidx) * a.values.row_bytes);
-                    st = tk_json_object_record<KIND>(rd, my_start, ft, row);
+                    st = obj_parse_record<KIND>(a, rd, my_start, ft, row);
                 }
                 __syncwarp();                               // the window is reused by the next run
                 g += k;
@@ -149,22 +161,23 @@ extern "C" int tk_ctx_set_object_fields(tk_ctx* ctx, const uint8_t* names, const
     return 0;
 }
 
-extern "C" int tk_json_object_decode(tk_ctx* ctx, int slot, int dtype, const tk_plane_t* values, void* stream) {
-    TK_ENTER(ctx, slot);
+static int obj_launch(tk_ctx* ctx, int slot, int dtype, const tk_plane_t* values, uint32_t row_elems, uint32_t ndim,
+                      const uint32_t* dims, void* stream) {
     tk_slot& s = ctx->slots[slot];
     TK_REQUIRE(values && values->base, "values plane is required");
     TK_REQUIRE(dtype >= TK_DTYPE_F32 && dtype <= TK_DTYPE_I64, "unknown dtype %d", dtype);
-    TK_REQUIRE(ctx->obj_fields, "tk_ctx_set_object_fields must be called first");
     const uint32_t esize = (dtype == TK_DTYPE_F32 || dtype == TK_DTYPE_I32) ? 4u : 8u;
-    TK_REQUIRE(values->row_bytes == (uint64_t)ctx->obj_fields * esize && ((uintptr_t)values->base & (esize - 1)) == 0,
-               "values rows must hold %u elements of %u bytes", ctx->obj_fields, esize);
+    TK_REQUIRE(values->row_bytes == (uint64_t)row_elems * esize && ((uintptr_t)values->base & (esize - 1)) == 0,
+               "values rows must hold %u elements of %u bytes", row_elems, esize);
     const uint32_t n = s.n_records;
     if (!n) return 0;
     obj_args a;
     a.bytes = s.d.bytes; a.recs = s.d.recs; a.n = n;
     a.rec_kidx = s.d.rec_kidx; a.rec_status = s.d.rec_status; a.res = s.d.result;
-    a.table = ctx->d_obj_table; a.n_fields = ctx->obj_fields;
-    a.name_bytes = ctx->obj_name_bytes;
+    a.table = ctx->d_obj_table; a.n_fields = ndim ? 0u : ctx->obj_fields;
+    a.name_bytes = ndim ? 0u : ctx->obj_name_bytes;
+    a.ndim = ndim;
+    for (uint32_t k = 0; k < TK_NESTED_MAX_DIMS; ++k) a.dims[k] = k < ndim ? dims[k] : 1u;
     a.values = *values;
     const uint32_t warps = (n + 31) / 32;
     const uint32_t blocks = min((warps + OBJ_WARPS - 1) / OBJ_WARPS, 148u * 8u);
@@ -176,4 +189,23 @@ extern "C" int tk_json_object_decode(tk_ctx* ctx, int slot, int dtype, const tk_
         default:           TK_LAUNCH_PDL(k_json_object<TK_I64>, blocks, OBJ_THREADS, st, a); break;
     }
     return 0;
+}
+
+extern "C" int tk_json_object_decode(tk_ctx* ctx, int slot, int dtype, const tk_plane_t* values, void* stream) {
+    TK_ENTER(ctx, slot);
+    TK_REQUIRE(ctx->obj_fields, "tk_ctx_set_object_fields must be called first");
+    return obj_launch(ctx, slot, dtype, values, ctx->obj_fields, 0, nullptr, stream);
+}
+
+extern "C" int tk_json_nested_decode(tk_ctx* ctx, int slot, int dtype, uint32_t ndim, const uint32_t* dims,
+                                     const tk_plane_t* values, void* stream) {
+    TK_ENTER(ctx, slot);
+    TK_REQUIRE(ndim >= 1 && ndim <= TK_NESTED_MAX_DIMS && dims, "1..%d dimensions", TK_NESTED_MAX_DIMS);
+    uint64_t elems = 1;
+    for (uint32_t k = 0; k < ndim; ++k) {
+        TK_REQUIRE(dims[k] >= 1, "dimension %u is empty", k);
+        elems *= dims[k];
+        TK_REQUIRE(elems <= (1u << 24), "more than 2^24 elements per record");
+    }
+    return obj_launch(ctx, slot, dtype, values, (uint32_t)elems, ndim, dims, stream);
 }

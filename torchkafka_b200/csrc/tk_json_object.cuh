@@ -256,3 +256,63 @@ TK_HD int tk_json_object_record(const R& rd, uint32_t pos, const tk_obj_fields& 
     if (bad_range) return TK_ERR_OVERFLOW;
     return TK_OK;
 }
+
+// ---------------------------------------------------------------- nested arrays of fixed shape
+// The record at pos must be arrays nested `ndim` deep with extents dims[0..ndim), numbers (or
+// true / false) at the leaves: what `torch.tensor(json.loads(v), dtype=...)` turns into a tensor
+// of that shape.  row[] receives the leaves in C order.  Another nesting depth
+// or another extent anywhere is TK_ERR_RAGGED (torch.tensor raises on ragged lists, torch.stack
+// on samples of different shapes).
+#define TK_NESTED_MAX_DIMS 4
+template <int KIND, class R>
+TK_HD int tk_json_nested_record(const R& rd, uint32_t pos, const uint32_t* dims, uint32_t ndim,
+                                typename tk_elem<KIND>::type* row) {
+    typedef typename tk_elem<KIND>::type T;
+    if (rd(pos) == 0xEF && rd(pos + 1) == 0xBB && rd(pos + 2) == 0xBF) pos += 3;   // utf-8-sig
+    uint32_t idx[TK_NESTED_MAX_DIMS];
+    uint32_t d = 0, n_out = 0;
+    int bad_range = 0;
+    for (;;) {
+        pos = tk_skip_ws(rd, pos);
+        int c = rd(pos);
+        if (d < ndim) {                                     // an array opens here
+            if (c != '[') return (tk_is_numclass(c) || c == '{' || c == '"') ? TK_ERR_RAGGED : TK_ERR_SYNTAX;
+            ++pos;
+            idx[d++] = 0;
+            continue;
+        }
+        if (c == '[' || c == '{' || c == '"') return TK_ERR_RAGGED;      // deeper than declared / not a number
+        const tk_token t = tk_scan_number(rd, pos);
+        if (t.err) return t.err;
+        int st;
+        if (KIND == TK_F32 || KIND == TK_F64) {
+            double v = 0.0;
+            st = tk_token_to_f64(rd, t, &v);
+            row[n_out] = (T)v;
+        } else {
+            int64_t v = 0;
+            st = tk_token_to_i64(rd, t, KIND == TK_I32 ? 32 : 64, &v);
+            row[n_out] = (T)v;
+        }
+        ++n_out;
+        bad_range |= st;
+        pos = t.end;
+        // a value ended: next element of the enclosing array, or close the arrays that are full
+        for (;;) {
+            if (d == 0) {
+                if (rd(tk_skip_ws(rd, pos)) != -1) return TK_ERR_SYNTAX;      // "Extra data"
+                return bad_range ? TK_ERR_OVERFLOW : TK_OK;
+            }
+            pos = tk_skip_ws(rd, pos);
+            c = rd(pos);
+            if (++idx[d - 1] < dims[d - 1]) {
+                if (c != ',') return c == ']' ? TK_ERR_RAGGED : TK_ERR_SYNTAX;     // too few elements
+                ++pos;
+                break;
+            }
+            if (c != ']') return c == ',' ? TK_ERR_RAGGED : TK_ERR_SYNTAX;         // too many
+            ++pos;
+            --d;
+        }
+    }
+}

@@ -16,7 +16,7 @@ extern "C" int tk_process_slot(tk_ctx* ctx, int slot, const tk_job_t* job, void*
         if (rc) return rc;
     }
     if (job->schema == TK_SCHEMA_JSON) rc = tk_json_scan(ctx, slot, job->max_len, job->min_size, stream);
-    else rc = tk_raw_scan(ctx, slot, job->schema == TK_SCHEMA_OBJECT ? TK_ANY_RECORD_BYTES : job->record_bytes, stream);
+    else rc = tk_raw_scan(ctx, slot, (job->schema == TK_SCHEMA_OBJECT || job->schema == TK_SCHEMA_NESTED) ? TK_ANY_RECORD_BYTES : job->record_bytes, stream);
     if (rc) return rc;
     rc = tk_compact(ctx, slot, job->batch_size, stream); if (rc) return rc;
     tk_slot& s = ctx->slots[slot];
@@ -39,6 +39,9 @@ extern "C" int tk_process_slot(tk_ctx* ctx, int slot, const tk_job_t* job, void*
             break;
         case TK_SCHEMA_OBJECT:
             rc = tk_json_object_decode(ctx, slot, job->dtype, &job->cur[0], stream);
+            break;
+        case TK_SCHEMA_NESTED:
+            rc = tk_json_nested_decode(ctx, slot, job->dtype, job->max_len, job->field_bytes, &job->cur[0], stream);
             break;
         case TK_SCHEMA_IMAGE:
             rc = tk_collate_image_u8_bf16_nchw(ctx, slot, job->height, job->width, job->channels,

@@ -25,7 +25,7 @@ import numpy as np
 import torch
 
 from . import _native
-from .schema import ImageU8, JsonArray, JsonObject, PayloadError, RawBytes, StructBytes
+from .schema import ImageU8, JsonArray, JsonNested, JsonObject, PayloadError, RawBytes, StructBytes
 
 # one packed record header: tk_rec_t in include/torchkafka_b200.h
 REC_DTYPE = np.dtype([("start", "<u4"), ("partition", "<i4"), ("offset", "<i8")])
@@ -231,6 +231,10 @@ class SlotEngine:
             values = torch.empty((rows, len(sc.fields)), dtype=sc.dtype, device=dev)
             tensors = [values]
             planes = [(values.data_ptr(), len(sc.fields) * values.element_size())]
+        elif isinstance(sc, JsonNested):
+            values = torch.empty((rows,) + sc.shape, dtype=sc.dtype, device=dev)
+            tensors = [values]
+            planes = [(values.data_ptr(), sc.elements * values.element_size())]
         elif isinstance(sc, ImageU8):
             out = torch.empty((rows, sc.channels, sc.height, sc.width), dtype=torch.bfloat16, device=dev)
             tensors = [out]
@@ -258,6 +262,10 @@ class SlotEngine:
             job.max_len, job.min_size, job.fixed_len = sc.max_len, sc.min_size, sc.fixed_len or 0
         elif isinstance(sc, JsonObject):
             job.schema, job.dtype = 4, sc.kind
+        elif isinstance(sc, JsonNested):
+            job.schema, job.dtype, job.max_len = 5, sc.kind, len(sc.shape)
+            for k, extent in enumerate(sc.shape):
+                job.field_bytes[k] = extent
         elif isinstance(sc, ImageU8):
             job.schema = 2
             job.height, job.width, job.channels = sc.height, sc.width, sc.channels
@@ -303,7 +311,7 @@ class SlotEngine:
                                                     out.planes, st))
                 if is_json:
                     _native.check(lib.tk_json_scan(ctx, slot, sc.max_len, sc.min_size, st))
-                elif isinstance(sc, JsonObject):
+                elif isinstance(sc, (JsonObject, JsonNested)):
                     _native.check(lib.tk_raw_scan(ctx, slot, 0xFFFFFFFFFFFFFFFF, st))     # TK_ANY_RECORD_BYTES
                 else:
                     _native.check(lib.tk_raw_scan(ctx, slot, sc.record_bytes, st))
@@ -321,6 +329,9 @@ class SlotEngine:
                         C.byref(P[1]) if variable else None, C.byref(P[2]) if variable else None, st))
                 elif isinstance(sc, JsonObject):
                     _native.check(lib.tk_json_object_decode(ctx, slot, sc.kind, C.byref(P[0]), st))
+                elif isinstance(sc, JsonNested):
+                    dims = (C.c_uint32 * len(sc.shape))(*sc.shape)
+                    _native.check(lib.tk_json_nested_decode(ctx, slot, sc.kind, len(sc.shape), dims, C.byref(P[0]), st))
                 elif isinstance(sc, ImageU8):
                     _native.check(lib.tk_collate_image_u8_bf16_nchw(ctx, slot, sc.height, sc.width,
                                                                     sc.channels, C.byref(P[0]), st))

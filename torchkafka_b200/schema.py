@@ -20,6 +20,9 @@ schema           equivalent reference ``_process`` + collate
 ``JsonObject``   ``d = json.loads(record.value)``;
                  ``torch.tensor([d[k] for k in fields], dtype=dtype)``; batches are
                  ``torch.stack`` ([B, len(fields)])
+``JsonNested``   ``torch.tensor(json.loads(record.value), dtype=dtype)`` of a declared
+                 shape (arrays nested ``len(shape)`` deep); batches are ``torch.stack``
+                 ([B, *shape])
 ``RawBytes``     ``torch.frombuffer(record.value, dtype=dtype).view(shape)``;
                  batches are ``torch.stack``
 ``StructBytes``  fixed-layout struct: field k is ``torch.frombuffer(value, dtype_k,
@@ -164,6 +167,40 @@ class JsonObject:
         for b in enc:
             offs.append(offs[-1] + len(b))
         return b"".join(enc), offs
+
+
+@dataclasses.dataclass(frozen=True)
+class JsonNested:
+    """Nested JSON arrays of a fixed shape, numbers at the leaves: ``[[1, 2, 3], [4, 5, 6]]`` is a
+    record of ``shape=(2, 3)``.  A record of another depth or extent is an error (``torch.tensor``
+    raises on ragged lists, ``torch.stack`` on samples of different shapes)."""
+
+    shape: Tuple[int, ...] = (1,)
+    dtype: torch.dtype = torch.float32
+
+    def __post_init__(self):
+        if self.dtype not in _JSON_DTYPES:
+            raise TypeError(f"JsonNested does not support dtype {self.dtype}")
+        shape = tuple(int(k) for k in (self.shape if isinstance(self.shape, (tuple, list)) else (self.shape,)))
+        if not 1 <= len(shape) <= 4 or any(k < 1 for k in shape):
+            raise ValueError("1 to 4 dimensions, each of at least 1")
+        n = 1
+        for k in shape:
+            n *= k
+        if n > 1 << 24:
+            raise ValueError("more than 2^24 elements per record")
+        object.__setattr__(self, "shape", shape)
+
+    @property
+    def kind(self) -> int:
+        return _JSON_DTYPES[self.dtype]
+
+    @property
+    def elements(self) -> int:
+        n = 1
+        for k in self.shape:
+            n *= k
+        return n
 
 
 @dataclasses.dataclass(frozen=True)

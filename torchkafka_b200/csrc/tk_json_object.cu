@@ -18,7 +18,8 @@
 //                     records that fits its shared-memory window (they lie back to back in the
 //                     slot's byte buffer), brings the run in with coalesced 16-byte loads, and
 //                     every lane scans its own record out of shared memory and writes its row.
-//                     A record larger than the window is scanned from global memory by one lane.
+//                     Records larger than the window are left to a second loop, one record per
+//                     warp, scanned from global memory by lane 0 (through L1).
 #include "tk_swar.cuh"
 #include "tk_json_object.cuh"
 
@@ -48,6 +49,7 @@ struct obj_args {
     const uint8_t*  table;
     uint32_t        n_fields, name_bytes;
     uint32_t        ndim, dims[TK_NESTED_MAX_DIMS];   // ndim > 0: nested arrays instead of an object
+    uint32_t        big_records;  // the slot may hold records larger than a window (mean size says so)
     tk_plane_t      values;
 };
 
@@ -95,13 +97,8 @@ __global__ void __launch_bounds__(OBJ_THREADS) k_json_object(const obj_args a) {
             int st = TK_OK;
             bool mine = false;
             if (k == 0) {
-                // the first record alone exceeds the window
-                if (lane == 0 && kidx >= 0) {
-                    const ObjGlobalReader rd = {a.bytes, my_end};
-                    T* row = reinterpret_cast<T*>((uint8_t*)a.values.base + ((uint64_t)B + (uint32_t)kidx) * a.values.row_bytes);
-                    st = obj_parse_record<KIND>(a, rd, my_start, ft, row);
-                }
-                mine = lane == 0;
+                // the first record alone exceeds the window: second loop below
+                if (lane == 0 && kidx < 0) mine = true;     // (only its status is left to report)
                 g += 1;
             } else {
                 const uint32_t span_end = __shfl_sync(0xffffffffu, my_end, (int)k - 1);
@@ -124,6 +121,19 @@ __global__ void __launch_bounds__(OBJ_THREADS) k_json_object(const obj_args a) {
                     if (pre) report_error(a.res, i, pre);
                 }
             }
+        }
+    }
+    // records larger than a window: one per warp
+    if (a.big_records) {
+        for (uint32_t i = warp; i < a.n; i += nwarps) {
+            if (lane != 0) continue;
+            const uint32_t start = a.recs[i].start, end = a.recs[i + 1].start;
+            const int32_t kidx = a.rec_kidx[i];
+            if (end - (start & ~15u) <= OBJ_WINDOW || kidx < 0) continue;
+            const ObjGlobalReader rd = {a.bytes, end};
+            T* row = reinterpret_cast<T*>((uint8_t*)a.values.base + ((uint64_t)B + (uint32_t)kidx) * a.values.row_bytes);
+            const int st = obj_parse_record<KIND>(a, rd, start, ft, row);
+            if (st) { a.rec_status[i] = st; report_error(a.res, i, st); }
         }
     }
 }
@@ -179,8 +189,11 @@ static int obj_launch(tk_ctx* ctx, int slot, int dtype, const tk_plane_t* values
     a.ndim = ndim;
     for (uint32_t k = 0; k < TK_NESTED_MAX_DIMS; ++k) a.dims[k] = k < ndim ? dims[k] : 1u;
     a.values = *values;
-    const uint32_t warps = (n + 31) / 32;
-    const uint32_t blocks = min((warps + OBJ_WARPS - 1) / OBJ_WARPS, 148u * 8u);
+    // a warp per 32 records -- or, when records can exceed the window, per window of bytes
+    const uint64_t by_bytes = s.n_bytes / OBJ_WINDOW + 1;
+    a.big_records = s.n_bytes > OBJ_WINDOW ? 1u : 0u;
+    const uint64_t warps = max((uint64_t)(n + 31) / 32, min(by_bytes, (uint64_t)n));
+    const uint32_t blocks = (uint32_t)min((warps + OBJ_WARPS - 1) / OBJ_WARPS, (uint64_t)(148u * 8u));
     cudaStream_t st = (cudaStream_t)stream;
     switch (dtype) {
         case TK_DTYPE_F32: TK_LAUNCH_PDL(k_json_object<TK_F32>, blocks, OBJ_THREADS, st, a); break;

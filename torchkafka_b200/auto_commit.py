@@ -67,7 +67,11 @@ def auto_commit(dataloader: DataLoader):
     # memory (set up before the workers are forked), the signal only says "look at it".
     delivered = None
     if dataset.commit_delivered_only:
-        delivered = multiprocessing.Array(ctypes.c_longlong, dataloader.num_workers, lock=False)
+        delivered = getattr(dataset, "_delivered", None)
+        if delivered is None or len(delivered) != dataloader.num_workers:
+            delivered = multiprocessing.Array(ctypes.c_longlong, dataloader.num_workers, lock=False)
+        for w in range(dataloader.num_workers):                     # persistent workers keep the array they
+            delivered[w] = 0                                        # were forked with: reuse it, restart the counts
         dataset._delivered = delivered                              # pylint: disable=protected-access
         dataset._delivered_batch_size = dataloader.batch_size or 1  # pylint: disable=protected-access
     batches = iter(dataloader)

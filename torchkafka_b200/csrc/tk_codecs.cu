@@ -459,6 +459,8 @@ __device__ __forceinline__ uint32_t snappy_run(cz_window& w, uint32_t lane, uint
     return TK_STATUS_OK;
 }
 
+#define CZ_SMALL_COPY 12u       // DEFLATE matches of at most this many bytes stay with lane 0
+
 // ---------------------------------------------------------------- DEFLATE (gzip)
 // Lane 0 owns the decoder state and runs tk_inflate_next up to the next match; its literals are
 // plain stores of lane 0 (ordered before the warp's reads by the __syncwarp in cz_match).
@@ -468,7 +470,18 @@ __device__ __forceinline__ uint32_t inflate_run(const uint8_t* raw, uint32_t lan
     tk_inflate_init(s, raw, p, end);
     for (;;) {
         uint32_t ev = TK_INF_DONE, mlen = 0, mdist = 0;
-        if (lane == 0) ev = (uint32_t)tk_inflate_next(s, tb, out, cap, op, &mlen, &mdist);
+        if (lane == 0) {
+            // short matches (most of them, in text) are cheaper copied by this lane than handed to
+            // the warp: no broadcast, no barriers; byte by byte also covers overlapping ones
+            for (;;) {
+                ev = (uint32_t)tk_inflate_next(s, tb, out, cap, op, &mlen, &mdist);
+                if (ev != TK_INF_MATCH || mlen > CZ_SMALL_COPY) break;
+                const uint8_t* src = out + op - mdist;
+                for (uint32_t k = 0; k < mlen; ++k) out[op + k] = src[k];
+                op += mlen;
+            }
+        }
+        __syncwarp();
         ev = __shfl_sync(0xffffffffu, ev, 0);
         if (ev == TK_INF_ERROR) return TK_STATUS_CORRUPT;
         op = __shfl_sync(0xffffffffu, op, 0);

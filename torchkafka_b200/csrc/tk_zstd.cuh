@@ -104,6 +104,20 @@ TK_HD uint32_t tk_zs_win_get(tk_zs_win& w, const uint8_t* in, uint32_t lo, uint3
     const uint32_t v = (uint32_t)(w.bits >> (bitpos - w.lo));
     return n >= 32 ? v : v & ((1u << n) - 1u);
 }
+// n <= 56 bits at bitpos, with garbage above them (the caller peels its fields off the bottom)
+TK_HD uint64_t tk_zs_win_get64(tk_zs_win& w, const uint8_t* in, uint32_t lo, uint32_t hi, int32_t bitpos, int n) {
+    if ((uint32_t)(bitpos - w.lo) > (uint32_t)(64 - n)) {
+        const int32_t b = ((bitpos + n + 7) >> 3) - 8;
+        uint64_t v = 0;
+        for (int k = 0; k < 8; ++k) {
+            const int32_t bk = b + k;
+            if (bk >= 0 && (uint32_t)bk < hi - lo) v |= (uint64_t)in[lo + (uint32_t)bk] << (8 * k);
+        }
+        w.bits = v;
+        w.lo = 8 * b;
+    }
+    return w.bits >> (bitpos - w.lo);
+}
 TK_HD uint32_t tk_zs_win_read(tk_zs_win& w, const uint8_t* in, uint32_t lo, uint32_t hi, int32_t* bitpos, int n) {
     *bitpos -= n;
     return tk_zs_win_get(w, in, lo, hi, *bitpos, n);
@@ -551,12 +565,43 @@ TK_HD int tk_zstd_next(tk_zstd_state& s, tk_zstd_tables& tb, uint8_t* out, uint3
             return TK_ZS_COPY;
         }
         const uint32_t lo = s.seq_lo, hi = s.block_end;
-        const uint32_t ofc = tb.of[s.st_of].symbol, mlc = tb.ml[s.st_ml].symbol, llc = tb.ll[s.st_ll].symbol;
+        // the three table entries (symbol, state bits, state base: one 32-bit word each)
+        const uint32_t e_of = reinterpret_cast<const uint32_t*>(tb.of)[s.st_of];
+        const uint32_t e_ml = reinterpret_cast<const uint32_t*>(tb.ml)[s.st_ml];
+        const uint32_t e_ll = reinterpret_cast<const uint32_t*>(tb.ll)[s.st_ll];
+        const uint32_t ofc = e_of & 0xFFu, mlc = e_ml & 0xFFu, llc = e_ll & 0xFFu;
         if (ofc > 31u || mlc > 52u || llc > 35u) return TK_ZS_ERROR;
-        const uint32_t ov = (1u << ofc) + tk_zs_win_read(s.win, in, lo, hi, &s.bitpos, (int)ofc);
-        const uint32_t mlen = tb.ml_base[mlc] + tk_zs_win_read(s.win, in, lo, hi, &s.bitpos, tb.ml_bits[mlc]);
-        const uint32_t llen = tb.ll_base[llc] + tk_zs_win_read(s.win, in, lo, hi, &s.bitpos, tb.ll_bits[llc]);
-        if (s.bitpos < 0) return TK_ZS_ERROR;
+        const uint32_t mlb = tb.ml_bits[mlc], llb = tb.ll_bits[llc];
+        const bool more = s.seq_left > 1u;                           // the states move on unless this is the last one
+        const uint32_t nb_ll = (e_ll >> 8) & 0xFFu, nb_ml = (e_ml >> 8) & 0xFFu, nb_of = (e_of >> 8) & 0xFFu;
+        const uint32_t total = ofc + mlb + llb + (more ? nb_ll + nb_ml + nb_of : 0u);
+        uint32_t ov, mlen, llen;
+        if (total <= 56u) {
+            // all fields of the sequence in one read: offset bits on top, then match length, literal
+            // length, and the bits of the three state updates at the bottom
+            s.bitpos -= (int32_t)total;
+            uint64_t v = total ? tk_zs_win_get64(s.win, in, lo, hi, s.bitpos, (int)total) : 0ull;
+            if (more) {
+                s.st_of = (e_of >> 16) + ((uint32_t)v & ((1u << nb_of) - 1u)); v >>= nb_of;
+                s.st_ml = (e_ml >> 16) + ((uint32_t)v & ((1u << nb_ml) - 1u)); v >>= nb_ml;
+                s.st_ll = (e_ll >> 16) + ((uint32_t)v & ((1u << nb_ll) - 1u)); v >>= nb_ll;
+            }
+            llen = tb.ll_base[llc] + ((uint32_t)v & ((1u << llb) - 1u)); v >>= llb;
+            mlen = tb.ml_base[mlc] + ((uint32_t)v & ((1u << mlb) - 1u)); v >>= mlb;
+            ov = (1u << ofc) + ((uint32_t)v & ((1u << ofc) - 1u));
+            if (s.bitpos < 0) return TK_ZS_ERROR;
+        } else {
+            ov = (1u << ofc) + tk_zs_win_read(s.win, in, lo, hi, &s.bitpos, (int)ofc);
+            mlen = tb.ml_base[mlc] + tk_zs_win_read(s.win, in, lo, hi, &s.bitpos, (int)mlb);
+            llen = tb.ll_base[llc] + tk_zs_win_read(s.win, in, lo, hi, &s.bitpos, (int)llb);
+            if (s.bitpos < 0) return TK_ZS_ERROR;
+            if (more) {
+                s.st_ll = (e_ll >> 16) + tk_zs_win_read(s.win, in, lo, hi, &s.bitpos, (int)nb_ll);
+                s.st_ml = (e_ml >> 16) + tk_zs_win_read(s.win, in, lo, hi, &s.bitpos, (int)nb_ml);
+                s.st_of = (e_of >> 16) + tk_zs_win_read(s.win, in, lo, hi, &s.bitpos, (int)nb_of);
+                if (s.bitpos < 0) return TK_ZS_ERROR;
+            }
+        }
         uint32_t offset;
         if (ov > 3u) {
             offset = ov - 3u;
@@ -572,14 +617,8 @@ TK_HD int tk_zstd_next(tk_zstd_state& s, tk_zstd_tables& tb, uint8_t* out, uint3
                 s.rep0 = offset;
             }
         }
-        if (--s.seq_left) {
-            s.st_ll = tb.ll[s.st_ll].base + tk_zs_win_read(s.win, in, lo, hi, &s.bitpos, tb.ll[s.st_ll].nbits);
-            s.st_ml = tb.ml[s.st_ml].base + tk_zs_win_read(s.win, in, lo, hi, &s.bitpos, tb.ml[s.st_ml].nbits);
-            s.st_of = tb.of[s.st_of].base + tk_zs_win_read(s.win, in, lo, hi, &s.bitpos, tb.of[s.st_of].nbits);
-            if (s.bitpos < 0) return TK_ZS_ERROR;
-        } else if (s.bitpos != 0) {
-            return TK_ZS_ERROR;                                      // the bit stream must end exactly
-        }
+        --s.seq_left;
+        if (!more && s.bitpos != 0) return TK_ZS_ERROR;              // the bit stream must end exactly
         if (llen > s.lit_left || llen > cap - op || mlen > cap - op - llen) return TK_ZS_ERROR;
         if (offset == 0 || offset > op + llen) return TK_ZS_ERROR;   // no dictionary: only this payload's output
         ev->lit_len = llen; ev->lit_kind = s.lit_kind; ev->lit_src = s.lit_src;

@@ -611,6 +611,17 @@ __device__ __forceinline__ uint32_t zstd_run(const uint8_t* raw, uint32_t lane, 
         }
         if (st != TK_ZS_COPY) return st == TK_ZS_UNSUPPORTED ? TK_STATUS_UNSUPPORTED : TK_STATUS_CORRUPT;
         const uint32_t n = ev.lit_len, kind = ev.lit_kind, src = ev.lit_src, mlen = ev.mlen, offset = ev.offset;
+        if (n + mlen <= 32u && offset >= n + mlen && (kind != TK_ZL_OUTPUT || src >= op + n + mlen)) {
+            // small sequence whose sources (literals, match) all lie outside what it writes: one
+            // load and one store per lane, no barrier in between (most sequences of text)
+            uint8_t v = 0;
+            if (lane < n) v = kind == TK_ZL_INPUT ? raw[src + lane] : kind == TK_ZL_RLE ? (uint8_t)src : out[src + lane];
+            else if (lane < n + mlen) v = out[op + lane - offset];
+            if (lane < n + mlen) out[op + lane] = v;
+            op += n + mlen;
+            __syncwarp();
+            continue;
+        }
         if (kind == TK_ZL_INPUT) {
             for (uint32_t k = lane; k < n; k += 32) out[op + k] = raw[src + k];
         } else if (kind == TK_ZL_RLE) {

@@ -143,7 +143,7 @@ extern "C" int tk_host_inflate(const uint8_t* in, uint32_t len, uint8_t* out, ui
     tk_inflate_init(s, in, 0, len);
     uint32_t op = 0, mlen = 0, mdist = 0;
     for (;;) {
-        const int ev = tk_inflate_next(s, tb, out, cap, op, &mlen, &mdist);
+        const int ev = tk_inflate_next(s, tb, out, cap, op, &mlen, &mdist, 12);
         if (ev == TK_INF_ERROR) return 1;
         if (ev == TK_INF_DONE) break;
         for (uint32_t k = 0; k < mlen; ++k) out[op + k] = out[op - mdist + k];

@@ -470,17 +470,9 @@ __device__ __forceinline__ uint32_t inflate_run(const uint8_t* raw, uint32_t lan
     tk_inflate_init(s, raw, p, end);
     for (;;) {
         uint32_t ev = TK_INF_DONE, mlen = 0, mdist = 0;
-        if (lane == 0) {
-            // short matches (most of them, in text) are cheaper copied by this lane than handed to
-            // the warp: no broadcast, no barriers; byte by byte also covers overlapping ones
-            for (;;) {
-                ev = (uint32_t)tk_inflate_next(s, tb, out, cap, op, &mlen, &mdist);
-                if (ev != TK_INF_MATCH || mlen > CZ_SMALL_COPY) break;
-                const uint8_t* src = out + op - mdist;
-                for (uint32_t k = 0; k < mlen; ++k) out[op + k] = src[k];
-                op += mlen;
-            }
-        }
+        // short matches (most of them, in text) are copied by the decoding lane itself, inside
+        // tk_inflate_next: no broadcast, no barriers; byte by byte also covers overlapping ones
+        if (lane == 0) ev = (uint32_t)tk_inflate_next(s, tb, out, cap, op, &mlen, &mdist, CZ_SMALL_COPY);
         __syncwarp();
         ev = __shfl_sync(0xffffffffu, ev, 0);
         if (ev == TK_INF_ERROR) return TK_STATUS_CORRUPT;

@@ -191,11 +191,12 @@ TK_HD bool tk_inf_dynamic_tables(tk_inflate_state& s, tk_inflate_tables& tb) {
     return true;
 }
 
-// Decodes on from the current state: literals go to out[op++] (capacity cap); returns at the next
-// match with *mlen / *mdist set (the caller copies out[op - dist ..] and advances op by mlen; both
-// are checked against op and cap here), at the end of the stream, or on an error.
+// Decodes on from the current state: literals go to out[op++] (capacity cap), matches of at most
+// `self_copy` bytes are copied here, byte by byte; returns at the next longer match with *mlen /
+// *mdist set (the caller copies out[op - dist ..] and advances op by mlen; both are checked
+// against op and cap here), at the end of the stream, or on an error.
 TK_HD int tk_inflate_next(tk_inflate_state& s, tk_inflate_tables& tb, uint8_t* out, uint32_t cap, uint32_t& op,
-                          uint32_t* mlen, uint32_t* mdist) {
+                          uint32_t* mlen, uint32_t* mdist, uint32_t self_copy = 0) {
     for (;;) {
         if (s.mode == TK_INF_HEADER) {
             if (s.last) {
@@ -225,7 +226,7 @@ TK_HD int tk_inflate_next(tk_inflate_state& s, tk_inflate_tables& tb, uint8_t* o
         if (s.mode == TK_INF_END) return TK_INF_DONE;
         for (;;) {
             tk_inf_refill(s);                                   // >= 33 bits: literal/length code 15 + 5 extra
-            if (tk_inf_consumed(s) > s.end) return TK_INF_ERROR;
+            if (s.pos > s.end && tk_inf_consumed(s) > s.end) return TK_INF_ERROR;   // (only once the input is all loaded)
             int sym = tk_huff_decode(s, tb.lit_count, tb.lit_symbol, tb.lit_fast, TK_INF_LIT_FAST);
             if (sym < 0) return TK_INF_ERROR;
             if (sym < 256) {
@@ -252,8 +253,14 @@ TK_HD int tk_inflate_next(tk_inflate_state& s, tk_inflate_tables& tb, uint8_t* o
                 const int e = (dsym >> 1) - 1;                  // 1..13 extra bits
                 dist = ((2u + (uint32_t)(dsym & 1)) << e) + 1u + tk_inf_bits(s, e);
             }
-            if (tk_inf_consumed(s) > s.end) return TK_INF_ERROR;
+            if (s.pos > s.end && tk_inf_consumed(s) > s.end) return TK_INF_ERROR;
             if (dist > op || len > cap - op) return TK_INF_ERROR;
+            if (len <= self_copy) {
+                const uint8_t* src = out + op - dist;
+                for (uint32_t k = 0; k < len; ++k) out[op + k] = src[k];
+                op += len;
+                continue;
+            }
             *mlen = len;
             *mdist = dist;
             return TK_INF_MATCH;

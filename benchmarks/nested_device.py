@@ -1,5 +1,17 @@
-import sys, json, numpy as np, torch
-sys.path.insert(0, '/root/repo'); sys.path.insert(0, '/root/repo/benchmarks'); sys.path.insert(0, '/root/repo/tests')
+#!/usr/bin/env python3
+"""Device-resident timing of the nested-array chain (JsonNested) for small records
+(thread per record out of the shared-memory window) and for records larger than the window (one
+per warp); the numbers quoted in DESIGN.md section 3."""
+import json
+import os
+import sys
+
+import numpy as np
+import torch
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.join(ROOT, "benchmarks"))
 import all_configs as ac
 from torchkafka_b200.schema import JsonNested
 from torchkafka_b200.testing.stub_kafka import RecordLog

@@ -314,6 +314,27 @@ def cpu_process_factory():
     return ref.process_json(torch.float32, MIN_SIZE), ref.pad_collate
 
 
+def cpu_baseline_for(schema, log, batch_size, seconds=6.0):
+    """cpu_baseline leg for any schema (benchmarks/all_configs.py calls this: outside tests/ and
+    smoke(), this file is the only place that executes the oracle): records/s of the oracle on one
+    core, bounded to `seconds`."""
+    import torch
+    from oracle import reference_path as ref
+    from torchkafka_b200.schema import JsonArray
+    from torchkafka_b200.testing import stub_kafka as sk
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    from helpers import oracle_process
+    torch.set_num_threads(1)
+    variable = isinstance(schema, JsonArray) and schema.fixed_len is None
+    collate = ref.pad_collate if variable else ref.default_collate
+    consumer = sk.KafkaConsumer("topic", log=log, repeat=1000)
+    t0 = time.perf_counter()
+    for _ in ref.run(consumer, oracle_process(schema), batch_size, False, collate):
+        if time.perf_counter() - t0 > seconds:
+            break
+    return consumer.consumed / (time.perf_counter() - t0)
+
+
 def run_cpu_single(log, max_records):
     """Oracle, one process, one thread: the reference's own num_workers=0 configuration."""
     import torch

@@ -131,19 +131,9 @@ def e2e(cfg, log, packed, repeat, batches_timed, warm):
 
 
 def cpu_oracle(cfg, log, seconds=6.0):
-    sys.path.insert(0, os.path.join(ROOT, "tests"))
-    from helpers import oracle_process
-    from oracle import reference_path as ref
-    torch.set_num_threads(1)
-    sc = cfg["schema"]
-    variable = isinstance(sc, JsonArray) and sc.fixed_len is None
-    collate = ref.pad_collate if variable else ref.default_collate
-    consumer = sk.KafkaConsumer("topic", log=log, repeat=1000)
-    t0 = time.perf_counter()
-    for _ in ref.run(consumer, oracle_process(sc), cfg["batch"], False, collate):
-        if time.perf_counter() - t0 > seconds:
-            break
-    return consumer.consumed / (time.perf_counter() - t0)
+    """The CPU arm is bench.py's cpu_baseline leg (the one place outside the tests that runs the oracle)."""
+    import bench
+    return bench.cpu_baseline_for(cfg["schema"], log, cfg["batch"], seconds)
 
 
 def main():

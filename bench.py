@@ -5,14 +5,24 @@ Workload ("cfg2"): variable-length JSON float arrays (16..256 elements,
 uniform(-1e3, 1e3), json.dumps default separators), min_size=32 filter, float32
 output, pad + length + mask collate, batch 1024, 64 partitions, commit offsets per
 batch.  One *step* = one batch of 1024 kept records (~1096 consumed records,
-~2.9 MB of payload).  The GPU pipeline works on staging slots of SLOT_BATCHES
-batches per kernel sequence; K steps are timed as ceil(K / SLOT_BATCHES) slot
-passes covering exactly K batches.
+~2.9 MB of payload).  With N ranks (torchrun), rank r owns the partitions p % N == r
+ and ingests its own log of the same volume: weak scaling, no collective on
+the data path.
 
-    value   consumed records/s, slot bytes already resident in HBM (device timed, CUDA events)
-    e2e     the same metric through the public API (auto_commit(DataLoader(dataset))) from
-            host ConsumerRecord objects: poll -> pack into pinned memory -> H2D -> kernels ->
-            result D2H, plus a D2H read of each batch's checksum
+    value   consumed records/s, slot bytes already resident in HBM, CUDA events on the stream
+            the kernels are launched on.  The pipeline's unit of work is a staging slot of
+            SLOT_BATCHES batches, so the K steps are repeated R times (R a multiple of
+            SLOT_BATCHES / gcd(K, SLOT_BATCHES), and large enough for a >= 0.5 s window) and
+            the K * R batches are issued as K * R / SLOT_BATCHES full slot passes; the
+            warm-up runs the same passes (same shapes: the caching allocator is warm).
+    e2e     the same metric through the public API, auto_commit(DataLoader(dataset)), from
+            host ConsumerRecord objects.  The clock starts BEFORE the iteration (and with it
+            the dataset's pipeline: poll, pack into pinned memory, H2D, kernels) is started
+            and stops after the last batch of the stream was delivered, its per-step result
+            (the int32 length vector) copied to the host and everything synchronised, so no
+            read-ahead lies outside the window.  The stream is long enough for a window of
+            seconds (raw / packed arms) or as long as the pre-built record objects allow
+            (poll arm).  A separate warm-up iteration runs first.  link_frac > 1 is an error.
     roofline  dominant kernel (k_json_parse: pad/length/mask rows + thread-per-element parse,
               the one kernel of tk_json_decode) against the measured HBM copy bandwidth
     cpu_baseline  the oracle (reference algorithm: json.loads + torch.tensor + pad collate)
@@ -23,7 +33,9 @@ passes covering exactly K batches.
 machine here) with a multi-worker DataLoader on all usable host cores.
 """
 import argparse
+import gc
 import json
+import math
 import os
 import statistics
 import subprocess
@@ -43,20 +55,34 @@ PARTITIONS = 64
 SEED = 2026
 METRIC = "records/sec"
 WORKLOAD = "cfg2: JSON float arrays len 16-256, min_size=32, f32 pad+mask collate, batch 1024"
+VALUE_MIN_SECONDS = float(os.environ.get("TK_VALUE_SECONDS", "0.5"))
+E2E_MIN_SECONDS = float(os.environ.get("TK_E2E_SECONDS", "2.5"))
+#: ConsumerRecord objects the poll arm may hold (they exist before the clock starts, as they do
+#: for the CPU arm): ~200 bytes each
+POLL_MAX_OBJECTS = int(os.environ.get("TK_POLL_OBJECTS", str(6_000_000)))
 
 
 def log(*a):
     print(*a, file=sys.stderr, flush=True)
 
 
+def shared_config(world):
+    """`config` of the JSON line: the same for the GPU arm and the reference arm."""
+    return {"workload": WORKLOAD, "batch": BATCH, "partitions": PARTITIONS,
+            "sharding": f"rank r of {world} owns the partitions p % {world} == r; per-rank volume fixed (weak)",
+            "l2": "device-resident leg: 4 distinct ~94 MB slots cycled (> 126 MB L2), inputs come from HBM; "
+                  "end-to-end leg: every slot arrives over the link"}
+
+
 # --------------------------------------------------------------------------- workload
-def build_base_log(n_batches: int):
-    """Seeded cfg2 records, cut so that exactly n_batches * BATCH of them pass the filter."""
+def build_base_log(n_batches: int, rank: int = 0, world: int = 1):
+    """Seeded cfg2 records of one rank, cut so that exactly n_batches * BATCH of them pass the
+    filter.  Rank r's records lie in its own partitions (p % world == r)."""
     import numpy as np
     from torchkafka_b200.testing import synthetic as syn
     from torchkafka_b200.testing.stub_kafka import RecordLog
     want = n_batches * BATCH
-    vals = syn.cfg2_values(int(want / 0.93) + 64, seed=SEED)
+    vals = syn.cfg2_values(int(want / 0.93) + 64, seed=SEED + rank)
     kept = 0
     cut = None
     for i, v in enumerate(vals):
@@ -68,10 +94,11 @@ def build_base_log(n_batches: int):
     assert cut is not None
     vals = vals[:cut]
     i = np.arange(cut)
+    owned = np.asarray([p for p in range(PARTITIONS) if p % world == rank], dtype=np.int32)
     # Kafka-like arrival: runs of 500 records per partition
     blk = i // 500
-    part = (blk % PARTITIONS).astype(np.int32)
-    off = (blk // PARTITIONS) * 500 + (i % 500)
+    part = owned[blk % len(owned)]
+    off = (blk // len(owned)) * 500 + (i % 500)
     return RecordLog(vals, part, off)
 
 
@@ -130,138 +157,121 @@ def slot_arrays(log, a, b):
             log.partitions[a:b], log.offsets[a:b])
 
 
-def prefix_for_batches(log, nb):
-    """Number of leading records of `log` that contain exactly nb * BATCH kept records."""
-    import numpy as np
-    lens = np.diff(log.starts)
-    # element count = commas + 1; recompute cheaply from the raw values
-    kept = np.fromiter((v.count(b",") + 1 >= MIN_SIZE for v in log._byte_values), dtype=bool, count=len(log))
-    cum = np.cumsum(kept)
-    idx = int(np.searchsorted(cum, nb * BATCH, side="left"))
-    assert cum[idx] == nb * BATCH
-    return idx + 1
-
-
 def run_device_resident(base_log, steps, warmup, device):
     """`value`: slots already in HBM, timed with CUDA events on the launching stream."""
     import torch
     from torchkafka_b200.engine import SlotEngine
     from torchkafka_b200.schema import JsonArray
     schema = JsonArray(torch.float32, max_len=MAX_LEN, min_size=MIN_SIZE)
-    n_full = prefix_for_batches(base_log, SLOT_BATCHES)
+    n_full = len(base_log)               # the base log holds exactly SLOT_BATCHES batches
     full = slot_arrays(base_log, 0, n_full)
-    slot_bytes = int(full[1][-1]) + 4096
+    n_bytes = int(base_log.starts[n_full])
+    slot_bytes = n_bytes + 4096
     n_slots = 4          # 4 slots of distinct addresses, together > 126 MB L2: every pass reads from HBM
     eng = SlotEngine(schema, BATCH, slot_bytes=slot_bytes, slot_records=n_full, n_slots=n_slots,
                      device=device, n_partitions=PARTITIONS)
     torch.cuda.set_device(device)
-
-    def plan(nsteps):
-        """list of (records, batches) slot passes covering exactly nsteps batches"""
-        out = [(n_full, SLOT_BATCHES)] * (nsteps // SLOT_BATCHES)
-        r = nsteps % SLOT_BATCHES
-        if r:
-            out.append((prefix_for_batches(base_log, r), r))
-        return out
-
     # preload every slot's device twin once (H2D outside the timed region)
     for s in range(n_slots):
         n, nb = eng.fill_packed(s, *full)
         eng.submit(s, n, nb)
     torch.cuda.synchronize()
-    starts = base_log.starts
 
-    def run(passes, dec_ms):
-        """One tk_process_slot call per slot pass.  The library brackets the decode kernels of
-        each slot with two CUDA events on the launching stream (tk_ctx_set_timing); a slot's
-        pair is read right before the slot is reused, n_slots passes later."""
-        prev_slot, prev_out, recs, byts = None, None, 0, 0
+    def run(n_passes, dec_ms=None):
+        """n_passes slot passes, one tk_process_slot call each, exactly as the pipeline issues
+        them.  With dec_ms, the library's event pair around the decode kernel of a slot is read
+        right before the slot is reused (n_slots passes later)."""
+        prev_slot, prev_out = None, None
         outs = []
-        for k, (n, nb) in enumerate(passes):
+        for k in range(n_passes):
             s = k % n_slots
             if dec_ms is not None and k >= n_slots:
                 dec_ms.append(eng.decode_ms(s))
-            eng.assume_resident(s, n, int(starts[n]))
-            out = eng.process(s, n, prev_slot, prev_out, resident=True)
+            eng.assume_resident(s, n_full, n_bytes)
+            out = eng.process(s, n_full, prev_slot, prev_out, resident=True)
             outs.append(out)
             if len(outs) > 2:
                 outs.pop(0)
             prev_slot, prev_out = s, out
-            recs += n
-            byts += int(starts[n])
-        return recs, byts
 
-    # NOTE: a shorter pass reuses the head of a preloaded slot: recs[n].start still closes the CSR
-    # because the full slot's header array is a superset.
-    run(plan(max(warmup, 1)), None)
-    torch.cuda.synchronize()
-    eng.reset()
-    passes = plan(steps)
-
-    def timed(dec_ms):
+    def timed(n_passes, dec_ms=None):
         e0 = torch.cuda.Event(enable_timing=True)
         e1 = torch.cuda.Event(enable_timing=True)
         torch.cuda.synchronize()
         e0.record(eng.stream)            # events on the stream the kernels are launched on
-        out = run(passes, dec_ms)
+        run(n_passes, dec_ms)
         e1.record(eng.stream)
         torch.cuda.synchronize()
-        return e0.elapsed_time(e1), out
+        return e0.elapsed_time(e1)
 
-    # Region 1 (`value`): the K steps exactly as the product issues them -- one tk_process_slot
-    # call per slot, no events inside the kernel chain.
+    # K steps repeated R times = K * R / SLOT_BATCHES full slot passes
+    unit = SLOT_BATCHES // math.gcd(steps, SLOT_BATCHES)
+    # warm-up: at least `warmup` steps and two rounds over the slots, same pass shape as the timed
+    # region (same output sizes: no allocator miss inside the clock)
+    warm_passes = max(-(-max(warmup, 3) // SLOT_BATCHES), 2 * n_slots)
+    run(warm_passes)
+    torch.cuda.synchronize()
+    probe_ms = timed(2 * n_slots) / (2 * n_slots)                 # one slot pass
+    eng.reset()
+    per_rep_ms = probe_ms * steps / SLOT_BATCHES
+    R = unit * max(1, math.ceil(VALUE_MIN_SECONDS * 1e3 / per_rep_ms / unit))
+    n_passes = steps * R // SLOT_BATCHES
+
+    # Region 1 (`value`): no events inside the kernel chain.
     launches0 = eng.launches
-    ms, (recs, byts) = timed(None)
+    ms = timed(n_passes)
     launches = eng.launches - launches0
-    # Region 2 (`roofline`): the same K steps once more with the library's timing events around
-    # the decode kernel of every slot.  The events cut the programmatic-launch chain at both ends
-    # of the kernel, so this region runs a little slower than region 1; the kernel's share of the
+    res = eng.result((n_passes - 1) % n_slots)
+    assert res.n_closed == SLOT_BATCHES and res.n_errors == 0 and res.carry_out == 0, \
+        (res.n_closed, res.n_errors, res.carry_out)
+    # Region 2 (`roofline`): the same passes once more with the library's timing events around the
+    # decode kernel of every slot.  The events cut the programmatic-launch chain at both ends of
+    # the kernel, so this region runs a little slower than region 1; the kernel's share of the
     # step is taken against this region's own time.
     eng.reset()
     eng.set_timing(True)
     dec_ms = []
-    ms_timed, _ = timed(dec_ms)
-    dec_ms += [eng.decode_ms(k % n_slots) for k in range(max(0, len(passes) - n_slots), len(passes))]
-    assert len(dec_ms) == len(passes)
+    ms_timed = timed(n_passes, dec_ms)
+    dec_ms += [eng.decode_ms(k % n_slots) for k in range(max(0, n_passes - n_slots), n_passes)]
+    assert len(dec_ms) == n_passes
     eng.set_timing(False)
-    # sanity: last pass really produced what the plan says
-    res = eng.result((len(passes) - 1) % n_slots)
-    assert res.n_closed == passes[-1][1] and res.n_errors == 0, (res.n_closed, res.n_errors)
-    launches = eng.launches - launches0
     # SURVEY.md §8(d): algorithmic HBM bytes = (v + 16) read per consumed record + row written
     # per kept record (MAX_LEN f32 + int32 length); the bool mask plane is extra, not counted.
-    algo = [int(starts[n]) + 16 * n + nb * BATCH * (MAX_LEN * 4 + 4) for n, nb in passes]
+    algo = n_bytes + 16 * n_full + SLOT_BATCHES * BATCH * (MAX_LEN * 4 + 4)
     info = {
-        "ms": ms, "ms_timed_region": ms_timed, "records": recs, "bytes": byts, "launches": launches,
+        "ms": ms, "ms_timed_region": ms_timed, "records": n_full * n_passes, "bytes": n_bytes * n_passes,
+        "launches": launches, "repeats": R, "passes": n_passes,
         "decode_ms_total": sum(dec_ms), "decode_launches": len(dec_ms),
-        "decode_algo_bytes_total": sum(algo),
+        "decode_algo_bytes_total": algo * n_passes, "algo_bytes_per_launch": algo,
         "slot_bytes": slot_bytes, "slot_records": n_full,
     }
-    h2d_peak = eng.h2d_peak_gbs(256 << 20, 5)
-    info["h2d_peak_gbs"] = h2d_peak
+    info["h2d_peak_gbs"] = eng.h2d_peak_gbs(256 << 20, 5)
     eng.close()
     return info
 
 
 RAW_BATCH_BYTES = int(os.environ.get("RAW_BATCH_BYTES", str(64 << 10)))   # producer batch.size of the raw arm
+E2E_SLOT_BYTES = 48 << 20
+E2E_SLOTS = 3
 
 
-def make_dataset_cls(log, packed, repeat=1):
-    """packed: False = poll() objects, True = poll_packed() arrays, "raw" = poll_raw() record batches."""
+def make_dataset_cls(log, mode, repeat=1):
+    """mode: "poll" = poll() objects, "packed" = poll_packed() arrays, "raw" = poll_raw() record
+    batches, "raw_into" = poll_raw_into() (record batches received straight into the pinned slot)."""
     import torch
     from torchkafka_b200 import KafkaDataset
     from torchkafka_b200.schema import JsonArray
     from torchkafka_b200.testing import stub_kafka as sk
-    consumer_cls = sk.KafkaConsumer if packed else sk.PollOnlyConsumer
-    mode = "raw" if packed == "raw" else "auto"
+    consumer_cls = sk.PollOnlyConsumer if mode == "poll" else sk.KafkaConsumer
+    input_mode = {"poll": "records", "packed": "packed", "raw": "raw", "raw_into": "raw_into"}[mode]
 
     class Cfg2Dataset(KafkaDataset):
         payload_schema = JsonArray(torch.float32, max_len=MAX_LEN, min_size=MIN_SIZE)
-        device_slot_bytes = 48 << 20
-        device_slots = 3
+        device_slot_bytes = E2E_SLOT_BYTES
+        device_slots = E2E_SLOTS
         device_producers = int(os.environ.get("TK_PRODUCERS", "2"))
         max_partitions = PARTITIONS
-        device_input = mode
+        device_input = input_mode
 
         @classmethod
         def new_consumer(cls, *a, **k):
@@ -271,40 +281,64 @@ def make_dataset_cls(log, packed, repeat=1):
     return Cfg2Dataset
 
 
-def run_e2e(log, steps, warmup, device, packed, repeat=1):
-    """`e2e`: public API, host buffers -> batches; wall clock bracketed by synchronize()."""
+def _iterate(cls, device, host_results):
+    """One complete iteration of auto_commit(DataLoader(dataset)) with the per-step D2H.
+    Returns (seconds, batches, stats); the clock covers everything from before the iteration is
+    created to the final synchronize."""
     import torch
     from torch.utils.data import DataLoader
     from torchkafka_b200 import auto_commit
-    torch.cuda.set_device(device)
-    cls = make_dataset_cls(log, packed, repeat)
     cls.device_index = device
     ds = cls("topic", group_id="bench")
     loader = DataLoader(ds, batch_size=BATCH)
-    # Every step's result (the batch's int32 length vector, BATCH * 4 bytes) is read back to the
-    # host inside the timed region: non-blocking D2H into pinned memory, consumed after the final
-    # synchronize -- the way a training loop logs its per-step metric without stalling the GPU.
-    host_results = torch.empty((steps, BATCH), dtype=torch.int32).pin_memory()
-    t0 = t1 = None
+    cap = host_results.shape[0]
+    torch.cuda.synchronize()
     seen = 0
+    t0 = time.perf_counter()
     for batch in auto_commit(loader):
-        if seen == warmup:
-            torch.cuda.synchronize()
-            t0 = time.perf_counter()
-        if seen >= warmup:
-            host_results[seen - warmup].copy_(batch.lengths, non_blocking=True)
+        # every step's result (the batch's int32 length vector) is read back to the host inside
+        # the timed region: non-blocking D2H into pinned memory, consumed after the final
+        # synchronize -- the way a training loop logs its per-step metric without stalling the GPU
+        row = host_results[seen % cap]
+        row[:batch.lengths.shape[0]].copy_(batch.lengths, non_blocking=True)
         seen += 1
-        if seen == warmup + steps:
-            torch.cuda.synchronize()
-            checksum = int(host_results.sum())
-            t1 = time.perf_counter()
-            break
-    assert t1 is not None, f"log too short: {seen} batches for warmup {warmup} + steps {steps}"
-    stats = dict(ds._pipeline.stats) if ds._pipeline is not None else dict(ds.last_pipeline_stats)
-    print("e2e total", round(t1 - t0, 4), "checksum", checksum, file=sys.stderr)
-    print("e2e", packed if packed == "raw" else "packed" if packed else "poll", {k: (round(v, 4) if isinstance(v, float) else v) for k, v in stats.items()}, file=sys.stderr, flush=True)
+    torch.cuda.synchronize()
+    checksum = int(host_results[:min(seen, cap)].sum())
+    t1 = time.perf_counter()
+    stats = dict(ds.last_pipeline_stats)
     ds.close()
-    return {"seconds": t1 - t0, "checksum": checksum, "stats": stats}
+    return t1 - t0, seen, stats, checksum
+
+
+def run_e2e(log, mode, device, min_seconds, rate_guess, max_records=None):
+    """`e2e` of one input protocol.  Warm-up: a complete iteration over the base log (its engine --
+    pinned slots, device twins -- goes back to the pool and serves the timed iteration).  Timed:
+    a complete iteration over `reps` repetitions of the log, sized from `rate_guess` for a window
+    of `min_seconds` and never shorter than 20x the pipeline's read-ahead."""
+    import torch
+    torch.cuda.set_device(device)
+    n = len(log)
+    slot_records = E2E_SLOT_BYTES / (log.nbytes / n)
+    readahead = (E2E_SLOTS + 2) * slot_records                    # every slot of the pipeline
+    want = max(min_seconds * rate_guess, 20 * readahead)
+    if max_records:
+        want = min(want, max_records)
+    reps = max(2, int(math.ceil(want / n)))
+    if mode == "poll":
+        for r in range(reps):            # ConsumerRecord objects exist before the clock starts,
+            log.rep_records(r)           # exactly as they do for the CPU arm
+        gc.collect()
+        gc.freeze()                      # (millions of live tuples: keep them out of later GC passes)
+    host_results = torch.zeros((reps * SLOT_BATCHES + 2, BATCH), dtype=torch.int32).pin_memory()
+    _iterate(make_dataset_cls(log, mode, 1), device, host_results)           # warm-up iteration
+    seconds, batches, stats, checksum = _iterate(make_dataset_cls(log, mode, reps), device, host_results)
+    # the iteration ran to the end of the stream: exactly reps * n records were consumed
+    if stats.get("records") != reps * n:
+        log(f"warning: pipeline counted {stats.get('records')} records, the stream holds {reps * n}")
+    log(f"e2e {mode}: {seconds:.3f} s, {batches} batches, checksum {checksum},",
+        {k: (round(v, 4) if isinstance(v, float) else v) for k, v in stats.items()})
+    return {"seconds": seconds, "batches": batches, "records": reps * n,
+            "bytes": int(stats["bytes"]), "reps": reps, "stats": stats}
 
 
 # --------------------------------------------------------------------------- CPU arms (oracle)
@@ -335,21 +369,23 @@ def cpu_baseline_for(schema, log, batch_size, seconds=6.0):
     return consumer.consumed / (time.perf_counter() - t0)
 
 
-def run_cpu_single(log, max_records):
-    """Oracle, one process, one thread: the reference's own num_workers=0 configuration."""
+def run_cpu_single(log, seconds):
+    """Oracle, one process, one thread: the reference's own num_workers=0 configuration, bounded
+    to about `seconds` of CPU work."""
     import torch
     from oracle import reference_path as ref
     from torchkafka_b200.testing import stub_kafka as sk
     torch.set_num_threads(1)
     process, collate = cpu_process_factory()
-    sub = log if max_records >= len(log) else None
-    consumer = sk.KafkaConsumer("topic", log=log)
-    log.records()
+    reps = 64
+    for r in range(8):
+        log.rep_records(r)
+    consumer = sk.KafkaConsumer("topic", log=log, repeat=reps)
     n_batches = 0
     t0 = time.perf_counter()
     for _batch, _commit in ref.run(consumer, process, BATCH, False, collate):
         n_batches += 1
-        if consumer.consumed >= max_records:
+        if time.perf_counter() - t0 >= seconds:
             break
     dt = time.perf_counter() - t0
     return {"records": consumer.consumed, "seconds": dt, "batches": n_batches}
@@ -376,6 +412,8 @@ def run_cpu_workers(base_log, steps, warmup, num_workers):
         sub = syn.tile_log(sub, reps * (W if W > 1 else 1)) if reps * W > 1 else sub
         sub.records()
         worker_logs.append(sub)
+    gc.collect()
+    gc.freeze()
 
     def factory(worker_id, n):
         return sk.KafkaConsumer("topic", log=worker_logs[worker_id], block_at_end=True)
@@ -422,11 +460,11 @@ def main_reference(args):
     line = {
         "impl": "reference", "metric": METRIC, "value": value, "unit": "records/s",
         "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
-        "ms_per_step": 1e3 * r["seconds"] / args.steps, "higher_is_better": True, "scaling": "weak",
+        "ms_per_step": 1e3 * r["seconds"] / (args.steps * per_step), "higher_is_better": True, "scaling": "weak",
         "vs_baseline": None, "dtype": "f64->f32", "data": "synthetic",
-        "config": {"workload": WORKLOAD, "batch": BATCH, "partitions": PARTITIONS,
-                   "num_workers": workers, "warmup_batches": r["warmup_batches"],
-                   "batches_per_step": per_step},
+        "config": shared_config(max(world, args.gpus, 1)),
+        "setup": {"num_workers": workers, "warmup_batches": r["warmup_batches"], "batches_per_step": per_step,
+                  "timed_region_s": r["seconds"]},
         "cpu_baseline": {"value": value, "unit": "records/s", "cores": workers + 1, "kind": "port",
                          "sample": f"{args.steps * per_step} batches of {BATCH} kept records via DataLoader("
                                    f"num_workers={workers}) + SIGUSR1 commits; oracle/ref_dataset.py"},
@@ -444,13 +482,13 @@ def main_gpu(args):
     if world > 1:
         import torch.distributed as dist
         # One rank per GPU.  The data path has no collective (partition sharding); the only
-        # exchanges here are the barrier and the max-over-ranks of three timings, done on host
+        # exchanges here are the barrier and the max-over-ranks of the timings, done on host
         # tensors (gloo) so that no NCCL banner can leak into the single JSON line on stdout.
         dist.init_process_group("cpu:gloo,cuda:nccl")
     device = local_rank if world > 1 else 0
     torch.cuda.set_device(device)
-    steps, warmup = args.steps, max(args.warmup, 0)
-    base = build_base_log(SLOT_BATCHES)
+    steps, warmup = max(args.steps, 1), max(args.warmup, 0)
+    base = build_base_log(SLOT_BATCHES, rank, world)
 
     def barrier():
         torch.cuda.synchronize()
@@ -466,37 +504,37 @@ def main_gpu(args):
     barrier()
     clocks = clk.summary()
 
-    # ---- e2e: public API from host records (both consumer protocols)
-    need = max(warmup, 3) + steps + 3
-    reps = -(-need // SLOT_BATCHES)
+    # ---- e2e: public API from host records, one arm per consumer protocol
+    arms = {}
     if not args.skip_e2e:
-        for r in range(reps):            # ConsumerRecord objects exist before the clock starts,
-            base.rep_records(r)          # exactly as they do for the CPU arm
-    barrier()
-    if args.skip_e2e:
-        e2e_poll = e2e_packed = e2e_raw = {"seconds": float("nan")}
-        raw_bytes_per_step = float("nan")
-    else:
-        e2e_poll = run_e2e(base, steps, max(warmup, 3), device, packed=False, repeat=reps)
-        barrier()
-        e2e_packed = run_e2e(base, steps, max(warmup, 3), device, packed=True, repeat=reps)
-        barrier()
-        enc = base.encoded(RAW_BATCH_BYTES)          # the broker's log segment exists before the clock starts
-        raw_bytes_per_step = enc.nbytes / SLOT_BATCHES
-        e2e_raw = run_e2e(base, steps, max(warmup, 3), device, packed="raw", repeat=reps)
+        from torchkafka_b200.testing import stub_kafka as sk
+        base.encoded(RAW_BATCH_BYTES)              # the broker's log segment exists before the clock starts
+        modes = ["poll", "packed", "raw"]
+        if hasattr(sk.KafkaConsumer, "poll_raw_into"):
+            modes.append("raw_into")
+        for mode in modes:
+            barrier()
+            arms[mode] = run_e2e(base, mode, device, E2E_MIN_SECONDS, 20e6,
+                                 max_records=POLL_MAX_OBJECTS if mode == "poll" else None)
     barrier()
 
-    rec_per_step = len(base) / SLOT_BATCHES
-    bytes_per_step = (base.nbytes + 16 * len(base)) / SLOT_BATCHES
-    t = torch.tensor([dev["ms"], e2e_poll["seconds"], e2e_packed["seconds"], e2e_raw["seconds"]], dtype=torch.float64)
+    n_arms = 4
+    order = ["poll", "packed", "raw", "raw_into"]
+    cols = [dev["ms"] / 1e3, float(dev["records"])]
+    for m in order:
+        a = arms.get(m)
+        cols += [a["seconds"], float(a["records"]), float(a["bytes"])] if a else [0.0, 0.0, 0.0]
+    t = torch.tensor(cols, dtype=torch.float64)
+    tmax, tsum = t.clone(), t.clone()
     if world > 1:
         import torch.distributed as dist
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-    ms, e2e_poll_s, e2e_packed_s, e2e_raw_s = [float(x) for x in t.tolist()]
-    total_records = dev["records"] * world
-    value = total_records / (ms / 1e3)
+        dist.all_reduce(tmax, op=dist.ReduceOp.MAX)
+        dist.all_reduce(tsum, op=dist.ReduceOp.SUM)
+    # whole-job throughput: the units all ranks processed / the slowest rank's time
+    value = float(tsum[1]) / float(tmax[0])
+    ms = float(tmax[0]) * 1e3
 
-    line = None
+    rc = 0
     if rank == 0:
         peaks = {}
         try:
@@ -511,55 +549,79 @@ def main_gpu(args):
             traffic = json.load(open(os.path.join(ROOT, "profiles", "roofline_traffic.json")))["bytes_per_launch"]
         except Exception:
             pass
-        e2e_value = steps * rec_per_step * world / e2e_poll_s
+        rec_per_step = len(base) / SLOT_BATCHES
+        bytes_per_rec = (base.nbytes + 16 * len(base)) / len(base)
+        d2h_per_step = 4 * BATCH + (64 + 8 * (SLOT_BATCHES + 1) * (PARTITIONS + 1)) // SLOT_BATCHES
+        link_peak = dev["h2d_peak_gbs"]
+
+        def arm_line(k, mode, path):
+            secs, recs, byts = float(tmax[2 + 3 * k]), float(tsum[3 + 3 * k]), float(tsum[4 + 3 * k])
+            if not secs:
+                return None
+            v = recs / secs
+            # link bytes: payload + 16 B of record header per record (CSR arms), or the raw
+            # RecordBatch bytes (raw arms) -- as counted by the pipeline over the whole window
+            link_bytes = byts + (16 * recs if mode in ("poll", "packed") else 0)
+            gbps_per_gpu = link_bytes / secs / 1e9 / world
+            a = arms[mode]
+            return {"value": v, "unit": "records/s", "path": path,
+                    "h2d_bytes_per_step": int(link_bytes / recs * rec_per_step), "d2h_bytes_per_step": d2h_per_step,
+                    "timed_region_s": secs, "steps_timed": int(a["batches"]) * world, "log_repeats": a["reps"],
+                    "link_GBps_per_gpu": gbps_per_gpu, "link_peak_GBps": link_peak,
+                    "link_frac": gbps_per_gpu / link_peak}
+
+        paths = {
+            "poll": "auto_commit(DataLoader(KafkaDataset with payload_schema)) over ConsumerRecord objects from "
+                    "consumer.poll(); clock from before the iteration starts to the last batch + synchronize",
+            "packed": "same API over consumer.poll_packed() (flat arrays, no per-record objects)",
+            "raw": "same API over consumer.poll_raw(): RecordBatch v2 blobs of the fetch response, "
+                   f"batch.size {RAW_BATCH_BYTES}; CRC-32C, varint framing and value gather on the GPU",
+            "raw_into": "same API over consumer.poll_raw_into(): the consumer receives the fetch response's "
+                        "RecordBatch v2 bytes straight into the slot's pinned buffer (no pack copy)",
+        }
+        lines = {m: arm_line(k, m, paths[m]) for k, m in enumerate(order) if m in arms}
         line = {
             "metric": METRIC, "value": value, "unit": "records/s", "n_gpus": world, "steps": steps,
-            "warmup": warmup, "ms_per_step": ms / steps, "higher_is_better": True, "scaling": "weak",
-            "vs_baseline": None, "dtype": "f64->f32", "data": "synthetic",
-            "config": {"workload": WORKLOAD, "batch": BATCH, "partitions": PARTITIONS,
-                       "slot_batches": SLOT_BATCHES, "slot_bytes": dev["slot_bytes"],
-                       "l2": f"4 distinct {dev['slot_bytes'] / 1e6:.0f} MB slots cycled "
-                             f"({4 * dev['slot_bytes'] / 1e6:.0f} MB > 126 MB L2): inputs come from HBM",
-                       "sharding": "one independent partition set per rank, no data-path collective"},
-            "batch_ready_GBps": value * bytes_per_step / rec_per_step / 1e9,
-            "e2e": {"value": e2e_value, "unit": "records/s",
-                    "h2d_bytes_per_step": int(bytes_per_step), "d2h_bytes_per_step": 4 * BATCH + (64 + 8 * (SLOT_BATCHES + 1) * (PARTITIONS + 1)) // SLOT_BATCHES,
-                    "path": "auto_commit(DataLoader(KafkaDataset with payload_schema)) over ConsumerRecord "
-                            "objects from consumer.poll()",
-                    "link_GBps": e2e_value * bytes_per_step / rec_per_step / 1e9 / world,
-                    "link_peak_GBps": dev["h2d_peak_gbs"],
-                    "link_frac": e2e_value * bytes_per_step / rec_per_step / 1e9 / world / dev["h2d_peak_gbs"]},
-            "e2e_packed": {"value": steps * rec_per_step * world / e2e_packed_s, "unit": "records/s",
-                           "path": "same API over consumer.poll_packed() (flat arrays, no per-record objects)",
-                           "link_frac": steps * bytes_per_step / e2e_packed_s / 1e9 / dev["h2d_peak_gbs"]},
-            "e2e_raw": {"value": steps * rec_per_step * world / e2e_raw_s, "unit": "records/s",
-                        "path": "same API over consumer.poll_raw(): RecordBatch v2 blobs of the fetch response, "
-                                f"batch.size {RAW_BATCH_BYTES}; CRC-32C, varint framing and value gather on the GPU",
-                        "h2d_bytes_per_step": None if raw_bytes_per_step != raw_bytes_per_step else int(raw_bytes_per_step),
-                        "link_frac": steps * raw_bytes_per_step / e2e_raw_s / 1e9 / dev["h2d_peak_gbs"]},
+            "warmup": warmup, "ms_per_step": ms / (steps * dev["repeats"]), "higher_is_better": True,
+            "scaling": "weak", "vs_baseline": None, "dtype": "f64->f32", "data": "synthetic",
+            "config": shared_config(world),
+            "repeats": dev["repeats"], "timed_region_s": ms / 1e3,
+            "setup": {"slot_batches": SLOT_BATCHES, "slot_bytes": dev["slot_bytes"],
+                      "passes": dev["passes"], "seed": f"{SEED} + rank"},
+            "batch_ready_GBps": value * bytes_per_rec / 1e9,
             "gpu_launches": dev["launches"],
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
                          "frac": achieved / peak, "traffic": traffic,
+                         "algo_bytes_per_launch": dev["algo_bytes_per_launch"],
                          "kernel": "tk_json_decode = k_json_parse<f32> (thread per element parse + pad/length/mask rows, one kernel)",
                          "share_of_step": dev["decode_ms_total"] / dev["ms_timed_region"],
                          "peak_source": peak_src, "launches_timed": dev["decode_launches"],
-                         "timed_in": "a second pass over the same K steps with the library's CUDA events "
+                         "timed_in": "a second pass over the same K*R steps with the library's CUDA events "
                                      "around the kernel (tk_ctx_set_timing); share_of_step is against that pass"},
             "clocks": clocks,
         }
+        if "poll" in lines:
+            line["e2e"] = lines["poll"]
+        for m in ("packed", "raw", "raw_into"):
+            if m in lines:
+                line["e2e_" + m] = lines[m]
+        bad = [m for m, l in lines.items() if l["link_frac"] > 1.0]
+        if bad:
+            log(f"INVALID: link_frac > 1 for {bad}: the timed region skipped work")
+            line["invalid"] = f"link_frac > 1 for {bad}"
+            rc = 3
         if world == 1 and not args.no_cpu:
-            sample = min(len(base), 20000)
-            c = run_cpu_single(base, sample)
+            c = run_cpu_single(base, args.cpu_seconds)
             line["cpu_baseline"] = {
                 "value": c["records"] / c["seconds"], "unit": "records/s", "cores": 1, "kind": "port",
-                "sample": f"{c['records']} records of the same workload, oracle/reference_path.py "
+                "sample": f"{c['records']} records ({c['seconds']:.1f} s) of the same workload, oracle/reference_path.py "
                           f"(json.loads + torch.tensor + pad collate + commit), 1 process, 1 thread"}
         print(json.dumps(line), flush=True)
     if world > 1:
         import torch.distributed as dist
         dist.all_reduce(torch.zeros(1))
         dist.destroy_process_group()
-    return 0
+    return rc
 
 
 def main():
@@ -569,6 +631,7 @@ def main():
     ap.add_argument("--warmup", type=int, default=128)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--no-cpu", action="store_true", help="skip the in-line cpu_baseline leg")
+    ap.add_argument("--cpu-seconds", type=float, default=10.0, help="bound of the cpu_baseline sample")
     ap.add_argument("--skip-e2e", action="store_true", help="device-resident leg only (profiling runs)")
     args = ap.parse_args()
     if args.impl == "reference":

@@ -75,6 +75,9 @@ class SlotResult:
 
 
 class SlotEngine:
+    #: key of the engine pool entry this engine belongs to (``acquire`` sets it)
+    pool_key = None
+
     def __init__(self, schema, batch_size: int, slot_bytes: int = 64 << 20,
                  slot_records: Optional[int] = None, n_slots: int = 3,
                  device: Optional[int] = None, n_partitions: int = 64):
@@ -480,3 +483,87 @@ class SlotEngine:
         r = _native.TkRbSummary()
         _native.check(self.lib.tk_slot_recordbatch_result(self.ctx, slot, C.byref(r)))
         return int(r.n_records), int(r.n_bytes), int(r.n_batches)
+
+
+# ---------------------------------------------------------------------- engine pool
+# Creating an engine pins host memory and allocates the device twins of every slot (hundreds of
+# megabytes, ~0.2 s); a dataset that is iterated again -- a new epoch, a re-opened pipeline after
+# a `break` -- would pay that each time.  Pipelines therefore take their engine from a small
+# pool and hand it back when they close.  An engine in the pool is idle (its stream is
+# synchronised) and reset (no open batch, no partition positions).
+_POOL: "collections.OrderedDict" = None
+_POOL_LOCK = None
+#: engines kept for reuse (least recently released ones are destroyed first)
+POOL_CAPACITY = 2
+
+
+def _pool():
+    global _POOL, _POOL_LOCK
+    if _POOL is None:
+        import atexit
+        import collections
+        import threading
+        _POOL = collections.OrderedDict()
+        _POOL_LOCK = threading.Lock()
+        atexit.register(clear_pool)          # before the CUDA runtime shuts down
+    return _POOL
+
+
+def acquire(schema, batch_size: int, slot_bytes: int, n_slots: int, device: Optional[int],
+            n_partitions: int) -> SlotEngine:
+    """An engine of this geometry: a pooled one if there is one, else a new one."""
+    dev = torch.cuda.current_device() if (device is None and torch.cuda.is_available()) else device
+    key = (dev, schema, int(batch_size), int(slot_bytes), int(n_slots), int(n_partitions))
+    pool = _pool()
+    try:
+        with _POOL_LOCK:
+            eng = pool.pop(key, None)
+    except TypeError:                        # unhashable schema: no pooling
+        eng, key = None, None
+    if eng is None:
+        eng = SlotEngine(schema, batch_size, slot_bytes=slot_bytes, n_slots=n_slots, device=device,
+                         n_partitions=n_partitions)
+    eng.pool_key = key
+    return eng
+
+
+def release(eng: SlotEngine):
+    """Hand an engine back (or destroy it when it cannot be pooled)."""
+    if getattr(eng, "ctx", None) is None or not eng.ctx.value:
+        return
+    key = eng.pool_key
+    if key is None or POOL_CAPACITY <= 0:
+        eng.close()
+        return
+    try:
+        eng.stream.synchronize()
+        eng.set_timing(False)
+        eng.json_decode_warp = False
+        eng.reset()
+    except Exception:
+        eng.close()
+        return
+    pool = _pool()
+    evicted = []
+    with _POOL_LOCK:
+        old = pool.pop(key, None)
+        if old is not None:
+            evicted.append(old)
+        pool[key] = eng
+        while len(pool) > POOL_CAPACITY:
+            evicted.append(pool.popitem(last=False)[1])
+    for e in evicted:
+        e.close()
+
+
+def clear_pool():
+    if _POOL is None:
+        return
+    with _POOL_LOCK:
+        engines = list(_POOL.values())
+        _POOL.clear()
+    for e in engines:
+        try:
+            e.close()
+        except Exception:
+            pass

@@ -26,7 +26,7 @@ from typing import Dict, Optional
 import numpy as np
 
 from . import _tkpack      # CPython helper built next to libtorchkafka_b200.so (csrc/tk_pymod.cpp)
-from .engine import SlotEngine
+from . import engine as _engine
 from .schema import PayloadError
 
 
@@ -54,9 +54,9 @@ class IngestPipeline:
         self.schema = schema
         self.batch_size = int(batch_size)
         self.drop_last = bool(drop_last)
-        self.engine = SlotEngine(schema, batch_size, slot_bytes=slot_bytes,
-                                 n_slots=max(n_slots, 2 + (int(n_producers) if threaded else 0)),
-                                 device=device, n_partitions=max_partitions)
+        self.engine = _engine.acquire(schema, batch_size, slot_bytes=slot_bytes,
+                                      n_slots=max(n_slots, 2 + (int(n_producers) if threaded else 0)),
+                                      device=device, n_partitions=max_partitions)
         self.poll_timeout_ms = poll_timeout_ms
         # kafka-python ends `for record in consumer` after consumer_timeout_ms without a record
         # (default: never).  The GPU path follows the same setting; the in-memory stub
@@ -119,6 +119,7 @@ class IngestPipeline:
             return
         self._closed = True
         self._stop.set()
+        alive = []
         if self._saved_switch is not None:
             sys.setswitchinterval(self._saved_switch)
             self._saved_switch = None
@@ -129,8 +130,13 @@ class IngestPipeline:
                 pass
             for t in self._threads:
                 t.join(timeout=30)
+            alive = list(self._threads)
             self._threads = []
-        self.engine.close()
+        # (a producer that did not stop in time may still touch its slot: such an engine is not reused)
+        if any(t.is_alive() for t in alive):
+            self.engine.close()
+        else:
+            _engine.release(self.engine)
 
     # ------------------------------------------------------------------ host side: poll + pack
     def _dense(self, tp) -> int:

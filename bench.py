@@ -263,7 +263,8 @@ def make_dataset_cls(log, mode, repeat=1):
     from torchkafka_b200.schema import JsonArray
     from torchkafka_b200.testing import stub_kafka as sk
     consumer_cls = sk.PollOnlyConsumer if mode == "poll" else sk.KafkaConsumer
-    input_mode = {"poll": "records", "packed": "packed", "raw": "raw", "raw_into": "raw_into"}[mode]
+    input_mode = {"poll": "records", "packed": "packed", "raw": "raw", "raw_into": "raw_into",
+                  "raw_dma": "raw_dma"}[mode]
 
     class Cfg2Dataset(KafkaDataset):
         payload_schema = JsonArray(torch.float32, max_len=MAX_LEN, min_size=MIN_SIZE)
@@ -310,15 +311,15 @@ def _iterate(cls, device, host_results):
     return t1 - t0, seen, stats, checksum
 
 
-def run_e2e(log, mode, device, min_seconds, rate_guess, max_records=None):
+def run_e2e(rlog, mode, device, min_seconds, rate_guess, max_records=None):
     """`e2e` of one input protocol.  Warm-up: a complete iteration over the base log (its engine --
     pinned slots, device twins -- goes back to the pool and serves the timed iteration).  Timed:
     a complete iteration over `reps` repetitions of the log, sized from `rate_guess` for a window
     of `min_seconds` and never shorter than 20x the pipeline's read-ahead."""
     import torch
     torch.cuda.set_device(device)
-    n = len(log)
-    slot_records = E2E_SLOT_BYTES / (log.nbytes / n)
+    n = len(rlog)
+    slot_records = E2E_SLOT_BYTES / (rlog.nbytes / n)
     readahead = (E2E_SLOTS + 2) * slot_records                    # every slot of the pipeline
     want = max(min_seconds * rate_guess, 20 * readahead)
     if max_records:
@@ -326,12 +327,12 @@ def run_e2e(log, mode, device, min_seconds, rate_guess, max_records=None):
     reps = max(2, int(math.ceil(want / n)))
     if mode == "poll":
         for r in range(reps):            # ConsumerRecord objects exist before the clock starts,
-            log.rep_records(r)           # exactly as they do for the CPU arm
+            rlog.rep_records(r)           # exactly as they do for the CPU arm
         gc.collect()
         gc.freeze()                      # (millions of live tuples: keep them out of later GC passes)
     host_results = torch.zeros((reps * SLOT_BATCHES + 2, BATCH), dtype=torch.int32).pin_memory()
-    _iterate(make_dataset_cls(log, mode, 1), device, host_results)           # warm-up iteration
-    seconds, batches, stats, checksum = _iterate(make_dataset_cls(log, mode, reps), device, host_results)
+    _iterate(make_dataset_cls(rlog, mode, 1), device, host_results)           # warm-up iteration
+    seconds, batches, stats, checksum = _iterate(make_dataset_cls(rlog, mode, reps), device, host_results)
     # the iteration ran to the end of the stream: exactly reps * n records were consumed
     if stats.get("records") != reps * n:
         log(f"warning: pipeline counted {stats.get('records')} records, the stream holds {reps * n}")
@@ -509,17 +510,14 @@ def main_gpu(args):
     if not args.skip_e2e:
         from torchkafka_b200.testing import stub_kafka as sk
         base.encoded(RAW_BATCH_BYTES)              # the broker's log segment exists before the clock starts
-        modes = ["poll", "packed", "raw"]
-        if hasattr(sk.KafkaConsumer, "poll_raw_into"):
-            modes.append("raw_into")
+        modes = [m for m in os.environ.get("TK_E2E_ARMS", "poll,packed,raw,raw_into,raw_dma").split(",") if m]
         for mode in modes:
             barrier()
             arms[mode] = run_e2e(base, mode, device, E2E_MIN_SECONDS, 20e6,
                                  max_records=POLL_MAX_OBJECTS if mode == "poll" else None)
     barrier()
 
-    n_arms = 4
-    order = ["poll", "packed", "raw", "raw_into"]
+    order = ["poll", "packed", "raw", "raw_into", "raw_dma"]
     cols = [dev["ms"] / 1e3, float(dev["records"])]
     for m in order:
         a = arms.get(m)
@@ -577,7 +575,9 @@ def main_gpu(args):
             "raw": "same API over consumer.poll_raw(): RecordBatch v2 blobs of the fetch response, "
                    f"batch.size {RAW_BATCH_BYTES}; CRC-32C, varint framing and value gather on the GPU",
             "raw_into": "same API over consumer.poll_raw_into(): the consumer receives the fetch response's "
-                        "RecordBatch v2 bytes straight into the slot's pinned buffer (no pack copy)",
+                        "RecordBatch v2 bytes straight into the slot's pinned buffer (its copy is the recv)",
+            "raw_dma": "same API over consumer.poll_raw() with fetch_arenas(): the consumer's receive buffer is "
+                       "page-locked once and every blob goes to the device straight out of it (no host copy)",
         }
         lines = {m: arm_line(k, m, paths[m]) for k, m in enumerate(order) if m in arms}
         line = {
@@ -602,7 +602,7 @@ def main_gpu(args):
         }
         if "poll" in lines:
             line["e2e"] = lines["poll"]
-        for m in ("packed", "raw", "raw_into"):
+        for m in ("packed", "raw", "raw_into", "raw_dma"):
             if m in lines:
                 line["e2e_" + m] = lines[m]
         bad = [m for m, l in lines.items() if l["link_frac"] > 1.0]

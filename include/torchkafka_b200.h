@@ -59,7 +59,8 @@ typedef enum {
     TK_STATUS_SIZE = 5,         /* raw record with the wrong byte count */
     TK_STATUS_RAGGED = 6,       /* fixed_len schema, other length (torch.stack raises) */
     TK_STATUS_CORRUPT = 7,      /* record batch failed its CRC or framing (kafka CorruptRecordException) */
-    TK_STATUS_MISSING_KEY = 8   /* JSON object without one of the named fields (KeyError) */
+    TK_STATUS_MISSING_KEY = 8,  /* JSON object without one of the named fields (KeyError) */
+    TK_STATUS_SLOT_OVERFLOW = 9 /* record batches whose (decompressed) values do not fit the slot's byte buffer */
 } tk_status_t;
 
 /* Per-slot result header, written by the kernels, fetched with tk_slot_fetch_result. */
@@ -118,6 +119,9 @@ int tk_slot_fill(tk_ctx* ctx, int slot, uint32_t first_record, uint64_t first_by
                  const uint8_t* values, const uint32_t* starts, const int32_t* partitions,
                  const int64_t* offsets, uint32_t n, int n_threads, uint64_t* bytes_after);
 int tk_h2d_peak_gbs(int device, uint64_t bytes, int iters, double* gbs_out);
+/* pin the pack helper's threads to the given cores (n = 0: no pinning): the staging slots should be
+ * filled by cores of the GPU's NUMA node (hard part 1) */
+int tk_pack_set_affinity(const int* cpus, int n);
 
 /* ---- K1a/K1b phase 1: element count per record + keep flag -----------------
  * replaces `len(json.loads(record.value)) < min_size -> None`
@@ -250,7 +254,10 @@ int tk_process_slot(tk_ctx* ctx, int slot, const tk_job_t* job, void* stream);
  * device pointers and needs no tk_ctx.
  *   - at most TK_NOALLOC_MAX_RECORDS records per call; larger n is rejected with an error
  *   - the first call on a device looks up the address of the scratch array
- *     (cudaGetSymbolAddress); make that first call before any stream capture
+ *     (cudaGetSymbolAddress); make that first call before any stream capture, and during
+ *     initialisation: with lazy module loading it is also when the driver loads this
+ *     library's device code, which may allocate inside the driver.  Host threads may make
+ *     it concurrently
  *   - all calls on a device share the scratch: calls that may overlap on the GPU
  *     (different streams without a dependency) race; issue them on one stream
  *   - no cudaMalloc / cudaFree / allocating library call is made */
@@ -294,12 +301,15 @@ typedef struct tk_rb_summary {
     uint32_t status;         /* TK_RB_OK */
     uint32_t reserved;
 } tk_rb_summary_t;
-enum { TK_RB_OK = 0 };
+enum { TK_RB_OK = 0, TK_RB_OVERFLOW = 1 /* some batches' values did not fit slot_bytes: their first
+                                           record carries TK_STATUS_SLOT_OVERFLOW, nothing was written
+                                           outside the slot */ };
 #define TK_MAX_BLOBS 1024u
 /* flags the split leaves in tk_rec_t.partition (the scans act on them) */
 #define TK_REC_DROPPED     0x40000000   /* below the fetch offset / control batch: not consumed */
 #define TK_REC_CORRUPT     0x20000000
 #define TK_REC_UNSUPPORTED 0x10000000
+#define TK_REC_OVERFLOW    0x30000000   /* both of the above: values did not fit the slot */
 #define TK_REC_FLAGS       0x70000000
 /* Raw bytes are in the slot's pinned buffer [0, n_bytes).  The call follows the chain of batch
  * headers of every blob on the host (one read per batch) and returns the number of record
@@ -309,6 +319,16 @@ enum { TK_RB_OK = 0 };
  * tk_slot_submit.  Fails at once if the slot geometry (slot_records) is too small. */
 int tk_slot_submit_recordbatches(tk_ctx* ctx, int slot, uint64_t n_bytes, const tk_blob_t* blobs,
                                  uint32_t n_blobs, uint32_t* n_records);
+/* Same, for a consumer that keeps the fetched bytes in buffers of its own (a receive arena): blob k
+ * lies at host_ptrs[k] (blobs[k].start is still its place in the slot's device buffer, blobs back
+ * to back) and is copied to the device straight from there -- no gather into the slot's pinned
+ * buffer.  Page-lock the arena once with tk_host_register so the copies are asynchronous DMA
+ * transfers; the memory must stay valid until the slot's split has run (tk_slot_recordbatch_result,
+ * or the slot's result). */
+int tk_slot_submit_recordbatches_ext(tk_ctx* ctx, int slot, uint64_t n_bytes, const tk_blob_t* blobs,
+                                     const uint8_t* const* host_ptrs, uint32_t n_blobs, uint32_t* n_records);
+int tk_host_register(void* ptr, uint64_t bytes);
+int tk_host_unregister(void* ptr);
 /* optional: wait for the split and read its totals (value bytes, batches) */
 int tk_slot_recordbatch_result(tk_ctx* ctx, int slot, tk_rb_summary_t* summary);
 /* one record header of the device twin (error reports) */

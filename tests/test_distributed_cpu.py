@@ -69,3 +69,51 @@ def test_commit_barrier_without_process_group_is_identity():
     v = torch.tensor([3, -1, 7], dtype=torch.int64)
     assert torch.equal(tkd.commit_barrier(v), v)
     assert tkd.owned_partitions(8, 1, 4) == [1, 5]
+
+
+def _barrier_worker(rank, world, port, out_dir):
+    """Two ranks with different batch counts drive auto_commit's per-batch barrier object."""
+    import collections
+    from torchkafka_b200.auto_commit import _CommitBarrier
+    from torchkafka_b200.testing.stub_kafka import OffsetAndMetadata, TopicPartition
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+
+    class FakeDataset:
+        max_partitions = 8
+        device_index = None
+
+    ds = FakeDataset()
+    barrier = _CommitBarrier(ds, True)
+    seen = []
+    n_batches = 3 if rank == 0 else 5                     # rank 0 finishes first and keeps answering
+    for k in range(n_batches):
+        barrier.note({TopicPartition("t", rank + 2 * (k % 2)): OffsetAndMetadata(10 * (k + 1) + rank, "")})
+        assert barrier.exchange(False) is False
+        seen.append(ds.group_offsets.tolist())
+    rounds = 0
+    while True:
+        done = barrier.exchange(True)
+        seen.append(ds.group_offsets.tolist())
+        if done:
+            break
+        rounds += 1
+    with open(os.path.join(out_dir, f"b{rank}.json"), "w") as f:
+        json.dump({"seen": seen, "rounds": rounds, "lat": len(ds.commit_barrier_us)}, f)
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+def test_auto_commit_barrier_object_with_uneven_ranks(tmp_path):
+    world = 2
+    mp.spawn(_barrier_worker, args=(world, _free_port(), str(tmp_path)), nprocs=world, join=True)
+    a, b = [json.load(open(tmp_path / f"b{r}.json")) for r in range(world)]
+    # both ranks took part in the same number of exchanges and saw the same vectors in each
+    assert a["lat"] == b["lat"] == 6
+    assert a["seen"] == b["seen"]
+    assert a["rounds"] == 2 and b["rounds"] == 0           # rank 0 answered rank 1's last two batches
+    # step 0: rank 0 reported partition 0 -> 10, rank 1 partition 1 -> 11; others unseen
+    assert a["seen"][0] == [10, 11, -1, -1, -1, -1, -1, -1]
+    # final vector: the last offset every rank reported per partition
+    assert a["seen"][-1] == [30, 51, 20, 41, -1, -1, -1, -1]

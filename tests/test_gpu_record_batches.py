@@ -370,3 +370,50 @@ def test_broken_snappy_batches_raise_at_their_batch(damage):
     with pytest.raises(PayloadError) as ei:
         run_blobs([(1, good + bytes(bad), 0, 0)], JsonArray(torch.float32, max_len=64), 2)
     assert ei.value.status == 7 and ei.value.partition == 1 and ei.value.offset == 4
+
+
+# ---------------------------------------------------------------- input modes without a gather copy
+@pytest.mark.parametrize("mode", ["raw_into", "raw_dma"])
+@pytest.mark.parametrize("codec", [0, 3])
+def test_cfg2_received_into_the_slot_or_copied_from_the_arena(mode, codec):
+    """`poll_raw_into` (the consumer writes the response into the pinned slot) and `raw_dma` (blobs go to
+    the device out of the consumer's page-locked arena) give the same batches and commits."""
+    log = syn.make_log(2, 5000, seed=31, partitions=8, layout="chunked", chunk=200)
+    schema = JsonArray(torch.float32, max_len=256, min_size=32)
+    gpu = run_gpu(log, schema, 128, device_input=mode, slot_bytes=1 << 20,
+                  consumer_kwargs={"raw_batch_bytes": 16384, "raw_codec": codec})
+    assert_same(gpu, run_oracle(log, schema, 128), schema)
+
+
+def test_decompressed_values_beyond_the_slot_are_reported_not_written():
+    """Compressed batches whose values need more room than the slot has: nothing may be written
+    outside the slot's byte buffer; the batch that does not fit raises PayloadError(status 9)."""
+    n = 400
+    vals = [json.dumps([0.0] * 200).encode() for _ in range(n)]          # ~1 KB each, compresses > 20x
+    log = RecordLog(vals, np.zeros(n, np.int32), np.arange(n))
+    schema = JsonArray(torch.float32, max_len=256, min_size=0)
+
+    from torchkafka_b200.pipeline import IngestPipeline
+    ds = make_dataset(log, schema, slot_bytes=64 << 10, device_input="raw",
+                      consumer_kwargs={"raw_batch_bytes": 32768, "raw_codec": 3})
+    # defeat the fetch budget's expansion estimate: ask for whole slots of compressed bytes
+    orig = IngestPipeline._gather_raw
+
+    def greedy(self, slot, scratch):
+        self._raw_expansion = 1.0
+        return orig(self, slot, scratch)
+
+    IngestPipeline._gather_raw = greedy
+    try:
+        got, err = 0, None
+        try:
+            for batch in ds.device_batches(16):
+                got += batch[0].shape[0]
+        except PayloadError as e:
+            err = e
+        assert err is not None and err.status == 9, (got, err)
+        # everything in front of the batch that did not fit was delivered intact
+        assert got > 0 and got % 16 == 0
+    finally:
+        IngestPipeline._gather_raw = orig
+        ds.close()

@@ -68,6 +68,7 @@ STATUS_NAMES = {
     6: "record length or shape differs from the schema's (torch.tensor / torch.stack would raise)",
     7: "record batch failed its CRC-32C or its record framing (CorruptRecordException in kafka-python)",
     8: "JSON object without one of the schema's fields (KeyError in the reference)",
+    9: "the (decompressed) records of this fetch do not fit the staging slot; raise device_slot_bytes",
 }
 
 _p = C.POINTER
@@ -110,6 +111,11 @@ _SIGNATURES = {
                                      C.c_void_p, C.c_void_p]),
     "tk_slot_submit_recordbatches": (C.c_int, [C.c_void_p, C.c_int, C.c_uint64, _p(TkBlob), C.c_uint32,
                                              _p(C.c_uint32)]),
+    "tk_slot_submit_recordbatches_ext": (C.c_int, [C.c_void_p, C.c_int, C.c_uint64, _p(TkBlob), C.c_void_p,
+                                                 C.c_uint32, _p(C.c_uint32)]),
+    "tk_host_register": (C.c_int, [C.c_void_p, C.c_uint64]),
+    "tk_host_unregister": (C.c_int, [C.c_void_p]),
+    "tk_pack_set_affinity": (C.c_int, [C.c_void_p, C.c_int]),
     "tk_slot_recordbatch_result": (C.c_int, [C.c_void_p, C.c_int, _p(TkRbSummary)]),
     "tk_slot_record": (C.c_int, [C.c_void_p, C.c_int, C.c_uint32, _p(TkRec)]),
     "tk_crc32c": (C.c_uint32, [C.c_void_p, C.c_uint64, C.c_uint32]),

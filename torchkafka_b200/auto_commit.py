@@ -20,19 +20,73 @@ loader only supplies ``batch_size`` and ``drop_last`` and whole device batches
 come from ``KafkaDataset.device_batches``.  The commit after each batch carries
 explicit offsets computed on the GPU (K4), identical to what the reference
 commits in single-process mode.
+
+Also new, for several ranks that each ingest their own partitions (one process per GPU,
+``torchkafka_b200.distributed``): ``auto_commit(dataloader, commit_barrier=True)`` (or a
+``torch.distributed`` process group) makes the commit after each batch a *commit barrier*.  In
+place of the reference's per-worker ``os.kill(pid, SIGUSR1)`` fan-out (``auto_commit.py:63-72``)
+every rank contributes its per-partition commit offsets, all ranks obtain the group's vector
+(element-wise maximum, ``dataset.group_offsets``) and then commit their own partitions, so the
+committed offsets of the whole group always describe the same training step.  A rank whose
+stream ended keeps answering the barrier until every rank has finished.
 """
 from __future__ import annotations
 
+import collections
 import ctypes
 import itertools
 import multiprocessing
+import time
 
 from torch.utils.data import DataLoader
 
 from .kafka_dataset import KafkaDataset
 
 
-def _device_path(dataloader: DataLoader):
+class _CommitBarrier:
+    """Per-batch exchange of the ranks' commit vectors (see ``distributed.commit_barrier``)."""
+
+    def __init__(self, dataset, group):
+        import torch
+        import torch.distributed as dist
+        from . import distributed as tkd
+        if not (dist.is_available() and dist.is_initialized()):
+            raise RuntimeError("commit_barrier needs an initialised torch.distributed process group")
+        self.tkd = tkd
+        self.group = None if group is True else group
+        backend = str(dist.get_backend(self.group))
+        # host tensors when the group can move them (gloo), else a small device tensor (NCCL)
+        self.device = None if "gloo" in backend or "mpi" in backend else torch.device(
+            "cuda", dataset.device_index if dataset.device_index is not None else torch.cuda.current_device())
+        self.n = int(dataset.max_partitions)
+        # [0, n): commit offset per partition id (-1: nothing to report), [n]: 1 = this rank's stream ended
+        self.vec = torch.full((self.n + 1,), -1, dtype=torch.int64)
+        self.vec[self.n] = 0
+        self.dataset = dataset
+        dataset.group_offsets = None
+        dataset.commit_barrier_us = collections.deque(maxlen=1 << 16)
+
+    def note(self, offsets):
+        """Merge the {TopicPartition: OffsetAndMetadata} of the batch just consumed."""
+        for tp, om in offsets.items():
+            p = int(tp.partition)
+            if not 0 <= p < self.n:
+                raise RuntimeError(f"partition {p} outside [0, max_partitions={self.n})")
+            self.vec[p] = int(om.offset)
+
+    def exchange(self, done: bool) -> bool:
+        """One barrier; returns True once every rank has reported the end of its stream."""
+        self.vec[self.n] = 1 if done else 0
+        t0 = time.perf_counter()
+        local = self.vec.to(self.device) if self.device is not None else self.vec
+        merged = self.tkd.commit_barrier_min_max(local, self.n, self.group)
+        merged = merged.cpu() if self.device is not None else merged
+        self.dataset.commit_barrier_us.append((time.perf_counter() - t0) * 1e6)
+        self.dataset.group_offsets = merged[:self.n]
+        return bool(merged[self.n] == 1)
+
+
+def _device_path(dataloader: DataLoader, commit_barrier=None):
     dataset = dataloader.dataset
     if dataloader.num_workers != 0:
         raise RuntimeError(
@@ -41,13 +95,26 @@ def _device_path(dataloader: DataLoader):
         )
     if dataloader.batch_size is None:
         raise ValueError("auto_commit needs a DataLoader with a batch_size for schema datasets.")
+    if commit_barrier is None or commit_barrier is False:
+        for batch in dataset.device_batches(dataloader.batch_size, dataloader.drop_last):
+            yield batch
+            dataset.commit()
+        return
+    barrier = _CommitBarrier(dataset, commit_barrier)
     for batch in dataset.device_batches(dataloader.batch_size, dataloader.drop_last):
         yield batch
-        dataset.commit()
+        barrier.note(dataset._explicit_offsets)         # pylint: disable=protected-access
+        barrier.exchange(False)                         # every rank has consumed this step's batch ...
+        dataset.commit()                                # ... then each commits its own partitions
+    while not barrier.exchange(True):                   # finished: answer the others' barriers
+        pass
 
 
-def auto_commit(dataloader: DataLoader):
-    """Generator over ``dataloader`` that commits each batch once it was consumed."""
+def auto_commit(dataloader: DataLoader, commit_barrier=None):
+    """Generator over ``dataloader`` that commits each batch once it was consumed.
+
+    ``commit_barrier`` (additive; schema datasets, one rank per GPU): ``True`` for the default
+    ``torch.distributed`` group or a process group -- see the module docstring."""
     if not isinstance(dataloader, DataLoader):
         raise TypeError("A DataLoader must be provided.")
     dataset = dataloader.dataset
@@ -55,8 +122,10 @@ def auto_commit(dataloader: DataLoader):
         yield from dataloader
         return
     if dataset.payload_schema is not None:
-        yield from _device_path(dataloader)
+        yield from _device_path(dataloader, commit_barrier)
         return
+    if commit_barrier:
+        raise ValueError("commit_barrier needs a dataset with a payload_schema (one rank per GPU)")
     if dataloader.num_workers == 0:
         for batch in dataloader:
             yield batch

@@ -11,9 +11,15 @@
 #include <vector>
 #include "tk_internal.h"
 
+#include <atomic>
 #include <condition_variable>
 #include <functional>
+#include <memory>
 #include <mutex>
+#if defined(__linux__)
+#include <pthread.h>
+#include <sched.h>
+#endif
 
 static thread_local char g_err[1024] = "";
 
@@ -62,18 +68,7 @@ private:
             }
         }
     }
-    void loop(int) {
-        unsigned long seen = 0;
-        for (;;) {
-            {
-                std::unique_lock<std::mutex> g(m_);
-                cv_.wait(g, [&]() { return gen_ != seen; });
-                seen = gen_;
-                if (stop_) return;
-            }
-            work();
-        }
-    }
+    void loop(int);
     std::vector<std::thread> workers_;
     std::mutex m_, run_m_;
     std::condition_variable cv_, done_cv_;
@@ -84,16 +79,82 @@ private:
     unsigned long gen_;
 };
 
-static CopyPool* g_pool = nullptr;
+// The pool is process-wide (one process drives one GPU).  A caller asking for more threads than
+// the pool has gets a new, larger pool; the old one is destroyed by whoever holds its last
+// reference, so a run() in flight on it finishes undisturbed.
+static std::shared_ptr<CopyPool> g_pool;
 static std::mutex g_pool_m;
 
-static CopyPool* copy_pool(int threads) {
-    std::lock_guard<std::mutex> g(g_pool_m);
-    if (!g_pool || g_pool->size() < threads - 1) {
-        delete g_pool;
-        g_pool = new CopyPool(threads > 1 ? threads - 1 : 0);
+// Cores the pack threads run on (tk_pack_set_affinity): applied by every worker when it wakes up
+// and finds a new generation of the list.
+static std::vector<int> g_pack_cpus;
+static std::atomic<unsigned> g_pack_cpus_gen{0};
+
+static void apply_pack_affinity(unsigned* seen) {
+#if defined(__linux__)
+    const unsigned gen = g_pack_cpus_gen.load(std::memory_order_acquire);
+    if (gen == *seen) return;
+    *seen = gen;
+    std::vector<int> cpus;
+    { std::lock_guard<std::mutex> g(g_pool_m); cpus = g_pack_cpus; }
+    if (cpus.empty()) return;
+    cpu_set_t set;
+    CPU_ZERO(&set);
+    for (int c : cpus) if (c >= 0 && c < CPU_SETSIZE) CPU_SET(c, &set);
+    pthread_setaffinity_np(pthread_self(), sizeof(set), &set);
+#else
+    (void)seen;
+#endif
+}
+
+void CopyPool::loop(int) {
+    unsigned long seen = 0;
+    unsigned cpus_seen = 0;
+    for (;;) {
+        {
+            std::unique_lock<std::mutex> g(m_);
+            cv_.wait(g, [&]() { return gen_ != seen; });
+            seen = gen_;
+            if (stop_) return;
+        }
+        apply_pack_affinity(&cpus_seen);
+        work();
     }
+}
+
+static std::shared_ptr<CopyPool> copy_pool(int threads) {
+    std::lock_guard<std::mutex> g(g_pool_m);
+    if (!g_pool || g_pool->size() < threads - 1)
+        g_pool = std::make_shared<CopyPool>(threads > 1 ? threads - 1 : 0);
     return g_pool;
+}
+
+// Pin the pack threads to `cpus` (n = 0: leave them where they are).  The pinned staging slots
+// should be filled by cores of the NUMA node the GPU hangs off (torchkafka_b200/affinity.py).
+extern "C" int tk_pack_set_affinity(const int* cpus, int n) {
+    TK_REQUIRE(n >= 0 && (cpus || n == 0), "bad cpu list");
+    {
+        std::lock_guard<std::mutex> g(g_pool_m);
+        g_pack_cpus.assign(cpus, cpus + n);
+    }
+    g_pack_cpus_gen.fetch_add(1, std::memory_order_release);
+    return 0;
+}
+
+// Page-lock a host buffer the caller owns (a consumer's receive arena) so that the H2D copies of
+// tk_slot_submit_recordbatches_ext are true asynchronous DMA transfers out of it.
+extern "C" int tk_host_register(void* ptr, uint64_t bytes) {
+    TK_REQUIRE(ptr && bytes, "bad buffer");
+    cudaError_t e = cudaHostRegister(ptr, bytes, cudaHostRegisterPortable);
+    if (e == cudaErrorHostMemoryAlreadyRegistered) { cudaGetLastError(); return 0; }
+    if (e != cudaSuccess) { cudaGetLastError(); tk_set_error("cudaHostRegister failed: %s", cudaGetErrorString(e)); return -1; }
+    return 0;
+}
+extern "C" int tk_host_unregister(void* ptr) {
+    TK_REQUIRE(ptr, "bad buffer");
+    cudaError_t e = cudaHostUnregister(ptr);
+    if (e != cudaSuccess) { cudaGetLastError(); tk_set_error("cudaHostUnregister failed: %s", cudaGetErrorString(e)); return -1; }
+    return 0;
 }
 
 // Gather copy with non-temporal stores: the destination (pinned staging) is written once and

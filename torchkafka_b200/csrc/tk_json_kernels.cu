@@ -86,7 +86,7 @@ __global__ void __launch_bounds__(256) k_json_scan(const scan_args a) {
         if (pflags) {
             if (lane == 0) {
                 a.rec_len[i] = 0;
-                a.rec_status[i] = (pflags & TK_REC_CORRUPT) ? TK_STATUS_CORRUPT
+                a.rec_status[i] = (pflags & TK_REC_OVERFLOW) == TK_REC_OVERFLOW ? TK_STATUS_SLOT_OVERFLOW : (pflags & TK_REC_CORRUPT) ? TK_STATUS_CORRUPT
                                 : (pflags & TK_REC_UNSUPPORTED) ? TK_STATUS_UNSUPPORTED : TK_STATUS_OK;
                 a.rec_kidx[i] = -1;
                 a.rec_tok[i] = 0;

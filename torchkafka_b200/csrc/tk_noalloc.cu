@@ -12,7 +12,10 @@
 // reserved until the process exits.
 //
 // The first call on a device resolves the array's device address (cudaGetSymbolAddress);
-// make that first call outside any stream capture.
+// make that first call outside any stream capture.  With CUDA's lazy module loading that
+// first call (symbol lookup, first launch) is also when the driver loads the library's
+// device code, which may allocate inside the driver: make it during initialisation, not in
+// the section that must not allocate.
 //
 // Limit: TK_NOALLOC_MAX_RECORDS records per call (scratch = one uint32 per tile of 1024
 // records, a little over 4 KiB in total).
@@ -22,6 +25,7 @@
 // reads, in stream order -- but two calls whose kernels overlap on the GPU (different
 // streams, no dependency) would overwrite each other's tile counts: callers must order
 // calls on one device, e.g. by issuing them on one stream.
+#include <atomic>
 #include "tk_internal.h"
 
 #define NA_THREADS 256
@@ -35,19 +39,21 @@ static __device__ __align__(256) uint32_t g_na_scratch[NA_MAX_TILES + 64];
 // Device address of g_na_scratch per device.  In host code the name g_na_scratch is only a
 // handle for the runtime, not an address a kernel can use, so the address is looked up once
 // per device with cudaGetSymbolAddress (with that device current) and passed to the kernels.
-static uint32_t* g_na_ptr[64];
-static bool g_na_ready[64];
+// Several host threads may make the first call on a device at the same time: the pointer is
+// published with release / read with acquire (every thread that loses the race stores the same value).
+static std::atomic<uint32_t*> g_na_ptr[64];
 
 static int na_setup(int device, uint32_t** out) {
     TK_REQUIRE(device >= 0 && device < 64, "device index %d not supported", device);
-    if (!g_na_ready[device]) {
+    uint32_t* ptr = g_na_ptr[device].load(std::memory_order_acquire);
+    if (!ptr) {
         void* p = nullptr;
         TK_CUDA(cudaGetSymbolAddress(&p, g_na_scratch));
         TK_REQUIRE(p != nullptr, "cudaGetSymbolAddress returned a null address");
-        g_na_ptr[device] = static_cast<uint32_t*>(p);
-        g_na_ready[device] = true;
+        ptr = static_cast<uint32_t*>(p);
+        g_na_ptr[device].store(ptr, std::memory_order_release);
     }
-    *out = g_na_ptr[device];
+    *out = ptr;
     return 0;
 }
 

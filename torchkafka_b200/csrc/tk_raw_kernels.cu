@@ -29,7 +29,7 @@ __global__ void __launch_bounds__(256) k_raw_scan(const tk_rec_t* __restrict__ r
     rec_len[i] = (int32_t)len;
     const int32_t pflags = recs[i].partition & TK_REC_FLAGS;    // set by the record-batch split
     if (pflags) {
-        rec_status[i] = (pflags & TK_REC_CORRUPT) ? TK_STATUS_CORRUPT
+        rec_status[i] = (pflags & TK_REC_OVERFLOW) == TK_REC_OVERFLOW ? TK_STATUS_SLOT_OVERFLOW : (pflags & TK_REC_CORRUPT) ? TK_STATUS_CORRUPT
                       : (pflags & TK_REC_UNSUPPORTED) ? TK_STATUS_UNSUPPORTED : TK_STATUS_OK;
         rec_kidx[i] = -1;
         return;

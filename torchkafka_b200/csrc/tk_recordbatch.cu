@@ -99,7 +99,9 @@ __device__ __forceinline__ bool rb_varint(const uint8_t* raw, uint32_t& p, uint3
 static inline uint32_t rb_host_be32(const uint8_t* p) {
     return ((uint32_t)p[0] << 24) | ((uint32_t)p[1] << 16) | ((uint32_t)p[2] << 8) | p[3];
 }
-static int rb_walk_host(const uint8_t* raw, const tk_blob_t* blobs, uint32_t n_blobs, tk_rb_batch* out,
+// `raw` addresses the slot's pinned buffer; with `ext` (one host pointer per blob) blob t's bytes are
+// read from ext[t] instead, wherever the caller keeps them (positions stay slot offsets).
+static int rb_walk_host(const uint8_t* raw_slot, const uint8_t* const* ext, const tk_blob_t* blobs, uint32_t n_blobs, tk_rb_batch* out,
                         uint32_t max_batches, uint32_t max_records, uint32_t* n_batches_out, uint32_t* n_records_out,
                         tk_rb_unit* units, uint32_t max_units, uint32_t* n_units_out, uint32_t* n_coded_out) {
     uint32_t nb = 0;
@@ -110,6 +112,7 @@ static int rb_walk_host(const uint8_t* raw, const tk_blob_t* blobs, uint32_t n_b
         const tk_blob_t& blob = blobs[t];
         const uint32_t blob_end = blob.start + blob.length;
         uint32_t pos = blob.start;
+        const uint8_t* raw = ext ? ext[t] - blob.start : raw_slot;       // raw + slot offset = the byte
         while (blob_end - pos >= 12u) {
             const uint32_t blen = rb_host_be32(raw + pos + 8);
             uint32_t end, status = TK_STATUS_OK, count = 1, codec = 0;
@@ -406,28 +409,41 @@ __global__ void __launch_bounds__(256) k_rb_check(const rb_args a) {
 // One block: exclusive scan of the batches' value bytes -> first byte of each batch in the slot.
 __global__ void __launch_bounds__(1024) k_rb_prefix(const rb_args a) {
     __shared__ unsigned long long warp_tot[32];
-    __shared__ unsigned long long s_total, s_run;
+    __shared__ unsigned long long s_total, s_run, s_fit;
     const uint32_t t = threadIdx.x;
     const uint32_t n_batches = a.n_batches;
-    if (t == 0) s_run = 0;
+    if (t == 0) { s_run = 0; s_fit = ~0ull; }
     __syncthreads();
     for (uint32_t base = 0; base < n_batches; base += blockDim.x) {
         const uint32_t i = base + t;
         const unsigned long long v = i < n_batches ? a.batches[i].value_bytes : 0ull;
         const unsigned long long excl = s_run + rb_block_scan(v, warp_tot, &s_total);
-        if (i < n_batches) a.batches[i].byte_base = (uint32_t)excl;
+        if (i < n_batches) {
+            // Values of compressed batches come out of the decompressed buffer, which can hold more
+            // than the slot: a batch whose values end behind the slot's byte buffer (and, the prefix
+            // being monotone, every batch after it) is not copied; its records surface as
+            // TK_STATUS_SLOT_OVERFLOW.  s_fit = value bytes of the batches in front of the first such one.
+            if (excl + v > a.slot_bytes) {
+                a.batches[i].status = TK_STATUS_SLOT_OVERFLOW;
+                a.batches[i].value_bytes = 0;
+                a.batches[i].byte_base = 0;
+                atomicMin(&s_fit, excl);
+            } else {
+                a.batches[i].byte_base = (uint32_t)excl;
+            }
+        }
         __syncthreads();
         if (t == 0) s_run += s_total;
         __syncthreads();
     }
     if (t == 0) {
-        // (the values are a subset of the raw bytes, which fit the slot: no capacity check needed)
+        const unsigned long long used = s_fit < s_run ? s_fit : s_run;
         a.summary->n_records = a.n_records;
         a.summary->n_batches = n_batches;
-        a.summary->n_bytes = s_run;
-        a.summary->status = TK_RB_OK;
+        a.summary->n_bytes = used;
+        a.summary->status = s_fit < s_run ? TK_RB_OVERFLOW : TK_RB_OK;
         a.summary->reserved = 0;                              // length of the big-record queue
-        a.recs[a.n_records].start = (uint32_t)s_run;          // closes the CSR
+        a.recs[a.n_records].start = (uint32_t)used;           // closes the CSR
     }
 }
 
@@ -459,6 +475,17 @@ __global__ void __launch_bounds__(256) k_rb_copy(const rb_args a) {
     const uint4* temp = reinterpret_cast<const uint4*>(a.temp);
     for (uint32_t i = warp; i < n; i += nwarps) {
         const uint4 t = __ldg(temp + i);                      // {src, len, rel, batch}
+        if (a.batches[t.w].status == TK_STATUS_SLOT_OVERFLOW) {
+            // did not fit the slot (k_rb_prefix): no bytes; the batch's first record carries the error
+            if (lane == 0) {
+                tk_rec_t rec;
+                rec.start = (uint32_t)a.summary->n_bytes;
+                rec.partition = a.batches[t.w].partition | (i == a.batches[t.w].rec_base ? TK_REC_OVERFLOW : TK_REC_DROPPED);
+                rec.offset = a.batches[t.w].base_offset;
+                a.recs[i] = rec;
+            }
+            continue;
+        }
         const uint32_t dst = a.batches[t.w].byte_base + t.z;
         if (lane == 0) {
             a.recs[i].start = dst;
@@ -576,8 +603,24 @@ static int rb_place_by_bounds(tk_ctx* ctx, tk_slot& s, tk_rb_unit* units, uint32
     return 0;
 }
 
+static int submit_recordbatches(tk_ctx* ctx, int slot, uint64_t n_bytes, const tk_blob_t* blobs, uint32_t n_blobs,
+                                const uint8_t* const* ext, uint32_t* n_records);
+
 extern "C" int tk_slot_submit_recordbatches(tk_ctx* ctx, int slot, uint64_t n_bytes, const tk_blob_t* blobs,
                                             uint32_t n_blobs, uint32_t* n_records) {
+    return submit_recordbatches(ctx, slot, n_bytes, blobs, n_blobs, nullptr, n_records);
+}
+
+extern "C" int tk_slot_submit_recordbatches_ext(tk_ctx* ctx, int slot, uint64_t n_bytes, const tk_blob_t* blobs,
+                                                const uint8_t* const* host_ptrs, uint32_t n_blobs,
+                                                uint32_t* n_records) {
+    TK_REQUIRE(host_ptrs || !n_blobs, "host_ptrs is null");
+    for (uint32_t k = 0; k < n_blobs; ++k) TK_REQUIRE(host_ptrs[k] || !blobs[k].length, "blob %u has no host pointer", k);
+    return submit_recordbatches(ctx, slot, n_bytes, blobs, n_blobs, host_ptrs, n_records);
+}
+
+static int submit_recordbatches(tk_ctx* ctx, int slot, uint64_t n_bytes, const tk_blob_t* blobs, uint32_t n_blobs,
+                                const uint8_t* const* ext, uint32_t* n_records) {
     TK_ENTER(ctx, slot);
     TK_REQUIRE(n_bytes <= ctx->slot_bytes, "n_bytes %llu exceeds slot_bytes %llu", (unsigned long long)n_bytes,
                (unsigned long long)ctx->slot_bytes);
@@ -590,7 +633,7 @@ extern "C" int tk_slot_submit_recordbatches(tk_ctx* ctx, int slot, uint64_t n_by
     tk_slot& s = ctx->slots[slot];
     cudaStream_t st = ctx->copy_stream;
     uint32_t n_batches = 0, n_rec = 0, n_units = 0, n_coded = 0;
-    rc = rb_walk_host(s.h_bytes, blobs, n_blobs, s.h_rb_batches, ctx->slot_records, ctx->slot_records, &n_batches,
+    rc = rb_walk_host(s.h_bytes, ext, blobs, n_blobs, s.h_rb_batches, ctx->slot_records, ctx->slot_records, &n_batches,
                       &n_rec, s.h_rb_units, (uint32_t)rb_max_units(ctx), &n_units, &n_coded);
     if (rc) return rc;
     if (n_coded) {
@@ -607,7 +650,14 @@ extern "C" int tk_slot_submit_recordbatches(tk_ctx* ctx, int slot, uint64_t n_by
         TK_CUDA(cudaStreamWaitEvent(st, s.ev_free, 0));
         TK_CUDA(cudaStreamWaitEvent(ks, s.ev_free, 0));
     }
-    if (n_bytes) TK_CUDA(cudaMemcpyAsync(s.d.raw, s.h_bytes, n_bytes, cudaMemcpyHostToDevice, st));
+    if (ext) {
+        // every blob straight out of the caller's (page-locked) buffer to its place in the device buffer
+        for (uint32_t k = 0; k < n_blobs; ++k)
+            if (blobs[k].length)
+                TK_CUDA(cudaMemcpyAsync(s.d.raw + blobs[k].start, ext[k], blobs[k].length, cudaMemcpyHostToDevice, st));
+    } else if (n_bytes) {
+        TK_CUDA(cudaMemcpyAsync(s.d.raw, s.h_bytes, n_bytes, cudaMemcpyHostToDevice, st));
+    }
     if (n_batches)
         TK_CUDA(cudaMemcpyAsync(s.d.rb_batches, s.h_rb_batches, sizeof(tk_rb_batch) * n_batches, cudaMemcpyHostToDevice, st));
     if (n_units)

@@ -51,6 +51,20 @@ def commit_barrier(local: torch.Tensor, group: Optional[dist.ProcessGroup] = Non
     return torch.stack(gathered, 0).max(dim=0).values
 
 
+def commit_barrier_min_max(local: torch.Tensor, n_max: int, group: Optional[dist.ProcessGroup] = None) -> torch.Tensor:
+    """``commit_barrier`` for a vector whose first ``n_max`` entries are commit offsets (maximum
+    over the ranks) and whose remaining entries are flags that only count when *every* rank set
+    them (minimum over the ranks): what ``auto_commit(..., commit_barrier=...)`` exchanges per batch
+    (offsets + "my stream has ended")."""
+    if not (dist.is_available() and dist.is_initialized()) or dist.get_world_size(group) == 1:
+        return local.clone()
+    world = dist.get_world_size(group)
+    gathered = [torch.empty_like(local) for _ in range(world)]
+    dist.all_gather(gathered, local, group=group)
+    stacked = torch.stack(gathered, 0)
+    return torch.cat([stacked[:, :n_max].max(dim=0).values, stacked[:, n_max:].min(dim=0).values])
+
+
 def global_commit(offsets: Dict[int, int], n_partitions: int, device=None,
                   group: Optional[dist.ProcessGroup] = None) -> Dict[int, int]:
     """Convenience: dict in, dict out (partitions never seen by any rank are omitted)."""

@@ -463,19 +463,26 @@ class SlotEngine:
             partition=part, offset=off, status=code)
 
     # ------------------------------------------------------------------ record batches
-    def submit_recordbatches(self, slot: int, n_bytes: int, blobs) -> int:
+    def submit_recordbatches(self, slot: int, n_bytes: int, blobs, host_ptrs=None) -> int:
         """Raw RecordBatch v2 bytes are in the slot's pinned buffer ``[0, n_bytes)``; ``blobs`` is a
         sequence of (start, length, dense partition, fetch_offset, offset_delta).  Returns the
         number of record entries of the slot (known from the batch headers); the copy to the
-        device and the split kernels are asynchronous."""
+        device and the split kernels are asynchronous.  With ``host_ptrs`` (one address per blob)
+        the bytes are not in the slot's buffer but wherever the consumer keeps them, and go to the
+        device straight from there (``tk_slot_submit_recordbatches_ext``)."""
         arr = (_native.TkBlob * max(len(blobs), 1))()
         for k, (start, length, part, fetch_offset, delta) in enumerate(blobs):
             b = arr[k]
             b.start, b.length, b.partition = int(start), int(length), int(part)
             b.fetch_offset, b.offset_delta = int(fetch_offset), int(delta)
         n = C.c_uint32()
-        _native.check(self.lib.tk_slot_submit_recordbatches(self.ctx, slot, C.c_uint64(int(n_bytes)), arr,
-                                                            len(blobs), C.byref(n)))
+        if host_ptrs is None:
+            _native.check(self.lib.tk_slot_submit_recordbatches(self.ctx, slot, C.c_uint64(int(n_bytes)), arr,
+                                                                len(blobs), C.byref(n)))
+        else:
+            ptrs = (C.c_void_p * max(len(blobs), 1))(*[int(p) for p in host_ptrs])
+            _native.check(self.lib.tk_slot_submit_recordbatches_ext(self.ctx, slot, C.c_uint64(int(n_bytes)), arr,
+                                                                    ptrs, len(blobs), C.byref(n)))
         return int(n.value)
 
     def recordbatch_result(self, slot: int):
@@ -559,6 +566,10 @@ def release(eng: SlotEngine):
 def clear_pool():
     if _POOL is None:
         return
+    try:
+        _clear_arenas()
+    except Exception:
+        pass
     with _POOL_LOCK:
         engines = list(_POOL.values())
         _POOL.clear()
@@ -567,3 +578,52 @@ def clear_pool():
             e.close()
         except Exception:
             pass
+
+
+# ---------------------------------------------------------------------- page-locked arenas
+# A consumer that keeps fetched bytes in long-lived buffers of its own can have them page-locked
+# once (cudaHostRegister); slots are then filled by DMA straight out of them.  The registry holds a
+# reference to every registered buffer (it must not be freed while registered) and forgets the
+# least recently used ones.
+_ARENAS: "collections.OrderedDict" = None
+ARENA_CAPACITY = 8
+
+
+def register_arena(buf) -> bool:
+    """Page-lock ``buf`` (anything with the buffer protocol / ``__array_interface__``).  Returns
+    False when the driver refuses (the copies then go through the driver's staging buffer)."""
+    global _ARENAS
+    import collections
+    arr = np.asarray(buf)
+    if arr.nbytes == 0:
+        return False
+    addr = arr.ctypes.data
+    _pool()                                  # installs the atexit hook
+    if _ARENAS is None:
+        _ARENAS = collections.OrderedDict()
+    with _POOL_LOCK:
+        if addr in _ARENAS:
+            _ARENAS.move_to_end(addr)
+            return True
+    lib = _native.load()
+    if lib.tk_host_register(C.c_void_p(addr), C.c_uint64(arr.nbytes)) != 0:
+        return False
+    drop = []
+    with _POOL_LOCK:
+        _ARENAS[addr] = arr
+        while len(_ARENAS) > ARENA_CAPACITY:
+            drop.append(_ARENAS.popitem(last=False))
+    for a, _keep in drop:
+        lib.tk_host_unregister(C.c_void_p(a))
+    return True
+
+
+def _clear_arenas():
+    if not _ARENAS:
+        return
+    lib = _native.load()
+    with _POOL_LOCK:
+        items = list(_ARENAS.items())
+        _ARENAS.clear()
+    for a, _keep in items:
+        lib.tk_host_unregister(C.c_void_p(a))

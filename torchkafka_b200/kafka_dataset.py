@@ -103,8 +103,14 @@ class KafkaDataset(IterableDataset):
     commit_all_partitions = False
     #: how records reach the GPU: "auto" (``poll_packed()`` if the consumer has it, else
     #: ``poll()``), "records", "packed", or "raw" (``poll_raw()``: RecordBatch v2 blobs of the
-    #: fetch response, CRC-checked and split on the device)
+    #: fetch response, CRC-checked and split on the device), "raw_into" (``poll_raw_into(buffer)``:
+    #: the consumer receives the response straight into the page-locked staging slot), "raw_dma"
+    #: (``poll_raw()`` blobs go to the device straight out of the consumer's own buffers,
+    #: page-locked once via ``fetch_arenas()``)
     device_input = "auto"
+    #: pin the producer threads and the pack helper's threads to the cores of the GPU's NUMA node,
+    #: and give each rank of a multi-GPU job its own share of the cores (affinity.py)
+    device_numa_affinity = True
     #: multi-worker CPU path: a worker commits the offsets of the batches the main process has
     #: *received* from it (explicit offsets, same values as single-process iteration), not its
     #: consumer's position, which runs ahead by the DataLoader's prefetched batches and would lose
@@ -121,6 +127,11 @@ class KafkaDataset(IterableDataset):
         self._explicit_offsets = None   # {TopicPartition: OffsetAndMetadata} of the last device batch
         self._pipeline = None
         self.last_pipeline_stats = {}
+        #: auto_commit(..., commit_barrier=...): the group's commit offsets after the last barrier
+        #: (int64[max_partitions], -1 = no rank has consumed that partition) and the barrier's
+        #: latencies in microseconds
+        self.group_offsets = None
+        self.commit_barrier_us = None
         if kwargs.get("_is_placeholder", False):
             self._consumer = None
             return
@@ -282,6 +293,7 @@ class KafkaDataset(IterableDataset):
             device=self.device_index, max_partitions=self.max_partitions,
             threaded=self.device_producer_thread, n_producers=self.device_producers,
             commit_all_partitions=self.commit_all_partitions, input_mode=self.device_input,
+            numa_affinity=self.device_numa_affinity,
         )
         return self._pipeline
 

@@ -17,6 +17,7 @@ from __future__ import annotations
 
 import collections
 import contextlib
+import ctypes as _ctypes
 import queue
 import sys
 import threading
@@ -26,6 +27,7 @@ from typing import Dict, Optional
 import numpy as np
 
 from . import _tkpack      # CPython helper built next to libtorchkafka_b200.so (csrc/tk_pymod.cpp)
+from . import affinity as _affinity
 from . import engine as _engine
 from .schema import PayloadError
 
@@ -49,7 +51,7 @@ class IngestPipeline:
                  slot_bytes: int = 64 << 20, n_slots: int = 3, device: Optional[int] = None,
                  max_partitions: int = 64, poll_timeout_ms: int = 100,
                  threaded: bool = True, commit_all_partitions: bool = False,
-                 n_producers: int = 2, input_mode: str = "auto"):
+                 n_producers: int = 2, input_mode: str = "auto", numa_affinity: bool = True):
         self.consumer = consumer
         self.schema = schema
         self.batch_size = int(batch_size)
@@ -82,15 +84,26 @@ class IngestPipeline:
         #   "raw"      consumer.poll_raw() -> RecordBatch v2 blobs of the fetch response, split on
         #              the GPU (additive protocol)
         #   "auto"     packed if the consumer offers it, else records
-        if input_mode not in ("auto", "records", "packed", "raw"):
+        #   "raw_into" consumer.poll_raw_into(buffer): the consumer receives the fetch response
+        #              straight into the slot's page-locked buffer -- no gather copy on the host
+        #   "raw_dma"  consumer.poll_raw() blobs are copied to the device straight out of the
+        #              consumer's own buffers (page-locked once if it offers fetch_arenas())
+        if input_mode not in ("auto", "records", "packed", "raw", "raw_into", "raw_dma"):
             raise ValueError(f"unknown input_mode {input_mode!r}")
         if input_mode == "auto":
             input_mode = "packed" if hasattr(consumer, "poll_packed") else "records"
         if input_mode == "packed" and not hasattr(consumer, "poll_packed"):
             raise TypeError("input_mode='packed' needs a consumer with poll_packed()")
-        if input_mode == "raw" and not hasattr(consumer, "poll_raw"):
-            raise TypeError("input_mode='raw' needs a consumer with poll_raw()")
+        if input_mode in ("raw", "raw_dma") and not hasattr(consumer, "poll_raw"):
+            raise TypeError(f"input_mode={input_mode!r} needs a consumer with poll_raw()")
+        if input_mode == "raw_into" and not hasattr(consumer, "poll_raw_into"):
+            raise TypeError("input_mode='raw_into' needs a consumer with poll_raw_into()")
         self.input_mode = input_mode
+        self._raw = input_mode in ("raw", "raw_into", "raw_dma")
+        if input_mode == "raw_dma" and hasattr(consumer, "fetch_arenas"):
+            for arena in consumer.fetch_arenas():
+                _engine.register_arena(arena)
+        self._raw_hold = {}                        # slot -> fetch whose memory the H2D copies read
         self._packed = input_mode == "packed"
         self._leftover = []                        # (tp, records) polled but not fitting the last slot
         self._mean_len = 0.0                       # running mean of the value size (poll sizing)
@@ -102,6 +115,13 @@ class IngestPipeline:
         self._raw_bytes_of = {}
         self._field_idx = {}                       # record type -> (value index, offset index)
         self.n_producers = max(1, int(n_producers))
+        # host threads of this rank stay on the cores of the GPU's NUMA node / on the rank's share
+        # of the cores (affinity.py); None = leave them alone
+        self._cpus = _affinity.rank_cpus(self.engine.device) if numa_affinity else None
+        if self._cpus:
+            arr = (_ctypes.c_int * len(self._cpus))(*self._cpus)
+            self.engine.lib.tk_pack_set_affinity(arr, len(self._cpus))
+            self.engine.pack_threads = max(1, min(self.engine.pack_threads, len(self._cpus)))
         self._threads = []
         self._seq = 0
         self._eof = False
@@ -199,7 +219,10 @@ class IngestPipeline:
             if self._raw_expansion > 1.0:
                 budget = max(int(eng.slot_bytes / (self._raw_expansion * 1.15)), min(eng.slot_bytes, 4096))
             with self.consumer_lock:
-                fetch = self.consumer.poll_raw(budget, eng.slot_records)
+                if self.input_mode == "raw_into":
+                    fetch = self.consumer.poll_raw_into(eng.host_views(slot)[0][:budget], eng.slot_records)
+                else:
+                    fetch = self.consumer.poll_raw(budget, eng.slot_records)
             self.stats["t_poll"] += time.perf_counter() - t0
             if fetch is not None and len(fetch.blobs):
                 break
@@ -210,15 +233,16 @@ class IngestPipeline:
             time.sleep(min(self.poll_timeout_ms, 50) / 1e3)
         topic = getattr(fetch, "topic", None) or "topic"
         nbytes = 0
-        for p, data, _fo, _delta in fetch.blobs:
-            p = int(p)
+        into = self.input_mode == "raw_into"
+        for blob in fetch.blobs:
+            p = int(blob[0])
             if p not in self._tp_of:                       # dense index == partition id (single topic)
                 if not 0 <= p < eng.n_partitions:
                     raise RuntimeError(f"partition {p} outside [0, max_partitions={eng.n_partitions})")
                 tp = self._tp_cls(topic, p)
                 self._tp_of[p] = tp
                 self._dense_of[tp] = p
-            nbytes += len(data)
+            nbytes += int(blob[2]) if into else len(blob[1])
         if nbytes > eng.slot_bytes:
             raise ValueError(f"a fetch of {nbytes} bytes exceeds the slot size ({eng.slot_bytes} bytes)")
         # n is not known before the device has split the batches: report blobs, fix up in _pack_raw
@@ -230,6 +254,27 @@ class IngestPipeline:
         eng = self.engine
         t0 = time.perf_counter()
         k = len(fetch.blobs)
+        if self.input_mode == "raw_into":
+            # the bytes are already in the slot's pinned buffer: (partition, start, length, fetch offset, delta)
+            total = sum(int(b[2]) for b in fetch.blobs)
+            n = eng.submit_recordbatches(slot, total, [(int(b[1]), int(b[2]), int(b[0]), int(b[3]), int(b[4]))
+                                                       for b in fetch.blobs])
+            self.stats["t_pack"] += time.perf_counter() - t0
+            self._raw_bytes_of[slot] = total
+            return n, total
+        if self.input_mode == "raw_dma":
+            lens = [len(b[1]) for b in fetch.blobs]
+            starts = [0]
+            for ln in lens:
+                starts.append(starts[-1] + ln)
+            self._raw_hold[slot] = fetch           # the copies read the consumer's memory: keep it alive
+            n = eng.submit_recordbatches(
+                slot, starts[k], [(starts[i], lens[i], int(b[0]), int(b[2]), int(b[3]))
+                                  for i, b in enumerate(fetch.blobs)],
+                host_ptrs=[np.asarray(b[1]).ctypes.data for b in fetch.blobs])
+            self.stats["t_pack"] += time.perf_counter() - t0
+            self._raw_bytes_of[slot] = starts[k]
+            return n, starts[k]
         ptrs = np.fromiter((b[1].ctypes.data for b in fetch.blobs), dtype=np.uint64, count=k)
         lens = np.fromiter((len(b[1]) for b in fetch.blobs), dtype=np.uint32, count=k)
         parts = np.fromiter((int(b[0]) for b in fetch.blobs), dtype=np.int32, count=k)
@@ -404,10 +449,11 @@ class IngestPipeline:
     def _produce(self, free_q, deliver):
         """Producer thread.  Gather (consumer calls, serialised, defines the slot order) then
         pack + submit (parallel across producer threads)."""
-        raw = self.input_mode == "raw"
+        raw = self._raw
         gather = self._gather_raw if raw else self._gather_packed if self._packed else self._gather_poll
         pack = self._pack_raw if raw else self._pack_packed if self._packed else self._pack_poll
         scratch = self._new_scratch() if self.input_mode == "records" else None
+        _affinity.pin_current_thread(self._cpus)
         try:
             while not self._stop.is_set():
                 slot = free_q.get()
@@ -445,7 +491,7 @@ class IngestPipeline:
         self._seq = 0
         self._eof = False
         if not self.threaded:
-            raw = self.input_mode == "raw"
+            raw = self._raw
             gather = self._gather_raw if raw else self._gather_packed if self._packed else self._gather_poll
             pack = self._pack_raw if raw else self._pack_packed if self._packed else self._pack_poll
             scratch = self._new_scratch() if self.input_mode == "records" else None
@@ -523,8 +569,12 @@ class IngestPipeline:
             t0 = time.perf_counter()
             res = eng.result(item.slot)
             self.stats["t_wait_result"] += time.perf_counter() - t0
-            if self.input_mode == "raw":
+            if self._raw:
                 self._note_raw_expansion(item.slot, res.n_records)
+                self._raw_hold.pop(item.slot, None)
+            # the error report reads the slot's device buffers: build it before the slot goes back
+            # to the producers, whose next submit overwrites them
+            error = self._error(item, res) if res.n_errors else None
             release(item.slot)         # pinned memory is reusable: H2D and kernels are done
             eng.publish(item.out)      # caller's stream waits for this slot only
             self.stats["records"] += res.n_records
@@ -543,10 +593,10 @@ class IngestPipeline:
                 self.stats["batches"] += good
                 yield from zip(views[:good], maps)
                 if good < nc:
-                    raise self._error(item, res)
+                    raise error
             if err_rec is not None:
                 # bad record sits in the still-open batch: it surfaces with that batch
-                raise self._error(item, res)
+                raise error
             tail_lmax = int(res.batch_lmax[res.n_closed])
             open_lmax = max(open_lmax, tail_lmax) if res.n_closed == 0 else tail_lmax
             last = (item, res)

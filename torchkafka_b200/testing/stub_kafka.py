@@ -364,6 +364,32 @@ class KafkaConsumer:
         self._cursor = cursor
         return RawFetch(blobs, self._log.topic)
 
+    def poll_raw_into(self, buffer, max_records: int):
+        """``poll_raw`` that *receives into the caller's buffer* (additive protocol): the next
+        fetch response's RecordBatch v2 bytes are written back to back into ``buffer`` (a writable
+        uint8 array, e.g. a page-locked staging slot), at most ``len(buffer)`` bytes.  Returns a
+        ``RawFetch`` whose blobs are ``(partition, start, length, fetch_offset, offset_delta)`` with
+        ``start`` an offset into ``buffer``, or ``None`` at the end of the log.  For a network
+        client this is ``recv_into``; the stub copies from its in-memory log segment."""
+        fetch = self.poll_raw(len(buffer), max_records)
+        if fetch is None:
+            return None
+        out = np.asarray(buffer)
+        pos = 0
+        blobs = []
+        for p, data, fetch_offset, delta in fetch.blobs:
+            n = len(data)
+            out[pos:pos + n] = data
+            blobs.append((p, pos, n, fetch_offset, delta))
+            pos += n
+        return RawFetch(blobs, fetch.topic)
+
+    def fetch_arenas(self):
+        """Long-lived buffers that every blob returned by ``poll_raw`` is a view of (additive
+        protocol): a caller may page-lock them once and DMA out of them.  The stub's arena is the
+        encoded log segment."""
+        return [self._log.encoded(self._raw_batch_bytes, self._raw_codec).data]
+
     # -- offsets -------------------------------------------------------------
     def position(self, tp):
         return self._positions.get(tp.partition)

@@ -7,7 +7,9 @@ import numpy as np
 import pytest
 import torch
 
-from helpers import assert_same, run_gpu, run_oracle
+from helpers import assert_same, bit_equal, make_dataset, run_gpu, run_oracle
+from torchkafka_b200 import KafkaDataset, auto_commit
+from torchkafka_b200.testing import stub_kafka as sk
 from torchkafka_b200.schema import ImageU8, JsonArray, PayloadError, RawBytes, TokenList
 from torchkafka_b200.testing import synthetic as syn
 from torchkafka_b200.testing.stub_kafka import RecordLog
@@ -468,3 +470,111 @@ def test_nested_arrays_of_another_shape_raise(bad):
     with pytest.raises(PayloadError) as ei:
         run_gpu(log, sc, 2)
     assert (ei.value.partition, ei.value.offset) == (1, 1)
+
+
+# ---------------------------------------------------------------- leaving the loop early, slow topics
+@pytest.mark.parametrize("mode,packed", [("records", False), ("packed", True), ("raw", True), ("raw_dma", True)])
+def test_break_then_iterate_again_continues_behind_the_last_delivered_batch(mode, packed):
+    """The pipeline polls ahead of what it has delivered.  Leaving the loop must not lose that
+    read-ahead: the consumer is sought back, and a second iteration delivers exactly the batches
+    the oracle delivers after the one the first iteration stopped at."""
+    from torch.utils.data import DataLoader
+    from helpers import to_cpu
+    log = syn.make_log(2, 5000, seed=77, partitions=8, layout="chunked", chunk=40)
+    schema = JsonArray(torch.float32, max_len=256, min_size=32)
+    ds = make_dataset(log, schema, slot_bytes=200_000, use_packed=packed, device_input=mode,
+                      consumer_kwargs={"raw_batch_bytes": 8192})
+    loader = DataLoader(ds, batch_size=64)
+    got = []
+    for k, batch in enumerate(auto_commit(loader)):
+        got.append(to_cpu(batch))
+        if k == 6:
+            break                                   # batch 6 delivered, never committed
+    n_commits = len(ds._consumer.committed_log)
+    assert n_commits == 6
+    for batch in auto_commit(loader):
+        got.append(to_cpu(batch))
+    want = run_oracle(log, schema, 64)
+    assert len(got) == len(want)
+    for k, (g, (w, _)) in enumerate(zip(got, want)):
+        assert bit_equal(g[0], w[0]) and torch.equal(g[1], w[1]) and torch.equal(g[2], w[2]), f"batch {k}"
+    # the group's committed offsets end where the oracle's do
+    assert dict(ds._consumer.committed_log[-1]) == want[-1][1]
+    # and the first commit of the second iteration covered the batch that was left uncommitted
+    assert dict(ds._consumer.committed_log[n_commits]) == want[7][1]
+    ds.close()
+
+
+def test_trickling_topic_is_delivered_within_the_latency_bound():
+    """A topic that always has a few more records never lets poll() come back empty and never fills
+    a slot: with device_max_latency_ms the partly filled slot is shipped after the bound."""
+    import time
+    log = syn.make_log(1, 600, seed=78, partitions=4, layout="chunked", chunk=5)
+
+    class Trickle(sk.PollOnlyConsumer):
+        def poll(self, timeout_ms=0, max_records=None, update_offsets=True):
+            time.sleep(0.002)
+            return super().poll(timeout_ms, min(max_records or 3, 3), update_offsets)
+
+    class DS(KafkaDataset):
+        payload_schema = JsonArray(torch.float32, fixed_len=8)
+        device_slot_bytes = 1 << 20
+        device_max_latency_ms = 40
+
+        @classmethod
+        def new_consumer(cls, *a, **k):
+            k.pop("enable_auto_commit", None)
+            return Trickle(*a, log=log, **k)
+
+    ds = DS("topic", group_id="g")
+    t0 = time.perf_counter()
+    first_at = None
+    rows = []
+    for batch in ds.device_batches(4):
+        if first_at is None:
+            first_at = time.perf_counter() - t0
+        rows.append(batch.cpu())
+    total = time.perf_counter() - t0
+    stats = ds.last_pipeline_stats
+    ds.close()
+    want = run_oracle(log, JsonArray(torch.float32, fixed_len=8), 4)
+    assert bit_equal(torch.cat(rows), torch.cat([w for w, _ in want]))
+    # ~0.4 s of trickling in ~40 ms slices: several slots, and the first batch long before the end
+    assert stats["slots"] >= 4, stats
+    assert first_at < 0.5 * total, (first_at, total)
+
+
+def test_short_records_under_a_wide_schema_stay_inside_the_output_budget():
+    """TokenList(max_len=2048) over ten-token records: one row per record at full width would be
+    gigabytes per slot; the slot is cut by the output-byte budget instead."""
+    import random
+    rng = random.Random(5)
+    n = 60000
+    vals = [json.dumps([rng.randrange(0, 128000) for _ in range(rng.randint(1, 10))]).encode() for _ in range(n)]
+    log = RecordLog(vals, (np.arange(n) % 8).astype(np.int32), np.arange(n) // 8)
+    schema = TokenList(torch.int32, max_len=2048)
+    torch.cuda.synchronize()
+    torch.cuda.empty_cache()
+    torch.cuda.reset_peak_memory_stats()
+    base = torch.cuda.memory_allocated()
+    budget = 64 << 20
+    ds = make_dataset(log, schema, slot_bytes=64 << 20, device_output_bytes=budget)
+    rows, lens = [], []
+    for batch in ds.device_batches(512):
+        assert batch.input_ids.shape[1] <= 10          # the view is as wide as the batch's longest record
+        rows.append(batch.input_ids.cpu())
+        lens.append(batch.lengths.cpu())
+    stats = ds.last_pipeline_stats
+    ds.close()
+    peak = torch.cuda.max_memory_allocated() - base
+    # slots in flight (default 3 + producers) times the budget, never "records x max_len"
+    assert peak <= 8 * budget, peak
+    assert stats["slots"] >= n * 10244 // budget       # the budget, not the byte size, cut the slots
+    got_lens = torch.cat(lens)
+    assert got_lens.tolist() == [v.count(b",") + 1 for v in vals]
+    k = 0
+    for r, ln in zip(rows, lens):
+        for row, m in zip(r.tolist(), ln.tolist()):
+            assert row[:m] == json.loads(vals[k]) and not any(row[m:])
+            k += 1
+    assert k == n

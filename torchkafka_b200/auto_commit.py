@@ -96,9 +96,15 @@ def _device_path(dataloader: DataLoader, commit_barrier=None):
     if dataloader.batch_size is None:
         raise ValueError("auto_commit needs a DataLoader with a batch_size for schema datasets.")
     if commit_barrier is None or commit_barrier is False:
-        for batch in dataset.device_batches(dataloader.batch_size, dataloader.drop_last):
-            yield batch
-            dataset.commit()
+        # Per slot, not per batch: the pipeline hands over the lists of a slot's batches and commit
+        # maps; per batch this loop does one yield and one commit (with batch_size=4 the depth of
+        # the generator chain is what the host spends its time on).
+        for views, maps, pipe in dataset._device_slot_batches(dataloader.batch_size, dataloader.drop_last):  # pylint: disable=protected-access
+            for j in range(len(views)):
+                pipe.delivered_index = j
+                dataset._note_offsets(maps[j])          # pylint: disable=protected-access
+                yield views[j]
+                dataset.commit()
         return
     barrier = _CommitBarrier(dataset, commit_barrier)
     for batch in dataset.device_batches(dataloader.batch_size, dataloader.drop_last):

@@ -32,6 +32,8 @@ REC_DTYPE = np.dtype([("start", "<u4"), ("partition", "<i4"), ("offset", "<i8")]
 
 #: a slot never closes more batches than this (bounds the commit matrix)
 MAX_BATCHES_CAP = 16384
+#: default budget for the output tensors of one slot (rows of every plane)
+DEFAULT_OUTPUT_BYTES = 2 << 30
 #: kernels launched per slot by ``process``: carry rows, scan, plan (compaction + commit maxima,
 #: one kernel), decode / collate (one kernel), commit running max (one block, beside the decode)
 LAUNCHES_PER_SLOT_JSON = 5
@@ -80,7 +82,8 @@ class SlotEngine:
 
     def __init__(self, schema, batch_size: int, slot_bytes: int = 64 << 20,
                  slot_records: Optional[int] = None, n_slots: int = 3,
-                 device: Optional[int] = None, n_partitions: int = 64):
+                 device: Optional[int] = None, n_partitions: int = 64,
+                 output_bytes: Optional[int] = None):
         if not torch.cuda.is_available():
             raise RuntimeError(
                 "payload_schema datasets need a CUDA device (B200); there is no CPU fallback."
@@ -105,7 +108,13 @@ class SlotEngine:
         else:
             auto_records = max(1, self.slot_bytes // 48)
         cap = MAX_BATCHES_CAP * self.batch_size
-        self.slot_records = int(min(slot_records or auto_records, cap, 1 << 22))
+        # Output tensors hold one row per record of the slot (kept or not) plus batch_size head
+        # rows, each as wide as the schema allows: short records under a wide schema
+        # (TokenList(max_len=2048) over ten-token records) would otherwise ask for gigabytes per
+        # slot.  The slot is therefore also cut by an output-byte budget.
+        self.output_bytes = int(output_bytes) if output_bytes else DEFAULT_OUTPUT_BYTES
+        by_output = max(1, self.output_bytes // max(self.row_bytes(schema), 1) - self.batch_size)
+        self.slot_records = int(min(slot_records or auto_records, cap, 1 << 22, by_output))
         self.max_batches = (self.slot_records + self.batch_size - 1) // self.batch_size + 1
         ctx = C.c_void_p()
         _native.check(self.lib.tk_ctx_create(self.device, self.slot_bytes, self.slot_records,
@@ -148,6 +157,22 @@ class SlotEngine:
         #: are left for the producer (GIL) and the consuming thread.  Measured on the 16-core
         #: B200 host: 7 threads 61 GB/s, 14 threads 92 GB/s (benchmarks/pack_bandwidth.py).
         self.pack_threads = int(os.environ.get("TK_PACK_THREADS", 0)) or max(1, min(16, cores - 2))
+
+    @staticmethod
+    def row_bytes(sc) -> int:
+        """Bytes one record's row takes in the output tensors (all planes)."""
+        if isinstance(sc, JsonArray):
+            width = sc.max_len * torch.empty((), dtype=sc.dtype).element_size()
+            return width + (4 + sc.max_len if sc.fixed_len is None else 0)
+        if isinstance(sc, JsonObject):
+            return len(sc.fields) * torch.empty((), dtype=sc.dtype).element_size()
+        if isinstance(sc, JsonNested):
+            return sc.elements * torch.empty((), dtype=sc.dtype).element_size()
+        if isinstance(sc, ImageU8):
+            return sc.record_bytes * 2
+        if isinstance(sc, (RawBytes, StructBytes)):
+            return sc.record_bytes
+        raise TypeError(f"unsupported schema {sc!r}")
 
     # ------------------------------------------------------------------ plumbing
     def _stream(self):
@@ -517,10 +542,10 @@ def _pool():
 
 
 def acquire(schema, batch_size: int, slot_bytes: int, n_slots: int, device: Optional[int],
-            n_partitions: int) -> SlotEngine:
+            n_partitions: int, output_bytes: Optional[int] = None) -> SlotEngine:
     """An engine of this geometry: a pooled one if there is one, else a new one."""
     dev = torch.cuda.current_device() if (device is None and torch.cuda.is_available()) else device
-    key = (dev, schema, int(batch_size), int(slot_bytes), int(n_slots), int(n_partitions))
+    key = (dev, schema, int(batch_size), int(slot_bytes), int(n_slots), int(n_partitions), output_bytes)
     pool = _pool()
     try:
         with _POOL_LOCK:
@@ -529,7 +554,7 @@ def acquire(schema, batch_size: int, slot_bytes: int, n_slots: int, device: Opti
         eng, key = None, None
     if eng is None:
         eng = SlotEngine(schema, batch_size, slot_bytes=slot_bytes, n_slots=n_slots, device=device,
-                         n_partitions=n_partitions)
+                         n_partitions=n_partitions, output_bytes=output_bytes)
     eng.pool_key = key
     return eng
 

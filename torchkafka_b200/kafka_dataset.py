@@ -111,6 +111,14 @@ class KafkaDataset(IterableDataset):
     #: pin the producer threads and the pack helper's threads to the cores of the GPU's NUMA node,
     #: and give each rank of a multi-GPU job its own share of the cores (affinity.py)
     device_numa_affinity = True
+    #: ship a partly filled staging slot once its first record has waited this many milliseconds
+    #: (``poll()`` input): bounds the delivery latency on a slow topic, where a slot would otherwise
+    #: go out only when full or when ``poll()`` comes back empty.  None = no time bound.
+    device_max_latency_ms = None
+    #: budget for the output tensors of one staging slot (default 2 GiB).  Rows are as wide as the
+    #: schema allows (``max_len``) and there is one per record, so a slot of very short records
+    #: under a wide schema is cut by this budget rather than by ``device_slot_bytes``.
+    device_output_bytes = None
     #: multi-worker CPU path: a worker commits the offsets of the batches the main process has
     #: *received* from it (explicit offsets, same values as single-process iteration), not its
     #: consumer's position, which runs ahead by the DataLoader's prefetched batches and would lose
@@ -126,6 +134,7 @@ class KafkaDataset(IterableDataset):
         self._snapshot_base = 0         # worker: batches whose snapshots were already dropped
         self._explicit_offsets = None   # {TopicPartition: OffsetAndMetadata} of the last device batch
         self._pipeline = None
+        #: counters of the last GPU-path iteration (``ingest_stats()`` reads the running one)
         self.last_pipeline_stats = {}
         #: auto_commit(..., commit_barrier=...): the group's commit offsets after the last barrier
         #: (int64[max_partitions], -1 = no rank has consumed that partition) and the barrier's
@@ -293,7 +302,8 @@ class KafkaDataset(IterableDataset):
             device=self.device_index, max_partitions=self.max_partitions,
             threaded=self.device_producer_thread, n_producers=self.device_producers,
             commit_all_partitions=self.commit_all_partitions, input_mode=self.device_input,
-            numa_affinity=self.device_numa_affinity,
+            numa_affinity=self.device_numa_affinity, max_latency_ms=self.device_max_latency_ms,
+            output_bytes=self.device_output_bytes,
         )
         return self._pipeline
 
@@ -308,16 +318,55 @@ class KafkaDataset(IterableDataset):
         if self.payload_schema is None:
             raise RuntimeError("device_batches() needs a payload_schema.")
         pipe = self._open_pipeline(int(batch_size), bool(drop_last))
-        self._explicit_offsets = None
-        try:
+        # (offsets of batches that were delivered but never committed -- the loop was left before
+        # the commit -- stay pending: they go out with the next commit)
+        if self._explicit_offsets is None:
             self._explicit_offsets = {}
+        try:
             for batch, offsets in pipe:
                 # offsets list the partitions that moved with this batch; merge them so that a
                 # caller who commits every few batches still commits everything consumed so far
-                self._explicit_offsets.update(offsets)
+                self._note_offsets(offsets)
                 yield batch
         finally:
-            self.last_pipeline_stats = dict(pipe.stats)
+            self.last_pipeline_stats = pipe.snapshot_stats()
+            pipe.close()
+            if self._pipeline is pipe:
+                self._pipeline = None
+
+    def ingest_stats(self):
+        """Counters of the GPU path (running iteration, else the last one): ``records``, ``kept``,
+        ``batches``, ``slots``, ``bytes`` (over the host-device link), ``decode_errors``,
+        ``errors_by_status``, ``seconds``, ``records_per_s``, ``h2d_GBps`` and the host-side
+        stage times ``t_poll`` / ``t_harvest`` / ``t_pack`` / ``t_launch`` / ``t_wait_slot`` /
+        ``t_wait_result`` (seconds, summed over the producer threads)."""
+        pipe = self._pipeline
+        return pipe.snapshot_stats() if pipe is not None else dict(self.last_pipeline_stats)
+
+    def _note_offsets(self, offsets):
+        """Offsets of the batch about to be delivered; they go out with the next commit."""
+        pending = self._explicit_offsets
+        if pending:
+            pending.update(offsets)
+        else:
+            self._explicit_offsets = offsets
+
+    def _device_slot_batches(self, batch_size: int, drop_last: bool = False):
+        """``device_batches`` one staging slot at a time: (list of batches, list of their commit
+        maps, pipeline).  The caller sets ``pipeline.delivered_index`` and calls ``_note_offsets``
+        per batch (``auto_commit`` does)."""
+        if self._consumer is None:
+            raise RuntimeError("Consumer is not initialized.")
+        if self.payload_schema is None:
+            raise RuntimeError("device_batches() needs a payload_schema.")
+        pipe = self._open_pipeline(int(batch_size), bool(drop_last))
+        if self._explicit_offsets is None:
+            self._explicit_offsets = {}
+        try:
+            for views, maps in pipe.slot_batches():
+                yield views, maps, pipe
+        finally:
+            self.last_pipeline_stats = pipe.snapshot_stats()
             pipe.close()
             if self._pipeline is pipe:
                 self._pipeline = None

@@ -42,8 +42,8 @@ class _Pending:
         self.slot = slot
         self.n = n
         self.out = out
-        self.partitions = partitions
-        self.offsets = offsets
+        self.partitions = partitions     # host copy of the record coordinates; raw slots: the
+        self.offsets = offsets           # fetch's {dense partition: fetch offset} and None
 
 
 class IngestPipeline:
@@ -51,14 +51,15 @@ class IngestPipeline:
                  slot_bytes: int = 64 << 20, n_slots: int = 3, device: Optional[int] = None,
                  max_partitions: int = 64, poll_timeout_ms: int = 100,
                  threaded: bool = True, commit_all_partitions: bool = False,
-                 n_producers: int = 2, input_mode: str = "auto", numa_affinity: bool = True):
+                 n_producers: int = 2, input_mode: str = "auto", numa_affinity: bool = True,
+                 max_latency_ms: Optional[float] = None, output_bytes: Optional[int] = None):
         self.consumer = consumer
         self.schema = schema
         self.batch_size = int(batch_size)
         self.drop_last = bool(drop_last)
         self.engine = _engine.acquire(schema, batch_size, slot_bytes=slot_bytes,
                                       n_slots=max(n_slots, 2 + (int(n_producers) if threaded else 0)),
-                                      device=device, n_partitions=max_partitions)
+                                      device=device, n_partitions=max_partitions, output_bytes=output_bytes)
         self.poll_timeout_ms = poll_timeout_ms
         # kafka-python ends `for record in consumer` after consumer_timeout_ms without a record
         # (default: never).  The GPU path follows the same setting; the in-memory stub
@@ -128,16 +129,32 @@ class IngestPipeline:
         self._last_column = None
         self.commit_all_partitions = bool(commit_all_partitions)
         self._closed = False
+        #: a partly filled slot is shipped once its first record has waited this long (records
+        #: mode; the other protocols ship one fetch per slot anyway).  None = only when the
+        #: stream pauses or the slot is full.
+        self.max_latency_s = None if max_latency_ms is None else float(max_latency_ms) / 1e3
+        # what an early close() needs to seek the consumer back (see _rewind)
+        self._iterating = False
+        self._base_delivered = None                # (commit columns of a slot, index of its last yielded batch)
+        self._base_tails = []                      # [(_Pending, first record not in a yielded batch)], in order
+        self._cur = None                           # (_Pending, result, commit columns) of the slot being handed out
+        self.delivered_index = -1                  # position of the batch being yielded within that slot
+        self._pending = collections.deque()
+        self._ready = {}
         self._stop = threading.Event()
         self._free_q = None
         self._saved_switch = None
         self.stats = collections.Counter()
+        self.errors_by_status = collections.Counter()   # status code -> slots whose first bad record had it
+        self._t_start = self._t_end = None
 
     # ------------------------------------------------------------------ lifecycle
     def close(self):
         if self._closed:
             return
         self._closed = True
+        if self._t_start is not None and self._t_end is None:
+            self._t_end = time.perf_counter()
         self._stop.set()
         alive = []
         if self._saved_switch is not None:
@@ -152,11 +169,89 @@ class IngestPipeline:
                 t.join(timeout=30)
             alive = list(self._threads)
             self._threads = []
+        if self._iterating and not any(t.is_alive() for t in alive):
+            self._iterating = False
+            try:
+                self._rewind()
+            except Exception as exc:  # pragma: no cover - depends on the consumer
+                import logging
+                logging.getLogger(__name__).error("Could not seek the consumer back to the last delivered batch: %s", exc)
         # (a producer that did not stop in time may still touch its slot: such an engine is not reused)
         if any(t.is_alive() for t in alive):
             self.engine.close()
         else:
             _engine.release(self.engine)
+
+    def snapshot_stats(self) -> dict:
+        """Counters so far plus the derived rates (``KafkaDataset.ingest_stats``)."""
+        out = dict(self.stats)
+        t0 = getattr(self, "_t_start", None)
+        if t0 is not None:
+            dt = max((self._t_end or time.perf_counter()) - t0, 1e-9)
+            out["seconds"] = dt
+            out["records_per_s"] = out.get("records", 0) / dt
+            out["h2d_GBps"] = out.get("bytes", 0) / dt / 1e9
+        out["errors_by_status"] = dict(self.errors_by_status)
+        return out
+
+    def _rewind(self):
+        """Early close (``break`` out of the loop, an exception): the producers have polled ahead of
+        what was delivered.  Seek every partition back to the position right after the last
+        yielded batch, so that iterating the dataset again continues there -- the reference,
+        which never reads ahead, behaves like that by construction (``src/kafka_dataset.py:156``).
+        Needs ``consumer.seek(TopicPartition, offset)`` (kafka-python has it)."""
+        seek = getattr(self.consumer, "seek", None)
+        if seek is None:
+            return
+        target = {}
+        delivered, tails = self._base_delivered, list(self._base_tails)
+        if self._cur is not None:
+            item, res, cols = self._cur
+            if self.delivered_index >= 0:
+                delivered = (cols, self.delivered_index)
+                tails = [(item, int(res.batch_end[self.delivered_index]) + 1)]
+            else:
+                tails.append((item, 0))
+        if delivered is not None:
+            cols, j = delivered
+            col = cols[j]
+            for p in np.flatnonzero(col >= 0).tolist():
+                target[p] = int(col[p])
+
+        def first_seen(parts, offs, start=0):
+            """First offset of every partition not delivered yet, in consumption order."""
+            if isinstance(parts, dict):                      # raw slot: {partition: fetch offset}
+                for p, off in parts.items():
+                    target.setdefault(int(p), int(off))
+                return
+            if parts is None or start >= len(parts):
+                return
+            sub = np.asarray(parts[start:])
+            uniq, idx = np.unique(sub, return_index=True)
+            for p, i in zip(uniq.tolist(), idx.tolist()):
+                target.setdefault(int(p), int(offs[start + i]))
+
+        for item, k0 in tails:
+            first_seen(item.partitions, item.offsets, k0)
+        for item in self._pending:
+            first_seen(item.partitions, item.offsets)
+        for seq in sorted(self._ready):
+            it = self._ready[seq]
+            if it is not None:
+                first_seen(it[3], it[4])
+        for tp, recs in self._leftover:
+            if recs:
+                r = recs[0]
+                target.setdefault(self._dense(tp), int(getattr(r, "offset", None) if not isinstance(r, tuple)
+                                                       else r[self._indices(r)[1]]))
+        with self.consumer_lock:
+            for p, off in target.items():
+                tp = self._tp_of.get(p)
+                if tp is not None:
+                    seek(tp, off)
+        self._pending = collections.deque()
+        self._ready = {}
+        self._leftover = []
 
     # ------------------------------------------------------------------ host side: poll + pack
     def _dense(self, tp) -> int:
@@ -289,6 +384,14 @@ class IngestPipeline:
         self._raw_bytes_of[slot] = int(starts[k])
         return n, int(starts[k])
 
+    @staticmethod
+    def _fetch_offsets(fetch, into: bool):
+        """{dense partition: fetch offset} of a raw fetch (first blob of every partition)."""
+        out = {}
+        for b in fetch.blobs:
+            out.setdefault(int(b[0]), int(b[3] if into else b[2]))
+        return out
+
     def _note_raw_expansion(self, slot: int, n_records: int):
         """Feedback for the fetch budget (the split of this slot is done: no waiting here)."""
         raw = self._raw_bytes_of.get(slot, 0)
@@ -328,7 +431,11 @@ class IngestPipeline:
         idle_since = None
         hold = []                       # keeps the record objects (and their bytes) alive until packed
         full = False
+        t_first = None                  # when the slot received its first record
         while not full and n < eng.slot_records:
+            if t_first is not None and self.max_latency_s is not None and \
+                    time.monotonic() - t_first >= self.max_latency_s:
+                break                   # a trickling topic: ship what is there
             if self._leftover:
                 items, self._leftover = self._leftover, []
             else:
@@ -338,8 +445,12 @@ class IngestPipeline:
                 want = eng.slot_records - n
                 if self._mean_len:
                     want = min(want, int((eng.slot_bytes - nbytes) / self._mean_len * 1.02) + 16)
+                timeout_ms = self.poll_timeout_ms
+                if t_first is not None and self.max_latency_s is not None:
+                    left = self.max_latency_s - (time.monotonic() - t_first)
+                    timeout_ms = max(0, min(timeout_ms, int(left * 1e3)))
                 with self.consumer_lock:
-                    polled = self.consumer.poll(timeout_ms=self.poll_timeout_ms,
+                    polled = self.consumer.poll(timeout_ms=timeout_ms,
                                                 max_records=max(1, min(want, 1 << 16)))
                 self.stats["t_poll"] += time.perf_counter() - t0
                 if not polled:
@@ -369,6 +480,8 @@ class IngestPipeline:
                 hold.append(keep)
             n += taken
             nbytes += tot
+            if taken and t_first is None:
+                t_first = time.monotonic()
             if taken:
                 m = tot / taken
                 self._mean_len = m if not self._mean_len else 0.75 * self._mean_len + 0.25 * m
@@ -399,7 +512,8 @@ class IngestPipeline:
 
     # ------------------------------------------------------------------ iteration
     def _error(self, item, res) -> PayloadError:
-        err = self.engine.error_for(item.slot, res, item.partitions, item.offsets)
+        coords = (item.partitions, item.offsets) if item.offsets is not None else (None, None)
+        err = self.engine.error_for(item.slot, res, *coords)
         tp = self._tp_of.get(err.partition)
         if tp is not None:                      # dense index -> the consumer's partition id
             err.partition = getattr(tp, "partition", err.partition)
@@ -473,8 +587,9 @@ class IngestPipeline:
                     return
                 if raw:
                     # the device splits the batches: record coordinates stay there
+                    fo = self._fetch_offsets(token, self.input_mode == "raw_into")
                     n, nbytes = pack(slot, scratch, n, token)
-                    deliver(seq, (slot, n, nbytes, None, None))
+                    deliver(seq, (slot, n, nbytes, fo, None))
                     continue
                 parts, offs = pack(slot, scratch, n, token)
                 self.engine.submit(slot, n, nbytes)
@@ -504,8 +619,9 @@ class IngestPipeline:
                     if n == 0:
                         return
                     if raw:
+                        fo = self._fetch_offsets(token, self.input_mode == "raw_into")
                         n, nbytes = pack(slot, scratch, n, token)
-                        yield slot, n, nbytes, None, None
+                        yield slot, n, nbytes, fo, None
                         continue
                     parts, offs = pack(slot, scratch, n, token)
                     eng.submit(slot, n, nbytes)
@@ -518,7 +634,7 @@ class IngestPipeline:
         self._free_q = free_q
         self._cv = threading.Condition()
         self._failure = None
-        ready = {}
+        ready = self._ready = {}
 
         def deliver(seq, item):
             with self._cv:
@@ -548,10 +664,29 @@ class IngestPipeline:
         return gen(), free_q.put
 
     def __iter__(self):
+        """(batch, offsets) pairs; see ``slot_batches`` for the per-slot form."""
+        for views, maps in self.slot_batches():
+            for j in range(len(views)):
+                self.delivered_index = j
+                yield views[j], maps[j]
+
+    def slot_batches(self):
+        """Per drained slot, the list of batches it closed and the list of their commit maps
+        (same length), in order.  A caller that hands the batches out one by one sets
+        ``delivered_index`` to the position of the batch it is about to yield, so that an early
+        ``close()`` knows where to seek the consumer back to (``__iter__`` does exactly that;
+        ``auto_commit`` uses this form directly: with small batches the cost per batch is the
+        depth of the generator chain)."""
         eng = self.engine
         B = self.batch_size
         self._leftover = []
-        pending = collections.deque()
+        pending = self._pending = collections.deque()
+        self._base_delivered = None
+        self._base_tails = []
+        self._cur = None
+        self.delivered_index = -1
+        self._iterating = True
+        self._t_start, self._t_end = time.perf_counter(), None
         depth = 1 if self.threaded else max(1, eng.n_slots - 1)
         prev_slot, prev_out = None, None
         open_lmax = 0                  # longest record among the rows of the open batch
@@ -579,6 +714,9 @@ class IngestPipeline:
             eng.publish(item.out)      # caller's stream waits for this slot only
             self.stats["records"] += res.n_records
             self.stats["kept"] += res.n_kept
+            if res.n_errors:
+                self.stats["decode_errors"] += res.n_errors
+                self.errors_by_status[int(error.status)] += 1
             err_rec = res.first_error_rec if res.n_errors else None
             first = B - res.carry_in
             nc = res.n_closed
@@ -591,12 +729,23 @@ class IngestPipeline:
                 good = nc if err_rec is None else int(np.searchsorted(res.batch_end[:nc], err_rec, side="left"))
                 maps = self._offsets_maps(commit_cols[:good])
                 self.stats["batches"] += good
-                yield from zip(views[:good], maps)
+                # (what an early close() seeks back to: the positions after the last yielded batch)
+                self._cur = (item, res, commit_cols)
+                self.delivered_index = -1
+                if good:
+                    yield views[:good] if good < nc else views, maps
+                    self._base_delivered = (commit_cols, good - 1)
+                    self._base_tails = [(item, int(res.batch_end[good - 1]) + 1)]
+                else:
+                    self._base_tails.append((item, 0))
+                self._cur = None
                 if good < nc:
                     raise error
             if err_rec is not None:
                 # bad record sits in the still-open batch: it surfaces with that batch
                 raise error
+            if not nc:
+                self._base_tails.append((item, 0))      # all of it sits in the still-open batch
             tail_lmax = int(res.batch_lmax[res.n_closed])
             open_lmax = max(open_lmax, tail_lmax) if res.n_closed == 0 else tail_lmax
             last = (item, res)
@@ -623,4 +772,6 @@ class IngestPipeline:
                 first = B + res.n_kept - res.carry_out
                 batch = eng.batch_view(item.out, first, res.carry_out, open_lmax)
                 self.stats["batches"] += 1
-                yield batch, self._offsets_map(np.ascontiguousarray(res.commit[:, res.n_closed]))
+                self._iterating = False         # everything the consumer handed out is delivered
+                yield [batch], [self._offsets_map(np.ascontiguousarray(res.commit[:, res.n_closed]))]
+        self._iterating = False

@@ -214,6 +214,7 @@ class KafkaConsumer:
         self._raw_codec = raw_codec
         self._fail_commits = fail_commits
         self._positions: Dict[int, int] = {}
+        self._seek_pending = False
         self.committed_log: List[Dict[int, int]] = []
         self.commit_calls: List[Optional[int]] = []
         self.closed = False
@@ -225,6 +226,8 @@ class KafkaConsumer:
 
     def _roll(self) -> bool:
         """Move to the next repetition when the current one is exhausted; False at the very end."""
+        if self._seek_pending:
+            self._apply_seek()
         if self._cursor < len(self._log):
             return True
         if self._rep + 1 < self._repeat and len(self._log):
@@ -389,6 +392,44 @@ class KafkaConsumer:
         protocol): a caller may page-lock them once and DMA out of them.  The stub's arena is the
         encoded log segment."""
         return [self._log.encoded(self._raw_batch_bytes, self._raw_codec).data]
+
+    # -- seek (kafka-python API) ---------------------------------------------
+    def seek(self, partition, offset):
+        """Next fetch of ``partition`` starts at ``offset``.  The stub serves one global log order,
+        so after seeking it resumes at the earliest log entry that some partition still has to
+        deliver (exact whenever the sought positions describe a prefix of the log order, which
+        is what a pipeline rewinding to its last delivered batch produces)."""
+        self._positions[partition.partition] = int(offset)
+        self._seek_pending = True
+
+    def _apply_seek(self):
+        self._seek_pending = False
+        log = self._log
+        n = len(log)
+        if not n:
+            return
+        counts = log.per_partition_count()
+        by_part = log.__dict__.setdefault("_idx_by_part", {})
+        best = None
+        for p in np.unique(log.partitions).tolist():
+            idx = by_part.get(p)
+            if idx is None:
+                idx = by_part[p] = np.flatnonzero(log.partitions == p)
+            offs = log.offsets[idx]                      # ascending within a partition
+            pos = self._positions.get(p, int(offs[0]))
+            cnt = int(counts[p])
+            rep = max(0, (pos - int(offs[0])) // cnt) if cnt else 0
+            k = int(np.searchsorted(offs, pos - rep * cnt, side="left"))
+            if k >= len(idx):
+                rep, k = rep + 1, 0
+            if rep >= self._repeat:
+                continue                                 # nothing left in this partition
+            g = rep * n + int(idx[k])
+            best = g if best is None else min(best, g)
+        if best is None:
+            self._rep, self._cursor = self._repeat - 1, n
+        else:
+            self._rep, self._cursor = divmod(best, n)
 
     # -- offsets -------------------------------------------------------------
     def position(self, tp):

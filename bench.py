@@ -277,7 +277,7 @@ def make_dataset_cls(log, mode, repeat=1):
         @classmethod
         def new_consumer(cls, *a, **k):
             k.pop("enable_auto_commit", None)
-            return consumer_cls(*a, log=log, repeat=repeat, raw_batch_bytes=RAW_BATCH_BYTES, **k)
+            return consumer_cls(*a, log=log, repeat=repeat, raw_batch_bytes=RAW_BATCH_BYTES, keep_commit_log=False, **k)
 
     return Cfg2Dataset
 

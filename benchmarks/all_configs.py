@@ -87,47 +87,52 @@ _rc = os.environ.get("RAW_CODEC", "0")                  # codec of the raw arm: 
 RAW_CODEC = int(_rc) if _rc.isdigit() else _rc
 
 
-def e2e(cfg, log, packed, repeat, batches_timed, warm):
-    """packed: False = poll() objects, True = poll_packed() arrays, "raw" = poll_raw() record batches."""
-    consumer_cls = sk.KafkaConsumer if packed else sk.PollOnlyConsumer
+def e2e(cfg, log, packed, repeat):
+    """packed: False = poll() objects, True = poll_packed() arrays, "raw" = poll_raw() record batches,
+    "raw_dma" = poll_raw() blobs copied to the device out of the consumer's page-locked buffer.
 
-    class DS(KafkaDataset):
-        payload_schema = cfg["schema"]
-        device_slot_bytes = cfg["slot_bytes"] + (cfg["slot_bytes"] >> 2 if packed == "raw" else 0)   # framing
-        device_slots = int(os.environ.get("DEVICE_SLOTS", "3"))
-        device_producers = int(os.environ.get("TK_PRODUCERS", "2"))
-        device_input = "raw" if packed == "raw" else "auto"
-
-        @classmethod
-        def new_consumer(cls, *a, **k):
-            k.pop("enable_auto_commit", None)
-            return consumer_cls(*a, log=log, repeat=repeat, raw_codec=RAW_CODEC,
-                                raw_batch_bytes=max(RAW_BATCH_BYTES, 2 * cfg.get("record_bytes", 0)), **k)
-
+    A complete iteration over `repeat` repetitions of the log, timed from before the iteration (and
+    the dataset's pipeline) is started until its last batch was delivered and the device is idle;
+    a warm-up iteration over one repetition runs first (bench.py's e2e leg, for any schema)."""
     from torch.utils.data import DataLoader
-    ds = DS("topic", group_id="cfg")
-    seen, t0, t1 = 0, None, None
-    last = None
-    for batch in auto_commit(DataLoader(ds, batch_size=cfg["batch"])):
-        if seen == warm:
-            torch.cuda.synchronize()
-            t0 = time.perf_counter()
-            r0 = ds._consumer.consumed
-        last = batch
-        seen += 1
-        if seen == warm + batches_timed:
-            torch.cuda.synchronize()
-            t1 = time.perf_counter()
-            break
-    if t1 is None:
+    consumer_cls = sk.KafkaConsumer if packed else sk.PollOnlyConsumer
+    raw = packed in ("raw", "raw_dma")
+
+    def make(reps):
+        class DS(KafkaDataset):
+            payload_schema = cfg["schema"]
+            device_slot_bytes = cfg["slot_bytes"] + (cfg["slot_bytes"] >> 2 if raw else 0)   # framing
+            device_slots = int(os.environ.get("DEVICE_SLOTS", "3"))
+            device_producers = int(os.environ.get("TK_PRODUCERS", "2"))
+            device_input = packed if raw else "auto"
+
+            @classmethod
+            def new_consumer(cls, *a, **k):
+                k.pop("enable_auto_commit", None)
+                return consumer_cls(*a, log=log, repeat=reps, raw_codec=RAW_CODEC, keep_commit_log=False,
+                                    raw_batch_bytes=max(RAW_BATCH_BYTES, 2 * cfg.get("record_bytes", 0)), **k)
+        return DS("topic", group_id="cfg")
+
+    def run(reps):
+        ds = make(reps)
+        sink = torch.zeros(256, dtype=torch.uint8).pin_memory()
         torch.cuda.synchronize()
-        t1 = time.perf_counter()
-    kept = (seen - warm) * cfg["batch"]
-    stats = dict(ds.last_pipeline_stats) if ds._pipeline is None else dict(ds._pipeline.stats)
-    keep_rate = (stats.get("kept", 1) / max(stats.get("records", 1), 1)) if stats else 1.0
-    ds.close()
-    del last
-    return kept / max(keep_rate, 1e-9) / (t1 - t0)
+        seen = 0
+        t0 = time.perf_counter()
+        for batch in auto_commit(DataLoader(ds, batch_size=cfg["batch"])):
+            seen += 1
+            if seen % 64 == 0:          # a slice of every 64th batch is read back (per-step D2H of 4-record
+                t = batch[0] if isinstance(batch, tuple) else batch          # batches would time cudaMemcpyAsync)
+                sink.copy_(t.reshape(-1).view(torch.uint8)[:256], non_blocking=True)
+        torch.cuda.synchronize()
+        dt = time.perf_counter() - t0
+        stats = dict(ds.last_pipeline_stats)
+        ds.close()
+        return dt, stats
+
+    run(1)
+    dt, stats = run(repeat)
+    return repeat * len(log) / dt, stats
 
 
 def cpu_oracle(cfg, log, seconds=6.0):
@@ -150,27 +155,34 @@ def main():
         log = syn.make_log(c, cfg["n"], seed=100 + c, partitions=64, layout="chunked", chunk=4 if c == 4 else 500)
         dev, peak = device_resident(cfg, log)
         link_bytes = (log.nbytes + 16 * len(log)) / len(log)
-        slot_recs = max(1, min(len(log), int(cfg["slot_bytes"] // max(log.nbytes / len(log), 1))))
-        per_batch_recs = cfg["batch"]
-        # enough repetitions for ~40 slots of work
-        target_records = 40 * slot_recs
-        repeat = max(2, target_records // len(log) + 2)
-        for r in range(repeat):
-            log.rep_records(r)
-        nb = max(8, int(0.8 * target_records / per_batch_recs))
-        warm = max(3, nb // 8)
+        slot_recs = max(1, int(cfg["slot_bytes"] // max(log.nbytes / len(log), 1)))
+        # the poll arm is bounded by the record objects it may hold (they exist before the clock
+        # starts, as they do for the CPU arm); the other arms run for ~2 s
+        link_rate = peak * 1e9 / link_bytes                       # records/s the link could carry
+        obj_budget = int(os.environ.get("TK_POLL_OBJECTS", "4000000"))
         row = {"config": c, "name": cfg["name"], "records": len(log), "avg_value_bytes": log.nbytes / len(log),
                "link_bytes_per_record": link_bytes, "device": dev, "h2d_peak_GBps": peak}
-        for packed in (False, True, "raw"):
-            if packed == "raw":
+        for packed in (False, True, "raw", "raw_dma"):
+            if packed in ("raw", "raw_dma"):
                 enc = log.encoded(max(RAW_BATCH_BYTES, 2 * cfg.get("record_bytes", 0)), RAW_CODEC)   # before the clock
                 lb = enc.nbytes / len(log)
             else:
                 lb = link_bytes
-            rps = e2e(cfg, log, packed, repeat, nb - warm, warm)
-            row["e2e_raw" if packed == "raw" else "e2e_packed" if packed else "e2e_poll"] = {
-                "records_per_s": rps, "link_GBps": rps * lb / 1e9,
-                "link_frac": rps * lb / 1e9 / peak}
+            want = max(2.0 * min(link_rate, 60e6), 20 * 5 * slot_recs)
+            if packed is False:
+                want = min(want, obj_budget)
+            repeat = max(2, int(want // len(log)) + 1)
+            if packed is False:
+                for r in range(repeat):
+                    log.rep_records(r)
+                import gc
+                gc.collect()
+                gc.freeze()
+            rps, stats = e2e(cfg, log, packed, repeat)
+            key = {False: "e2e_poll", True: "e2e_packed", "raw": "e2e_raw", "raw_dma": "e2e_raw_dma"}[packed]
+            row[key] = {"records_per_s": rps, "link_GBps": rps * lb / 1e9, "link_frac": rps * lb / 1e9 / peak,
+                        "seconds": repeat * len(log) / rps, "log_repeats": repeat}
+            assert row[key]["link_frac"] <= 1.0, (key, row[key])
         if not args.no_cpu:
             row["cpu_oracle_1core_records_per_s"] = cpu_oracle(cfg, log)
         rows.append(row)

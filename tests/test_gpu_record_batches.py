@@ -417,3 +417,25 @@ def test_decompressed_values_beyond_the_slot_are_reported_not_written():
     finally:
         IngestPipeline._gather_raw = orig
         ds.close()
+
+
+def test_device_split_of_kafka_python_golden_batches():
+    """Bytes of kafka-python's own test suite (tests/golden/kafka_python_record_batches.py), not written
+    by this repository's encoder: CRC check, header walk and record framing on the device."""
+    from golden import kafka_python_record_batches as kp
+    eng, n, nbytes, nbatches = split_on_gpu([(5, kp.STREAM, 0, 0), (6, b"".join(kp.BATCHES[1:]), 2, 100)])
+    assert nbatches == 5 and n == 4 + 3
+    recs = device_records(eng, n, nbytes)
+    want = [(5, o, v, False) for o, v in kp.RECORDS] + [(6, 101, b"", True), (6, 102, b"", False), (6, 103, b"123", False)]
+    for (start, part, off), (p, o, v, dropped), nxt in zip(recs, want, recs[1:]):
+        assert part == (p | (0x40000000 if dropped else 0)) and off == o, (part, off, p, o)
+        assert nxt[0] - start == (0 if dropped else len(v))
+    assert nbytes == 3 + 3 + 3
+    # the gathered value bytes, read through the slot's device pointer
+    ptr, _ = eng.device_views(0)
+
+    class _Slot:
+        __cuda_array_interface__ = {"shape": (nbytes,), "typestr": "|u1", "data": (ptr, True), "version": 2}
+
+    assert bytes(torch.as_tensor(_Slot(), device="cuda").cpu().numpy()) == b"123" * 3
+    eng.close()

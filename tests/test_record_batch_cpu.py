@@ -226,3 +226,37 @@ def test_compressed_batches_roundtrip_through_the_oracle(codec):
             got += orb.split_blob(bytes(data), p, fetch_offset, delta)
     want = list(sk.KafkaConsumer("topic", log=log))
     assert [(r.partition, r.offset, r.value) for r in got] == [(r.partition, r.offset, r.value) for r in want]
+
+
+# ---------------------------------------------------------------- bytes of kafka-python's own test suite
+def _independent_crc32c(data: bytes) -> int:
+    """A CRC-32C that shares no code with this repository (TensorBoard's record writer)."""
+    from tensorboard.compat.tensorflow_stub.pywrap_tensorflow import crc32c
+    return crc32c(data)
+
+
+def test_kafka_python_golden_batches_are_intact_and_every_crc_agrees():
+    from golden import kafka_python_record_batches as kp
+    assert len(kp.STREAM) == kp.SIZE_IN_BYTES and sum(len(b) for b in kp.BATCHES) == kp.VALID_BYTES
+    for blob, want in zip(kp.BATCHES, kp.CRCS):
+        assert struct.unpack(">I", blob[17:21])[0] == want
+        assert struct.unpack(">i", blob[8:12])[0] + 12 == len(blob)             # batchLength
+        covered = blob[21:]                                                       # attributes .. end
+        assert _independent_crc32c(covered) == want      # the hand-entered bytes are the producer's bytes
+        assert orb.crc32c(covered) == want               # oracle restatement
+        assert rb.crc32c(covered) == want                # library host CRC (tk_crc32c)
+
+
+def test_oracle_reads_kafka_python_golden_batches_like_kafka_python_does():
+    from golden import kafka_python_record_batches as kp
+    recs = orb.split_blob(kp.STREAM, 5)                  # the 4 stray bytes are an incomplete batch: ignored
+    assert [(r.partition, r.offset, r.value) for r in recs] == [(5, o, v) for o, v in kp.RECORDS]
+    # a consumer positioned inside the second batch gets the batch whole and skips below its position
+    recs = orb.split_blob(b"".join(kp.BATCHES[1:]), 5, fetch_offset=2)
+    assert [(r.offset, r.value) for r in recs] == [(2, b""), (3, b"123")]
+    # the repository's own encoder writes the same bytes for the same records (timestamps aside):
+    # header layout and record framing agree field by field where both are defined
+    mine = rb.encode_batch(3, [b"123"])
+    theirs = kp.BATCHES[2]
+    assert len(mine) == len(theirs) and mine[:8] == theirs[:8] and mine[8:12] == theirs[8:12]
+    assert mine[16] == theirs[16] == 2 and mine[21:27] == theirs[21:27] and mine[57:] == theirs[57:]

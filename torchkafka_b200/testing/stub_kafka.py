@@ -199,7 +199,7 @@ class KafkaConsumer:
 
     def __init__(self, *topics, log: Optional[RecordLog] = None, block_at_end: bool = False,
                  fail_commits: bool = False, repeat: int = 1, raw_batch_bytes: int = 16384,
-                 raw_codec=0, **configs):
+                 raw_codec=0, keep_commit_log: bool = True, **configs):
         self.topics = topics
         self.config = dict(configs)
         # the end of the in-memory log is the end of the stream, unless the stub is told to
@@ -215,6 +215,11 @@ class KafkaConsumer:
         self._fail_commits = fail_commits
         self._positions: Dict[int, int] = {}
         self._seek_pending = False
+        #: False: only the current table (``committed_table``) and the number of commits are kept
+        #: (long benchmark runs commit millions of times)
+        self._keep_commit_log = bool(keep_commit_log)
+        self.committed_table: Dict[int, int] = {}
+        self.n_commits = 0
         self.committed_log: List[Dict[int, int]] = []
         self.commit_calls: List[Optional[int]] = []
         self.closed = False
@@ -438,6 +443,14 @@ class KafkaConsumer:
     def commit(self, offsets=None):
         if self._fail_commits:
             raise CommitFailedError("stub commit failure")
+        self.n_commits += 1
+        if not self._keep_commit_log:
+            if offsets is None:
+                self.committed_table.update(self._positions)
+            else:
+                for tp, om in offsets.items():
+                    self.committed_table[tp.partition] = om.offset
+            return
         # committed_log[k] = the group's committed-offset table right after commit k
         snap = dict(self.committed_log[-1]) if self.committed_log else {}
         if offsets is None:
@@ -446,6 +459,7 @@ class KafkaConsumer:
             for tp, om in offsets.items():
                 snap[tp.partition] = om.offset
         self.committed_log.append(snap)
+        self.committed_table = snap
         self.commit_calls.append(None if offsets is None else len(offsets))
 
     def committed(self, tp):

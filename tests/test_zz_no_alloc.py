@@ -76,6 +76,14 @@ def test_noalloc_compaction_matches_context_compaction_twice():
                                                  hdr.data_ptr(), C.c_void_p(stream.cuda_stream)))
             torch.cuda.synchronize()
             assert np.array_equal(kidx.cpu().numpy(), want_kidx), f"call {call}: indices differ"
+            # ... and both equal the definition, computed without any of the library's code: a kept
+            # record's index is the number of kept records before it, a skipped one's is -1 - that
+            flags = keep.cpu().numpy() >= 0
+            before = np.cumsum(flags) - flags
+            assert np.array_equal(kidx.cpu().numpy(), np.where(flags, before, -1 - before)), f"call {call}"
+            n_kept = int(flags.sum())
+            assert (want.n_kept, want.n_closed, want.carry_out) == (
+                n_kept, (carry + n_kept) // BATCH, (carry + n_kept) % BATCH)
             got = hdr.cpu().numpy().astype(np.int64) & 0xFFFFFFFF
             assert (got[0], got[1], got[2], got[3], got[4], got[5]) == (
                 want.n_records, want.n_kept, want.carry_in, want.carry_out, want.n_closed, BATCH)

@@ -385,9 +385,13 @@ def test_cfg2_received_into_the_slot_or_copied_from_the_arena(mode, codec):
     assert_same(gpu, run_oracle(log, schema, 128), schema)
 
 
-def test_decompressed_values_beyond_the_slot_are_reported_not_written():
+@pytest.mark.parametrize("codec", [3, 4])
+def test_decompressed_values_beyond_the_slot_are_reported_not_written(codec):
     """Compressed batches whose values need more room than the slot has: nothing may be written
-    outside the slot's byte buffer; the batch that does not fit raises PayloadError(status 9)."""
+    outside the slot's byte buffer; the batch that does not fit raises PayloadError(status 9).
+    (LZ4: the decompressed buffer is as large as the slot and refuses the batch; zstd frames
+    without content size are placed by their upper bounds in a buffer that grows, so the values
+    reach the gather step, which refuses them.)"""
     n = 400
     vals = [json.dumps([0.0] * 200).encode() for _ in range(n)]          # ~1 KB each, compresses > 20x
     log = RecordLog(vals, np.zeros(n, np.int32), np.arange(n))
@@ -395,7 +399,7 @@ def test_decompressed_values_beyond_the_slot_are_reported_not_written():
 
     from torchkafka_b200.pipeline import IngestPipeline
     ds = make_dataset(log, schema, slot_bytes=64 << 10, device_input="raw",
-                      consumer_kwargs={"raw_batch_bytes": 32768, "raw_codec": 3})
+                      consumer_kwargs={"raw_batch_bytes": 32768, "raw_codec": codec})
     # defeat the fetch budget's expansion estimate: ask for whole slots of compressed bytes
     orig = IngestPipeline._gather_raw
 

@@ -542,7 +542,7 @@ __global__ void __launch_bounds__(1024) k_unit_place(const rb_args a) {
         }
         const unsigned long long first = a.units[b.unit_first].out;
         if (failed) b.status = TK_STATUS_CORRUPT;
-        else if (first + total > a.raw2_bytes) b.status = TK_STATUS_UNSUPPORTED;   // does not fit the buffer
+        else if (first + total > a.raw2_bytes) b.status = TK_STATUS_SLOT_OVERFLOW;   // does not fit the buffer
         else { b.rec_start = (uint32_t)first; b.rec_end = (uint32_t)(first + total); }
     }
 }

@@ -393,7 +393,8 @@ __global__ void __launch_bounds__(256) k_rb_check(const rb_args a) {
                 tk_rec_t rec;
                 rec.start = 0;
                 rec.partition = b.partition | (k ? TK_REC_DROPPED
-                                                 : status == TK_STATUS_UNSUPPORTED ? TK_REC_UNSUPPORTED : TK_REC_CORRUPT);
+                                                 : status == TK_STATUS_UNSUPPORTED ? TK_REC_UNSUPPORTED
+                                                 : status == TK_STATUS_SLOT_OVERFLOW ? TK_REC_OVERFLOW : TK_REC_CORRUPT);
                 rec.offset = b.base_offset;
                 a.recs[b.rec_base + k] = rec;
             }

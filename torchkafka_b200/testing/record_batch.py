@@ -230,6 +230,16 @@ class EncodedLog:
         ends = np.concatenate([change, [nbt]]).astype(np.int64)
         self.run_end = ends[np.searchsorted(ends, np.arange(nbt), side="right")] if nbt else np.zeros(0, np.int64)
 
+    def pin(self):
+        """Move the segment into page-locked memory (a consumer that receives into pinned arenas):
+        DMA straight out of it then runs at the link's full rate.  Needs CUDA; idempotent."""
+        if not getattr(self, "_pinned", None):
+            import torch
+            t = torch.from_numpy(self.data.copy()).pin_memory()
+            self._pinned = t                         # keeps the allocation alive
+            self.data = t.numpy()
+        return self
+
     @property
     def nbytes(self) -> int:
         return int(self.start[-1])

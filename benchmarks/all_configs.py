@@ -123,7 +123,9 @@ def e2e(cfg, log, packed, repeat):
             seen += 1
             if seen % 64 == 0:          # a slice of every 64th batch is read back (per-step D2H of 4-record
                 t = batch[0] if isinstance(batch, tuple) else batch          # batches would time cudaMemcpyAsync)
-                sink.copy_(t.reshape(-1).view(torch.uint8)[:256], non_blocking=True)
+                flat = t.reshape(-1).view(torch.uint8)
+                k = min(256, flat.numel())
+                sink[:k].copy_(flat[:k], non_blocking=True)
         torch.cuda.synchronize()
         dt = time.perf_counter() - t0
         stats = dict(ds.last_pipeline_stats)

@@ -167,6 +167,20 @@ int tk_json_decode(tk_ctx* ctx, int slot, int dtype, uint32_t max_len, uint32_t 
                    const tk_plane_t* values, const tk_plane_t* lengths, const tk_plane_t* mask,
                    void* stream);
 
+/* ---- the JSON array path of a slot in one pass over the payload ---------------
+ * Same reference lines as tk_json_scan + tk_compact + tk_json_decode together (README.md:74-77,
+ * src/kafka_dataset.py:161-162, fetch.py:27-45, collate.py:275): element counts, keep flags,
+ * compaction, batch boundaries, the per-(batch, partition) commit maxima, pad / length / mask rows
+ * and the parsed values, by one persistent kernel that brings every tile of the byte buffer into
+ * shared memory once (bulk asynchronous copy) and chains the tiles' kept counts with a decoupled
+ * look-back.  Follow with tk_commit_offsets and tk_slot_fetch_result.  This is what tk_process_slot
+ * runs for TK_SCHEMA_JSON; tk_ctx_set_json_flat(ctx, 1) (or TK_JSON_FLAT=1 in the environment when
+ * the context is created) selects the three-kernel chain instead. */
+int tk_json_ingest(tk_ctx* ctx, int slot, int dtype, uint32_t max_len, uint32_t min_size,
+                   uint32_t fixed_len, uint32_t batch_size, const tk_plane_t* values,
+                   const tk_plane_t* lengths, const tk_plane_t* mask, void* stream);
+int tk_ctx_set_json_flat(tk_ctx* ctx, int enabled);
+
 /* Same contract, earlier single-kernel decomposition (one warp per record, shared-memory ring,
  * number-run validation); kept as a cross-check and for comparison runs. */
 int tk_json_decode_warp(tk_ctx* ctx, int slot, int dtype, uint32_t max_len, uint32_t fixed_len,

@@ -427,7 +427,7 @@ def test_device_split_of_kafka_python_golden_batches():
     """Bytes of kafka-python's own test suite (tests/golden/kafka_python_record_batches.py), not written
     by this repository's encoder: CRC check, header walk and record framing on the device."""
     from golden import kafka_python_record_batches as kp
-    eng, n, nbytes, nbatches = split_on_gpu([(5, kp.STREAM, 0, 0), (6, b"".join(kp.BATCHES[1:]), 2, 100)])
+    eng, n, nbytes, nbatches = split_on_gpu([(5, kp.STREAM, 0, 0), (6, b"".join(kp.BATCHES[1:]), 102, 100)])
     assert nbatches == 5 and n == 4 + 3
     recs = device_records(eng, n, nbytes)
     want = [(5, o, v, False) for o, v in kp.RECORDS] + [(6, 101, b"", True), (6, 102, b"", False), (6, 103, b"123", False)]

@@ -96,6 +96,9 @@ _SIGNATURES = {
     "tk_carry_rows": (C.c_int, [C.c_void_p, C.c_int, C.c_int, _p(TkPlane), _p(TkPlane), C.c_void_p]),
     "tk_json_decode": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_uint32, C.c_uint32, _p(TkPlane),
                                  _p(TkPlane), _p(TkPlane), C.c_void_p]),
+    "tk_json_ingest": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_uint32, C.c_uint32, C.c_uint32, C.c_uint32,
+                                 _p(TkPlane), _p(TkPlane), _p(TkPlane), C.c_void_p]),
+    "tk_ctx_set_json_flat": (C.c_int, [C.c_void_p, C.c_int]),
     "tk_json_decode_warp": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_uint32, C.c_uint32, _p(TkPlane),
                                       _p(TkPlane), _p(TkPlane), C.c_void_p]),
     "tk_collate_raw": (C.c_int, [C.c_void_p, C.c_int, C.c_uint64, _p(TkPlane), C.c_void_p]),

@@ -5,6 +5,7 @@
 // host memory with a device twin; tk_slot_submit() copies it on the library's own
 // copy stream so the transfer overlaps the kernels working on the previous slot.
 #include <stdarg.h>
+#include <stdlib.h>
 #include <string.h>
 #include <new>
 #include <thread>
@@ -225,6 +226,7 @@ static void free_slot(tk_slot& s) {
     cudaFree(s.d.rec_kidx); cudaFree(s.d.tile_agg); cudaFree(s.d.tile_incl); cudaFree(s.d.tile_flag);
     cudaFree(s.d.plan_ctr); cudaFree(s.d.block);
     cudaFree(s.d.rec_tok); cudaFree(s.d.tok_pos); cudaFree(s.d.tok_count);
+    cudaFree(s.d.fz_tile_first); cudaFree(s.d.fz_agg); cudaFree(s.d.fz_incl); cudaFree(s.d.fz_flag); cudaFree(s.d.fz_ctr);
     if (s.ev_h2d) cudaEventDestroy(s.ev_h2d);
     if (s.ev_free) cudaEventDestroy(s.ev_free);
     if (s.ev_result) cudaEventDestroy(s.ev_result);
@@ -325,6 +327,7 @@ extern "C" int tk_ctx_create(int device, uint64_t slot_bytes, uint32_t slot_reco
     ctx->max_batches = max_batches;
     ctx->commit_pitch = (max_batches + 1 + 3) & ~3u;
     ctx->n_partitions = n_partitions;
+    { const char* e = getenv("TK_JSON_FLAT"); ctx->json_flat = (e && e[0] == '1') ? 1 : 0; }
     int rc = create_impl(ctx);
     if (rc) { char keep[1024]; strncpy(keep, g_err, sizeof(keep)); keep[1023] = 0; tk_ctx_destroy(ctx); tk_set_error("%s", keep); return rc; }
     *out = ctx;

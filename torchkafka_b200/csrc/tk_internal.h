@@ -71,6 +71,13 @@ struct tk_slot_dev {
     uint32_t*    tok_pos;      // [tok_cap] token array of the flat decode path: uint2 {byte position, record}
     uint32_t*    tok_count;    // [2] elements emitted so far (token array allocation cursor): two
                                // counters used alternately, each scan zeroes the one of the next
+    // single-pass JSON kernel (tk_json_fused.cu; allocated on first use): first record of every
+    // tile of the byte buffer, look-back arrays over the tiles, counters (ticket, finished, exited)
+    uint32_t*    fz_tile_first;
+    unsigned long long* fz_agg;
+    unsigned long long* fz_incl;
+    uint32_t*    fz_flag;
+    uint32_t*    fz_ctr;
     // raw record-batch input (allocated on first tk_slot_submit_recordbatches)
     uint8_t*     raw;          // [slot_bytes + pad]
     uint8_t*     raw2;         // [raw2_bytes + pad] decompressed records of compressed batches (first use)
@@ -113,6 +120,7 @@ struct tk_slot {
     bool         dec_timed;
     uint32_t     tok_use;     // tk_json_scan calls on this slot: selects the token counter
     uint32_t     plan_epoch;  // tk_compact calls on this slot: tags the tile status words
+    uint32_t     fz_epoch;    // tk_json_ingest calls on this slot: tags the fused kernel's tile status words
     bool         free_recorded;
 };
 
@@ -126,6 +134,8 @@ struct tk_ctx {
     uint32_t  n_partitions;
     size_t    block_bytes;     // size of a slot's result block
     size_t    tok_cap;         // entries of the token array (a token needs >= 2 bytes)
+    size_t    fz_tiles;        // entries of the fused kernel's tile arrays (0: not allocated)
+    int       json_flat;       // 1: tk_process_slot uses the three-kernel JSON chain (scan, plan, parse)
     uint32_t  batch_size;      // of the last tk_compact
     cudaStream_t copy_stream;
     tk_state* d_state;
@@ -204,6 +214,7 @@ __device__ __forceinline__ void tk_plan_reset_run(const tk_plan_reset& r, uint32
 #endif
 
 int tk_ensure_token_arrays(tk_ctx* ctx);
+int tk_ensure_fused(tk_ctx* ctx);
 tk_plan_reset tk_plan_reset_args(tk_ctx* ctx, int slot);
 // K4 second half; wait_for_prior = 0 only behind a kernel that released its dependents after its own wait
 int tk_commit_final(tk_ctx* ctx, int slot, int wait_for_prior, void* stream);

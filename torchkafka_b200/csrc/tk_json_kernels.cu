@@ -237,7 +237,6 @@ struct flat_args {
 #define ROWS_GROUP 8
 template <int ELEM_BYTES>
 __device__ __forceinline__ void json_rows_part(const flat_args& a, uint32_t warp, uint32_t nwarps, uint32_t lane) {
-    constexpr uint32_t PER16 = 16 / ELEM_BYTES;                 // elements per 16-byte store
     const uint32_t B = a.res->batch_size;
     const bool vec_values = ((a.values.row_bytes | (uintptr_t)a.values.base) & 15u) == 0;
     const bool vec_mask = a.mask.base && ((a.mask.row_bytes | (uintptr_t)a.mask.base | a.max_len) & 15u) == 0;
@@ -258,44 +257,8 @@ __device__ __forceinline__ void json_rows_part(const flat_args& a, uint32_t warp
             const int32_t kidx = __shfl_sync(0xffffffffu, my_kidx, r);
             const uint32_t len = __shfl_sync(0xffffffffu, my_len, r);
             if (kidx < 0) continue;
-            const uint64_t row = (uint64_t)B + (uint32_t)kidx;
-            const uint32_t fill_from = min(len, a.max_len);
-            uint8_t* vrow = (uint8_t*)a.values.base + row * a.values.row_bytes;
-            // pad [fill_from, max_len): scalar stores up to the next 16-byte boundary, then 16 bytes per lane
-            uint32_t e0 = fill_from;
-            if (vec_values) {
-                const uint32_t up = min((fill_from + PER16 - 1) & ~(PER16 - 1), a.max_len);
-                if (fill_from + lane < up) {
-                    if (ELEM_BYTES == 4) reinterpret_cast<uint32_t*>(vrow)[fill_from + lane] = 0u;
-                    else reinterpret_cast<unsigned long long*>(vrow)[fill_from + lane] = 0ull;
-                }
-                const uint32_t vend = a.max_len & ~(PER16 - 1);
-                for (uint32_t e = up + lane * PER16; e < vend; e += 32 * PER16)
-                    *reinterpret_cast<uint4*>(vrow + (size_t)e * ELEM_BYTES) = make_uint4(0, 0, 0, 0);
-                e0 = max(up, vend);
-            }
-            if (ELEM_BYTES == 4) {
-                uint32_t* p = reinterpret_cast<uint32_t*>(vrow);
-                for (uint32_t e = e0 + lane; e < a.max_len; e += 32) p[e] = 0u;
-            } else {
-                unsigned long long* p = reinterpret_cast<unsigned long long*>(vrow);
-                for (uint32_t e = e0 + lane; e < a.max_len; e += 32) p[e] = 0ull;
-            }
-            if (a.lengths.base && lane == 0)
-                *reinterpret_cast<int32_t*>((uint8_t*)a.lengths.base + row * a.lengths.row_bytes) = (int32_t)len;
-            if (a.mask.base) {
-                uint8_t* m = (uint8_t*)a.mask.base + row * a.mask.row_bytes;
-                if (vec_mask) {
-                    for (uint32_t e = lane * 16; e < a.max_len; e += 32 * 16)
-                        *reinterpret_cast<uint4*>(m + e) = make_uint4(mask_word(len, e), mask_word(len, e + 4),
-                                                                      mask_word(len, e + 8), mask_word(len, e + 12));
-                } else if ((a.max_len & 3u) == 0 && ((uintptr_t)m & 3u) == 0) {
-                    uint32_t* m32 = reinterpret_cast<uint32_t*>(m);
-                    for (uint32_t w = lane; w < a.max_len / 4; w += 32) m32[w] = mask_word(len, w * 4);
-                } else {
-                    for (uint32_t e = lane; e < a.max_len; e += 32) m[e] = e < len ? 1 : 0;
-                }
-            }
+            json_write_row<ELEM_BYTES>(a.values, a.lengths, a.mask, a.max_len, (uint64_t)B + (uint32_t)kidx, len, lane,
+                                       vec_values, vec_mask);
         }
     }
 }
@@ -344,38 +307,7 @@ __global__ void __launch_bounds__(256, 5) k_json_parse(const flat_args a) {
         uint64_t F;
         uint32_t I, L2, neg;
         bool fast = flags != TOK_LAST && fast_number(a.bytes, pos, stop, tb.pow10, &I, &F, &L2, &neg);
-        if (fast) {
-            // torch.tensor(json.loads(..)): an int literal is a Python int ("-0" is +0.0), a float
-            // literal keeps its sign ("-0.0" is -0.0)
-            const bool minus = neg && (I | L2 | (uint32_t)F | (uint32_t)(F >> 32));
-            if (KIND == TK_F32) {
-                // The reference rounds twice: text -> double (json.loads), double -> float
-                // (torch.tensor).  d = I + F * 10^-L2 in one fused multiply-add is within 2.5 ulp
-                // (double) of the exact value x: F -> double and the rounded 10^-L2 contribute a
-                // relative 2^-52 of the fraction (< 1), the final rounding half an ulp.  The
-                // correctly rounded double y is within 3.5 ulp of d, so unless a float rounding
-                // boundary (low 29 mantissa bits = 0x10000000) lies within 8 ulp of d, float(d)
-                // == float(y) bit for bit.  Otherwise (2^-25 of the inputs): exact conversion.
-                double d = (double)I;
-                if (L2) d = fma((double)F, tb.inv10[L2], d);
-                const uint32_t low = (uint32_t)__double_as_longlong(d) & 0x1FFFFFFFu;
-                if (low - (0x10000000u - 8u) <= 16u) {
-                    const uint64_t w = (uint64_t)I * tb.pow10w[L2] + F;
-                    d = __longlong_as_double((long long)(w ? el_small_neg_exp(w, L2, tb.pow5) : 0ull));
-                }
-                const float f = (float)d;
-                v = (T)(minus ? -f : f);
-            } else if (KIND == TK_F64) {
-                const uint64_t w = (uint64_t)I * tb.pow10w[L2] + F;
-                uint64_t bits = w ? el_small_neg_exp(w, L2, tb.pow5) : 0ull;
-                if (minus) bits |= 0x8000000000000000ull;
-                v = (T)__longlong_as_double((long long)bits);
-            } else if (L2 == 0) {
-                v = (T)(neg ? -(int32_t)I : (int32_t)I);         // < 10^8: fits every integer target
-            } else {
-                fast = false;                                    // float literal, integer target
-            }
-        }
+        if (fast) fast = fast_convert<KIND>(I, F, L2, neg, tb, &v);
         if (!fast) {
             GlobalReader rd{a.bytes, end};
             st = tk_json_element_flat<KIND>(rd, pos, &v);

@@ -149,3 +149,89 @@ __device__ __forceinline__ bool fast_number(const uint8_t* bytes, uint32_t pos, 
     return true;
 }
 
+// Value of a literal the fast lane accepted (I integer digits, F the L2 fraction digits): the same
+// bits as json.loads + torch.tensor give.  False: float literal with an integer target (scalar path).
+template <int KIND>
+__device__ __forceinline__ bool fast_convert(uint32_t I, uint64_t F, uint32_t L2, uint32_t neg, const parse_tables& tb,
+                                             typename tk_elem<KIND>::type* out) {
+    typedef typename tk_elem<KIND>::type T;
+    T v;
+    // torch.tensor(json.loads(..)): an int literal is a Python int ("-0" is +0.0), a float
+    // literal keeps its sign ("-0.0" is -0.0)
+    const bool minus = neg && (I | L2 | (uint32_t)F | (uint32_t)(F >> 32));
+    if (KIND == TK_F32) {
+        // The reference rounds twice: text -> double (json.loads), double -> float
+        // (torch.tensor).  d = I + F * 10^-L2 in one fused multiply-add is within 2.5 ulp
+        // (double) of the exact value x: F -> double and the rounded 10^-L2 contribute a
+        // relative 2^-52 of the fraction (< 1), the final rounding half an ulp.  The
+        // correctly rounded double y is within 3.5 ulp of d, so unless a float rounding
+        // boundary (low 29 mantissa bits = 0x10000000) lies within 8 ulp of d, float(d)
+        // == float(y) bit for bit.  Otherwise (2^-25 of the inputs): exact conversion.
+        double d = (double)I;
+        if (L2) d = fma((double)F, tb.inv10[L2], d);
+        const uint32_t low = (uint32_t)__double_as_longlong(d) & 0x1FFFFFFFu;
+        if (low - (0x10000000u - 8u) <= 16u) {
+            const uint64_t w = (uint64_t)I * tb.pow10w[L2] + F;
+            d = __longlong_as_double((long long)(w ? el_small_neg_exp(w, L2, tb.pow5) : 0ull));
+        }
+        const float f = (float)d;
+        v = (T)(minus ? -f : f);
+    } else if (KIND == TK_F64) {
+        const uint64_t w = (uint64_t)I * tb.pow10w[L2] + F;
+        uint64_t bits = w ? el_small_neg_exp(w, L2, tb.pow5) : 0ull;
+        if (minus) bits |= 0x8000000000000000ull;
+        v = (T)__longlong_as_double((long long)bits);
+    } else if (L2 == 0) {
+        v = (T)(neg ? -(int32_t)I : (int32_t)I);         // < 10^8: fits every integer target
+    } else {
+        return false;                                    // float literal, integer target
+    }
+    *out = v;
+    return true;
+}
+
+// Pad, length and mask of one kept record's row (row = its index in the output planes, len = its
+// element count), whole warp: store-only work, 16 bytes per lane where the planes allow it.
+template <int ELEM_BYTES>
+__device__ __forceinline__ void json_write_row(const tk_plane_t& values, const tk_plane_t& lengths, const tk_plane_t& mask,
+                                               uint32_t max_len, uint64_t row, uint32_t len, uint32_t lane,
+                                               bool vec_values, bool vec_mask) {
+    constexpr uint32_t PER16 = 16 / ELEM_BYTES;                 // elements per 16-byte store
+    const uint32_t fill_from = min(len, max_len);
+    uint8_t* vrow = (uint8_t*)values.base + row * values.row_bytes;
+    // pad [fill_from, max_len): scalar stores up to the next 16-byte boundary, then 16 bytes per lane
+    uint32_t e0 = fill_from;
+    if (vec_values) {
+        const uint32_t up = min((fill_from + PER16 - 1) & ~(PER16 - 1), max_len);
+        if (fill_from + lane < up) {
+            if (ELEM_BYTES == 4) reinterpret_cast<uint32_t*>(vrow)[fill_from + lane] = 0u;
+            else reinterpret_cast<unsigned long long*>(vrow)[fill_from + lane] = 0ull;
+        }
+        const uint32_t vend = max_len & ~(PER16 - 1);
+        for (uint32_t e = up + lane * PER16; e < vend; e += 32 * PER16)
+            *reinterpret_cast<uint4*>(vrow + (size_t)e * ELEM_BYTES) = make_uint4(0, 0, 0, 0);
+        e0 = max(up, vend);
+    }
+    if (ELEM_BYTES == 4) {
+        uint32_t* p = reinterpret_cast<uint32_t*>(vrow);
+        for (uint32_t e = e0 + lane; e < max_len; e += 32) p[e] = 0u;
+    } else {
+        unsigned long long* p = reinterpret_cast<unsigned long long*>(vrow);
+        for (uint32_t e = e0 + lane; e < max_len; e += 32) p[e] = 0ull;
+    }
+    if (lengths.base && lane == 0)
+        *reinterpret_cast<int32_t*>((uint8_t*)lengths.base + row * lengths.row_bytes) = (int32_t)len;
+    if (mask.base) {
+        uint8_t* m = (uint8_t*)mask.base + row * mask.row_bytes;
+        if (vec_mask) {
+            for (uint32_t e = lane * 16; e < max_len; e += 32 * 16)
+                *reinterpret_cast<uint4*>(m + e) = make_uint4(mask_word(len, e), mask_word(len, e + 4),
+                                                              mask_word(len, e + 8), mask_word(len, e + 12));
+        } else if ((max_len & 3u) == 0 && ((uintptr_t)m & 3u) == 0) {
+            uint32_t* m32 = reinterpret_cast<uint32_t*>(m);
+            for (uint32_t w = lane; w < max_len / 4; w += 32) m32[w] = mask_word(len, w * 4);
+        } else {
+            for (uint32_t e = lane; e < max_len; e += 32) m[e] = e < len ? 1 : 0;
+        }
+    }
+}

@@ -15,11 +15,27 @@ extern "C" int tk_process_slot(tk_ctx* ctx, int slot, const tk_job_t* job, void*
         rc = tk_carry_rows(ctx, job->prev_slot, job->n_planes, job->prev, job->cur, stream);
         if (rc) return rc;
     }
+    // JSON arrays: one single-pass kernel (tk_json_fused.cu) does scan, compaction, commit maxima, rows
+    // and parse; the three-kernel chain stays available (tk_ctx_set_json_flat / TK_JSON_FLAT=1) as a
+    // cross-check and for comparison runs
+    const bool fused = job->schema == TK_SCHEMA_JSON && !ctx->json_flat;
+    tk_slot& s = ctx->slots[slot];
+    if (fused) {
+        s.dec_timed = false;
+        if (ctx->timing) TK_CUDA(cudaEventRecord(s.ev_dec0, (cudaStream_t)stream));
+        rc = tk_json_ingest(ctx, slot, job->dtype, job->max_len, job->min_size, job->fixed_len, job->batch_size,
+                            &job->cur[0], job->n_planes > 1 ? &job->cur[1] : nullptr,
+                            job->n_planes > 2 ? &job->cur[2] : nullptr, stream);
+        if (rc) return rc;
+        if (ctx->timing) { TK_CUDA(cudaEventRecord(s.ev_dec1, (cudaStream_t)stream)); s.dec_timed = true; }
+        rc = tk_commit_final(ctx, slot, (s.n_records == 0 || ctx->timing) ? 1 : 0, stream);
+        if (rc) return rc;
+        return tk_slot_fetch_result(ctx, slot, stream);
+    }
     if (job->schema == TK_SCHEMA_JSON) rc = tk_json_scan(ctx, slot, job->max_len, job->min_size, stream);
     else rc = tk_raw_scan(ctx, slot, (job->schema == TK_SCHEMA_OBJECT || job->schema == TK_SCHEMA_NESTED) ? TK_ANY_RECORD_BYTES : job->record_bytes, stream);
     if (rc) return rc;
     rc = tk_compact(ctx, slot, job->batch_size, stream); if (rc) return rc;
-    tk_slot& s = ctx->slots[slot];
     s.dec_timed = false;
     if (ctx->timing) TK_CUDA(cudaEventRecord(s.ev_dec0, (cudaStream_t)stream));
     switch (job->schema) {
@@ -58,6 +74,12 @@ extern "C" int tk_process_slot(tk_ctx* ctx, int slot, const tk_job_t* job, void*
     rc = tk_commit_final(ctx, slot, (s.n_records == 0 || ctx->timing) ? 1 : 0, stream);
     if (rc) return rc;
     return tk_slot_fetch_result(ctx, slot, stream);
+}
+
+extern "C" int tk_ctx_set_json_flat(tk_ctx* ctx, int enabled) {
+    TK_REQUIRE(ctx, "null context");
+    ctx->json_flat = enabled ? 1 : 0;
+    return 0;
 }
 
 extern "C" int tk_ctx_set_timing(tk_ctx* ctx, int enabled) {

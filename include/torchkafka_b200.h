@@ -181,12 +181,6 @@ int tk_json_ingest(tk_ctx* ctx, int slot, int dtype, uint32_t max_len, uint32_t 
                    const tk_plane_t* lengths, const tk_plane_t* mask, void* stream);
 int tk_ctx_set_json_flat(tk_ctx* ctx, int enabled);
 
-/* Same contract, earlier single-kernel decomposition (one warp per record, shared-memory ring,
- * number-run validation); kept as a cross-check and for comparison runs. */
-int tk_json_decode_warp(tk_ctx* ctx, int slot, int dtype, uint32_t max_len, uint32_t fixed_len,
-                        const tk_plane_t* values, const tk_plane_t* lengths, const tk_plane_t* mask,
-                        void* stream);
-
 /* ---- K1c + K3: fixed-layout bytes -> rows (torch.frombuffer + torch.stack) -- */
 int tk_collate_raw(tk_ctx* ctx, int slot, uint64_t record_bytes, const tk_plane_t* out,
                    void* stream);

@@ -263,41 +263,71 @@ def test_live_stream_with_pauses_and_batch_iteration():
     ds.close()
 
 
-def test_two_decode_decompositions_agree():
-    """The flat path (comma-split segments, thread per element) and the earlier warp-per-record
-    kernel (number-run validation, shared-memory ring) are independent implementations of the
-    same contract; they must produce identical tensors, statuses and commit offsets."""
-    import ctypes as C
+def _fused_case(name):
+    """(values, schema, batch size) of one scenario for the single-pass / three-kernel comparison."""
+    import random
+    rng = random.Random(hash(name) & 0xFFFF)
+    if name == "cfg2_with_bad_records":
+        vals = list(syn.make_log(2, 3000, seed=41)._byte_values)
+        vals[17] = b"[1, 2,, 3]"                 # malformed: both must flag it
+        vals[18] = b" [ 1 ,\t2.5e3 , -0 ,1e400 ] "
+        vals[19] = b""
+        vals[20] = b"[]"
+        vals[21] = b"\xef\xbb\xbf[3.5]"
+        return vals, JsonArray(torch.float32, max_len=256, min_size=32), 128
+    if name == "tiny_records":                   # more records per tile than the per-tile tables hold
+        vals = [rng.choice([b"[1]", b"[]", b"[1,2]", b"[7, 8, 9]", b"[x]", b"1"]) for _ in range(30000)]
+        return vals, JsonArray(torch.int64, max_len=8, min_size=0), 64
+    if name == "huge_records":                   # records longer than the shared-memory window
+        vals = list(syn.make_log(2, 400, seed=42)._byte_values)
+        big = json.dumps([rng.uniform(-1e3, 1e3) for _ in range(9000)]).encode()
+        vals[50] = big
+        vals[51] = b"[" + b" " * 70000 + b"1.5,2.5 ]"
+        vals[399] = big[:-1] + b", 1e3]"
+        return vals, JsonArray(torch.float64, max_len=16384, min_size=2), 32
+    if name == "tokens":
+        return list(syn.make_log(3, 700, seed=43)._byte_values), TokenList(torch.int32, max_len=2048), 32
+    if name == "fixed_len_ragged":
+        vals = list(syn.make_log(1, 5000, seed=44)._byte_values)
+        vals[1234] = b"[1.0, 2.0]"
+        return vals, JsonArray(torch.float32, fixed_len=8), 4
+    raise KeyError(name)
+
+
+@pytest.mark.parametrize("case", ["cfg2_with_bad_records", "tiny_records", "huge_records", "tokens", "fixed_len_ragged"])
+def test_single_pass_kernel_agrees_with_the_three_kernel_chain(case):
+    """tk_json_ingest (one pass over the payload, tiles in shared memory) and the chain
+    tk_json_scan -> tk_compact -> tk_json_decode are independent decompositions of the same
+    contract: identical rows, lengths, masks, per-record status and index, batch ends, longest
+    records and commit matrix -- including tiles that take the single-pass kernel's scalar path."""
     from torchkafka_b200.engine import SlotEngine
-    log = syn.make_log(2, 3000, seed=41, layout="chunked", chunk=200)
-    vals = list(log._byte_values)
-    vals[17] = b"[1, 2,, 3]"                 # one malformed record: both must flag it
-    vals[18] = b" [ 1 ,\t2.5e3 , -0 ,1e400 ] "
-    log = RecordLog(vals, log.partitions, log.offsets)
-    sc = JsonArray(torch.float32, max_len=256, min_size=32)
+    vals, sc, B = _fused_case(case)
+    n = len(vals)
+    log = RecordLog(vals, (np.arange(n) // 7 % 16).astype(np.int32), np.arange(n) // 16 + (np.arange(n) % 7))
     outs = []
-    for warp in (False, True):
-        eng = SlotEngine(sc, 128, slot_bytes=16 << 20, slot_records=4000, n_slots=2, device=0, n_partitions=64)
-        eng.json_decode_warp = warp
-        n, nb = eng.fill_packed(0, log.values, log.starts.astype(np.uint32), log.partitions, log.offsets)
-        eng.submit(0, n, nb)
-        out = eng.process(0, n, None, None)
+    for flat in (True, False):
+        eng = SlotEngine(sc, B, slot_bytes=16 << 20, slot_records=n + 8, n_slots=2, device=0, n_partitions=16)
+        eng.set_json_flat(flat)
+        m, nb = eng.fill_packed(0, log.values, log.starts.astype(np.uint32), log.partitions, log.offsets)
+        eng.submit(0, m, nb)
+        out = eng.process(0, m, None, None)
         res = eng.result(0)
-        ln, st, kx = eng.record_debug(0, n)
-        rows = 128 + res.n_kept
-        outs.append(([t[128:rows].cpu() for t in out.tensors], res, st.copy(), kx.copy()))
+        ln, st, kx = eng.record_debug(0, m)
+        rows = B + res.n_kept
+        outs.append(([t[B:rows].cpu() for t in out.tensors], res, ln.copy(), st.copy(), kx.copy()))
         eng.close()
-    (ta, ra, sa, ka), (tb, rb, sb, kb) = outs
-    assert ra.n_kept == rb.n_kept and ra.n_closed == rb.n_closed and ra.first_error_rec == rb.first_error_rec == 17
-    assert np.array_equal(ka, kb) and np.array_equal(sa != 0, sb != 0)
+    (ta, ra, la, sa, ka), (tb, rb, lb, sb, kb) = outs
+    assert (ra.n_records, ra.n_kept, ra.n_closed, ra.carry_out) == (rb.n_records, rb.n_kept, rb.n_closed, rb.carry_out)
+    assert ra.n_errors == rb.n_errors and ra.first_error_rec == rb.first_error_rec
+    assert np.array_equal(la, lb) and np.array_equal(sa, sb) and np.array_equal(ka, kb)
     assert np.array_equal(ra.commit, rb.commit)
-    ok_rows = torch.ones(ra.n_kept, dtype=torch.bool)
+    assert np.array_equal(ra.batch_end, rb.batch_end) and np.array_equal(ra.batch_lmax, rb.batch_lmax)
+    # rows of records without an error are identical bit for bit (a bad record's row is unspecified)
+    good = torch.from_numpy(sa[ka >= 0] == 0)
+    assert int(good.sum()) > 0
     for x, y in zip(ta, tb):
         assert x.shape == y.shape
-        if x.dtype.is_floating_point:
-            assert torch.equal(x.view(torch.int32)[ok_rows], y.view(torch.int32)[ok_rows])
-        else:
-            assert torch.equal(x[ok_rows], y[ok_rows])
+        assert bit_equal(x[good], y[good])
 
 
 def test_images_table_fallback_when_fma_is_not_exact():

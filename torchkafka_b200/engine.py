@@ -19,6 +19,7 @@ Kernel sequence per slot (all on the caller's current CUDA stream):
 from __future__ import annotations
 
 import ctypes as C
+import os
 from typing import List, Optional
 
 import numpy as np
@@ -35,8 +36,11 @@ MAX_BATCHES_CAP = 16384
 #: default budget for the output tensors of one slot (rows of every plane)
 DEFAULT_OUTPUT_BYTES = 2 << 30
 #: kernels launched per slot by ``process``: carry rows, scan, plan (compaction + commit maxima,
-#: one kernel), decode / collate (one kernel), commit running max (one block, beside the decode)
+#: one kernel), decode / collate (one kernel), commit running max (one block, beside the decode);
+#: JSON arrays through the single-pass kernel: carry rows, tile table + resets, the single-pass
+#: kernel, commit running max
 LAUNCHES_PER_SLOT_JSON = 5
+LAUNCHES_PER_SLOT_JSON_FUSED = 4
 LAUNCHES_PER_SLOT_RAW = 5
 
 
@@ -142,10 +146,9 @@ class SlotEngine:
                 _native.check(self.lib.tk_ctx_set_object_fields(self.ctx, blob.ctypes.data, off.ctypes.data,
                                                                 len(schema.fields), self._stream()))
         self.launches = 0
-        #: use the earlier warp-per-record decode kernel (tk_json_decode_warp) instead of the flat
-        #: token-array path; kept for cross-checks and comparison runs
-        self.json_decode_warp = False
-        import os
+        #: JSON arrays: three-kernel chain (scan, plan, parse) instead of the single-pass kernel;
+        #: kept as an independent cross-check and for comparison runs (``set_json_flat``)
+        self.json_flat = bool(int(os.environ.get("TK_JSON_FLAT", "0") or 0))
         try:
             cores = len(os.sched_getaffinity(0))
         except AttributeError:  # pragma: no cover
@@ -328,7 +331,7 @@ class SlotEngine:
         is_json = isinstance(sc, JsonArray)
         with torch.cuda.device(self.device), torch.cuda.stream(self.stream):
             out = self._allocate(n)
-            if timers is None and not self.json_decode_warp:
+            if timers is None:
                 job = self._job(out, prev_slot, prev_out, resident)
                 _native.check(lib.tk_process_slot(ctx, slot, C.byref(job), st))
             else:
@@ -351,8 +354,7 @@ class SlotEngine:
                 P = out.planes
                 if is_json:
                     variable = sc.fixed_len is None
-                    decode = lib.tk_json_decode_warp if self.json_decode_warp else lib.tk_json_decode
-                    _native.check(decode(
+                    _native.check(lib.tk_json_decode(
                         ctx, slot, sc.kind, sc.max_len, sc.fixed_len or 0, C.byref(P[0]),
                         C.byref(P[1]) if variable else None, C.byref(P[2]) if variable else None, st))
                 elif isinstance(sc, JsonObject):
@@ -372,11 +374,18 @@ class SlotEngine:
                 if timers is not None:
                     timers.append((ev0, ev1))
                 _native.check(lib.tk_slot_fetch_result(ctx, slot, st))
-            self.launches += (LAUNCHES_PER_SLOT_JSON if is_json else LAUNCHES_PER_SLOT_RAW) \
+            per_slot = LAUNCHES_PER_SLOT_RAW if not is_json else (
+                LAUNCHES_PER_SLOT_JSON if (self.json_flat or timers is not None) else LAUNCHES_PER_SLOT_JSON_FUSED)
+            self.launches += per_slot \
                 - (1 if prev_out is None else 0) + (len(out.planes) - 1 if isinstance(sc, StructBytes) else 0)
             out.done = torch.cuda.Event()
             out.done.record(self.stream)
         return out
+
+    def set_json_flat(self, enabled: bool):
+        """JSON arrays through the three-kernel chain (True) or the single-pass kernel (False)."""
+        self.json_flat = bool(enabled)
+        _native.check(self.lib.tk_ctx_set_json_flat(self.ctx, 1 if enabled else 0))
 
     def set_timing(self, enabled: bool):
         """Bracket the decode / collate kernels of every following ``process`` call with CUDA
@@ -570,7 +579,7 @@ def release(eng: SlotEngine):
     try:
         eng.stream.synchronize()
         eng.set_timing(False)
-        eng.json_decode_warp = False
+        eng.set_json_flat(bool(int(os.environ.get("TK_JSON_FLAT", "0") or 0)))
         eng.reset()
     except Exception:
         eng.close()

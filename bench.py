@@ -342,6 +342,50 @@ def run_e2e(rlog, mode, device, min_seconds, rate_guess, max_records=None):
             "bytes": int(stats["bytes"]), "reps": reps, "stats": stats}
 
 
+def run_commit_barrier(rank, world, device, n_batches=600, warm=16):
+    """BASELINE config 5 with its cross-rank commit barrier: 64 partitions x 64-byte records, every
+    rank ingests its own partitions (p % world == rank) in batches of 256 through
+    auto_commit(loader, commit_barrier=True): after each batch the ranks exchange their commit
+    vectors (all_gather, host tensors over gloo), then commit.  Latency-bound by design
+    (SURVEY.md §8d row 5): reports the barrier's p50 / p99 and batches/s per rank."""
+    import torch
+    from torch.utils.data import DataLoader
+    from torchkafka_b200 import KafkaDataset, RawBytes, auto_commit
+    from torchkafka_b200.testing import stub_kafka as sk
+    from torchkafka_b200.testing import synthetic as syn
+    import numpy as np
+    B = 256
+    n = (n_batches + warm) * B
+    owned = np.asarray([p for p in range(PARTITIONS) if p % world == rank], dtype=np.int32)
+    i = np.arange(n)
+    clog = sk.RecordLog(syn.cfg5_values(n, seed=5 + rank), owned[i % len(owned)], i // len(owned))
+
+    class Cfg5(KafkaDataset):
+        payload_schema = RawBytes((64,), torch.uint8)
+        device_slot_bytes = 64 * B * 8              # small slots: latency, not throughput
+        device_index = device
+        max_partitions = PARTITIONS
+
+        @classmethod
+        def new_consumer(cls, *a, **k):
+            k.pop("enable_auto_commit", None)
+            return sk.KafkaConsumer(*a, log=clog, keep_commit_log=False, **k)
+
+    ds = Cfg5("topic", group_id="cfg5")
+    seen, t0 = 0, None
+    for _batch in auto_commit(DataLoader(ds, batch_size=B), commit_barrier=True):
+        if seen == warm:
+            torch.cuda.synchronize()
+            t0 = time.perf_counter()
+        seen += 1
+    torch.cuda.synchronize()
+    dt = time.perf_counter() - t0
+    lat = sorted(list(ds.commit_barrier_us)[warm:warm + n_batches])
+    ds.close()
+    pct = lambda q: lat[min(len(lat) - 1, int(q * len(lat)))] if lat else float("nan")   # noqa: E731
+    return {"p50_us": pct(0.5), "p99_us": pct(0.99), "batches_per_s": (seen - warm) / dt, "batches": seen - warm}
+
+
 # --------------------------------------------------------------------------- CPU arms (oracle)
 def cpu_process_factory():
     import torch
@@ -518,12 +562,17 @@ def main_gpu(args):
             arms[mode] = run_e2e(base, mode, device, E2E_MIN_SECONDS, 20e6,
                                  max_records=POLL_MAX_OBJECTS if mode == "poll" else None)
     barrier()
+    cb = None
+    if world > 1 and not args.skip_e2e:
+        cb = run_commit_barrier(rank, world, device)
+        barrier()
 
     order = ["poll", "packed", "raw", "raw_into", "raw_dma"]
     cols = [dev["ms"] / 1e3, float(dev["records"])]
     for m in order:
         a = arms.get(m)
         cols += [a["seconds"], float(a["records"]), float(a["bytes"])] if a else [0.0, 0.0, 0.0]
+    cols += [cb["p50_us"], cb["p99_us"], cb["batches_per_s"]] if cb else [0.0, 0.0, 0.0]
     t = torch.tensor(cols, dtype=torch.float64)
     tmax, tsum = t.clone(), t.clone()
     if world > 1:
@@ -607,6 +656,13 @@ def main_gpu(args):
         for m in ("packed", "raw", "raw_into", "raw_dma"):
             if m in lines:
                 line["e2e_" + m] = lines[m]
+        if cb:
+            k = 2 + 3 * len(order)
+            line["commit_barrier"] = {
+                "workload": "cfg5: 64 partitions x 64-byte records, batch 256, auto_commit(loader, commit_barrier=True)",
+                "ranks": world, "transport": "torch.distributed all_gather of int64[65] host tensors (gloo)",
+                "p50_us_max_over_ranks": float(tmax[k]), "p99_us_max_over_ranks": float(tmax[k + 1]),
+                "batches_per_s_per_rank": float(tsum[k + 2]) / world, "batches_timed": cb["batches"]}
         bad = [m for m, l in lines.items() if l["link_frac"] > 1.0]
         if bad:
             log(f"INVALID: link_frac > 1 for {bad}: the timed region skipped work")

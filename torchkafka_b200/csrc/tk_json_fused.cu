@@ -55,14 +55,14 @@ struct fused_args {
     int32_t*        rec_len;
     int32_t*        rec_status;
     int32_t*        rec_kidx;
-    const uint32_t* tile_first;      // [n_tiles + 1]
+    const uint2*    tile_info;       // [n_tiles + 1] {first record, its first byte}
     uint32_t        n_tiles;
     uint32_t        win_bytes;       // shared-memory window (multiple of FZ_CHUNK)
     uint32_t        max_recs;        // per-tile record tables
     unsigned long long* tile_agg;
     unsigned long long* tile_incl;
     uint32_t*       tile_flag;
-    uint32_t*       ctr;             // [0] tile ticket, [1] finished tiles
+    uint32_t*       ctr;             // [0] tile ticket, [2] blocks that have left
     uint32_t        epoch;
     tk_state*       state;
     tk_result_t*    res;
@@ -79,7 +79,7 @@ struct fused_args {
 struct prep_args {
     const tk_rec_t* recs;
     uint32_t        n, n_tiles;
-    uint32_t*       tile_first;
+    uint2*          tile_info;       // [n_tiles + 1] {first record of the tile, its first byte}
     tk_result_t*    res;
     tk_plan_reset   reset;
 };
@@ -103,7 +103,8 @@ __global__ void __launch_bounds__(256) k_fused_prep(const prep_args a) {
     for (uint32_t i = gtid; i <= a.n; i += nthr) {
         const uint32_t lo = i == 0 ? 0u : fz_tile_of(a.recs[i - 1].start, a.n_tiles) + 1u;
         const uint32_t hi = i == a.n ? a.n_tiles : fz_tile_of(a.recs[i].start, a.n_tiles);
-        for (uint32_t t = lo; t <= hi; ++t) a.tile_first[t] = i;
+        const uint32_t byte = a.recs[i].start;            // (i == n: the closing entry, start = n_bytes)
+        for (uint32_t t = lo; t <= hi; ++t) a.tile_info[t] = make_uint2(i, byte);
     }
 }
 
@@ -234,14 +235,45 @@ __device__ __forceinline__ unsigned long long fz_lookback(const fused_args& a, u
 //   rfirst  [max_recs] u16     where the record's first element starts (behind '[')
 //   rlen    [max_recs] u16     element count
 //   rrow    [max_recs] u32     output row, 0xFFFFFFFF if skipped
+//   rpart   [max_recs] u32     partition | flags of the record header
 //   rinfo   [max_recs] u8      FR_*
 static size_t fz_smem_bytes(uint32_t win_bytes, uint32_t max_recs) {
     const size_t nch = win_bytes / FZ_CHUNK;
     size_t b = win_bytes + 64;
-    b += 4 * nch + 4 * (nch + 1) + 4 * (FZ_TOKCAP + 1) + 4 * (size_t)max_recs;       // u32 arrays
+    b += 4 * nch + 4 * (nch + 1) + 4 * (FZ_TOKCAP + 1) + 8 * (size_t)max_recs;       // u32 arrays
     b += 2 * nch + 2 * (size_t)(max_recs + 1) * 2 + 2 * (size_t)max_recs * 2;         // u16 arrays
     b += max_recs;                                                                    // u8
     return (b + 64 + 15) & ~(size_t)15;
+}
+
+// Segment list of one round [sbase, sbase + FZ_TOKCAP]: the first segment of every record and one
+// behind every comma, window position | local record << 16, by `nthr` threads (`t` = this one).
+__device__ __forceinline__ void fz_scatter(uint32_t sbase, uint32_t n_seg, uint32_t m, uint32_t nch, uint32_t t, uint32_t nthr,
+                                           const uint32_t* cmask, const uint32_t* pre, const uint16_t* rcnt,
+                                           const uint16_t* rst, const uint16_t* fseg, const uint16_t* rfirst, uint32_t* tok) {
+    for (uint32_t k = t; k < m; k += nthr) {
+        const uint32_t s = (uint32_t)fseg[k] - sbase;
+        if (s <= FZ_TOKCAP) tok[s] = (uint32_t)rfirst[k] | (k << 16);
+    }
+    for (uint32_t c = t; c < nch; c += nthr) {
+        uint32_t mk = cmask[c];
+        if (!mk) continue;
+        const uint32_t pc = pre[c];
+        uint32_t kc = pc & 0xFFFFu;                         // commas before the chunk
+        const uint32_t rbefore = pc >> 16;                   // records started before the chunk
+        uint32_t cand = rbefore;
+        const uint32_t cend = rbefore + rcnt[c];
+        uint32_t k = rbefore - 1u;                           // the record the chunk starts in
+        while (mk) {
+            const uint32_t b = __ffs(mk) - 1;
+            mk &= mk - 1;
+            const uint32_t pos = c * FZ_CHUNK + b;
+            while (cand < cend && rst[cand] <= pos) { k = cand; ++cand; }
+            const uint32_t s = kc + k + 1u - sbase;
+            if (s <= FZ_TOKCAP) tok[s] = (pos + 1u) | (k << 16);
+            ++kc;
+        }
+    }
 }
 
 template <int KIND>
@@ -251,7 +283,8 @@ __global__ void __launch_bounds__(FZ_THREADS) k_json_fused(const fused_args a) {
     __shared__ parse_tables tb;
     __shared__ __align__(8) uint64_t s_bar;
     __shared__ uint32_t s_warp_tot[32];
-    __shared__ uint32_t s_total, s_tile, s_last, s_kept, s_elems;
+    __shared__ uint32_t s_total, s_kept, s_elems;
+    __shared__ uint32_t s_next[5];          // the block's next tile: index, first record, first byte, end record, end byte
     __shared__ unsigned long long s_excl;
 
     const uint32_t tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
@@ -261,13 +294,15 @@ __global__ void __launch_bounds__(FZ_THREADS) k_json_fused(const fused_args a) {
     uint32_t* pre = cmask + nch;
     uint32_t* tok = pre + nch + 1;
     uint32_t* rrow = tok + FZ_TOKCAP + 1;
-    uint16_t* rcnt = reinterpret_cast<uint16_t*>(rrow + a.max_recs);
+    uint32_t* rpart = rrow + a.max_recs;
+    uint16_t* rcnt = reinterpret_cast<uint16_t*>(rpart + a.max_recs);
     uint16_t* rst = rcnt + nch;
     uint16_t* fseg = rst + a.max_recs + 1;
     uint16_t* rfirst = fseg + a.max_recs + 1;
     uint16_t* rlen = rfirst + a.max_recs;
     uint8_t* rinfo = reinterpret_cast<uint8_t*>(rlen + a.max_recs);
 
+    tk_pdl_launch_dependents();             // (the commit kernel behind this one waits for all of it)
     parse_tables_init(tb);                  // constants only: overlaps the tail of the previous kernel
     if (tid == 0) {
         mbar_init(&s_bar, 1);
@@ -275,7 +310,6 @@ __global__ void __launch_bounds__(FZ_THREADS) k_json_fused(const fused_args a) {
     }
     __syncthreads();
     tk_pdl_wait();
-    tk_pdl_launch_dependents();             // after the wait: k_commit_final may then skip its own (tk_plan.cu)
 
     const uint32_t B = a.batch_size;
     const uint32_t carry = a.state->carry_rows;
@@ -284,29 +318,47 @@ __global__ void __launch_bounds__(FZ_THREADS) k_json_fused(const fused_args a) {
     T* values = reinterpret_cast<T*>(a.values.base);
     uint32_t phase = 0;
 
+    // Tiles are taken from a ticket counter, one ahead: while a tile is processed, thread 0 already
+    // holds the ticket of the block's next tile and has its bounds on the way, so neither the
+    // atomic nor the dependent loads of the tile table are waited for.
+    if (tid == 0) {
+        const uint32_t t = atomicAdd(&a.ctr[0], 1u);
+        s_next[0] = t;
+        if (t < a.n_tiles) {
+            const uint2 x = a.tile_info[t], y = a.tile_info[t + 1];
+            s_next[1] = x.x; s_next[2] = x.y; s_next[3] = y.x; s_next[4] = y.y;
+        }
+    }
+    __syncthreads();
+
     for (;;) {
-        if (tid == 0) s_tile = atomicAdd(&a.ctr[0], 1u);
-        __syncthreads();
-        const uint32_t tile = s_tile;
+        const uint32_t tile = s_next[0];
         if (tile >= a.n_tiles) break;
-        const uint32_t r0 = a.tile_first[tile], r1 = a.tile_first[tile + 1];
+        const uint32_t r0 = s_next[1], lo = s_next[2], r1 = s_next[3], hi = s_next[4];
         const uint32_t m = r1 - r0;
-        const uint32_t lo = m ? a.recs[r0].start : 0u, hi = m ? a.recs[r1].start : 0u;
         const uint32_t base = lo & ~15u;                             // window origin in the slot buffer
-        const uint32_t span = ((hi + 15u) & ~15u) - base;            // bytes to bring in
+        const uint32_t span = m ? ((hi + 15u) & ~15u) - base : 0u;   // bytes to bring in
         // (strictly inside the window: positions up to `span` index the per-chunk tables)
         const bool fast_tile = m && span + FZ_CHUNK <= a.win_bytes && m <= a.max_recs;
-        if (tid == 0) { s_kept = 0; s_elems = 0; }
-        __syncthreads();
-
-        // ---------------- cut
-        if (fast_tile) {
-            if (tid == 0 && span) {
+        __syncthreads();                                             // everyone has read s_next
+        uint32_t next_ticket = 0;
+        if (tid == 0) {
+            s_kept = 0; s_elems = 0;
+            if (fast_tile && span) {
                 mbar_expect_tx(&s_bar, span);
                 bulk_load(win, a.bytes + base, span, &s_bar);
             }
-            // meanwhile: record starts, chunk tables cleared
-            for (uint32_t k = tid; k <= m; k += FZ_THREADS) rst[k] = (uint16_t)(a.recs[r0 + k].start - base);
+            next_ticket = atomicAdd(&a.ctr[0], 1u);
+        }
+
+        // ---------------- cut
+        if (fast_tile) {
+            // meanwhile: record headers (start, partition | flags), chunk tables cleared
+            for (uint32_t k = tid; k <= m; k += FZ_THREADS) {
+                const uint2 h = __ldg(reinterpret_cast<const uint2*>(a.recs + r0 + k));
+                rst[k] = (uint16_t)(h.x - base);
+                if (k < m) rpart[k] = h.y;
+            }
             for (uint32_t c = tid; c < nch; c += FZ_THREADS) rcnt[c] = 0;
             __syncthreads();
             // records starting in each chunk (several may: short or empty records)
@@ -349,7 +401,7 @@ __global__ void __launch_bounds__(FZ_THREADS) k_json_fused(const fused_args a) {
             for (uint32_t k = tid; k < m; k += FZ_THREADS) {
                 const uint32_t i = r0 + k;
                 const uint32_t ra = rst[k], rb = rst[k + 1];
-                const int32_t pflags = a.recs[i].partition & TK_REC_FLAGS;
+                const int32_t pflags = (int32_t)rpart[k] & TK_REC_FLAGS;
                 const uint32_t ca = (pre[ra / FZ_CHUNK] & 0xFFFFu) + __popc(cmask[ra / FZ_CHUNK] & ((1u << (ra & 31u)) - 1u));
                 uint32_t len = 0, first = ra, info = 0;
                 int status;
@@ -397,6 +449,7 @@ __global__ void __launch_bounds__(FZ_THREADS) k_json_fused(const fused_args a) {
             if (lane == 0 && (my_kept | my_elems)) { atomicAdd(&s_kept, my_kept); atomicAdd(&s_elems, my_elems); }
         } else if (m) {
             // scalar path: thread per record out of global memory
+            __syncthreads();                                         // s_kept / s_elems are reset
             uint32_t my_kept = 0, my_elems = 0;
             for (uint32_t k = tid; k < m; k += FZ_THREADS) {
                 const uint32_t i = r0 + k;
@@ -437,13 +490,18 @@ __global__ void __launch_bounds__(FZ_THREADS) k_json_fused(const fused_args a) {
         }
         __syncthreads();
 
-        // ---------------- place: publish the tile's sum, look back for its exclusive prefix
+        // ---------------- place, first half: warp 0 publishes the tile's sum and looks back for its
+        // exclusive prefix (and fetches the next tile's bounds) while the other warps scatter the
+        // first round of segments
+        const uint32_t n_seg = fast_tile ? (uint32_t)fseg[m] : 0u;
         if (wid == 0) {
             const unsigned long long tot = ((unsigned long long)s_kept << FZ_PACK_SHIFT) + s_elems;
+            uint2 nx = make_uint2(0, 0), ny = make_uint2(0, 0);
             if (lane == 0) {
                 a.tile_agg[tile] = tot;
                 if (tile == 0) a.tile_incl[0] = tot;
                 fz_st_release(a.tile_flag + tile, (a.epoch << 2) | (tile == 0 ? 2u : 1u));
+                if (next_ticket < a.n_tiles) { nx = a.tile_info[next_ticket]; ny = a.tile_info[next_ticket + 1]; }
             }
             const unsigned long long excl = tile ? fz_lookback(a, tile, lane) : 0ull;
             if (lane == 0) {
@@ -452,7 +510,10 @@ __global__ void __launch_bounds__(FZ_THREADS) k_json_fused(const fused_args a) {
                     fz_st_release(a.tile_flag + tile, (a.epoch << 2) | 2u);
                 }
                 s_excl = excl;
+                s_next[0] = next_ticket; s_next[1] = nx.x; s_next[2] = nx.y; s_next[3] = ny.x; s_next[4] = ny.y;
             }
+        } else if (fast_tile) {
+            fz_scatter(0, n_seg, m, nch, tid - 32, FZ_THREADS - 32, cmask, pre, rcnt, rst, fseg, rfirst, tok);
         }
         __syncthreads();
         const uint32_t excl_kept = (uint32_t)(s_excl >> FZ_PACK_SHIFT);
@@ -517,35 +578,12 @@ __global__ void __launch_bounds__(FZ_THREADS) k_json_fused(const fused_args a) {
                 if (row != 0xFFFFFFFFu)
                     json_write_row<sizeof(T)>(a.values, a.lengths, a.mask, a.max_len, row, rlen[k], lane, vec_values, vec_mask);
             }
-            // ---------------- parse: segments in rounds of FZ_TOKCAP
-            const uint32_t n_seg = fseg[m];
+            // ---------------- parse: segments in rounds of FZ_TOKCAP (round 0 is already scattered)
             for (uint32_t sbase = 0; sbase < n_seg; sbase += FZ_TOKCAP) {
-                // scatter: the first segment of every record ...
-                for (uint32_t k = tid; k < m; k += FZ_THREADS) {
-                    const uint32_t s = (uint32_t)fseg[k] - sbase;
-                    if (s <= FZ_TOKCAP) tok[s] = (uint32_t)rfirst[k] | (k << 16);
+                if (sbase) {
+                    fz_scatter(sbase, n_seg, m, nch, tid, FZ_THREADS, cmask, pre, rcnt, rst, fseg, rfirst, tok);
+                    __syncthreads();
                 }
-                // ... and one behind every comma
-                for (uint32_t c = tid; c < nch; c += FZ_THREADS) {
-                    uint32_t mk = cmask[c];
-                    if (!mk) continue;
-                    const uint32_t pc = pre[c];
-                    uint32_t kc = pc & 0xFFFFu;                         // commas before the chunk
-                    const uint32_t rbefore = pc >> 16;                   // records started before the chunk
-                    uint32_t cand = rbefore;
-                    const uint32_t cend = rbefore + rcnt[c];
-                    uint32_t k = rbefore - 1u;                           // the record the chunk starts in
-                    while (mk) {
-                        const uint32_t b = __ffs(mk) - 1;
-                        mk &= mk - 1;
-                        const uint32_t pos = c * FZ_CHUNK + b;
-                        while (cand < cend && rst[cand] <= pos) { k = cand; ++cand; }
-                        const uint32_t s = kc + k + 1u - sbase;
-                        if (s <= FZ_TOKCAP) tok[s] = (pos + 1u) | (k << 16);
-                        ++kc;
-                    }
-                }
-                __syncthreads();
                 const uint32_t cnt = min(FZ_TOKCAP, n_seg - sbase);
                 for (uint32_t s = tid; s < cnt; s += FZ_THREADS) {
                     const uint32_t t = tok[s];
@@ -573,7 +611,7 @@ __global__ void __launch_bounds__(FZ_THREADS) k_json_fused(const fused_args a) {
                     const uint32_t row = rrow[k];
                     if (row != 0xFFFFFFFFu && e < a.max_len) values[(uint64_t)row * a.max_len + e] = v;
                 }
-                __syncthreads();
+                if (sbase + FZ_TOKCAP < n_seg) __syncthreads();         // the next round overwrites tok
             }
         } else if (m) {
             // scalar path: warp per record for the row, thread per record for the elements
@@ -604,35 +642,32 @@ __global__ void __launch_bounds__(FZ_THREADS) k_json_fused(const fused_args a) {
                 }
             }
         }
-
-        // ---------------- the last tile to finish writes the slot's result header
-        __threadfence();
-        __syncthreads();
-        if (tid == 0) s_last = atomicAdd(&a.ctr[1], 1u) == a.n_tiles - 1 ? 1u : 0u;
-        __syncthreads();
-        if (s_last) {
-            __threadfence();
-            if (tid == 0) {
-                const unsigned long long total = *(volatile unsigned long long*)&a.tile_incl[a.n_tiles - 1];
-                const uint32_t n_kept = (uint32_t)(total >> FZ_PACK_SHIFT);
-                const unsigned long long n_tokens = total & ((1ull << FZ_PACK_SHIFT) - 1);
-                tk_result_t* res = a.res;
-                res->n_records = a.n;
-                res->n_kept = n_kept;
-                res->carry_in = carry;
-                res->carry_out = (carry + n_kept) % B;
-                res->n_closed = (carry + n_kept) / B;
-                res->batch_size = B;
-                res->reserved[0] = (uint32_t)(n_tokens > 0xFFFFFFFFull ? 0xFFFFFFFFu : n_tokens);
-                a.state->carry_rows = (carry + n_kept) % B;
-                a.ctr[1] = 0;
-            }
-        }
+        __syncthreads();                    // the window and the tables are free for the next tile
     }
-    // every block leaves through the ticket counter: the last one to see it exhausted resets it
+
+    // Every block leaves through this counter; all tiles are done when the last one does, and it
+    // writes the slot's result header and resets the counters for the slot's next pass.
+    __threadfence();
+    __syncthreads();
     if (tid == 0) {
         const uint32_t left = atomicAdd(&a.ctr[2], 1u);
-        if (left == gridDim.x - 1) { a.ctr[0] = 0; a.ctr[2] = 0; }
+        if (left == gridDim.x - 1) {
+            __threadfence();
+            const unsigned long long total = *(volatile unsigned long long*)&a.tile_incl[a.n_tiles - 1];
+            const uint32_t n_kept = (uint32_t)(total >> FZ_PACK_SHIFT);
+            const unsigned long long n_tokens = total & ((1ull << FZ_PACK_SHIFT) - 1);
+            tk_result_t* res = a.res;
+            res->n_records = a.n;
+            res->n_kept = n_kept;
+            res->carry_in = carry;
+            res->carry_out = (carry + n_kept) % B;
+            res->n_closed = (carry + n_kept) / B;
+            res->batch_size = B;
+            res->reserved[0] = (uint32_t)(n_tokens > 0xFFFFFFFFull ? 0xFFFFFFFFu : n_tokens);
+            a.state->carry_rows = (carry + n_kept) % B;
+            a.ctr[0] = 0;
+            a.ctr[2] = 0;
+        }
     }
 }
 
@@ -644,7 +679,7 @@ int tk_ensure_fused(tk_ctx* ctx) {
     const size_t tiles = (size_t)(ctx->slot_bytes / FZ_TILE_BYTES) + 2;
     for (int i = 0; i < ctx->n_slots; ++i) {
         tk_slot& s = ctx->slots[i];
-        TK_CUDA(cudaMalloc(&s.d.fz_tile_first, sizeof(uint32_t) * (tiles + 1)));
+        TK_CUDA(cudaMalloc(&s.d.fz_tile_first, sizeof(uint2) * (tiles + 1)));
         TK_CUDA(cudaMalloc(&s.d.fz_agg, sizeof(unsigned long long) * tiles));
         TK_CUDA(cudaMalloc(&s.d.fz_incl, sizeof(unsigned long long) * tiles));
         TK_CUDA(cudaMalloc(&s.d.fz_flag, sizeof(uint32_t) * tiles));
@@ -711,7 +746,7 @@ extern "C" int tk_json_ingest(tk_ctx* ctx, int slot, int dtype, uint32_t max_len
     TK_REQUIRE((size_t)n_tiles + 1 <= ctx->fz_tiles, "slot bytes exceed the context geometry");
 
     prep_args p;
-    p.recs = s.d.recs; p.n = n; p.n_tiles = n_tiles; p.tile_first = s.d.fz_tile_first; p.res = s.d.result;
+    p.recs = s.d.recs; p.n = n; p.n_tiles = n_tiles; p.tile_info = reinterpret_cast<uint2*>(s.d.fz_tile_first); p.res = s.d.result;
     p.reset = tk_plan_reset_args(ctx, slot);
     const uint32_t pblocks = min(max((n + 256u) / 256u, 1u), 148u * 8u);
     TK_LAUNCH_PDL(k_fused_prep, pblocks, 256, st, p);
@@ -728,7 +763,7 @@ extern "C" int tk_json_ingest(tk_ctx* ctx, int slot, int dtype, uint32_t max_len
     a.bytes = s.d.bytes; a.recs = s.d.recs; a.n = n; a.n_bytes = n_bytes;
     a.max_len = max_len; a.min_size = min_size; a.fixed_len = fixed_len; a.batch_size = batch_size;
     a.rec_len = s.d.rec_len; a.rec_status = s.d.rec_status; a.rec_kidx = s.d.rec_kidx;
-    a.tile_first = s.d.fz_tile_first; a.n_tiles = n_tiles;
+    a.tile_info = reinterpret_cast<const uint2*>(s.d.fz_tile_first); a.n_tiles = n_tiles;
     a.win_bytes = FZ_TILE_BYTES + (uint32_t)over;                 // <= 57344: positions fit 16 bits
     a.max_recs = a.win_bytes <= 32768 ? 768u : 512u;
     a.tile_agg = s.d.fz_agg; a.tile_incl = s.d.fz_incl; a.tile_flag = s.d.fz_flag; a.ctr = s.d.fz_ctr;

@@ -28,7 +28,9 @@ extern "C" int tk_process_slot(tk_ctx* ctx, int slot, const tk_job_t* job, void*
                             job->n_planes > 2 ? &job->cur[2] : nullptr, stream);
         if (rc) return rc;
         if (ctx->timing) { TK_CUDA(cudaEventRecord(s.ev_dec1, (cudaStream_t)stream)); s.dec_timed = true; }
-        rc = tk_commit_final(ctx, slot, (s.n_records == 0 || ctx->timing) ? 1 : 0, stream);
+        // the per-(batch, partition) maxima are produced inside the single-pass kernel: the running
+        // max has to wait for all of it
+        rc = tk_commit_final(ctx, slot, 1, stream);
         if (rc) return rc;
         return tk_slot_fetch_result(ctx, slot, stream);
     }

@@ -439,7 +439,7 @@ def test_device_split_of_kafka_python_golden_batches():
     ptr, _ = eng.device_views(0)
 
     class _Slot:
-        __cuda_array_interface__ = {"shape": (nbytes,), "typestr": "|u1", "data": (ptr, True), "version": 2}
+        __cuda_array_interface__ = {"shape": (nbytes,), "typestr": "|u1", "data": (ptr, False), "version": 2}
 
     assert bytes(torch.as_tensor(_Slot(), device="cuda").cpu().numpy()) == b"123" * 3
     eng.close()

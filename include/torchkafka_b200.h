@@ -173,13 +173,14 @@ int tk_json_decode(tk_ctx* ctx, int slot, int dtype, uint32_t max_len, uint32_t 
  * compaction, batch boundaries, the per-(batch, partition) commit maxima, pad / length / mask rows
  * and the parsed values, by one persistent kernel that brings every tile of the byte buffer into
  * shared memory once (bulk asynchronous copy) and chains the tiles' kept counts with a decoupled
- * look-back.  Follow with tk_commit_offsets and tk_slot_fetch_result.  This is what tk_process_slot
- * runs for TK_SCHEMA_JSON; tk_ctx_set_json_flat(ctx, 1) (or TK_JSON_FLAT=1 in the environment when
- * the context is created) selects the three-kernel chain instead. */
+ * look-back.  Follow with tk_commit_offsets and tk_slot_fetch_result.  HBM traffic is the algorithmic
+ * minimum (payload read once), but the kernel is bound by its per-tile synchronisation and is the
+ * slower of the two paths today; tk_process_slot runs the three-kernel chain for TK_SCHEMA_JSON unless
+ * tk_ctx_set_json_fused(ctx, 1) (or TK_JSON_FUSED=1 in the environment when the context is created). */
 int tk_json_ingest(tk_ctx* ctx, int slot, int dtype, uint32_t max_len, uint32_t min_size,
                    uint32_t fixed_len, uint32_t batch_size, const tk_plane_t* values,
                    const tk_plane_t* lengths, const tk_plane_t* mask, void* stream);
-int tk_ctx_set_json_flat(tk_ctx* ctx, int enabled);
+int tk_ctx_set_json_fused(tk_ctx* ctx, int enabled);
 
 /* ---- K1c + K3: fixed-layout bytes -> rows (torch.frombuffer + torch.stack) -- */
 int tk_collate_raw(tk_ctx* ctx, int slot, uint64_t record_bytes, const tk_plane_t* out,

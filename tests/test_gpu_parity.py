@@ -305,9 +305,9 @@ def test_single_pass_kernel_agrees_with_the_three_kernel_chain(case):
     n = len(vals)
     log = RecordLog(vals, (np.arange(n) // 7 % 16).astype(np.int32), np.arange(n) // 16 + (np.arange(n) % 7))
     outs = []
-    for flat in (True, False):
+    for fused in (False, True):
         eng = SlotEngine(sc, B, slot_bytes=16 << 20, slot_records=n + 8, n_slots=2, device=0, n_partitions=16)
-        eng.set_json_flat(flat)
+        eng.set_json_fused(fused)
         m, nb = eng.fill_packed(0, log.values, log.starts.astype(np.uint32), log.partitions, log.offsets)
         eng.submit(0, m, nb)
         out = eng.process(0, m, None, None)
@@ -608,3 +608,17 @@ def test_short_records_under_a_wide_schema_stay_inside_the_output_budget():
             assert row[:m] == json.loads(vals[k]) and not any(row[m:])
             k += 1
     assert k == n
+
+
+@pytest.mark.parametrize("cfg,schema,batch", [
+    (1, JsonArray(torch.float32, fixed_len=8), 4),
+    (2, JsonArray(torch.float32, max_len=256, min_size=32), 256),
+    (2, JsonArray(torch.float64, max_len=256, min_size=100), 64),
+    (3, TokenList(torch.int32, max_len=2048), 32),
+])
+def test_single_pass_kernel_through_the_public_api(cfg, schema, batch):
+    """The same oracle comparison as the config tests above, with the dataset switched to the
+    single-pass JSON kernel (small slots: batches straddle slots, carries, many tiles)."""
+    log = syn.make_log(cfg, 4000 if cfg != 3 else 700, seed=60 + cfg, partitions=8, layout="chunked", chunk=30)
+    gpu = run_gpu(log, schema, batch, slot_bytes=400_000, device_json_single_pass=True)
+    assert_same(gpu, run_oracle(log, schema, batch), schema)

@@ -12,8 +12,8 @@
 // every payload byte once and keeps everything in between in shared memory:
 //
 //   tile      the records whose first byte lies in one TILE_BYTES stretch of the slot's byte buffer
-//             (k_fused_prep finds the first record of every tile).  Persistent blocks take tiles in
-//             order (ticket counter).
+//             (k_fused_prep finds the first record and first byte of every tile).  Persistent blocks
+//             take tiles in order (ticket counter).
 //   load      the tile's bytes come in with one bulk asynchronous copy (cp.async.bulk, completion
 //             on an mbarrier) into a shared-memory window; record starts come in meanwhile.
 //   cut       every thread classifies 32-byte chunks of the window: comma masks, their prefix
@@ -39,7 +39,7 @@
 #define FZ_THREADS 256
 #define FZ_WARPS (FZ_THREADS / 32)
 #define FZ_TILE_BYTES 16384u
-#define FZ_TOKCAP 2048u              // segments per round
+#define FZ_TOKCAP 1536u              // segments per round
 #define FZ_CHUNK 32u                 // bytes per comma-mask word
 
 // record info bits kept in shared memory
@@ -196,12 +196,17 @@ __device__ __forceinline__ uint32_t fz_block_scan(uint32_t v, uint32_t* warp_tot
     return r;
 }
 
-// exclusive prefix (packed kept << 40 | elements) of tile `tile`: warp 0, result in every lane
-__device__ __forceinline__ unsigned long long fz_lookback(const fused_args& a, uint32_t tile, uint32_t lane) {
+// Exclusive prefix (packed kept << 40 | elements) of tile `tile`, whole block, result in every
+// thread.  Decoupled look-back, FZ_THREADS predecessors per round: with hundreds of tiles in flight
+// the nearest predecessor that already knows its inclusive sum is typically a few hundred tiles
+// back, and a round costs one acquire-load latency whatever its width.
+__device__ __forceinline__ unsigned long long fz_lookback(const fused_args& a, uint32_t tile, uint32_t* s_first,
+                                                          unsigned long long* s_sum) {
+    const uint32_t tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
     unsigned long long excl = 0;
     int p = (int)tile - 1;
     while (p >= 0) {
-        const int q = p - (int)lane;                      // lane 0 looks at the nearest predecessor
+        const int q = p - (int)tid;                       // thread 0 looks at the nearest predecessor
         uint32_t st = 2;                                  // tiles before 0: "inclusive sum 0"
         if (q >= 0) {
             uint32_t f;
@@ -209,14 +214,22 @@ __device__ __forceinline__ unsigned long long fz_lookback(const fused_args& a, u
             st = f & 3u;
         }
         const uint32_t full = __ballot_sync(0xffffffffu, st == 2);
-        const uint32_t first = full ? (uint32_t)__ffs(full) - 1 : 32u;      // nearest inclusive sum
+        if (lane == 0) s_first[wid] = full ? wid * 32u + (uint32_t)__ffs(full) - 1u : 0xFFFFFFFFu;
+        __syncthreads();
+        uint32_t first = 0xFFFFFFFFu;                     // nearest inclusive sum of this round
+#pragma unroll
+        for (int w = 0; w < FZ_WARPS; ++w) first = min(first, s_first[w]);
         unsigned long long v = 0;
-        if (q >= 0 && lane <= first) v = lane == first ? a.tile_incl[q] : a.tile_agg[q];
+        if (q >= 0 && tid <= first) v = tid == first ? a.tile_incl[q] : a.tile_agg[q];
 #pragma unroll
         for (int d = 16; d > 0; d >>= 1) v += __shfl_xor_sync(0xffffffffu, v, d);
-        excl += v;
-        if (full) break;
-        p -= 32;
+        if (lane == 0) s_sum[wid] = v;
+        __syncthreads();
+#pragma unroll
+        for (int w = 0; w < FZ_WARPS; ++w) excl += s_sum[w];
+        __syncthreads();                                  // s_first / s_sum are reused by the next round
+        if (first != 0xFFFFFFFFu) break;
+        p -= FZ_THREADS;
     }
     return excl;
 }
@@ -226,6 +239,7 @@ __device__ __forceinline__ unsigned long long fz_lookback(const fused_args& a, u
 // ---------------------------------------------------------------- shared-memory layout
 // Dynamic shared memory, carved by the kernel:
 //   win     [win_bytes + 64]   the tile's bytes (16-byte aligned, padded for the fast lane's window reads)
+//   val     [TOKCAP]   T       values of the first round of segments, until their rows are known
 //   cmask   [nch]      u32     comma bits per 32-byte chunk
 //   pre     [nch + 1]  u32     exclusive prefix per chunk: commas (low 16 bits) | record starts (high 16)
 //   rcnt    [nch]      u16     records starting in the chunk
@@ -237,9 +251,9 @@ __device__ __forceinline__ unsigned long long fz_lookback(const fused_args& a, u
 //   rrow    [max_recs] u32     output row, 0xFFFFFFFF if skipped
 //   rpart   [max_recs] u32     partition | flags of the record header
 //   rinfo   [max_recs] u8      FR_*
-static size_t fz_smem_bytes(uint32_t win_bytes, uint32_t max_recs) {
+static size_t fz_smem_bytes(uint32_t win_bytes, uint32_t max_recs, size_t elem_bytes) {
     const size_t nch = win_bytes / FZ_CHUNK;
-    size_t b = win_bytes + 64;
+    size_t b = win_bytes + 64 + elem_bytes * FZ_TOKCAP;
     b += 4 * nch + 4 * (nch + 1) + 4 * (FZ_TOKCAP + 1) + 8 * (size_t)max_recs;       // u32 arrays
     b += 2 * nch + 2 * (size_t)(max_recs + 1) * 2 + 2 * (size_t)max_recs * 2;         // u16 arrays
     b += max_recs;                                                                    // u8
@@ -276,8 +290,48 @@ __device__ __forceinline__ void fz_scatter(uint32_t sbase, uint32_t n_seg, uint3
     }
 }
 
+// One round of segments, thread per element out of the window.  STAGE: the value goes to the
+// staging array (its row is not known yet); else straight to the record's row.
+template <int KIND, bool STAGE>
+__device__ __forceinline__ void fz_parse_round(const fused_args& a, const parse_tables& tb, const uint8_t* win,
+                                               const uint32_t* tok, const uint8_t* rinfo, const uint16_t* fseg,
+                                               const uint16_t* rlen, const uint16_t* rst, const uint32_t* rrow,
+                                               typename tk_elem<KIND>::type* val, typename tk_elem<KIND>::type* values,
+                                               uint32_t sbase, uint32_t cnt, uint32_t r0, uint32_t tid) {
+    typedef typename tk_elem<KIND>::type T;
+    for (uint32_t s = tid; s < cnt; s += FZ_THREADS) {
+        const uint32_t t = tok[s];
+        const uint32_t pos = t & 0xFFFFu, k = t >> 16;
+        const uint32_t info = rinfo[k];
+        if (!(info & FR_PARSE)) continue;
+        const uint32_t e = sbase + s - fseg[k];             // element index inside the record
+        const uint32_t end = rst[k + 1];
+        const bool last = e + 1 == rlen[k];
+        // the element ends at the next ',' -- or, for the last one, at the ']' that closes the record
+        const uint32_t stop = (last ? end : (tok[s + 1] & 0xFFFFu)) - 1u;
+        T v;
+        int st = TK_OK;
+        uint64_t F;
+        uint32_t I, L2, neg;
+        // (the last element takes the fast lane only when the record's final byte is ']')
+        bool fast = !(last && !(info & FR_TAIL)) && fast_number<true>(win, pos, stop, tb.pow10, &I, &F, &L2, &neg);
+        if (fast) fast = fast_convert<KIND>(I, F, L2, neg, tb, &v);
+        if (!fast) {
+            WindowReader rd{win, end};
+            st = tk_json_element_flat<KIND>(rd, pos, &v);
+        }
+        if (st) { flag_record(a.rec_status, a.res, r0 + k, st); continue; }
+        if (STAGE) {
+            val[s] = v;
+        } else {
+            const uint32_t row = rrow[k];
+            if (row != 0xFFFFFFFFu && e < a.max_len) values[(uint64_t)row * a.max_len + e] = v;
+        }
+    }
+}
+
 template <int KIND>
-__global__ void __launch_bounds__(FZ_THREADS) k_json_fused(const fused_args a) {
+__global__ void __launch_bounds__(FZ_THREADS, 4) k_json_fused(const fused_args a) {
     typedef typename tk_elem<KIND>::type T;
     extern __shared__ __align__(128) uint8_t fz_smem[];
     __shared__ parse_tables tb;
@@ -285,12 +339,14 @@ __global__ void __launch_bounds__(FZ_THREADS) k_json_fused(const fused_args a) {
     __shared__ uint32_t s_warp_tot[32];
     __shared__ uint32_t s_total, s_kept, s_elems;
     __shared__ uint32_t s_next[5];          // the block's next tile: index, first record, first byte, end record, end byte
-    __shared__ unsigned long long s_excl;
+    __shared__ uint32_t s_first[FZ_WARPS];
+    __shared__ unsigned long long s_sum[FZ_WARPS];
 
     const uint32_t tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
     const uint32_t nch = a.win_bytes / FZ_CHUNK;
     uint8_t* win = fz_smem;
-    uint32_t* cmask = reinterpret_cast<uint32_t*>(win + a.win_bytes + 64);
+    T* val = reinterpret_cast<T*>(win + a.win_bytes + 64);               // staged values of the first round
+    uint32_t* cmask = reinterpret_cast<uint32_t*>(val + FZ_TOKCAP);
     uint32_t* pre = cmask + nch;
     uint32_t* tok = pre + nch + 1;
     uint32_t* rrow = tok + FZ_TOKCAP + 1;
@@ -318,20 +374,19 @@ __global__ void __launch_bounds__(FZ_THREADS) k_json_fused(const fused_args a) {
     T* values = reinterpret_cast<T*>(a.values.base);
     uint32_t phase = 0;
 
-    // Tiles are taken from a ticket counter, one ahead: while a tile is processed, thread 0 already
-    // holds the ticket of the block's next tile and has its bounds on the way, so neither the
-    // atomic nor the dependent loads of the tile table are waited for.
-    if (tid == 0) {
-        const uint32_t t = atomicAdd(&a.ctr[0], 1u);
-        s_next[0] = t;
-        if (t < a.n_tiles) {
-            const uint2 x = a.tile_info[t], y = a.tile_info[t + 1];
-            s_next[1] = x.x; s_next[2] = x.y; s_next[3] = y.x; s_next[4] = y.y;
-        }
-    }
-    __syncthreads();
-
+    // Tiles are taken from a ticket counter when the block is ready for one (not earlier: a ticket
+    // held by a busy block would stall the look-back of every tile behind it).
     for (;;) {
+        if (tid == 0) {
+            const uint32_t t = atomicAdd(&a.ctr[0], 1u);
+            s_next[0] = t;
+            if (t < a.n_tiles) {
+                const uint2 x = a.tile_info[t], y = a.tile_info[t + 1];
+                s_next[1] = x.x; s_next[2] = x.y; s_next[3] = y.x; s_next[4] = y.y;
+            }
+            s_kept = 0; s_elems = 0;
+        }
+        __syncthreads();
         const uint32_t tile = s_next[0];
         if (tile >= a.n_tiles) break;
         const uint32_t r0 = s_next[1], lo = s_next[2], r1 = s_next[3], hi = s_next[4];
@@ -340,15 +395,9 @@ __global__ void __launch_bounds__(FZ_THREADS) k_json_fused(const fused_args a) {
         const uint32_t span = m ? ((hi + 15u) & ~15u) - base : 0u;   // bytes to bring in
         // (strictly inside the window: positions up to `span` index the per-chunk tables)
         const bool fast_tile = m && span + FZ_CHUNK <= a.win_bytes && m <= a.max_recs;
-        __syncthreads();                                             // everyone has read s_next
-        uint32_t next_ticket = 0;
-        if (tid == 0) {
-            s_kept = 0; s_elems = 0;
-            if (fast_tile && span) {
-                mbar_expect_tx(&s_bar, span);
-                bulk_load(win, a.bytes + base, span, &s_bar);
-            }
-            next_ticket = atomicAdd(&a.ctr[0], 1u);
+        if (tid == 0 && fast_tile && span) {
+            mbar_expect_tx(&s_bar, span);
+            bulk_load(win, a.bytes + base, span, &s_bar);
         }
 
         // ---------------- cut
@@ -449,7 +498,6 @@ __global__ void __launch_bounds__(FZ_THREADS) k_json_fused(const fused_args a) {
             if (lane == 0 && (my_kept | my_elems)) { atomicAdd(&s_kept, my_kept); atomicAdd(&s_elems, my_elems); }
         } else if (m) {
             // scalar path: thread per record out of global memory
-            __syncthreads();                                         // s_kept / s_elems are reset
             uint32_t my_kept = 0, my_elems = 0;
             for (uint32_t k = tid; k < m; k += FZ_THREADS) {
                 const uint32_t i = r0 + k;
@@ -490,34 +538,30 @@ __global__ void __launch_bounds__(FZ_THREADS) k_json_fused(const fused_args a) {
         }
         __syncthreads();
 
-        // ---------------- place, first half: warp 0 publishes the tile's sum and looks back for its
-        // exclusive prefix (and fetches the next tile's bounds) while the other warps scatter the
-        // first round of segments
+        // ---------------- publish the tile's sum (the tiles behind this one wait for it), then do
+        // everything that does not need the tile's place among the kept records: scatter the first
+        // round of segments and parse them into the staging array.  By the time the block looks
+        // back, the tiles in front of it have long published theirs.
         const uint32_t n_seg = fast_tile ? (uint32_t)fseg[m] : 0u;
-        if (wid == 0) {
-            const unsigned long long tot = ((unsigned long long)s_kept << FZ_PACK_SHIFT) + s_elems;
-            uint2 nx = make_uint2(0, 0), ny = make_uint2(0, 0);
-            if (lane == 0) {
-                a.tile_agg[tile] = tot;
-                if (tile == 0) a.tile_incl[0] = tot;
-                fz_st_release(a.tile_flag + tile, (a.epoch << 2) | (tile == 0 ? 2u : 1u));
-                if (next_ticket < a.n_tiles) { nx = a.tile_info[next_ticket]; ny = a.tile_info[next_ticket + 1]; }
-            }
-            const unsigned long long excl = tile ? fz_lookback(a, tile, lane) : 0ull;
-            if (lane == 0) {
-                if (tile) {
-                    a.tile_incl[tile] = excl + tot;
-                    fz_st_release(a.tile_flag + tile, (a.epoch << 2) | 2u);
-                }
-                s_excl = excl;
-                s_next[0] = next_ticket; s_next[1] = nx.x; s_next[2] = nx.y; s_next[3] = ny.x; s_next[4] = ny.y;
-            }
-        } else if (fast_tile) {
-            fz_scatter(0, n_seg, m, nch, tid - 32, FZ_THREADS - 32, cmask, pre, rcnt, rst, fseg, rfirst, tok);
+        const unsigned long long tot = ((unsigned long long)s_kept << FZ_PACK_SHIFT) + s_elems;
+        if (tid == 0) {
+            a.tile_agg[tile] = tot;
+            if (tile == 0) a.tile_incl[0] = tot;
+            fz_st_release(a.tile_flag + tile, (a.epoch << 2) | (tile == 0 ? 2u : 1u));
+        }
+        const uint32_t cnt0 = min(FZ_TOKCAP, n_seg);
+        if (fast_tile) {
+            fz_scatter(0, n_seg, m, nch, tid, FZ_THREADS, cmask, pre, rcnt, rst, fseg, rfirst, tok);
+            __syncthreads();
+            fz_parse_round<KIND, true>(a, tb, win, tok, rinfo, fseg, rlen, rst, rrow, val, values, 0, cnt0, r0, tid);
+        }
+        const unsigned long long excl = tile ? fz_lookback(a, tile, s_first, s_sum) : 0ull;
+        if (tid == 0 && tile) {
+            a.tile_incl[tile] = excl + tot;
+            fz_st_release(a.tile_flag + tile, (a.epoch << 2) | 2u);
         }
         __syncthreads();
-        const uint32_t excl_kept = (uint32_t)(s_excl >> FZ_PACK_SHIFT);
-
+        const uint32_t excl_kept = (uint32_t)(excl >> FZ_PACK_SHIFT);
         // rows of the kept records, batch boundaries, longest record per batch, commit maxima:
         // thread per record in record order (uniform trip count: the loop body uses warp collectives)
         uint32_t running = 0;
@@ -578,40 +622,20 @@ __global__ void __launch_bounds__(FZ_THREADS) k_json_fused(const fused_args a) {
                 if (row != 0xFFFFFFFFu)
                     json_write_row<sizeof(T)>(a.values, a.lengths, a.mask, a.max_len, row, rlen[k], lane, vec_values, vec_mask);
             }
-            // ---------------- parse: segments in rounds of FZ_TOKCAP (round 0 is already scattered)
-            for (uint32_t sbase = 0; sbase < n_seg; sbase += FZ_TOKCAP) {
-                if (sbase) {
-                    fz_scatter(sbase, n_seg, m, nch, tid, FZ_THREADS, cmask, pre, rcnt, rst, fseg, rfirst, tok);
-                    __syncthreads();
-                }
-                const uint32_t cnt = min(FZ_TOKCAP, n_seg - sbase);
-                for (uint32_t s = tid; s < cnt; s += FZ_THREADS) {
-                    const uint32_t t = tok[s];
-                    const uint32_t pos = t & 0xFFFFu, k = t >> 16;
-                    const uint32_t info = rinfo[k];
-                    if (!(info & FR_PARSE)) continue;
-                    const uint32_t e = sbase + s - fseg[k];             // element index inside the record
-                    const uint32_t len = rlen[k];
-                    const uint32_t end = rst[k + 1];
-                    const bool last = e + 1 == len;
-                    // the element ends at the next ',' -- or, for the last one, at the ']' that closes the record
-                    const uint32_t stop = (last ? end : (tok[s + 1] & 0xFFFFu)) - 1u;
-                    T v;
-                    int st = TK_OK;
-                    uint64_t F;
-                    uint32_t I, L2, neg;
-                    // (the last element takes the fast lane only when the record's final byte is ']')
-                    bool fast = !(last && !(info & FR_TAIL)) && fast_number<true>(win, pos, stop, tb.pow10, &I, &F, &L2, &neg);
-                    if (fast) fast = fast_convert<KIND>(I, F, L2, neg, tb, &v);
-                    if (!fast) {
-                        WindowReader rd{win, end};
-                        st = tk_json_element_flat<KIND>(rd, pos, &v);
-                    }
-                    if (st) { flag_record(a.rec_status, a.res, r0 + k, st); continue; }
-                    const uint32_t row = rrow[k];
-                    if (row != 0xFFFFFFFFu && e < a.max_len) values[(uint64_t)row * a.max_len + e] = v;
-                }
-                if (sbase + FZ_TOKCAP < n_seg) __syncthreads();         // the next round overwrites tok
+            // ---------------- the staged values of the first round go to their rows
+            for (uint32_t s = tid; s < cnt0; s += FZ_THREADS) {
+                const uint32_t k = tok[s] >> 16;
+                if (!(rinfo[k] & FR_PARSE)) continue;
+                const uint32_t row = rrow[k], e = s - fseg[k];
+                if (row != 0xFFFFFFFFu && e < a.max_len) values[(uint64_t)row * a.max_len + e] = val[s];
+            }
+            // ---------------- further rounds (records with very many short elements): rows are known
+            for (uint32_t sbase = FZ_TOKCAP; sbase < n_seg; sbase += FZ_TOKCAP) {
+                __syncthreads();                                        // tok is reused
+                fz_scatter(sbase, n_seg, m, nch, tid, FZ_THREADS, cmask, pre, rcnt, rst, fseg, rfirst, tok);
+                __syncthreads();
+                fz_parse_round<KIND, false>(a, tb, win, tok, rinfo, fseg, rlen, rst, rrow, val, values, sbase,
+                                            min(FZ_TOKCAP, n_seg - sbase), r0, tid);
             }
         } else if (m) {
             // scalar path: warp per record for the row, thread per record for the elements
@@ -642,7 +666,7 @@ __global__ void __launch_bounds__(FZ_THREADS) k_json_fused(const fused_args a) {
                 }
             }
         }
-        __syncthreads();                    // the window and the tables are free for the next tile
+        __syncthreads();                    // the window, the tables and s_next are free for the next tile
     }
 
     // Every block leaves through this counter; all tiles are done when the last one does, and it
@@ -765,7 +789,7 @@ extern "C" int tk_json_ingest(tk_ctx* ctx, int slot, int dtype, uint32_t max_len
     a.rec_len = s.d.rec_len; a.rec_status = s.d.rec_status; a.rec_kidx = s.d.rec_kidx;
     a.tile_info = reinterpret_cast<const uint2*>(s.d.fz_tile_first); a.n_tiles = n_tiles;
     a.win_bytes = FZ_TILE_BYTES + (uint32_t)over;                 // <= 57344: positions fit 16 bits
-    a.max_recs = a.win_bytes <= 32768 ? 768u : 512u;
+    a.max_recs = 512u;
     a.tile_agg = s.d.fz_agg; a.tile_incl = s.d.fz_incl; a.tile_flag = s.d.fz_flag; a.ctr = s.d.fz_ctr;
     s.fz_epoch = (s.fz_epoch + 1) & 0x3FFFFFFFu;
     if (!s.fz_epoch) s.fz_epoch = 1;                              // 0 is the state of a fresh allocation
@@ -776,7 +800,7 @@ extern "C" int tk_json_ingest(tk_ctx* ctx, int slot, int dtype, uint32_t max_len
     a.values = *values;
     a.lengths = lengths ? *lengths : z;
     a.mask = mask ? *mask : z;
-    const size_t smem = fz_smem_bytes(a.win_bytes, a.max_recs);
+    const size_t smem = fz_smem_bytes(a.win_bytes, a.max_recs, (dtype == TK_DTYPE_F64 || dtype == TK_DTYPE_I64) ? 8 : 4);
     switch (dtype) {
         case TK_DTYPE_F32: return fz_launch<TK_F32>(a, smem, st);
         case TK_DTYPE_F64: return fz_launch<TK_F64>(a, smem, st);

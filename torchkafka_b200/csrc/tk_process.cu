@@ -15,10 +15,10 @@ extern "C" int tk_process_slot(tk_ctx* ctx, int slot, const tk_job_t* job, void*
         rc = tk_carry_rows(ctx, job->prev_slot, job->n_planes, job->prev, job->cur, stream);
         if (rc) return rc;
     }
-    // JSON arrays: one single-pass kernel (tk_json_fused.cu) does scan, compaction, commit maxima, rows
-    // and parse; the three-kernel chain stays available (tk_ctx_set_json_flat / TK_JSON_FLAT=1) as a
-    // cross-check and for comparison runs
-    const bool fused = job->schema == TK_SCHEMA_JSON && !ctx->json_flat;
+    // JSON arrays: the three-kernel chain (scan, plan, parse), or -- tk_ctx_set_json_fused /
+    // TK_JSON_FUSED=1 -- the single-pass kernel of tk_json_fused.cu, which reads the payload from HBM
+    // once but is the slower of the two today
+    const bool fused = job->schema == TK_SCHEMA_JSON && ctx->json_fused;
     tk_slot& s = ctx->slots[slot];
     if (fused) {
         s.dec_timed = false;
@@ -78,9 +78,9 @@ extern "C" int tk_process_slot(tk_ctx* ctx, int slot, const tk_job_t* job, void*
     return tk_slot_fetch_result(ctx, slot, stream);
 }
 
-extern "C" int tk_ctx_set_json_flat(tk_ctx* ctx, int enabled) {
+extern "C" int tk_ctx_set_json_fused(tk_ctx* ctx, int enabled) {
     TK_REQUIRE(ctx, "null context");
-    ctx->json_flat = enabled ? 1 : 0;
+    ctx->json_fused = enabled ? 1 : 0;
     return 0;
 }
 

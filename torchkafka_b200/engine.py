@@ -146,9 +146,10 @@ class SlotEngine:
                 _native.check(self.lib.tk_ctx_set_object_fields(self.ctx, blob.ctypes.data, off.ctypes.data,
                                                                 len(schema.fields), self._stream()))
         self.launches = 0
-        #: JSON arrays: three-kernel chain (scan, plan, parse) instead of the single-pass kernel;
-        #: kept as an independent cross-check and for comparison runs (``set_json_flat``)
-        self.json_flat = bool(int(os.environ.get("TK_JSON_FLAT", "0") or 0))
+        #: JSON arrays through the single-pass kernel (tk_json_fused.cu) instead of the three-kernel
+        #: chain (scan, plan, parse): an independent decomposition of the same contract, used as a
+        #: cross-check and for comparison runs (``set_json_fused``)
+        self.json_fused = bool(int(os.environ.get("TK_JSON_FUSED", "0") or 0))
         try:
             cores = len(os.sched_getaffinity(0))
         except AttributeError:  # pragma: no cover
@@ -375,17 +376,17 @@ class SlotEngine:
                     timers.append((ev0, ev1))
                 _native.check(lib.tk_slot_fetch_result(ctx, slot, st))
             per_slot = LAUNCHES_PER_SLOT_RAW if not is_json else (
-                LAUNCHES_PER_SLOT_JSON if (self.json_flat or timers is not None) else LAUNCHES_PER_SLOT_JSON_FUSED)
+                LAUNCHES_PER_SLOT_JSON_FUSED if (self.json_fused and timers is None) else LAUNCHES_PER_SLOT_JSON)
             self.launches += per_slot \
                 - (1 if prev_out is None else 0) + (len(out.planes) - 1 if isinstance(sc, StructBytes) else 0)
             out.done = torch.cuda.Event()
             out.done.record(self.stream)
         return out
 
-    def set_json_flat(self, enabled: bool):
-        """JSON arrays through the three-kernel chain (True) or the single-pass kernel (False)."""
-        self.json_flat = bool(enabled)
-        _native.check(self.lib.tk_ctx_set_json_flat(self.ctx, 1 if enabled else 0))
+    def set_json_fused(self, enabled: bool):
+        """JSON arrays through the single-pass kernel (True) or the three-kernel chain (False)."""
+        self.json_fused = bool(enabled)
+        _native.check(self.lib.tk_ctx_set_json_fused(self.ctx, 1 if enabled else 0))
 
     def set_timing(self, enabled: bool):
         """Bracket the decode / collate kernels of every following ``process`` call with CUDA
@@ -579,7 +580,7 @@ def release(eng: SlotEngine):
     try:
         eng.stream.synchronize()
         eng.set_timing(False)
-        eng.set_json_flat(bool(int(os.environ.get("TK_JSON_FLAT", "0") or 0)))
+        eng.set_json_fused(bool(int(os.environ.get("TK_JSON_FUSED", "0") or 0)))
         eng.reset()
     except Exception:
         eng.close()

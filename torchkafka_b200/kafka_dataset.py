@@ -119,6 +119,10 @@ class KafkaDataset(IterableDataset):
     #: schema allows (``max_len``) and there is one per record, so a slot of very short records
     #: under a wide schema is cut by this budget rather than by ``device_slot_bytes``.
     device_output_bytes = None
+    #: JSON arrays through the single-pass kernel (``tk_json_ingest``: payload read from HBM once)
+    #: instead of the three-kernel chain; None = the library's default (the chain, or
+    #: ``TK_JSON_FUSED=1``).  Same results; the chain is the faster one today.
+    device_json_single_pass = None
     #: multi-worker CPU path: a worker commits the offsets of the batches the main process has
     #: *received* from it (explicit offsets, same values as single-process iteration), not its
     #: consumer's position, which runs ahead by the DataLoader's prefetched batches and would lose
@@ -303,7 +307,7 @@ class KafkaDataset(IterableDataset):
             threaded=self.device_producer_thread, n_producers=self.device_producers,
             commit_all_partitions=self.commit_all_partitions, input_mode=self.device_input,
             numa_affinity=self.device_numa_affinity, max_latency_ms=self.device_max_latency_ms,
-            output_bytes=self.device_output_bytes,
+            output_bytes=self.device_output_bytes, json_single_pass=self.device_json_single_pass,
         )
         return self._pipeline
 

@@ -71,7 +71,8 @@ class IngestPipeline:
                  max_partitions: int = 64, poll_timeout_ms: int = 100,
                  threaded: bool = True, commit_all_partitions: bool = False,
                  n_producers: int = 2, input_mode: str = "auto", numa_affinity: bool = True,
-                 max_latency_ms: Optional[float] = None, output_bytes: Optional[int] = None):
+                 max_latency_ms: Optional[float] = None, output_bytes: Optional[int] = None,
+                 json_single_pass: Optional[bool] = None):
         self.consumer = consumer
         self.schema = schema
         self.batch_size = int(batch_size)
@@ -79,6 +80,8 @@ class IngestPipeline:
         self.engine = _engine.acquire(schema, batch_size, slot_bytes=slot_bytes,
                                       n_slots=max(n_slots, 2 + (int(n_producers) if threaded else 0)),
                                       device=device, n_partitions=max_partitions, output_bytes=output_bytes)
+        if json_single_pass is not None:
+            self.engine.set_json_fused(bool(json_single_pass))
         self.poll_timeout_ms = poll_timeout_ms
         # kafka-python ends `for record in consumer` after consumer_timeout_ms without a record
         # (default: never).  The GPU path follows the same setting; the in-memory stub

@@ -652,10 +652,19 @@ static int submit_recordbatches(tk_ctx* ctx, int slot, uint64_t n_bytes, const t
         TK_CUDA(cudaStreamWaitEvent(ks, s.ev_free, 0));
     }
     if (ext) {
-        // every blob straight out of the caller's (page-locked) buffer to its place in the device buffer
-        for (uint32_t k = 0; k < n_blobs; ++k)
-            if (blobs[k].length)
-                TK_CUDA(cudaMemcpyAsync(s.d.raw + blobs[k].start, ext[k], blobs[k].length, cudaMemcpyHostToDevice, st));
+        // every blob straight out of the caller's (page-locked) buffer to its place in the device buffer;
+        // blobs that follow one another in the caller's buffer as they do in the slot (a consumer
+        // that receives a whole fetch response into one arena) go as one copy
+        for (uint32_t k = 0; k < n_blobs;) {
+            uint32_t j = k + 1;
+            uint64_t len = blobs[k].length;
+            while (j < n_blobs && ext[k] + len == ext[j] && (uint64_t)blobs[k].start + len == blobs[j].start) {
+                len += blobs[j].length;
+                ++j;
+            }
+            if (len) TK_CUDA(cudaMemcpyAsync(s.d.raw + blobs[k].start, ext[k], len, cudaMemcpyHostToDevice, st));
+            k = j;
+        }
     } else if (n_bytes) {
         TK_CUDA(cudaMemcpyAsync(s.d.raw, s.h_bytes, n_bytes, cudaMemcpyHostToDevice, st));
     }

@@ -183,6 +183,20 @@ class KafkaDataset(IterableDataset):
         if self._consumer is None:
             raise RuntimeError("Consumer is not initialized.")
         if self._worker_id is None:
+            pending = self._explicit_offsets
+            pipe = self._pipeline
+            if pending is not None and pipe is not None and not _logger.isEnabledFor(logging.DEBUG):
+                # GPU path, once per batch: the same steps as _commit_if_required(force=True) without
+                # the (disabled) log calls -- with batches of a few records this is the host's hot loop
+                try:
+                    with pipe.consumer_lock:
+                        self._consumer.commit(pending)
+                    if self._explicit_offsets is pending:
+                        self._explicit_offsets = {}
+                except _commit_failed_types():
+                    _logger.error("Commit failed.")
+                self._commit_required = False
+                return
             self._commit_if_required(force=True)
             return
         if signum is None:

@@ -59,7 +59,7 @@ VALUE_MIN_SECONDS = float(os.environ.get("TK_VALUE_SECONDS", "0.5"))
 E2E_MIN_SECONDS = float(os.environ.get("TK_E2E_SECONDS", "2.5"))
 #: ConsumerRecord objects the poll arm may hold (they exist before the clock starts, as they do
 #: for the CPU arm): ~200 bytes each
-POLL_MAX_OBJECTS = int(os.environ.get("TK_POLL_OBJECTS", str(6_000_000)))
+POLL_MAX_OBJECTS = int(os.environ.get("TK_POLL_OBJECTS", str(12_000_000)))
 
 
 def log(*a):

@@ -132,10 +132,10 @@ def e2e(cfg, log, packed, repeat):
         ds.close()
         return dt, stats
 
-    dt1, _ = run(1)
-    # (small batches are bound by the host's per-batch work, far below the link: size the timed
-    # iteration from the warm-up's rate so that it lasts about two seconds)
-    repeat = max(2, min(repeat, int(2.5 * len(log) / dt1 * 2.0 / len(log)) + 1))
+    run(1)                                  # cold: context creation, first allocations
+    pilot = max(1, min(4, repeat))
+    dtp, _ = run(pilot)                     # warm pilot: its rate sizes the timed iteration (~2.5 s)
+    repeat = max(2, min(repeat, int(2.5 * pilot / dtp) + 1))
     dt, stats = run(repeat)
     return repeat * len(log) / dt, stats, repeat
 

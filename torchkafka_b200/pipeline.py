@@ -32,7 +32,7 @@ from . import engine as _engine
 from .schema import PayloadError
 
 
-from .structs import _offset_struct, _tp_struct  # noqa: E402  (kafka-python's structs, or the stub's)
+from .structs import _offset_make, _offset_struct, _tp_struct  # noqa: E402  (kafka-python's structs, or the stub's)
 
 
 try:  # NVTX ranges around the per-slot stages (visible in nsys / ncu timelines; ~0.1 us each otherwise)
@@ -98,6 +98,7 @@ class IngestPipeline:
         #: producers take turns gathering (poll + harvest) so slots follow consumption order
         self._order_lock = threading.Lock()
         self._mk_offset = _offset_struct()
+        self._om_make, self._om_rest = _offset_make()
         self._tp_cls = _tp_struct()
         self._tp_of: Dict[int, object] = {}        # dense partition index -> TopicPartition
         self._dense_of: Dict[object, int] = {}     # TopicPartition -> dense index
@@ -576,11 +577,14 @@ class IngestPipeline:
         self._last_column = cols[nc - 1]
         rows, parts = np.nonzero(changed)
         vals = cols[rows, parts].tolist()
-        parts = parts.tolist()
         cut = np.searchsorted(rows, np.arange(nc + 1)).tolist()
-        mk = self._mk_offset
-        tp_of = self._tp_of
-        return [{tp_of[parts[k]]: mk(vals[k]) for k in range(cut[j], cut[j + 1])} for j in range(nc)]
+        # Everything per entry runs in C: the OffsetAndMetadata tuples come from the class's _make
+        # over zipped columns, the TopicPartitions from a table lookup; with small batches (one or
+        # two partitions move per batch) building these maps is what the host spends its time on.
+        tps = list(map(self._tp_of.__getitem__, parts.tolist()))
+        oms = list(map(self._om_make, zip(vals, *self._om_rest)))
+        return [{tps[a]: oms[a]} if b == a + 1 else dict(zip(tps[a:b], oms[a:b]))
+                for a, b in zip(cut, cut[1:])]
 
     def _produce(self, free_q, deliver):
         """Producer thread.  Gather (consumer calls, serialised, defines the slot order) then

@@ -215,6 +215,15 @@ int tk_json_object_decode(tk_ctx* ctx, int slot, int dtype, const tk_plane_t* va
 #define TK_MAX_NESTED_DIMS 4
 int tk_json_nested_decode(tk_ctx* ctx, int slot, int dtype, uint32_t ndim, const uint32_t* dims,
                           const tk_plane_t* values, void* stream);
+/* The same contract through the flat chain (what tk_process_slot runs for two or more dimensions):
+ * every comma of such a record separates two leaves, so the comma split of tk_json_scan cuts it into
+ * one segment per leaf, and the brackets around leaf e follow from e and the shape -- each leaf's
+ * thread checks its own.  Large records (a 64 x 24 matrix is 30 KB of text) are decoded by as many
+ * threads as they have leaves instead of one.  Scan: tk_json_nested_scan (in place of tk_raw_scan),
+ * then tk_compact, then tk_json_nested_decode_flat. */
+int tk_json_nested_scan(tk_ctx* ctx, int slot, uint32_t ndim, const uint32_t* dims, void* stream);
+int tk_json_nested_decode_flat(tk_ctx* ctx, int slot, int dtype, uint32_t ndim, const uint32_t* dims,
+                               const tk_plane_t* values, void* stream);
 
 /* HWC uint8 -> normalised bfloat16 CHW:  bf16(((x / 255) - mean[c]) / std[c]) in
  * float32 with IEEE division, the op order of SURVEY.md §8c */

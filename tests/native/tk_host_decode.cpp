@@ -195,3 +195,48 @@ extern "C" int tk_host_decode_nested(const uint8_t* buf, uint32_t len, int kind,
     }
     return -1;
 }
+
+// Mirror of the flat (comma-split) path for nested arrays of a fixed shape (tk_json.cuh): head,
+// one segment per comma, count check.  Same contract as tk_host_decode_nested.
+template <int KIND>
+static int decode_nested_flat(const uint8_t* buf, uint32_t len, const uint32_t* dims, uint32_t ndim, void* row) {
+    typedef typename tk_elem<KIND>::type T;
+    HostReader rd{buf, len};
+    tk_nested_shape sh;
+    sh.ndim = ndim;
+    uint32_t prod = 1;
+    for (uint32_t j = ndim; j-- > 0;) { prod *= dims[j]; sh.span[j] = prod; }
+    uint32_t first = 0;
+    int st = tk_json_prefix_nested(rd, 0, ndim, &first);
+    if (st) return st;
+    uint32_t commas = 0;
+    for (uint32_t p = 0; p < len; ++p) commas += buf[p] == ',';
+    const uint32_t n = commas + 1;
+    if (n != prod) return TK_ERR_RAGGED;
+    int worst = TK_OK;
+    uint32_t seg = first;
+    for (uint32_t e = 0; e < n; ++e) {
+        const bool last = e + 1 == n;
+        T v = (T)0;
+        st = tk_json_element_nested<KIND>(rd, seg, e ? tk_nested_opens(sh, e) : 0u,
+                                          last ? ndim : tk_nested_opens(sh, e + 1), last, &v);
+        if (st && !worst) worst = st;
+        ((T*)row)[e] = st ? (T)0 : v;
+        uint32_t p = seg;
+        while (p < len && buf[p] != ',') ++p;
+        seg = p + 1;
+    }
+    return worst;
+}
+
+extern "C" int tk_host_decode_nested_flat(const uint8_t* buf, uint32_t len, int kind, const uint32_t* dims,
+                                          uint32_t ndim, void* row) {
+    switch (kind) {
+        case TK_F32: return decode_nested_flat<TK_F32>(buf, len, dims, ndim, row);
+        case TK_F64: return decode_nested_flat<TK_F64>(buf, len, dims, ndim, row);
+        case TK_I32: return decode_nested_flat<TK_I32>(buf, len, dims, ndim, row);
+        case TK_I64: return decode_nested_flat<TK_I64>(buf, len, dims, ndim, row);
+    }
+    return -1;
+}
+

@@ -485,6 +485,46 @@ def test_nested_arrays_match_torch_tensor(shape, dtype):
     check(log, JsonNested(shape, dtype), 5, slot_bytes=40000)           # many slots, carried rows
 
 
+@pytest.mark.parametrize("shape,dtype", [((5, 7), torch.float32), ((3, 2, 4), torch.int64), ((64, 24), torch.float64)])
+def test_nested_flat_chain_agrees_with_the_sequential_scanner(shape, dtype):
+    """Nested arrays run through the flat chain (one thread per leaf, brackets checked from the leaf
+    index); the object kernel's sequential scanner (`tk_json_nested_decode`, the staged entry point)
+    is an independent implementation: same rows, same records flagged."""
+    from torchkafka_b200.engine import SlotEngine
+    from torchkafka_b200.schema import JsonNested
+    log = nested_log(300, shape, seed=62, ints=not dtype.is_floating_point)
+    vals = list(log._byte_values)
+    vals[7] = vals[7].replace(b"], [", b"] ,\n [", 2)                 # white space around the brackets
+    vals[11] = vals[11][:-2] + b", 1]]"                               # one leaf too many
+    vals[13] = vals[13].replace(b"], [", b", ", 1)                    # a bracket pair missing: ragged
+    vals[17] = b"[" + vals[17] + b"]"                                 # one level too deep
+    n = len(vals)
+    log = RecordLog(vals, np.arange(n) % 4, np.arange(n) // 4)
+    sc = JsonNested(shape, dtype)
+    outs = []
+    for staged in (True, False):
+        eng = SlotEngine(sc, 16, slot_bytes=16 << 20, slot_records=n + 8, n_slots=2, device=0, n_partitions=4)
+        m, nb = eng.fill_packed(0, log.values, log.starts.astype(np.uint32), log.partitions, log.offsets)
+        eng.submit(0, m, nb)
+        out = eng.process(0, m, None, None, timers=[] if staged else None)
+        res = eng.result(0)
+        _, st, kx = eng.record_debug(0, m)
+        rows = out.tensors[0][16:].cpu()
+        outs.append((rows, res, st.copy(), kx.copy()))
+        eng.close()
+    (ra, resa, sa, ka), (rb, resb, sb, kb) = outs
+    bad = {11, 13, 17}
+    assert set(np.flatnonzero(sa).tolist()) == bad == set(np.flatnonzero(sb).tolist())
+    assert resa.n_errors == resb.n_errors == 3 and resa.first_error_rec == resb.first_error_rec == 11
+    # the sequential scanner keeps every record (its errors surface in the decode), the flat chain
+    # drops the ones its scan already rejects: compare the rows record by record
+    for i in range(n):
+        if i in bad:
+            continue
+        assert ka[i] >= 0 and kb[i] >= 0
+        assert bit_equal(ra[ka[i]], rb[kb[i]]), i
+
+
 @pytest.mark.parametrize("bad", [b"[[1, 2, 3], [4, 5]]", b"[[1, 2, 3]]", b"[1, 2, 3]", b"[[[1, 2, 3], [4, 5, 6]]]",
                                  b"[[1, 2, 3], [4, 5, 6]] x", b"[[1, 2, 3], [4, 5, null]]",
                                  b"[[1, 2, 3], [4, 5, " + b"9" * 400 + b"]]"])

@@ -209,15 +209,23 @@ def test_many_fields_and_schema_order(lib):
 
 
 # ---------------------------------------------------------------- nested arrays of a fixed shape
-def decode_nested(lib, payload: bytes, shape, kind: int):
+def decode_nested(lib, payload: bytes, shape, kind: int, flat: bool = False):
+    """flat: the comma-split decomposition the flat decode kernels run (tk_json.cuh) instead of the
+    sequential scanner of the object kernel (tk_json_object.cuh)."""
     dims = np.asarray(shape, np.uint32)
     row = np.zeros(int(np.prod(shape)), DTYPES[kind][1])
-    st = lib.tk_host_decode_nested(payload, len(payload), kind, dims.ctypes.data_as(ctypes.c_void_p), len(shape),
-                                   row.ctypes.data_as(ctypes.c_void_p))
+    fn = lib.tk_host_decode_nested_flat if flat else lib.tk_host_decode_nested
+    st = fn(payload, len(payload), kind, dims.ctypes.data_as(ctypes.c_void_p), len(shape),
+            row.ctypes.data_as(ctypes.c_void_p))
     return st, row.reshape(shape)
 
 
 def check_nested(lib, payload, shape, kinds=(0, 1, 2, 3)):
+    for flat in (False, True):
+        _check_nested(lib, payload, shape, kinds, flat)
+
+
+def _check_nested(lib, payload, shape, kinds, flat):
     for kind in kinds:
         try:
             want = torch.tensor(json.loads(payload), dtype=DTYPES[kind][0])
@@ -225,11 +233,11 @@ def check_nested(lib, payload, shape, kinds=(0, 1, 2, 3)):
                 want = None                               # a tensor, but not a sample of this schema
         except Exception:                                 # noqa: BLE001
             want = None
-        st, got = decode_nested(lib, payload, shape, kind)
+        st, got = decode_nested(lib, payload, shape, kind, flat)
         if want is None:
-            assert st != 0, (payload, shape, kind)
+            assert st != 0, (payload, shape, kind, flat)
         else:
-            assert st == 0, (payload, shape, kind, st)
+            assert st == 0, (payload, shape, kind, st, flat)
             bits = DTYPES[kind][2]
             assert np.array_equal(got.view(bits), want.numpy().view(bits)), (payload, kind)
 

@@ -104,6 +104,8 @@ _SIGNATURES = {
     "tk_ctx_set_object_fields": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint32, C.c_void_p]),
     "tk_json_object_decode": (C.c_int, [C.c_void_p, C.c_int, C.c_int, _p(TkPlane), C.c_void_p]),
     "tk_json_nested_decode": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_uint32, C.c_void_p, _p(TkPlane), C.c_void_p]),
+    "tk_json_nested_scan": (C.c_int, [C.c_void_p, C.c_int, C.c_uint32, C.c_void_p, C.c_void_p]),
+    "tk_json_nested_decode_flat": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_uint32, C.c_void_p, _p(TkPlane), C.c_void_p]),
     "tk_image_set_norm": (C.c_int, [C.c_void_p, C.c_int, _p(C.c_float), _p(C.c_float), C.c_void_p]),
     "tk_collate_image_u8_bf16_nchw": (C.c_int, [C.c_void_p, C.c_int, C.c_uint32, C.c_uint32, C.c_uint32,
                                                 _p(TkPlane), C.c_void_p]),

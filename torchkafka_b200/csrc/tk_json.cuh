@@ -136,3 +136,101 @@ TK_HD int tk_json_element_flat(const R& rd, uint32_t pos, typename tk_elem<KIND>
     }
     return TK_OK;
 }
+
+// ---------------------------------------------------------------------------------------------
+// Nested arrays of a fixed shape in the comma-split decomposition: what
+// `torch.tensor(json.loads(record.value))` accepts for a declared shape dims[0..ndim).  Every comma of
+// such a record separates two leaves (whatever the depth), so cutting at the commas yields one
+// segment per leaf, and what surrounds leaf e is a function of e and the shape alone:
+//     ws* ('[' ws*){opens(e)}  number  ws* (']' ws*){opens(e + 1)}   then ','
+// with opens(e) = the number of dimensions j >= 1 whose sub-array starts at leaf e (e is a
+// multiple of dims[j] * ... * dims[ndim-1]); the first leaf follows the head `[BOM] ws* ('[' ws*){ndim}`
+// and the last one is followed by (']' ws*){ndim} END.  Together with the count check (leaves ==
+// product of the extents) the segments tile the record, so a record is accepted iff the
+// sequential scanner of tk_json_object.cuh (tk_json_nested_record) accepts it.
+#define TK_JSON_NESTED_MAX_DIMS 4
+
+// suffix products of the shape: span[j] = dims[j] * ... * dims[ndim - 1]  (span[0] = leaves per record)
+struct tk_nested_shape {
+    uint32_t ndim;
+    uint32_t span[TK_JSON_NESTED_MAX_DIMS];
+};
+
+TK_HD uint32_t tk_nested_opens(const tk_nested_shape& sh, uint32_t e) {
+    uint32_t n = 0;
+    for (uint32_t j = sh.ndim; j-- > 1;) {           // innermost dimension first
+        if (e % sh.span[j]) break;
+        ++n;
+    }
+    return n;
+}
+
+template <class R>
+TK_HD uint32_t tk_json_skip_ws(const R& rd, uint32_t pos) {
+    while (tk_is_ws(rd(pos))) ++pos;
+    return pos;
+}
+
+// Head of a nested record.  On success *first is the position of the first leaf.
+template <class R>
+TK_HD int tk_json_prefix_nested(const R& rd, uint32_t pos, uint32_t ndim, uint32_t* first) {
+    if (rd(pos) == 0xEF && rd(pos + 1) == 0xBB && rd(pos + 2) == 0xBF) pos += 3;   // utf-8-sig
+    for (uint32_t d = 0; d < ndim; ++d) {
+        pos = tk_json_skip_ws(rd, pos);
+        const int c = rd(pos);
+        if (c != '[') return (tk_is_numclass(c) || c == '{' || c == '"') ? TK_ERR_RAGGED : TK_ERR_SYNTAX;
+        ++pos;
+    }
+    pos = tk_json_skip_ws(rd, pos);
+    const int c = rd(pos);
+    if (c == '[' || c == '{' || c == '"' || c == ']') return TK_ERR_RAGGED;     // deeper / not a number / empty
+    if (!tk_is_numclass(c)) return TK_ERR_SYNTAX;
+    *first = pos;
+    return TK_OK;
+}
+
+// One leaf segment starting at `pos` (right behind a ',' -- or, for the first leaf, at the leaf).
+template <int KIND, class R>
+TK_HD int tk_json_element_nested(const R& rd, uint32_t pos, uint32_t n_open, uint32_t n_close, bool last,
+                                 typename tk_elem<KIND>::type* out) {
+    for (uint32_t k = 0; k < n_open; ++k) {
+        pos = tk_json_skip_ws(rd, pos);
+        const int c = rd(pos);
+        if (c != '[') return (tk_is_numclass(c) || c == '{' || c == '"') ? TK_ERR_RAGGED : TK_ERR_SYNTAX;
+        ++pos;
+    }
+    pos = tk_json_skip_ws(rd, pos);
+    {
+        const int c = rd(pos);
+        if (c == '[' || c == '{' || c == '"') return TK_ERR_RAGGED;           // deeper than declared / not a number
+    }
+    const tk_token t = tk_scan_number(rd, pos);
+    if (t.err) return t.err;
+    pos = t.end;
+    for (uint32_t k = 0; k < n_close; ++k) {
+        pos = tk_json_skip_ws(rd, pos);
+        const int c = rd(pos);
+        if (c != ']') return c == ',' ? TK_ERR_RAGGED : TK_ERR_SYNTAX;           // the sub-array goes on
+        ++pos;
+    }
+    pos = tk_json_skip_ws(rd, pos);
+    {
+        const int c = rd(pos);
+        if (last) { if (c != -1) return TK_ERR_SYNTAX; }                        // "Extra data"
+        else if (c != ',') return c == ']' ? TK_ERR_RAGGED : TK_ERR_SYNTAX;      // the sub-array ends early
+    }
+    int st;
+    if (KIND == TK_F32 || KIND == TK_F64) {
+        double d;
+        st = tk_token_to_f64(rd, t, &d);
+        if (st) return st;
+        *out = (typename tk_elem<KIND>::type)d;
+    } else {
+        int64_t v;
+        st = tk_token_to_i64(rd, t, KIND == TK_I32 ? 32 : 64, &v);
+        if (st) return st;
+        *out = (typename tk_elem<KIND>::type)v;
+    }
+    return TK_OK;
+}
+

@@ -34,6 +34,7 @@ struct scan_args {
     uint32_t*       tok_count;
     uint32_t*       tok_count_next;   // counter of the slot's next scan: zeroed here
     uint32_t        tok_cap;
+    uint32_t        ndim;         // > 1: nested arrays of a fixed shape (head = ndim brackets, every comma a leaf)
     tk_plan_reset   reset;
 };
 
@@ -124,7 +125,10 @@ __global__ void __launch_bounds__(256) k_json_scan(const scan_args a) {
             const uint32_t w0 = off < 4 ? head_chunk.x : off < 8 ? head_chunk.y : off < 12 ? head_chunk.z : head_chunk.w;
             const uint32_t w1 = off < 4 ? head_chunk.y : off < 8 ? head_chunk.z : off < 12 ? head_chunk.w : 0u;
             const uint32_t two = __funnelshift_r(w0, w1, 8 * (off & 3u));     // bytes start, start + 1
-            if (off < 15 && start + 1 < end && (two & 0xFFu) == '[' && tk_is_numclass((int)((two >> 8) & 0xFFu))) {
+            if (a.ndim > 1) {
+                GlobalReader rd{a.bytes, end};
+                head = end > start ? tk_json_prefix_nested(rd, start, a.ndim, &first) : TK_ERR_SYNTAX;
+            } else if (off < 15 && start + 1 < end && (two & 0xFFu) == '[' && tk_is_numclass((int)((two >> 8) & 0xFFu))) {
                 head = TK_OK;
                 first = start + 1;
             } else {
@@ -132,7 +136,7 @@ __global__ void __launch_bounds__(256) k_json_scan(const scan_args a) {
                 head = end > start ? tk_json_prefix(rd, start, &first, &empty) : TK_ERR_SYNTAX;
             }
             len = (!head && empty) ? 0u : commas + 1u;
-            const int status = head ? head : (len > a.max_len ? TK_ERR_TOO_LONG : TK_OK);
+            const int status = head ? head : (len > a.max_len ? (a.ndim > 1 ? TK_ERR_RAGGED : TK_ERR_TOO_LONG) : TK_OK);
             a.rec_len[i] = (int32_t)len;
             a.rec_status[i] = status;
             a.rec_kidx[i] = (status == TK_OK && len >= a.min_size) ? 0 : -1;
@@ -180,7 +184,31 @@ __global__ void __launch_bounds__(256) k_json_scan(const scan_args a) {
     }
 }
 
+static int json_scan_impl(tk_ctx* ctx, int slot, uint32_t max_len, uint32_t min_size, uint32_t ndim, void* stream);
+
 extern "C" int tk_json_scan(tk_ctx* ctx, int slot, uint32_t max_len, uint32_t min_size, void* stream) {
+    return json_scan_impl(ctx, slot, max_len, min_size, 0, stream);
+}
+
+// leaves per record of a [dims] array; 0 if the shape is not acceptable
+static uint64_t nested_leaves(uint32_t ndim, const uint32_t* dims) {
+    if (ndim < 1 || ndim > TK_JSON_NESTED_MAX_DIMS || !dims) return 0;
+    uint64_t n = 1;
+    for (uint32_t k = 0; k < ndim; ++k) {
+        if (!dims[k]) return 0;
+        n *= dims[k];
+        if (n > (1u << 24)) return 0;
+    }
+    return n;
+}
+
+extern "C" int tk_json_nested_scan(tk_ctx* ctx, int slot, uint32_t ndim, const uint32_t* dims, void* stream) {
+    const uint64_t leaves = nested_leaves(ndim, dims);
+    TK_REQUIRE(leaves, "1..%d dimensions of at least 1, at most 2^24 elements", TK_JSON_NESTED_MAX_DIMS);
+    return json_scan_impl(ctx, slot, (uint32_t)leaves, 0, ndim, stream);
+}
+
+static int json_scan_impl(tk_ctx* ctx, int slot, uint32_t max_len, uint32_t min_size, uint32_t ndim, void* stream) {
     TK_ENTER(ctx, slot);
     tk_slot& s = ctx->slots[slot];
     const uint32_t n = s.n_records;
@@ -194,6 +222,7 @@ extern "C" int tk_json_scan(tk_ctx* ctx, int slot, uint32_t max_len, uint32_t mi
     s.tok_use++;
     a.tok = s.d.tok_pos; a.tok_count = s.d.tok_count + (s.tok_use & 1u); a.tok_count_next = s.d.tok_count + ((s.tok_use + 1) & 1u);
     a.tok_cap = (uint32_t)(ctx->tok_cap > 0xFFFFFFFFull ? 0xFFFFFFFFull : ctx->tok_cap);
+    a.ndim = ndim;
     a.reset = tk_plan_reset_args(ctx, slot);
     // one warp per record; 4-warp blocks: records differ in length, and a block holds its
     // slots until its longest record is done
@@ -225,6 +254,7 @@ struct flat_args {
     const uint2*    tok;          // {byte position, record} per element
     const uint32_t* tok_count;
     uint32_t        tok_cap;
+    tk_nested_shape shape;        // ndim > 1: nested arrays of a fixed shape
     tk_plane_t      values, lengths, mask;
 };
 
@@ -306,11 +336,20 @@ __global__ void __launch_bounds__(256, 5) k_json_parse(const flat_args a) {
         int st = TK_OK;
         uint64_t F;
         uint32_t I, L2, neg;
-        bool fast = flags != TOK_LAST && fast_number(a.bytes, pos, stop, tb.pow10, &I, &F, &L2, &neg);
+        // nested arrays: the brackets around leaf e follow from e and the shape; leaves without any
+        // take the same fast lane as the elements of a flat array
+        uint32_t n_open = 0, n_close = 0;
+        if (a.shape.ndim > 1) {
+            n_open = e ? tk_nested_opens(a.shape, e) : 0u;               // (the head took the first leaf's)
+            n_close = flags ? a.shape.ndim : tk_nested_opens(a.shape, e + 1);
+        }
+        bool fast = flags != TOK_LAST && !(n_open | n_close) &&
+                    fast_number(a.bytes, pos, stop, tb.pow10, &I, &F, &L2, &neg);
         if (fast) fast = fast_convert<KIND>(I, F, L2, neg, tb, &v);
         if (!fast) {
             GlobalReader rd{a.bytes, end};
-            st = tk_json_element_flat<KIND>(rd, pos, &v);
+            st = a.shape.ndim > 1 ? tk_json_element_nested<KIND>(rd, pos, n_open, n_close, flags != 0, &v)
+                                  : tk_json_element_flat<KIND>(rd, pos, &v);
         }
         if (st) { flag_record(a.rec_status, a.res, rec, st); continue; }
         if (kidx >= 0 && e < a.max_len) values[(uint64_t)(B + (uint32_t)kidx) * a.max_len + e] = v;
@@ -336,9 +375,26 @@ static uint32_t parse_grid(int dtype) {
     return cached[k];
 }
 
+static int json_decode_impl(tk_ctx* ctx, int slot, int dtype, uint32_t max_len, uint32_t fixed_len, uint32_t ndim,
+                            const uint32_t* dims, const tk_plane_t* values, const tk_plane_t* lengths,
+                            const tk_plane_t* mask, void* stream);
+
 extern "C" int tk_json_decode(tk_ctx* ctx, int slot, int dtype, uint32_t max_len, uint32_t fixed_len,
                               const tk_plane_t* values, const tk_plane_t* lengths, const tk_plane_t* mask,
                               void* stream) {
+    return json_decode_impl(ctx, slot, dtype, max_len, fixed_len, 0, nullptr, values, lengths, mask, stream);
+}
+
+extern "C" int tk_json_nested_decode_flat(tk_ctx* ctx, int slot, int dtype, uint32_t ndim, const uint32_t* dims,
+                                          const tk_plane_t* values, void* stream) {
+    const uint64_t leaves = nested_leaves(ndim, dims);
+    TK_REQUIRE(leaves, "1..%d dimensions of at least 1, at most 2^24 elements", TK_JSON_NESTED_MAX_DIMS);
+    return json_decode_impl(ctx, slot, dtype, (uint32_t)leaves, (uint32_t)leaves, ndim, dims, values, nullptr, nullptr, stream);
+}
+
+static int json_decode_impl(tk_ctx* ctx, int slot, int dtype, uint32_t max_len, uint32_t fixed_len, uint32_t ndim,
+                            const uint32_t* dims, const tk_plane_t* values, const tk_plane_t* lengths,
+                            const tk_plane_t* mask, void* stream) {
     TK_ENTER(ctx, slot);
     tk_slot& s = ctx->slots[slot];
     cudaStream_t st = (cudaStream_t)stream;
@@ -354,6 +410,14 @@ extern "C" int tk_json_decode(tk_ctx* ctx, int slot, int dtype, uint32_t max_len
     a.rec_tok = s.d.rec_tok; a.res = s.d.result;
     a.tok = reinterpret_cast<const uint2*>(s.d.tok_pos); a.tok_count = s.d.tok_count + (s.tok_use & 1u);
     a.tok_cap = (uint32_t)(ctx->tok_cap > 0xFFFFFFFFull ? 0xFFFFFFFFull : ctx->tok_cap);
+    a.shape.ndim = ndim;
+    {
+        uint32_t prod = 1;
+        for (uint32_t j = TK_JSON_NESTED_MAX_DIMS; j-- > 0;) {
+            if (j < ndim) prod *= dims[j];
+            a.shape.span[j] = prod;
+        }
+    }
     tk_plane_t z; z.base = nullptr; z.row_bytes = 0;
     a.values = *values;
     a.lengths = lengths ? *lengths : z;

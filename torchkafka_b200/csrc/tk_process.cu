@@ -34,7 +34,12 @@ extern "C" int tk_process_slot(tk_ctx* ctx, int slot, const tk_job_t* job, void*
         if (rc) return rc;
         return tk_slot_fetch_result(ctx, slot, stream);
     }
+    // nested arrays of two or more dimensions go through the flat chain too: every comma separates two
+    // leaves, the brackets around a leaf follow from its index (tk_json.cuh); the object kernel's
+    // sequential scanner (tk_json_nested_decode) stays the staged entry point and the cross-check
+    const bool nested_flat = job->schema == TK_SCHEMA_NESTED && job->max_len >= 2;
     if (job->schema == TK_SCHEMA_JSON) rc = tk_json_scan(ctx, slot, job->max_len, job->min_size, stream);
+    else if (nested_flat) rc = tk_json_nested_scan(ctx, slot, job->max_len, job->field_bytes, stream);
     else rc = tk_raw_scan(ctx, slot, (job->schema == TK_SCHEMA_OBJECT || job->schema == TK_SCHEMA_NESTED) ? TK_ANY_RECORD_BYTES : job->record_bytes, stream);
     if (rc) return rc;
     rc = tk_compact(ctx, slot, job->batch_size, stream); if (rc) return rc;
@@ -59,7 +64,8 @@ extern "C" int tk_process_slot(tk_ctx* ctx, int slot, const tk_job_t* job, void*
             rc = tk_json_object_decode(ctx, slot, job->dtype, &job->cur[0], stream);
             break;
         case TK_SCHEMA_NESTED:
-            rc = tk_json_nested_decode(ctx, slot, job->dtype, job->max_len, job->field_bytes, &job->cur[0], stream);
+            rc = nested_flat ? tk_json_nested_decode_flat(ctx, slot, job->dtype, job->max_len, job->field_bytes, &job->cur[0], stream)
+                             : tk_json_nested_decode(ctx, slot, job->dtype, job->max_len, job->field_bytes, &job->cur[0], stream);
             break;
         case TK_SCHEMA_IMAGE:
             rc = tk_collate_image_u8_bf16_nchw(ctx, slot, job->height, job->width, job->channels,

@@ -11,10 +11,6 @@
 #define PY_SSIZE_T_CLEAN
 #include <Python.h>
 #include <stdint.h>
-#include <stdlib.h>
-#include <algorithm>
-#include <atomic>
-#include <thread>
 #include <vector>
 
 struct Sink {
@@ -27,18 +23,6 @@ struct Sink {
     unsigned long long max_bytes;
     PyObject* keep;              // owns temporaries of the slow paths (created on demand)
 };
-
-// threads of the GIL-free harvest (TK_HARVEST_THREADS, default 4, at most 16)
-static int harvest_threads() {
-    static int n = 0;
-    if (!n) {
-        const char* e = getenv("TK_HARVEST_THREADS");
-        n = e ? atoi(e) : 4;
-        if (n < 1) n = 1;
-        if (n > 16) n = 16;
-    }
-    return n;
-}
 
 static PyObject* s_value = nullptr;
 static PyObject* s_offset = nullptr;
@@ -244,67 +228,14 @@ static PyObject* harvest_groups(PyObject*, PyObject* args) {
     if (vi >= 0 && oi >= 0) {
         bool bail = false;
         Py_ssize_t bail_at = 0;
-        // Large poll results are harvested by several threads: every record is three dependent
-        // cache misses, and this stretch is what serialises the producer threads (records must be
-        // gathered in consumption order).  Phase A, parallel: (address, length, offset, partition)
-        // of record i of the flattened result go to entry i; phase B, sequential over the flat
-        // lengths: where the slot is full.
-        std::vector<Py_ssize_t> gstart((size_t)ng + 1, 0);
-        for (Py_ssize_t q = 0; q < ng; ++q) gstart[(size_t)q + 1] = gstart[(size_t)q] + gs[(size_t)q].size;
-        const Py_ssize_t n_all = gstart[(size_t)ng] < max_records ? gstart[(size_t)ng] : max_records;
-        const int n_thr = harvest_threads();
-        if (n_thr > 1 && n_all >= 4096) {
-            std::atomic<Py_ssize_t> first_bad(n_all);
-            Py_BEGIN_ALLOW_THREADS
-            auto slice = [&](Py_ssize_t a, Py_ssize_t b) {
-                size_t q = (size_t)(std::upper_bound(gstart.begin(), gstart.end(), a) - gstart.begin()) - 1;
-                Py_ssize_t i = a;
-                while (i < b) {
-                    const Group& gr = gs[q];
-                    const Py_ssize_t lo = i - gstart[q], hi = (b < gstart[q + 1] ? b : gstart[q + 1]) - gstart[q];
-                    Sink part = {k.ptrs + i, k.lens + i, k.offs + i, 0, hi - lo, 0, ~0ull, nullptr};
-                    bool bad = false;
-                    const Py_ssize_t got = harvest_nogil(part, gr.items + lo, hi - lo, vi, oi, &bad);
-                    for (Py_ssize_t j = 0; j < got; ++j) parts[i + j] = (int32_t)gr.dense;
-                    if (bad) {
-                        Py_ssize_t cur = first_bad.load();
-                        while (i + got < cur && !first_bad.compare_exchange_weak(cur, i + got)) {}
-                        return;
-                    }
-                    i += hi - lo;
-                    ++q;
-                }
-            };
-            std::vector<std::thread> pool;
-            const Py_ssize_t per = (n_all + n_thr - 1) / n_thr;
-            for (int t = 1; t < n_thr; ++t) {
-                const Py_ssize_t a = per * t, b = a + per < n_all ? a + per : n_all;
-                if (a < b) pool.emplace_back(slice, a, b);
-            }
-            slice(0, per < n_all ? per : n_all);
-            for (auto& th : pool) th.join();
-            const Py_ssize_t n_ok = first_bad.load();
-            Py_ssize_t i = 0;
-            for (; i < n_ok; ++i) {
-                if (k.total + k.lens[i] > k.max_bytes) break;
-                k.total += k.lens[i];
-            }
-            k.taken = i;
-            bail = i == n_ok && n_ok < n_all;               // reached a record that needs the general path
-            g = (Py_ssize_t)(std::upper_bound(gstart.begin(), gstart.end(), i) - gstart.begin()) - 1;
-            if (g >= ng) { g = ng; partial = 0; }
-            else { partial = i - gstart[(size_t)g]; bail_at = partial; }
-            Py_END_ALLOW_THREADS
-        } else {
-            Py_BEGIN_ALLOW_THREADS
-            for (; g < ng; ++g) {
-                const Py_ssize_t before = k.taken;
-                const Py_ssize_t got = harvest_nogil(k, gs[g].items, gs[g].size, vi, oi, &bail);
-                for (Py_ssize_t j = before; j < k.taken; ++j) parts[j] = (int32_t)gs[g].dense;
-                if (got < gs[g].size) { partial = got; bail_at = got; break; }
-            }
-            Py_END_ALLOW_THREADS
+        Py_BEGIN_ALLOW_THREADS
+        for (; g < ng; ++g) {
+            const Py_ssize_t before = k.taken;
+            const Py_ssize_t got = harvest_nogil(k, gs[g].items, gs[g].size, vi, oi, &bail);
+            for (Py_ssize_t j = before; j < k.taken; ++j) parts[j] = (int32_t)gs[g].dense;
+            if (got < gs[g].size) { partial = got; bail_at = got; break; }
         }
+        Py_END_ALLOW_THREADS
         if (!bail) done = true;              // all groups taken, or the sink is full
         else {
             // finish group g from record bail_at under the GIL (general path), then go on below

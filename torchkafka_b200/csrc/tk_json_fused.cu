@@ -20,13 +20,17 @@
 //             sums (block scan) -> the element count of every record (commas + 1), its keep flag
 //             (min_size), the head check ([BOM] ws* '['), and a list of segments (one per element:
 //             window position, record) scattered into shared memory.
-//   place     single-pass scan with decoupled look-back over the tiles (as tk_plan.cu does over
-//             blocks of records): the tile publishes its kept count, looks back for its exclusive
-//             prefix -> output row of every kept record, batch boundaries, longest record per
-//             batch, and the segmented max of (offset + 1) per (batch, partition) for the commit.
-//   rows      pad / length / mask of every kept record's row (warp per record).
 //   parse     thread per element out of the window: the fast lane of tk_json_parse.cuh (what
-//             json.dumps writes), else the scalar grammar; value stored in the record's row.
+//             json.dumps writes), else the scalar grammar.  The values of the first round of
+//             segments are staged in shared memory: their rows are not known yet.
+//   place     single-pass scan with decoupled look-back over the tiles (as tk_plan.cu does over
+//             blocks of records): the tile publishes its kept count right after the cut and looks
+//             back for its exclusive prefix only after the parse, when the tiles in front of it
+//             have long published theirs -> output row of every kept record, batch boundaries,
+//             longest record per batch, and the segmented max of (offset + 1) per (batch,
+//             partition) for the commit.
+//   rows      pad / length / mask of every kept record's row (warp per record); the staged values
+//             go to their rows.
 //
 // A tile that does not fit the window (a record longer than the window's slack) or holds more
 // records than the per-tile tables takes a scalar path, thread per record, out of global memory:

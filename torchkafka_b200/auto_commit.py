@@ -35,12 +35,18 @@ from __future__ import annotations
 import collections
 import ctypes
 import itertools
+import logging
 import multiprocessing
 import time
 
 from torch.utils.data import DataLoader
 
+from . import kafka_dataset as _kd
 from .kafka_dataset import KafkaDataset
+
+#: "no offsets pending": an empty map that is never written to (``_note_offsets`` replaces an empty
+#: pending map instead of updating it)
+_NOTHING_PENDING: dict = {}
 
 
 class _CommitBarrier:
@@ -99,12 +105,30 @@ def _device_path(dataloader: DataLoader, commit_barrier=None):
         # Per slot, not per batch: the pipeline hands over the lists of a slot's batches and commit
         # maps; per batch this loop does one yield and one commit (with batch_size=4 the depth of
         # the generator chain is what the host spends its time on).
+        # When commit() is the stock method and nothing is pending from an earlier batch, the commit
+        # of a batch is issued right here (same steps as KafkaDataset.commit: the consumer lock, the
+        # explicit offsets of the batch, failures logged not raised).
+        stock = type(dataset).commit is KafkaDataset.commit and not _kd._logger.isEnabledFor(logging.DEBUG)
+        failed = _kd._commit_failed_types()
         for views, maps, pipe in dataset._device_slot_batches(dataloader.batch_size, dataloader.drop_last):  # pylint: disable=protected-access
-            for j in range(len(views)):
+            lock = pipe.consumer_lock
+            commit = dataset._consumer.commit                       # pylint: disable=protected-access
+            for j, batch in enumerate(views):
                 pipe.delivered_index = j
-                dataset._note_offsets(maps[j])          # pylint: disable=protected-access
-                yield views[j]
-                dataset.commit()
+                offsets = maps[j]
+                if stock and not dataset._explicit_offsets:         # pylint: disable=protected-access
+                    dataset._explicit_offsets = offsets             # (what leaving the loop here leaves pending)
+                    yield batch
+                    try:
+                        with lock:
+                            commit(offsets)
+                        dataset._explicit_offsets = _NOTHING_PENDING
+                    except failed:
+                        _kd._logger.error("Commit failed.")
+                else:
+                    dataset._note_offsets(offsets)                  # pylint: disable=protected-access
+                    yield batch
+                    dataset.commit()
         return
     barrier = _CommitBarrier(dataset, commit_barrier)
     for batch in dataset.device_batches(dataloader.batch_size, dataloader.drop_last):

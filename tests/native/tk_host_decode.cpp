@@ -183,6 +183,73 @@ extern "C" int tk_host_zstd(const uint8_t* in, uint32_t len, uint8_t* out, uint3
     return 0;
 }
 
+// The same through the batched sequence decoder (tk_zstd_next_batch), the copies of a batch executed
+// in the order the device executes them: every literal run, then the matches that do not depend on
+// an earlier match of the batch, then the dependent ones in sequence order.
+extern "C" int tk_host_zstd_batched(const uint8_t* in, uint32_t len, uint8_t* out, uint32_t cap, uint32_t* out_len) {
+    static tk_zstd_tables tb;
+    static tk_zstd_batch b;
+    tk_zstd_state s;
+    tk_zstd_init(s, tb, in, 0, len);
+    uint32_t op = 0;
+    tk_zstd_event ev;
+    for (;;) {
+        const int n = tk_zstd_next_batch(s, tb, cap, op, true, &b);
+        if (n < 0) return -n;
+        if (n > 0) {
+            uint32_t dst[TK_ZS_BATCH], pos = op, first_dst = 0;
+            bool have_first = false;
+            for (int k = 0; k < n; ++k) { dst[k] = pos; pos += b.lit_len[k] + b.mlen[k]; }
+            if (b.lit_kind == TK_ZL_OUTPUT && pos > b.lit_src[0]) {
+                // the batch writes into parked literals it still reads: sequence order
+                for (int k = 0; k < n; ++k) {
+                    for (uint32_t j = 0; j < b.lit_len[k]; ++j) out[dst[k] + j] = out[b.lit_src[k] + j];
+                    const uint32_t mdst = dst[k] + b.lit_len[k];
+                    for (uint32_t j = 0; j < b.mlen[k]; ++j) out[mdst + j] = out[mdst - b.offset[k] + j];
+                }
+                op = pos;
+                continue;
+            }
+            // literals, last run first: the device copies them side by side, so no run may write
+            // what another one reads -- the reverse order makes such a dependency visible here
+            for (int k = n - 1; k >= 0; --k) {
+                if (b.lit_kind == TK_ZL_INPUT) memmove(out + dst[k], in + b.lit_src[k], b.lit_len[k]);
+                else if (b.lit_kind == TK_ZL_RLE) memset(out + dst[k], (int)b.lit_src[k], b.lit_len[k]);
+                else for (uint32_t j = 0; j < b.lit_len[k]; ++j) out[dst[k] + j] = out[b.lit_src[k] + j];
+            }
+            bool dep[TK_ZS_BATCH];
+            for (int k = 0; k < n; ++k) {
+                const uint32_t mdst = dst[k] + b.lit_len[k];
+                if (b.mlen[k] && !have_first) { have_first = true; first_dst = mdst; }
+                dep[k] = b.mlen[k] && (mdst - b.offset[k] + b.mlen[k] > first_dst || b.offset[k] < b.mlen[k] || b.mlen[k] > 32u);
+            }
+            for (int pass = 0; pass < 2; ++pass)                 // independent matches first, then the dependent ones
+                for (int k = 0; k < n; ++k) {
+                    if ((int)dep[k] != pass) continue;
+                    const uint32_t mdst = dst[k] + b.lit_len[k];
+                    for (uint32_t j = 0; j < b.mlen[k]; ++j) out[mdst + j] = out[mdst - b.offset[k] + j];
+                }
+            op = pos;
+            continue;
+        }
+        const int st = tk_zstd_next(s, tb, out, cap, op, true, &ev);
+        if (st == TK_ZS_DONE) break;
+        if (st == TK_ZS_HUF) {
+            for (uint32_t k = 0; k < ev.h_streams; ++k)
+                if (!tk_huf_stream(in, ev.h_lo[k], ev.h_hi[k], tb.huf, (int)ev.h_log, out + ev.h_dst[k], ev.h_n[k])) return TK_ZS_ERROR;
+            continue;
+        }
+        if (st != TK_ZS_COPY) return st;
+        if (ev.lit_kind == TK_ZL_INPUT) memmove(out + op, in + ev.lit_src, ev.lit_len);
+        else if (ev.lit_kind == TK_ZL_RLE) memset(out + op, (int)ev.lit_src, ev.lit_len);
+        else for (uint32_t k = 0; k < ev.lit_len; ++k) out[op + k] = out[ev.lit_src + k];
+        for (uint32_t k = 0; k < ev.mlen; ++k) out[op + ev.lit_len + k] = out[op + ev.lit_len - ev.offset + k];
+        op += ev.lit_len + ev.mlen;
+    }
+    *out_len = op;
+    return 0;
+}
+
 // Nested arrays of a fixed shape (tk_json_object.cuh): leaves in C order, status.
 extern "C" int tk_host_decode_nested(const uint8_t* buf, uint32_t len, int kind, const uint32_t* dims, uint32_t ndim,
                                      void* row) {

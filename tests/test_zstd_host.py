@@ -28,6 +28,16 @@ def unzstd(lib, z: bytes, cap: int, emit: bool = True):
     n = ctypes.c_uint32()
     st = lib.tk_host_zstd(z, len(z), out.ctypes.data_as(ctypes.c_void_p), cap, 1 if emit else 0, ctypes.byref(n))
     assert (out[cap:] == 0xA5).all(), "wrote past the output buffer"
+    if emit:
+        # the batched sequence decoder (tk_zstd_next_batch) with the device's execution order of a
+        # batch's copies must agree with the sequence-by-sequence decoder: status and bytes
+        out2 = np.full(cap + CANARY, 0xA5, np.uint8)
+        n2 = ctypes.c_uint32()
+        st2 = lib.tk_host_zstd_batched(z, len(z), out2.ctypes.data_as(ctypes.c_void_p), cap, ctypes.byref(n2))
+        assert (out2[cap:] == 0xA5).all(), "batched decoder wrote past the output buffer"
+        assert (st2 == 0) == (st == 0), (st, st2)
+        if st == 0:
+            assert n2.value == n.value and bytes(out2[:n2.value]) == bytes(out[:n.value])
     return st, (bytes(out[:n.value]) if emit else n.value)
 
 

@@ -583,11 +583,94 @@ union unit_tables {
 // Lane 0 owns the decoder state and produces copy events; the warp executes them.  Literals that
 // lane 0 decoded itself (Huffman) are parked at the end of the unit's output and move down from
 // there: the destination is below the source, so chunks of 32 bytes go load, barrier, store.
+// The copies of a batch of sequences (tk_zstd_next_batch), lane per sequence: places by a warp prefix
+// sum, every literal run, then the matches that read nothing an earlier match of the batch writes
+// (most of them), then the dependent ones in sequence order, each by the whole warp.
+__device__ __forceinline__ void zstd_exec_batch(const tk_zstd_batch& b, uint32_t n, const uint8_t* raw, uint8_t* out,
+                                                uint32_t& op, uint32_t lane) {
+    uint32_t ll = 0, ml = 0, off = 0, src = 0;
+    if (lane < n) { ll = b.lit_len[lane]; ml = b.mlen[lane]; off = b.offset[lane]; src = b.lit_src[lane]; }
+    const uint32_t kind = b.lit_kind;
+    uint32_t incl = ll + ml;
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+        const uint32_t o = __shfl_up_sync(0xffffffffu, incl, d);
+        if (lane >= (uint32_t)d) incl += o;
+    }
+    const uint32_t dst = op + incl - (ll + ml);
+    const uint32_t total = __shfl_sync(0xffffffffu, incl, 31);
+    // Parked literals (TK_ZL_OUTPUT) lie ahead of the write position of the sequence that reads
+    // them, not of the later sequences' of the batch: near the end of a unit whose output region
+    // is exactly its size, sequence e may write where sequence j < e still has to read.  Such a
+    // batch (its writes reach the first parked byte it reads) goes in sequence order.
+    if (kind == TK_ZL_OUTPUT && op + total > __shfl_sync(0xffffffffu, src, 0)) {
+        for (uint32_t e = 0; e < n; ++e) {
+            const uint32_t sE = __shfl_sync(0xffffffffu, src, e), dE = __shfl_sync(0xffffffffu, dst, e);
+            const uint32_t nE = __shfl_sync(0xffffffffu, ll, e), mE = __shfl_sync(0xffffffffu, ml, e);
+            const uint32_t oE = __shfl_sync(0xffffffffu, off, e);
+            if (sE != dE) {
+                for (uint32_t base = 0; base < nE; base += 32) {      // destination below the source
+                    const uint32_t k = base + lane;
+                    const uint8_t v = k < nE ? out[sE + k] : 0;
+                    __syncwarp();
+                    if (k < nE) out[dE + k] = v;
+                }
+            }
+            __syncwarp();
+            if (mE) cz_match(out, dE + nE, oE, mE, lane);
+            __syncwarp();
+        }
+        op += total;
+        return;
+    }
+    // literal runs (their sources are the input, a byte, or parked literals ahead of every write
+    // position of the batch); long ones by the whole warp
+    uint32_t longs = __ballot_sync(0xffffffffu, ll > 32u);
+    if (ll <= 32u) {
+        if (kind == TK_ZL_INPUT) { for (uint32_t k = 0; k < ll; ++k) out[dst + k] = raw[src + k]; }
+        else if (kind == TK_ZL_RLE) { for (uint32_t k = 0; k < ll; ++k) out[dst + k] = (uint8_t)src; }
+        else { for (uint32_t k = 0; k < ll; ++k) out[dst + k] = out[src + k]; }
+    }
+    while (longs) {
+        const int L = __ffs((int)longs) - 1;
+        longs &= longs - 1u;
+        const uint32_t sL = __shfl_sync(0xffffffffu, src, L), dL = __shfl_sync(0xffffffffu, dst, L);
+        const uint32_t nL = __shfl_sync(0xffffffffu, ll, L);
+        for (uint32_t k = lane; k < nL; k += 32)
+            out[dL + k] = kind == TK_ZL_INPUT ? raw[sL + k] : kind == TK_ZL_RLE ? (uint8_t)sL : out[sL + k];
+    }
+    __syncwarp();
+    // matches: one depends on earlier matches of the batch only if its source reaches behind the
+    // first match destination of the batch (or into its own destination)
+    const uint32_t mdst = dst + ll;
+    const uint32_t has = __ballot_sync(0xffffffffu, ml > 0u);
+    const uint32_t first_dst = __shfl_sync(0xffffffffu, mdst, has ? __ffs((int)has) - 1 : 0);
+    const bool dep = ml && (mdst - off + ml > first_dst || off < ml || ml > 32u);
+    if (ml && !dep) { for (uint32_t k = 0; k < ml; ++k) out[mdst + k] = out[mdst - off + k]; }
+    uint32_t deps = __ballot_sync(0xffffffffu, dep);
+    while (deps) {
+        const int L = __ffs((int)deps) - 1;
+        deps &= deps - 1u;
+        cz_match(out, __shfl_sync(0xffffffffu, mdst, L), __shfl_sync(0xffffffffu, off, L), __shfl_sync(0xffffffffu, ml, L), lane);
+    }
+    op += __shfl_sync(0xffffffffu, incl, 31);
+    __syncwarp();
+}
+
 __device__ __forceinline__ uint32_t zstd_run(const uint8_t* raw, uint32_t lane, uint32_t p, uint32_t end, uint8_t* out,
                                              uint32_t cap, uint32_t& op, tk_zstd_tables& tb, tk_zstd_event& ev) {
     tk_zstd_state s;
     if (lane == 0) tk_zstd_init(s, tb, raw, p, end);
+    tk_zstd_batch* batch = tk_zstd_batch_of(tb);
     for (;;) {
+        // inside a sequence section: up to 32 sequences decoded by lane 0 in one tight loop, their
+        // copies executed by the warp side by side
+        int nb = 0;
+        if (lane == 0) nb = tk_zstd_next_batch(s, tb, cap, op, true, batch);
+        __syncwarp();
+        nb = __shfl_sync(0xffffffffu, nb, 0);
+        if (nb < 0) return nb == -(int)TK_ZS_UNSUPPORTED ? TK_STATUS_UNSUPPORTED : TK_STATUS_CORRUPT;
+        if (nb > 0) { zstd_exec_batch(*batch, (uint32_t)nb, raw, out, op, lane); continue; }
         uint32_t st = TK_ZS_DONE;
         if (lane == 0) st = (uint32_t)tk_zstd_next(s, tb, out, cap, op, true, &ev);
         __syncwarp();                                       // the event (shared memory) and the tables are written

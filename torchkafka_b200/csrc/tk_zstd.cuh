@@ -39,11 +39,13 @@ struct tk_fse_entry {
 struct tk_zstd_tables {
     tk_fse_entry ll[512], ml[512], of[256], wt[64];   // sequences (accuracy <= 9, 9, 8), Huffman weights (<= 6)
     uint16_t huf[2048];            // literals: symbol | code length << 8, indexed by the next huf_log bits
+    // scratch of the table builds (1 KiB, word aligned); between the builds of two blocks it holds
+    // the batch of decoded sequences (tk_zstd_batch, tk_zstd_batch_of)
+    int16_t  norm[256];            // normalised counts of a table description
+    uint16_t desc[256];            // per-symbol state counter of the table build
     uint32_t ll_base[36], ml_base[53];
     uint8_t  ll_bits[36], ml_bits[53];
     uint8_t  weights[256];
-    int16_t  norm[256];            // scratch: normalised counts of a table description
-    uint16_t desc[256];            // scratch: per-symbol state counter of the table build
 };
 
 TK_HD int tk_zs_highbit(uint32_t x) {                  // index of the highest set bit, x != 0
@@ -88,17 +90,37 @@ struct tk_zs_win {
     int32_t  lo;
 };
 TK_HD void tk_zs_win_init(tk_zs_win& w) { w.bits = 0; w.lo = -(1 << 30); }
+// bytes [b, b + 8) of the array in[lo, hi) as a little-endian word, bytes outside it read as zero.
+// Inside the array (all reloads but the ones at its two ends): three aligned word loads and a
+// funnel shift on the device (the compressed bytes sit in a padded, word-aligned buffer), one
+// unaligned load on the host; byte by byte only at the ends.
+TK_HD uint64_t tk_zs_load64(const uint8_t* in, uint32_t lo, uint32_t hi, int32_t b) {
+    if (b >= 0 && (uint32_t)b + 8u <= hi - lo) {
+        const uint8_t* a = in + lo + (uint32_t)b;
+#if defined(__CUDA_ARCH__)
+        const uint32_t* w = reinterpret_cast<const uint32_t*>(reinterpret_cast<uintptr_t>(a) & ~(uintptr_t)3);
+        const uint32_t sh = ((uint32_t)reinterpret_cast<uintptr_t>(a) & 3u) * 8u;
+        const uint32_t w0 = w[0], w1 = w[1], w2 = sh ? w[2] : 0u;
+        return ((uint64_t)__funnelshift_r(w1, w2, sh) << 32) | __funnelshift_r(w0, w1, sh);
+#else
+        uint64_t v;
+        memcpy(&v, a, 8);
+        return v;
+#endif
+    }
+    uint64_t v = 0;
+    for (int k = 0; k < 8; ++k) {
+        const int32_t bk = b + k;
+        if (bk >= 0 && (uint32_t)bk < hi - lo) v |= (uint64_t)in[lo + (uint32_t)bk] << (8 * k);
+    }
+    return v;
+}
 TK_HD uint32_t tk_zs_win_get(tk_zs_win& w, const uint8_t* in, uint32_t lo, uint32_t hi, int32_t bitpos, int n) {
     if (n == 0) return 0;
     if ((uint32_t)(bitpos - w.lo) > (uint32_t)(64 - n)) {
         // reload so that the window ends just above these bits: the readers move downwards
         const int32_t b = ((bitpos + n + 7) >> 3) - 8;
-        uint64_t v = 0;
-        for (int k = 0; k < 8; ++k) {
-            const int32_t bk = b + k;
-            if (bk >= 0 && (uint32_t)bk < hi - lo) v |= (uint64_t)in[lo + (uint32_t)bk] << (8 * k);
-        }
-        w.bits = v;
+        w.bits = tk_zs_load64(in, lo, hi, b);
         w.lo = 8 * b;
     }
     const uint32_t v = (uint32_t)(w.bits >> (bitpos - w.lo));
@@ -108,12 +130,7 @@ TK_HD uint32_t tk_zs_win_get(tk_zs_win& w, const uint8_t* in, uint32_t lo, uint3
 TK_HD uint64_t tk_zs_win_get64(tk_zs_win& w, const uint8_t* in, uint32_t lo, uint32_t hi, int32_t bitpos, int n) {
     if ((uint32_t)(bitpos - w.lo) > (uint32_t)(64 - n)) {
         const int32_t b = ((bitpos + n + 7) >> 3) - 8;
-        uint64_t v = 0;
-        for (int k = 0; k < 8; ++k) {
-            const int32_t bk = b + k;
-            if (bk >= 0 && (uint32_t)bk < hi - lo) v |= (uint64_t)in[lo + (uint32_t)bk] << (8 * k);
-        }
-        w.bits = v;
+        w.bits = tk_zs_load64(in, lo, hi, b);
         w.lo = 8 * b;
     }
     return w.bits >> (bitpos - w.lo);
@@ -629,4 +646,112 @@ TK_HD int tk_zstd_next(tk_zstd_state& s, tk_zstd_tables& tb, uint8_t* out, uint3
         if (emit && s.lit_kind == TK_ZL_OUTPUT && s.lit_left && op + llen + mlen > s.lit_src) return TK_ZS_ERROR;
         return TK_ZS_COPY;
     }
+}
+
+// ---------------------------------------------------------------------------------------------
+// Sequences in batches.  The sequence chain of a block is serial (three FSE states), but nothing
+// else about a sequence is: tk_zstd_next_batch decodes up to TK_ZS_BATCH sequences in one tight
+// loop (state in registers, no dispatch, no event per call) and leaves their copies to the caller,
+// who can place them with a prefix sum and execute them side by side:
+//   * the literal runs of a batch never depend on one another (their sources are the input, a
+//     byte, or the block's parked literals, which stay ahead of every write position);
+//   * a match depends on earlier matches of the batch only when its source reaches into what
+//     they write, i.e. ends behind the first match destination of the batch (or overlaps its own
+//     destination); on text that is one sequence in twenty.  The others can be copied in any
+//     order once the literals are in place; the dependent ones follow in sequence order.
+// Returns the number of sequences decoded (>= 1), 0 when the decoder is not inside a sequence
+// section (the caller goes on with tk_zstd_next), or -status on a broken stream.  `op` is the
+// output position in front of the first sequence of the batch.
+#define TK_ZS_BATCH 32
+struct tk_zstd_batch {
+    uint32_t lit_len[TK_ZS_BATCH], lit_src[TK_ZS_BATCH], mlen[TK_ZS_BATCH], offset[TK_ZS_BATCH];
+    uint32_t lit_kind;             // of every literal run of the batch (the block's)
+};
+
+// The batch's place inside the tables' scratch (dead while a block's sequences are decoded).
+TK_HD tk_zstd_batch* tk_zstd_batch_of(tk_zstd_tables& tb) {
+    static_assert(sizeof(tk_zstd_batch) <= sizeof(tb.norm) + sizeof(tb.desc), "the batch must fit the scratch");
+    return reinterpret_cast<tk_zstd_batch*>(tb.norm);
+}
+
+TK_HD int tk_zstd_next_batch(tk_zstd_state& s, const tk_zstd_tables& tb, uint32_t cap, uint32_t op, bool emit,
+                             tk_zstd_batch* b) {
+    if (s.mode != TK_ZM_SEQ || s.seq_left == 0) return 0;
+    const uint8_t* in = s.in;
+    const uint32_t lo = s.seq_lo, hi = s.block_end;
+    // the state of the chain, in registers for the duration of the batch
+    uint32_t st_ll = s.st_ll, st_ml = s.st_ml, st_of = s.st_of;
+    uint32_t rep0 = s.rep0, rep1 = s.rep1, rep2 = s.rep2;
+    uint32_t seq_left = s.seq_left, lit_left = s.lit_left, lit_src = s.lit_src;
+    const uint32_t lit_kind = s.lit_kind;
+    int32_t bitpos = s.bitpos;
+    tk_zs_win win = s.win;
+    b->lit_kind = lit_kind;
+    int n = 0;
+    for (; n < TK_ZS_BATCH && seq_left; ++n) {
+        const uint32_t e_of = reinterpret_cast<const uint32_t*>(tb.of)[st_of];
+        const uint32_t e_ml = reinterpret_cast<const uint32_t*>(tb.ml)[st_ml];
+        const uint32_t e_ll = reinterpret_cast<const uint32_t*>(tb.ll)[st_ll];
+        const uint32_t ofc = e_of & 0xFFu, mlc = e_ml & 0xFFu, llc = e_ll & 0xFFu;
+        if (ofc > 31u || mlc > 52u || llc > 35u) return -TK_ZS_ERROR;
+        const uint32_t mlb = tb.ml_bits[mlc], llb = tb.ll_bits[llc];
+        const bool more = seq_left > 1u;
+        const uint32_t nb_ll = (e_ll >> 8) & 0xFFu, nb_ml = (e_ml >> 8) & 0xFFu, nb_of = (e_of >> 8) & 0xFFu;
+        const uint32_t total = ofc + mlb + llb + (more ? nb_ll + nb_ml + nb_of : 0u);
+        uint32_t ov, mlen, llen;
+        if (total <= 56u) {
+            bitpos -= (int32_t)total;
+            uint64_t v = total ? tk_zs_win_get64(win, in, lo, hi, bitpos, (int)total) : 0ull;
+            if (more) {
+                st_of = (e_of >> 16) + ((uint32_t)v & ((1u << nb_of) - 1u)); v >>= nb_of;
+                st_ml = (e_ml >> 16) + ((uint32_t)v & ((1u << nb_ml) - 1u)); v >>= nb_ml;
+                st_ll = (e_ll >> 16) + ((uint32_t)v & ((1u << nb_ll) - 1u)); v >>= nb_ll;
+            }
+            llen = tb.ll_base[llc] + ((uint32_t)v & ((1u << llb) - 1u)); v >>= llb;
+            mlen = tb.ml_base[mlc] + ((uint32_t)v & ((1u << mlb) - 1u)); v >>= mlb;
+            ov = (1u << ofc) + ((uint32_t)v & ((1u << ofc) - 1u));
+        } else {
+            ov = (1u << ofc) + tk_zs_win_read(win, in, lo, hi, &bitpos, (int)ofc);
+            mlen = tb.ml_base[mlc] + tk_zs_win_read(win, in, lo, hi, &bitpos, (int)mlb);
+            llen = tb.ll_base[llc] + tk_zs_win_read(win, in, lo, hi, &bitpos, (int)llb);
+            if (bitpos < 0) return -TK_ZS_ERROR;
+            if (more) {
+                st_ll = (e_ll >> 16) + tk_zs_win_read(win, in, lo, hi, &bitpos, (int)nb_ll);
+                st_ml = (e_ml >> 16) + tk_zs_win_read(win, in, lo, hi, &bitpos, (int)nb_ml);
+                st_of = (e_of >> 16) + tk_zs_win_read(win, in, lo, hi, &bitpos, (int)nb_of);
+            }
+        }
+        if (bitpos < 0) return -TK_ZS_ERROR;
+        uint32_t offset;
+        if (ov > 3u) {
+            offset = ov - 3u;
+            rep2 = rep1; rep1 = rep0; rep0 = offset;
+        } else {
+            const uint32_t idx = ov - 1u + (llen == 0 ? 1u : 0u);
+            if (idx == 0) {
+                offset = rep0;
+            } else {
+                offset = idx == 1u ? rep1 : idx == 2u ? rep2 : rep0 - 1u;
+                if (idx > 1u) rep2 = rep1;
+                rep1 = rep0;
+                rep0 = offset;
+            }
+        }
+        --seq_left;
+        if (!more && bitpos != 0) return -TK_ZS_ERROR;               // the bit stream must end exactly
+        if (llen > lit_left || llen > cap - op || mlen > cap - op - llen) return -TK_ZS_ERROR;
+        if (offset == 0 || offset > op + llen) return -TK_ZS_ERROR;  // no dictionary: only this payload's output
+        b->lit_len[n] = llen; b->lit_src[n] = lit_src; b->mlen[n] = mlen; b->offset[n] = offset;
+        lit_left -= llen;
+        if (lit_kind != TK_ZL_RLE) lit_src += llen;
+        op += llen + mlen;
+        // parked literals not yet read must stay ahead of the write position
+        if (emit && lit_kind == TK_ZL_OUTPUT && lit_left && op > lit_src) return -TK_ZS_ERROR;
+    }
+    s.st_ll = st_ll; s.st_ml = st_ml; s.st_of = st_of;
+    s.rep0 = rep0; s.rep1 = rep1; s.rep2 = rep2;
+    s.seq_left = seq_left; s.lit_left = lit_left; s.lit_src = lit_src;
+    s.bitpos = bitpos;
+    s.win = win;
+    return n;
 }

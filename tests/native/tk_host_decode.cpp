@@ -307,3 +307,36 @@ extern "C" int tk_host_decode_nested_flat(const uint8_t* buf, uint32_t len, int 
     return -1;
 }
 
+
+// The fast lane of the JSON array kernels (tk_fastlane.cuh) on one element [pos, stop) of a padded
+// buffer.  Returns 1 and the value when the lane accepts the literal, 0 when it leaves it to the
+// scalar grammar.
+#include "../../torchkafka_b200/csrc/tk_fastlane.cuh"
+struct HostWords {
+    const uint8_t* p;
+    uint32_t word(uint32_t a, int k) const { uint32_t v; memcpy(&v, p + a + 4 * k, 4); return v; }
+};
+extern "C" int tk_host_fastlane(const uint8_t* buf, uint32_t pos, uint32_t stop, int kind, void* out) {
+    static tk_fl_tables tb;
+    static bool ready = false;
+    if (!ready) { tk_fl_tables_fill(tb, 0, 1); ready = true; }
+    HostWords src{buf};
+    uint64_t w;
+    uint32_t K, dot, neg;
+    if (!tk_fl_scan(src, pos, stop, tb, &w, &K, &dot, &neg)) return 0;
+    switch (kind) {
+        case TK_F32: return tk_fl_value<TK_F32>(w, K, dot, neg, tb, (float*)out) ? 1 : 0;
+        case TK_F64: return tk_fl_value<TK_F64>(w, K, dot, neg, tb, (double*)out) ? 1 : 0;
+        case TK_I32: return tk_fl_value<TK_I32>(w, K, dot, neg, tb, (int32_t*)out) ? 1 : 0;
+        case TK_I64: return tk_fl_value<TK_I64>(w, K, dot, neg, tb, (int64_t*)out) ? 1 : 0;
+    }
+    return -1;
+}
+
+// Many elements at once (the Python loop would dominate): n elements, element i = [pos[i], stop[i]).
+extern "C" void tk_host_fastlane_many(const uint8_t* buf, const uint32_t* pos, const uint32_t* stop, uint32_t n, int kind,
+                                      void* out, uint8_t* accepted) {
+    const size_t sz = (kind == TK_F32 || kind == TK_I32) ? 4 : 8;
+    for (uint32_t i = 0; i < n; ++i)
+        accepted[i] = (uint8_t)tk_host_fastlane(buf, pos[i], stop[i], kind, (uint8_t*)out + sz * i);
+}

@@ -225,7 +225,7 @@ static void free_slot(tk_slot& s) {
     cudaFree(s.d.bytes); cudaFree(s.d.recs); cudaFree(s.d.rec_len); cudaFree(s.d.rec_status);
     cudaFree(s.d.rec_kidx); cudaFree(s.d.tile_agg); cudaFree(s.d.tile_incl); cudaFree(s.d.tile_flag);
     cudaFree(s.d.plan_ctr); cudaFree(s.d.block);
-    cudaFree(s.d.rec_tok); cudaFree(s.d.tok_pos); cudaFree(s.d.tok_count);
+    cudaFree(s.d.rec_tok); cudaFree(s.d.rec_base); cudaFree(s.d.tok_pos); cudaFree(s.d.tok_count);
     cudaFree(s.d.fz_tile_first); cudaFree(s.d.fz_agg); cudaFree(s.d.fz_incl); cudaFree(s.d.fz_flag); cudaFree(s.d.fz_ctr);
     if (s.ev_h2d) cudaEventDestroy(s.ev_h2d);
     if (s.ev_free) cudaEventDestroy(s.ev_free);
@@ -294,6 +294,7 @@ static int create_impl(tk_ctx* ctx) {
         TK_CUDA(cudaMalloc(&s.d.plan_ctr, 2 * sizeof(uint32_t)));
         TK_CUDA(cudaMemset(s.d.plan_ctr, 0, 2 * sizeof(uint32_t)));
         TK_CUDA(cudaMalloc(&s.d.rec_tok, sizeof(uint32_t) * (nrec + 1)));
+        TK_CUDA(cudaMalloc(&s.d.rec_base, sizeof(long long) * (nrec + 1)));
         // token arrays of the JSON path are allocated on first use (tk_ensure_token_arrays)
         TK_CUDA(cudaMalloc(&s.d.block, ctx->block_bytes));
         s.d.result = reinterpret_cast<tk_result_t*>(s.d.block);

@@ -68,6 +68,9 @@ struct tk_slot_dev {
     uint32_t*    tile_flag;
     uint32_t*    plan_ctr;
     uint32_t*    rec_tok;      // [slot_records] index of each record's first element in the token array
+    long long*   rec_base;     // [slot_records] flat JSON decode: (output row of the record) * max_len - rec_tok,
+                               // so that element t of the token array goes to values[rec_base + t];
+                               // TK_REC_BASE_SKIP for a record without a row (written by k_plan)
     uint32_t*    tok_pos;      // [tok_cap] token array of the flat decode path: uint2 {byte position, record}
     uint32_t*    tok_count;    // [2] elements emitted so far (token array allocation cursor): two
                                // counters used alternately, each scan zeroes the one of the next
@@ -119,6 +122,8 @@ struct tk_slot {
     cudaEvent_t  ev_dec0, ev_dec1;   // timing events around the decode / collate kernels (tk_ctx_set_timing)
     bool         dec_timed;
     uint32_t     tok_use;     // tk_json_scan calls on this slot: selects the token counter
+    uint32_t     json_row_elems;   // max_len of the slot's last scan if that was tk_json_scan (k_plan then
+                                   // writes rec_base), 0 after any other scan
     uint32_t     plan_epoch;  // tk_compact calls on this slot: tags the tile status words
     uint32_t     fz_epoch;    // tk_json_ingest calls on this slot: tags the fused kernel's tile status words
     bool         free_recorded;
@@ -221,3 +226,4 @@ int tk_commit_final(tk_ctx* ctx, int slot, int wait_for_prior, void* stream);
 
 // bytes the kernels may over-read past n_bytes (aligned vector loads of the last tile)
 #define TK_BYTES_PAD 4096
+#define TK_REC_BASE_SKIP (-0x7FFFFFFFFFFFFFFFLL - 1)

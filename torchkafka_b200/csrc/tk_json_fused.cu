@@ -297,7 +297,7 @@ __device__ __forceinline__ void fz_scatter(uint32_t sbase, uint32_t n_seg, uint3
 // One round of segments, thread per element out of the window.  STAGE: the value goes to the
 // staging array (its row is not known yet); else straight to the record's row.
 template <int KIND, bool STAGE>
-__device__ __forceinline__ void fz_parse_round(const fused_args& a, const parse_tables& tb, const uint8_t* win,
+__device__ __forceinline__ void fz_parse_round(const fused_args& a, const tk_fl_tables& tb, const uint8_t* win,
                                                const uint32_t* tok, const uint8_t* rinfo, const uint16_t* fseg,
                                                const uint16_t* rlen, const uint16_t* rst, const uint32_t* rrow,
                                                typename tk_elem<KIND>::type* val, typename tk_elem<KIND>::type* values,
@@ -315,11 +315,12 @@ __device__ __forceinline__ void fz_parse_round(const fused_args& a, const parse_
         const uint32_t stop = (last ? end : (tok[s + 1] & 0xFFFFu)) - 1u;
         T v;
         int st = TK_OK;
-        uint64_t F;
-        uint32_t I, L2, neg;
-        // (the last element takes the fast lane only when the record's final byte is ']')
-        bool fast = !(last && !(info & FR_TAIL)) && fast_number<true>(win, pos, stop, tb.pow10, &I, &F, &L2, &neg);
-        if (fast) fast = fast_convert<KIND>(I, F, L2, neg, tb, &v);
+        uint64_t w;
+        uint32_t K, dot, neg;
+        // (the last element takes the fast lane only when the record's final byte is ']'; an element
+        // that ends in the window's first 20 bytes cannot be anchored at its end: scalar grammar)
+        bool fast = !(last && !(info & FR_TAIL)) && tk_fl_scan(SmemWords{win}, pos, stop, tb, &w, &K, &dot, &neg);
+        if (fast) fast = tk_fl_value<KIND>(w, K, dot, neg, tb, &v);
         if (!fast) {
             WindowReader rd{win, end};
             st = tk_json_element_flat<KIND>(rd, pos, &v);
@@ -338,7 +339,7 @@ template <int KIND>
 __global__ void __launch_bounds__(FZ_THREADS, 4) k_json_fused(const fused_args a) {
     typedef typename tk_elem<KIND>::type T;
     extern __shared__ __align__(128) uint8_t fz_smem[];
-    __shared__ parse_tables tb;
+    __shared__ tk_fl_tables tb;
     __shared__ __align__(8) uint64_t s_bar;
     __shared__ uint32_t s_warp_tot[32];
     __shared__ uint32_t s_total, s_kept, s_elems;
@@ -363,7 +364,8 @@ __global__ void __launch_bounds__(FZ_THREADS, 4) k_json_fused(const fused_args a
     uint8_t* rinfo = reinterpret_cast<uint8_t*>(rlen + a.max_recs);
 
     tk_pdl_launch_dependents();             // (the commit kernel behind this one waits for all of it)
-    parse_tables_init(tb);                  // constants only: overlaps the tail of the previous kernel
+    tk_fl_tables_fill(tb, threadIdx.x, blockDim.x);   // constants only: overlaps the tail of the previous kernel
+    __syncthreads();
     if (tid == 0) {
         mbar_init(&s_bar, 1);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");

@@ -223,6 +223,7 @@ static int json_scan_impl(tk_ctx* ctx, int slot, uint32_t max_len, uint32_t min_
     a.tok = s.d.tok_pos; a.tok_count = s.d.tok_count + (s.tok_use & 1u); a.tok_count_next = s.d.tok_count + ((s.tok_use + 1) & 1u);
     a.tok_cap = (uint32_t)(ctx->tok_cap > 0xFFFFFFFFull ? 0xFFFFFFFFull : ctx->tok_cap);
     a.ndim = ndim;
+    s.json_row_elems = max_len;                            // k_plan writes rec_base for rows of max_len elements
     a.reset = tk_plan_reset_args(ctx, slot);
     // one warp per record; 4-warp blocks: records differ in length, and a block holds its
     // slots until its longest record is done
@@ -250,6 +251,7 @@ struct flat_args {
     const int32_t*  rec_len;
     int32_t*        rec_status;
     const uint32_t* rec_tok;
+    const long long* rec_base;    // values index of token t of record r = rec_base[r] + t (tk_internal.h)
     tk_result_t*    res;
     const uint2*    tok;          // {byte position, record} per element
     const uint32_t* tok_count;
@@ -293,66 +295,84 @@ __device__ __forceinline__ void json_rows_part(const flat_args& a, uint32_t warp
     }
 }
 
-// Token entry written by k_json_scan: .x = byte position of the element, .y = record index with
-// TOK_LAST on the record's last element and TOK_TAIL when the record's final byte is ']'.
+// Elements the fast lane does not take: the scalar grammar.  Out of line: it is the rare case and
+// would otherwise sit inside the (unrolled) element loop.
+// (Arguments by value: a reference to the kernel's parameter block would force a copy of it into
+// local memory, and every parameter read of the element loop with it.)
 template <int KIND>
-__global__ void __launch_bounds__(256, 5) k_json_parse(const flat_args a) {
+__device__ __noinline__ int json_element_slow(const uint8_t* bytes, uint32_t end, uint32_t pos, uint32_t e, uint32_t flags,
+                                              const tk_nested_shape shape, typename tk_elem<KIND>::type* v) {
+    GlobalReader rd{bytes, end};
+    if (shape.ndim <= 1) return tk_json_element_flat<KIND>(rd, pos, v);
+    // nested arrays: the brackets around leaf e follow from e and the shape
+    const uint32_t n_open = e ? tk_nested_opens(shape, e) : 0u;                  // (the head took the first leaf's)
+    const uint32_t n_close = flags ? shape.ndim : tk_nested_opens(shape, e + 1);
+    return tk_json_element_nested<KIND>(rd, pos, n_open, n_close, flags != 0, v);
+}
+
+// One element: token entry tk (.x = byte position, .y = record index with TOK_LAST on the record's
+// last element and TOK_TAIL when the record's final byte is ']'), next_pos = position of the
+// element behind it in the token array.
+template <int KIND>
+__device__ __forceinline__ void json_parse_one(const flat_args& a, const tk_fl_tables& tb, uint32_t t, uint2 tk,
+                                               uint32_t next_pos, typename tk_elem<KIND>::type* values) {
     typedef typename tk_elem<KIND>::type T;
-    __shared__ parse_tables tb;
-    parse_tables_init(tb);                  // constants only: overlaps the tail of the previous kernel
+    const uint32_t pos = tk.x, rec = tk.y & TOK_REC_MASK, flags = tk.y & ~TOK_REC_MASK;
+    const long long base = a.rec_base[rec];
+    // the element ends at the next ',' -- or, for the last one, at the ']' that closes the record
+    uint32_t stop = next_pos - 1u;
+    if (flags) stop = a.recs[rec + 1].start - 1u;
+    T v;
+    uint64_t w;
+    uint32_t K, dot, neg;
+    // nested arrays: leaves without brackets around them take the same fast lane as the elements of
+    // a flat array
+    bool fast = flags != TOK_LAST;
+    if (a.shape.ndim > 1) {
+        const uint32_t e = t - a.rec_tok[rec];
+        fast = fast && !((e ? tk_nested_opens(a.shape, e) : 0u) | (flags ? a.shape.ndim : tk_nested_opens(a.shape, e + 1)));
+    }
+    fast = fast && tk_fl_scan(LdgWords{a.bytes}, pos, stop, tb, &w, &K, &dot, &neg);
+    if (fast) fast = tk_fl_value<KIND>(w, K, dot, neg, tb, &v);
+    if (!fast) {
+        const uint32_t e = a.shape.ndim > 1 ? t - a.rec_tok[rec] : 0u;
+        const int st = json_element_slow<KIND>(a.bytes, a.recs[rec + 1].start, pos, e, flags, a.shape, &v);
+        if (st) { flag_record(a.rec_status, a.res, rec, st); return; }
+    }
+    // (a record with a row has at most max_len elements: longer ones were rejected by the scan)
+    if (base != TK_REC_BASE_SKIP) values[base + (long long)t] = v;
+}
+
+// 6 blocks per SM (40 registers): measured best of 4 / 5 / 6 (profiles/r02_parse_variants.md)
+template <int KIND>
+__global__ void __launch_bounds__(256, 6) k_json_parse(const flat_args a) {
+    typedef typename tk_elem<KIND>::type T;
+    __shared__ tk_fl_tables tb;
+    tk_fl_tables_fill(tb, threadIdx.x, blockDim.x);   // constants only: overlaps the tail of the previous kernel
+    __syncthreads();
     tk_pdl_wait();
     tk_pdl_launch_dependents();             // after the wait: see k_commit_final (tk_plan.cu)
     json_rows_part<sizeof(T)>(a, (blockIdx.x * blockDim.x + threadIdx.x) >> 5, (gridDim.x * blockDim.x) >> 5,
                               threadIdx.x & 31);
     const uint32_t n_tok = min(*a.tok_count, a.tok_cap);
-    const uint32_t B = a.res->batch_size;
     T* values = reinterpret_cast<T*>(a.values.base);
     // Persistent grid, software-pipelined two elements deep: the token entry of iteration i + 2
     // is requested and the text of element i + 1 is prefetched into L1 while element i is parsed,
     // so neither of the two dependent DRAM round trips (entry -> text) is waited for.
     const uint32_t stride = gridDim.x * blockDim.x;
     uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
-    uint2 tk = make_uint2(0, 0), tk1 = make_uint2(0, 0);
-    uint32_t next_pos = 0, next_pos1 = 0;
-    if (t < n_tok) { tk = __ldg(a.tok + t); next_pos = __ldg(&a.tok[t + 1].x); }   // one spare entry behind the array
-    if (t + stride < n_tok) { tk1 = __ldg(a.tok + t + stride); next_pos1 = __ldg(&a.tok[t + stride + 1].x); }
-    uint2 tk2 = make_uint2(0, 0);
-    uint32_t next_pos2 = 0;
-    for (; t < n_tok; t += stride, tk = tk1, next_pos = next_pos1, tk1 = tk2, next_pos1 = next_pos2) {
-        {
-            const uint32_t t2 = t + 2 * stride;
-            const uint8_t* ahead = a.bytes + tk1.x;
-            asm volatile("prefetch.global.L1 [%0];" ::"l"(ahead));
-            asm volatile("prefetch.global.L1 [%0];" ::"l"(ahead + 27));
-            if (t2 < n_tok) { tk2 = __ldg(a.tok + t2); next_pos2 = __ldg(&a.tok[t2 + 1].x); }
-        }
-        const uint32_t pos = tk.x, rec = tk.y & TOK_REC_MASK, flags = tk.y & ~TOK_REC_MASK;
-        const uint32_t end = a.recs[rec + 1].start;
-        const int32_t kidx = a.rec_kidx[rec];
-        const uint32_t e = t - a.rec_tok[rec];                   // element index inside the record
-        // the element ends at the next ',' -- or, for the last one, at the ']' that closes the record
-        const uint32_t stop = (flags ? end : next_pos) - 1u;
-        T v;
-        int st = TK_OK;
-        uint64_t F;
-        uint32_t I, L2, neg;
-        // nested arrays: the brackets around leaf e follow from e and the shape; leaves without any
-        // take the same fast lane as the elements of a flat array
-        uint32_t n_open = 0, n_close = 0;
-        if (a.shape.ndim > 1) {
-            n_open = e ? tk_nested_opens(a.shape, e) : 0u;               // (the head took the first leaf's)
-            n_close = flags ? a.shape.ndim : tk_nested_opens(a.shape, e + 1);
-        }
-        bool fast = flags != TOK_LAST && !(n_open | n_close) &&
-                    fast_number(a.bytes, pos, stop, tb.pow10, &I, &F, &L2, &neg);
-        if (fast) fast = fast_convert<KIND>(I, F, L2, neg, tb, &v);
-        if (!fast) {
-            GlobalReader rd{a.bytes, end};
-            st = a.shape.ndim > 1 ? tk_json_element_nested<KIND>(rd, pos, n_open, n_close, flags != 0, &v)
-                                  : tk_json_element_flat<KIND>(rd, pos, &v);
-        }
-        if (st) { flag_record(a.rec_status, a.res, rec, st); continue; }
-        if (kidx >= 0 && e < a.max_len) values[(uint64_t)(B + (uint32_t)kidx) * a.max_len + e] = v;
+    uint2 tk = make_uint2(0, 0), tk1 = make_uint2(0, 0), tk2 = make_uint2(0, 0);
+    uint32_t np = 0, np1 = 0, np2 = 0;
+    if (t < n_tok) { tk = __ldg(a.tok + t); np = __ldg(&a.tok[t + 1].x); }   // one spare entry behind the array
+    if (t + stride < n_tok) { tk1 = __ldg(a.tok + t + stride); np1 = __ldg(&a.tok[t + stride + 1].x); }
+#pragma unroll 1
+    for (; t < n_tok; t += stride, tk = tk1, np = np1, tk1 = tk2, np1 = np2) {
+        const uint32_t t2 = t + 2 * stride;
+        const uint8_t* ahead = a.bytes + tk1.x;
+        asm volatile("prefetch.global.L1 [%0];" ::"l"(ahead));
+        asm volatile("prefetch.global.L1 [%0];" ::"l"(ahead + 27));
+        if (t2 < n_tok) { tk2 = __ldg(a.tok + t2); np2 = __ldg(&a.tok[t2 + 1].x); }
+        json_parse_one<KIND>(a, tb, t, tk, np, values);
     }
 }
 
@@ -407,7 +427,10 @@ static int json_decode_impl(tk_ctx* ctx, int slot, int dtype, uint32_t max_len, 
     flat_args a;
     a.bytes = s.d.bytes; a.recs = s.d.recs; a.n = n; a.max_len = max_len; a.fixed_len = fixed_len;
     a.rec_kidx = s.d.rec_kidx; a.rec_len = s.d.rec_len; a.rec_status = s.d.rec_status;
-    a.rec_tok = s.d.rec_tok; a.res = s.d.result;
+    a.rec_tok = s.d.rec_tok; a.rec_base = s.d.rec_base; a.res = s.d.result;
+    TK_REQUIRE(s.json_row_elems == max_len,
+               "tk_json_scan + tk_compact must run before tk_json_decode, with the same max_len (scan %u, decode %u)",
+               s.json_row_elems, max_len);
     a.tok = reinterpret_cast<const uint2*>(s.d.tok_pos); a.tok_count = s.d.tok_count + (s.tok_use & 1u);
     a.tok_cap = (uint32_t)(ctx->tok_cap > 0xFFFFFFFFull ? 0xFFFFFFFFull : ctx->tok_cap);
     a.shape.ndim = ndim;

@@ -79,6 +79,10 @@ struct plan_args {
     unsigned long long* tile_incl;
     uint32_t*       tile_flag;
     uint32_t*       ctr;          // [0] tile ticket, [1] finished tiles
+    // flat JSON slots (row_elems != 0): where the record's elements go (tk_internal.h: rec_base)
+    const uint32_t* rec_tok;
+    long long*      rec_base;
+    uint32_t        row_elems;
 };
 
 __device__ __forceinline__ uint32_t ld_acquire_u32(const uint32_t* p) {
@@ -168,8 +172,11 @@ __global__ void __launch_bounds__(CMP_THREADS) k_plan(const plan_args a) {
                 a.rec_kidx[i] = (int32_t)ex;
                 len = lens[k];
                 if ((carry + ex + 1) % B == 0) a.batch_end[j] = i;
+                // (the first B rows of the output planes hold the batch left open by the previous slot)
+                if (a.row_elems) a.rec_base[i] = (long long)((unsigned long long)(B + ex) * a.row_elems) - (long long)a.rec_tok[i];
             } else {
                 a.rec_kidx[i] = -1 - (int32_t)ex;
+                if (a.row_elems) a.rec_base[i] = TK_REC_BASE_SKIP;
             }
         }
         // longest kept record of the batch: one atomic per warp when the warp lies inside one batch
@@ -249,6 +256,7 @@ extern "C" int tk_compact(tk_ctx* ctx, int slot, uint32_t batch_size, void* stre
     a.state = ctx->d_state; a.res = s.d.result; a.batch_end = s.d.batch_end; a.batch_lmax = s.d.batch_lmax;
     a.commit = s.d.commit; a.positions = ctx->d_positions;
     a.tile_agg = s.d.tile_agg; a.tile_incl = s.d.tile_incl; a.tile_flag = s.d.tile_flag; a.ctr = s.d.plan_ctr;
+    a.rec_tok = s.d.rec_tok; a.rec_base = s.d.rec_base; a.row_elems = s.json_row_elems;
     TK_LAUNCH_PDL(k_plan, a.n_tiles, CMP_THREADS, st, a);
     return 0;
 }

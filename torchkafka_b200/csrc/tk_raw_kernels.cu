@@ -43,6 +43,7 @@ extern "C" int tk_raw_scan(tk_ctx* ctx, int slot, uint64_t record_bytes, void* s
     TK_ENTER(ctx, slot);
     tk_slot& s = ctx->slots[slot];
     const uint32_t n = s.n_records;                        // (an empty slot still resets the plan outputs)
+    s.json_row_elems = 0;
     TK_LAUNCH_PDL(k_raw_scan, max((n + 255) / 256, 1u), 256, (cudaStream_t)stream, s.d.recs, n, record_bytes, s.d.rec_len,
                   s.d.rec_status, s.d.rec_kidx, tk_plan_reset_args(ctx, slot));
     return 0;

@@ -154,6 +154,39 @@ extern "C" int tk_host_inflate(const uint8_t* in, uint32_t len, uint8_t* out, ui
     return 0;
 }
 
+// The same with the matches collected in batches (tk_inflate_next with a batch) and copied in the
+// least favourable order the device may use: the matches that read nothing an earlier match of the
+// batch writes first, last one first, then the others in order.
+extern "C" int tk_host_inflate_batched(const uint8_t* in, uint32_t len, uint8_t* out, uint32_t cap, uint32_t* out_len,
+                                       uint32_t* consumed) {
+    tk_inflate_state s;
+    static tk_inflate_tables tb;
+    tk_inflate_init(s, in, 0, len);
+    tb.batch.n = 0;
+    uint32_t op = 0, mlen = 0, mdist = 0;
+    for (;;) {
+        const int ev = tk_inflate_next(s, tb, out, cap, op, &mlen, &mdist, 0, &tb.batch);
+        if (ev == TK_INF_ERROR) return 1;
+        const tk_inflate_batch& b = tb.batch;
+        bool dep[TK_INF_BATCH_MAX];
+        for (uint32_t k = 0; k < b.n; ++k) dep[k] = b.dst[k] - b.dist[k] + b.len[k] > b.dst[0] || b.len[k] > 32u;
+        for (uint32_t k = b.n; k-- > 0;)
+            if (!dep[k]) {
+                uint8_t tmp[32];
+                memcpy(tmp, out + b.dst[k] - b.dist[k], b.len[k]);          // every load before the first store
+                memcpy(out + b.dst[k], tmp, b.len[k]);
+            }
+        for (uint32_t k = 0; k < b.n; ++k)
+            if (dep[k])
+                for (uint32_t j = 0; j < b.len[k]; ++j) out[b.dst[k] + j] = out[b.dst[k] - b.dist[k] + j];
+        tb.batch.n = 0;
+        if (ev == TK_INF_DONE) break;
+    }
+    *out_len = op;
+    *consumed = tk_inf_consumed(s);
+    return 0;
+}
+
 // Zstandard payload (tk_zstd.cuh) with the copies done serially.  emit = 0: size pass only.
 // Returns 0 ok, else the decoder's status; *out_len = bytes produced.
 extern "C" int tk_host_zstd(const uint8_t* in, uint32_t len, uint8_t* out, uint32_t cap, int emit, uint32_t* out_len) {

@@ -24,6 +24,17 @@ def inflate(lib, z: bytes, cap: int):
     out = np.zeros(max(cap, 1), np.uint8)
     n, used = ctypes.c_uint32(), ctypes.c_uint32()
     st = lib.tk_host_inflate(z, len(z), out.ctypes.data_as(ctypes.c_void_p), cap, ctypes.byref(n), ctypes.byref(used))
+    # the batched form (matches collected 32 at a time, copied in the device's least favourable
+    # order) must agree with the serial one: status, bytes, input consumed
+    out2 = np.zeros(max(cap, 1) + 64, np.uint8)
+    out2[max(cap, 1):] = 0xA5
+    n2, used2 = ctypes.c_uint32(), ctypes.c_uint32()
+    st2 = lib.tk_host_inflate_batched(z, len(z), out2.ctypes.data_as(ctypes.c_void_p), cap, ctypes.byref(n2),
+                                      ctypes.byref(used2))
+    assert (out2[max(cap, 1):] == 0xA5).all(), "batched decoder wrote past the output buffer"
+    assert st2 == st, (st, st2)
+    if st == 0:
+        assert n2.value == n.value and used2.value == used.value and bytes(out2[:n2.value]) == bytes(out[:n.value])
     return st, bytes(out[:n.value]), used.value
 
 

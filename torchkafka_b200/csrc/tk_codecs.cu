@@ -30,6 +30,7 @@
 // the fields of an element depend on one another, a cache round trip each would dominate);
 // literals and matches are copied by the whole warp, overlapping matches by repeating the source
 // with period `offset`; matches are read back from the unit's own output through L1.
+#include <type_traits>
 #include "tk_rb.h"
 #include "tk_inflate.cuh"
 #include "tk_zstd.cuh"
@@ -464,25 +465,57 @@ __device__ __forceinline__ uint32_t snappy_run(cz_window& w, uint32_t lane, uint
 // ---------------------------------------------------------------- DEFLATE (gzip)
 // Lane 0 owns the decoder state and runs tk_inflate_next up to the next match; its literals are
 // plain stores of lane 0 (ordered before the warp's reads by the __syncwarp in cz_match).
+// A run of at most 32 bytes whose source lies below everything the batch writes: all loads of a
+// chunk are issued before its stores (the output is read back through L2: one round trip per
+// chunk, not per byte).
+__device__ __forceinline__ void cz_copy_small(uint8_t* out, uint32_t dst, uint32_t src, uint32_t len) {
+    for (uint32_t k0 = 0; k0 < len; k0 += 8) {
+        uint8_t v[8];
+#pragma unroll
+        for (int j = 0; j < 8; ++j) v[j] = k0 + j < len ? out[src + k0 + j] : (uint8_t)0;
+#pragma unroll
+        for (int j = 0; j < 8; ++j) if (k0 + j < len) out[dst + k0 + j] = v[j];
+    }
+}
+
+// The matches of a batch (tk_inflate_next), lane per match; the dependent ones by the whole warp in order.
+__device__ __forceinline__ void inflate_exec_batch(const tk_inflate_batch& b, uint8_t* out, uint32_t lane) {
+    const uint32_t n = b.n;
+    if (!n) return;
+    uint32_t dst = 0, len = 0, dist = 1;
+    if (lane < n) { dst = b.dst[lane]; len = b.len[lane]; dist = b.dist[lane]; }
+    const uint32_t first_dst = b.dst[0], src = dst - dist;
+    // (a match that overlaps its own destination has its source end behind its destination too)
+    const bool dep = len && (src + len > first_dst || len > 32u);
+    if (len && !dep) cz_copy_small(out, dst, src, len);
+    uint32_t deps = __ballot_sync(0xffffffffu, dep);
+    while (deps) {
+        const int L = __ffs((int)deps) - 1;
+        deps &= deps - 1u;
+        cz_match(out, __shfl_sync(0xffffffffu, dst, L), __shfl_sync(0xffffffffu, dist, L), __shfl_sync(0xffffffffu, len, L), lane);
+    }
+    __syncwarp();
+}
+
+// Lane 0 walks the stream: literals go straight to their place, matches are collected in batches
+// of 32 and copied by the warp.
 __device__ __forceinline__ uint32_t inflate_run(const uint8_t* raw, uint32_t lane, uint32_t p, uint32_t end, uint8_t* out,
                                                 uint32_t cap, uint32_t& op, tk_inflate_tables& tb) {
     tk_inflate_state s;
     tk_inflate_init(s, raw, p, end);
+    if (lane == 0) tb.batch.n = 0;
     for (;;) {
         uint32_t ev = TK_INF_DONE, mlen = 0, mdist = 0;
-        // short matches (most of them, in text) are copied by the decoding lane itself, inside
-        // tk_inflate_next: no broadcast, no barriers; byte by byte also covers overlapping ones
-        if (lane == 0) ev = (uint32_t)tk_inflate_next(s, tb, out, cap, op, &mlen, &mdist, CZ_SMALL_COPY);
-        __syncwarp();
+        if (lane == 0) ev = (uint32_t)tk_inflate_next(s, tb, out, cap, op, &mlen, &mdist, 0, &tb.batch);
+        __syncwarp();                                       // the batch and lane 0's literals are written
         ev = __shfl_sync(0xffffffffu, ev, 0);
         if (ev == TK_INF_ERROR) return TK_STATUS_CORRUPT;
-        op = __shfl_sync(0xffffffffu, op, 0);
+        inflate_exec_batch(tb.batch, out, lane);
+        if (lane == 0) tb.batch.n = 0;
+        __syncwarp();
         if (ev == TK_INF_DONE) break;
-        mlen = __shfl_sync(0xffffffffu, mlen, 0);
-        mdist = __shfl_sync(0xffffffffu, mdist, 0);
-        cz_match(out, op, mdist, mlen, lane);
-        op += mlen;
     }
+    op = __shfl_sync(0xffffffffu, op, 0);
     // the stream must end where the trailer begins (a second member behind it is not followed)
     const uint32_t used = __shfl_sync(0xffffffffu, tk_inf_consumed(s), 0);
     return used == end ? TK_STATUS_OK : TK_STATUS_CORRUPT;
@@ -575,11 +608,6 @@ __global__ void __launch_bounds__(128) k_unit_decode(const rb_args a) {
 }
 
 // ---------------------------------------------------------------- serial formats: gzip, zstd
-union unit_tables {
-    tk_inflate_tables inflate;
-    tk_zstd_tables    zstd;
-};
-
 // Lane 0 owns the decoder state and produces copy events; the warp executes them.  Literals that
 // lane 0 decoded itself (Huffman) are parked at the end of the unit's output and move down from
 // there: the destination is below the source, so chunks of 32 bytes go load, barrier, store.
@@ -646,7 +674,7 @@ __device__ __forceinline__ void zstd_exec_batch(const tk_zstd_batch& b, uint32_t
     const uint32_t has = __ballot_sync(0xffffffffu, ml > 0u);
     const uint32_t first_dst = __shfl_sync(0xffffffffu, mdst, has ? __ffs((int)has) - 1 : 0);
     const bool dep = ml && (mdst - off + ml > first_dst || off < ml || ml > 32u);
-    if (ml && !dep) { for (uint32_t k = 0; k < ml; ++k) out[mdst + k] = out[mdst - off + k]; }
+    if (ml && !dep) cz_copy_small(out, mdst, mdst - off, ml);
     uint32_t deps = __ballot_sync(0xffffffffu, dep);
     while (deps) {
         const int L = __ffs((int)deps) - 1;
@@ -717,15 +745,17 @@ __device__ __forceinline__ uint32_t zstd_run(const uint8_t* raw, uint32_t lane, 
 }
 
 // Size pass of zstd units without a content size: lane 0 walks the sequences, nothing is written.
-__global__ void __launch_bounds__(128) k_unit_size_zstd(const rb_args a) {
-    __shared__ unit_tables tables[4];
+#define SERIAL_WARPS 2       // units per block of the serial decoders: small blocks, so that the shared
+                             // memory of an SM divides into as many tables as possible
+__global__ void __launch_bounds__(32 * SERIAL_WARPS) k_unit_size_zstd(const rb_args a) {
+    __shared__ tk_zstd_tables tables[SERIAL_WARPS];
     const uint32_t lane = threadIdx.x & 31;
     const uint32_t warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, nwarps = (gridDim.x * blockDim.x) >> 5;
     for (uint32_t i = warp; i < a.n_units; i += nwarps) {
         const tk_rb_unit u = a.units[i];
         if ((u.kind & 0xFFu) != RB_UNIT_ZSTD || (u.kind & (RB_UNIT_SIZED | RB_UNIT_BOUND))) continue;
         if (lane == 0) {
-            tk_zstd_tables& tb = tables[threadIdx.x >> 5].zstd;
+            tk_zstd_tables& tb = tables[threadIdx.x >> 5];
             tk_zstd_state s;
             tk_zstd_init(s, tb, a.raw, u.src, u.src + u.src_len);
             tk_zstd_event ev;
@@ -739,22 +769,25 @@ __global__ void __launch_bounds__(128) k_unit_size_zstd(const rb_args a) {
     }
 }
 
-__global__ void __launch_bounds__(128) k_unit_decode_serial(const rb_args a) {
-    __shared__ unit_tables tables[4];
-    __shared__ tk_zstd_event events[4];
+// One kernel per format: a DEFLATE unit needs 3.9 KB of tables, a zstd unit 10.8 KB, and the number of
+// units an SM works on at a time is what its shared memory divides into.
+template <bool ZSTD>
+__global__ void __launch_bounds__(32 * SERIAL_WARPS) k_unit_decode_serial(const rb_args a) {
+    __shared__ typename std::conditional<ZSTD, tk_zstd_tables, tk_inflate_tables>::type tables[SERIAL_WARPS];
+    __shared__ tk_zstd_event events[ZSTD ? SERIAL_WARPS : 1];
     const uint32_t lane = threadIdx.x & 31;
     const uint32_t warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, nwarps = (gridDim.x * blockDim.x) >> 5;
     for (uint32_t i = warp; i < a.n_units; i += nwarps) {
         const tk_rb_unit u = a.units[i];
         const uint32_t kind = u.kind & 0xFFu;
-        if (kind < RB_UNIT_DEFLATE || a.batches[u.batch].status) continue;
+        if (kind != (ZSTD ? RB_UNIT_ZSTD : RB_UNIT_DEFLATE) || a.batches[u.batch].status) continue;
         uint8_t* out = a.raw2 + u.out;
         uint32_t op = 0, st;
-        if (kind == RB_UNIT_DEFLATE)
-            st = inflate_run(a.raw, lane, u.src, u.src + u.src_len, out, u.unc_len, op, tables[threadIdx.x >> 5].inflate);
-        else
-            st = zstd_run(a.raw, lane, u.src, u.src + u.src_len, out, u.unc_len, op, tables[threadIdx.x >> 5].zstd,
+        if constexpr (ZSTD)
+            st = zstd_run(a.raw, lane, u.src, u.src + u.src_len, out, u.unc_len, op, tables[threadIdx.x >> 5],
                           events[threadIdx.x >> 5]);
+        else
+            st = inflate_run(a.raw, lane, u.src, u.src + u.src_len, out, u.unc_len, op, tables[threadIdx.x >> 5]);
         if (u.kind & RB_UNIT_BOUND) {                       // placed by its upper bound: the records end here
             if (!st && lane == 0) a.batches[u.batch].rec_end = a.batches[u.batch].rec_start + op;
         } else if (!st && op != u.unc_len) {
@@ -765,21 +798,44 @@ __global__ void __launch_bounds__(128) k_unit_decode_serial(const rb_args a) {
     }
 }
 
+// resident blocks of a kernel on this device (asked once per kernel)
+template <class K>
+static uint32_t serial_grid(K kernel, uint32_t* cache) {
+    if (!*cache) {
+        int per_sm = 0, sms = 0, dev = 0;
+        if (cudaGetDevice(&dev) != cudaSuccess ||
+            cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess ||
+            cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kernel, 32 * SERIAL_WARPS, 0) != cudaSuccess || per_sm < 1) {
+            (void)cudaGetLastError();
+            per_sm = 8; sms = 148;
+        }
+        *cache = (uint32_t)(per_sm * sms);
+    }
+    return *cache;
+}
+
 int tk_codec_launch(const rb_args& a, const tk_rb_unit* h_units, cudaStream_t stream) {
     // which kernels this slot needs
-    uint32_t lz_unsized = 0, zs_unsized = 0, warp_units = 0, serial_units = 0;
+    uint32_t lz_unsized = 0, zs_unsized = 0, warp_units = 0, deflate_units = 0, zstd_units = 0;
     for (uint32_t i = 0; i < a.n_units; ++i) {
         const uint32_t kind = h_units[i].kind & 0xFFu;
         const bool sized = h_units[i].kind & (RB_UNIT_SIZED | RB_UNIT_BOUND);
-        if (kind >= RB_UNIT_DEFLATE) { ++serial_units; if (kind == RB_UNIT_ZSTD && !sized) ++zs_unsized; }
+        if (kind == RB_UNIT_ZSTD) { ++zstd_units; if (!sized) ++zs_unsized; }
+        else if (kind >= RB_UNIT_DEFLATE) ++deflate_units;
         else { ++warp_units; if (!sized) ++lz_unsized; }
     }
     if (lz_unsized) k_unit_size<<<min((a.n_units + 7) / 8, 148u * 8u), 256, 0, stream>>>(a);
-    if (zs_unsized) k_unit_size_zstd<<<min((a.n_units + 3) / 4, 148u * 5u), 128, 0, stream>>>(a);
+    static uint32_t g_size = 0, g_inflate = 0, g_zstd = 0;
+    const uint32_t blocks_wanted = (a.n_units + SERIAL_WARPS - 1) / SERIAL_WARPS;
+    if (zs_unsized)
+        k_unit_size_zstd<<<min(blocks_wanted, serial_grid(k_unit_size_zstd, &g_size)), 32 * SERIAL_WARPS, 0, stream>>>(a);
     // (also sets the empty record ranges of compressed batches without a single block)
     k_unit_place<<<1, 1024, 0, stream>>>(a);
     if (warp_units) k_unit_decode<<<min((a.n_units + 3) / 4, 148u * 16u), 128, 0, stream>>>(a);
-    if (serial_units) k_unit_decode_serial<<<min((a.n_units + 3) / 4, 148u * 5u), 128, 0, stream>>>(a);
+    if (deflate_units)
+        k_unit_decode_serial<false><<<min(blocks_wanted, serial_grid(k_unit_decode_serial<false>, &g_inflate)), 32 * SERIAL_WARPS, 0, stream>>>(a);
+    if (zstd_units)
+        k_unit_decode_serial<true><<<min(blocks_wanted, serial_grid(k_unit_decode_serial<true>, &g_zstd)), 32 * SERIAL_WARPS, 0, stream>>>(a);
     TK_LAUNCH_CHECK();
     return 0;
 }

@@ -15,16 +15,27 @@
 #include <string.h>
 #include "tk_number.cuh"      // TK_HD
 
-enum { TK_INF_MATCH = 0, TK_INF_DONE = 1, TK_INF_ERROR = 2 };
+enum { TK_INF_MATCH = 0, TK_INF_DONE = 1, TK_INF_ERROR = 2, TK_INF_BATCH = 3 };
 enum { TK_INF_HEADER = 0, TK_INF_CODES = 1, TK_INF_END = 2 };
 
 #define TK_INF_LIT_FAST 10
 #define TK_INF_DIST_FAST 8
+// Matches whose copy is left to the caller (tk_inflate_next with a batch): destination, length and
+// distance of each; the literals around them are already in place.  The copies may run side by side
+// except where a match reads what an earlier match of the batch writes (source end behind the first
+// destination of the batch): those follow in order.
+#define TK_INF_BATCH_MAX 32
+struct tk_inflate_batch {
+    uint32_t dst[TK_INF_BATCH_MAX], len[TK_INF_BATCH_MAX], dist[TK_INF_BATCH_MAX];
+    uint32_t n;
+};
+
 struct tk_inflate_tables {
     uint16_t lit_count[16], lit_symbol[288];
     uint16_t dist_count[16], dist_symbol[32];
     uint16_t lengths[320];         // scratch: code lengths of a dynamic block
     uint16_t lit_fast[1 << TK_INF_LIT_FAST], dist_fast[1 << TK_INF_DIST_FAST];   // 0: longer code
+    tk_inflate_batch batch;
 };
 
 struct tk_inflate_state {
@@ -195,8 +206,11 @@ TK_HD bool tk_inf_dynamic_tables(tk_inflate_state& s, tk_inflate_tables& tb) {
 // `self_copy` bytes are copied here, byte by byte; returns at the next longer match with *mlen /
 // *mdist set (the caller copies out[op - dist ..] and advances op by mlen; both are checked
 // against op and cap here), at the end of the stream, or on an error.
+// With `batch`: no match is copied or returned; each is appended to the batch and op moves past it.
+// Returns TK_INF_BATCH when the batch is full; at the end of the stream (or on an error) the batch
+// may hold matches too.  The caller copies them and sets batch->n = 0.
 TK_HD int tk_inflate_next(tk_inflate_state& s, tk_inflate_tables& tb, uint8_t* out, uint32_t cap, uint32_t& op,
-                          uint32_t* mlen, uint32_t* mdist, uint32_t self_copy = 0) {
+                          uint32_t* mlen, uint32_t* mdist, uint32_t self_copy = 0, tk_inflate_batch* batch = nullptr) {
     for (;;) {
         if (s.mode == TK_INF_HEADER) {
             if (s.last) {
@@ -255,6 +269,14 @@ TK_HD int tk_inflate_next(tk_inflate_state& s, tk_inflate_tables& tb, uint8_t* o
             }
             if (s.pos > s.end && tk_inf_consumed(s) > s.end) return TK_INF_ERROR;
             if (dist > op || len > cap - op) return TK_INF_ERROR;
+            if (batch) {
+                const uint32_t k = batch->n;
+                batch->dst[k] = op; batch->len[k] = len; batch->dist[k] = dist;
+                batch->n = k + 1u;
+                op += len;
+                if (k + 1u == TK_INF_BATCH_MAX) return TK_INF_BATCH;
+                continue;
+            }
             if (len <= self_copy) {
                 const uint8_t* src = out + op - dist;
                 for (uint32_t k = 0; k < len; ++k) out[op + k] = src[k];

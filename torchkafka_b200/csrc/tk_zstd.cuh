@@ -36,6 +36,34 @@ struct tk_fse_entry {
     uint16_t base;
 };
 
+// code -> baseline << 5 | extra bits of literal lengths (36 codes) and match lengths (53 codes): RFC 8878
+// 3.1.1.3.2.1.1.  Constants: read by the one lane that walks a sequence section (constant bank on
+// the device).
+#define TK_ZS_LL_CODES { 0x0u, 0x20u, 0x40u, 0x60u, 0x80u, 0xA0u, 0xC0u, 0xE0u, 0x100u, 0x120u, 0x140u, 0x160u, 0x180u, 0x1A0u, 0x1C0u, 0x1E0u, 0x201u, 0x241u, 0x281u, 0x2C1u, 0x302u, 0x382u, 0x403u, 0x503u, 0x604u, 0x806u, 0x1007u, 0x2008u, 0x4009u, 0x800Au, 0x1000Bu, 0x2000Cu, 0x4000Du, 0x8000Eu, 0x10000Fu, 0x200010u }
+#define TK_ZS_ML_CODES { 0x60u, 0x80u, 0xA0u, 0xC0u, 0xE0u, 0x100u, 0x120u, 0x140u, 0x160u, 0x180u, 0x1A0u, 0x1C0u, 0x1E0u, 0x200u, 0x220u, 0x240u, 0x260u, 0x280u, 0x2A0u, 0x2C0u, 0x2E0u, 0x300u, 0x320u, 0x340u, 0x360u, 0x380u, 0x3A0u, 0x3C0u, 0x3E0u, 0x400u, 0x420u, 0x440u, 0x461u, 0x4A1u, 0x4E1u, 0x521u, 0x562u, 0x5E2u, 0x663u, 0x763u, 0x864u, 0xA64u, 0xC65u, 0x1067u, 0x2068u, 0x4069u, 0x806Au, 0x1006Bu, 0x2006Cu, 0x4006Du, 0x8006Eu, 0x10006Fu, 0x200070u }
+#if defined(__CUDACC__)
+static __constant__ uint32_t tk_zs_ll_dev[36] = TK_ZS_LL_CODES;
+static __constant__ uint32_t tk_zs_ml_dev[53] = TK_ZS_ML_CODES;
+#endif
+#if !defined(__CUDA_ARCH__)
+static const uint32_t tk_zs_ll_host[36] = TK_ZS_LL_CODES;
+static const uint32_t tk_zs_ml_host[53] = TK_ZS_ML_CODES;
+#endif
+TK_HD uint32_t tk_zs_ll_code(uint32_t c) {
+#if defined(__CUDA_ARCH__)
+    return tk_zs_ll_dev[c];
+#else
+    return tk_zs_ll_host[c];
+#endif
+}
+TK_HD uint32_t tk_zs_ml_code(uint32_t c) {
+#if defined(__CUDA_ARCH__)
+    return tk_zs_ml_dev[c];
+#else
+    return tk_zs_ml_host[c];
+#endif
+}
+
 struct tk_zstd_tables {
     tk_fse_entry ll[512], ml[512], of[256], wt[64];   // sequences (accuracy <= 9, 9, 8), Huffman weights (<= 6)
     uint16_t huf[2048];            // literals: symbol | code length << 8, indexed by the next huf_log bits
@@ -43,8 +71,6 @@ struct tk_zstd_tables {
     // the batch of decoded sequences (tk_zstd_batch, tk_zstd_batch_of)
     int16_t  norm[256];            // normalised counts of a table description
     uint16_t desc[256];            // per-symbol state counter of the table build
-    uint32_t ll_base[36], ml_base[53];
-    uint8_t  ll_bits[36], ml_bits[53];
     uint8_t  weights[256];
 };
 
@@ -339,21 +365,6 @@ TK_HD void tk_zstd_init(tk_zstd_state& s, tk_zstd_tables& tb, const uint8_t* in,
     s.in = in; s.pos = pos; s.end = end; s.mode = TK_ZM_FRAME;
     s.last_block = 0; s.checksum = 0; s.seq_left = 0; s.lit_left = 0; s.huf_log = 0;
     s.ll_log = s.ml_log = s.of_log = -1;
-    // code -> (baseline, extra bits) of literal lengths and match lengths: the bases accumulate
-    const char* llb = "\1\1\1\1\2\2\3\3\4\6\7\10\11\12\13\14\15\16\17\20";                 // codes 16..35
-    const char* mlb = "\1\1\1\1\2\2\3\3\4\4\5\7\10\11\12\13\14\15\16\17\20";              // codes 32..52
-    uint32_t base = 16;
-    for (int c = 0; c < 36; ++c) {
-        if (c < 16) { tb.ll_base[c] = (uint32_t)c; tb.ll_bits[c] = 0; continue; }
-        tb.ll_base[c] = base; tb.ll_bits[c] = (uint8_t)llb[c - 16];
-        base += 1u << llb[c - 16];
-    }
-    base = 35;
-    for (int c = 0; c < 53; ++c) {
-        if (c < 32) { tb.ml_base[c] = (uint32_t)c + 3u; tb.ml_bits[c] = 0; continue; }
-        tb.ml_base[c] = base; tb.ml_bits[c] = (uint8_t)mlb[c - 32];
-        base += 1u << mlb[c - 32];
-    }
 }
 
 // One of the three sequence tables, as the block's compression mode says.
@@ -588,7 +599,7 @@ TK_HD int tk_zstd_next(tk_zstd_state& s, tk_zstd_tables& tb, uint8_t* out, uint3
         const uint32_t e_ll = reinterpret_cast<const uint32_t*>(tb.ll)[s.st_ll];
         const uint32_t ofc = e_of & 0xFFu, mlc = e_ml & 0xFFu, llc = e_ll & 0xFFu;
         if (ofc > 31u || mlc > 52u || llc > 35u) return TK_ZS_ERROR;
-        const uint32_t mlb = tb.ml_bits[mlc], llb = tb.ll_bits[llc];
+        const uint32_t mlp = tk_zs_ml_code(mlc), llp = tk_zs_ll_code(llc), mlb = mlp & 31u, llb = llp & 31u;
         const bool more = s.seq_left > 1u;                           // the states move on unless this is the last one
         const uint32_t nb_ll = (e_ll >> 8) & 0xFFu, nb_ml = (e_ml >> 8) & 0xFFu, nb_of = (e_of >> 8) & 0xFFu;
         const uint32_t total = ofc + mlb + llb + (more ? nb_ll + nb_ml + nb_of : 0u);
@@ -603,14 +614,14 @@ TK_HD int tk_zstd_next(tk_zstd_state& s, tk_zstd_tables& tb, uint8_t* out, uint3
                 s.st_ml = (e_ml >> 16) + ((uint32_t)v & ((1u << nb_ml) - 1u)); v >>= nb_ml;
                 s.st_ll = (e_ll >> 16) + ((uint32_t)v & ((1u << nb_ll) - 1u)); v >>= nb_ll;
             }
-            llen = tb.ll_base[llc] + ((uint32_t)v & ((1u << llb) - 1u)); v >>= llb;
-            mlen = tb.ml_base[mlc] + ((uint32_t)v & ((1u << mlb) - 1u)); v >>= mlb;
+            llen = (llp >> 5) + ((uint32_t)v & ((1u << llb) - 1u)); v >>= llb;
+            mlen = (mlp >> 5) + ((uint32_t)v & ((1u << mlb) - 1u)); v >>= mlb;
             ov = (1u << ofc) + ((uint32_t)v & ((1u << ofc) - 1u));
             if (s.bitpos < 0) return TK_ZS_ERROR;
         } else {
             ov = (1u << ofc) + tk_zs_win_read(s.win, in, lo, hi, &s.bitpos, (int)ofc);
-            mlen = tb.ml_base[mlc] + tk_zs_win_read(s.win, in, lo, hi, &s.bitpos, (int)mlb);
-            llen = tb.ll_base[llc] + tk_zs_win_read(s.win, in, lo, hi, &s.bitpos, (int)llb);
+            mlen = (mlp >> 5) + tk_zs_win_read(s.win, in, lo, hi, &s.bitpos, (int)mlb);
+            llen = (llp >> 5) + tk_zs_win_read(s.win, in, lo, hi, &s.bitpos, (int)llb);
             if (s.bitpos < 0) return TK_ZS_ERROR;
             if (more) {
                 s.st_ll = (e_ll >> 16) + tk_zs_win_read(s.win, in, lo, hi, &s.bitpos, (int)nb_ll);
@@ -694,7 +705,7 @@ TK_HD int tk_zstd_next_batch(tk_zstd_state& s, const tk_zstd_tables& tb, uint32_
         const uint32_t e_ll = reinterpret_cast<const uint32_t*>(tb.ll)[st_ll];
         const uint32_t ofc = e_of & 0xFFu, mlc = e_ml & 0xFFu, llc = e_ll & 0xFFu;
         if (ofc > 31u || mlc > 52u || llc > 35u) return -TK_ZS_ERROR;
-        const uint32_t mlb = tb.ml_bits[mlc], llb = tb.ll_bits[llc];
+        const uint32_t mlp = tk_zs_ml_code(mlc), llp = tk_zs_ll_code(llc), mlb = mlp & 31u, llb = llp & 31u;
         const bool more = seq_left > 1u;
         const uint32_t nb_ll = (e_ll >> 8) & 0xFFu, nb_ml = (e_ml >> 8) & 0xFFu, nb_of = (e_of >> 8) & 0xFFu;
         const uint32_t total = ofc + mlb + llb + (more ? nb_ll + nb_ml + nb_of : 0u);
@@ -707,13 +718,13 @@ TK_HD int tk_zstd_next_batch(tk_zstd_state& s, const tk_zstd_tables& tb, uint32_
                 st_ml = (e_ml >> 16) + ((uint32_t)v & ((1u << nb_ml) - 1u)); v >>= nb_ml;
                 st_ll = (e_ll >> 16) + ((uint32_t)v & ((1u << nb_ll) - 1u)); v >>= nb_ll;
             }
-            llen = tb.ll_base[llc] + ((uint32_t)v & ((1u << llb) - 1u)); v >>= llb;
-            mlen = tb.ml_base[mlc] + ((uint32_t)v & ((1u << mlb) - 1u)); v >>= mlb;
+            llen = (llp >> 5) + ((uint32_t)v & ((1u << llb) - 1u)); v >>= llb;
+            mlen = (mlp >> 5) + ((uint32_t)v & ((1u << mlb) - 1u)); v >>= mlb;
             ov = (1u << ofc) + ((uint32_t)v & ((1u << ofc) - 1u));
         } else {
             ov = (1u << ofc) + tk_zs_win_read(win, in, lo, hi, &bitpos, (int)ofc);
-            mlen = tb.ml_base[mlc] + tk_zs_win_read(win, in, lo, hi, &bitpos, (int)mlb);
-            llen = tb.ll_base[llc] + tk_zs_win_read(win, in, lo, hi, &bitpos, (int)llb);
+            mlen = (mlp >> 5) + tk_zs_win_read(win, in, lo, hi, &bitpos, (int)mlb);
+            llen = (llp >> 5) + tk_zs_win_read(win, in, lo, hi, &bitpos, (int)llb);
             if (bitpos < 0) return -TK_ZS_ERROR;
             if (more) {
                 st_ll = (e_ll >> 16) + tk_zs_win_read(win, in, lo, hi, &bitpos, (int)nb_ll);

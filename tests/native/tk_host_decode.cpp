@@ -162,24 +162,23 @@ extern "C" int tk_host_inflate_batched(const uint8_t* in, uint32_t len, uint8_t*
     tk_inflate_state s;
     static tk_inflate_tables tb;
     tk_inflate_init(s, in, 0, len);
-    tb.batch.n = 0;
     uint32_t op = 0, mlen = 0, mdist = 0;
     for (;;) {
         const int ev = tk_inflate_next(s, tb, out, cap, op, &mlen, &mdist, 0, &tb.batch);
         if (ev == TK_INF_ERROR) return 1;
-        const tk_inflate_batch& b = tb.batch;
+        const tk_inflate_match* b = tb.batch.m;
         bool dep[TK_INF_BATCH_MAX];
-        for (uint32_t k = 0; k < b.n; ++k) dep[k] = b.dst[k] - b.dist[k] + b.len[k] > b.dst[0] || b.len[k] > 32u;
-        for (uint32_t k = b.n; k-- > 0;)
+        for (uint32_t k = 0; k < s.nb; ++k) dep[k] = b[k].dst - b[k].dist + b[k].len > b[0].dst || b[k].len > 32u;
+        for (uint32_t k = s.nb; k-- > 0;)
             if (!dep[k]) {
                 uint8_t tmp[32];
-                memcpy(tmp, out + b.dst[k] - b.dist[k], b.len[k]);          // every load before the first store
-                memcpy(out + b.dst[k], tmp, b.len[k]);
+                memcpy(tmp, out + b[k].dst - b[k].dist, b[k].len);          // every load before the first store
+                memcpy(out + b[k].dst, tmp, b[k].len);
             }
-        for (uint32_t k = 0; k < b.n; ++k)
+        for (uint32_t k = 0; k < s.nb; ++k)
             if (dep[k])
-                for (uint32_t j = 0; j < b.len[k]; ++j) out[b.dst[k] + j] = out[b.dst[k] - b.dist[k] + j];
-        tb.batch.n = 0;
+                for (uint32_t j = 0; j < b[k].len; ++j) out[b[k].dst + j] = out[b[k].dst - b[k].dist + j];
+        s.nb = 0;
         if (ev == TK_INF_DONE) break;
     }
     *out_len = op;

@@ -479,12 +479,11 @@ __device__ __forceinline__ void cz_copy_small(uint8_t* out, uint32_t dst, uint32
 }
 
 // The matches of a batch (tk_inflate_next), lane per match; the dependent ones by the whole warp in order.
-__device__ __forceinline__ void inflate_exec_batch(const tk_inflate_batch& b, uint8_t* out, uint32_t lane) {
-    const uint32_t n = b.n;
+__device__ __forceinline__ void inflate_exec_batch(const tk_inflate_batch& b, uint32_t n, uint8_t* out, uint32_t lane) {
     if (!n) return;
     uint32_t dst = 0, len = 0, dist = 1;
-    if (lane < n) { dst = b.dst[lane]; len = b.len[lane]; dist = b.dist[lane]; }
-    const uint32_t first_dst = b.dst[0], src = dst - dist;
+    if (lane < n) { const tk_inflate_match e = b.m[lane]; dst = e.dst; len = e.len; dist = e.dist; }
+    const uint32_t first_dst = __shfl_sync(0xffffffffu, dst, 0), src = dst - dist;
     // (a match that overlaps its own destination has its source end behind its destination too)
     const bool dep = len && (src + len > first_dst || len > 32u);
     if (len && !dep) cz_copy_small(out, dst, src, len);
@@ -503,16 +502,14 @@ __device__ __forceinline__ uint32_t inflate_run(const uint8_t* raw, uint32_t lan
                                                 uint32_t cap, uint32_t& op, tk_inflate_tables& tb) {
     tk_inflate_state s;
     tk_inflate_init(s, raw, p, end);
-    if (lane == 0) tb.batch.n = 0;
     for (;;) {
         uint32_t ev = TK_INF_DONE, mlen = 0, mdist = 0;
         if (lane == 0) ev = (uint32_t)tk_inflate_next(s, tb, out, cap, op, &mlen, &mdist, 0, &tb.batch);
         __syncwarp();                                       // the batch and lane 0's literals are written
         ev = __shfl_sync(0xffffffffu, ev, 0);
         if (ev == TK_INF_ERROR) return TK_STATUS_CORRUPT;
-        inflate_exec_batch(tb.batch, out, lane);
-        if (lane == 0) tb.batch.n = 0;
-        __syncwarp();
+        inflate_exec_batch(tb.batch, __shfl_sync(0xffffffffu, s.nb, 0), out, lane);
+        s.nb = 0;
         if (ev == TK_INF_DONE) break;
     }
     op = __shfl_sync(0xffffffffu, op, 0);

@@ -18,17 +18,44 @@
 enum { TK_INF_MATCH = 0, TK_INF_DONE = 1, TK_INF_ERROR = 2, TK_INF_BATCH = 3 };
 enum { TK_INF_HEADER = 0, TK_INF_CODES = 1, TK_INF_END = 2 };
 
-#define TK_INF_LIT_FAST 10
-#define TK_INF_DIST_FAST 8
+#define TK_INF_LIT_FAST 11
+#define TK_INF_DIST_FAST 9
 // Matches whose copy is left to the caller (tk_inflate_next with a batch): destination, length and
 // distance of each; the literals around them are already in place.  The copies may run side by side
 // except where a match reads what an earlier match of the batch writes (source end behind the first
 // destination of the batch): those follow in order.
 #define TK_INF_BATCH_MAX 32
+struct alignas(16) tk_inflate_match { uint32_t dst, len, dist, reserved; };
 struct tk_inflate_batch {
-    uint32_t dst[TK_INF_BATCH_MAX], len[TK_INF_BATCH_MAX], dist[TK_INF_BATCH_MAX];
-    uint32_t n;
+    tk_inflate_match m[TK_INF_BATCH_MAX];      // the first tk_inflate_state::nb are valid
 };
+
+// length code - 257 / distance code -> baseline << 4 | extra bits (RFC 1951, 3.2.5).  Constants:
+// read by the one lane that walks the stream (constant bank on the device).
+#define TK_INF_LEN_CODES { 0x30u, 0x40u, 0x50u, 0x60u, 0x70u, 0x80u, 0x90u, 0xA0u, 0xB1u, 0xD1u, 0xF1u, 0x111u, 0x132u, 0x172u, 0x1B2u, 0x1F2u, 0x233u, 0x2B3u, 0x333u, 0x3B3u, 0x434u, 0x534u, 0x634u, 0x734u, 0x835u, 0xA35u, 0xC35u, 0xE35u, 0x1020u }
+#define TK_INF_DIST_CODES { 0x10u, 0x20u, 0x30u, 0x40u, 0x51u, 0x71u, 0x92u, 0xD2u, 0x113u, 0x193u, 0x214u, 0x314u, 0x415u, 0x615u, 0x816u, 0xC16u, 0x1017u, 0x1817u, 0x2018u, 0x3018u, 0x4019u, 0x6019u, 0x801Au, 0xC01Au, 0x1001Bu, 0x1801Bu, 0x2001Cu, 0x3001Cu, 0x4001Du, 0x6001Du }
+#if defined(__CUDACC__)
+static __constant__ uint32_t tk_inf_len_dev[29] = TK_INF_LEN_CODES;
+static __constant__ uint32_t tk_inf_dist_dev[30] = TK_INF_DIST_CODES;
+#endif
+#if !defined(__CUDA_ARCH__)
+static const uint32_t tk_inf_len_host[29] = TK_INF_LEN_CODES;
+static const uint32_t tk_inf_dist_host[30] = TK_INF_DIST_CODES;
+#endif
+TK_HD uint32_t tk_inf_len_code(int c) {
+#if defined(__CUDA_ARCH__)
+    return tk_inf_len_dev[c];
+#else
+    return tk_inf_len_host[c];
+#endif
+}
+TK_HD uint32_t tk_inf_dist_code(int c) {
+#if defined(__CUDA_ARCH__)
+    return tk_inf_dist_dev[c];
+#else
+    return tk_inf_dist_host[c];
+#endif
+}
 
 struct tk_inflate_tables {
     uint16_t lit_count[16], lit_symbol[288];
@@ -44,6 +71,7 @@ struct tk_inflate_state {
     uint64_t buf;                  // bit buffer, least significant bit first
     int      cnt;                  // bits in buf
     int      mode, last;
+    uint32_t nb;                   // matches waiting in the caller's batch
 };
 
 // Brings the buffer to at least 33 bits with one aligned 4-byte load (every field group of the
@@ -67,7 +95,7 @@ TK_HD void tk_inf_refill(tk_inflate_state& s) {
     s.cnt += 32;
 }
 TK_HD void tk_inflate_init(tk_inflate_state& s, const uint8_t* in, uint32_t pos, uint32_t end) {
-    s.in = in; s.pos = pos; s.end = end; s.buf = 0; s.cnt = 0; s.mode = TK_INF_HEADER; s.last = 0;
+    s.in = in; s.pos = pos; s.end = end; s.buf = 0; s.cnt = 0; s.mode = TK_INF_HEADER; s.last = 0; s.nb = 0;
     while (((uintptr_t)(in + s.pos) & 3u) && s.pos < end) {         // up to the first aligned word
         s.buf |= (uint64_t)in[s.pos++] << s.cnt;
         s.cnt += 8;
@@ -208,7 +236,7 @@ TK_HD bool tk_inf_dynamic_tables(tk_inflate_state& s, tk_inflate_tables& tb) {
 // against op and cap here), at the end of the stream, or on an error.
 // With `batch`: no match is copied or returned; each is appended to the batch and op moves past it.
 // Returns TK_INF_BATCH when the batch is full; at the end of the stream (or on an error) the batch
-// may hold matches too.  The caller copies them and sets batch->n = 0.
+// may hold matches too.  The caller copies the first s.nb entries and sets s.nb = 0.
 TK_HD int tk_inflate_next(tk_inflate_state& s, tk_inflate_tables& tb, uint8_t* out, uint32_t cap, uint32_t& op,
                           uint32_t* mlen, uint32_t* mdist, uint32_t self_copy = 0, tk_inflate_batch* batch = nullptr) {
     for (;;) {
@@ -251,30 +279,21 @@ TK_HD int tk_inflate_next(tk_inflate_state& s, tk_inflate_tables& tb, uint8_t* o
             if (sym == 256) { s.mode = TK_INF_HEADER; break; }
             sym -= 257;
             if (sym >= 29) return TK_INF_ERROR;
-            uint32_t len;
-            if (sym < 8) len = 3u + (uint32_t)sym;
-            else if (sym == 28) len = 258u;
-            else {
-                const int k = sym - 4, e = k >> 2;              // 1..5 extra bits
-                len = ((4u + (uint32_t)(k & 3)) << e) + 3u + tk_inf_bits(s, e);
-            }
+            const uint32_t lc = tk_inf_len_code(sym);
+            const uint32_t len = (lc >> 4) + tk_inf_bits(s, (int)(lc & 15u));          // 0..5 extra bits
             tk_inf_refill(s);                                   // distance code 15 + 13 extra
             const int dsym = tk_huff_decode(s, tb.dist_count, tb.dist_symbol, tb.dist_fast, TK_INF_DIST_FAST);
             if (dsym < 0 || dsym >= 30) return TK_INF_ERROR;
-            uint32_t dist;
-            if (dsym < 4) dist = (uint32_t)dsym + 1u;
-            else {
-                const int e = (dsym >> 1) - 1;                  // 1..13 extra bits
-                dist = ((2u + (uint32_t)(dsym & 1)) << e) + 1u + tk_inf_bits(s, e);
-            }
+            const uint32_t dc = tk_inf_dist_code(dsym);
+            const uint32_t dist = (dc >> 4) + tk_inf_bits(s, (int)(dc & 15u));         // 0..13 extra bits
             if (s.pos > s.end && tk_inf_consumed(s) > s.end) return TK_INF_ERROR;
             if (dist > op || len > cap - op) return TK_INF_ERROR;
             if (batch) {
-                const uint32_t k = batch->n;
-                batch->dst[k] = op; batch->len[k] = len; batch->dist[k] = dist;
-                batch->n = k + 1u;
+                tk_inflate_match e;
+                e.dst = op; e.len = len; e.dist = dist; e.reserved = 0;
+                batch->m[s.nb++] = e;
                 op += len;
-                if (k + 1u == TK_INF_BATCH_MAX) return TK_INF_BATCH;
+                if (s.nb == TK_INF_BATCH_MAX) return TK_INF_BATCH;
                 continue;
             }
             if (len <= self_copy) {

@@ -282,68 +282,113 @@ __device__ __forceinline__ bool lz4_length(cz_window& w, uint32_t lane, uint32_t
     return true;
 }
 
-// The sequences of one block [p, bend).  EMIT = false: only counts (op advances); EMIT = true: writes
-// out[op...] (capacity cap); matches may reach back to out[window].
-// One sequence at p, general form (every field through the checked window).  *last: the block ended
-// with this sequence's literals.
-template <bool EMIT>
-__device__ __forceinline__ uint32_t lz4_sequence(cz_window& w, uint32_t lane, uint32_t& p, uint32_t bend, uint8_t* out,
-                                                 uint32_t cap, uint32_t window, uint32_t& op, bool* last) {
+// A run of at most 32 bytes whose source is not written by anything that runs beside it: all loads
+// of a chunk are issued before its stores (the output is read back through L2: one round trip per
+// chunk, not per byte).
+__device__ __forceinline__ void cz_copy_small(uint8_t* dst, const uint8_t* src, uint32_t len) {
+    for (uint32_t k0 = 0; k0 < len; k0 += 8) {
+        uint8_t v[8];
+#pragma unroll
+        for (int j = 0; j < 8; ++j) v[j] = k0 + j < len ? src[k0 + j] : (uint8_t)0;
+#pragma unroll
+        for (int j = 0; j < 8; ++j) if (k0 + j < len) dst[k0 + j] = v[j];
+    }
+}
+
+// The copies of up to 32 sequences, lane per sequence (ll literal bytes from raw[lsrc..] to out[dst..],
+// then a match of ml bytes at distance off): every literal run side by side, then the matches that
+// read nothing an earlier match of the batch writes (source end not behind the first match
+// destination of the batch; most of them), then the others in sequence order, each by the whole warp.
+__device__ __forceinline__ void cz_exec_seqs(const uint8_t* raw, uint8_t* out, uint32_t lane, uint32_t ll, uint32_t lsrc,
+                                             uint32_t dst, uint32_t ml, uint32_t off) {
+    uint32_t longs = __ballot_sync(0xffffffffu, ll > 32u);
+    if (ll && ll <= 32u) cz_copy_small(out + dst, raw + lsrc, ll);
+    while (longs) {
+        const int L = __ffs((int)longs) - 1;
+        longs &= longs - 1u;
+        const uint32_t sL = __shfl_sync(0xffffffffu, lsrc, L), dL = __shfl_sync(0xffffffffu, dst, L);
+        const uint32_t nL = __shfl_sync(0xffffffffu, ll, L);
+        for (uint32_t k = lane; k < nL; k += 32) out[dL + k] = raw[sL + k];
+    }
+    __syncwarp();
+    const uint32_t mdst = dst + ll;
+    const uint32_t has = __ballot_sync(0xffffffffu, ml > 0u);
+    if (!has) return;
+    const uint32_t first_dst = __shfl_sync(0xffffffffu, mdst, __ffs((int)has) - 1);
+    // (a match that overlaps its own destination has its source end behind its destination too)
+    const bool dep = ml && (mdst - off + ml > first_dst || ml > 32u);
+    if (ml && !dep) cz_copy_small(out + mdst, out + mdst - off, ml);
+    uint32_t deps = __ballot_sync(0xffffffffu, dep);
+    while (deps) {
+        const int L = __ffs((int)deps) - 1;
+        deps &= deps - 1u;
+        cz_match(out, __shfl_sync(0xffffffffu, mdst, L), __shfl_sync(0xffffffffu, off, L), __shfl_sync(0xffffffffu, ml, L), lane);
+    }
+    __syncwarp();
+}
+
+// One sequence at p, general form (every field through the checked window): literal run [*lit_at,
+// + *lit), then -- unless the block ends with the literals (*last) -- offset and match length.
+__device__ __forceinline__ uint32_t lz4_parse_general(cz_window& w, uint32_t lane, uint32_t& p, uint32_t bend, uint32_t* lit,
+                                                      uint32_t* lit_at, uint32_t* offset, uint32_t* mlen, bool* last) {
     const uint32_t token = cz_byte(w, p, lane);
-    uint32_t lit, lit_at = p + 1;
-    if (!lz4_length(w, lane, lit_at, bend, token >> 4, lit) || lit > bend - lit_at) return TK_STATUS_CORRUPT;
-    if (lit > cap - op) return EMIT ? TK_STATUS_CORRUPT : TK_STATUS_UNSUPPORTED;
-    if (EMIT) cz_literals(w, lane, lit_at, lit, out, op);
-    op += lit;
-    p = lit_at + lit;
+    uint32_t at = p + 1, n;
+    if (!lz4_length(w, lane, at, bend, token >> 4, n) || n > bend - at) return TK_STATUS_CORRUPT;
+    *lit = n; *lit_at = at;
+    p = at + n;
+    *offset = 1; *mlen = 0;
     if (p >= bend) { *last = true; return TK_STATUS_OK; }       // the last sequence has no match
     if (bend - p < 2u) return TK_STATUS_CORRUPT;
-    const uint32_t offset = cz_byte(w, p, lane) | (cz_byte(w, p + 1, lane) << 8);
+    *offset = cz_byte(w, p, lane) | (cz_byte(w, p + 1, lane) << 8);
     p += 2;
-    uint32_t mlen;
-    if (!lz4_length(w, lane, p, bend, token & 15u, mlen)) return TK_STATUS_CORRUPT;
-    mlen += 4u;
-    if (offset == 0 || offset > op - window) return TK_STATUS_CORRUPT;
-    if (mlen > cap - op) return EMIT ? TK_STATUS_CORRUPT : TK_STATUS_UNSUPPORTED;
-    if (EMIT) cz_match(out, op, offset, mlen, lane);
-    op += mlen;
+    uint32_t m;
+    if (!lz4_length(w, lane, p, bend, token & 15u, m)) return TK_STATUS_CORRUPT;
+    *mlen = m + 4u;
     return TK_STATUS_OK;
 }
 
 // The sequences of one block [p, bend).  EMIT = false: only counts (op advances); EMIT = true: writes
 // out[op...] (capacity cap); matches may reach back to out[window].
-// Fast lane (literal run < 15, the usual case in text): lane i takes byte p + i out of the window
-// with one shuffle; the token is lane 0's byte, the literals are the bytes of lanes 1..lit (stored
-// straight from the register), the offset the bytes of lanes lit+1, lit+2.
+// The fields of a sequence depend on one another but on nothing the decoder writes, so the warp
+// first parses up to 32 sequences (every lane the same parse on bytes taken from the shuffled
+// window; lane e keeps sequence e), then copies them side by side (cz_exec_seqs).  Fast lane of the
+// parse (literal run < 15, the usual case in text): lane i takes byte p + i out of the window with
+// one shuffle; the token is lane 0's byte, the offset the bytes of lanes lit + 1, lit + 2.
 template <bool EMIT>
 __device__ __forceinline__ uint32_t lz4_block_run(cz_window& w, uint32_t lane, uint32_t p, uint32_t bend, uint8_t* out,
                                                   uint32_t cap, uint32_t window, uint32_t& op) {
-    while (p < bend) {
-        if (p - w.at > 96u) cz_load(w, p, lane);              // [p, p + 32) is inside the window
-        const uint32_t jj = p - w.at + lane;
-        const uint32_t mine = (__shfl_sync(0xffffffffu, w.word, jj >> 2) >> ((jj & 3u) * 8u)) & 0xFFu;
-        const uint32_t token = __shfl_sync(0xffffffffu, mine, 0);
-        const uint32_t lit = token >> 4;
-        if (lit == 15u || bend - p < 32u) {                   // long literal run / end of the block
+    bool block_done = false;
+    while (p < bend && !block_done) {
+        uint32_t my_ll = 0, my_lsrc = 0, my_dst = 0, my_ml = 0, my_off = 1;
+        uint32_t n = 0;
+        for (; n < 32u && p < bend; ++n) {
+            uint32_t lit, lit_at, offset, mlen;
             bool last = false;
-            const uint32_t st = lz4_sequence<EMIT>(w, lane, p, bend, out, cap, window, op, &last);
-            if (st) return st;
-            if (last) break;
-            continue;
+            if (p - w.at > 96u) cz_load(w, p, lane);              // [p, p + 32) is inside the window
+            const uint32_t jj = p - w.at + lane;
+            const uint32_t mine = (__shfl_sync(0xffffffffu, w.word, jj >> 2) >> ((jj & 3u) * 8u)) & 0xFFu;
+            const uint32_t token = __shfl_sync(0xffffffffu, mine, 0);
+            if ((token >> 4) == 15u || bend - p < 32u) {          // long literal run / end of the block
+                const uint32_t st = lz4_parse_general(w, lane, p, bend, &lit, &lit_at, &offset, &mlen, &last);
+                if (st) return st;
+            } else {
+                lit = token >> 4;
+                lit_at = p + 1u;
+                offset = __shfl_sync(0xffffffffu, mine, lit + 1u) | (__shfl_sync(0xffffffffu, mine, lit + 2u) << 8);
+                p += lit + 3u;
+                if (!lz4_length(w, lane, p, bend, token & 15u, mlen)) return TK_STATUS_CORRUPT;
+                mlen += 4u;
+            }
+            if (lit > cap - op) return EMIT ? TK_STATUS_CORRUPT : TK_STATUS_UNSUPPORTED;
+            if (!last) {
+                if (offset == 0 || offset > op + lit - window) return TK_STATUS_CORRUPT;
+                if (mlen > cap - op - lit) return EMIT ? TK_STATUS_CORRUPT : TK_STATUS_UNSUPPORTED;
+            }
+            if (lane == n) { my_ll = lit; my_lsrc = lit_at; my_dst = op; my_ml = mlen; my_off = offset; }
+            op += lit + mlen;
+            if (last) { block_done = true; ++n; break; }
         }
-        if (lit > cap - op) return EMIT ? TK_STATUS_CORRUPT : TK_STATUS_UNSUPPORTED;
-        if (EMIT && lane - 1u < lit) out[op + lane - 1u] = (uint8_t)mine;
-        op += lit;
-        uint32_t offset = 1;                                 // (the size pass leaves offsets to the decode pass)
-        if (EMIT) offset = __shfl_sync(0xffffffffu, mine, lit + 1u) | (__shfl_sync(0xffffffffu, mine, lit + 2u) << 8);
-        p += lit + 3u;
-        uint32_t mlen;
-        if (!lz4_length(w, lane, p, bend, token & 15u, mlen)) return TK_STATUS_CORRUPT;
-        mlen += 4u;
-        if (EMIT && (offset == 0 || offset > op - window)) return TK_STATUS_CORRUPT;
-        if (mlen > cap - op) return EMIT ? TK_STATUS_CORRUPT : TK_STATUS_UNSUPPORTED;
-        if (EMIT) cz_match(out, op, offset, mlen, lane);
-        op += mlen;
+        if (EMIT) cz_exec_seqs(w.raw, out, lane, my_ll, my_lsrc, my_dst, my_ml, my_off);
     }
     return TK_STATUS_OK;
 }
@@ -465,19 +510,6 @@ __device__ __forceinline__ uint32_t snappy_run(cz_window& w, uint32_t lane, uint
 // ---------------------------------------------------------------- DEFLATE (gzip)
 // Lane 0 owns the decoder state and runs tk_inflate_next up to the next match; its literals are
 // plain stores of lane 0 (ordered before the warp's reads by the __syncwarp in cz_match).
-// A run of at most 32 bytes whose source lies below everything the batch writes: all loads of a
-// chunk are issued before its stores (the output is read back through L2: one round trip per
-// chunk, not per byte).
-__device__ __forceinline__ void cz_copy_small(uint8_t* out, uint32_t dst, uint32_t src, uint32_t len) {
-    for (uint32_t k0 = 0; k0 < len; k0 += 8) {
-        uint8_t v[8];
-#pragma unroll
-        for (int j = 0; j < 8; ++j) v[j] = k0 + j < len ? out[src + k0 + j] : (uint8_t)0;
-#pragma unroll
-        for (int j = 0; j < 8; ++j) if (k0 + j < len) out[dst + k0 + j] = v[j];
-    }
-}
-
 // The matches of a batch (tk_inflate_next), lane per match; the dependent ones by the whole warp in order.
 __device__ __forceinline__ void inflate_exec_batch(const tk_inflate_batch& b, uint32_t n, uint8_t* out, uint32_t lane) {
     if (!n) return;
@@ -486,7 +518,7 @@ __device__ __forceinline__ void inflate_exec_batch(const tk_inflate_batch& b, ui
     const uint32_t first_dst = __shfl_sync(0xffffffffu, dst, 0), src = dst - dist;
     // (a match that overlaps its own destination has its source end behind its destination too)
     const bool dep = len && (src + len > first_dst || len > 32u);
-    if (len && !dep) cz_copy_small(out, dst, src, len);
+    if (len && !dep) cz_copy_small(out + dst, out + src, len);
     uint32_t deps = __ballot_sync(0xffffffffu, dep);
     while (deps) {
         const int L = __ffs((int)deps) - 1;
@@ -671,7 +703,7 @@ __device__ __forceinline__ void zstd_exec_batch(const tk_zstd_batch& b, uint32_t
     const uint32_t has = __ballot_sync(0xffffffffu, ml > 0u);
     const uint32_t first_dst = __shfl_sync(0xffffffffu, mdst, has ? __ffs((int)has) - 1 : 0);
     const bool dep = ml && (mdst - off + ml > first_dst || off < ml || ml > 32u);
-    if (ml && !dep) cz_copy_small(out, mdst, mdst - off, ml);
+    if (ml && !dep) cz_copy_small(out + mdst, out + mdst - off, ml);
     uint32_t deps = __ballot_sync(0xffffffffu, dep);
     while (deps) {
         const int L = __ffs((int)deps) - 1;

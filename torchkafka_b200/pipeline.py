@@ -65,6 +65,10 @@ class _Pending:
         self.offsets = offsets           # fetch's {dense partition: fetch offset} and None
 
 
+#: staging slots of a pipeline fed with record batches (see IngestPipeline.__init__)
+RAW_MIN_SLOTS = 6
+
+
 class IngestPipeline:
     def __init__(self, consumer, schema, batch_size: int, drop_last: bool = False,
                  slot_bytes: int = 64 << 20, n_slots: int = 3, device: Optional[int] = None,
@@ -77,8 +81,14 @@ class IngestPipeline:
         self.schema = schema
         self.batch_size = int(batch_size)
         self.drop_last = bool(drop_last)
+        # Record-batch input may be compressed, and a decompression unit (an LZ4 block, the DEFLATE
+        # stream or the zstd frames of one batch) is decoded by one warp from end to end: a slot of
+        # 64 KB batches occupies 5 warps per SM for milliseconds.  What fills the GPU then is slots
+        # in flight (each decompresses on its own stream): at least RAW_MIN_SLOTS of them.
+        raw_input = input_mode in ("raw", "raw_into", "raw_dma")
         self.engine = _engine.acquire(schema, batch_size, slot_bytes=slot_bytes,
-                                      n_slots=max(n_slots, 2 + (int(n_producers) if threaded else 0)),
+                                      n_slots=max(n_slots, 2 + (int(n_producers) if threaded else 0),
+                                                  RAW_MIN_SLOTS if raw_input else 0),
                                       device=device, n_partitions=max_partitions, output_bytes=output_bytes)
         if json_single_pass is not None:
             self.engine.set_json_fused(bool(json_single_pass))

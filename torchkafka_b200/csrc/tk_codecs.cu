@@ -30,6 +30,7 @@
 // the fields of an element depend on one another, a cache round trip each would dominate);
 // literals and matches are copied by the whole warp, overlapping matches by repeating the source
 // with period `offset`; matches are read back from the unit's own output through L1.
+#include <algorithm>
 #include <type_traits>
 #include "tk_rb.h"
 #include "tk_inflate.cuh"
@@ -61,14 +62,36 @@ static uint32_t lz4_units(const uint8_t* raw, uint32_t p, uint32_t end, unit_sin
     if ((flg >> 6) != 1u) return TK_STATUS_CORRUPT;
     if (flg & 1u) return TK_STATUS_UNSUPPORTED;                              // dictionary
     const bool independent = flg & 0x20u, block_checksum = flg & 0x10u, content_checksum = flg & 0x04u;
+    // BD byte: the largest block the frame may hold decompressed (64 KB .. 4 MB).  A batch whose
+    // frame is one unit (one block, or a chain) is placed by that bound and needs no size pass.
+    const uint32_t bd = (raw[p + 5] >> 4) & 7u;
+    if (bd < 4u) return TK_STATUS_CORRUPT;
+    const uint64_t block_max = 1ull << (8u + 2u * bd);
     p += 6u + ((flg & 0x08u) ? 8u : 0u) + 1u;                                // content size, header checksum
     if (p > end) return TK_STATUS_CORRUPT;
     if (!independent) {
-        // blocks may refer to the output of earlier blocks: one unit decodes the chain in order
+        // blocks may refer to the output of earlier blocks: one unit decodes the chain in order;
+        // its bound follows from a walk over the block headers
+        uint64_t bound = 0;
+        bool walked = false;
+        for (uint32_t q = p; end - q >= 4u;) {
+            uint32_t size = cu_le32(raw + q);
+            q += 4;
+            if (size == 0) { walked = true; break; }
+            const bool stored = size >> 31;
+            size &= 0x7FFFFFFFu;
+            if (size > end - q) break;
+            bound += stored ? size : std::min<uint64_t>(block_max, 255ull * size);
+            q += size + (block_checksum ? 4u : 0u);
+            if (q > end) break;
+        }
+        const bool bounded = walked && bound <= 0x7FFFFFFFull;     // (a broken chain is found by the decoder)
         sink.add(p, end - p, RB_UNIT_LZ4_CHAIN | (block_checksum ? RB_UNIT_BLOCK_CHECKSUM : 0u) |
-                                 (content_checksum ? RB_UNIT_CONTENT_CHECKSUM : 0u), 0);
+                                 (content_checksum ? RB_UNIT_CONTENT_CHECKSUM : 0u) | (bounded ? RB_UNIT_BOUND : 0u),
+                 bounded ? (uint32_t)bound : 0u);
         return TK_STATUS_OK;
     }
+    const uint32_t first_unit = sink.n;
     for (;;) {
         if (end - p < 4u) return TK_STATUS_CORRUPT;
         uint32_t size = cu_le32(raw + p);
@@ -81,6 +104,11 @@ static uint32_t lz4_units(const uint8_t* raw, uint32_t p, uint32_t end, unit_sin
         else sink.add(p, size, RB_UNIT_LZ4_BLOCK, 0);
         p += size + (block_checksum ? 4u : 0u);
         if (p > end) return TK_STATUS_CORRUPT;
+    }
+    if (!sink.full && sink.n == first_unit + 1u && (sink.units[first_unit].kind & 0xFFu) == RB_UNIT_LZ4_BLOCK) {
+        tk_rb_unit& u = sink.units[first_unit];                               // the frame's only block
+        u.kind |= RB_UNIT_BOUND;
+        u.unc_len = (uint32_t)std::min<uint64_t>(block_max, 255ull * u.src_len);
     }
     return p + (content_checksum ? 4u : 0u) == end ? TK_STATUS_OK : TK_STATUS_CORRUPT;
 }
@@ -556,7 +584,7 @@ __global__ void __launch_bounds__(256) k_unit_size(const rb_args a) {
     const uint32_t warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, nwarps = (gridDim.x * blockDim.x) >> 5;
     for (uint32_t i = warp; i < a.n_units; i += nwarps) {
         const tk_rb_unit u = a.units[i];
-        if ((u.kind & RB_UNIT_SIZED) || (u.kind & 0xFFu) > RB_UNIT_LZ4_CHAIN) continue;
+        if ((u.kind & (RB_UNIT_SIZED | RB_UNIT_BOUND)) || (u.kind & 0xFFu) > RB_UNIT_LZ4_CHAIN) continue;
         cz_window w;
         w.raw = a.raw;
         cz_load(w, u.src, lane);
@@ -630,7 +658,11 @@ __global__ void __launch_bounds__(128) k_unit_decode(const rb_args a) {
             else if (kind == RB_UNIT_LZ4_CHAIN) st = lz4_chain_run<true>(w, lane, u.src, u.src + u.src_len, u.kind, out, u.unc_len, op);
             else st = snappy_run(w, lane, u.src, u.src + u.src_len, out, u.unc_len, op);
         }
-        if (!st && op != u.unc_len) st = TK_STATUS_CORRUPT;
+        if (u.kind & RB_UNIT_BOUND) {                       // placed by its upper bound: the records end here
+            if (!st && lane == 0) a.batches[u.batch].rec_end = a.batches[u.batch].rec_start + op;
+        } else if (!st && op != u.unc_len) {
+            st = TK_STATUS_CORRUPT;
+        }
         // (k_rb_check runs behind this kernel and turns the status into the batch's error entry)
         if (st && lane == 0) a.batches[u.batch].status = TK_STATUS_CORRUPT;
     }

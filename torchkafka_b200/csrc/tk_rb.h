@@ -18,7 +18,7 @@ enum { RB_UNIT_LZ4_BLOCK = 1, RB_UNIT_LZ4_CHAIN = 2, RB_UNIT_STORED = 3, RB_UNIT
 #define RB_UNIT_CONTENT_CHECKSUM 0x200u  // LZ4 chain: 4 checksum bytes behind the end mark
 #define RB_UNIT_SIZED 0x400u             // unc_len is known from the framing (no size pass)
 #define RB_UNIT_FAILED 0x800u            // the size pass found the stream broken
-#define RB_UNIT_BOUND 0x1000u            // unc_len is an upper bound (zstd frames without content size):
+#define RB_UNIT_BOUND 0x1000u            // unc_len is an upper bound (zstd frames without content size, LZ4 frames of one unit):
                                          // no size pass, the decode sets the batch's record range
 struct tk_rb_unit {
     uint32_t src, src_len;     // compressed bytes in the raw buffer

@@ -569,8 +569,9 @@ static int rb_ensure_codecs(tk_ctx* ctx) {
     return 0;
 }
 
-// zstd frames without a content size are placed in the decompressed buffer by their upper bound
-// (128 KiB per compressed block), which saves the size pass -- as long as the bounds of the slot
+// zstd frames without a content size and LZ4 frames that are one unit are placed in the decompressed
+// buffer by their upper bound (128 KiB per compressed zstd block; the LZ4 frame's maximal block size),
+// which saves the size pass -- as long as the bounds of the slot
 // fit a buffer of at most RB_BOUND_FACTOR x slot_bytes (below the 2 GiB the copy descriptors
 // address); the buffer grows to what the largest slot so far needed.  Otherwise (or with
 // TK_ZSTD_SIZE_PASS=1 in the environment, for tests and comparisons) the units go back to the

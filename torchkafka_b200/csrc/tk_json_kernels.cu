@@ -356,41 +356,23 @@ __global__ void __launch_bounds__(256, 6) k_json_parse(const flat_args a) {
                               threadIdx.x & 31);
     const uint32_t n_tok = min(*a.tok_count, a.tok_cap);
     T* values = reinterpret_cast<T*>(a.values.base);
-    // Persistent grid, software-pipelined two elements deep.  While element i is parsed, the token
-    // entry of element i + 2 travels from DRAM to a per-thread shared-memory slot (cp.async: no
-    // register holds it -- an entry loaded into registers two iterations ahead is spilled at 40
-    // registers, and the spill store waits for the load), and the text of element i + 1, whose entry
-    // arrived during the previous iteration, is prefetched into L1: neither of the two dependent
-    // DRAM round trips (entry -> text) is waited for.
-    __shared__ uint4 ring[2][256];           // {position, record | flags, next position, -} per thread
+    // Persistent grid, software-pipelined two elements deep: the token entry of iteration i + 2
+    // is requested and the text of element i + 1 is prefetched into L1 while element i is parsed,
+    // so neither of the two dependent DRAM round trips (entry -> text) is waited for.
     const uint32_t stride = gridDim.x * blockDim.x;
     uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
-    auto request = [&](uint32_t tt, uint32_t slot) {            // entry tt and the position behind it
-        const uint32_t dst = (uint32_t)__cvta_generic_to_shared(&ring[slot][threadIdx.x]);
-        asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"(dst), "l"(a.tok + tt) : "memory");
-        asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(dst + 8u), "l"(&a.tok[tt + 1].x) : "memory");  // one spare entry behind the array
-    };
-    uint2 tk = make_uint2(0, 0);
-    uint32_t np = 0, par = 0;
-    if (t < n_tok) { tk = __ldg(a.tok + t); np = __ldg(&a.tok[t + 1].x); }
-    if (t + stride < n_tok) request(t + stride, 0);
-    asm volatile("cp.async.commit_group;" ::: "memory");
+    uint2 tk = make_uint2(0, 0), tk1 = make_uint2(0, 0), tk2 = make_uint2(0, 0);
+    uint32_t np = 0, np1 = 0, np2 = 0;
+    if (t < n_tok) { tk = __ldg(a.tok + t); np = __ldg(&a.tok[t + 1].x); }   // one spare entry behind the array
+    if (t + stride < n_tok) { tk1 = __ldg(a.tok + t + stride); np1 = __ldg(&a.tok[t + stride + 1].x); }
 #pragma unroll 1
-    for (; t < n_tok; t += stride) {
-        asm volatile("cp.async.wait_group 0;" ::: "memory");    // entry i + 1 (requested an iteration ago)
-        const uint4* next_entry = &ring[par][threadIdx.x];
-        if (t + stride < n_tok) {
-            const uint8_t* ahead = a.bytes + next_entry->x;
-            asm volatile("prefetch.global.L1 [%0];" ::"l"(ahead));
-            asm volatile("prefetch.global.L1 [%0];" ::"l"(ahead + 27));
-        }
-        par ^= 1u;
-        if (t + 2 * stride < n_tok) request(t + 2 * stride, par);
-        asm volatile("cp.async.commit_group;" ::: "memory");
+    for (; t < n_tok; t += stride, tk = tk1, np = np1, tk1 = tk2, np1 = np2) {
+        const uint32_t t2 = t + 2 * stride;
+        const uint8_t* ahead = a.bytes + tk1.x;
+        asm volatile("prefetch.global.L1 [%0];" ::"l"(ahead));
+        asm volatile("prefetch.global.L1 [%0];" ::"l"(ahead + 27));
+        if (t2 < n_tok) { tk2 = __ldg(a.tok + t2); np2 = __ldg(&a.tok[t2 + 1].x); }
         json_parse_one<KIND>(a, tb, t, tk, np, values);
-        const uint4 nxt = *next_entry;                          // (re-read: nothing of it lives across the element)
-        tk = make_uint2(nxt.x, nxt.y);
-        np = nxt.z;
     }
 }
 

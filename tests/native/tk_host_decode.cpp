@@ -231,13 +231,13 @@ extern "C" int tk_host_zstd_batched(const uint8_t* in, uint32_t len, uint8_t* ou
         if (n > 0) {
             uint32_t dst[TK_ZS_BATCH], pos = op, first_dst = 0;
             bool have_first = false;
-            for (int k = 0; k < n; ++k) { dst[k] = pos; pos += b.lit_len[k] + b.mlen[k]; }
-            if (b.lit_kind == TK_ZL_OUTPUT && pos > b.lit_src[0]) {
+            for (int k = 0; k < n; ++k) { dst[k] = pos; pos += b.q[k].lit_len + b.q[k].mlen; }
+            if (b.lit_kind == TK_ZL_OUTPUT && pos > b.q[0].lit_src) {
                 // the batch writes into parked literals it still reads: sequence order
                 for (int k = 0; k < n; ++k) {
-                    for (uint32_t j = 0; j < b.lit_len[k]; ++j) out[dst[k] + j] = out[b.lit_src[k] + j];
-                    const uint32_t mdst = dst[k] + b.lit_len[k];
-                    for (uint32_t j = 0; j < b.mlen[k]; ++j) out[mdst + j] = out[mdst - b.offset[k] + j];
+                    for (uint32_t j = 0; j < b.q[k].lit_len; ++j) out[dst[k] + j] = out[b.q[k].lit_src + j];
+                    const uint32_t mdst = dst[k] + b.q[k].lit_len;
+                    for (uint32_t j = 0; j < b.q[k].mlen; ++j) out[mdst + j] = out[mdst - b.q[k].offset + j];
                 }
                 op = pos;
                 continue;
@@ -245,21 +245,21 @@ extern "C" int tk_host_zstd_batched(const uint8_t* in, uint32_t len, uint8_t* ou
             // literals, last run first: the device copies them side by side, so no run may write
             // what another one reads -- the reverse order makes such a dependency visible here
             for (int k = n - 1; k >= 0; --k) {
-                if (b.lit_kind == TK_ZL_INPUT) memmove(out + dst[k], in + b.lit_src[k], b.lit_len[k]);
-                else if (b.lit_kind == TK_ZL_RLE) memset(out + dst[k], (int)b.lit_src[k], b.lit_len[k]);
-                else for (uint32_t j = 0; j < b.lit_len[k]; ++j) out[dst[k] + j] = out[b.lit_src[k] + j];
+                if (b.lit_kind == TK_ZL_INPUT) memmove(out + dst[k], in + b.q[k].lit_src, b.q[k].lit_len);
+                else if (b.lit_kind == TK_ZL_RLE) memset(out + dst[k], (int)b.q[k].lit_src, b.q[k].lit_len);
+                else for (uint32_t j = 0; j < b.q[k].lit_len; ++j) out[dst[k] + j] = out[b.q[k].lit_src + j];
             }
             bool dep[TK_ZS_BATCH];
             for (int k = 0; k < n; ++k) {
-                const uint32_t mdst = dst[k] + b.lit_len[k];
-                if (b.mlen[k] && !have_first) { have_first = true; first_dst = mdst; }
-                dep[k] = b.mlen[k] && (mdst - b.offset[k] + b.mlen[k] > first_dst || b.offset[k] < b.mlen[k] || b.mlen[k] > 32u);
+                const uint32_t mdst = dst[k] + b.q[k].lit_len;
+                if (b.q[k].mlen && !have_first) { have_first = true; first_dst = mdst; }
+                dep[k] = b.q[k].mlen && (mdst - b.q[k].offset + b.q[k].mlen > first_dst || b.q[k].offset < b.q[k].mlen || b.q[k].mlen > 32u);
             }
             for (int pass = 0; pass < 2; ++pass)                 // independent matches first, then the dependent ones
                 for (int k = 0; k < n; ++k) {
                     if ((int)dep[k] != pass) continue;
-                    const uint32_t mdst = dst[k] + b.lit_len[k];
-                    for (uint32_t j = 0; j < b.mlen[k]; ++j) out[mdst + j] = out[mdst - b.offset[k] + j];
+                    const uint32_t mdst = dst[k] + b.q[k].lit_len;
+                    for (uint32_t j = 0; j < b.q[k].mlen; ++j) out[mdst + j] = out[mdst - b.q[k].offset + j];
                 }
             op = pos;
             continue;

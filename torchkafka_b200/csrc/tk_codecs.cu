@@ -678,7 +678,7 @@ __global__ void __launch_bounds__(128) k_unit_decode(const rb_args a) {
 __device__ __forceinline__ void zstd_exec_batch(const tk_zstd_batch& b, uint32_t n, const uint8_t* raw, uint8_t* out,
                                                 uint32_t& op, uint32_t lane) {
     uint32_t ll = 0, ml = 0, off = 0, src = 0;
-    if (lane < n) { ll = b.lit_len[lane]; ml = b.mlen[lane]; off = b.offset[lane]; src = b.lit_src[lane]; }
+    if (lane < n) { const tk_zstd_seq q = b.q[lane]; ll = q.lit_len; ml = q.mlen; off = q.offset; src = q.lit_src; }
     const uint32_t kind = b.lit_kind;
     uint32_t incl = ll + ml;
 #pragma unroll

@@ -674,8 +674,9 @@ TK_HD int tk_zstd_next(tk_zstd_state& s, tk_zstd_tables& tb, uint8_t* out, uint3
 // section (the caller goes on with tk_zstd_next), or -status on a broken stream.  `op` is the
 // output position in front of the first sequence of the batch.
 #define TK_ZS_BATCH 32
+struct alignas(16) tk_zstd_seq { uint32_t lit_len, lit_src, mlen, offset; };
 struct tk_zstd_batch {
-    uint32_t lit_len[TK_ZS_BATCH], lit_src[TK_ZS_BATCH], mlen[TK_ZS_BATCH], offset[TK_ZS_BATCH];
+    tk_zstd_seq q[TK_ZS_BATCH];
     uint32_t lit_kind;             // of every literal run of the batch (the block's)
 };
 
@@ -698,13 +699,18 @@ TK_HD int tk_zstd_next_batch(tk_zstd_state& s, const tk_zstd_tables& tb, uint32_
     int32_t bitpos = s.bitpos;
     tk_zs_win win = s.win;
     b->lit_kind = lit_kind;
+    // Errors are collected, not branched on: nothing inside the loop reads memory through a value
+    // a broken stream controls (the states stay inside their tables by construction, the window
+    // reads zeros outside the stream, the batch index is the loop counter), so a broken sequence
+    // only produces garbage that is thrown away when the loop is left.
+    uint32_t bad = 0;
     int n = 0;
     for (; n < TK_ZS_BATCH && seq_left; ++n) {
         const uint32_t e_of = reinterpret_cast<const uint32_t*>(tb.of)[st_of];
         const uint32_t e_ml = reinterpret_cast<const uint32_t*>(tb.ml)[st_ml];
         const uint32_t e_ll = reinterpret_cast<const uint32_t*>(tb.ll)[st_ll];
+        // (the symbols are below 32 / 53 / 36: the table builds admit no others)
         const uint32_t ofc = e_of & 0xFFu, mlc = e_ml & 0xFFu, llc = e_ll & 0xFFu;
-        if (ofc > 31u || mlc > 52u || llc > 35u) return -TK_ZS_ERROR;
         const uint32_t mlp = tk_zs_ml_code(mlc), llp = tk_zs_ll_code(llc), mlb = mlp & 31u, llb = llp & 31u;
         const bool more = seq_left > 1u;
         const uint32_t nb_ll = (e_ll >> 8) & 0xFFu, nb_ml = (e_ml >> 8) & 0xFFu, nb_of = (e_of >> 8) & 0xFFu;
@@ -725,14 +731,14 @@ TK_HD int tk_zstd_next_batch(tk_zstd_state& s, const tk_zstd_tables& tb, uint32_
             ov = (1u << ofc) + tk_zs_win_read(win, in, lo, hi, &bitpos, (int)ofc);
             mlen = (mlp >> 5) + tk_zs_win_read(win, in, lo, hi, &bitpos, (int)mlb);
             llen = (llp >> 5) + tk_zs_win_read(win, in, lo, hi, &bitpos, (int)llb);
-            if (bitpos < 0) return -TK_ZS_ERROR;
+            bad |= (uint32_t)bitpos >> 31;
             if (more) {
                 st_ll = (e_ll >> 16) + tk_zs_win_read(win, in, lo, hi, &bitpos, (int)nb_ll);
                 st_ml = (e_ml >> 16) + tk_zs_win_read(win, in, lo, hi, &bitpos, (int)nb_ml);
                 st_of = (e_of >> 16) + tk_zs_win_read(win, in, lo, hi, &bitpos, (int)nb_of);
             }
         }
-        if (bitpos < 0) return -TK_ZS_ERROR;
+        bad |= (uint32_t)bitpos >> 31;                                 // ran off the front of the stream
         uint32_t offset;
         if (ov > 3u) {
             offset = ov - 3u;
@@ -749,16 +755,20 @@ TK_HD int tk_zstd_next_batch(tk_zstd_state& s, const tk_zstd_tables& tb, uint32_
             }
         }
         --seq_left;
-        if (!more && bitpos != 0) return -TK_ZS_ERROR;               // the bit stream must end exactly
-        if (llen > lit_left || llen > cap - op || mlen > cap - op - llen) return -TK_ZS_ERROR;
-        if (offset == 0 || offset > op + llen) return -TK_ZS_ERROR;  // no dictionary: only this payload's output
-        b->lit_len[n] = llen; b->lit_src[n] = lit_src; b->mlen[n] = mlen; b->offset[n] = offset;
+        const uint32_t room = cap - op;
+        bad |= (uint32_t)(!more & (bitpos != 0))                        // the bit stream must end exactly
+             | (uint32_t)(llen > lit_left) | (uint32_t)(llen > room) | (uint32_t)(mlen > room - llen)
+             | (uint32_t)(offset == 0) | (uint32_t)(offset > op + llen);   // no dictionary: only this payload's output
+        tk_zstd_seq q;
+        q.lit_len = llen; q.lit_src = lit_src; q.mlen = mlen; q.offset = offset;
+        b->q[n] = q;
         lit_left -= llen;
         if (lit_kind != TK_ZL_RLE) lit_src += llen;
         op += llen + mlen;
         // parked literals not yet read must stay ahead of the write position
-        if (emit && lit_kind == TK_ZL_OUTPUT && lit_left && op > lit_src) return -TK_ZS_ERROR;
+        bad |= (uint32_t)(emit & (lit_kind == TK_ZL_OUTPUT) & (lit_left != 0) & (op > lit_src));
     }
+    if (bad) return -TK_ZS_ERROR;
     s.st_ll = st_ll; s.st_ml = st_ml; s.st_of = st_of;
     s.rep0 = rep0; s.rep1 = rep1; s.rep2 = rep2;
     s.seq_left = seq_left; s.lit_left = lit_left; s.lit_src = lit_src;

@@ -266,28 +266,34 @@ TK_HD int tk_inflate_next(tk_inflate_state& s, tk_inflate_tables& tb, uint8_t* o
             s.mode = TK_INF_CODES;
         }
         if (s.mode == TK_INF_END) return TK_INF_DONE;
+        // (the error conditions of a symbol are collected and branched on once: with a single lane
+        // active every branch costs its convergence bookkeeping)
         for (;;) {
             tk_inf_refill(s);                                   // >= 33 bits: literal/length code 15 + 5 extra
-            if (s.pos > s.end && tk_inf_consumed(s) > s.end) return TK_INF_ERROR;   // (only once the input is all loaded)
+            // (the input position is only checked once the input is all loaded)
+            bool bad = s.pos > s.end && tk_inf_consumed(s) > s.end;
             int sym = tk_huff_decode(s, tb.lit_count, tb.lit_symbol, tb.lit_fast, TK_INF_LIT_FAST);
-            if (sym < 0) return TK_INF_ERROR;
-            if (sym < 256) {
-                if (op >= cap) return TK_INF_ERROR;
+            if (sym < 256) {                                    // a literal (or no code at all)
+                if (bad | (sym < 0) | (op >= cap)) return TK_INF_ERROR;
                 out[op++] = (uint8_t)sym;
                 continue;
             }
-            if (sym == 256) { s.mode = TK_INF_HEADER; break; }
+            if (sym == 256) {
+                if (bad) return TK_INF_ERROR;
+                s.mode = TK_INF_HEADER;
+                break;
+            }
             sym -= 257;
-            if (sym >= 29) return TK_INF_ERROR;
-            const uint32_t lc = tk_inf_len_code(sym);
+            bad |= sym >= 29;
+            const uint32_t lc = tk_inf_len_code(sym < 29 ? sym : 28);
             const uint32_t len = (lc >> 4) + tk_inf_bits(s, (int)(lc & 15u));          // 0..5 extra bits
             tk_inf_refill(s);                                   // distance code 15 + 13 extra
             const int dsym = tk_huff_decode(s, tb.dist_count, tb.dist_symbol, tb.dist_fast, TK_INF_DIST_FAST);
-            if (dsym < 0 || dsym >= 30) return TK_INF_ERROR;
-            const uint32_t dc = tk_inf_dist_code(dsym);
+            bad |= (dsym < 0) | (dsym >= 30);
+            const uint32_t dc = tk_inf_dist_code((uint32_t)dsym < 30u ? dsym : 0);
             const uint32_t dist = (dc >> 4) + tk_inf_bits(s, (int)(dc & 15u));         // 0..13 extra bits
-            if (s.pos > s.end && tk_inf_consumed(s) > s.end) return TK_INF_ERROR;
-            if (dist > op || len > cap - op) return TK_INF_ERROR;
+            bad |= s.pos > s.end && tk_inf_consumed(s) > s.end;
+            if (bad | (dist > op) | (len > cap - op)) return TK_INF_ERROR;
             if (batch) {
                 tk_inflate_match e;
                 e.dst = op; e.len = len; e.dist = dist; e.reserved = 0;

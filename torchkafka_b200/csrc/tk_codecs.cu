@@ -462,73 +462,76 @@ __device__ __forceinline__ uint32_t snappy_run(cz_window& w, uint32_t lane, uint
         if (p >= end) return TK_STATUS_CORRUPT;
         b = cz_byte(w, p++, lane);
     } while (b & 0x80u);
+    // As for LZ4: the warp parses up to 32 elements (lane e keeps element e: a literal run or a
+    // copy), then copies them side by side (cz_exec_seqs).
     while (p < end) {
-        if (end - p >= 32u) {
-            // fast lane: lane i takes byte p + i with one shuffle; tag = lane 0's byte, a short
-            // literal is the bytes of lanes 1..len, a copy's offset the bytes of lanes 1 (, 2)
-            if (p - w.at > 96u) cz_load(w, p, lane);
-            const uint32_t jj = p - w.at + lane;
-            const uint32_t mine = (__shfl_sync(0xffffffffu, w.word, jj >> 2) >> ((jj & 3u) * 8u)) & 0xFFu;
-            const uint32_t tag = __shfl_sync(0xffffffffu, mine, 0);
-            const uint32_t kind = tag & 3u;
-            if (kind == 0u && (tag >> 2) < 31u) {
-                const uint32_t len = (tag >> 2) + 1u;
-                if (len > cap - op) return TK_STATUS_CORRUPT;
-                if (lane - 1u < len) out[op + lane - 1u] = (uint8_t)mine;
-                op += len;
-                p += 1u + len;
-                continue;
+        uint32_t my_ll = 0, my_lsrc = 0, my_dst = 0, my_ml = 0, my_off = 1;
+        uint32_t n = 0;
+        for (; n < 32u && p < end; ++n) {
+            uint32_t lit = 0, lit_at = 0, len = 0, offset = 1;
+            bool parsed = false;
+            if (end - p >= 32u) {
+                // fast lane: lane i takes byte p + i with one shuffle; tag = lane 0's byte, a copy's
+                // offset the bytes of lanes 1 (, 2)
+                if (p - w.at > 96u) cz_load(w, p, lane);
+                const uint32_t jj = p - w.at + lane;
+                const uint32_t mine = (__shfl_sync(0xffffffffu, w.word, jj >> 2) >> ((jj & 3u) * 8u)) & 0xFFu;
+                const uint32_t tag = __shfl_sync(0xffffffffu, mine, 0);
+                const uint32_t kind = tag & 3u;
+                if (kind == 0u && (tag >> 2) < 60u) {
+                    lit = (tag >> 2) + 1u;
+                    lit_at = p + 1u;
+                    if (lit > end - lit_at) return TK_STATUS_CORRUPT;
+                    p = lit_at + lit;
+                    parsed = true;
+                } else if (kind == 1u || kind == 2u) {
+                    const uint32_t b1 = __shfl_sync(0xffffffffu, mine, 1), b2 = __shfl_sync(0xffffffffu, mine, 2);
+                    len = kind == 1u ? 4u + ((tag >> 2) & 7u) : 1u + (tag >> 2);
+                    offset = kind == 1u ? (((tag >> 5) << 8) | b1) : (b1 | (b2 << 8));
+                    p += kind == 1u ? 2u : 3u;
+                    parsed = true;
+                }
             }
-            if (kind == 1u || kind == 2u) {
-                const uint32_t b1 = __shfl_sync(0xffffffffu, mine, 1), b2 = __shfl_sync(0xffffffffu, mine, 2);
-                const uint32_t len = kind == 1u ? 4u + ((tag >> 2) & 7u) : 1u + (tag >> 2);
-                const uint32_t offset = kind == 1u ? (((tag >> 5) << 8) | b1) : (b1 | (b2 << 8));
-                if (offset == 0 || offset > op || len > cap - op) return TK_STATUS_CORRUPT;
-                cz_match(out, op, offset, len, lane);
-                op += len;
-                p += kind == 1u ? 2u : 3u;
-                continue;
+            if (!parsed) {
+                const uint32_t tag = cz_byte(w, p++, lane);
+                if ((tag & 3u) == 0u) {
+                    lit = tag >> 2;
+                    if (lit >= 60u) {
+                        const uint32_t nb = lit - 59u;
+                        if (end - p < nb) return TK_STATUS_CORRUPT;
+                        lit = 0;
+                        for (uint32_t k = 0; k < nb; ++k) lit |= cz_byte(w, p + k, lane) << (8u * k);
+                        p += nb;
+                    }
+                    if (lit >= 0x7FFFFFFFu) return TK_STATUS_CORRUPT;
+                    lit += 1u;
+                    if (lit > end - p) return TK_STATUS_CORRUPT;
+                    lit_at = p;
+                    p += lit;
+                } else if ((tag & 3u) == 1u) {
+                    if (p >= end) return TK_STATUS_CORRUPT;
+                    len = 4u + ((tag >> 2) & 7u);
+                    offset = ((tag >> 5) << 8) | cz_byte(w, p, lane);
+                    p += 1;
+                } else if ((tag & 3u) == 2u) {
+                    if (end - p < 2u) return TK_STATUS_CORRUPT;
+                    len = 1u + (tag >> 2);
+                    offset = cz_byte(w, p, lane) | (cz_byte(w, p + 1, lane) << 8);
+                    p += 2;
+                } else {
+                    if (end - p < 4u) return TK_STATUS_CORRUPT;
+                    len = 1u + (tag >> 2);
+                    offset = cz_byte(w, p, lane) | (cz_byte(w, p + 1, lane) << 8) | (cz_byte(w, p + 2, lane) << 16) |
+                             (cz_byte(w, p + 3, lane) << 24);
+                    p += 4;
+                }
             }
+            if (lit > cap - op) return TK_STATUS_CORRUPT;
+            if (len && (offset == 0 || offset > op || len > cap - op)) return TK_STATUS_CORRUPT;
+            if (lane == n) { my_ll = lit; my_lsrc = lit_at; my_dst = op; my_ml = len; my_off = offset; }
+            op += lit + len;
         }
-        const uint32_t tag = cz_byte(w, p++, lane);
-        if ((tag & 3u) == 0u) {
-            uint32_t len = tag >> 2;
-            if (len >= 60u) {
-                const uint32_t nb = len - 59u;
-                if (end - p < nb) return TK_STATUS_CORRUPT;
-                len = 0;
-                for (uint32_t k = 0; k < nb; ++k) len |= cz_byte(w, p + k, lane) << (8u * k);
-                p += nb;
-            }
-            if (len >= 0x7FFFFFFFu) return TK_STATUS_CORRUPT;
-            len += 1u;
-            if (len > end - p || len > cap - op) return TK_STATUS_CORRUPT;
-            cz_literals(w, lane, p, len, out, op);
-            op += len;
-            p += len;
-        } else {
-            uint32_t len, offset;
-            if ((tag & 3u) == 1u) {
-                if (p >= end) return TK_STATUS_CORRUPT;
-                len = 4u + ((tag >> 2) & 7u);
-                offset = ((tag >> 5) << 8) | cz_byte(w, p, lane);
-                p += 1;
-            } else if ((tag & 3u) == 2u) {
-                if (end - p < 2u) return TK_STATUS_CORRUPT;
-                len = 1u + (tag >> 2);
-                offset = cz_byte(w, p, lane) | (cz_byte(w, p + 1, lane) << 8);
-                p += 2;
-            } else {
-                if (end - p < 4u) return TK_STATUS_CORRUPT;
-                len = 1u + (tag >> 2);
-                offset = cz_byte(w, p, lane) | (cz_byte(w, p + 1, lane) << 8) | (cz_byte(w, p + 2, lane) << 16) |
-                         (cz_byte(w, p + 3, lane) << 24);
-                p += 4;
-            }
-            if (offset == 0 || offset > op || len > cap - op) return TK_STATUS_CORRUPT;
-            cz_match(out, op, offset, len, lane);
-            op += len;
-        }
+        cz_exec_seqs(w.raw, out, lane, my_ll, my_lsrc, my_dst, my_ml, my_off);
     }
     return TK_STATUS_OK;
 }

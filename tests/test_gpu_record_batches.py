@@ -225,11 +225,13 @@ def test_slot_too_small_is_reported():
 
 
 # ---------------------------------------------------------------- LZ4-compressed batches (§8f-2)
-@pytest.mark.parametrize("codec", [3, "lz4i", "lz4ic", 2, "snappy_raw", 1, "gzipx", "gzip0", 4, "zstds", "zstd19"])
+@pytest.mark.parametrize("codec", [3, "lz4i", "lz4ic", "lz4if", 2, "snappy_raw", 1, "gzipx", "gzip0", 4, "zstds", "zstd19"])
 @pytest.mark.parametrize("cfg,n,batch_bytes", [(2, 3000, 16384), (2, 3000, 200000), (3, 600, 65536), (5, 20000, 16384)])
 def test_compressed_batches_match_the_oracle(cfg, n, batch_bytes, codec):
     """LZ4 frames with dependent blocks (liblz4's default), with independent blocks and checksums
-    (Kafka's Java client), snappy in xerial framing and raw.  cfg2/cfg3: text (matches; several
+    (Kafka's Java client), with blocks that end before they are full ("lz4if": the blocks of a frame
+    are placed by the frame's maximal block size and moved together afterwards), snappy in xerial
+    framing and raw.  cfg2/cfg3: text (matches; several
     blocks / chunks per batch with batch_bytes 200000); cfg5: random bytes (stored blocks, tiny
     matches).  gzip: one member per batch, dynamic and fixed Huffman blocks, with the optional
     header fields ("gzipx"), stored blocks only ("gzip0").  zstd: frames without a content size

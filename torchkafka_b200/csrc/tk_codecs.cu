@@ -105,11 +105,16 @@ static uint32_t lz4_units(const uint8_t* raw, uint32_t p, uint32_t end, unit_sin
         p += size + (block_checksum ? 4u : 0u);
         if (p > end) return TK_STATUS_CORRUPT;
     }
-    if (!sink.full && sink.n == first_unit + 1u && (sink.units[first_unit].kind & 0xFFu) == RB_UNIT_LZ4_BLOCK) {
-        tk_rb_unit& u = sink.units[first_unit];                               // the frame's only block
-        u.kind |= RB_UNIT_BOUND;
-        u.unc_len = (uint32_t)std::min<uint64_t>(block_max, 255ull * u.src_len);
-    }
+    // Every compressed block is placed by its bound, the frame's maximal block size: writers fill
+    // every block but the last (Kafka's KafkaLZ4BlockOutputStream, LZ4F_compressUpdate), so the blocks
+    // land back to back; k_unit_close moves them together where one was shorter.
+    if (!sink.full)
+        for (uint32_t i = first_unit; i < sink.n; ++i) {
+            tk_rb_unit& u = sink.units[i];
+            if ((u.kind & 0xFFu) != RB_UNIT_LZ4_BLOCK) continue;
+            u.kind |= RB_UNIT_BOUND;
+            u.unc_len = (uint32_t)std::min<uint64_t>(block_max, 255ull * u.src_len);
+        }
     return p + (content_checksum ? 4u : 0u) == end ? TK_STATUS_OK : TK_STATUS_CORRUPT;
 }
 
@@ -661,13 +666,51 @@ __global__ void __launch_bounds__(128) k_unit_decode(const rb_args a) {
             else if (kind == RB_UNIT_LZ4_CHAIN) st = lz4_chain_run<true>(w, lane, u.src, u.src + u.src_len, u.kind, out, u.unc_len, op);
             else st = snappy_run(w, lane, u.src, u.src + u.src_len, out, u.unc_len, op);
         }
-        if (u.kind & RB_UNIT_BOUND) {                       // placed by its upper bound: the records end here
-            if (!st && lane == 0) a.batches[u.batch].rec_end = a.batches[u.batch].rec_start + op;
+        if (u.kind & RB_UNIT_BOUND) {                       // placed by its upper bound
+            if (!st && lane == 0) {
+                // the batch's only unit: the records end here; one of several: k_unit_close adds them up
+                if (a.batches[u.batch].unit_count == 1u) a.batches[u.batch].rec_end = a.batches[u.batch].rec_start + op;
+                else a.units[i].unc_len = op;
+            }
         } else if (!st && op != u.unc_len) {
             st = TK_STATUS_CORRUPT;
         }
         // (k_rb_check runs behind this kernel and turns the status into the batch's error entry)
         if (st && lane == 0) a.batches[u.batch].status = TK_STATUS_CORRUPT;
+    }
+}
+
+// Batches of several units placed by their bounds (LZ4 frames of several blocks): the units decoded
+// to their real sizes (k_unit_decode left them in unc_len); where one was shorter than its bound
+// the units behind it move down (destination below source: chunks of 32 x 16 bytes, loaded before
+// they are stored), and the batch's record range ends where the last one ends.  Warp per batch.
+__global__ void __launch_bounds__(128) k_unit_close(const rb_args a) {
+    const uint32_t lane = threadIdx.x & 31;
+    const uint32_t warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, nwarps = (gridDim.x * blockDim.x) >> 5;
+    for (uint32_t i = warp; i < a.n_batches; i += nwarps) {
+        const tk_rb_batch b = a.batches[i];
+        if (b.status || b.unit_count < 2u) continue;
+        bool bounded = false;                               // (a stored block among them has its exact size)
+        for (uint32_t k = 0; k < b.unit_count; ++k) bounded |= (a.units[b.unit_first + k].kind & RB_UNIT_BOUND) != 0;
+        if (!bounded) continue;
+        uint32_t pos = b.rec_start;
+        for (uint32_t k = 0; k < b.unit_count; ++k) {
+            const tk_rb_unit u = a.units[b.unit_first + k];
+            if (u.out != pos) {
+                for (uint32_t base = 0; base < u.unc_len; base += 32u * 16u) {
+                    uint8_t v[16];
+                    const uint32_t at = base + lane * 16u;
+#pragma unroll
+                    for (int j = 0; j < 16; ++j) v[j] = at + j < u.unc_len ? a.raw2[u.out + at + j] : (uint8_t)0;
+                    __syncwarp();
+#pragma unroll
+                    for (int j = 0; j < 16; ++j) if (at + j < u.unc_len) a.raw2[pos + at + j] = v[j];
+                    __syncwarp();
+                }
+            }
+            pos += u.unc_len;
+        }
+        if (lane == 0) a.batches[i].rec_end = pos;
     }
 }
 
@@ -880,13 +923,13 @@ static uint32_t serial_grid(K kernel, uint32_t* cache) {
 
 int tk_codec_launch(const rb_args& a, const tk_rb_unit* h_units, cudaStream_t stream) {
     // which kernels this slot needs
-    uint32_t lz_unsized = 0, zs_unsized = 0, warp_units = 0, deflate_units = 0, zstd_units = 0;
+    uint32_t lz_unsized = 0, zs_unsized = 0, warp_units = 0, deflate_units = 0, zstd_units = 0, lz_bound = 0;
     for (uint32_t i = 0; i < a.n_units; ++i) {
         const uint32_t kind = h_units[i].kind & 0xFFu;
         const bool sized = h_units[i].kind & (RB_UNIT_SIZED | RB_UNIT_BOUND);
         if (kind == RB_UNIT_ZSTD) { ++zstd_units; if (!sized) ++zs_unsized; }
         else if (kind >= RB_UNIT_DEFLATE) ++deflate_units;
-        else { ++warp_units; if (!sized) ++lz_unsized; }
+        else { ++warp_units; if (!sized) ++lz_unsized; if (h_units[i].kind & RB_UNIT_BOUND) ++lz_bound; }
     }
     if (lz_unsized) k_unit_size<<<min((a.n_units + 7) / 8, 148u * 8u), 256, 0, stream>>>(a);
     static uint32_t g_size = 0, g_inflate = 0, g_zstd = 0;
@@ -896,6 +939,8 @@ int tk_codec_launch(const rb_args& a, const tk_rb_unit* h_units, cudaStream_t st
     // (also sets the empty record ranges of compressed batches without a single block)
     k_unit_place<<<1, 1024, 0, stream>>>(a);
     if (warp_units) k_unit_decode<<<min((a.n_units + 3) / 4, 148u * 16u), 128, 0, stream>>>(a);
+    // (batches of one bounded unit were closed by the decode kernel itself)
+    if (lz_bound) k_unit_close<<<min((a.n_batches + 3) / 4, 148u * 8u), 128, 0, stream>>>(a);
     if (deflate_units)
         k_unit_decode_serial<false><<<min(blocks_wanted, serial_grid(k_unit_decode_serial<false>, &g_inflate)), 32 * SERIAL_WARPS, 0, stream>>>(a);
     if (zstd_units)

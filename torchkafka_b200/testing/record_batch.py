@@ -78,9 +78,11 @@ def lz4_frame(data: bytes) -> bytes:
 
 
 def lz4_frame_independent(data: bytes, block_bytes: int = 65536, block_checksum: bool = False,
-                          content_checksum: bool = False) -> bytes:
+                          content_checksum: bool = False, short_blocks: Sequence[int] = ()) -> bytes:
     """LZ4 frame with independent blocks, the way Kafka's Java client writes it
-    (KafkaLZ4BlockOutputStream: FLG = version 01 | block independence, BD = 64 KiB)."""
+    (KafkaLZ4BlockOutputStream: FLG = version 01 | block independence, BD = 64 KiB).
+    `short_blocks`: sizes of leading blocks that end before they are full (a writer that flushes;
+    the format allows any block up to the maximum)."""
     import pyarrow as pa
     import xxhash
     raw = pa.Codec("lz4_raw")
@@ -88,8 +90,14 @@ def lz4_frame_independent(data: bytes, block_bytes: int = 65536, block_checksum:
     bd = {65536: 0x40, 262144: 0x50, 1 << 20: 0x60, 4 << 20: 0x70}[block_bytes]
     head = bytes([flg, bd])
     out = bytearray(b"\x04\x22\x4d\x18" + head + bytes([(xxhash.xxh32(head, seed=0).intdigest() >> 8) & 0xFF]))
-    for k in range(0, len(data), block_bytes):
-        chunk = data[k:k + block_bytes]
+    cuts = [0]
+    for n in short_blocks:
+        if cuts[-1] + n < len(data):
+            cuts.append(cuts[-1] + min(int(n), block_bytes))
+    while cuts[-1] < len(data):
+        cuts.append(min(cuts[-1] + block_bytes, len(data)))
+    for a, b in zip(cuts, cuts[1:]):
+        chunk = data[a:b]
         z = raw.compress(chunk, asbytes=True)
         if len(z) >= len(chunk):                               # stored block
             out += struct.pack("<I", len(chunk) | 0x80000000) + chunk
@@ -164,6 +172,7 @@ CODECS = {
     "gzipx": (1, lambda d: gzip_member(d, 9, name=b"records.bin", extra=b"\x01\x02\x03", comment=b"c", header_crc=True)),
     3: (3, lz4_frame), "lz4": (3, lz4_frame), "lz4i": (3, lz4_frame_independent),
     "lz4ic": (3, lambda d: lz4_frame_independent(d, block_checksum=True, content_checksum=True)),
+    "lz4if": (3, lambda d: lz4_frame_independent(d, short_blocks=(20000, 65536, 7))),
     2: (2, snappy_xerial), "snappy": (2, snappy_xerial), "snappy_raw": (2, snappy_raw),
 }
 
@@ -172,7 +181,7 @@ def encode_batch(base_offset: int, values: Sequence[Optional[bytes]], attributes
                  offset_deltas: Optional[Sequence[int]] = None, keys: Optional[Sequence] = None,
                  headers: Optional[Sequence] = None, crc: Optional[int] = None, codec: int = 0) -> bytes:
     """One RecordBatch v2.  `offset_deltas` default to 0, 1, 2, ... (a compacted topic has gaps).
-    `codec` (a key of CODECS: 3 / "lz4", "lz4i", "lz4ic", 2 / "snappy", "snappy_raw", 1 / "gzip", "gzip0",
+    `codec` (a key of CODECS: 3 / "lz4", "lz4i", "lz4ic", "lz4if", 2 / "snappy", "snappy_raw", 1 / "gzip", "gzip0",
     "gzipx", 4 / "zstd", "zstds", "zstd19") compresses the
     records and sets the attribute bits."""
     n = len(values)

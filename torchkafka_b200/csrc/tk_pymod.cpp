@@ -144,13 +144,21 @@ static inline bool long_to_i64_nogil(PyObject* o, int64_t* out) {
 
 // returns the number of records consumed from items[first..n); *stopped is set when the sink is
 // full (records / bytes) and *bail when a record needs the general path
+#ifndef PF_FAR
+#define PF_FAR 32
+#define PF_NEAR 16
+#endif
 static Py_ssize_t harvest_nogil(Sink& k, PyObject** items, Py_ssize_t n, Py_ssize_t vi, Py_ssize_t oi,
                                 bool* bail) {
     Py_ssize_t i = 0;
     for (; i < n && k.taken < k.max_records; ++i) {
-        if (i + 16 < n) __builtin_prefetch(items[i + 16]);
-        if (i + 8 < n) {
-            PyObject* r8 = items[i + 8];
+        if (i + PF_FAR < n) {
+            const char* far = reinterpret_cast<const char*>(items[i + PF_FAR]);
+            __builtin_prefetch(far);
+            __builtin_prefetch(far + 64);          // ob_item[vi] of a 12-field record lies in the tuple's second line
+        }
+        if (i + PF_NEAR < n) {
+            PyObject* r8 = items[i + PF_NEAR];
             if (PyType_HasFeature(Py_TYPE(r8), Py_TPFLAGS_TUPLE_SUBCLASS) && Py_SIZE(r8) > vi && Py_SIZE(r8) > oi) {
                 __builtin_prefetch(reinterpret_cast<PyTupleObject*>(r8)->ob_item[vi]);
                 __builtin_prefetch(reinterpret_cast<PyTupleObject*>(r8)->ob_item[oi]);

@@ -11,6 +11,12 @@
 #include "../../torchkafka_b200/csrc/tk_inflate.cuh"
 #include "../../torchkafka_b200/csrc/tk_zstd.cuh"
 
+// word source of the fast lanes over a host buffer
+struct HostWords {
+    const uint8_t* p;
+    uint32_t word(uint32_t a, int k) const { uint32_t v; memcpy(&v, p + a + 4 * k, 4); return v; }
+};
+
 struct HostReader {
     const uint8_t* p;
     uint32_t end;
@@ -121,9 +127,47 @@ extern "C" int tk_host_strtod_many(const uint8_t* buf, const uint32_t* starts, u
     return 0;
 }
 
-// One JSON object with named numeric fields (tk_json_object.cuh): row[f] per field, status.
+// One JSON object with named numeric fields: row[f] per field, status -- as the device decodes it:
+// the fast lane (tk_object_fast.cuh) first, the sequential scanner (tk_json_object.cuh) for what it
+// does not take.  *fast (optional) = 1 if the fast lane decoded the record.
+#include "../../torchkafka_b200/csrc/tk_object_fast.cuh"
+#include <vector>
+template <int KIND>
+static int decode_object(const uint8_t* buf, uint32_t len, const tk_obj_fields& ft, void* row, int* fast) {
+    typedef typename tk_elem<KIND>::type T;
+    static tk_fl_tables tb;
+    static bool ready = false;
+    if (!ready) { tk_fl_tables_fill(tb, 0, 1); ready = true; }
+    // the record with bytes in front of it and behind it, as in the device's window
+    std::vector<uint8_t> pad(32 + (size_t)len + 64, 0);
+    memcpy(pad.data() + 32, buf, len);
+    HostReader rd{pad.data(), 32 + len};
+    HostWords src{pad.data()};
+    if (tk_json_object_fast<KIND>(src, rd, 0u, 32u, 32u + len, ft, tb, (T*)row)) {
+        if (fast) *fast = 1;
+        return TK_OK;
+    }
+    if (fast) *fast = 0;
+    return tk_json_object_record<KIND>(rd, 32, ft, (T*)row);
+}
+extern "C" int tk_host_decode_object_ex(const uint8_t* buf, uint32_t len, int kind, const uint8_t* names,
+                                        const uint32_t* name_off, uint32_t n_fields, void* row, int* fast) {
+    tk_obj_fields ft{names, name_off, n_fields};
+    switch (kind) {
+        case TK_F32: return decode_object<TK_F32>(buf, len, ft, row, fast);
+        case TK_F64: return decode_object<TK_F64>(buf, len, ft, row, fast);
+        case TK_I32: return decode_object<TK_I32>(buf, len, ft, row, fast);
+        case TK_I64: return decode_object<TK_I64>(buf, len, ft, row, fast);
+    }
+    return -1;
+}
 extern "C" int tk_host_decode_object(const uint8_t* buf, uint32_t len, int kind, const uint8_t* names,
                                      const uint32_t* name_off, uint32_t n_fields, void* row) {
+    return tk_host_decode_object_ex(buf, len, kind, names, name_off, n_fields, row, nullptr);
+}
+// The sequential scanner alone (the fast lane's results are compared with it).
+extern "C" int tk_host_decode_object_scanner(const uint8_t* buf, uint32_t len, int kind, const uint8_t* names,
+                                             const uint32_t* name_off, uint32_t n_fields, void* row) {
     HostReader rd{buf, len};
     tk_obj_fields ft{names, name_off, n_fields};
     switch (kind) {
@@ -344,10 +388,6 @@ extern "C" int tk_host_decode_nested_flat(const uint8_t* buf, uint32_t len, int 
 // buffer.  Returns 1 and the value when the lane accepts the literal, 0 when it leaves it to the
 // scalar grammar.
 #include "../../torchkafka_b200/csrc/tk_fastlane.cuh"
-struct HostWords {
-    const uint8_t* p;
-    uint32_t word(uint32_t a, int k) const { uint32_t v; memcpy(&v, p + a + 4 * k, 4); return v; }
-};
 extern "C" int tk_host_fastlane(const uint8_t* buf, uint32_t pos, uint32_t stop, int kind, void* out) {
     static tk_fl_tables tb;
     static bool ready = false;

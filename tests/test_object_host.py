@@ -287,3 +287,89 @@ def test_nested_arrays_random_records(lib):
             cut = rng.randrange(len(payload) + 1)
             payload = payload[:cut] + rng.choice([b"", b",", b"]", b"[", b"x", b"1"]) + payload[cut + rng.randint(0, 1):]
         check_nested(lib, payload, shape, kinds=(it % 4,))
+
+
+# ---------------------------------------------------------------- the fast lane (tk_object_fast.cuh)
+def decode_ex(lib, payload: bytes, fields, kind: int):
+    blob, off = field_table(fields)
+    row = np.zeros(max(len(fields), 1), DTYPES[kind][1])
+    fast = ctypes.c_int(-1)
+    st = lib.tk_host_decode_object_ex(payload, len(payload), kind, blob, off.ctypes.data_as(ctypes.c_void_p),
+                                      len(fields), row.ctypes.data_as(ctypes.c_void_p), ctypes.byref(fast))
+    row2 = np.zeros(max(len(fields), 1), DTYPES[kind][1])
+    st2 = lib.tk_host_decode_object_scanner(payload, len(payload), kind, blob, off.ctypes.data_as(ctypes.c_void_p),
+                                            len(fields), row2.ctypes.data_as(ctypes.c_void_p))
+    return st, row[:len(fields)], fast.value, st2, row2[:len(fields)]
+
+
+def dumps_record(rng, fields, separators):
+    d = {}
+    names = list(fields)
+    if rng.random() < 0.2:
+        rng.shuffle(names)
+    extras = ["id", "note", "ts", "k_%d" % rng.randrange(5)]
+    for name in names:
+        if rng.random() < 0.15:
+            e = rng.choice(extras)
+            d[e] = rng.choice([rng.randrange(10 ** 6), rng.uniform(-5, 5), "abc", "a b,c}d", ""])
+        k = rng.randrange(6)
+        d[name] = (rng.uniform(-1e3, 1e3) if k < 3 else rng.randrange(-10 ** 7, 10 ** 7) if k == 3
+                   else float(rng.randrange(-50, 50)) if k == 4 else 0.1 + rng.random() * 10 ** rng.randrange(0, 9))
+    return json.dumps(d, separators=separators).encode()
+
+
+@pytest.mark.parametrize("separators", [None, (",", ":")])
+def test_fast_lane_takes_what_json_dumps_writes_and_agrees_with_the_scanner(lib, separators):
+    rng = random.Random(9)
+    fields = ("x", "y", "label", "weight", "a1", "velocity_mps", "q", "z")
+    taken = total = 0
+    for it in range(4000):
+        payload = dumps_record(rng, fields, separators)
+        kind = it % 2                                     # float32 / float64 (ints: next test)
+        st, row, fast, st2, row2 = decode_ex(lib, payload, fields, kind)
+        assert st == st2 == 0, payload
+        bits = DTYPES[kind][2]
+        assert np.array_equal(row.view(bits), row2.view(bits)), (payload, row, row2)
+        want = reference(payload, fields, kind)
+        assert want is not None and np.array_equal(row.view(bits), want.numpy().view(bits)), payload
+        taken += fast
+        total += 1
+    assert taken >= 0.97 * total, (taken, total)
+
+
+def test_fast_lane_never_disagrees_on_variants_and_damage(lib):
+    """Records around the edge of what the fast lane takes: the combined decoder (fast lane, else
+    scanner) must answer as the scanner alone and as CPython do."""
+    rng = random.Random(10)
+    fields = ("x", "y", "n")
+    base = [b'{"x": 1.5, "y": -2.25, "n": 7}', b'{"x":1.5,"y":-2.25,"n":7}', b'{"n": 7, "y": 2, "x": 0.5, "x": 9.75}',
+            b'{"x": 1.5, "s": "plain string", "y": 2, "n": 3}', b'{"x": 1.5, "s": "esc \\" aped", "y": 2, "n": 3}',
+            b'{"x": 1.5, "s": "h\xc3\xa9", "y": 2, "n": 3}', b'{"x": 1.5, "y": 2, "n": 3} ', b' {"x": 1.5, "y": 2, "n": 3}',
+            b'{"x": 1.5,  "y": 2, "n": 3}', b'{"x" : 1.5, "y": 2, "n": 3}', b'{"x": 1.5, "y": 2, "n": true}',
+            b'{"x": 1.5, "y": 2, "n": null}', b'{"x": 1.5, "y": [2], "n": 3}', b'{"x": 1.5, "y": 2}', b'{"x": 1e5, "y": 2, "n": 3}',
+            b'{"x": 01.5, "y": 2, "n": 3}', b'{"x": -0, "y": -0.0, "n": 0}', b'{"x": 1.5, "y": 2, "n": 3, "long_member_name_of_30_bytes__": 1}',
+            b'{"x": 1.5, "y": 2, "n": 3, "s": "' + b"v" * 40 + b'"}', b'{"x": 12345678901234567890, "y": 2, "n": 3}',
+            b'{"x": 0.1234567890123456789012, "y": 2, "n": 3}', b'{"x": 1.5, "y": 2, "n": 3}x', b'{"x": 1.5, "y": 2, "n": 3',
+            b'{"x": 1.5, "y": 2, "n": 3}}', b'{"x": 1.5, "y": 2,, "n": 3}', b'{"x": 1.5 "y": 2, "n": 3}', b'{"x": "1.5", "y": 2, "n": 3}',
+            b'{"": 1, "x": 1.5, "y": 2, "n": 3}', b'{"x": 99999999, "y": 100000000, "n": 3}']
+    for payload in base:
+        for kind in range(4):
+            st, row, fast, st2, row2 = decode_ex(lib, payload, fields, kind)
+            assert st == st2, (payload, kind, st, st2, fast)
+            if st == 0:
+                bits = DTYPES[kind][2]
+                assert np.array_equal(row.view(bits), row2.view(bits)), (payload, kind)
+        check(lib, payload, fields)
+    for it in range(6000):
+        payload = bytearray(dumps_record(rng, fields, rng.choice([None, (",", ":")])))
+        for _ in range(rng.randint(1, 2)):
+            cut = rng.randrange(len(payload) + 1)
+            payload[cut:cut + rng.randint(0, 1)] = rng.choice([b"", b",", b"}", b"{", b'"', b"\\", b":", b"x", b"\xff", b"\x00", b" ",
+                                                               b".", b"-", b"e", b"1", b"\x7f", b"/"])
+        payload = bytes(payload)
+        kind = it % 4
+        st, row, fast, st2, row2 = decode_ex(lib, payload, fields, kind)
+        assert st == st2, (payload, kind, st, st2, fast)
+        if st == 0:
+            bits = DTYPES[kind][2]
+            assert np.array_equal(row.view(bits), row2.view(bits)), (payload, kind)

@@ -17,21 +17,33 @@
 //                     parallelism is across records.  A warp takes the next run of consecutive
 //                     records that fits its shared-memory window (they lie back to back in the
 //                     slot's byte buffer), brings the run in with coalesced 16-byte loads, and
-//                     every lane scans its own record out of shared memory and writes its row.
+//                     every lane decodes its own record out of shared memory and writes its row:
+//                     first with the fast lane of tk_object_fast.cuh (flat objects as json.dumps
+//                     writes them: member by member in straight-line code, so the lanes stay in
+//                     step), else with the sequential scanner.
 //                     Records larger than the window are left to a second loop, one record per
 //                     warp, scanned from global memory by lane 0 (through L1).
 #include "tk_swar.cuh"
 #include "tk_json_object.cuh"
+#include "tk_object_fast.cuh"
 
 #define OBJ_THREADS 128
 #define OBJ_WARPS (OBJ_THREADS / 32)
-#define OBJ_WINDOW 6144u                                   // bytes of shared memory per warp
+#define OBJ_WINDOW 8192u                                   // bytes of shared memory per warp
 #define OBJ_TABLE_OFFSETS ((TK_OBJ_MAX_FIELDS + 1) * 4)    // device table: offsets, then names
 
 struct ObjSharedReader {
     const uint8_t* win;
     uint32_t base, end;
     __device__ __forceinline__ int operator()(uint32_t pos) const { return pos < end ? (int)win[pos - base] : -1; }
+};
+// word source of the fast lane (tk_object_fast.cuh) over the same window
+struct ObjSharedWords {
+    const uint8_t* win;
+    uint32_t base;
+    __device__ __forceinline__ uint32_t word(uint32_t a, int k) const {
+        return reinterpret_cast<const uint32_t*>(win + (a - base))[k];
+    }
 };
 struct ObjGlobalReader {
     const uint8_t* bytes;
@@ -63,7 +75,10 @@ __device__ __forceinline__ int obj_parse_record(const obj_args& a, const R& rd, 
 template <int KIND>
 __global__ void __launch_bounds__(OBJ_THREADS) k_json_object(const obj_args a) {
     typedef typename tk_elem<KIND>::type T;
-    __shared__ __align__(16) uint8_t win[OBJ_WARPS][OBJ_WINDOW];
+    // (slack behind the window: the fast lane's word reads may run 28 bytes past a record's end)
+    __shared__ __align__(16) uint8_t win[OBJ_WARPS][OBJ_WINDOW + 64];
+    __shared__ tk_fl_tables fl;
+    tk_fl_tables_fill(fl, threadIdx.x, OBJ_THREADS);
     __shared__ uint32_t s_off[TK_OBJ_MAX_FIELDS + 1];
     __shared__ uint8_t s_names[TK_MAX_OBJECT_NAME_BYTES];
     // the field table was written by tk_ctx_set_object_fields (synchronous): not data of the chain
@@ -91,7 +106,10 @@ __global__ void __launch_bounds__(OBJ_THREADS) k_json_object(const obj_args a) {
                 my_end = a.recs[i + 1].start;
                 kidx = a.rec_kidx[i];
             }
-            const uint32_t base = __shfl_sync(0xffffffffu, my_start, 0) & ~15u;
+            // (32 bytes in front of the first record come along: the fast lane reads 20 bytes in
+            // front of a number's end)
+            const uint32_t first16 = __shfl_sync(0xffffffffu, my_start, 0) & ~15u;
+            const uint32_t base = first16 >= 32u ? first16 - 32u : 0u;
             const uint32_t fits = __ballot_sync(0xffffffffu, have && my_end - base <= OBJ_WINDOW);
             const uint32_t k = fits == 0xffffffffu ? 32u : (uint32_t)__ffs((int)~fits) - 1u;   // leading records that fit
             int st = TK_OK;
@@ -109,7 +127,8 @@ __global__ void __launch_bounds__(OBJ_THREADS) k_json_object(const obj_args a) {
                 if (mine && kidx >= 0) {
                     const ObjSharedReader rd = {w, base, my_end};
                     T* row = reinterpret_cast<T*>((uint8_t*)a.values.base + ((uint64_t)B + (uint32_t)kidx) * a.values.row_bytes);
-                    st = obj_parse_record<KIND>(a, rd, my_start, ft, row);
+                    if (a.ndim || !tk_json_object_fast<KIND>(ObjSharedWords{w, base}, rd, base, my_start, my_end, ft, fl, row))
+                        st = obj_parse_record<KIND>(a, rd, my_start, ft, row);
                 }
                 __syncwarp();                               // the window is reused by the next run
                 g += k;

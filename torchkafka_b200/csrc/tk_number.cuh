@@ -198,8 +198,7 @@ TK_HD bool tk_is_digit(int c) { return (unsigned)(c - '0') <= 9u; }
 TK_HD bool tk_is_ws(int c) { return c == ' ' || c == '\t' || c == '\n' || c == '\r'; }
 // Characters that can belong to a token (number-like run).  Deliberately a cheap superset of
 // the characters of JSON numbers / NaN / Infinity / true / false: 0x2B..0x7F without ',' and
-// without the four codes with (c | 6) == 0x5F ('[', ']', 'Y', '_').  The CUDA kernels classify
-// four bytes at a time with the same rule (tokclass4 in tk_json_kernels.cu).
+// without the four codes with (c | 6) == 0x5F ('[', ']', 'Y', '_').
 TK_HD bool tk_is_numclass(int c) {
     return c >= 0x2B && c <= 0x7F && c != ',' && (c | 6) != 0x5F;
 }

@@ -182,6 +182,15 @@ int tk_json_ingest(tk_ctx* ctx, int slot, int dtype, uint32_t max_len, uint32_t 
                    const tk_plane_t* lengths, const tk_plane_t* mask, void* stream);
 int tk_ctx_set_json_fused(tk_ctx* ctx, int enabled);
 
+/* Variant of the parse kernel of tk_json_decode (the per-element part of README.md:74,
+ * json.loads, and README.md:41-43, torch.tensor).  0 (default; TK_JSON_WIDE=1 in the environment
+ * changes it): the leanest element loop -- number literals of at most 20 bytes are decoded inline,
+ * "0.00..." literals of 21 / 22 bytes and literals with an exponent by an out-of-line call.  1: the
+ * 21 / 22-byte literals inline as well: a few percent slower on data without them, faster as soon as
+ * one number in a few hundred is below 0.01.  Results are identical.  The Python engine chooses from a
+ * sample of the payload. */
+int tk_ctx_set_json_wide(tk_ctx* ctx, int enabled);
+
 /* ---- K1c + K3: fixed-layout bytes -> rows (torch.frombuffer + torch.stack) -- */
 int tk_collate_raw(tk_ctx* ctx, int slot, uint64_t record_bytes, const tk_plane_t* out,
                    void* stream);

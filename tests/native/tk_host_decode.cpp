@@ -395,7 +395,18 @@ extern "C" int tk_host_fastlane(const uint8_t* buf, uint32_t pos, uint32_t stop,
     HostWords src{buf};
     uint64_t w;
     uint32_t K, dot, neg;
-    if (!tk_fl_scan(src, pos, stop, tb, &w, &K, &dot, &neg)) return 0;
+    if (!tk_fl_scan(src, pos, stop, tb, &w, &K, &dot, &neg)) {
+        // the kernels' slow branch: the long forms, before the grammar
+        const tk_fl_num num = tk_fl_scan_long(src, pos, stop);
+        if (!num.ok) return 0;
+        switch (kind) {
+            case TK_F32: return tk_fl_value_long<TK_F32>(num, (float*)out) ? 1 : 0;
+            case TK_F64: return tk_fl_value_long<TK_F64>(num, (double*)out) ? 1 : 0;
+            case TK_I32: return tk_fl_value_long<TK_I32>(num, (int32_t*)out) ? 1 : 0;
+            case TK_I64: return tk_fl_value_long<TK_I64>(num, (int64_t*)out) ? 1 : 0;
+        }
+        return -1;
+    }
     switch (kind) {
         case TK_F32: return tk_fl_value<TK_F32>(w, K, dot, neg, tb, (float*)out) ? 1 : 0;
         case TK_F64: return tk_fl_value<TK_F64>(w, K, dot, neg, tb, (double*)out) ? 1 : 0;

@@ -1,7 +1,8 @@
 """The fast lane of the JSON array kernels (csrc/tk_fastlane.cuh), compiled for the host, against
 CPython on the same literals: float(text) for float64, numpy.float32(float(text)) for float32 (the
 reference rounds twice: json.loads, then torch.tensor), int(text) for the integer targets.  The lane
-must accept exactly  [' ']['-'](0|[1-9]d*)['.'d+]  within its digit limits and nothing else; what
+must accept exactly  [' ']['-'](0|[1-9]d*)['.'d+][('e'|'E')['+'|'-']d{1,3}]  within its digit limits and
+nothing else; what
 it does not accept goes to the scalar grammar, which has its own tests.  Runs without a GPU."""
 import ctypes
 import json
@@ -16,7 +17,7 @@ import pytest
 
 HERE = os.path.dirname(os.path.abspath(__file__))
 KINDS = {"f32": (0, np.float32), "f64": (1, np.float64), "i32": (2, np.int32), "i64": (3, np.int64)}
-FORM = re.compile(rb"^ ?(-?)(0|[1-9][0-9]*)(?:\.([0-9]+))?$")
+FORM = re.compile(rb"^ ?(-?)(0|[1-9][0-9]*)(?:\.([0-9]+))?(?:[eE]([+-]?)([0-9]{1,3}))?$")
 
 
 @pytest.fixture(scope="module")
@@ -55,22 +56,32 @@ def run_lane(lib, buf, pos, stop, kind):
 def lane_takes(text: bytes, stop: int, kind: str) -> bool:
     """What the lane is specified to accept (text = the element's bytes, leading space included)."""
     m = FORM.match(text)
-    if not m or stop < 20:
+    if not m or len(text) > 30:
         return False
-    digits = len(m.group(2)) + (len(m.group(3)) if m.group(3) is not None else 0)
-    if m.group(3) is None:
-        return digits <= 8
+    ipart, frac, exp = m.group(2), m.group(3), m.group(5)
+    # the window is anchored at the end of the mantissa
+    mant_end = stop - (len(text) - m.end(3 if frac is not None else 2))
+    if mant_end < 20:
+        return False
+    if frac is None:
+        ok = len(ipart) <= 8
+    else:
+        body = len(ipart) + 1 + len(frac)
+        ok = body <= 20 or (ipart == b"0" and (body == 21 or (body == 22 and frac[:1] == b"0")))
+    if not ok:
+        return False
     if kind in ("i32", "i64"):
-        return False
-    return digits + 1 <= 20
+        return frac is None and exp is None
+    return True
 
 
 def expected(text: bytes, kind: str):
     s = text.decode().strip()
-    if kind == "f64":
-        return np.float64(float(int(s)) if re.fullmatch(r"-?\d+", s) else float(s))
-    if kind == "f32":
-        return np.float32(float(int(s)) if re.fullmatch(r"-?\d+", s) else float(s))
+    with np.errstate(over="ignore"):
+        if kind == "f64":
+            return np.float64(float(int(s)) if re.fullmatch(r"-?\d+", s) else float(s))
+        if kind == "f32":
+            return np.float32(float(int(s)) if re.fullmatch(r"-?\d+", s) else float(s))
     return KINDS[kind][1](int(s))
 
 
@@ -95,11 +106,11 @@ def check(lib, literals, kind, sep=b", ", prefix=b"x" * 24, must_take=None):
 @pytest.mark.parametrize("sep", [b", ", b","])
 def test_what_json_dumps_writes(lib, kind, sep):
     rng = random.Random(11)
-    for scale in (1e3, 1.0, 1e7, 30.0):
-        vals = [rng.uniform(-scale, scale) for _ in range(40000)]
+    for scale in (1e3, 1.0, 1e7, 30.0, 1e-3, 1e-9, 1e18, 1e300):
+        vals = [rng.uniform(-scale, scale) for _ in range(30000)]
         lits = [json.dumps(v).encode() for v in vals]
         for shift in range(4):
-            check(lib, lits, kind, sep=sep, prefix=b"y" * (24 + shift), must_take=0.99)
+            check(lib, lits, kind, sep=sep, prefix=b"y" * (24 + shift), must_take=0.999)
 
 
 @pytest.mark.parametrize("kind", ["f32", "f64", "i32", "i64"])
@@ -155,7 +166,13 @@ def test_everything_else_is_left_to_the_grammar(lib):
     odd = [b".5", b"5.", b"-.5", b"-", b"--1", b"+1", b"1..2", b"1.2.3", b"1e5", b"1.5E-3", b"1.5e+3", b"01", b"00.5",
            b"-01.5", b" 1", b"1 ", b"\t1", b"1.5 ", b"NaN", b"Infinity", b"-Infinity", b"true", b"null", b"\"1\"", b"1/2",
            b"1./5", b"1.\x2f5", b"1:5", b"0x10", b"1_000", b"1.5f", b"12345678901234567890", b"1.2345678901234567890123",
-           b"", b"1,5"[:1] + b"\x00", b"\xff1", b"1\xff", b"1.\xff", b"\x80.5", b"3.1\x1f4", b"3\x1f.14"]
+           b"", b"1,5"[:1] + b"\x00", b"\xff1", b"1\xff", b"1.\xff", b"\x80.5", b"3.1\x1f4", b"3\x1f.14",
+           b"1e", b"1e+", b"1e-", b"e5", b"-e5", b"1.e5", b".5e5", b"1e5.5", b"1e1234", b"1e0005", b"1ee5", b"1e+-5", b"1E5", b"1E+05",
+           b"1e-400", b"1e400", b"-1e400", b"0e0", b"-0e5", b"0.0e-3", b"1.5e300", b"9.999999999999999e22", b"1e23", b"2.5e-324",
+           b"4.9e-324", b"2.2250738585072014e-308", b"1.7976931348623157e+308", b"1.7976931348623159e+308",
+           b"0.000123456789012345", b"0.0001234567890123456", b"0.00012345678901234567", b"0.000123456789012345678",
+           b"0.1234567890123456789", b"0.12345678901234567890", b"0.01234567890123456789", b"1.01234567890123456789",
+           b"-0.00012345678901234567", b"0.00000000000000000001", b"0.00000000000000000000"]
     rng = random.Random(2)
     for _ in range(20000):
         n = rng.randrange(1, 24)

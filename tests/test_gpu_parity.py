@@ -2,6 +2,7 @@
 oracle on identical seeded records.  Bit-exact for every dtype, including float
 (0 ulp: the decimal->binary conversion is correctly rounded like CPython's)."""
 import json
+import random
 
 import numpy as np
 import pytest
@@ -328,6 +329,46 @@ def test_single_pass_kernel_agrees_with_the_three_kernel_chain(case):
     for x, y in zip(ta, tb):
         assert x.shape == y.shape
         assert bit_equal(x[good], y[good])
+
+
+@pytest.mark.parametrize("dist", ["unit", "tiny", "huge", "mixed"])
+@pytest.mark.parametrize("dtype", [torch.float32, torch.float64])
+def test_numbers_of_every_magnitude_and_both_parse_kernel_variants(dist, dtype):
+    """json.dumps writes "0.00123..." (21-22 bytes) below 0.01 and exponents below 1e-4 and from
+    1e16: the parse kernel takes them in its wide variant inline / through the out-of-line long lane
+    (tk_fl_scan_long).  Both variants of the kernel and the engine's own choice must give the
+    oracle's bits."""
+    from torchkafka_b200.engine import SlotEngine
+    rng = random.Random({"unit": 1, "tiny": 2, "huge": 3, "mixed": 4}[dist])
+    draw = {"unit": lambda: rng.uniform(-1, 1), "tiny": lambda: rng.gauss(0, 1e-3),
+            "huge": lambda: rng.uniform(-1, 1) * 10 ** rng.randrange(14, 300),
+            "mixed": lambda: rng.choice([rng.uniform(-1e3, 1e3), rng.gauss(0, 1e-6), rng.randrange(-10 ** 7, 10 ** 7),
+                                         rng.random() * 1e-320, 0.0, -0.0, 1e22, 5e-324])}[dist]
+    vals = [json.dumps([draw() for _ in range(rng.randint(16, 120))]).encode() for _ in range(1500)]
+    sc, B, n = JsonArray(dtype, max_len=128, min_size=20), 64, len(vals)
+    log = RecordLog(vals, (np.arange(n) // 7 % 16).astype(np.int32), np.arange(n) // 16 + (np.arange(n) % 7))
+    outs = []
+    for wide in (False, True, None):
+        eng = SlotEngine(sc, B, slot_bytes=16 << 20, slot_records=n + 8, n_slots=2, device=0, n_partitions=16)
+        if wide is not None:
+            eng.json_wide_fixed = wide
+            eng.set_json_wide(wide)
+        m, nb = eng.fill_packed(0, log.values, log.starts.astype(np.uint32), log.partitions, log.offsets)
+        eng.submit(0, m, nb)
+        out = eng.process(0, m, None, None)
+        res = eng.result(0)
+        assert res.n_errors == 0
+        if wide is None and dist != "mixed":
+            assert eng.json_wide, "small / large magnitudes: the engine must pick the wide kernel"
+        outs.append([t[B:B + res.n_kept].cpu() for t in out.tensors])
+        eng.close()
+    kept = [json.loads(v) for v in vals if v.count(b",") + 1 >= 20]
+    want = torch.zeros((len(kept), 128), dtype=dtype)
+    for i, row in enumerate(kept):
+        want[i, :len(row)] = torch.tensor(row, dtype=dtype)
+    for tensors in outs:
+        assert bit_equal(tensors[0], want)
+        assert tensors[1].tolist() == [len(r) for r in kept]
 
 
 def test_images_table_fallback_when_fma_is_not_exact():

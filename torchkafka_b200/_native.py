@@ -99,6 +99,7 @@ _SIGNATURES = {
     "tk_json_ingest": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_uint32, C.c_uint32, C.c_uint32, C.c_uint32,
                                  _p(TkPlane), _p(TkPlane), _p(TkPlane), C.c_void_p]),
     "tk_ctx_set_json_fused": (C.c_int, [C.c_void_p, C.c_int]),
+    "tk_ctx_set_json_wide": (C.c_int, [C.c_void_p, C.c_int]),
     "tk_collate_raw": (C.c_int, [C.c_void_p, C.c_int, C.c_uint64, _p(TkPlane), C.c_void_p]),
     "tk_collate_field": (C.c_int, [C.c_void_p, C.c_int, C.c_uint64, C.c_uint32, C.c_uint32, _p(TkPlane), C.c_void_p]),
     "tk_ctx_set_object_fields": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint32, C.c_void_p]),

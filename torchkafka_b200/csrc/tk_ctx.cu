@@ -329,6 +329,7 @@ extern "C" int tk_ctx_create(int device, uint64_t slot_bytes, uint32_t slot_reco
     ctx->commit_pitch = (max_batches + 1 + 3) & ~3u;
     ctx->n_partitions = n_partitions;
     { const char* e = getenv("TK_JSON_FUSED"); ctx->json_fused = (e && e[0] == '1') ? 1 : 0; }
+    { const char* e = getenv("TK_JSON_WIDE"); ctx->json_wide = (e && e[0] == '1') ? 1 : 0; }   // (the default; tk_ctx_set_json_wide)
     int rc = create_impl(ctx);
     if (rc) { char keep[1024]; strncpy(keep, g_err, sizeof(keep)); keep[1023] = 0; tk_ctx_destroy(ctx); tk_set_error("%s", keep); return rc; }
     *out = ctx;

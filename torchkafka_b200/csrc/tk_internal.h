@@ -141,6 +141,7 @@ struct tk_ctx {
     size_t    tok_cap;         // entries of the token array (a token needs >= 2 bytes)
     size_t    fz_tiles;        // entries of the fused kernel's tile arrays (0: not allocated)
     int       json_fused;      // 1: tk_process_slot runs JSON arrays through the single-pass kernel (tk_json_fused.cu)
+    int       json_wide;       // 1: k_json_parse with the "0.00..." bodies inline (tk_ctx_set_json_wide)
     uint32_t  batch_size;      // of the last tk_compact
     cudaStream_t copy_stream;
     tk_state* d_state;

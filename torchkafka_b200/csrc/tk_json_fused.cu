@@ -322,8 +322,16 @@ __device__ __forceinline__ void fz_parse_round(const fused_args& a, const tk_fl_
         bool fast = !(last && !(info & FR_TAIL)) && tk_fl_scan(SmemWords{win}, pos, stop, tb, &w, &K, &dot, &neg);
         if (fast) fast = tk_fl_value<KIND>(w, K, dot, neg, tb, &v);
         if (!fast) {
-            WindowReader rd{win, end};
-            st = tk_json_element_flat<KIND>(rd, pos, &v);
+            // the lane's long forms ("0.00…" with 20 digits, exponents), then the grammar
+            bool done = false;
+            if (!(last && !(info & FR_TAIL))) {
+                const tk_fl_num num = tk_fl_scan_long(SmemWords{win}, pos, stop);
+                done = num.ok && tk_fl_value_long<KIND>(num, &v);
+            }
+            if (!done) {
+                WindowReader rd{win, end};
+                st = tk_json_element_flat<KIND>(rd, pos, &v);
+            }
         }
         if (st) { flag_record(a.rec_status, a.res, r0 + k, st); continue; }
         if (STAGE) {

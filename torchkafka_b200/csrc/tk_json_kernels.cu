@@ -299,10 +299,24 @@ __device__ __forceinline__ void json_rows_part(const flat_args& a, uint32_t warp
 // would otherwise sit inside the (unrolled) element loop.
 // (Arguments by value: a reference to the kernel's parameter block would force a copy of it into
 // local memory, and every parameter read of the element loop with it.)
-template <int KIND>
+// (LONG: only the wide variant of the kernel carries the long lane -- what the callee needs in
+// registers the element loop of the caller spills.)
+template <int KIND, bool LONG>
 __device__ __noinline__ int json_element_slow(const uint8_t* bytes, uint32_t end, uint32_t pos, uint32_t e, uint32_t flags,
                                               const tk_nested_shape shape, typename tk_elem<KIND>::type* v) {
     GlobalReader rd{bytes, end};
+    if (LONG && shape.ndim <= 1) {
+        // the fast lane's long forms first ("0.00..." with 20 digits, exponents: tk_fl_scan_long): the
+        // element ends at the next ',' or at the ']' that closes the record
+        uint32_t stop = pos;
+        while (stop < end && stop - pos < 31u && bytes[stop] != ',' && bytes[stop] != ']') ++stop;
+        // (']' must be the record's last byte: what follows it is the grammar's business)
+        if (stop < end && (bytes[stop] == ',' || stop + 1u == end)) {
+            const tk_fl_num num = tk_fl_scan_long(LdgWords{bytes}, pos, stop);
+            if (num.ok && tk_fl_value_long<KIND>(num, v)) return TK_OK;
+        }
+        return tk_json_element_flat<KIND>(rd, pos, v);
+    }
     if (shape.ndim <= 1) return tk_json_element_flat<KIND>(rd, pos, v);
     // nested arrays: the brackets around leaf e follow from e and the shape
     const uint32_t n_open = e ? tk_nested_opens(shape, e) : 0u;                  // (the head took the first leaf's)
@@ -313,7 +327,7 @@ __device__ __noinline__ int json_element_slow(const uint8_t* bytes, uint32_t end
 // One element: token entry tk (.x = byte position, .y = record index with TOK_LAST on the record's
 // last element and TOK_TAIL when the record's final byte is ']'), next_pos = position of the
 // element behind it in the token array.
-template <int KIND>
+template <int KIND, bool WIDE>
 __device__ __forceinline__ void json_parse_one(const flat_args& a, const tk_fl_tables& tb, uint32_t t, uint2 tk,
                                                uint32_t next_pos, typename tk_elem<KIND>::type* values) {
     typedef typename tk_elem<KIND>::type T;
@@ -332,19 +346,24 @@ __device__ __forceinline__ void json_parse_one(const flat_args& a, const tk_fl_t
         const uint32_t e = t - a.rec_tok[rec];
         fast = fast && !((e ? tk_nested_opens(a.shape, e) : 0u) | (flags ? a.shape.ndim : tk_nested_opens(a.shape, e + 1)));
     }
-    fast = fast && tk_fl_scan(LdgWords{a.bytes}, pos, stop, tb, &w, &K, &dot, &neg);
+    fast = fast && tk_fl_scan<WIDE>(LdgWords{a.bytes}, pos, stop, tb, &w, &K, &dot, &neg);
     if (fast) fast = tk_fl_value<KIND>(w, K, dot, neg, tb, &v);
     if (!fast) {
         const uint32_t e = a.shape.ndim > 1 ? t - a.rec_tok[rec] : 0u;
-        const int st = json_element_slow<KIND>(a.bytes, a.recs[rec + 1].start, pos, e, flags, a.shape, &v);
+        const int st = json_element_slow<KIND, WIDE>(a.bytes, a.recs[rec + 1].start, pos, e, flags, a.shape, &v);
         if (st) { flag_record(a.rec_status, a.res, rec, st); return; }
     }
     // (a record with a row has at most max_len elements: longer ones were rejected by the scan)
     if (base != TK_REC_BASE_SKIP) values[base + (long long)t] = v;
 }
 
-// 6 blocks per SM (40 registers): measured best of 4 / 5 / 6 (profiles/r02_parse_variants.md)
-template <int KIND>
+// 6 blocks per SM (40 registers): measured best of 4 / 5 / 6 (profiles/r02_parse_variants.md).
+// Two variants: WIDE = false, the leanest element loop, for data whose numbers the 20-byte lane
+// takes (magnitudes of 0.01 and more: BASELINE's uniform(-1e3, 1e3)); WIDE = true with the "0.00..."
+// bodies inline (3 us slower per 94 MB slot on such data, 15 % faster on uniform(-1, 1) or
+// gauss(0, 1), where one element in a hundred is below 0.01 and would take the out-of-line call,
+// 1.5 x faster on gauss(0, 1e-3)).  tk_ctx_set_json_wide chooses.
+template <int KIND, bool WIDE>
 __global__ void __launch_bounds__(256, 6) k_json_parse(const flat_args a) {
     typedef typename tk_elem<KIND>::type T;
     __shared__ tk_fl_tables tb;
@@ -372,7 +391,7 @@ __global__ void __launch_bounds__(256, 6) k_json_parse(const flat_args a) {
         asm volatile("prefetch.global.L1 [%0];" ::"l"(ahead));
         asm volatile("prefetch.global.L1 [%0];" ::"l"(ahead + 27));
         if (t2 < n_tok) { tk2 = __ldg(a.tok + t2); np2 = __ldg(&a.tok[t2 + 1].x); }
-        json_parse_one<KIND>(a, tb, t, tk, np, values);
+        json_parse_one<KIND, WIDE>(a, tb, t, tk, np, values);
     }
 }
 
@@ -382,8 +401,8 @@ static uint32_t parse_grid(int dtype) {
     const int k = dtype - TK_DTYPE_F32;
     if (!cached[k]) {
         int per_sm = 0, sms = 0, dev = 0;
-        const void* fn = k == 0 ? (const void*)k_json_parse<TK_F32> : k == 1 ? (const void*)k_json_parse<TK_F64>
-                       : k == 2 ? (const void*)k_json_parse<TK_I32> : (const void*)k_json_parse<TK_I64>;
+        const void* fn = k == 0 ? (const void*)k_json_parse<TK_F32, false> : k == 1 ? (const void*)k_json_parse<TK_F64, false>
+                       : k == 2 ? (const void*)k_json_parse<TK_I32, false> : (const void*)k_json_parse<TK_I64, false>;
         if (cudaGetDevice(&dev) != cudaSuccess ||
             cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess ||
             cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, fn, 256, 0) != cudaSuccess || per_sm < 1 || sms < 1) {
@@ -450,11 +469,21 @@ static int json_decode_impl(tk_ctx* ctx, int slot, int dtype, uint32_t max_len, 
     const uint64_t max_tok = (uint64_t)s.n_bytes / 2 + n;
     // (the rows part wants a warp per ~record too: never fewer blocks than records / 8 would use)
     const uint32_t pblocks = (uint32_t)min(max((max_tok + 255) / 256, ((uint64_t)n + 7) / 8), (uint64_t)parse_grid(dtype));
-    switch (dtype) {
-        case TK_DTYPE_F32: TK_LAUNCH_PDL(k_json_parse<TK_F32>, pblocks, 256, st, a); break;
-        case TK_DTYPE_F64: TK_LAUNCH_PDL(k_json_parse<TK_F64>, pblocks, 256, st, a); break;
-        case TK_DTYPE_I32: TK_LAUNCH_PDL(k_json_parse<TK_I32>, pblocks, 256, st, a); break;
-        default:           TK_LAUNCH_PDL(k_json_parse<TK_I64>, pblocks, 256, st, a); break;
+    // the variant is the caller's choice (tk_ctx_set_json_wide: the Python engine samples the payload)
+    if (ctx->json_wide) {
+        switch (dtype) {
+            case TK_DTYPE_F32: TK_LAUNCH_PDL((k_json_parse<TK_F32, true>), pblocks, 256, st, a); break;
+            case TK_DTYPE_F64: TK_LAUNCH_PDL((k_json_parse<TK_F64, true>), pblocks, 256, st, a); break;
+            case TK_DTYPE_I32: TK_LAUNCH_PDL((k_json_parse<TK_I32, true>), pblocks, 256, st, a); break;
+            default:           TK_LAUNCH_PDL((k_json_parse<TK_I64, true>), pblocks, 256, st, a); break;
+        }
+    } else {
+        switch (dtype) {
+            case TK_DTYPE_F32: TK_LAUNCH_PDL((k_json_parse<TK_F32, false>), pblocks, 256, st, a); break;
+            case TK_DTYPE_F64: TK_LAUNCH_PDL((k_json_parse<TK_F64, false>), pblocks, 256, st, a); break;
+            case TK_DTYPE_I32: TK_LAUNCH_PDL((k_json_parse<TK_I32, false>), pblocks, 256, st, a); break;
+            default:           TK_LAUNCH_PDL((k_json_parse<TK_I64, false>), pblocks, 256, st, a); break;
+        }
     }
     return 0;
 }

@@ -129,13 +129,19 @@ TK_HD bool tk_json_object_fast(const Src& src, const R& rd, uint32_t lo, uint32_
             const uint32_t stop_at = tk_of_first(tk_of_eq_mask(W, 0x2C2C2C2Cu) | tk_of_eq_mask(W, 0x7D7D7D7Du));
             if (stop_at == 0u || stop_at >= TK_OF_WIN - 1u) return false;
             ve = vb + stop_at;
-            if (ve < lo + TK_FL_WIN) return false;                             // the lane reads 20 bytes in front of the end
+            // (the lane reads 20 bytes in front of the number's end, or of its mantissa's)
+            if (ve < lo + TK_FL_WIN + 5u) return false;
             uint64_t w;
             uint32_t K, dot, neg;
-            if (!tk_fl_scan(src, vb, ve, tb, &w, &K, &dot, &neg)) return false;
+            T v;
+            if (tk_fl_scan(src, vb, ve, tb, &w, &K, &dot, &neg)) {
+                if (f >= 0 && !tk_fl_value<KIND>(w, K, dot, neg, tb, &v)) return false;
+            } else {
+                const tk_fl_num num = tk_fl_scan_long(src, vb, ve);              // "0.00…", exponents
+                if (!num.ok) return false;
+                if (f >= 0 && !tk_fl_value_long<KIND>(num, &v)) return false;
+            }
             if (f >= 0) {
-                T v;
-                if (!tk_fl_value<KIND>(w, K, dot, neg, tb, &v)) return false;
                 row[f] = v;
                 found |= 1ull << f;
                 expect = (uint32_t)f + 1u == ft.n ? 0u : (uint32_t)f + 1u;

@@ -90,6 +90,12 @@ extern "C" int tk_ctx_set_json_fused(tk_ctx* ctx, int enabled) {
     return 0;
 }
 
+extern "C" int tk_ctx_set_json_wide(tk_ctx* ctx, int enabled) {
+    TK_REQUIRE(ctx, "null context");
+    ctx->json_wide = enabled ? 1 : 0;
+    return 0;
+}
+
 extern "C" int tk_ctx_set_timing(tk_ctx* ctx, int enabled) {
     TK_REQUIRE(ctx, "null context");
     ctx->timing = enabled ? 1 : 0;

@@ -150,6 +150,13 @@ class SlotEngine:
         #: chain (scan, plan, parse): an independent decomposition of the same contract, used as a
         #: cross-check and for comparison runs (``set_json_fused``)
         self.json_fused = bool(int(os.environ.get("TK_JSON_FUSED", "0") or 0))
+        #: variant of the JSON parse kernel (csrc/tk_json_kernels.cu): None = chosen from a sample of
+        #: the payload (``_choose_json_variant``), True / False = fixed (TK_JSON_WIDE=1 / 0)
+        _w = os.environ.get("TK_JSON_WIDE")
+        self.json_wide_fixed = None if _w in (None, "") else bool(int(_w))
+        self.json_wide = bool(self.json_wide_fixed)
+        self._variant_checks = 0
+        self._slot_payload = {}              # slot -> payload bytes in its pinned buffer (not for raw submissions)
         try:
             cores = len(os.sched_getaffinity(0))
         except AttributeError:  # pragma: no cover
@@ -242,7 +249,36 @@ class SlotEngine:
         return int(after.value)
 
     def submit(self, slot: int, n: int, nbytes: int):
+        self._slot_payload[slot] = nbytes
         _native.check(self.lib.tk_slot_submit(self.ctx, slot, n, nbytes))
+
+    def set_json_wide(self, enabled: bool):
+        """Parse kernel with the ``0.00...`` literals inline (True) or the leanest element loop (False)."""
+        self.json_wide = bool(enabled)
+        _native.check(self.lib.tk_ctx_set_json_wide(self.ctx, 1 if enabled else 0))
+
+    def _choose_json_variant(self, slot: int):
+        """Every 32nd slot: how many numbers of a 64 KB sample of the payload start with ``0.0`` or
+        carry an exponent?  The lean parse kernel leaves those to an out-of-line call (one element in a
+        hundred of them costs 15 %); above one in 300 the wide kernel runs, below one in 3 000 the lean
+        one.  Slots submitted as record batches hold no plain payload on the host: wide."""
+        if self.json_wide_fixed is not None or not isinstance(self.schema, JsonArray):
+            return
+        self._variant_checks += 1
+        if (self._variant_checks - 1) % 32:
+            return
+        nbytes = self._slot_payload.get(slot)
+        if nbytes is None:
+            want = True
+        else:
+            lo = max(0, nbytes // 2 - 32768)
+            sample = self._host_bytes[slot][lo:lo + 65536].tobytes()
+            elements = sample.count(b",") + 1
+            odd = (sample.count(b" 0.0") + sample.count(b"-0.0") + sample.count(b",0.0") + sample.count(b"[0.0")
+                   + sample.count(b"e-") + sample.count(b"e+"))
+            want = True if odd * 300 > elements else False if odd * 3000 < elements else self.json_wide
+        if want != self.json_wide:
+            self.set_json_wide(want)
 
     # ------------------------------------------------------------------ kernels
     def _allocate(self, n: int) -> SlotOutput:
@@ -330,6 +366,8 @@ class SlotEngine:
         lib, ctx, st = self.lib, self.ctx, self._stream()
         sc = self.schema
         is_json = isinstance(sc, JsonArray)
+        if is_json:
+            self._choose_json_variant(slot)
         with torch.cuda.device(self.device), torch.cuda.stream(self.stream):
             out = self._allocate(n)
             if timers is None:
@@ -407,6 +445,7 @@ class SlotEngine:
                 t.record_stream(cur)
 
     def assume_resident(self, slot: int, n: int, nbytes: int):
+        self._slot_payload[slot] = nbytes
         _native.check(self.lib.tk_slot_assume_resident(self.ctx, slot, n, nbytes))
 
     def device_views(self, slot: int):
@@ -505,6 +544,7 @@ class SlotEngine:
         device and the split kernels are asynchronous.  With ``host_ptrs`` (one address per blob)
         the bytes are not in the slot's buffer but wherever the consumer keeps them, and go to the
         device straight from there (``tk_slot_submit_recordbatches_ext``)."""
+        self._slot_payload.pop(slot, None)
         arr = (_native.TkBlob * max(len(blobs), 1))()
         for k, (start, length, part, fetch_offset, delta) in enumerate(blobs):
             b = arr[k]

@@ -9,8 +9,10 @@
 // (tests/native, differential test against zlib).  Host+device code (TK_HD).
 // Huffman decoding is canonical: per code length the number of codes and the symbols in code
 // order.  Codes of up to TK_INF_LIT_FAST / TK_INF_DIST_FAST bits are found with one lookup of the
-// next bits in a table of (symbol << 4 | length); longer ones are walked one bit at a time until
-// they fall into the range of their length.
+// next bits in a table; longer ones are walked one bit at a time until they fall into the range of
+// their length.  The tables of the literal / length and the distance code hold what the symbol
+// means (tk_inf_lit_entry, tk_inf_dist_entry: the literal, or the baseline and the number of extra
+// bits), so that a match costs two table lookups and no further ones.
 #pragma once
 #include <string.h>
 #include "tk_number.cuh"      // TK_HD
@@ -18,7 +20,9 @@
 enum { TK_INF_MATCH = 0, TK_INF_DONE = 1, TK_INF_ERROR = 2, TK_INF_BATCH = 3 };
 enum { TK_INF_HEADER = 0, TK_INF_CODES = 1, TK_INF_END = 2 };
 
-#define TK_INF_LIT_FAST 11
+#ifndef TK_INF_LIT_FAST
+#define TK_INF_LIT_FAST 10
+#endif
 #define TK_INF_DIST_FAST 9
 // Matches whose copy is left to the caller (tk_inflate_next with a batch): destination, length and
 // distance of each; the literals around them are already in place.  The copies may run side by side
@@ -57,11 +61,17 @@ TK_HD uint32_t tk_inf_dist_code(int c) {
 #endif
 }
 
+// Where the bit-by-bit walk through a canonical code stands after `len` bits that matched no code:
+// the walk for a code the table of `len` index bits does not hold starts there.
+struct tk_huff_walk { uint32_t len, first, index; };
+
 struct tk_inflate_tables {
     uint16_t lit_count[16], lit_symbol[288];
     uint16_t dist_count[16], dist_symbol[32];
     uint16_t lengths[320];         // scratch: code lengths of a dynamic block
-    uint16_t lit_fast[1 << TK_INF_LIT_FAST], dist_fast[1 << TK_INF_DIST_FAST];   // 0: longer code
+    uint32_t lit_fast[1 << TK_INF_LIT_FAST], dist_fast[1 << TK_INF_DIST_FAST];   // entries (below); 0: longer code
+    tk_huff_walk lit_walk, dist_walk;               // where the walk for a longer code starts
+    uint16_t code_fast[128];       // the code of the code lengths (dynamic block header): symbol << 4 | length
     tk_inflate_batch batch;
 };
 
@@ -74,22 +84,28 @@ struct tk_inflate_state {
     uint32_t nb;                   // matches waiting in the caller's batch
 };
 
-// Brings the buffer to at least 33 bits with one aligned 4-byte load (every field group of the
-// format needs at most 32: see the callers).  Past the end of the input zeros are fed; the position
-// check (tk_inf_consumed) catches a stream that used them.
-TK_HD void tk_inf_refill(tk_inflate_state& s) {
-    if (s.cnt > 32) return;
+// The 4 input bytes at pos (4-byte aligned); zeros behind the end of the input.
+TK_HD uint32_t tk_inf_word(const tk_inflate_state& s, uint32_t pos) {
     uint32_t w = 0;
-    if (s.pos < s.end && s.end - s.pos >= 4u) {
+    if (pos < s.end && s.end - pos >= 4u) {
 #if defined(__CUDA_ARCH__)
-        w = *reinterpret_cast<const uint32_t*>(s.in + s.pos);      // aligned: tk_inflate_init
+        w = *reinterpret_cast<const uint32_t*>(s.in + pos);        // aligned: tk_inflate_init
 #else
-        memcpy(&w, s.in + s.pos, 4);
+        memcpy(&w, s.in + pos, 4);
 #endif
     } else {
         for (uint32_t k = 0; k < 4; ++k)
-            if (s.pos + k < s.end) w |= (uint32_t)s.in[s.pos + k] << (8 * k);
+            if (pos + k < s.end) w |= (uint32_t)s.in[pos + k] << (8 * k);
     }
+    return w;
+}
+// Brings the buffer to at least 33 bits with one aligned 4-byte word (every field group of the
+// format needs at most 32: see the callers).  Past the end of the input zeros are fed; the position
+// check (tk_inf_consumed) catches a stream that used them.  (Loading the word one refill ahead,
+// with or without a prefetch of the line behind it, made the device decoder slower.)
+TK_HD void tk_inf_refill(tk_inflate_state& s) {
+    if (s.cnt > 32) return;
+    const uint32_t w = tk_inf_word(s, s.pos);
     s.pos += 4;
     s.buf |= (uint64_t)w << s.cnt;
     s.cnt += 32;
@@ -148,18 +164,71 @@ TK_HD void tk_huff_fast(uint16_t* fast, int fast_bits, const uint16_t* count, co
     }
 }
 
-// Next symbol (the buffer holds at least 15 bits), -1 if the bits are no code.
-TK_HD int tk_huff_decode(tk_inflate_state& s, const uint16_t* count, const uint16_t* symbol, const uint16_t* fast,
-                         int fast_bits) {
-    const uint32_t e = fast[(uint32_t)s.buf & ((1u << fast_bits) - 1u)];
-    if (e) {
-        s.buf >>= (e & 15u);
-        s.cnt -= (int)(e & 15u);
-        return (int)(e >> 4);
+// Table entries of the literal / length code and of the distance code:
+//   bits 0-3    length of the code (0 in an entry made for a symbol the bit-by-bit walk found)
+//   bits 4-7    number of extra bits that follow the code
+//   bits 8-9    TK_INF_E_LITERAL / _MATCH (length or distance) / _END (end of block) / _BAD (a
+//               symbol the format does not define, or no symbol at all)
+//   bits 16-31  the literal, or the baseline of the length / distance
+enum { TK_INF_E_LITERAL = 0u << 8, TK_INF_E_MATCH = 1u << 8, TK_INF_E_END = 2u << 8, TK_INF_E_BAD = 3u << 8, TK_INF_E_KIND = 3u << 8 };
+TK_HD uint32_t tk_inf_lit_entry(int sym, uint32_t l) {
+    if (sym < 0 || sym > 285) return TK_INF_E_BAD | l;
+    if (sym < 256) return TK_INF_E_LITERAL | l | ((uint32_t)sym << 16);
+    if (sym == 256) return TK_INF_E_END | l;
+    const uint32_t lc = tk_inf_len_code(sym - 257);
+    return TK_INF_E_MATCH | l | ((lc & 15u) << 4) | ((lc >> 4) << 16);
+}
+TK_HD uint32_t tk_inf_dist_entry(int sym, uint32_t l) {
+    if (sym < 0 || sym > 29) return TK_INF_E_BAD | l;
+    const uint32_t dc = tk_inf_dist_code(sym);
+    return TK_INF_E_MATCH | l | ((dc & 15u) << 4) | ((dc >> 4) << 16);
+}
+// Like tk_huff_fast, with such entries (DIST: of the distance code).
+template <bool DIST>
+TK_HD void tk_huff_fast_entries(uint32_t* fast, int fast_bits, const uint16_t* count, const uint16_t* length, int n) {
+    uint32_t next[16];
+    next[1] = 0;
+    for (int l = 1; l < 15; ++l) next[l + 1] = (next[l] + count[l]) << 1;
+    for (int k = 0; k < (1 << fast_bits); ++k) fast[k] = 0;
+    for (int i = 0; i < n; ++i) {
+        const int l = length[i];
+        if (!l) continue;
+        const uint32_t code = next[l]++;
+        if (l > fast_bits) continue;
+        uint32_t rev = 0;
+        for (int b = 0; b < l; ++b) rev |= ((code >> b) & 1u) << (l - 1 - b);
+        const uint32_t e = DIST ? tk_inf_dist_entry(i, (uint32_t)l) : tk_inf_lit_entry(i, (uint32_t)l);
+        for (uint32_t k = rev; k < (1u << fast_bits); k += 1u << l) fast[k] = e;
     }
+}
+
+TK_HD tk_huff_walk tk_huff_walk_from(const uint16_t* count, int len) {
+    tk_huff_walk w;
+    w.len = (uint32_t)len; w.first = 0; w.index = 0;
+    for (int l = 1; l <= len; ++l) {
+        w.index += count[l];
+        w.first = (w.first + count[l]) << 1;
+    }
+    return w;
+}
+TK_HD uint32_t tk_inf_reverse(uint32_t bits, uint32_t n) {         // the low n bits, first one highest (n <= 15)
+#if defined(__CUDA_ARCH__)
+    return n ? __brev(bits) >> (32u - n) : 0u;
+#else
+    uint32_t r = 0;
+    for (uint32_t b = 0; b < n; ++b) r |= ((bits >> b) & 1u) << (n - 1u - b);
+    return r;
+#endif
+}
+
+// Next symbol of a code the table does not hold: bit by bit through the canonical code, from
+// where the table's index bits end (`from`; {0, 0, 0}: from the first bit); -1 if the bits are no
+// code.  The buffer holds at least 15 bits.
+TK_HD int tk_huff_decode_slow(tk_inflate_state& s, const uint16_t* count, const uint16_t* symbol, const tk_huff_walk& from) {
     uint32_t bits = (uint32_t)s.buf;
-    int code = 0, first = 0, index = 0;
-    for (int len = 1; len < 16; ++len) {
+    int code = (int)(tk_inf_reverse(bits, from.len) << 1), first = (int)from.first, index = (int)from.index;
+    bits >>= from.len;
+    for (int len = (int)from.len + 1; len < 16; ++len) {
         code |= (int)(bits & 1u);
         bits >>= 1;
         const int c = count[len];
@@ -175,13 +244,28 @@ TK_HD int tk_huff_decode(tk_inflate_state& s, const uint16_t* count, const uint1
     return -1;
 }
 
+// Next symbol (the buffer holds at least 15 bits), -1 if the bits are no code.
+TK_HD int tk_huff_decode(tk_inflate_state& s, const uint16_t* count, const uint16_t* symbol, const uint16_t* fast,
+                         int fast_bits) {
+    const uint32_t e = fast[(uint32_t)s.buf & ((1u << fast_bits) - 1u)];
+    if (e) {
+        s.buf >>= (e & 15u);
+        s.cnt -= (int)(e & 15u);
+        return (int)(e >> 4);
+    }
+    const tk_huff_walk from = {0u, 0u, 0u};
+    return tk_huff_decode_slow(s, count, symbol, from);
+}
+
 TK_HD bool tk_inf_fixed_tables(tk_inflate_tables& tb) {
     for (int i = 0; i < 288; ++i) tb.lengths[i] = (uint16_t)(i < 144 ? 8 : i < 256 ? 9 : i < 280 ? 7 : 8);
     tk_huff_build(tb.lit_count, tb.lit_symbol, tb.lengths, 288);
-    tk_huff_fast(tb.lit_fast, TK_INF_LIT_FAST, tb.lit_count, tb.lengths, 288);
+    tk_huff_fast_entries<false>(tb.lit_fast, TK_INF_LIT_FAST, tb.lit_count, tb.lengths, 288);
+    tb.lit_walk = tk_huff_walk_from(tb.lit_count, TK_INF_LIT_FAST);
     for (int i = 0; i < 30; ++i) tb.lengths[i] = 5;
     tk_huff_build(tb.dist_count, tb.dist_symbol, tb.lengths, 30);
-    tk_huff_fast(tb.dist_fast, TK_INF_DIST_FAST, tb.dist_count, tb.lengths, 30);
+    tk_huff_fast_entries<true>(tb.dist_fast, TK_INF_DIST_FAST, tb.dist_count, tb.lengths, 30);
+    tb.dist_walk = tk_huff_walk_from(tb.dist_count, TK_INF_DIST_FAST);
     return true;
 }
 
@@ -197,11 +281,11 @@ TK_HD bool tk_inf_dynamic_tables(tk_inflate_state& s, tk_inflate_tables& tb) {
     }
     // the code of the code lengths lives in the literal table for the moment (codes of <= 7 bits)
     if (tk_huff_build(tb.lit_count, tb.lit_symbol, tb.lengths, 19) != 0) return false;      // must be complete
-    tk_huff_fast(tb.dist_fast, 7, tb.lit_count, tb.lengths, 19);
+    tk_huff_fast(tb.code_fast, 7, tb.lit_count, tb.lengths, 19);
     int i = 0;
     while (i < nlen + ndist) {
         tk_inf_refill(s);
-        const int sym = tk_huff_decode(s, tb.lit_count, tb.lit_symbol, tb.dist_fast, 7);
+        const int sym = tk_huff_decode(s, tb.lit_count, tb.lit_symbol, tb.code_fast, 7);
         if (sym < 0) return false;
         if (sym < 16) { tb.lengths[i++] = (uint16_t)sym; continue; }
         int rep, val = 0;
@@ -223,10 +307,12 @@ TK_HD bool tk_inf_dynamic_tables(tk_inflate_state& s, tk_inflate_tables& tb) {
     // literal build reads lengths[0, nlen) which must stay intact: build dist from its own range)
     int err = tk_huff_build(tb.dist_count, tb.dist_symbol, tb.lengths + nlen, ndist);
     if (err && (err < 0 || ndist != tb.dist_count[0] + tb.dist_count[1])) return false;   // incomplete: only a single 1-bit code
-    tk_huff_fast(tb.dist_fast, TK_INF_DIST_FAST, tb.dist_count, tb.lengths + nlen, ndist);
+    tk_huff_fast_entries<true>(tb.dist_fast, TK_INF_DIST_FAST, tb.dist_count, tb.lengths + nlen, ndist);
+    tb.dist_walk = tk_huff_walk_from(tb.dist_count, TK_INF_DIST_FAST);
     err = tk_huff_build(tb.lit_count, tb.lit_symbol, tb.lengths, nlen);
     if (err && (err < 0 || nlen != tb.lit_count[0] + tb.lit_count[1])) return false;
-    tk_huff_fast(tb.lit_fast, TK_INF_LIT_FAST, tb.lit_count, tb.lengths, nlen);
+    tk_huff_fast_entries<false>(tb.lit_fast, TK_INF_LIT_FAST, tb.lit_count, tb.lengths, nlen);
+    tb.lit_walk = tk_huff_walk_from(tb.lit_count, TK_INF_LIT_FAST);
     return true;
 }
 
@@ -272,32 +358,42 @@ TK_HD int tk_inflate_next(tk_inflate_state& s, tk_inflate_tables& tb, uint8_t* o
             tk_inf_refill(s);                                   // >= 33 bits: literal/length code 15 + 5 extra
             // (the input position is only checked once the input is all loaded)
             bool bad = s.pos > s.end && tk_inf_consumed(s) > s.end;
-            int sym = tk_huff_decode(s, tb.lit_count, tb.lit_symbol, tb.lit_fast, TK_INF_LIT_FAST);
-            if (sym < 256) {                                    // a literal (or no code at all)
-                if (bad | (sym < 0) | (op >= cap)) return TK_INF_ERROR;
-                out[op++] = (uint8_t)sym;
+            uint32_t e = tb.lit_fast[(uint32_t)s.buf & ((1u << TK_INF_LIT_FAST) - 1u)];
+            if (e) {
+                s.buf >>= (e & 15u);
+                s.cnt -= (int)(e & 15u);
+            } else {
+                e = tk_inf_lit_entry(tk_huff_decode_slow(s, tb.lit_count, tb.lit_symbol, tb.lit_walk), 0u);
+            }
+            const uint32_t kind = e & TK_INF_E_KIND;
+            if (kind == TK_INF_E_LITERAL) {
+                if (bad | (op >= cap)) return TK_INF_ERROR;
+                out[op++] = (uint8_t)(e >> 16);
                 continue;
             }
-            if (sym == 256) {
+            if (kind == TK_INF_E_END) {
                 if (bad) return TK_INF_ERROR;
                 s.mode = TK_INF_HEADER;
                 break;
             }
-            sym -= 257;
-            bad |= sym >= 29;
-            const uint32_t lc = tk_inf_len_code(sym < 29 ? sym : 28);
-            const uint32_t len = (lc >> 4) + tk_inf_bits(s, (int)(lc & 15u));          // 0..5 extra bits
+            bad |= kind == TK_INF_E_BAD;
+            const uint32_t len = (e >> 16) + tk_inf_bits(s, (int)((e >> 4) & 15u));    // 0..5 extra bits
             tk_inf_refill(s);                                   // distance code 15 + 13 extra
-            const int dsym = tk_huff_decode(s, tb.dist_count, tb.dist_symbol, tb.dist_fast, TK_INF_DIST_FAST);
-            bad |= (dsym < 0) | (dsym >= 30);
-            const uint32_t dc = tk_inf_dist_code((uint32_t)dsym < 30u ? dsym : 0);
-            const uint32_t dist = (dc >> 4) + tk_inf_bits(s, (int)(dc & 15u));         // 0..13 extra bits
+            uint32_t d = tb.dist_fast[(uint32_t)s.buf & ((1u << TK_INF_DIST_FAST) - 1u)];
+            if (d) {
+                s.buf >>= (d & 15u);
+                s.cnt -= (int)(d & 15u);
+            } else {
+                d = tk_inf_dist_entry(tk_huff_decode_slow(s, tb.dist_count, tb.dist_symbol, tb.dist_walk), 0u);
+            }
+            bad |= (d & TK_INF_E_KIND) == TK_INF_E_BAD;
+            const uint32_t dist = (d >> 16) + tk_inf_bits(s, (int)((d >> 4) & 15u));   // 0..13 extra bits
             bad |= s.pos > s.end && tk_inf_consumed(s) > s.end;
             if (bad | (dist > op) | (len > cap - op)) return TK_INF_ERROR;
             if (batch) {
-                tk_inflate_match e;
-                e.dst = op; e.len = len; e.dist = dist; e.reserved = 0;
-                batch->m[s.nb++] = e;
+                tk_inflate_match m;
+                m.dst = op; m.len = len; m.dist = dist; m.reserved = 0;
+                batch->m[s.nb++] = m;
                 op += len;
                 if (s.nb == TK_INF_BATCH_MAX) return TK_INF_BATCH;
                 continue;

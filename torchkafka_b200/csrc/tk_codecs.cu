@@ -878,8 +878,9 @@ __global__ void __launch_bounds__(32 * SERIAL_WARPS) k_unit_size_zstd(const rb_a
 
 // One kernel per format: a DEFLATE unit needs 3.9 KB of tables, a zstd unit 10.8 KB, and the number of
 // units an SM works on at a time is what its shared memory divides into.
+// (zstd: eleven 2-warp blocks on an SM -- the tables are sized for that, the registers capped to it)
 template <bool ZSTD>
-__global__ void __launch_bounds__(32 * SERIAL_WARPS) k_unit_decode_serial(const rb_args a) {
+__global__ void __launch_bounds__(32 * SERIAL_WARPS, ZSTD ? 11 : 1) k_unit_decode_serial(const rb_args a) {
     __shared__ typename std::conditional<ZSTD, tk_zstd_tables, tk_inflate_tables>::type tables[SERIAL_WARPS];
     __shared__ tk_zstd_event events[ZSTD ? SERIAL_WARPS : 1];
     const uint32_t lane = threadIdx.x & 31;

@@ -14,6 +14,7 @@
 // are not decoded: the events then only carry the sizes (the size pass; Kafka's Java client
 // writes frames without a content size).  Host+device code (TK_HD).
 #pragma once
+#include <stddef.h>
 #include <string.h>
 #include "tk_number.cuh"      // TK_HD
 
@@ -64,15 +65,22 @@ TK_HD uint32_t tk_zs_ml_code(uint32_t c) {
 #endif
 }
 
+// One decoder's tables.  Their size decides how many payloads an SM decodes side by side (shared
+// memory), so what is dead when something else is alive shares its place:
+//  * the FSE table of the Huffman weights (tk_zstd_wt: 64 entries) lives at the head of `huf`, which
+//    is written only after the weights are decoded;
+//  * the batch of decoded sequences (tk_zstd_batch_of) lives in the scratch of the table builds.
+#define TK_ZS_MAX_SYMBOLS 64       // symbols of a table description: 36 / 53 / 32 for sequences, weights 0..11
 struct tk_zstd_tables {
-    tk_fse_entry ll[512], ml[512], of[256], wt[64];   // sequences (accuracy <= 9, 9, 8), Huffman weights (<= 6)
+    tk_fse_entry ll[512], ml[512], of[256];   // sequences (accuracy <= 9, 9, 8)
     uint16_t huf[2048];            // literals: symbol | code length << 8, indexed by the next huf_log bits
-    // scratch of the table builds (1 KiB, word aligned); between the builds of two blocks it holds
-    // the batch of decoded sequences (tk_zstd_batch, tk_zstd_batch_of)
-    int16_t  norm[256];            // normalised counts of a table description
-    uint16_t desc[256];            // per-symbol state counter of the table build
+    // scratch of the table builds (528 bytes, 16-byte aligned)
+    int16_t  norm[TK_ZS_MAX_SYMBOLS];   // normalised counts of a table description
+    uint16_t desc[TK_ZS_MAX_SYMBOLS];   // per-symbol state counter of the table build
     uint8_t  weights[256];
+    uint8_t  scratch_tail[16];
 };
+TK_HD tk_fse_entry* tk_zstd_wt(tk_zstd_tables& tb) { return reinterpret_cast<tk_fse_entry*>(tb.huf); }
 
 TK_HD int tk_zs_highbit(uint32_t x) {                  // index of the highest set bit, x != 0
 #if defined(__CUDA_ARCH__)
@@ -247,8 +255,11 @@ TK_HD bool tk_fse_build(tk_fse_entry* table, int log, const int16_t* norm, int n
 TK_HD int tk_huf_fse_weights(const uint8_t* in, uint32_t lo, uint32_t hi, tk_zstd_tables& tb) {
     int log, nsym;
     uint32_t body;
-    if (!tk_fse_read_norm(in, lo, hi, 6, 256, tb.norm, &log, &nsym, &body)) return -1;
-    if (!tk_fse_build(tb.wt, log, tb.norm, nsym, tb.desc)) return -1;
+    // (weights are 0..11: a description that gives a value of TK_ZS_MAX_SYMBOLS or more a probability is
+    // refused here, whether or not the stream ever produces it)
+    if (!tk_fse_read_norm(in, lo, hi, 6, TK_ZS_MAX_SYMBOLS, tb.norm, &log, &nsym, &body)) return -1;
+    tk_fse_entry* wt = tk_zstd_wt(tb);                   // at the head of tb.huf, which is built from the weights afterwards
+    if (!tk_fse_build(wt, log, tb.norm, nsym, tb.desc)) return -1;
     int32_t bitpos;
     if (!tk_zs_bwd_init(in, body, hi, &bitpos)) return -1;
     uint32_t s1 = tk_zs_bwd_read(in, body, hi, &bitpos, log);
@@ -257,12 +268,12 @@ TK_HD int tk_huf_fse_weights(const uint8_t* in, uint32_t lo, uint32_t hi, tk_zst
     int n = 0;
     for (;;) {                                           // at most 255 explicit weights (one more is implied)
         if (n > 252) return -1;
-        tb.weights[n++] = tb.wt[s1].symbol;
-        s1 = tb.wt[s1].base + tk_zs_bwd_read(in, body, hi, &bitpos, tb.wt[s1].nbits);
-        if (bitpos < 0) { tb.weights[n++] = tb.wt[s2].symbol; break; }
-        tb.weights[n++] = tb.wt[s2].symbol;
-        s2 = tb.wt[s2].base + tk_zs_bwd_read(in, body, hi, &bitpos, tb.wt[s2].nbits);
-        if (bitpos < 0) { tb.weights[n++] = tb.wt[s1].symbol; break; }
+        tb.weights[n++] = wt[s1].symbol;
+        s1 = wt[s1].base + tk_zs_bwd_read(in, body, hi, &bitpos, wt[s1].nbits);
+        if (bitpos < 0) { tb.weights[n++] = wt[s2].symbol; break; }
+        tb.weights[n++] = wt[s2].symbol;
+        s2 = wt[s2].base + tk_zs_bwd_read(in, body, hi, &bitpos, wt[s2].nbits);
+        if (bitpos < 0) { tb.weights[n++] = wt[s1].symbol; break; }
     }
     return n;
 }
@@ -682,7 +693,8 @@ struct tk_zstd_batch {
 
 // The batch's place inside the tables' scratch (dead while a block's sequences are decoded).
 TK_HD tk_zstd_batch* tk_zstd_batch_of(tk_zstd_tables& tb) {
-    static_assert(sizeof(tk_zstd_batch) <= sizeof(tb.norm) + sizeof(tb.desc), "the batch must fit the scratch");
+    static_assert(sizeof(tk_zstd_batch) <= sizeof(tb.norm) + sizeof(tb.desc) + sizeof(tb.weights) + sizeof(tb.scratch_tail), "the batch must fit the scratch");
+    static_assert(offsetof(tk_zstd_tables, norm) % 16 == 0, "the batch is read with 16-byte loads");
     return reinterpret_cast<tk_zstd_batch*>(tb.norm);
 }
 
